@@ -1,0 +1,236 @@
+"""Seeded synthetic RPGGs and reads (SURVEY.md §8(d) S2/S3 shapes) -- tests/bench workload plumbing.
+
+build_rpgg() restates what the reference's `fa2kmers -k K -fsi F -fso F` (src/fa2kmers.cpp:131-167,
+buildNuKmers src/aQueryFasta_thread.h:185-213) + `ktools serialize` (src/kmertools.cpp:221-345,
+readKmerIndex src/kmerIO.hpp:47-78) produce from haplotype sequences, and writes the reference's file
+formats directly; tests/test_synth.py checks it against the real tools.
+"""
+import os
+
+import numpy as np
+
+from . import rpgg_io
+
+_CODE = np.full(256, 255, np.uint8)
+for _i, _c in enumerate(b"ACGT"):
+    _CODE[_c] = _i
+_ASCII = np.frombuffer(b"ACGT", np.uint8)
+_COMP = np.zeros(256, np.uint8)
+for _a, _b in zip(b"ACGTN", b"TGCAN"):
+    _COMP[_a] = _b
+
+
+def canonical_kmers(codes, k):
+    """codes: u8 array of 0..3 -> canonical k-mers of every window (u64[len-k+1])."""
+    n = len(codes) - k + 1
+    if n <= 0:
+        return np.zeros(0, np.uint64)
+    f = np.zeros(n, np.uint64)
+    r = np.zeros(n, np.uint64)
+    c = codes.astype(np.uint64)
+    for j in range(k):
+        w = c[j:j + n]
+        f |= w << np.uint64(2 * (k - 1 - j))
+        r |= (np.uint64(3) - w) << np.uint64(2 * j)
+    return np.minimum(f, r)
+
+
+def make_loci(nloci, seed=20261104, nhap=8, flank=700, share_frac=0.05, share_len=200, tr_median=300,
+              tr_min=50, tr_max=5000, sub_rate=0.02):
+    """Returns haps[locus][hap] = ASCII bytes (flank + TR + flank). A fraction of loci copy a segment
+    of another locus' TR/flank so that multi-locus k-mers (the vv path) occur."""
+    loci = []
+    for l in range(nloci):
+        rng = np.random.default_rng([seed, l])
+        lf = rng.integers(0, 4, flank, dtype=np.uint8)
+        rf = rng.integers(0, 4, flank, dtype=np.uint8)
+        mlen = int(rng.integers(6, 61))
+        motif = rng.integers(0, 4, mlen, dtype=np.uint8)
+        haps = []
+        for h in range(nhap):
+            trlen = int(np.clip(rng.lognormal(np.log(tr_median), 0.6), tr_min, tr_max))
+            ncopy = max(1, trlen // mlen)
+            tr = np.tile(motif, ncopy)
+            mut = rng.random(len(tr)) < sub_rate
+            tr = np.where(mut, (tr + rng.integers(1, 4, len(tr), dtype=np.uint8)) % 4, tr).astype(np.uint8)
+            haps.append(np.concatenate([lf, tr, rf]))
+        loci.append(haps)
+    rng = np.random.default_rng([seed, 10 ** 9])
+    nshare = int(round(nloci * share_frac)) if nloci > 1 else 0
+    for _ in range(nshare):
+        a, b = rng.choice(nloci, 2, replace=False)
+        src = loci[b][0]
+        s0 = int(rng.integers(0, max(1, len(src) - share_len)))
+        seg = src[s0:s0 + share_len]
+        for h in range(nhap):
+            d = loci[a][h]
+            # drop the shared segment into the TR/flank boundary region of locus a
+            p0 = int(min(max(flank - share_len // 2, 0), len(d) - len(seg)))
+            d[p0:p0 + len(seg)] = seg
+    return [[_ASCII[h].tobytes() for h in haps] for haps in loci]
+
+
+def write_hap_fastas(loci, pref):
+    """One FASTA per haplotype, one record per locus (fa2kmers input convention). Returns file names."""
+    nhap = len(loci[0])
+    fns = []
+    for h in range(nhap):
+        fn = f"{pref}.hap{h}.fa"
+        with open(fn, "wb") as f:
+            for l, haps in enumerate(loci):
+                f.write(b">locus%d.hap%d\n" % (l, h))
+                f.write(haps[h] + b"\n")
+        fns.append(fn)
+    return fns
+
+
+def locus_kmer_sets(haps, k, fsi, fso):
+    """(tr_kmers, fl_kmers) unique canonical k-mer arrays of one locus; fa2kmers.cpp:139-156."""
+    tr, fl = [], []
+    for s in haps:
+        codes = _CODE[np.frombuffer(s, np.uint8)]
+        assert codes.max() < 4, "synthetic haplotypes contain only ACGT"
+        km = canonical_kmers(codes, k)
+        n = len(s)
+        tr.append(km[fsi: n - k - fsi + 1])
+        if fso:
+            fl.append(km[fsi - fso: fsi])
+            fl.append(km[n - fsi - (k - 1): n - k - (fsi - fso) + 1])
+    tr = np.unique(np.concatenate(tr)) if tr else np.zeros(0, np.uint64)
+    fl = np.unique(np.concatenate(fl)) if fl else np.zeros(0, np.uint64)
+    return tr, fl
+
+
+def build_dbi(tr_n, tr_k, fl_n, fl_k):
+    """readKmerIndex over .tr.kmers then .fl.kmers (kio:47-78) + vv flattening (kmertools.cpp:243-258).
+    List order inside vv = order of first sighting: TR loci ascending, then flank-only loci ascending."""
+    tr_l = np.repeat(np.arange(len(tr_n), dtype=np.uint64), tr_n.astype(np.int64))
+    fl_l = np.repeat(np.arange(len(fl_n), dtype=np.uint64), fl_n.astype(np.int64))
+    km = np.concatenate([tr_k, fl_k])
+    lo = np.concatenate([tr_l, fl_l])
+    src = np.concatenate([np.zeros(len(tr_k), np.uint8), np.ones(len(fl_k), np.uint8)])
+    order = np.lexsort((lo, src, km))           # by k-mer, then TR before FL, then locus
+    km, lo, src = km[order], lo[order], src[order]
+    # drop (kmer, locus) duplicates (flank sighting of a pair already seen in TR)
+    pair_order = np.lexsort((src, lo, km))
+    km2, lo2 = km[pair_order], lo[pair_order]
+    first = np.ones(len(km2), bool)
+    first[1:] = (km2[1:] != km2[:-1]) | (lo2[1:] != lo2[:-1])
+    keep = np.zeros(len(km), bool)
+    keep[pair_order[first]] = True
+    km, lo = km[keep], lo[keep]
+    keys, start, cnt = np.unique(km, return_index=True, return_counts=True)
+    vals = np.zeros(len(keys), np.uint32)
+    single = cnt == 1
+    vals[single] = (lo[start[single]] << np.uint64(1)).astype(np.uint32)
+    vv = []
+    off = 0
+    multi = np.nonzero(~single)[0]
+    for i in multi:
+        n = int(cnt[i])
+        vals[i] = (off << 1) | 1
+        vv.append(n)
+        vv.extend(int(x) for x in lo[start[i]: start[i] + n])
+        off += n + 1
+    return keys.astype("<u8"), vals.astype("<u4"), np.array(vv, "<u4")
+
+
+def build_rpgg(loci, pref, k=21, fsi=700, fso=700, write_text=True):
+    """Writes PREF.tr.kmers, PREF.fl.kmers (text), PREF.kmers.dbi, PREF.fl.kdb, PREF.tre.kdb (valid, empty).
+    Returns the host index dict (tr order = file order)."""
+    trs, fls = zip(*[locus_kmer_sets(h, k, fsi, fso) for h in loci])
+    tr_n = np.array([len(t) for t in trs], "<u8")
+    fl_n = np.array([len(t) for t in fls], "<u8")
+    tr_k = np.concatenate(trs).astype("<u8") if len(trs) else np.zeros(0, "<u8")
+    fl_k = np.concatenate(fls).astype("<u8") if len(fls) else np.zeros(0, "<u8")
+    keys, vals, vv = build_dbi(tr_n, tr_k, fl_n, fl_k)
+    os.makedirs(os.path.dirname(os.path.abspath(pref)), exist_ok=True)
+    if write_text:
+        rpgg_io.write_kmers_text(pref + ".tr.kmers", tr_n, tr_k)
+        rpgg_io.write_kmers_text(pref + ".fl.kmers", fl_n, fl_k)
+    rpgg_io.write_dbi(pref + ".kmers.dbi", keys, vals, vv)
+    rpgg_io.write_kdb(pref + ".fl.kdb", fl_n, fl_k)
+    rpgg_io.write_kdb(pref + ".tre.kdb", np.zeros(len(tr_n), "<u8"), np.zeros(0, "<u8"))
+    return dict(nloci=len(tr_n), dbi_keys=keys, dbi_vals=vals, vv=vv, tr_n=tr_n, tr_kmers=tr_k, fl_n=fl_n, fl_kmers=fl_k)
+
+
+# --------------------------------------------------------------------------------------------
+# reads (small-scale numpy simulator for tests; bench.py uses the CUDA generator in csrc/synth.cu)
+# --------------------------------------------------------------------------------------------
+def revcomp(s):
+    return _COMP[np.frombuffer(s, np.uint8)][::-1].tobytes()
+
+
+def sim_pair(hap, rng, rlen=150, flen=500):
+    """error-free pair like src/sim_reads.cpp:74-104: forward read + reverse-complemented far end."""
+    beg = int(rng.integers(0, len(hap) - flen + 1))
+    return hap[beg:beg + rlen], revcomp(hap[beg + flen - rlen: beg + flen])
+
+
+def mutate(s, rng, rate):
+    a = np.frombuffer(s, np.uint8).copy()
+    m = rng.random(len(a)) < rate
+    a[m] = _ASCII[rng.integers(0, 4, int(m.sum()))]
+    return a.tobytes()
+
+
+def random_read(rng, rlen=150):
+    return _ASCII[rng.integers(0, 4, rlen)].tobytes()
+
+
+def sim_reads(loci, npairs, seed=1, frac_locus=0.5, frac_chimeric=0.1, frac_border=0.1, frac_n=0.05,
+              frac_short=0.01, frac_lower=0.01, err=0.0, rlen=150):
+    """Mixed test workload: list of (title, mate_first, mate_second) in ARRIVAL order (/1 then /2).
+    Includes the trap cases of SURVEY.md F4: chimeric two-locus pairs (trap 5), corrupted tails,
+    N / lower-case bases (trap 1-2), short mates (trap 4), pure background."""
+    rng = np.random.default_rng(seed)
+    out = []
+    L = len(loci)
+    for i in range(npairs):
+        u = rng.random()
+        l = int(rng.integers(0, L))
+        hap = loci[l][int(rng.integers(0, len(loci[l])))]
+        if u < frac_locus:
+            a, b = sim_pair(hap, rng, rlen)
+            kind = "loc%d" % l
+        elif u < frac_locus + frac_chimeric and L > 1:
+            l2 = int((l + 1 + rng.integers(0, L - 1)) % L)
+            hap2 = loci[l2][int(rng.integers(0, len(loci[l2])))]
+            a1, b1 = sim_pair(hap, rng, rlen)
+            a2, b2 = sim_pair(hap2, rng, rlen)
+            c1, c2 = int(rng.integers(30, 121)), int(rng.integers(30, 121))
+            a, b = a1[:c1] + a2[c1:], b1[:c2] + b2[c2:]
+            kind = "chi%d_%d" % (l, l2)
+        elif u < frac_locus + frac_chimeric + frac_border:
+            a, b = sim_pair(hap, rng, rlen)
+            c1, c2 = int(rng.integers(40, 140)), int(rng.integers(40, 140))
+            a, b = a[:c1] + random_read(rng, rlen - c1), b[:c2] + random_read(rng, rlen - c2)
+            kind = "bor%d" % l
+        else:
+            a, b = random_read(rng, rlen), random_read(rng, rlen)
+            kind = "bg"
+        if err:
+            a, b = mutate(a, rng, err), mutate(b, rng, err)
+        v = rng.random()
+        if v < frac_n:
+            aa = bytearray(a)
+            for p in rng.integers(0, rlen, int(rng.integers(1, 4))):
+                aa[int(p)] = ord("N")
+            a = bytes(aa)
+            if rng.random() < 0.2:
+                b = b"N" * rlen
+        elif v < frac_n + frac_lower:
+            bb = bytearray(b)
+            p = int(rng.integers(0, rlen))
+            bb[p] = ord(chr(bb[p]).lower())
+            b = bytes(bb)
+        elif v < frac_n + frac_lower + frac_short:
+            a = a[: int(rng.integers(1, 90))]
+        out.append((">r%d.%s" % (i, kind), a, b))
+    return out
+
+
+def write_fasta(fn, reads):
+    with open(fn, "wb") as f:
+        for t, a, b in reads:
+            f.write(t.encode() + b"/1\n" + a + b"\n" + t.encode() + b"/2\n" + b + b"\n")

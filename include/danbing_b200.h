@@ -1,0 +1,238 @@
+/*
+ * danbing_b200.h -- C ABI of libdanbing_b200.so, the B200-native (sm_100a) implementation of the
+ * `danbing-tk align` hot path (read pair -> VNTR locus -> per-locus k-mer counts).
+ *
+ * The reference (ChaissonLab/danbing-tk @ 324930d) has no plugin / FFI interface for this path: it
+ * sits behind a process boundary (argv + files + stdin/stdout, src/aQueryFasta_thread.cpp:2286-2660).
+ * The drop-in is therefore (1) the `danbing-tk` CLI built from host/ on top of this ABI and (2) this
+ * ABI itself, which is what a maintainer's binding (cgo / JNI / ctypes / a patched CountWords) would
+ * call instead of the per-pair loop of CountWords (src/aQueryFasta_thread.cpp:2002-2249).
+ * INTEGRATION.md shows that binding.  Every entry point below cites the reference code it replaces;
+ * "cpp" = src/aQueryFasta_thread.cpp, "h" = src/aQueryFasta_thread.h, "bio" = src/binaryKmerIO.hpp,
+ * "kio" = src/kmerIO.hpp.
+ *
+ * Conventions: plain C, no exceptions, no C++/torch types.  Return 0 = OK, negative = error
+ * (dbt_strerror / dbt_last_error).  The caller owns every host pointer; a dbt_ctx owns all device
+ * memory, streams and events.  A context is driven by one host thread at a time; different
+ * contexts (GPUs) may be driven concurrently.  There is NO CPU fallback: without a CUDA device
+ * dbt_create fails with DBT_E_CUDA.
+ */
+#ifndef DANBING_B200_H_
+#define DANBING_B200_H_
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DBT_ABI_VERSION 1
+
+/* ---- error codes -------------------------------------------------------------------------- */
+#define DBT_OK            0
+#define DBT_E_CUDA       (-1)  /* CUDA runtime/driver error (message in dbt_last_error)         */
+#define DBT_E_NOMEM      (-2)  /* host or device allocation failed                             */
+#define DBT_E_BADARG     (-3)  /* NULL / out-of-range argument                                 */
+#define DBT_E_CAPACITY   (-4)  /* batch, read length or record buffer exceeds the context's     */
+#define DBT_E_STATE      (-5)  /* call order violated (e.g. submit before load_index)          */
+#define DBT_E_INDEX      (-6)  /* inconsistent RPGG index (tr/fl k-mer missing from kmers.dbi) */
+#define DBT_E_IO         (-7)  /* file missing/short (host loaders); the reference asserts or, */
+                               /* for .fl.kdb/.tre.kdb, reads garbage (h:681) -- we fail loudly */
+#define DBT_E_NCCL       (-8)  /* NCCL unavailable or a collective failed                      */
+
+/* ---- run flags (dbt_params.flags) ---------------------------------------------------------- */
+#define DBT_F_KAM        0x001u /* kam records wanted (reference default; `-ka` clears, cpp:2368) */
+#define DBT_F_QC         0x002u /* `-qc FILE` locus mask active (cpp:2381, 2059-2062)           */
+#define DBT_F_TRACE      0x004u /* test/diagnostic: emit a record for EVERY pair, not only kam   */
+#define DBT_F_THREADING  0x008u /* `-g/-gc/-gcc` (cpp:2360); dead at reference HEAD (cpp:2072)  */
+#define DBT_F_CORRECTION 0x010u /* `-gc` error-correcting threading                            */
+#define DBT_F_ALN        0x020u /* `-a`                                                        */
+#define DBT_F_ALN_MIN    0x040u /* `-ae`                                                       */
+
+/* ---- per-pair status (dbt_pair_record.status); order = the order of the exits in cpp:2035-2145 */
+#define DBT_ST_SHORT       0   /* a mate has no valid k-mer window            (cpp:2037)       */
+#define DBT_ST_SUBFILTERED 1   /* rejected by subfilter                       (cpp:2046)       */
+#define DBT_ST_KFILTERED   2   /* both mates removed by kfilter               (cpp:2054)       */
+#define DBT_ST_UNASSIGNED  3   /* countHit returned nloci                     (cpp:2058)       */
+#define DBT_ST_QCFILTERED  4   /* locus fails QC                              (cpp:2059)       */
+#define DBT_ST_ASGN_REMOVED 5  /* both mates removed by assignTRkmc           (cpp:2145)       */
+#define DBT_ST_COUNTED     6   /* counts accumulated, kam line written        (cpp:2146-2175)  */
+
+/* ---- counters (dbt_download / dbt_batch_result.counters); cpp:1820, 2617-2626 --------------- */
+enum {
+  DBT_C_NREADS = 0,            /* reads (2 per pair) submitted                                 */
+  DBT_C_NSHORT,                /* PAIRS skipped as short (cpp:2038 counts pairs)               */
+  DBT_C_NSUBFILTERED,          /* reads                                                        */
+  DBT_C_NKMERFILTERED,
+  DBT_C_NBAITFILTERED,
+  DBT_C_NQUALFILTERED,
+  DBT_C_NLOCUSASSIGNFILTERED,
+  DBT_C_NQCFILTERED,
+  DBT_C_NTHREADINGREADS,
+  DBT_C_NFEASIBLEREADS,
+  DBT_C_NASGNREADS,
+  DBT_C_NHASH0,                /* subfilter probe count, counted as cpp:176,182 do              */
+  DBT_C_NHASH1,                /* kfilter probe count, cpp:206,217                              */
+  DBT_C_NINC,                  /* TR k-mer occurrences incremented (= sum of counts delta)      */
+  DBT_C_NCANDIDATES,           /* pairs that reached kfilter                                    */
+  DBT_C_NRECORDS,              /* records emitted                                               */
+  DBT_N_COUNTERS = 16
+};
+
+typedef struct dbt_ctx dbt_ctx;
+
+/* Run parameters == the reference's globals/flags (cpp:25-34, 2336-2339, 2344-2429). */
+typedef struct {
+  int32_t  device;             /* CUDA device ordinal                                          */
+  uint32_t k;                  /* -k   ksize, 1..31 (cpp:2376)                                  */
+  uint32_t n_filter;           /* -kf INT1  N_FILTER  (cpp:2370); 0 disables subfilter          */
+  uint32_t nm_filter;          /* -kf INT2  NM_FILTER (cpp:2371); 0 disables subfilter          */
+  uint32_t cth;                /* -cth Cthreshold (cpp:2422)                                    */
+  uint32_t nm_tr;              /* -c   NM_TR (cpp:2374)                                         */
+  uint32_t max_nt;             /* MAX_NT, fixed 2 in the reference (cpp:31)                     */
+  uint32_t thread_cth;         /* -g/-gc INT1 (cpp:2363)                                        */
+  uint32_t max_ncorrection;    /* -gc INT2 (cpp:2364)                                           */
+  uint32_t flags;              /* DBT_F_*                                                       */
+  uint32_t max_read_len;       /* longest read a batch may contain (bases)                      */
+  uint32_t max_batch_pairs;    /* largest npairs of one dbt_submit                              */
+  uint32_t max_records;        /* record buffer capacity per slot; 0 = max_batch_pairs          */
+  float    table_load;         /* hash table load factor; 0 = default                           */
+  uint32_t bucket_slots;       /* 16-byte slots per probe bucket: 2 (32 B sector) or 4 or 8; 0 = default */
+  uint32_t reserved[3];
+} dbt_params;
+
+/*
+ * Host view of the RPGG index == the containers the reference builds at start-up (cpp:2465-2504):
+ *   dbi_keys/dbi_vals/vv : PREF.kmers.dbi  (readBinaryIndex, h:654-673; value encoding kio:59-74)
+ *   tr_n/tr_kmers        : PREF.tr.kmers   (readKmersWithZeroCount, h:469-480), per-locus sizes +
+ *                          keys ALREADY in the reference's output order (the libstdc++
+ *                          unordered_map iteration order of each locus map; dbt_host_load_index
+ *                          reproduces it) -- counts[] comes back in exactly this order
+ *   fl_n/fl_kmers        : PREF.fl.kdb     (readBinaryKmerSetDB, h:675-698)
+ *   qc                   : -qc FILE after `- '0'` (readQCFile, kio:111-120); NULL unless DBT_F_QC
+ * The caller may free everything once dbt_load_index returns.
+ */
+typedef struct {
+  uint64_t nloci;
+  uint64_t nk_dbi;  const uint64_t* dbi_keys;  const uint32_t* dbi_vals;
+  uint64_t nvv;     const uint32_t* vv;
+  const uint64_t* tr_n;   const uint64_t* tr_kmers;
+  const uint64_t* fl_n;   const uint64_t* fl_kmers;
+  const uint8_t*  qc;
+} dbt_index;
+
+#define DBT_LAYOUT_ASCII   0   /* concatenated ASCII read sequences + byte offsets               */
+#define DBT_LAYOUT_PACKED  1   /* output of dbt_pack_reads (2-bit bases + invalid mask, SoA)    */
+
+/*
+ * One batch of read pairs == seqs[] of one CountWords batch (cpp:1857, 1972-1974).
+ * Read 2i is the reference's "read 1" (seq1, the mate that ARRIVED SECOND), read 2i+1 its "read 2".
+ *   ASCII : bases = concatenated sequences, offsets[2*npairs+1] = byte offset of each read.
+ *   PACKED: bases = buffer filled by dbt_pack_reads for exactly this npairs; offsets = NULL.
+ * Host buffers should be pinned (dbt_host_alloc) for asynchronous copies; pageable works, slower.
+ */
+typedef struct {
+  uint64_t first_pair_index;   /* global index of pair 0 (only echoed into records)             */
+  uint64_t npairs;
+  int32_t  layout;
+  const uint8_t*  bases;
+  const uint64_t* offsets;
+} dbt_batch;
+
+/* per-mate part of a record == km_asgn_read_t (cpp:93-108) */
+typedef struct {
+  int16_t  si, ei, si_, ei_, ti;
+  int8_t   nt, bs;
+  uint8_t  flags;              /* bit0 kf, bit1 hf, bit2 bf, bit3 qf, bit4 af, bit5 rm          */
+  uint8_t  pad;
+  uint16_t nk;                 /* length of the annotation `as` (0 when the reference leaves it empty) */
+} dbt_mate_record;
+#define DBT_MF_KF 0x01
+#define DBT_MF_HF 0x02
+#define DBT_MF_BF 0x04
+#define DBT_MF_QF 0x08
+#define DBT_MF_AF 0x10
+#define DBT_MF_RM 0x20
+
+/*
+ * One record == one km_asgn_t / kam line (cpp:110-144, 1646-1681) plus trace fields.
+ * A record occupies dbt_record_stride(ctx) bytes: this 64-byte header, then the 2-bit k-mer
+ * annotation (`as`: 0 '*', 1 '.', 2 '=', cpp:122) of mate[0] and of mate[1], each
+ * dbt_record_as_stride(ctx) bytes, k-mer i in bits 2*(i%4) of byte i/4.
+ * mate[0] is the reference's r1 (read 2i), mate[1] its r2.
+ */
+typedef struct {
+  uint64_t pair_index;
+  uint32_t dst, dst0;          /* destLocus (nloci = unassigned), destLocus0 (cpp:2056)         */
+  uint32_t fc, rc;             /* top.fc / top.rc when voting stopped (nm1, nm2, cpp:437-438)   */
+  uint16_t nhash0, nhash1;     /* probes this pair added to nhash0 / nhash1                     */
+  uint8_t  status;             /* DBT_ST_*                                                      */
+  uint8_t  pad[3];
+  dbt_mate_record mate[2];
+} dbt_pair_record;
+
+typedef struct {
+  uint64_t n_records;          /* out */
+  uint64_t capacity;           /* in: records the buffer can hold                               */
+  uint8_t* records;            /* in: caller buffer, capacity * dbt_record_stride bytes (pinned) */
+  uint64_t counters[DBT_N_COUNTERS]; /* out: this batch's counter deltas                        */
+} dbt_batch_result;
+
+/* ---- lifecycle ----------------------------------------------------------------------------- */
+int  dbt_abi_version(void);
+int  dbt_device_count(void);                         /* <0 on error; 0 = no GPU                  */
+void dbt_default_params(dbt_params* p);              /* the reference's defaults (cpp:26-33, 2338) */
+int  dbt_create(dbt_ctx** out, const dbt_params* p); /* replaces Counts/Threads set-up, cpp:2509-2565 */
+void dbt_destroy(dbt_ctx*);
+const char* dbt_strerror(int code);
+const char* dbt_last_error(void);                    /* thread-local detail of the last failure  */
+
+/* Builds the device-resident index (replaces cpp:2484-2504 + the per-pair container lookups). */
+int  dbt_load_index(dbt_ctx*, const dbt_index*);
+
+/* ---- per batch (replaces the pair loop of CountWords, cpp:2002-2249) ------------------------ */
+int  dbt_upload (dbt_ctx*, const dbt_batch*, int slot);       /* async H2D (+ device 2-bit pack) */
+int  dbt_process(dbt_ctx*, int slot);                         /* async kernels on the uploaded slot */
+int  dbt_fetch  (dbt_ctx*, dbt_batch_result*, int slot);      /* async D2H of records + counters */
+int  dbt_submit (dbt_ctx*, const dbt_batch*, dbt_batch_result*, int slot); /* upload+process+fetch */
+int  dbt_wait   (dbt_ctx*, int slot);                         /* blocks; finalises dbt_batch_result */
+#define DBT_N_SLOTS 2
+
+/* ---- results (replaces dumpTRKmers/writeTRKmerSummary inputs, cpp:2631-2641) ---------------- */
+int  dbt_download(dbt_ctx*, uint64_t* trkmc /*[nk_tr]*/, uint64_t* kmc /*[nloci]*/,
+                  uint32_t* nmapread /*[nloci]*/, uint64_t counters[DBT_N_COUNTERS]);
+int  dbt_reset_counts(dbt_ctx*);
+uint64_t dbt_nk_tr(const dbt_ctx*);
+uint64_t dbt_nloci(const dbt_ctx*);
+uint32_t dbt_record_stride(const dbt_ctx*);
+uint32_t dbt_record_as_stride(const dbt_ctx*);
+
+/* ---- multi-GPU: one context per GPU, reads sharded, one sum-reduce at the end --------------- */
+#define DBT_NCCL_ID_BYTES 128
+int  dbt_nccl_unique_id(uint8_t id[DBT_NCCL_ID_BYTES]);
+int  dbt_comm_init(dbt_ctx*, int nranks, int rank, const uint8_t id[DBT_NCCL_ID_BYTES]);
+int  dbt_allreduce(dbt_ctx*);   /* in-place ncclAllReduce(sum) of counts, kmc, nmapread, counters */
+
+/* ---- measurement helpers (CUDA events on the context's own streams) ------------------------- */
+int  dbt_timer_start(dbt_ctx*, int slot);
+int  dbt_timer_stop (dbt_ctx*, int slot, float* ms);          /* synchronises the slot           */
+int  dbt_kernel_times(dbt_ctx*, int slot, float ms[8], uint32_t launches[8]); /* last dbt_process */
+uint64_t dbt_launch_count(const dbt_ctx*);                    /* kernels launched since create   */
+int  dbt_table_stats(const dbt_ctx*, uint64_t stats[8]);      /* buckets, slots, keys, overflowed, bytes... */
+int  dbt_random_gather_bench(int device, uint64_t table_bytes, uint32_t sector_bytes,
+                             uint64_t n_gathers, int iters, float* best_ms); /* R_rand roofline    */
+
+/* ---- host helpers --------------------------------------------------------------------------- */
+void* dbt_host_alloc(size_t bytes);                           /* pinned */
+void  dbt_host_free(void*);
+/* packed layout sizes for npairs reads of <= max_read_len bases */
+size_t dbt_packed_bytes(uint32_t max_read_len, uint64_t npairs);
+/* Multi-threaded host packer (north_star item 1). nthreads<=0: hardware concurrency. */
+int  dbt_pack_reads(uint32_t k, uint32_t max_read_len, uint64_t npairs, const uint8_t* ascii,
+                    const uint64_t* offsets, uint8_t* packed_out, int nthreads);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DANBING_B200_H_ */
