@@ -1,0 +1,697 @@
+// C ABI of libdanbing_b200.so (include/danbing_b200.h): context, device-resident index, batch
+// pipeline (upload -> subfilter -> compaction -> candidate kernel -> fetch), results, NCCL reduce.
+// No CPU fallback: every entry point that computes needs a CUDA device.
+#include <algorithm>
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <thread>
+#include <vector>
+#include <dlfcn.h>
+
+#include "launchers.h"
+
+using namespace dbt;
+
+// ------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+static int fail(int code, const char* fmt, ...) {
+	va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
+	return code;
+}
+#define CU(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return fail(DBT_E_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); } while (0)
+
+extern "C" const char* dbt_strerror(int code) {
+	switch (code) {
+	case DBT_OK: return "ok";
+	case DBT_E_CUDA: return "CUDA error";
+	case DBT_E_NOMEM: return "out of memory";
+	case DBT_E_BADARG: return "bad argument";
+	case DBT_E_CAPACITY: return "capacity exceeded";
+	case DBT_E_STATE: return "invalid call order";
+	case DBT_E_INDEX: return "inconsistent RPGG index";
+	case DBT_E_IO: return "I/O error";
+	case DBT_E_NCCL: return "NCCL error";
+	default: return "unknown error";
+	}
+}
+extern "C" const char* dbt_last_error(void) { return g_err; }
+extern "C" int dbt_abi_version(void) { return DBT_ABI_VERSION; }
+extern "C" int dbt_device_count(void) {
+	int n = 0;
+	cudaError_t e = cudaGetDeviceCount(&n);
+	if (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) { cudaGetLastError(); return 0; }
+	if (e != cudaSuccess) { fail(DBT_E_CUDA, "cudaGetDeviceCount: %s", cudaGetErrorString(e)); cudaGetLastError(); return -1; }
+	return n;
+}
+
+extern "C" void dbt_default_params(dbt_params* p) {
+	memset(p, 0, sizeof(*p));
+	p->device = 0; p->k = 21; p->n_filter = 4; p->nm_filter = 1; p->cth = 10; p->nm_tr = 40; p->max_nt = 2;   // cpp:26-33, 2338
+	p->thread_cth = 100; p->max_ncorrection = 4; p->flags = DBT_F_KAM;
+	p->max_read_len = 150; p->max_batch_pairs = 1u << 20; p->max_records = 0; p->table_load = 0.f; p->bucket_slots = 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// context
+// ------------------------------------------------------------------------------------------
+enum { KT_PACK = 0, KT_SUBFILTER, KT_COMPACT, KT_CANDIDATE, KT_N };
+
+struct Slot {
+	bool ready = false;
+	cudaStream_t st = nullptr;
+	uint8_t* d_ascii = nullptr; uint64_t* d_offsets = nullptr;
+	uint64_t* d_packed[2] = {nullptr, nullptr}; uint16_t* d_meta[2] = {nullptr, nullptr};
+	uint32_t* d_passmask = nullptr; uint32_t* d_blocksum = nullptr; uint32_t* d_cand = nullptr; uint32_t* d_ncand = nullptr;
+	uint8_t* d_records = nullptr; unsigned long long* d_counters = nullptr;
+	uint8_t* h_records = nullptr;            // pinned staging
+	uint64_t* h_counters = nullptr;          // pinned: DBT_N_COUNTERS u64 + 2 u32 (ncand, err)
+	uint64_t npairs = 0, first_pair_index = 0;
+	bool uploaded = false, processed = false, fetch_pending = false;
+	dbt_batch_result* result = nullptr;
+	cudaEvent_t ev[KT_N + 1] = {};
+	cudaEvent_t t0 = nullptr, t1 = nullptr;
+	bool ev_pack = false, ev_proc = false;
+};
+
+struct Id128 { char b[128]; };       // ncclUniqueId is passed BY VALUE to ncclCommInitRank
+struct NcclApi {
+	void* lib = nullptr;
+	int (*GetUniqueId)(void*) = nullptr;
+	int (*CommInitRank)(void**, int, Id128, int) = nullptr;
+	int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+	int (*CommDestroy)(void*) = nullptr;
+	const char* (*GetErrorString)(int) = nullptr;
+};
+
+struct dbt_ctx {
+	dbt_params p;
+	RunParams rp;
+	int B = 2, nsm = 0;
+	size_t smem_optin = 0;
+	unsigned cand_grid = 0;
+	bool index_loaded = false;
+	DevIndex ix{};
+	// owned device memory of the index
+	uint4* d_slots = nullptr; uint32_t* d_vv = nullptr; uint32_t* d_vv_aux = nullptr;
+	uint64_t* d_counts = nullptr; uint64_t* d_kmc = nullptr; uint32_t* d_nmapread = nullptr; uint8_t* d_qc = nullptr;
+	uint16_t* d_permtab = nullptr; uint64_t* d_vote_scratch = nullptr; uint32_t* d_vote_epoch = nullptr;
+	uint64_t* d_totals = nullptr;
+	uint64_t table_bytes = 0, nkeys = 0;
+	Slot slot[DBT_N_SLOTS];
+	uint64_t totals[DBT_N_COUNTERS] = {};
+	std::atomic<uint64_t> launches{0};
+	void* nccl_comm = nullptr; int nranks = 1, rank = 0;
+};
+
+static NcclApi g_nccl;
+
+static int set_device(const dbt_ctx* c) { CU(cudaSetDevice(c->p.device)); return DBT_OK; }
+
+static uint32_t round_up(uint32_t v, uint32_t m) { return (v + m - 1) / m * m; }
+
+extern "C" int dbt_create(dbt_ctx** out, const dbt_params* p) {
+	if (!out || !p) return fail(DBT_E_BADARG, "null argument");
+	*out = nullptr;
+	if (p->k < 1 || p->k > 27) return fail(DBT_E_BADARG, "k=%u outside 1..27 (sort keys pack k-mer<<10|mate|pos into 64 bits)", p->k);
+	if (p->max_read_len < p->k || p->max_read_len - p->k + 1 > 512) return fail(DBT_E_BADARG, "max_read_len=%u must satisfy k <= len <= k+511", p->max_read_len);
+	if (p->n_filter == 1 && p->nm_filter) return fail(DBT_E_BADARG, "-kf 1 x divides by zero in the reference (cpp:174)");
+	if (!p->max_batch_pairs) return fail(DBT_E_BADARG, "max_batch_pairs == 0");
+	if (p->bucket_slots && p->bucket_slots != 2 && p->bucket_slots != 4 && p->bucket_slots != 8) return fail(DBT_E_BADARG, "bucket_slots must be 2, 4 or 8");
+	int ndev = dbt_device_count();
+	if (ndev <= 0) return fail(DBT_E_CUDA, "no CUDA device available (this library has no CPU fallback)");
+	if (p->device < 0 || p->device >= ndev) return fail(DBT_E_BADARG, "device %d out of range (%d devices)", p->device, ndev);
+	dbt_ctx* c = new (std::nothrow) dbt_ctx();
+	if (!c) return fail(DBT_E_NOMEM, "host allocation");
+	c->p = *p;
+	if (c->p.max_nt == 0) c->p.max_nt = 2;
+	if (c->p.max_records == 0) c->p.max_records = c->p.max_batch_pairs;
+	if (c->p.flags & DBT_F_TRACE) c->p.max_records = c->p.max_batch_pairs;
+	if (c->p.table_load <= 0.f || c->p.table_load > 0.9f) c->p.table_load = 0.4f;
+	c->B = c->p.bucket_slots ? (int)c->p.bucket_slots : 2;
+	cudaError_t e = cudaSetDevice(p->device);
+	cudaDeviceProp prop;
+	if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, p->device);
+	if (e != cudaSuccess) { delete c; return fail(DBT_E_CUDA, "cudaSetDevice/GetDeviceProperties: %s", cudaGetErrorString(e)); }
+	c->nsm = prop.multiProcessorCount;
+	c->smem_optin = prop.sharedMemPerBlockOptin;
+
+	RunParams& rp = c->rp;
+	rp.k = p->k; rp.n_filter = p->n_filter; rp.nm_filter = p->nm_filter; rp.cth = p->cth; rp.nm_tr = p->nm_tr; rp.max_nt = c->p.max_nt;
+	rp.flags = p->flags;
+	rp.lay = make_layout(p->max_read_len);
+	rp.max_read_len = p->max_read_len;
+	rp.nk_max = p->max_read_len - p->k + 1;
+	rp.nkp = round_up(rp.nk_max, 32);
+	rp.umax = round_up(2 * rp.nk_max, 4);
+	rp.sortn = 2; while (rp.sortn < 2 * rp.nk_max) rp.sortn <<= 1;
+	rp.as_stride = round_up((rp.nk_max + 3) / 4, 8);
+	rp.rec_stride = (uint32_t)sizeof(dbt_pair_record) + 2 * rp.as_stride;
+	rp.max_records = c->p.max_records;
+	// must mirror the carve-up in candidate_kernel
+	size_t ws = 0;
+	ws += (size_t)2 * rp.lay.W64 * 8;                // pk
+	ws += (size_t)rp.sortn * 8;                      // sortk
+	ws += (size_t)4 * rp.nkp * 4;                    // pval, paux
+	ws += (size_t)3 * rp.umax * 4;                   // uval, uaux, unml
+	ws += (size_t)3 * VOTE_SMEM_SLOTS * 4;           // vote table
+	ws += (size_t)2 * rp.umax * 2;                   // utf, utr
+	ws += (size_t)(rp.umax + 2) * 2;                 // ustart
+	ws += (size_t)2 * rp.umax * 2;                   // umid, perm
+	ws += (size_t)2 * rp.nkp;                        // as
+	rp.warp_smem = round_up((uint32_t)ws, 16);
+	size_t block_smem = (size_t)rp.warp_smem * CAND_WARPS_PER_BLOCK;
+	if (block_smem > c->smem_optin) {
+		const size_t lim = c->smem_optin;
+		delete c;
+		return fail(DBT_E_CAPACITY, "max_read_len=%u needs %zu B shared memory per block (> %zu)", p->max_read_len, block_smem, lim);
+	}
+	unsigned blocks_per_sm = (unsigned)std::max<size_t>(1, std::min<size_t>(8, (size_t)(prop.sharedMemPerMultiprocessor - 1024) / (block_smem + 1024)));
+	c->cand_grid = (unsigned)c->nsm * blocks_per_sm;
+	*out = c;
+	return DBT_OK;
+}
+
+static void free_slot(Slot& s) {
+	if (s.st) cudaStreamSynchronize(s.st);
+	cudaFree(s.d_ascii); cudaFree(s.d_offsets);
+	for (int m = 0; m < 2; ++m) { cudaFree(s.d_packed[m]); cudaFree(s.d_meta[m]); }
+	cudaFree(s.d_passmask); cudaFree(s.d_blocksum); cudaFree(s.d_cand); cudaFree(s.d_ncand); cudaFree(s.d_records); cudaFree(s.d_counters);
+	if (s.h_records) cudaFreeHost(s.h_records);
+	if (s.h_counters) cudaFreeHost(s.h_counters);
+	for (auto& e : s.ev) if (e) cudaEventDestroy(e);
+	if (s.t0) cudaEventDestroy(s.t0);
+	if (s.t1) cudaEventDestroy(s.t1);
+	if (s.st) cudaStreamDestroy(s.st);
+	s = Slot();
+}
+
+extern "C" void dbt_destroy(dbt_ctx* c) {
+	if (!c) return;
+	cudaSetDevice(c->p.device);
+	for (auto& s : c->slot) free_slot(s);
+	if (c->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
+	cudaFree(c->d_slots); cudaFree(c->d_vv); cudaFree(c->d_vv_aux); cudaFree(c->d_counts); cudaFree(c->d_kmc); cudaFree(c->d_nmapread);
+	cudaFree(c->d_qc); cudaFree(c->d_permtab); cudaFree(c->d_vote_scratch); cudaFree(c->d_vote_epoch); cudaFree(c->d_totals);
+	delete c;
+}
+
+template <typename T>
+static int dev_alloc(T** p, size_t n, const char* what) {
+	*p = nullptr;
+	cudaError_t e = cudaMalloc((void**)p, std::max<size_t>(n, 1) * sizeof(T));
+	if (e != cudaSuccess) { cudaGetLastError(); return fail(DBT_E_NOMEM, "cudaMalloc(%s, %zu B): %s", what, n * sizeof(T), cudaGetErrorString(e)); }
+	return DBT_OK;
+}
+#define TRY(x) do { int r__ = (x); if (r__ != DBT_OK) return r__; } while (0)
+
+static int ensure_slot(dbt_ctx* c, int si) {
+	Slot& s = c->slot[si];
+	if (s.ready) return DBT_OK;
+	const RunParams& rp = c->rp;
+	const uint64_t P = c->p.max_batch_pairs;
+	CU(cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking));
+	TRY(dev_alloc(&s.d_ascii, (size_t)2 * P * rp.max_read_len + 16, "ascii"));
+	TRY(dev_alloc(&s.d_offsets, 2 * P + 1, "offsets"));
+	for (int m = 0; m < 2; ++m) { TRY(dev_alloc(&s.d_packed[m], P * rp.lay.W64, "packed")); TRY(dev_alloc(&s.d_meta[m], P, "meta")); }
+	const uint64_t nwords = (P + 31) / 32;
+	TRY(dev_alloc(&s.d_passmask, nwords, "passmask"));
+	TRY(dev_alloc(&s.d_blocksum, (nwords + COMPACT_WORDS_H - 1) / COMPACT_WORDS_H + 1, "blocksum"));
+	TRY(dev_alloc(&s.d_cand, P, "cand"));
+	TRY(dev_alloc(&s.d_ncand, 2, "ncand"));
+	TRY(dev_alloc(&s.d_counters, DBT_N_COUNTERS, "counters"));
+	const bool want_records = (c->p.flags & (DBT_F_KAM | DBT_F_TRACE)) != 0;
+	if (want_records) {
+		TRY(dev_alloc(&s.d_records, (size_t)c->p.max_records * rp.rec_stride, "records"));
+		cudaError_t e = cudaHostAlloc((void**)&s.h_records, std::max<size_t>((size_t)c->p.max_records * rp.rec_stride, 16), cudaHostAllocDefault);
+		if (e != cudaSuccess) { cudaGetLastError(); return fail(DBT_E_NOMEM, "cudaHostAlloc(records): %s", cudaGetErrorString(e)); }
+	}
+	CU(cudaHostAlloc((void**)&s.h_counters, (DBT_N_COUNTERS + 1) * sizeof(uint64_t), cudaHostAllocDefault));
+	for (auto& e : s.ev) CU(cudaEventCreate(&e));
+	CU(cudaEventCreate(&s.t0)); CU(cudaEventCreate(&s.t1));
+	s.ready = true;
+	return DBT_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// index
+// ------------------------------------------------------------------------------------------
+extern "C" int dbt_load_index(dbt_ctx* c, const dbt_index* in) {
+	if (!c || !in) return fail(DBT_E_BADARG, "null argument");
+	if (c->index_loaded) return fail(DBT_E_STATE, "index already loaded");
+	if (!in->nloci || !in->tr_n || (in->nk_dbi && (!in->dbi_keys || !in->dbi_vals))) return fail(DBT_E_BADARG, "incomplete dbt_index");
+	if ((c->p.flags & DBT_F_QC) && !in->qc) return fail(DBT_E_BADARG, "DBT_F_QC set but qc == NULL");
+	TRY(set_device(c));
+	const uint64_t nloci = in->nloci;
+	uint64_t ntr = 0, nfl = 0;
+	for (uint64_t l = 0; l < nloci; ++l) { ntr += in->tr_n[l]; nfl += in->fl_n ? in->fl_n[l] : 0; }
+	if (ntr >= (1ull << AUX_CLASS_SHIFT)) return fail(DBT_E_CAPACITY, "%llu TR k-mers exceed the 30-bit count index", (unsigned long long)ntr);
+	if (nloci >= 0x7FFFFFFFull) return fail(DBT_E_CAPACITY, "too many loci");
+	const uint64_t kmax = 1ull << (2 * c->p.k);
+	for (uint64_t i = 0; i < in->nk_dbi; ++i) if (in->dbi_keys[i] >= kmax) return fail(DBT_E_INDEX, "kmers.dbi key %llu does not fit k=%u", (unsigned long long)in->dbi_keys[i], c->p.k);
+
+	cudaStream_t st;
+	CU(cudaStreamCreate(&st));
+	// table
+	const int B = c->B;
+	uint64_t nslots_min = (uint64_t)((double)std::max<uint64_t>(in->nk_dbi, 1) / c->p.table_load) + B;
+	uint64_t nbuckets = (nslots_min + B - 1) / B;
+	if (nbuckets < 64) nbuckets = 64;
+	c->table_bytes = nbuckets * B * sizeof(uint4);
+	c->nkeys = in->nk_dbi;
+	TRY(dev_alloc(&c->d_slots, nbuckets * B, "index table"));
+	CU(cudaMemsetAsync(c->d_slots, 0xFF, c->table_bytes, st));
+	TRY(dev_alloc(&c->d_vv, in->nvv + 1, "vv"));
+	TRY(dev_alloc(&c->d_vv_aux, in->nvv + 1, "vv_aux"));
+	CU(cudaMemsetAsync(c->d_vv_aux, 0, (in->nvv + 1) * 4, st));
+	if (in->nvv) CU(cudaMemcpyAsync(c->d_vv, in->vv, in->nvv * 4, cudaMemcpyHostToDevice, st));
+	uint32_t* d_err; TRY(dev_alloc(&d_err, 1, "err"));
+	CU(cudaMemsetAsync(d_err, 0, 4, st));
+	Table t{c->d_slots, nbuckets};
+	{	// bulk insert of kmers.dbi (readBinaryIndex, h:671)
+		uint64_t* dk; uint32_t* dv;
+		TRY(dev_alloc(&dk, in->nk_dbi, "dbi keys")); TRY(dev_alloc(&dv, in->nk_dbi, "dbi vals"));
+		if (in->nk_dbi) {
+			CU(cudaMemcpyAsync(dk, in->dbi_keys, in->nk_dbi * 8, cudaMemcpyHostToDevice, st));
+			CU(cudaMemcpyAsync(dv, in->dbi_vals, in->nk_dbi * 4, cudaMemcpyHostToDevice, st));
+			CU(launch_insert(st, B, t, dk, dv, in->nk_dbi, d_err)); ++c->launches;
+		}
+		CU(cudaStreamSynchronize(st));
+		cudaFree(dk); cudaFree(dv);
+	}
+	{	// per-locus classes: TR first, flank second (flank wins, cpp:1467-1468)
+		for (int pass = 0; pass < 2; ++pass) {
+			const uint64_t n = pass == 0 ? ntr : nfl;
+			const uint64_t* hn = pass == 0 ? in->tr_n : in->fl_n;
+			const uint64_t* hk = pass == 0 ? in->tr_kmers : in->fl_kmers;
+			if (!n) continue;
+			if (!hk || !hn) return fail(DBT_E_BADARG, "missing k-mer array");
+			std::vector<uint32_t> loc(n);
+			uint64_t j = 0;
+			for (uint64_t l = 0; l < nloci; ++l) for (uint64_t i = 0; i < hn[l]; ++i) loc[j++] = (uint32_t)l;
+			uint64_t* dk; uint32_t* dl;
+			TRY(dev_alloc(&dk, n, "locus kmers")); TRY(dev_alloc(&dl, n, "locus ids"));
+			CU(cudaMemcpyAsync(dk, hk, n * 8, cudaMemcpyHostToDevice, st));
+			CU(cudaMemcpyAsync(dl, loc.data(), n * 4, cudaMemcpyHostToDevice, st));
+			CU(launch_fill_aux(st, B, t, c->d_vv, c->d_vv_aux, dk, dl, n, pass == 0 ? 2u : 1u, d_err)); ++c->launches;
+			CU(cudaStreamSynchronize(st));
+			cudaFree(dk); cudaFree(dl);
+		}
+	}
+	uint32_t herr = 0;
+	CU(cudaMemcpy(&herr, d_err, 4, cudaMemcpyDeviceToHost));
+	cudaFree(d_err);
+	if (herr & ERR_INDEX_DUPKEY) return fail(DBT_E_INDEX, "duplicate key in kmers.dbi");
+	if (herr & ERR_INDEX_MISSING) return fail(DBT_E_INDEX, "a tr/fl k-mer is missing from kmers.dbi for its locus (index files out of sync)");
+	if (herr & ERR_INDEX_DUPTR) return fail(DBT_E_INDEX, "duplicate TR k-mer within a locus");
+
+	// results
+	TRY(dev_alloc(&c->d_counts, ntr, "counts")); TRY(dev_alloc(&c->d_kmc, nloci, "kmc")); TRY(dev_alloc(&c->d_nmapread, nloci, "nmapread"));
+	TRY(dev_alloc(&c->d_totals, DBT_N_COUNTERS, "totals"));
+	CU(cudaMemsetAsync(c->d_counts, 0, std::max<uint64_t>(ntr, 1) * 8, st));
+	CU(cudaMemsetAsync(c->d_kmc, 0, nloci * 8, st));
+	CU(cudaMemsetAsync(c->d_nmapread, 0, nloci * 4, st));
+	if (in->qc) { TRY(dev_alloc(&c->d_qc, nloci, "qc")); CU(cudaMemcpyAsync(c->d_qc, in->qc, nloci, cudaMemcpyHostToDevice, st)); }
+	// all-ties visiting orders: what std::sort does with a comparator that never says "less"
+	// (getSortedIndex on nmappedloci == 1 everywhere, cpp:247-250, 320-321).  Computed with the host's
+	// own std::sort, i.e. the libstdc++ the reference would be built with on this machine.
+	{
+		const uint32_t maxU = c->rp.umax;
+		std::vector<uint16_t> tab((size_t)maxU * (maxU + 1) / 2 + 1);
+		std::vector<uint64_t> idx;
+		for (uint32_t U = 1; U <= maxU; ++U) {
+			idx.resize(U);
+			for (uint32_t i = 0; i < U; ++i) idx[i] = i;
+			std::sort(idx.begin(), idx.end(), [](uint64_t, uint64_t) { return false; });
+			uint16_t* o = tab.data() + (size_t)U * (U - 1) / 2;
+			for (uint32_t i = 0; i < U; ++i) o[i] = (uint16_t)idx[i];
+		}
+		TRY(dev_alloc(&c->d_permtab, tab.size(), "permtab"));
+		CU(cudaMemcpyAsync(c->d_permtab, tab.data(), tab.size() * 2, cudaMemcpyHostToDevice, st));
+		CU(cudaStreamSynchronize(st));
+		c->ix.permtab_maxU = maxU;
+	}
+	// vote fallback scratch: one epoch-tagged hits array per resident warp
+	const uint64_t nwarps = (uint64_t)c->cand_grid * CAND_WARPS_PER_BLOCK;
+	TRY(dev_alloc(&c->d_vote_scratch, nwarps * (nloci + 1), "vote scratch"));
+	TRY(dev_alloc(&c->d_vote_epoch, nwarps, "vote epoch"));
+	CU(cudaMemsetAsync(c->d_vote_scratch, 0, nwarps * (nloci + 1) * 8, st));
+	CU(cudaMemsetAsync(c->d_vote_epoch, 0, nwarps * 4, st));
+	CU(cudaStreamSynchronize(st));
+	CU(cudaStreamDestroy(st));
+
+	c->ix.table = t; c->ix.vv = c->d_vv; c->ix.vv_aux = c->d_vv_aux; c->ix.nvv = in->nvv;
+	c->ix.counts = c->d_counts; c->ix.kmc = c->d_kmc; c->ix.nmapread = c->d_nmapread; c->ix.qc = c->d_qc;
+	c->ix.permtab = c->d_permtab; c->ix.vote_scratch = c->d_vote_scratch; c->ix.vote_epoch = c->d_vote_epoch;
+	c->ix.nloci = nloci; c->ix.nk_tr = ntr;
+	c->index_loaded = true;
+	return DBT_OK;
+}
+
+extern "C" uint64_t dbt_nk_tr(const dbt_ctx* c) { return c ? c->ix.nk_tr : 0; }
+extern "C" uint64_t dbt_nloci(const dbt_ctx* c) { return c ? c->ix.nloci : 0; }
+extern "C" uint32_t dbt_record_stride(const dbt_ctx* c) { return c ? c->rp.rec_stride : 0; }
+extern "C" uint32_t dbt_record_as_stride(const dbt_ctx* c) { return c ? c->rp.as_stride : 0; }
+extern "C" uint64_t dbt_launch_count(const dbt_ctx* c) { return c ? c->launches.load() : 0; }
+
+// ------------------------------------------------------------------------------------------
+// packed host layout: [packed mate0 | packed mate1 | meta mate0 | meta mate1], sized for npairs
+// ------------------------------------------------------------------------------------------
+extern "C" size_t dbt_packed_bytes(uint32_t max_read_len, uint64_t npairs) {
+	ReadLayout l = make_layout(max_read_len);
+	return (size_t)npairs * (2 * (size_t)l.W64 * 8 + 2 * 2);
+}
+
+static void pack_one(const uint8_t* s, uint32_t len, uint32_t k, const ReadLayout& lay, uint64_t* out, uint16_t* meta) {
+	for (uint32_t w = 0; w < lay.W64; ++w) out[w] = 0;
+	uint32_t run = 0; bool any = false;
+	const uint32_t nbits = lay.WM * 64;
+	for (uint32_t i = 0; i < nbits; ++i) {
+		uint32_t c = i < len ? base_code(s[i]) : 4;
+		if (c < 4) { out[i >> 5] |= (uint64_t)c << (2 * (i & 31)); if (++run >= k) any = true; }
+		else { out[lay.WB + (i >> 6)] |= 1ull << (i & 63); run = 0; }
+	}
+	*meta = (uint16_t)(len | (any ? 0 : META_NOVALID));
+}
+
+extern "C" int dbt_pack_reads(uint32_t k, uint32_t max_read_len, uint64_t npairs, const uint8_t* ascii,
+                              const uint64_t* offsets, uint8_t* packed_out, int nthreads) {
+	if (!ascii || !offsets || !packed_out) return fail(DBT_E_BADARG, "null argument");
+	const ReadLayout lay = make_layout(max_read_len);
+	uint64_t* p0 = reinterpret_cast<uint64_t*>(packed_out);
+	uint64_t* p1 = p0 + npairs * lay.W64;
+	uint16_t* m0 = reinterpret_cast<uint16_t*>(p1 + npairs * lay.W64);
+	uint16_t* m1 = m0 + npairs;
+	if (nthreads <= 0) nthreads = (int)std::max(1u, std::thread::hardware_concurrency());
+	nthreads = (int)std::min<uint64_t>((uint64_t)nthreads, std::max<uint64_t>(1, npairs / 4096));
+	std::atomic<int> bad{0};
+	auto work = [&](uint64_t a, uint64_t b) {
+		for (uint64_t p = a; p < b; ++p) {
+			for (int m = 0; m < 2; ++m) {
+				uint64_t off = offsets[2 * p + m], len = offsets[2 * p + m + 1] - off;
+				if (len > max_read_len) { bad = 1; len = max_read_len; }
+				pack_one(ascii + off, (uint32_t)len, k, lay, (m ? p1 : p0) + p * lay.W64, (m ? m1 : m0) + p);
+			}
+		}
+	};
+	std::vector<std::thread> th;
+	uint64_t chunk = (npairs + nthreads - 1) / nthreads;
+	for (int t = 1; t < nthreads; ++t) th.emplace_back(work, std::min<uint64_t>(npairs, t * chunk), std::min<uint64_t>(npairs, (t + 1) * chunk));
+	work(0, std::min<uint64_t>(npairs, chunk));
+	for (auto& x : th) x.join();
+	if (bad) return fail(DBT_E_CAPACITY, "a read is longer than max_read_len=%u", max_read_len);
+	return DBT_OK;
+}
+
+extern "C" void* dbt_host_alloc(size_t bytes) {
+	void* p = nullptr;
+	if (cudaHostAlloc(&p, std::max<size_t>(bytes, 1), cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+	return p;
+}
+extern "C" void dbt_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+// ------------------------------------------------------------------------------------------
+// batches
+// ------------------------------------------------------------------------------------------
+static SlotView slot_view(const dbt_ctx* c, const Slot& s) {
+	SlotView v;
+	v.packed[0] = s.d_packed[0]; v.packed[1] = s.d_packed[1]; v.meta[0] = s.d_meta[0]; v.meta[1] = s.d_meta[1];
+	v.passmask = s.d_passmask; v.blocksum = s.d_blocksum; v.cand = s.d_cand; v.ncand = s.d_ncand; v.records = s.d_records;
+	v.counters = s.d_counters; v.npairs = s.npairs; v.first_pair_index = s.first_pair_index;
+	(void)c;
+	return v;
+}
+
+static int check_slot(dbt_ctx* c, int slot) {
+	if (!c) return fail(DBT_E_BADARG, "null context");
+	if (slot < 0 || slot >= DBT_N_SLOTS) return fail(DBT_E_BADARG, "slot %d out of range", slot);
+	if (!c->index_loaded) return fail(DBT_E_STATE, "dbt_load_index has not been called");
+	TRY(set_device(c));
+	return ensure_slot(c, slot);
+}
+
+extern "C" int dbt_upload(dbt_ctx* c, const dbt_batch* b, int slot) {
+	TRY(check_slot(c, slot));
+	if (!b) return fail(DBT_E_BADARG, "null batch");
+	Slot& s = c->slot[slot];
+	if (s.fetch_pending) return fail(DBT_E_STATE, "slot %d has an unfinished fetch; call dbt_wait", slot);
+	if (b->npairs > c->p.max_batch_pairs) return fail(DBT_E_CAPACITY, "npairs=%llu > max_batch_pairs=%u", (unsigned long long)b->npairs, c->p.max_batch_pairs);
+	s.npairs = b->npairs; s.first_pair_index = b->first_pair_index; s.processed = false; s.ev_pack = false;
+	const RunParams& rp = c->rp;
+	CU(cudaMemsetAsync(s.d_ncand, 0, 8, s.st));
+	if (b->npairs) {
+		if (!b->bases) return fail(DBT_E_BADARG, "null bases");
+		if (b->layout == DBT_LAYOUT_ASCII) {
+			if (!b->offsets) return fail(DBT_E_BADARG, "null offsets");
+			const uint64_t nbytes = b->offsets[2 * b->npairs] - b->offsets[0];
+			if (nbytes > (uint64_t)2 * c->p.max_batch_pairs * rp.max_read_len) return fail(DBT_E_CAPACITY, "batch holds %llu bases, more than max_batch_pairs*2*max_read_len", (unsigned long long)nbytes);
+			CU(cudaMemcpyAsync(s.d_ascii, b->bases + b->offsets[0], nbytes, cudaMemcpyHostToDevice, s.st));
+			CU(cudaMemcpyAsync(s.d_offsets, b->offsets, (2 * b->npairs + 1) * 8, cudaMemcpyHostToDevice, s.st));
+			// offsets are used relative to bases: shift by offsets[0] inside the kernel via pointer arithmetic
+			CU(launch_pack(s.st, s.d_ascii - b->offsets[0], s.d_offsets, b->npairs, rp, s.d_packed[0], s.d_packed[1], s.d_meta[0], s.d_meta[1], s.d_ncand + 1)); ++c->launches;
+			s.ev_pack = true;
+		} else if (b->layout == DBT_LAYOUT_PACKED) {
+			const uint64_t* p0 = reinterpret_cast<const uint64_t*>(b->bases);
+			const uint64_t* p1 = p0 + b->npairs * rp.lay.W64;
+			const uint16_t* m0 = reinterpret_cast<const uint16_t*>(p1 + b->npairs * rp.lay.W64);
+			const uint16_t* m1 = m0 + b->npairs;
+			CU(cudaMemcpyAsync(s.d_packed[0], p0, b->npairs * rp.lay.W64 * 8, cudaMemcpyHostToDevice, s.st));
+			CU(cudaMemcpyAsync(s.d_packed[1], p1, b->npairs * rp.lay.W64 * 8, cudaMemcpyHostToDevice, s.st));
+			CU(cudaMemcpyAsync(s.d_meta[0], m0, b->npairs * 2, cudaMemcpyHostToDevice, s.st));
+			CU(cudaMemcpyAsync(s.d_meta[1], m1, b->npairs * 2, cudaMemcpyHostToDevice, s.st));
+		} else return fail(DBT_E_BADARG, "unknown layout %d", b->layout);
+	}
+	s.uploaded = true;
+	return DBT_OK;
+}
+
+extern "C" int dbt_process(dbt_ctx* c, int slot) {
+	TRY(check_slot(c, slot));
+	Slot& s = c->slot[slot];
+	if (!s.uploaded) return fail(DBT_E_STATE, "slot %d has no uploaded batch", slot);
+	SlotView sv = slot_view(c, s);
+	CU(cudaMemsetAsync(s.d_counters, 0, DBT_N_COUNTERS * 8, s.st));
+	CU(cudaMemsetAsync(s.d_ncand, 0, 4, s.st));
+	CU(cudaEventRecord(s.ev[1], s.st));
+	CU(launch_subfilter(s.st, c->B, c->nsm, c->ix, c->rp, sv)); ++c->launches;
+	CU(cudaEventRecord(s.ev[2], s.st));
+	if (s.npairs) { CU(launch_compact(s.st, sv)); c->launches += 3; }
+	CU(cudaEventRecord(s.ev[3], s.st));
+	CU(launch_candidate(s.st, c->B, c->cand_grid, c->ix, c->rp, sv)); ++c->launches;
+	CU(cudaEventRecord(s.ev[4], s.st));
+	s.processed = true; s.ev_proc = true;
+	return DBT_OK;
+}
+
+extern "C" int dbt_fetch(dbt_ctx* c, dbt_batch_result* r, int slot) {
+	TRY(check_slot(c, slot));
+	Slot& s = c->slot[slot];
+	if (!s.processed) return fail(DBT_E_STATE, "slot %d has not been processed", slot);
+	if (!r) return fail(DBT_E_BADARG, "null result");
+	CU(cudaMemcpyAsync(s.h_counters, s.d_counters, DBT_N_COUNTERS * 8, cudaMemcpyDeviceToHost, s.st));
+	CU(cudaMemcpyAsync(s.h_counters + DBT_N_COUNTERS, s.d_ncand, 8, cudaMemcpyDeviceToHost, s.st));
+	s.result = r; s.fetch_pending = true;
+	return DBT_OK;
+}
+
+extern "C" int dbt_submit(dbt_ctx* c, const dbt_batch* b, dbt_batch_result* r, int slot) {
+	TRY(dbt_upload(c, b, slot));
+	TRY(dbt_process(c, slot));
+	return dbt_fetch(c, r, slot);
+}
+
+extern "C" int dbt_wait(dbt_ctx* c, int slot) {
+	TRY(check_slot(c, slot));
+	Slot& s = c->slot[slot];
+	CU(cudaStreamSynchronize(s.st));
+	if (!s.fetch_pending) return DBT_OK;
+	s.fetch_pending = false;
+	dbt_batch_result* r = s.result; s.result = nullptr;
+	const uint32_t* tail = reinterpret_cast<const uint32_t*>(s.h_counters + DBT_N_COUNTERS);
+	const uint32_t ncand = tail[0], err = tail[1];
+	if (err & ERR_READ_TOO_LONG) return fail(DBT_E_CAPACITY, "a read is longer than max_read_len=%u", c->p.max_read_len);
+	for (int i = 0; i < DBT_N_COUNTERS; ++i) r->counters[i] = s.h_counters[i];
+	r->counters[DBT_C_NREADS] = 2 * s.npairs;
+	r->n_records = 0;
+	const bool trace = (c->p.flags & DBT_F_TRACE) != 0, okam = (c->p.flags & DBT_F_KAM) != 0;
+	int rc = DBT_OK;
+	if ((trace || okam) && r->records) {
+		if (err & ERR_RECORD_OVERFLOW) rc = fail(DBT_E_CAPACITY, "%u candidate pairs exceed max_records=%u", ncand, c->p.max_records);
+		const uint64_t nslots = trace ? s.npairs : std::min<uint64_t>(ncand, c->p.max_records);
+		const uint32_t stride = c->rp.rec_stride;
+		if (nslots) {
+			CU(cudaMemcpyAsync(s.h_records, s.d_records, nslots * stride, cudaMemcpyDeviceToHost, s.st));
+			CU(cudaStreamSynchronize(s.st));
+		}
+		uint64_t n = 0;
+		for (uint64_t i = 0; i < nslots; ++i) {
+			const uint8_t* src = s.h_records + i * stride;
+			if (!trace && reinterpret_cast<const dbt_pair_record*>(src)->status != DBT_ST_COUNTED) continue;
+			if (n >= r->capacity) { rc = fail(DBT_E_CAPACITY, "result buffer holds %llu records, more are pending", (unsigned long long)r->capacity); break; }
+			memcpy(r->records + n * stride, src, stride);
+			++n;
+		}
+		r->n_records = n;
+	}
+	r->counters[DBT_C_NRECORDS] = r->n_records;
+	for (int i = 0; i < DBT_N_COUNTERS; ++i) c->totals[i] += r->counters[i];
+	return rc;
+}
+
+// ------------------------------------------------------------------------------------------
+// results
+// ------------------------------------------------------------------------------------------
+static int sync_all(dbt_ctx* c) {
+	for (auto& s : c->slot) if (s.ready) CU(cudaStreamSynchronize(s.st));
+	return DBT_OK;
+}
+
+extern "C" int dbt_download(dbt_ctx* c, uint64_t* trkmc, uint64_t* kmc, uint32_t* nmapread, uint64_t counters[DBT_N_COUNTERS]) {
+	if (!c) return fail(DBT_E_BADARG, "null context");
+	if (!c->index_loaded) return fail(DBT_E_STATE, "no index");
+	TRY(set_device(c)); TRY(sync_all(c));
+	if (trkmc && c->ix.nk_tr) CU(cudaMemcpy(trkmc, c->d_counts, c->ix.nk_tr * 8, cudaMemcpyDeviceToHost));
+	if (kmc) CU(cudaMemcpy(kmc, c->d_kmc, c->ix.nloci * 8, cudaMemcpyDeviceToHost));
+	if (nmapread) CU(cudaMemcpy(nmapread, c->d_nmapread, c->ix.nloci * 4, cudaMemcpyDeviceToHost));
+	if (counters) for (int i = 0; i < DBT_N_COUNTERS; ++i) counters[i] = c->totals[i];
+	return DBT_OK;
+}
+
+extern "C" int dbt_reset_counts(dbt_ctx* c) {
+	if (!c) return fail(DBT_E_BADARG, "null context");
+	if (!c->index_loaded) return fail(DBT_E_STATE, "no index");
+	TRY(set_device(c)); TRY(sync_all(c));
+	CU(cudaMemset(c->d_counts, 0, std::max<uint64_t>(c->ix.nk_tr, 1) * 8));
+	CU(cudaMemset(c->d_kmc, 0, c->ix.nloci * 8));
+	CU(cudaMemset(c->d_nmapread, 0, c->ix.nloci * 4));
+	memset(c->totals, 0, sizeof(c->totals));
+	return DBT_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// measurement helpers
+// ------------------------------------------------------------------------------------------
+extern "C" int dbt_timer_start(dbt_ctx* c, int slot) {
+	TRY(check_slot(c, slot));
+	CU(cudaEventRecord(c->slot[slot].t0, c->slot[slot].st));
+	return DBT_OK;
+}
+extern "C" int dbt_timer_stop(dbt_ctx* c, int slot, float* ms) {
+	TRY(check_slot(c, slot));
+	Slot& s = c->slot[slot];
+	CU(cudaEventRecord(s.t1, s.st));
+	CU(cudaEventSynchronize(s.t1));
+	if (ms) CU(cudaEventElapsedTime(ms, s.t0, s.t1));
+	return DBT_OK;
+}
+extern "C" int dbt_kernel_times(dbt_ctx* c, int slot, float ms[8], uint32_t launches[8]) {
+	TRY(check_slot(c, slot));
+	Slot& s = c->slot[slot];
+	CU(cudaStreamSynchronize(s.st));
+	for (int i = 0; i < 8; ++i) { ms[i] = 0; launches[i] = 0; }
+	if (s.ev_proc) {
+		CU(cudaEventElapsedTime(&ms[KT_SUBFILTER], s.ev[1], s.ev[2])); launches[KT_SUBFILTER] = 1;
+		CU(cudaEventElapsedTime(&ms[KT_COMPACT], s.ev[2], s.ev[3])); launches[KT_COMPACT] = 3;
+		CU(cudaEventElapsedTime(&ms[KT_CANDIDATE], s.ev[3], s.ev[4])); launches[KT_CANDIDATE] = 1;
+	}
+	return DBT_OK;
+}
+
+extern "C" int dbt_table_stats(const dbt_ctx* cc, uint64_t stats[8]) {
+	dbt_ctx* c = const_cast<dbt_ctx*>(cc);
+	if (!c || !stats) return fail(DBT_E_BADARG, "null argument");
+	if (!c->index_loaded) return fail(DBT_E_STATE, "no index");
+	TRY(set_device(c));
+	unsigned long long* d; TRY(dev_alloc(&d, 4, "stats"));
+	CU(cudaMemset(d, 0, 32));
+	CU(launch_table_stats(0, c->B, c->ix.table, d));
+	unsigned long long h[4];
+	CU(cudaMemcpy(h, d, 32, cudaMemcpyDeviceToHost));
+	cudaFree(d);
+	stats[0] = c->ix.table.nbuckets; stats[1] = (uint64_t)c->B; stats[2] = c->nkeys; stats[3] = h[0]; stats[4] = h[1]; stats[5] = h[2];
+	stats[6] = c->table_bytes; stats[7] = (uint64_t)c->rp.warp_smem;
+	return DBT_OK;
+}
+
+extern "C" int dbt_random_gather_bench(int device, uint64_t table_bytes, uint32_t sector_bytes, uint64_t n_gathers, int iters, float* best_ms) {
+	if (!best_ms) return fail(DBT_E_BADARG, "null argument");
+	CU(cudaSetDevice(device));
+	cudaDeviceProp prop; CU(cudaGetDeviceProperties(&prop, device));
+	uint4* t; TRY(dev_alloc(&t, table_bytes / 16, "gather table"));
+	uint32_t* sink; TRY(dev_alloc(&sink, 1, "sink"));
+	CU(cudaMemset(t, 1, table_bytes));
+	cudaEvent_t a, b; CU(cudaEventCreate(&a)); CU(cudaEventCreate(&b));
+	float best = 1e30f;
+	for (int it = 0; it < iters + 1; ++it) {
+		CU(cudaEventRecord(a, 0));
+		CU(launch_random_gather(0, prop.multiProcessorCount, t, table_bytes, sector_bytes, n_gathers, 0x9E3779B97F4A7C15ull * (it + 1), sink));
+		CU(cudaEventRecord(b, 0));
+		CU(cudaEventSynchronize(b));
+		float ms; CU(cudaEventElapsedTime(&ms, a, b));
+		if (it > 0 && ms < best) best = ms;
+	}
+	cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(t); cudaFree(sink);
+	*best_ms = best;
+	return DBT_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// NCCL (dlopen'ed: the library loads and runs single-GPU without libnccl)
+// ------------------------------------------------------------------------------------------
+static int nccl_load() {
+	if (g_nccl.lib) return DBT_OK;
+	const char* names[] = {"libnccl.so.2", "libnccl.so"};
+	for (const char* n : names) { g_nccl.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (g_nccl.lib) break; }
+	if (!g_nccl.lib) return fail(DBT_E_NCCL, "cannot dlopen libnccl.so.2: %s", dlerror());
+	g_nccl.GetUniqueId = (int (*)(void*))dlsym(g_nccl.lib, "ncclGetUniqueId");
+	g_nccl.CommInitRank = (int (*)(void**, int, Id128, int))dlsym(g_nccl.lib, "ncclCommInitRank");
+	g_nccl.AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(g_nccl.lib, "ncclAllReduce");
+	g_nccl.CommDestroy = (int (*)(void*))dlsym(g_nccl.lib, "ncclCommDestroy");
+	g_nccl.GetErrorString = (const char* (*)(int))dlsym(g_nccl.lib, "ncclGetErrorString");
+	if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce || !g_nccl.CommDestroy) return fail(DBT_E_NCCL, "libnccl lacks a required symbol");
+	return DBT_OK;
+}
+#define NC(call) do { int r__ = (call); if (r__ != 0) return fail(DBT_E_NCCL, "%s: %s", #call, g_nccl.GetErrorString ? g_nccl.GetErrorString(r__) : "?"); } while (0)
+
+extern "C" int dbt_nccl_unique_id(uint8_t id[DBT_NCCL_ID_BYTES]) {
+	TRY(nccl_load());
+	NC(g_nccl.GetUniqueId(id));
+	return DBT_OK;
+}
+
+extern "C" int dbt_comm_init(dbt_ctx* c, int nranks, int rank, const uint8_t id[DBT_NCCL_ID_BYTES]) {
+	if (!c || !id || nranks < 1 || rank < 0 || rank >= nranks) return fail(DBT_E_BADARG, "bad communicator arguments");
+	TRY(set_device(c));
+	c->nranks = nranks; c->rank = rank;
+	if (nranks == 1) return DBT_OK;
+	TRY(nccl_load());
+	Id128 u; memcpy(u.b, id, 128);
+	NC(g_nccl.CommInitRank(&c->nccl_comm, nranks, u, rank));
+	return DBT_OK;
+}
+
+// One exchange step at the end of a run: integer sums are order-independent, so
+// N-GPU outputs are bit-identical to the single-GPU ones.
+extern "C" int dbt_allreduce(dbt_ctx* c) {
+	if (!c) return fail(DBT_E_BADARG, "null context");
+	if (!c->index_loaded) return fail(DBT_E_STATE, "no index");
+	TRY(set_device(c)); TRY(sync_all(c));
+	if (c->nranks == 1) return DBT_OK;
+	if (!c->nccl_comm) return fail(DBT_E_STATE, "dbt_comm_init has not been called");
+	enum { ncclUint32 = 3, ncclUint64 = 5, ncclSum = 0 };
+	cudaStream_t st = 0;
+	CU(cudaMemcpy(c->d_totals, c->totals, sizeof(c->totals), cudaMemcpyHostToDevice));
+	if (c->ix.nk_tr) NC(g_nccl.AllReduce(c->d_counts, c->d_counts, c->ix.nk_tr, ncclUint64, ncclSum, c->nccl_comm, st));
+	NC(g_nccl.AllReduce(c->d_kmc, c->d_kmc, c->ix.nloci, ncclUint64, ncclSum, c->nccl_comm, st));
+	NC(g_nccl.AllReduce(c->d_nmapread, c->d_nmapread, c->ix.nloci, ncclUint32, ncclSum, c->nccl_comm, st));
+	NC(g_nccl.AllReduce(c->d_totals, c->d_totals, DBT_N_COUNTERS, ncclUint64, ncclSum, c->nccl_comm, st));
+	CU(cudaStreamSynchronize(st));
+	CU(cudaMemcpy(c->totals, c->d_totals, sizeof(c->totals), cudaMemcpyDeviceToHost));
+	return DBT_OK;
+}

@@ -1,0 +1,63 @@
+// Device-side views shared by the kernels and the C ABI implementation.
+#pragma once
+#include <stdint.h>
+#include "../../include/danbing_b200.h"
+#include "kmer.cuh"
+#include "table.cuh"
+
+namespace dbt {
+
+constexpr uint32_t NAN32 = 0xFFFFFFFFu;
+constexpr int VOTE_SMEM_SLOTS = 64;          // per-pair shared-memory (locus -> hits1,hits2) entries
+constexpr int CAND_WARPS_PER_BLOCK = 4;
+
+// resident RPGG index
+struct DevIndex {
+	Table    table;
+	const uint32_t* vv;         // kmerDBi_vv (cpp:2470): [n, locus_0 .. locus_{n-1}]*
+	const uint32_t* vv_aux;     // parallel to vv: (class<<30)|idx of the k-mer in that locus
+	uint64_t nvv;
+	uint64_t* counts;           // trResults flattened in output order (cpp:2465, h:968-973)
+	uint64_t* kmc;              // cpp:2476
+	uint32_t* nmapread;         // cpp:2475
+	const uint8_t* qc;          // qcFilter (cpp:2471) or nullptr
+	const uint16_t* permtab;    // all-ties std::sort permutations, perm_U at offset U*(U-1)/2
+	uint32_t permtab_maxU;
+	uint64_t* vote_scratch;     // per-warp epoch-tagged hits arrays [(nloci+1)] (fallback of the smem table)
+	uint32_t* vote_epoch;       // per-warp epoch
+	uint64_t nloci, nk_tr;
+};
+
+struct RunParams {
+	uint32_t k, n_filter, nm_filter, cth, nm_tr, max_nt, flags;
+	ReadLayout lay;
+	uint32_t max_read_len;
+	uint32_t nk_max;            // max_read_len - k + 1
+	uint32_t nkp;               // nk_max rounded up to a multiple of 32
+	uint32_t umax;              // 2*nk_max rounded up to 4
+	uint32_t sortn;             // power of two >= 2*nk_max
+	uint32_t as_stride, rec_stride;
+	uint32_t warp_smem;         // bytes of shared memory per warp in candidate_kernel
+	uint32_t max_records;
+};
+
+// one in-flight batch
+struct SlotView {
+	const uint64_t* packed[2];  // [mate][pair][W64]
+	const uint16_t* meta[2];    // [mate][pair]
+	uint32_t* passmask;         // bit per pair: passed subfilter
+	uint32_t* blocksum;         // compaction scratch
+	uint32_t* cand;             // candidate pair ids, ascending
+	uint32_t* ncand;            // [0] = number of candidates, [1] = error flags
+	uint8_t*  records;
+	unsigned long long* counters;   // DBT_N_COUNTERS
+	uint64_t npairs, first_pair_index;
+};
+
+constexpr uint32_t ERR_RECORD_OVERFLOW = 1u;
+constexpr uint32_t ERR_READ_TOO_LONG   = 2u;
+constexpr uint32_t ERR_INDEX_MISSING   = 4u;   // tr/fl k-mer not in kmers.dbi for its locus
+constexpr uint32_t ERR_INDEX_DUPKEY    = 8u;
+constexpr uint32_t ERR_INDEX_DUPTR     = 16u;
+
+}  // namespace dbt

@@ -1,0 +1,17 @@
+// host-callable launchers implemented in kernels.cu
+#pragma once
+#include "device_types.cuh"
+namespace dbt {
+cudaError_t launch_pack(cudaStream_t st, const uint8_t* ascii, const uint64_t* offsets, uint64_t npairs, const RunParams& rp,
+                        uint64_t* p0, uint64_t* p1, uint16_t* m0, uint16_t* m1, uint32_t* err);
+cudaError_t launch_subfilter(cudaStream_t st, int B, int nsm, const DevIndex& ix, const RunParams& rp, const SlotView& sv);
+cudaError_t launch_compact(cudaStream_t st, const SlotView& sv);
+cudaError_t launch_candidate(cudaStream_t st, int B, unsigned grid, const DevIndex& ix, const RunParams& rp, const SlotView& sv);
+cudaError_t launch_insert(cudaStream_t st, int B, Table t, const uint64_t* keys, const uint32_t* vals, uint64_t n, uint32_t* err);
+cudaError_t launch_fill_aux(cudaStream_t st, int B, Table t, const uint32_t* vv, uint32_t* vv_aux, const uint64_t* kmers,
+                            const uint32_t* locus_of, uint64_t n, uint32_t cls, uint32_t* err);
+cudaError_t launch_table_stats(cudaStream_t st, int B, Table t, unsigned long long* out);
+cudaError_t launch_random_gather(cudaStream_t st, int nsm, const uint4* table, uint64_t table_bytes, uint32_t sector_bytes,
+                                 uint64_t ngathers, uint64_t seed, uint32_t* sink);
+constexpr int COMPACT_WORDS_H = 1024;
+}

@@ -1,0 +1,118 @@
+// GPU-resident RPGG index (SURVEY.md §8(a) types Y1-Y3): ONE open-addressing table in HBM.
+//
+// What it replaces in the reference:
+//   kmerDBi      unordered_map<size_t,size_t>   canonical k-mer -> val         (h:35, kio:59-74)
+//   trResults[l] unordered_map<size_t,atomic>   TR k-mers of locus l -> count  (h:31, cpp:2465)
+//   flankDB[l]   unordered_set<uint64_t>        flank k-mers of locus l        (h:47, cpp:2466)
+// Every TR / flank k-mer of locus l is also a key of kmerDBi that lists l (ktools serialize builds
+// kmerDBi as the union of .tr.kmers and .fl.kmers, kmertools.cpp:236-237), so the per-locus class
+// ("flank" / "TR" + position in the count array) is folded into the index entry itself: one probe
+// answers kfilter (cpp:207), the locus vote (cpp:367) AND assignTRkmc (cpp:1466-1468).
+//
+// Slot (16 B): { u64 key | bit63 = bucket-overflow flag (slot 0 only) ; u32 val ; u32 aux }
+//   val : the reference's value -- even: locus<<1, odd: (offset into vv)<<1|1
+//   aux : (class<<30) | idx for single-locus keys; class 0 none, 1 flank, 2 TR (= the `as` states of
+//         cpp:78-92); idx = position in the output-ordered count array.  Multi-locus keys keep their
+//         per-locus aux in vv_aux[], parallel to vv[].
+// Bucket = B consecutive slots (B*16 bytes: 32 B = one L2 sector for B=2, 64 B for B=4), home bucket
+// = mulhi(mix64(key), nbuckets).  A probe reads one bucket; it goes on to the next bucket only when
+// the bucket is full AND its overflow flag is set, so a miss -- the dominant case for background
+// reads in subfilter -- costs one sector unless more than B keys hashed to that bucket.
+#pragma once
+#include <stdint.h>
+#include <cuda_runtime.h>
+
+namespace dbt {
+
+constexpr uint64_t SLOT_EMPTY = 0xFFFFFFFFFFFFFFFFull;
+constexpr uint64_t SLOT_OVF   = 0x8000000000000000ull;
+constexpr uint64_t SLOT_KEYMASK = ~SLOT_OVF;
+constexpr uint32_t AUX_CLASS_SHIFT = 30;
+constexpr uint32_t AUX_IDX_MASK = (1u << AUX_CLASS_SHIFT) - 1;
+constexpr uint32_t AUX_MISS = 3u << AUX_CLASS_SHIFT;      // per-position marker: k-mer not in the index
+
+struct Table {
+	uint4*   slots;      // nbuckets * B slots
+	uint64_t nbuckets;
+};
+
+__host__ __device__ __forceinline__ uint64_t mix64(uint64_t x) {
+	x ^= x >> 33; x *= 0xff51afd7ed558ccdull; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ull; x ^= x >> 33;
+	return x;
+}
+
+__device__ __forceinline__ uint64_t home_bucket(const Table& t, uint64_t key) {
+	return __umul64hi(mix64(key), t.nbuckets);
+}
+
+__device__ __forceinline__ uint64_t slot_key(const uint4& s) { return ((uint64_t)s.y << 32) | s.x; }
+
+// read-only 128-bit load through the non-coherent path (the table is immutable after load_index)
+__device__ __forceinline__ uint4 ldg128(const uint4* p) { return __ldg(p); }
+
+// Looks key up. Returns true on hit and sets val/aux. key must be < 2^63 and != invalid.
+// nsect (optional) accumulates the number of buckets read (sectors/probe statistics).
+template <int B>
+__device__ __forceinline__ bool table_lookup(const Table& t, uint64_t key, uint32_t& val, uint32_t& aux) {
+	uint64_t b = home_bucket(t, key);
+	for (;;) {
+		const uint4* bp = t.slots + b * B;
+		uint4 s[B];
+#pragma unroll
+		for (int i = 0; i < B; ++i) s[i] = ldg128(bp + i);
+		bool full = true;
+#pragma unroll
+		for (int i = 0; i < B; ++i) {
+			uint64_t k = slot_key(s[i]);
+			if (k == SLOT_EMPTY) full = false;
+			else if ((k & SLOT_KEYMASK) == key) { val = s[i].z; aux = s[i].w; return true; }
+		}
+		if (!full || !(slot_key(s[0]) & SLOT_OVF)) return false;
+		if (++b == t.nbuckets) b = 0;
+	}
+}
+
+// Same walk, but returns the slot address (used by the aux-fill kernels at load time).
+template <int B>
+__device__ __forceinline__ uint4* table_find_slot(const Table& t, uint64_t key) {
+	uint64_t b = home_bucket(t, key);
+	for (;;) {
+		uint4* bp = t.slots + b * B;
+		bool full = true;
+		uint64_t k0 = 0;
+#pragma unroll
+		for (int i = 0; i < B; ++i) {
+			uint64_t k = *reinterpret_cast<volatile uint64_t*>(bp + i);
+			if (i == 0) k0 = k;
+			if (k == SLOT_EMPTY) full = false;
+			else if ((k & SLOT_KEYMASK) == key) return bp + i;
+		}
+		if (!full || !(k0 & SLOT_OVF)) return nullptr;
+		if (++b == t.nbuckets) b = 0;
+	}
+}
+
+// Inserts (key,val); aux starts at 0. Returns 0 ok, 1 duplicate key.
+template <int B>
+__device__ __forceinline__ int table_insert(const Table& t, uint64_t key, uint32_t val) {
+	uint64_t b = home_bucket(t, key);
+	for (;;) {
+		uint4* bp = t.slots + b * B;
+#pragma unroll
+		for (int i = 0; i < B; ++i) {
+			unsigned long long* kp = reinterpret_cast<unsigned long long*>(bp + i);
+			unsigned long long old = atomicCAS(kp, (unsigned long long)SLOT_EMPTY, (unsigned long long)key);
+			if (old == SLOT_EMPTY) {
+				uint32_t* w = reinterpret_cast<uint32_t*>(bp + i);
+				w[2] = val; w[3] = 0;
+				return 0;
+			}
+			if ((old & SLOT_KEYMASK) == key) return 1;
+		}
+		// bucket full: leave the overflow mark so lookups continue past it
+		atomicOr(reinterpret_cast<unsigned long long*>(bp), (unsigned long long)SLOT_OVF);
+		if (++b == t.nbuckets) b = 0;
+	}
+}
+
+}  // namespace dbt

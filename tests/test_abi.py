@@ -1,0 +1,78 @@
+"""CPU-only: the C-ABI library loads, exports every symbol include/danbing_b200.h declares, and
+refuses to compute without a GPU (no CPU fallback)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+
+from oracle_abi import ROOT, abi
+
+
+def declared_symbols():
+    hdr = open(os.path.join(ROOT, "include", "danbing_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    return sorted(set(re.findall(r"\b(dbt_[a-z0-9_]+)\s*\(", hdr)))
+
+
+def test_header_and_python_mirror_agree():
+    assert declared_symbols() == sorted(abi.ABI_SYMBOLS)
+
+
+def test_library_exports_every_declared_symbol(lib):
+    for s in declared_symbols():
+        assert hasattr(lib, s), s
+    assert lib.dbt_abi_version() == 1
+
+
+def test_struct_sizes():
+    assert C.sizeof(abi.Params) == 18 * 4
+    assert C.sizeof(abi.Index) == 11 * 8
+    assert C.sizeof(abi.Batch) == 40
+    assert C.sizeof(abi.BatchResult) == 24 + 16 * 8
+    assert abi.RECORD_HEADER_DTYPE.itemsize == 64
+
+
+def test_no_cpu_fallback(lib):
+    if lib.dbt_device_count() > 0:
+        return
+    p = abi.default_params()
+    h = C.c_void_p()
+    rc = lib.dbt_create(C.byref(h), C.byref(p))
+    assert rc == -1 and b"no CPU fallback" in lib.dbt_last_error()
+
+
+def test_bad_arguments(lib):
+    h = C.c_void_p()
+    for k, v in (("k", 0), ("k", 28), ("max_read_len", 10), ("max_batch_pairs", 0), ("bucket_slots", 3)):
+        p = abi.default_params()
+        setattr(p, k, v)
+        assert lib.dbt_create(C.byref(h), C.byref(p)) == -3, k
+    p = abi.default_params(n_filter=1)
+    assert lib.dbt_create(C.byref(h), C.byref(p)) == -3          # -kf 1 x divides by zero in the reference
+
+
+def test_host_packer_layout(lib):
+    """dbt_pack_reads (host side of north_star item 1): 2-bit codes + invalid mask + no-valid-window flag"""
+    seqs = ["ACGTACGTACGTACGTACGTACGTA", "ACGTNNNNacgtACGTACGTACGTACGT", "NNNN", "A" * 150]
+    bases = np.frombuffer("".join(seqs).encode(), np.uint8).copy()
+    off = np.zeros(5, np.uint64)
+    off[1:] = np.cumsum([len(s) for s in seqs])
+    n = lib.dbt_packed_bytes(150, 2)
+    out = np.zeros(n, np.uint8)
+    assert lib.dbt_pack_reads(21, 150, 2, abi.ptr(bases, abi.u8p), abi.ptr(off, abi.u64p), abi.ptr(out, abi.u8p), 1) == 0
+    W = 8
+    p = out[: 2 * 2 * W * 8].view("<u8").reshape(2, 2, W)          # [mate][pair][word]
+    meta = out[2 * 2 * W * 8:].view("<u2").reshape(2, 2)
+    code = {"A": 0, "C": 1, "G": 2, "T": 3}
+    for r, s in enumerate(seqs):
+        m, pair = r & 1, r >> 1
+        rec = p[m, pair]
+        for i, ch in enumerate(s):
+            inv = (int(rec[5 + i // 64]) >> (i % 64)) & 1
+            assert inv == (ch not in code)
+            if not inv:
+                assert (int(rec[i // 32]) >> (2 * (i % 32))) & 3 == code[ch]
+        assert (int(rec[5 + len(s) // 64]) >> (len(s) % 64)) & 1 == 1 or len(s) == 192
+        assert int(meta[m, pair]) & 0x7FFF == len(s)
+    assert [int(meta[r & 1, r >> 1]) >> 15 for r in range(4)] == [0, 1, 1, 0]

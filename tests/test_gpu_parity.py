@@ -1,0 +1,180 @@
+"""GPU parity tests (run with `-m gpu` on the B200 box): the CUDA path, called through the C ABI,
+against the golden vectors of the unmodified reference and against the CPU oracle on seeded inputs.
+Integer / byte work: every comparison is bit-exact."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from common import golden_case, golden_outputs, golden_reads, params_for, summary_text, synthetic_case
+from oracle_abi import Oracle, abi, rpgg_io
+
+pytestmark = pytest.mark.gpu
+
+CASES = [("s1", "cth45"), ("s1", "cth10"), ("s1", "kf0"), ("multi", "cth45"), ("multi", "cth10"), ("multi", "kf0")]
+
+
+def run_gpu(ix, params, seqs, batch=None):
+    ctx = abi.Context(params, abi.make_index_struct(ix))
+    bases, off = rpgg_io.seqs_to_batch(seqs)
+    npairs = len(seqs) // 2
+    batch = batch or npairs
+    recs_all, cnt = [], np.zeros(abi.DBT_N_COUNTERS, np.uint64)
+    for b0 in range(0, max(npairs, 1), batch):
+        b1 = min(npairs, b0 + batch)
+        o = off[2 * b0: 2 * b1 + 1]
+        recs, c = ctx.run(bases, o, first_pair_index=b0, slot=(b0 // batch) % 2)
+        recs_all.append(recs.copy())
+        cnt += c
+    trkmc, kmc, nmap, tot = ctx.download()
+    assert np.array_equal(tot, cnt)
+    recs = np.concatenate(recs_all) if recs_all else None
+    ctx.close()
+    return recs, cnt, trkmc, kmc, nmap
+
+
+@pytest.mark.parametrize("case_name,run_name", CASES)
+def test_gpu_matches_reference_golden(case_name, run_name):
+    """kam records, .trkmc.ar, .tr.summary.txt and the stderr counters of the reference binary"""
+    case = golden_case(case_name)
+    run = case["meta"]["runs"][run_name]
+    titles, seqs = golden_reads(case, run_name)
+    exp = golden_outputs(case, run_name)
+    recs, cnt, trkmc, kmc, nmap = run_gpu(case["ix"], params_for(run), seqs)
+    assert np.array_equal(trkmc, exp["trkmc"])
+    assert summary_text(nmap, kmc) == exp["summary"]
+    kam = [rpgg_io.kam_line(r, titles[int(r["h"]["pair_index"])], seqs[2 * int(r["h"]["pair_index"])],
+                            seqs[2 * int(r["h"]["pair_index"]) + 1]) for r in recs]
+    assert kam == exp["kam"]
+    c = dict(zip(abi.COUNTER_NAMES, cnt.tolist()))
+    ref, hc = run["counters"], run["harness_counters"]
+    assert c["nReads"] == ref["reads processed in total"]
+    assert c["nSubFiltered"] == ref["removed by subsampled kmer-filter"]
+    assert c["nKmerFiltered"] == ref["removed by kmer-filter"]
+    assert c["nLocusAssignFiltered"] == ref["removed during locus assignment"]
+    assert c["nThreadingReads"] == ref["entered threading step"] == c["nFeasibleReads"]
+    assert c["nAsgnReads"] == ref["assigned to TR region"]
+    assert (c["nShort"], c["nhash0"], c["nhash1"]) == (hc["nShort"], hc["nhash0"], hc["nhash1"])
+    assert c["ninc"] == int(exp["trkmc"].sum())
+
+
+@pytest.mark.parametrize("case_name,run_name", [("s1", "cth45"), ("multi", "cth45"), ("multi", "cth10"), ("multi", "kf0")])
+def test_gpu_trace_matches_reference_functions(case_name, run_name):
+    """every pair's internals (status, probe counts, dst/dst0, top.fc/top.rc at the early stop, flags,
+    segment, annotation) vs the reference's own functions driven pair by pair (harness trace)"""
+    case = golden_case(case_name)
+    run = case["meta"]["runs"][run_name]
+    titles, seqs = golden_reads(case, run_name)
+    exp = golden_outputs(case, run_name)
+    recs, cnt, trkmc, kmc, nmap = run_gpu(case["ix"], params_for(run, flags=abi.F_KAM | abi.F_TRACE), seqs)
+    got = [rpgg_io.trace_line(r, case["ix"]["nloci"]) for r in recs]
+    assert len(got) == len(exp["trace"])
+    bad = [i for i, (a, b) in enumerate(zip(got, exp["trace"])) if a != b]
+    assert not bad, f"{len(bad)} pairs differ, first: {bad[0]}\n gpu {got[bad[0]]}\n ref {exp['trace'][bad[0]]}"
+    assert np.array_equal(trkmc, exp["trkmc"])
+
+
+def oracle_vs_gpu(ix, seqs, p_gpu, p_oracle=None, batch=None):
+    bases, off = rpgg_io.seqs_to_batch(seqs)
+    orecs, ocnt, otr, okmc, onmap = Oracle(ix).run(p_oracle or p_gpu, bases, off)
+    recs, cnt, trkmc, kmc, nmap = run_gpu(ix, p_gpu, seqs, batch=batch)
+    assert np.array_equal(trkmc, otr)
+    assert np.array_equal(kmc, okmc) and np.array_equal(nmap, onmap)
+    trace = (p_gpu.flags & abi.F_TRACE) != 0
+    if trace:
+        assert recs.tobytes() == orecs.tobytes()                       # record buffers byte-identical
+    else:
+        keep = orecs[orecs["h"]["status"] == 6].copy()
+        keep["h"]["nhash0"] = 0                                         # per-pair nhash0 is a trace-mode field
+        assert recs.tobytes() == keep.tobytes()
+    names = [n for n in abi.COUNTER_NAMES if n not in ("nrecords",)]
+    assert {n: int(cnt[i]) for i, n in enumerate(abi.COUNTER_NAMES) if n in names} == \
+           {n: int(ocnt[i]) for i, n in enumerate(abi.COUNTER_NAMES) if n in names}
+    return recs, cnt
+
+
+@pytest.mark.parametrize("k,cth,flank,bucket", [(21, 45, 300, 2), (21, 10, 300, 4), (17, 30, 250, 2), (25, 20, 300, 8), (21, 45, 300, 4)])
+def test_gpu_matches_oracle_seeded(k, cth, flank, bucket):
+    """fresh synthetic RPGG with shared segments + chimeric/borderline/N/short reads; k = 17/21/25"""
+    ix, seqs, _ = synthetic_case(nloci=60, seed=200 + k + cth, k=k, flank=flank, npairs=8000, read_seed=cth,
+                                 frac_locus=0.4, frac_chimeric=0.3, frac_border=0.15)
+    p = abi.default_params(k=k, cth=cth, flags=abi.F_KAM | abi.F_TRACE, max_batch_pairs=8192)
+    p.bucket_slots = bucket
+    oracle_vs_gpu(ix, seqs, p)
+
+
+def test_gpu_batches_and_slots_accumulate():
+    """same reads in 5 batches over both slots == one batch (counts are order-independent sums)"""
+    ix, seqs, _ = synthetic_case(nloci=40, seed=5, npairs=5000, read_seed=9, frac_locus=0.5, frac_chimeric=0.2, frac_border=0.1)
+    p = abi.default_params(k=21, cth=30, flags=abi.F_KAM, max_batch_pairs=1024)
+    oracle_vs_gpu(ix, seqs, p, batch=1000)
+
+
+def test_gpu_ka_and_qc_flags():
+    """-ka (no kam records; assignTRkmc skips removed mates, cpp:1451) and -qc (cpp:2059-2062)"""
+    ix, seqs, _ = synthetic_case(nloci=40, seed=6, npairs=4000, read_seed=10, frac_locus=0.5, frac_chimeric=0.2, frac_border=0.1)
+    qc = (np.arange(ix["nloci"]) % 3 != 0).astype(np.uint8)
+    ix = dict(ix, qc=qc)
+    p = abi.default_params(k=21, cth=30, flags=abi.F_QC | abi.F_TRACE, max_batch_pairs=4096)
+    recs, cnt = oracle_vs_gpu(ix, seqs, p)
+    assert int(cnt[abi.COUNTER_NAMES.index("nQCFiltered")]) > 0
+    p2 = abi.default_params(k=21, cth=30, flags=0, max_batch_pairs=4096)
+    bases, off = rpgg_io.seqs_to_batch(seqs)
+    ctx = abi.Context(p2, abi.make_index_struct(ix))
+    recs, c = ctx.run(bases, off)
+    assert len(recs) == 0                                              # -ka: nothing on stdout
+    o = Oracle(ix).run(p2, bases, off)
+    assert np.array_equal(ctx.download()[0], o[2])
+
+
+def test_gpu_empty_and_degenerate_batches():
+    ix, seqs, _ = synthetic_case(nloci=10, seed=7, npairs=50, read_seed=11)
+    p = abi.default_params(k=21, cth=10, flags=abi.F_KAM | abi.F_TRACE, max_batch_pairs=64)
+    ctx = abi.Context(p, abi.make_index_struct(ix))
+    recs, cnt = ctx.run(np.zeros(1, np.uint8), np.zeros(1, np.uint64))     # empty batch
+    assert len(recs) == 0 and int(cnt.sum()) == 0
+    weird = ["N" * 150, "ACGT" * 30, "A" * 20, "ACGTACGTAC" * 15, "acgt" * 37, "ACGT" * 37, "", "ACGT" * 37]
+    bases, off = rpgg_io.seqs_to_batch(weird)
+    recs, cnt = ctx.run(bases, off)
+    orecs = Oracle(ix).run(p, bases, off)[0]
+    assert recs.tobytes() == orecs.tobytes()
+    too_long = ["A" * 151, "C" * 150]
+    bases, off = rpgg_io.seqs_to_batch(too_long)
+    with pytest.raises(abi.DbtError, match="capacity"):
+        ctx.run(bases, off)
+    ctx.close()
+
+
+def test_gpu_packed_layout_equals_ascii(lib):
+    """host packer + DBT_LAYOUT_PACKED upload == device pack kernel"""
+    ix, seqs, _ = synthetic_case(nloci=30, seed=8, npairs=3000, read_seed=12, frac_locus=0.5, frac_chimeric=0.2)
+    bases, off = rpgg_io.seqs_to_batch(seqs)
+    npairs = len(seqs) // 2
+    p = abi.default_params(k=21, cth=30, flags=abi.F_KAM | abi.F_TRACE, max_batch_pairs=4096)
+    ctx = abi.Context(p, abi.make_index_struct(ix))
+    r1, c1 = ctx.run(bases, off)
+    r1 = r1.copy()
+    t1 = ctx.download()[0].copy()
+    ctx.reset()
+    packed = np.zeros(lib.dbt_packed_bytes(150, npairs), np.uint8)
+    assert lib.dbt_pack_reads(21, 150, npairs, abi.ptr(bases, abi.u8p), abi.ptr(off, abi.u64p), abi.ptr(packed, abi.u8p), 4) == 0
+    b = ctx.make_batch(packed, None, layout=abi.LAYOUT_PACKED, npairs=npairs)
+    rec = np.zeros(npairs * ctx.stride, np.uint8)
+    r = abi.BatchResult()
+    r.capacity = npairs
+    r.records = abi.ptr(rec, abi.u8p)
+    abi.check(lib, lib.dbt_submit(ctx.h, C.byref(b), C.byref(r), 0), "submit")
+    abi.check(lib, lib.dbt_wait(ctx.h, 0), "wait")
+    assert rec.tobytes() == r1.tobytes()
+    assert np.array_equal(ctx.download()[0], t1)
+    ctx.close()
+
+
+def test_gpu_index_consistency_is_checked():
+    ix, seqs, _ = synthetic_case(nloci=10, seed=9, npairs=10, read_seed=13)
+    bad = dict(ix)
+    bad["tr_kmers"] = ix["tr_kmers"].copy()
+    bad["tr_kmers"][0] ^= np.uint64(0x155)                # a TR k-mer that kmers.dbi does not hold
+    p = abi.default_params(k=21, cth=10, max_batch_pairs=64)
+    with pytest.raises(abi.DbtError, match="index"):
+        abi.Context(p, abi.make_index_struct(bad))
