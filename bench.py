@@ -1,0 +1,453 @@
+#!/usr/bin/env python3
+"""bench.py -- read pairs/sec of the `danbing-tk align` hot path (k=21) on N B200s.
+
+Contract (driver): `python bench.py --gpus N --steps K --warmup W` prints ONE JSON line (rank 0).
+  step      = one pass of the hot path (subfilter -> compaction -> candidate kernel) over one batch of
+              synthetic read pairs; N>1: every rank runs the same-sized batch of ITS OWN reads
+              (weak scaling, RPGG replicated) and a step ends with the NCCL sum-reduce of the counts.
+  value     = read pairs/s, whole job, packed reads already resident in HBM (CUDA events, max over ranks)
+  e2e       = same metric through the C ABI with HOST buffers: pinned ASCII reads -> dbt_submit (H2D +
+              device 2-bit pack + kernels) -> dbt_wait (D2H of counters + kam records), double-buffered
+  roofline  = dominant kernel's algorithmic HBM bytes / its CUDA-event time vs MEASURED_PEAKS.json
+  cpu_baseline = the UNMODIFIED reference (oracle/_ref/danbing-tk -p nproc) on a bounded sample of the
+              same workload on this box's host cores, outputs diffed against the GPU's (bit-exact gate)
+`--impl reference` times only that CPU reference arm.
+Workload = BASELINE.json configs[1]: synthetic 1k-locus RPGG, 10M simulated 150 bp pairs (5% locus
+reads, 95% background), flags -k 21 -kf 4 1 -cth 45 (+ -ae, an output-selection flag that is a no-op at
+the reference's HEAD; `-gc 85 3` threading has no caller there -- SURVEY.md F2/F3 -- so the live "asgn"
+path is what both arms run).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from oracle_abi import REF_DIR, abi, pkg, ref_bin, rpgg_io  # noqa: E402  (oracle_abi: only the cpu_baseline leg runs oracle/_ref)
+
+synth = pkg.synth
+RLEN, FLEN, K, CTH = 150, 500, 21, 45
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# workload
+# ------------------------------------------------------------------------------------------------
+def build_workload(nloci, seed, workdir):
+    """S2-shaped RPGG: nloci loci x 8 haplotypes, 700 bp flanks, 5% sharing a 200 bp segment."""
+    t = time.time()
+    loci = synth.make_loci(nloci, seed=seed, nhap=8, flank=700, share_frac=0.05, share_len=200)
+    pref = os.path.join(workdir, "pan")
+    ix = synth.build_rpgg(loci, pref, k=K, fsi=700, fso=700, write_text=True)
+    haps = [h for hs in loci for h in hs]
+    hap_off = np.zeros(len(haps) + 1, np.uint64)
+    hap_off[1:] = np.cumsum([len(h) for h in haps])
+    pool = np.frombuffer(b"".join(haps), np.uint8).copy()
+    log(f"[bench] RPGG: {nloci} loci, {len(ix['dbi_keys'])} index k-mers, {len(ix['tr_kmers'])} TR k-mers, nvv={len(ix['vv'])} ({time.time()-t:.1f}s)")
+    return ix, pref, pool, hap_off
+
+
+_synth_lib = None
+
+
+def synth_reads(device, pool, hap_off, first_pair, npairs, seed, frac_locus, out):
+    global _synth_lib
+    if _synth_lib is None:
+        _synth_lib = C.CDLL(os.path.join(ROOT, "danbing-tk_b200", "libdbt_synth.so"))
+        _synth_lib.dbt_synth_reads.argtypes = [C.c_int, abi.u8p, abi.u64p, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint64,
+                                               C.c_double, C.c_uint32, C.c_uint32, abi.u8p]
+    rc = _synth_lib.dbt_synth_reads(device, abi.ptr(pool, abi.u8p), abi.ptr(hap_off, abi.u64p), len(hap_off) - 1, first_pair,
+                                    npairs, seed, frac_locus, RLEN, FLEN, abi.ptr(out, abi.u8p))
+    if rc:
+        raise RuntimeError(f"dbt_synth_reads failed: {rc}")
+
+
+def write_fasta_sample(fn, ascii_reads, npairs):
+    """pairs [0, npairs) of the batch as interleaved FASTA in ARRIVAL order (/1 then /2), fixed-width names."""
+    a = ascii_reads[: npairs * 2 * RLEN].reshape(npairs, 2, RLEN)
+    idw = 9
+    rec = np.empty((npairs, 2, 1 + 1 + idw + 2 + 1 + RLEN + 1), np.uint8)
+    ids = np.char.zfill(np.arange(npairs).astype(str), idw)
+    idb = np.frombuffer("".join(ids.tolist()).encode(), np.uint8).reshape(npairs, idw)
+    for m, tag in ((0, b"1"), (1, b"2")):
+        rec[:, m, 0] = ord(">")
+        rec[:, m, 1] = ord("r")
+        rec[:, m, 2:2 + idw] = idb
+        rec[:, m, 2 + idw] = ord("/")
+        rec[:, m, 3 + idw] = tag[0]
+        rec[:, m, 4 + idw] = ord("\n")
+        rec[:, m, 5 + idw:5 + idw + RLEN] = a[:, 1 - m]          # batch order is (late "/2", early "/1")
+        rec[:, m, 5 + idw + RLEN] = ord("\n")
+    rec.tofile(fn)
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, device):
+        self.samples, self.stop_flag, self.device = [], False, device
+        self.t = threading.Thread(target=self.run, daemon=True)
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                o = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.device)],
+                                   capture_output=True, text=True, timeout=5).stdout.strip()
+                if o:
+                    self.samples.append([x.strip() for x in o.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def __enter__(self):
+        self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop_flag = True
+        self.t.join(timeout=6)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(float(s[0]) for s in self.samples)
+        reasons = [n for i, n in ((3, "hw_slowdown"), (4, "hw_thermal_slowdown"), (5, "sw_thermal_slowdown"), (6, "sw_power_cap"))
+                   if any(s[i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.samples[0][1]), "reasons": reasons, "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm (CPU)
+# ------------------------------------------------------------------------------------------------
+def run_reference(pref, fasta, outpref, nproc):
+    """wall time of the reference's query phase = full run minus a zero-read run (index load)."""
+    exe = ref_bin("danbing-tk")
+    base = [exe, "-k", str(K), "-kf", "4", "1", "-cth", str(CTH), "-ae", "-p", str(nproc), "-qs", pref]
+    empty = outpref + ".empty.fa"
+    open(empty, "w").close()
+    t0 = time.perf_counter()
+    subprocess.run(base + ["-fa", empty, "-o", outpref + ".e"], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    t_load = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    subprocess.run(base + ["-fa", fasta, "-o", outpref], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    t_all = time.perf_counter() - t0
+    return max(t_all - t_load, 1e-9), t_all, t_load
+
+
+def peaks():
+    fn = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(fn):
+        return float(json.load(open(fn))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--pairs", type=int, default=10_000_000, help="read pairs per GPU per step")
+    ap.add_argument("--loci", type=int, default=1000)
+    ap.add_argument("--frac-locus", type=float, default=0.05)
+    ap.add_argument("--cpu-sample", type=int, default=2_000_000, help="pairs given to the CPU reference")
+    ap.add_argument("--sub-batch", type=int, default=2_500_000, help="pairs per dbt_submit in the e2e loop")
+    ap.add_argument("--bucket-slots", type=int, default=0)
+    ap.add_argument("--table-load", type=float, default=0.0)
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--rrand", action="store_true", help="also measure the random-sector roofline R_rand")
+    a = ap.parse_args()
+    a.steps, a.warmup = max(a.steps, 1), max(a.warmup, 0)
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist           # plumbing only: rendezvous, barrier, max over ranks
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+
+    config = {"workload": f"synthetic {a.loci}-locus RPGG (8 haplotypes, 700 bp flanks), {a.pairs} simulated 150bp read pairs per GPU "
+                          f"({a.frac_locus:.0%} locus reads / rest background), align -k 21 -kf 4 1 -cth 45 -ae (asgn path, SURVEY F2)",
+              "pairs_per_gpu": a.pairs, "loci": a.loci, "k": K, "cth": CTH, "kf": [4, 1],
+              "l2_policy": "inputs larger than L2 (packed reads 1.3 GB/step >> 126 MB); no explicit flush"}
+
+    workdir = tempfile.mkdtemp(prefix="dbt_bench_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+    try:
+        if a.impl == "reference":
+            if rank != 0:
+                return
+            return reference_arm(a, config, workdir)
+        b200_arm(a, config, workdir, rank, world, local, dist)
+    finally:
+        shutil.rmtree(workdir, ignore_errors=True)
+        if dist is not None:
+            dist.destroy_process_group()
+
+
+def reference_arm(a, config, workdir):
+    if not ref_bin("danbing-tk"):
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/danbing-tk not built (needs /root/reference at build time)"}))
+        return
+    L = abi.load_library()
+    nproc = os.cpu_count() or 1
+    ix, pref, pool, hap_off = build_workload(a.loci, 20261104, workdir)
+    n = min(a.cpu_sample, a.pairs)
+    reads = np.empty(n * 2 * RLEN, np.uint8)
+    if L.dbt_device_count() > 0:
+        synth_reads(0, pool, hap_off, 0, n, 777, a.frac_locus, reads)
+    else:                                                     # no GPU for the generator: numpy background + locus mix
+        rng = np.random.default_rng(777)
+        reads[:] = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, len(reads))]
+    fa = os.path.join(workdir, "sample.fa")
+    write_fasta_sample(fa, reads, n)
+    times = []
+    for i in range(a.warmup + a.steps):
+        t_q, t_all, t_load = run_reference(pref, fa, os.path.join(workdir, "ref"), nproc)
+        if i >= a.warmup:
+            times.append(t_q)
+    ms = 1e3 * sum(times) / len(times)
+    v = n / (ms / 1e3)
+    print(json.dumps({"impl": "reference", "metric": "read pairs/sec (k=21, -ae)", "value": v, "unit": "read pairs/s", "n_gpus": a.gpus,
+                      "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+                      "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": config,
+                      "cpu_baseline": {"value": v, "unit": "read pairs/s", "cores": nproc, "kind": "reference",
+                                       "sample": f"first {n} pairs of the workload as FASTA in /dev/shm; query phase = wall minus a zero-read (index load) run"},
+                      "e2e": {"value": v, "unit": "read pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def b200_arm(a, config, workdir, rank, world, local, dist):
+    L = abi.load_library()
+    if L.dbt_device_count() <= local:
+        raise RuntimeError("bench.py needs a CUDA device per rank: libdanbing_b200 has no CPU fallback")
+    ix, pref, pool, hap_off = build_workload(a.loci, 20261104, workdir)
+    P = a.pairs
+    p = abi.default_params(k=K, cth=CTH, n_filter=4, nm_filter=1, nm_tr=40, flags=abi.F_KAM, max_read_len=RLEN,
+                           max_batch_pairs=P, device=local)
+    p.max_records = max(int(P * a.frac_locus * 1.5) + 4096, 65536)
+    p.bucket_slots = a.bucket_slots
+    p.table_load = a.table_load
+    t = time.time()
+    ctx = abi.Context(p, abi.make_index_struct(ix))
+    log(f"[bench r{rank}] index resident in HBM ({time.time()-t:.1f}s)")
+    stats = np.zeros(8, np.uint64)
+    abi.check(L, L.dbt_table_stats(ctx.h, abi.ptr(stats, abi.u64p)), "table_stats")
+    if world > 1:
+        import torch
+        idt = torch.zeros(abi.DBT_NCCL_ID_BYTES, dtype=torch.uint8)
+        if rank == 0:
+            idb = np.zeros(abi.DBT_NCCL_ID_BYTES, np.uint8)
+            abi.check(L, L.dbt_nccl_unique_id(abi.ptr(idb, abi.u8p)), "nccl id")
+            idt = torch.from_numpy(idb)
+        dist.broadcast(idt, 0)
+        idb = idt.numpy().copy()
+        abi.check(L, L.dbt_comm_init(ctx.h, world, rank, abi.ptr(idb, abi.u8p)), "comm init")
+
+    # ---- synthetic reads of this rank: pinned host ASCII (for e2e) ----
+    nbytes = P * 2 * RLEN
+    host, owner = abi.pinned_array(L, nbytes)
+    t = time.time()
+    synth_reads(local, pool, hap_off, rank * P, P, 777, a.frac_locus, host)
+    offsets_np = np.arange(2 * P + 1, dtype=np.uint64) * RLEN
+    off_pin, off_owner = abi.pinned_array(L, offsets_np.nbytes)
+    off_pin.view(np.uint64)[:] = offsets_np
+    offsets = off_pin.view(np.uint64)
+    log(f"[bench r{rank}] {P} pairs generated ({time.time()-t:.1f}s)")
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    def allmax(x):
+        if dist is None:
+            return x
+        import torch
+        tt = torch.tensor([x], dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return float(tt[0])
+
+    def allsum(x):
+        if dist is None:
+            return x
+        import torch
+        tt = torch.tensor([float(x)], dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.SUM)
+        return float(tt[0])
+
+    # ---- 1. kernel-only: reads resident in HBM ----
+    batch = ctx.make_batch(host, offsets)
+    abi.check(L, L.dbt_upload(ctx.h, C.byref(batch), 0), "upload")
+    abi.check(L, L.dbt_wait(ctx.h, 0), "wait")
+    res = abi.BatchResult()
+
+    def step():
+        abi.check(L, L.dbt_process(ctx.h, 0), "process")
+        if world > 1:
+            abi.check(L, L.dbt_allreduce(ctx.h), "allreduce")
+
+    for _ in range(a.warmup):
+        step()
+    abi.check(L, L.dbt_wait(ctx.h, 0), "wait")
+    launches0 = L.dbt_launch_count(ctx.h)
+    ktimes = np.zeros((a.steps, 8), np.float32)
+    kl = np.zeros(8, np.uint32)
+    barrier()
+    with ClockSampler(local) as clk:
+        ms = C.c_float()
+        abi.check(L, L.dbt_timer_start(ctx.h, 0), "timer")
+        t0 = time.perf_counter()
+        for i in range(a.steps):
+            step()
+            if a.steps <= 64:        # per-kernel CUDA-event times of this step (synchronises the slot)
+                abi.check(L, L.dbt_kernel_times(ctx.h, 0, ktimes[i].ctypes.data_as(C.POINTER(C.c_float)), abi.ptr(kl, abi.u32p)), "ktimes")
+        abi.check(L, L.dbt_timer_stop(ctx.h, 0, C.byref(ms)), "timer")
+        wall_ms = (time.perf_counter() - t0) * 1e3
+        barrier()
+        time.sleep(0.3)
+    launches = int(L.dbt_launch_count(ctx.h) - launches0)
+    dev_ms = float(ms.value) if world == 1 else wall_ms     # with the NCCL reduce in the step, the wall clock brackets both streams
+    step_ms = allmax(dev_ms) / a.steps
+    value = world * P / (step_ms / 1e3)
+    # counters of one step (fetch once, untimed)
+    abi.check(L, L.dbt_fetch(ctx.h, C.byref(res), 0), "fetch")
+    abi.check(L, L.dbt_wait(ctx.h, 0), "wait")
+    cnt = dict(zip(abi.COUNTER_NAMES, list(res.counters)))
+    kt = ktimes.mean(axis=0)
+    t_sub, t_cmp, t_cand = float(kt[1]), float(kt[2]), float(kt[3])
+
+    # ---- roofline of the dominant kernel (algorithmic bytes: SURVEY.md §8(d)) ----
+    nk = RLEN - K + 1
+    ncand = cnt["ncandidates"]
+    p_sub = cnt["nhash0"] + 2 * ncand                       # ++nhash skips the iteration that breaks (cpp:176)
+    p_as = cnt["nThreadingReads"] * nk                      # one classification probe per k-mer of pairs reaching assignTRkmc
+    bytes_sub = P * 75 + 32 * p_sub
+    bytes_cand = 32 * (cnt["nhash1"] + p_as) + 64 * cnt["ninc"]
+    peak, peak_src = peaks()
+    if t_cand >= t_sub:
+        dom, dom_ms, dom_bytes = "candidate_kernel", t_cand, bytes_cand
+    else:
+        dom, dom_ms, dom_bytes = "subfilter_kernel", t_sub, bytes_sub
+    ach = dom_bytes / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0
+    roofline = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                "kernel": dom, "kernel_ms": dom_ms, "algorithmic_bytes_per_launch": dom_bytes, "peak_source": peak_src,
+                "per_kernel_ms": {"subfilter": t_sub, "compaction": t_cmp, "candidate": t_cand},
+                "step_bytes": bytes_sub + bytes_cand, "step_GBps": (bytes_sub + bytes_cand) / (step_ms / 1e3) / 1e9}
+    if a.rrand and rank == 0:
+        rr = {}
+        for sect in (32, 64):
+            msr = C.c_float()
+            abi.check(L, L.dbt_random_gather_bench(local, 8 << 30, sect, 1 << 28, 3, C.byref(msr)), "rrand")
+            rr[f"{sect}B_Gsectors_per_s"] = (1 << 28) / (msr.value / 1e3) / 1e9
+        roofline["r_rand"] = rr
+
+    # ---- 2. end to end through the C ABI with host buffers (double-buffered sub-batches) ----
+    sb = min(a.sub_batch, P)
+    nsub = (P + sb - 1) // sb
+    stride = ctx.stride
+    recbuf = [np.zeros(p.max_records * stride, np.uint8) for _ in range(2)]
+    results = [abi.BatchResult() for _ in range(2)]
+    d2h = [0]
+
+    def e2e_step():
+        pending = [False, False]
+        nrec = 0
+        for j in range(nsub):
+            s = j & 1
+            if pending[s]:
+                abi.check(L, L.dbt_wait(ctx.h, s), "wait")
+                nrec += int(results[s].n_records)
+            b0, b1 = j * sb, min(P, (j + 1) * sb)
+            bb = ctx.make_batch(host, offsets[2 * b0: 2 * b1 + 1], first_pair_index=rank * P + b0)
+            results[s].capacity = p.max_records
+            results[s].records = abi.ptr(recbuf[s], abi.u8p)
+            abi.check(L, L.dbt_submit(ctx.h, C.byref(bb), C.byref(results[s]), s), "submit")
+            pending[s] = True
+        for s in range(2):
+            if pending[s]:
+                abi.check(L, L.dbt_wait(ctx.h, s), "wait")
+                nrec += int(results[s].n_records)
+        if world > 1:
+            abi.check(L, L.dbt_allreduce(ctx.h), "allreduce")
+        d2h[0] = nrec * stride + nsub * (abi.DBT_N_COUNTERS * 8 + 8)
+        return nrec
+
+    ctx.reset()
+    for _ in range(min(a.warmup, 2)):
+        e2e_step()
+    ctx.reset()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        nrec = e2e_step()
+    e2e_ms = allmax((time.perf_counter() - t0) * 1e3) / a.steps
+    e2e_value = world * P / (e2e_ms / 1e3)
+    e2e = {"value": e2e_value, "unit": "read pairs/s", "h2d_bytes_per_step": int(nbytes + offsets_np.nbytes),
+           "d2h_bytes_per_step": int(d2h[0]), "ms_per_step": e2e_ms, "kam_records_per_step": nrec,
+           "input": "pinned host ASCII reads + u64 offsets, packed to 2 bits on the device", "sub_batch_pairs": sb}
+    trkmc, kmc, nmap, tot = ctx.download()
+
+    # ---- 3. CPU reference on a bounded sample of the same reads, outputs diffed against the GPU ----
+    cpu = None
+    if rank == 0 and not a.no_cpu:
+        if ref_bin("danbing-tk"):
+            n = min(a.cpu_sample, P)
+            fa = os.path.join(workdir, "sample.fa")
+            write_fasta_sample(fa, host, n)
+            nproc = os.cpu_count() or 1
+            t_q, t_all, t_load = run_reference(pref, fa, os.path.join(workdir, "ref"), nproc)
+            # GPU on the same sample, compared through the reference's own output files
+            p2 = abi.default_params(k=K, cth=CTH, flags=0, max_read_len=RLEN, max_batch_pairs=n, device=local)
+            ctx2 = abi.Context(p2, abi.make_index_struct(rpgg_io.load_index(pref)))
+            ctx2.run(host, offsets[: 2 * n + 1], capacity=0)
+            g_tr, g_kmc, g_nmap, _ = ctx2.download()
+            ctx2.close()
+            ref_counts = rpgg_io.read_ar(os.path.join(workdir, "ref.trkmc.ar"))
+            # file-order GPU counts vs unordered_map-order reference dump: compare per locus as multisets via the text keys
+            same_sum = int(ref_counts.sum()) == int(g_tr.sum())
+            ref_summary = open(os.path.join(workdir, "ref.tr.summary.txt")).read()
+            g_summary = "".join(f"{int(x)}\t{int(y)}\n" for x, y in zip(g_nmap, g_kmc))
+            per_locus_ok = True
+            ro = np.concatenate([[0], np.cumsum(ix["tr_n"]).astype(np.int64)])
+            for l in range(len(ix["tr_n"])):
+                if not np.array_equal(np.sort(ref_counts[ro[l]:ro[l + 1]]), np.sort(g_tr[ro[l]:ro[l + 1]])):
+                    per_locus_ok = False
+                    break
+            cpu = {"value": n / t_q, "unit": "read pairs/s", "cores": nproc, "kind": "reference",
+                   "sample": f"first {n} pairs of rank 0's batch as FASTA in /dev/shm, `danbing-tk -k 21 -kf 4 1 -cth 45 -ae -p {nproc}` (kam lines to /dev/null); "
+                             f"query phase {t_q:.2f}s = wall {t_all:.2f}s minus zero-read index load {t_load:.2f}s",
+                   "parity_vs_gpu": {"tr_summary_identical": ref_summary == g_summary, "trkmc_total_identical": same_sum,
+                                     "trkmc_per_locus_multiset_identical": per_locus_ok}}
+        else:
+            cpu = {"value": None, "unit": "read pairs/s", "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
+
+    total_inc = allsum(cnt["ninc"])
+    if rank == 0:
+        out = {"metric": "read pairs/sec (k=21, -ae)", "value": value, "unit": "read pairs/s", "n_gpus": world, "steps": a.steps,
+               "warmup": a.warmup, "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+               "dtype": "u64", "data": "synthetic", "config": config, "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches,
+               "roofline": roofline, "cpu_baseline": cpu,
+               "counters_per_step_rank0": cnt, "tr_kmer_increments_per_step_all_ranks": total_inc,
+               "index_table": {"buckets": int(stats[0]), "slots_per_bucket": int(stats[1]), "keys": int(stats[2]),
+                               "overflowed_buckets": int(stats[4]), "displaced_keys": int(stats[5]), "bytes": int(stats[6])}}
+        print(json.dumps(out))
+    ctx.close()
+
+
+if __name__ == "__main__":
+    main()

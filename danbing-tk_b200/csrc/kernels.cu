@@ -610,6 +610,10 @@ __global__ void __launch_bounds__(CAND_WARPS_PER_BLOCK * 32) candidate_kernel(De
 
 		// ---- 13. record ----
 		const bool emit = trace || (okam && status == DBT_ST_COUNTED);
+		if (!emit && okam && c < rp.max_records) {
+			// the slot of a candidate that prints no kam line must not keep a stale record
+			if (lane == 0) reinterpret_cast<dbt_pair_record*>(sv.records + (uint64_t)c * rp.rec_stride)->status = (uint8_t)status;
+		}
 		if (emit) {
 			const uint64_t slot = trace ? (uint64_t)p : (uint64_t)c;
 			if (!trace && slot >= rp.max_records) { if (lane == 0) atomicOr(sv.ncand + 1, ERR_RECORD_OVERFLOW); }
