@@ -68,7 +68,7 @@ struct Slot {
 	cudaStream_t st = nullptr;
 	uint8_t* d_ascii = nullptr; uint64_t* d_offsets = nullptr;
 	uint64_t* d_packed[2] = {nullptr, nullptr}; uint16_t* d_meta[2] = {nullptr, nullptr};
-	uint32_t* d_passmask = nullptr; uint32_t* d_blocksum = nullptr; uint32_t* d_cand = nullptr; uint32_t* d_ncand = nullptr;
+	uint32_t* d_passmask = nullptr; uint32_t* d_blocksum = nullptr; uint32_t* d_cand = nullptr; uint32_t* d_ncand = nullptr; uint32_t* d_slow = nullptr;
 	uint8_t* d_records = nullptr; unsigned long long* d_counters = nullptr;
 	uint8_t* h_records = nullptr;            // pinned staging
 	uint64_t* h_counters = nullptr;          // pinned: DBT_N_COUNTERS u64 + 2 u32 (ncand, err)
@@ -95,7 +95,7 @@ struct dbt_ctx {
 	RunParams rp;
 	int B = 2, nsm = 0;
 	size_t smem_optin = 0;
-	unsigned cand_grid = 0;
+	unsigned cand_grid = 0, cand_grid_fast = 0;
 	bool index_loaded = false;
 	DevIndex ix{};
 	// owned device memory of the index
@@ -123,7 +123,7 @@ extern "C" int dbt_create(dbt_ctx** out, const dbt_params* p) {
 	if (p->max_read_len < p->k || p->max_read_len - p->k + 1 > 512) return fail(DBT_E_BADARG, "max_read_len=%u must satisfy k <= len <= k+511", p->max_read_len);
 	if (p->n_filter == 1 && p->nm_filter) return fail(DBT_E_BADARG, "-kf 1 x divides by zero in the reference (cpp:174)");
 	if (!p->max_batch_pairs) return fail(DBT_E_BADARG, "max_batch_pairs == 0");
-	if (p->bucket_slots && p->bucket_slots != 2 && p->bucket_slots != 4 && p->bucket_slots != 8) return fail(DBT_E_BADARG, "bucket_slots must be 2, 4 or 8");
+	if (p->bucket_slots && p->bucket_slots != 2 && p->bucket_slots != 4) return fail(DBT_E_BADARG, "bucket_slots must be 2 (32 B sector) or 4 (64 B)");
 	int ndev = dbt_device_count();
 	if (ndev <= 0) return fail(DBT_E_CUDA, "no CUDA device available (this library has no CPU fallback)");
 	if (p->device < 0 || p->device >= ndev) return fail(DBT_E_BADARG, "device %d out of range (%d devices)", p->device, ndev);
@@ -131,6 +131,7 @@ extern "C" int dbt_create(dbt_ctx** out, const dbt_params* p) {
 	if (!c) return fail(DBT_E_NOMEM, "host allocation");
 	c->p = *p;
 	if (c->p.max_nt == 0) c->p.max_nt = 2;
+	if (c->p.max_nt != 2) { delete c; return fail(DBT_E_BADARG, "max_nt must be 2: MAX_NT is a constant of the reference (cpp:31)"); }
 	if (c->p.max_records == 0) c->p.max_records = c->p.max_batch_pairs;
 	if (c->p.flags & DBT_F_TRACE) c->p.max_records = c->p.max_batch_pairs;
 	if (c->p.table_load <= 0.f || c->p.table_load > 0.9f) c->p.table_load = 0.4f;
@@ -149,31 +150,34 @@ extern "C" int dbt_create(dbt_ctx** out, const dbt_params* p) {
 	rp.max_read_len = p->max_read_len;
 	rp.nk_max = p->max_read_len - p->k + 1;
 	rp.nkp = round_up(rp.nk_max, 32);
+	rp.nkp = rp.nkp <= 5 * 32 ? 5 * 32 : (rp.nkp <= 8 * 32 ? 8 * 32 : 16 * 32);     // = 32 * MAXJ of the candidate_kernel instantiation
 	rp.umax = round_up(2 * rp.nk_max, 4);
-	rp.sortn = 2; while (rp.sortn < 2 * rp.nk_max) rp.sortn <<= 1;
+	rp.sortn = (rp.nkp / 32 <= 8) ? 512 : 1024;       // = 32*E of candidate_kernel<B, MAXJ>: E = 16 for MAXJ <= 8, else 32
 	rp.as_stride = round_up((rp.nk_max + 3) / 4, 8);
 	rp.rec_stride = (uint32_t)sizeof(dbt_pair_record) + 2 * rp.as_stride;
 	rp.max_records = c->p.max_records;
 	// must mirror the carve-up in candidate_kernel
 	size_t ws = 0;
 	ws += (size_t)2 * rp.lay.W64 * 8;                // pk
-	ws += (size_t)rp.sortn * 8;                      // sortk
+	ws += (size_t)2 * rp.nkp * 8;                    // pkey
 	ws += (size_t)4 * rp.nkp * 4;                    // pval, paux
 	ws += (size_t)3 * rp.umax * 4;                   // uval, uaux, unml
 	ws += (size_t)3 * VOTE_SMEM_SLOTS * 4;           // vote table
 	ws += (size_t)2 * rp.umax * 2;                   // utf, utr
 	ws += (size_t)(rp.umax + 2) * 2;                 // ustart
 	ws += (size_t)2 * rp.umax * 2;                   // umid, perm
-	ws += (size_t)2 * rp.nkp;                        // as
 	rp.warp_smem = round_up((uint32_t)ws, 16);
-	size_t block_smem = (size_t)rp.warp_smem * CAND_WARPS_PER_BLOCK;
+	size_t block_smem = (size_t)rp.warp_smem * CAND_WARPS_FAST;
 	if (block_smem > c->smem_optin) {
 		const size_t lim = c->smem_optin;
 		delete c;
 		return fail(DBT_E_CAPACITY, "max_read_len=%u needs %zu B shared memory per block (> %zu)", p->max_read_len, block_smem, lim);
 	}
-	unsigned blocks_per_sm = (unsigned)std::max<size_t>(1, std::min<size_t>(8, (size_t)(prop.sharedMemPerMultiprocessor - 1024) / (block_smem + 1024)));
+	const size_t slow_smem = (size_t)rp.warp_smem * CAND_WARPS_SLOW;
+	unsigned blocks_per_sm = (unsigned)std::max<size_t>(1, std::min<size_t>(4, (size_t)(prop.sharedMemPerMultiprocessor - 1024) / (slow_smem + 1024)));
 	c->cand_grid = (unsigned)c->nsm * blocks_per_sm;
+	unsigned fast_per_sm = (unsigned)std::max<size_t>(1, std::min<size_t>(2, (size_t)(prop.sharedMemPerMultiprocessor - 1024) / (block_smem + 1024)));
+	c->cand_grid_fast = (unsigned)c->nsm * fast_per_sm;
 	*out = c;
 	return DBT_OK;
 }
@@ -182,7 +186,7 @@ static void free_slot(Slot& s) {
 	if (s.st) cudaStreamSynchronize(s.st);
 	cudaFree(s.d_ascii); cudaFree(s.d_offsets);
 	for (int m = 0; m < 2; ++m) { cudaFree(s.d_packed[m]); cudaFree(s.d_meta[m]); }
-	cudaFree(s.d_passmask); cudaFree(s.d_blocksum); cudaFree(s.d_cand); cudaFree(s.d_ncand); cudaFree(s.d_records); cudaFree(s.d_counters);
+	cudaFree(s.d_passmask); cudaFree(s.d_blocksum); cudaFree(s.d_cand); cudaFree(s.d_ncand); cudaFree(s.d_slow); cudaFree(s.d_records); cudaFree(s.d_counters);
 	if (s.h_records) cudaFreeHost(s.h_records);
 	if (s.h_counters) cudaFreeHost(s.h_counters);
 	for (auto& e : s.ev) if (e) cudaEventDestroy(e);
@@ -224,7 +228,8 @@ static int ensure_slot(dbt_ctx* c, int si) {
 	TRY(dev_alloc(&s.d_passmask, nwords, "passmask"));
 	TRY(dev_alloc(&s.d_blocksum, (nwords + COMPACT_WORDS_H - 1) / COMPACT_WORDS_H + 1, "blocksum"));
 	TRY(dev_alloc(&s.d_cand, P, "cand"));
-	TRY(dev_alloc(&s.d_ncand, 2, "ncand"));
+	TRY(dev_alloc(&s.d_ncand, 4, "ncand"));
+	TRY(dev_alloc(&s.d_slow, P, "slow list"));
 	TRY(dev_alloc(&s.d_counters, DBT_N_COUNTERS, "counters"));
 	const bool want_records = (c->p.flags & (DBT_F_KAM | DBT_F_TRACE)) != 0;
 	if (want_records) {
@@ -338,7 +343,7 @@ extern "C" int dbt_load_index(dbt_ctx* c, const dbt_index* in) {
 		c->ix.permtab_maxU = maxU;
 	}
 	// vote fallback scratch: one epoch-tagged hits array per resident warp
-	const uint64_t nwarps = (uint64_t)c->cand_grid * CAND_WARPS_PER_BLOCK;
+	const uint64_t nwarps = (uint64_t)c->cand_grid * CAND_WARPS_SLOW;
 	TRY(dev_alloc(&c->d_vote_scratch, nwarps * (nloci + 1), "vote scratch"));
 	TRY(dev_alloc(&c->d_vote_epoch, nwarps, "vote epoch"));
 	CU(cudaMemsetAsync(c->d_vote_scratch, 0, nwarps * (nloci + 1) * 8, st));
@@ -422,7 +427,7 @@ extern "C" void dbt_host_free(void* p) { if (p) cudaFreeHost(p); }
 static SlotView slot_view(const dbt_ctx* c, const Slot& s) {
 	SlotView v;
 	v.packed[0] = s.d_packed[0]; v.packed[1] = s.d_packed[1]; v.meta[0] = s.d_meta[0]; v.meta[1] = s.d_meta[1];
-	v.passmask = s.d_passmask; v.blocksum = s.d_blocksum; v.cand = s.d_cand; v.ncand = s.d_ncand; v.records = s.d_records;
+	v.passmask = s.d_passmask; v.blocksum = s.d_blocksum; v.cand = s.d_cand; v.ncand = s.d_ncand; v.slow = s.d_slow; v.records = s.d_records;
 	v.counters = s.d_counters; v.npairs = s.npairs; v.first_pair_index = s.first_pair_index;
 	(void)c;
 	return v;
@@ -444,7 +449,7 @@ extern "C" int dbt_upload(dbt_ctx* c, const dbt_batch* b, int slot) {
 	if (b->npairs > c->p.max_batch_pairs) return fail(DBT_E_CAPACITY, "npairs=%llu > max_batch_pairs=%u", (unsigned long long)b->npairs, c->p.max_batch_pairs);
 	s.npairs = b->npairs; s.first_pair_index = b->first_pair_index; s.processed = false; s.ev_pack = false;
 	const RunParams& rp = c->rp;
-	CU(cudaMemsetAsync(s.d_ncand, 0, 8, s.st));
+	CU(cudaMemsetAsync(s.d_ncand, 0, 16, s.st));
 	if (b->npairs) {
 		if (!b->bases) return fail(DBT_E_BADARG, "null bases");
 		if (b->layout == DBT_LAYOUT_ASCII) {
@@ -478,12 +483,13 @@ extern "C" int dbt_process(dbt_ctx* c, int slot) {
 	SlotView sv = slot_view(c, s);
 	CU(cudaMemsetAsync(s.d_counters, 0, DBT_N_COUNTERS * 8, s.st));
 	CU(cudaMemsetAsync(s.d_ncand, 0, 4, s.st));
+	CU(cudaMemsetAsync(s.d_ncand + 2, 0, 4, s.st));
 	CU(cudaEventRecord(s.ev[1], s.st));
 	CU(launch_subfilter(s.st, c->B, c->nsm, c->ix, c->rp, sv)); ++c->launches;
 	CU(cudaEventRecord(s.ev[2], s.st));
 	if (s.npairs) { CU(launch_compact(s.st, sv)); c->launches += 3; }
 	CU(cudaEventRecord(s.ev[3], s.st));
-	CU(launch_candidate(s.st, c->B, c->cand_grid, c->ix, c->rp, sv)); ++c->launches;
+	CU(launch_candidate(s.st, c->B, c->cand_grid_fast, c->cand_grid, c->ix, c->rp, sv)); c->launches += 2;
 	CU(cudaEventRecord(s.ev[4], s.st));
 	s.processed = true; s.ev_proc = true;
 	return DBT_OK;
@@ -598,7 +604,7 @@ extern "C" int dbt_kernel_times(dbt_ctx* c, int slot, float ms[8], uint32_t laun
 	if (s.ev_proc) {
 		CU(cudaEventElapsedTime(&ms[KT_SUBFILTER], s.ev[1], s.ev[2])); launches[KT_SUBFILTER] = 1;
 		CU(cudaEventElapsedTime(&ms[KT_COMPACT], s.ev[2], s.ev[3])); launches[KT_COMPACT] = 3;
-		CU(cudaEventElapsedTime(&ms[KT_CANDIDATE], s.ev[3], s.ev[4])); launches[KT_CANDIDATE] = 1;
+		CU(cudaEventElapsedTime(&ms[KT_CANDIDATE], s.ev[3], s.ev[4])); launches[KT_CANDIDATE] = 2;
 	}
 	return DBT_OK;
 }

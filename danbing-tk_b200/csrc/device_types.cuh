@@ -9,7 +9,8 @@ namespace dbt {
 
 constexpr uint32_t NAN32 = 0xFFFFFFFFu;
 constexpr int VOTE_SMEM_SLOTS = 64;          // per-pair shared-memory (locus -> hits1,hits2) entries
-constexpr int CAND_WARPS_PER_BLOCK = 4;
+constexpr int CAND_WARPS_FAST = 8;             // phase-synchronous kernel: warps per block (2 blocks / SM)
+constexpr int CAND_WARPS_SLOW = 4;             // generic kernel
 
 // resident RPGG index
 struct DevIndex {
@@ -48,7 +49,8 @@ struct SlotView {
 	uint32_t* passmask;         // bit per pair: passed subfilter
 	uint32_t* blocksum;         // compaction scratch
 	uint32_t* cand;             // candidate pair ids, ascending
-	uint32_t* ncand;            // [0] = number of candidates, [1] = error flags
+	uint32_t* ncand;            // [0] = number of candidates, [1] = error flags, [2] = length of slow[]
+	uint32_t* slow;             // candidate ordinals left to the generic kernel
 	uint8_t*  records;
 	unsigned long long* counters;   // DBT_N_COUNTERS
 	uint64_t npairs, first_pair_index;

@@ -10,7 +10,6 @@
 //   index build        A14     bulk insert + per-locus class fill
 // "cpp" = src/aQueryFasta_thread.cpp, "h" = src/aQueryFasta_thread.h of the reference.
 #include "device_types.cuh"
-#include "introsort.cuh"
 
 namespace dbt {
 
@@ -220,448 +219,11 @@ __global__ void __launch_bounds__(256) compact_scatter_kernel(SlotView sv) {
 	}
 }
 
-// ============================================================================================
-// candidate_kernel: one warp per pair that survived subfilter
-// ============================================================================================
-struct Asgn { uint32_t idx; uint64_t fc, rc; };               // asgn_t, cpp:146-149
+}  // namespace dbt
 
-__device__ __forceinline__ void updatetop2(uint64_t cf, uint32_t ind, uint64_t cr, Asgn& top, Asgn& second) {   // cpp:331-347
-	if (cf + cr > top.fc + top.rc) {
-		if (top.idx != ind) { second = top; top.idx = ind; }
-		top.fc = cf; top.rc = cr;
-	} else if (cf + cr > second.fc + second.rc) {
-		second.idx = ind; second.fc = cf; second.rc = cr;
-	}
-}
+#include "candidate.cuh"
 
-// per-pair hits1/hits2 (cpp:432-434): small shared-memory table, falling back to a per-warp
-// epoch-tagged global array when a pair touches more than VOTE_SMEM_SLOTS loci
-struct VoteHits {
-	uint32_t* lkey; uint32_t* lf; uint32_t* lr;    // shared memory, VOTE_SMEM_SLOTS entries, key = locus+1
-	uint64_t* scratch; uint32_t epoch; uint32_t used;
-	__device__ __forceinline__ void add(uint32_t locus, uint32_t df, uint32_t dr, uint32_t& f, uint32_t& r) {
-		uint32_t h = (locus * 2654435761u) >> 26;            // 6 bits
-		for (int probe = 0; probe < VOTE_SMEM_SLOTS; ++probe) {
-			uint32_t s = (h + probe) & (VOTE_SMEM_SLOTS - 1);
-			uint32_t kk = lkey[s];
-			if (kk == locus + 1) { f = (lf[s] += df); r = (lr[s] += dr); return; }
-			if (kk == 0) {
-				if (used >= VOTE_SMEM_SLOTS - 8) break;          // keep the table sparse; spill to global
-				lkey[s] = locus + 1; lf[s] = df; lr[s] = dr; ++used; f = df; r = dr; return;
-			}
-		}
-		uint64_t e = scratch[locus];
-		uint32_t ef = 0, er = 0;
-		if ((uint32_t)(e >> 40) == epoch) { ef = (uint32_t)(e >> 20) & 0xFFFFF; er = (uint32_t)e & 0xFFFFF; }
-		ef += df; er += dr;
-		scratch[locus] = ((uint64_t)epoch << 40) | ((uint64_t)(ef & 0xFFFFF) << 20) | (er & 0xFFFFF);
-		f = ef; r = er;
-	}
-};
-
-// class/idx word of an index entry with respect to locus `loc` (0 = k-mer unknown in that locus)
-__device__ __forceinline__ uint32_t classify(const DevIndex& ix, uint32_t val, uint32_t aux, uint32_t loc) {
-	if (aux == AUX_MISS) return 0;
-	if (!(val & 1)) return ((val >> 1) == loc) ? aux : 0;
-	uint32_t off = val >> 1, n = __ldg(ix.vv + off);
-	for (uint32_t j = 1; j <= n; ++j) if (__ldg(ix.vv + off + j) == loc) return __ldg(ix.vv_aux + off + j);
-	return 0;
-}
-
-struct MateOut { int si, ei, si_, ei_, ti, nt, bs, af, rm; };
-
-// assignTRkmc state machine (cpp:1477-1555) over the 0/1/2 annotation of one mate; one lane.
-__device__ void assign_state_machine(const uint8_t* as, int nk, uint32_t ntr8, uint32_t max_nt, uint32_t nm_tr, MateOut& r) {
-	int s = 0, s_ = 0, s__ = 0;
-	int ti2 = -1, si1 = -1, ei1 = -1, si2 = -1, ei2 = -1;
-	for (int i = 0; i < nk; ++i) {
-		s = as[i];
-		if (s && s__ && s != s__) {
-			++r.nt;
-			if ((uint32_t)r.nt > max_nt) { r.af = 1; r.rm = 1; return; }
-			if (r.nt == 1) { r.ti = i; if (s_) { si1 = -1; ei1 = -1; } }
-			else if (r.nt == 2) {
-				if (r.bs == 2) { r.af = 1; r.rm = 1; return; }
-				ti2 = i; if (s_) { si2 = -1; ei2 = -1; }
-			}
-		}
-		if (!r.bs && s) r.bs = s;
-		if (!s) {
-			if (r.nt == 0) { if (!s_) ++ei1; else { si1 = i; ei1 = i + 1; } }
-			if (r.nt == 1) { if (!s_) ++ei2; else { si2 = i; ei2 = i + 1; } }
-		}
-		s_ = s;
-		if (s) s__ = s;
-	}
-	const int ti1 = r.ti;
-	if (r.nt == 0) {
-		if (r.bs != 2) { r.af = 1; r.rm = 1; return; }
-		r.si = 0; r.ei = nk; r.si_ = 0; r.ei_ = nk;
-	} else if (r.nt == 1) {
-		if (r.bs == 1) { r.si = si1 >= 0 ? (si1 + ei1) / 2 : ti1; r.ei = nk; r.si_ = si1 >= 0 ? ei1 : ti1; r.ei_ = nk; }
-		else           { r.si = 0; r.ei = si1 >= 0 ? (si1 + ei1) / 2 : ti1; r.si_ = 0; r.ei_ = si1 >= 0 ? si1 : ti1; }
-	} else {
-		if (ntr8 < nm_tr) { r.af = 1; r.rm = 1; return; }
-		r.si = (si1 >= 0 ? (si1 + ei1) / 2 : ti1);
-		r.ei = (si2 >= 0 ? (si2 + ei2) / 2 : ti2);
-		r.si_ = ei1 >= 0 ? ei1 : ti1;
-		r.ei_ = si2 >= 0 ? si2 : ti2;
-	}
-}
-
-template <int B, int MAXJ>
-__global__ void __launch_bounds__(CAND_WARPS_PER_BLOCK * 32) candidate_kernel(DevIndex ix, RunParams rp, SlotView sv) {
-	extern __shared__ __align__(16) uint8_t smem_raw[];
-	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-	const uint32_t gwarp = blockIdx.x * CAND_WARPS_PER_BLOCK + wib;
-	const uint32_t nwarps = gridDim.x * CAND_WARPS_PER_BLOCK;
-	const uint32_t W64 = rp.lay.W64, WB = rp.lay.WB, K = rp.k, NKP = rp.nkp, UMAX = rp.umax, SORTN = rp.sortn;
-	const bool okam = (rp.flags & DBT_F_KAM) != 0, trace = (rp.flags & DBT_F_TRACE) != 0;
-
-	// ---- shared-memory carve-up (per warp) ----
-	uint8_t* ws = smem_raw + (size_t)wib * rp.warp_smem;
-	uint64_t* pk    = reinterpret_cast<uint64_t*>(ws);                  // [2][W64] packed records
-	uint64_t* sortk = pk + 2 * W64;                                     // [SORTN]  key<<10 | mate<<9 | pos
-	uint32_t* pval  = reinterpret_cast<uint32_t*>(sortk + SORTN);       // [2][NKP] index value per position
-	uint32_t* paux  = pval + 2 * NKP;                                   // [2][NKP] aux word or AUX_MISS
-	uint32_t* uval  = paux + 2 * NKP;                                   // [UMAX]   unique k-mers: value
-	uint32_t* uaux  = uval + UMAX;
-	uint32_t* unml  = uaux + UMAX;                                      // number of mapped loci (cpp:314-317)
-	uint32_t* lkey  = unml + UMAX;                                      // vote table
-	uint32_t* lf    = lkey + VOTE_SMEM_SLOTS;
-	uint32_t* lr    = lf + VOTE_SMEM_SLOTS;
-	uint16_t* utf   = reinterpret_cast<uint16_t*>(lr + VOTE_SMEM_SLOTS);// true multiplicity in mate 0 / mate 1
-	uint16_t* utr   = utf + UMAX;
-	uint16_t* ustart = utr + UMAX;                                      // [UMAX+2] group start in the sorted array
-	uint16_t* umid  = ustart + UMAX + 2;                                // first mate-1 element of the group
-	uint16_t* perm  = umid + UMAX;                                      // visiting order (cpp:320-327)
-	uint8_t*  as    = reinterpret_cast<uint8_t*>(perm + UMAX);          // [2][NKP] 0 unknown / 1 flank / 2 TR
-
-	uint32_t c_kf = 0, c_laf = 0, c_qc = 0, c_thr = 0, c_asgn = 0, c_h1 = 0, c_inc = 0;   // lane-0 accumulators
-	uint32_t epoch = ix.vote_epoch[gwarp];
-	uint64_t* scratch = ix.vote_scratch + (uint64_t)gwarp * (ix.nloci + 1);
-	const uint32_t ncand = sv.ncand[0];
-
-	for (uint32_t c = gwarp; c < ncand; c += nwarps) {
-		const uint32_t p = sv.cand[c];
-		__syncwarp();
-		// ---- 1. packed records -> shared ----
-		for (uint32_t i = lane; i < 2 * W64; i += 32) {
-			uint32_t m = i >= W64;
-			pk[i] = sv.packed[m][(uint64_t)p * W64 + (i - m * W64)];
-		}
-		const uint32_t len0 = sv.meta[0][p] & META_LENMASK, len1 = sv.meta[1][p] & META_LENMASK;
-		const uint32_t nk[2] = { len0 - K + 1, len1 - K + 1 };
-		for (uint32_t i = lane; i < VOTE_SMEM_SLOTS; i += 32) lkey[i] = 0;
-		__syncwarp();
-
-		// ---- 2. all canonical k-mers + index probes (A2 + the lookups of kfilter, cpp:207/218) ----
-		uint64_t key[2][MAXJ];
-#pragma unroll
-		for (int m = 0; m < 2; ++m) {
-#pragma unroll
-			for (int j = 0; j < MAXJ; ++j) {
-				uint32_t i = j * 32 + lane;
-				key[m][j] = (i < nk[m]) ? canonical_kmer_at(pk + m * W64, WB, i, K) : KMER_INVALID;
-			}
-#pragma unroll
-			for (int j = 0; j < MAXJ; ++j) {
-				uint32_t i = j * 32 + lane;
-				uint32_t v = 0, a = AUX_MISS;
-				if (key[m][j] != KMER_INVALID) { if (!table_lookup<B>(ix.table, key[m][j], v, a)) a = AUX_MISS; }
-				if (i < NKP) { pval[m * NKP + i] = v; paux[m * NKP + i] = a; }
-			}
-		}
-		__syncwarp();
-
-		// ---- 3. kfilter (cpp:190-224): abort a mate at its (nk-cth+1)-th miss ----
-		int kf[2], rm[2], hf[2] = {0, 0};
-		kf[0] = nk[0] < rp.cth; kf[1] = nk[1] < rp.cth;
-		rm[0] = kf[0]; rm[1] = kf[1];
-		uint32_t nhash1 = 0;
-		if (!(rm[0] && rm[1])) {
-#pragma unroll
-			for (int m = 0; m < 2; ++m) {
-				if (rm[m]) continue;
-				const uint32_t max_ns = nk[m] - rp.cth;
-				uint32_t cum = 0, probes = nk[m]; bool aborted = false;
-#pragma unroll
-				for (int j = 0; j < MAXJ; ++j) {
-					uint32_t i = j * 32 + lane;
-					bool miss = (i < nk[m]) && (paux[m * NKP + i] == AUX_MISS);
-					uint32_t mm = __ballot_sync(0xffffffffu, miss);
-					if (!aborted && cum + __popc(mm) > max_ns) {
-						aborted = true;
-						probes = j * 32 + __fns(mm, 0, max_ns + 1 - cum) + 1;
-					}
-					cum += __popc(mm);
-				}
-				nhash1 += probes;
-				kf[m] = aborted; rm[m] |= kf[m];
-			}
-		}
-		if (lane == 0) { c_kf += kf[0] + kf[1]; c_h1 += nhash1; }
-
-		int status = -1;
-		uint32_t dst = (uint32_t)ix.nloci, dst0 = NAN32, fc = 0, rc = 0;
-		MateOut mo[2];
-#pragma unroll
-		for (int m = 0; m < 2; ++m) { mo[m].si = mo[m].ei = mo[m].si_ = mo[m].ei_ = mo[m].ti = -1; mo[m].nt = 0; mo[m].bs = 0; mo[m].af = 0; mo[m].rm = 0; }
-		uint32_t nas[2] = {0, 0};
-		if (rm[0] && rm[1]) status = DBT_ST_KFILTERED;
-
-		if (status < 0) {
-			// ---- 4. hits of the surviving mates -> sort array (countDupRemove, cpp:263-266) ----
-			uint32_t n = 0;
-#pragma unroll
-			for (int m = 0; m < 2; ++m) {
-				if (rm[m]) continue;
-#pragma unroll
-				for (int j = 0; j < MAXJ; ++j) {
-					uint32_t i = j * 32 + lane;
-					bool hit = (i < nk[m]) && (paux[m * NKP + i] != AUX_MISS);
-					uint32_t hm = __ballot_sync(0xffffffffu, hit);
-					if (hit) sortk[n + __popc(hm & ((1u << lane) - 1))] = (key[m][j] << 10) | ((uint64_t)m << 9) | i;
-					n += __popc(hm);
-				}
-			}
-			__syncwarp();
-			// ---- 5. bitonic sort, ascending, virtual +inf padding above n (flip formulation) ----
-			uint32_t npow = 2; while (npow < n) npow <<= 1;
-			for (uint32_t size = 2; size <= npow; size <<= 1) {
-				for (uint32_t t = lane; t < npow / 2; t += 32) {            // flip step
-					uint32_t blk = t / (size / 2), o = t % (size / 2);
-					uint32_t a = blk * size + o, b = blk * size + size - 1 - o;
-					if (b < n) { uint64_t x = sortk[a], y = sortk[b]; if (x > y) { sortk[a] = y; sortk[b] = x; } }
-				}
-				__syncwarp();
-				for (uint32_t stride = size / 4; stride >= 1; stride >>= 1) {
-					for (uint32_t t = lane; t < npow / 2; t += 32) {
-						uint32_t a = 2 * stride * (t / stride) + (t % stride), b = a + stride;
-						if (b < n) { uint64_t x = sortk[a], y = sortk[b]; if (x > y) { sortk[a] = y; sortk[b] = x; } }
-					}
-					__syncwarp();
-				}
-			}
-			// ---- 6. collapse equal keys (cpp:278-295): U unique entries with per-mate multiplicities ----
-			uint32_t U = 0;
-			for (uint32_t base = 0; base < n; base += 32) {
-				uint32_t i = base + lane;
-				bool head = false, mid = false; uint64_t e = 0;
-				if (i < n) {
-					e = sortk[i];
-					uint64_t prev = i ? sortk[i - 1] : 0;
-					head = (i == 0) || ((prev >> 10) != (e >> 10));
-					mid = ((e >> 9) & 1) && (head || !((prev >> 9) & 1));
-				}
-				uint32_t hm = __ballot_sync(0xffffffffu, head);
-				uint32_t u = U + __popc(hm & ((2u << lane) - 1)) - 1;       // group of element i
-				if (head) {
-					ustart[u] = (uint16_t)i; umid[u] = 0xFFFF;
-					uint32_t m = (uint32_t)(e >> 9) & 1, pos = (uint32_t)e & 511;
-					uval[u] = pval[m * NKP + pos]; uaux[u] = paux[m * NKP + pos];
-				}
-				__syncwarp();
-				if (mid) umid[u] = (uint16_t)i;
-				U += __popc(hm);
-			}
-			if (lane == 0) ustart[U] = (uint16_t)n;
-			__syncwarp();
-			bool odd = false; uint32_t wsum8 = 0;
-			for (uint32_t u = lane; u < U; u += 32) {
-				uint32_t s = ustart[u], e = ustart[u + 1], md = umid[u] == 0xFFFF ? e : umid[u];
-				utf[u] = (uint16_t)(md - s); utr[u] = (uint16_t)(e - md);
-				wsum8 += ((md - s) & 0xFF) + ((e - md) & 0xFF);              // PE_KMC is uint8 (cpp:42)
-				uint32_t v = uval[u];
-				uint32_t nm = 1;
-				if (v & 1) { nm = __ldg(ix.vv + (v >> 1)); odd = true; }
-				unml[u] = nm;
-			}
-			const bool any_odd = __any_sync(0xffffffffu, odd);
-			const uint32_t total = warp_sum(wsum8);                           // dupsum of countRemain (cpp:300)
-			// ---- 7. visiting order = std::sort by number of mapped loci (cpp:320-327) ----
-			if (!any_odd && U <= ix.permtab_maxU) {
-				const uint16_t* pt = ix.permtab + (size_t)U * (U - 1) / 2;
-				for (uint32_t u = lane; u < U; u += 32) perm[u] = pt[u];
-			} else {
-				for (uint32_t u = lane; u < U; u += 32) perm[u] = (uint16_t)u;
-				__syncwarp();
-				if (lane == 0) { IntroSort<uint16_t, uint32_t> s{perm, unml}; s.sort((int)U); }
-			}
-			__syncwarp();
-			// ---- 8. find_matching_locus (cpp:364-422), one lane ----
-			Asgn top = {NAN32, 0, 0}, second = {NAN32, 0, 0};
-			if (lane == 0) {
-				VoteHits vh{lkey, lf, lr, scratch, epoch + 1, 0};
-				uint64_t rem = total;
-				const uint64_t cth = rp.cth;
-				for (uint32_t i = 0; i < U; ++i) {
-					const uint32_t u = perm[i];
-					const uint32_t vi = uval[u], df = utf[u] & 0xFF, dr = utr[u] & 0xFF;
-					rem = (i + 1 < U) ? rem - df - dr : 0;                    // remain[i] (cpp:302-305; last entry stays 0)
-					if (vi & 1) {
-						uint32_t j0 = (vi >> 1) + 1, j1 = j0 + __ldg(ix.vv + (vi >> 1));
-						for (; j0 < j1; ++j0) {
-							uint32_t locus = __ldg(ix.vv + j0), f, r;
-							vh.add(locus, df, dr, f, r);
-							updatetop2(f, locus, r, top, second);
-						}
-					} else {
-						uint32_t locus = vi >> 1, f, r;
-						vh.add(locus, df, dr, f, r);
-						updatetop2(f, locus, r, top, second);
-					}
-					if (!((top.fc + top.rc - second.fc - second.rc) < rem)) {        // not get_acm2 (cpp:383)
-						uint32_t j = i; uint64_t remj = rem;
-						while ((top.fc < cth && cth - top.fc <= remj) || (top.rc < cth && cth - top.rc <= remj)) {   // get_acm1
-							if (++j >= U) break;
-							const uint32_t uj = perm[j];
-							const uint32_t vj = uval[uj], dfj = utf[uj] & 0xFF, drj = utr[uj] & 0xFF;
-							remj = (j + 1 < U) ? remj - dfj - drj : 0;
-							if (vj & 1) {
-								uint32_t j0 = (vj >> 1) + 1, j1 = j0 + __ldg(ix.vv + (vj >> 1));
-								for (; j0 < j1; ++j0) if (__ldg(ix.vv + j0) == top.idx) { top.fc += dfj; top.rc += drj; break; }
-							} else if ((vj >> 1) == top.idx) { top.fc += dfj; top.rc += drj; }
-						}
-						break;
-					}
-				}
-			}
-			// the global fallback may have been written under epoch+1: retire that epoch
-			epoch += 1;
-			if (epoch >= 0xFFFFF0u) {                       // 24-bit tag about to wrap: clear this warp's scratch
-				for (uint64_t i = lane; i < ix.nloci + 1; i += 32) scratch[i] = 0;
-				epoch = 0;
-			}
-			dst0 = __shfl_sync(0xffffffffu, top.idx, 0);
-			fc = (uint32_t)__shfl_sync(0xffffffffu, (uint32_t)top.fc, 0);
-			rc = (uint32_t)__shfl_sync(0xffffffffu, (uint32_t)top.rc, 0);
-			// ---- 9. countHit tail (cpp:436-452) ----
-			const bool test1 = fc >= rp.cth && rc >= rp.cth, test2 = (fc + rc) >= 2 * rp.cth;
-			if ((test1 || test2) && dst0 != NAN32) dst = dst0;
-			else { hf[0] = 1 & !rm[0]; hf[1] = 1 & !rm[1]; rm[0] = rm[1] = 1; status = DBT_ST_UNASSIGNED; if (lane == 0) c_laf += hf[0] + hf[1]; }
-
-			// ---- 10. QC gate (cpp:2059-2062) ----
-			if (status < 0 && (rp.flags & DBT_F_QC) && ix.qc && !ix.qc[dst]) { status = DBT_ST_QCFILTERED; if (lane == 0) c_qc += 2 - rm[0] - rm[1]; }
-
-			if (status < 0) {
-				if (lane == 0) c_thr += 2;
-				// ---- 11. assignTRkmc (cpp:1450-1556) against the tables of destLocus0 ----
-				uint32_t ntr8[2] = {0, 0};
-#pragma unroll
-				for (int m = 0; m < 2; ++m) {
-					if (!okam && rm[m]) continue;                           // cpp:1451
-					nas[m] = nk[m];
-					uint32_t cnt = 0;
-					for (uint32_t i = lane; i < NKP; i += 32) {
-						uint32_t cls = 0;
-						if (i < nk[m]) cls = classify(ix, pval[m * NKP + i], paux[m * NKP + i], dst0) >> AUX_CLASS_SHIFT;
-						as[m * NKP + i] = (uint8_t)cls;
-						cnt += (cls == 2);
-					}
-					ntr8[m] = warp_sum(cnt) & 0xFF;                         // uint8_t ntr (cpp:1454)
-				}
-				__syncwarp();
-				if (lane < 2) {
-					const int m = lane;
-					MateOut r = mo[m];
-					r.rm = rm[m];
-					if (!(!okam && rm[m])) {
-						if (rm[m]) { r.nt = -1; r.bs = -1; r.ti = -1; }       // cpp:1470-1475
-						else assign_state_machine(as + m * NKP, (int)nk[m], ntr8[m], rp.max_nt, rp.nm_tr, r);
-					}
-					mo[m] = r;
-				}
-#pragma unroll
-				for (int m = 0; m < 2; ++m) {
-					mo[m].si = __shfl_sync(0xffffffffu, mo[m].si, m); mo[m].ei = __shfl_sync(0xffffffffu, mo[m].ei, m);
-					mo[m].si_ = __shfl_sync(0xffffffffu, mo[m].si_, m); mo[m].ei_ = __shfl_sync(0xffffffffu, mo[m].ei_, m);
-					mo[m].ti = __shfl_sync(0xffffffffu, mo[m].ti, m); mo[m].nt = __shfl_sync(0xffffffffu, mo[m].nt, m);
-					mo[m].bs = __shfl_sync(0xffffffffu, mo[m].bs, m); mo[m].af = __shfl_sync(0xffffffffu, mo[m].af, m);
-					mo[m].rm = __shfl_sync(0xffffffffu, mo[m].rm, m);
-					rm[m] = mo[m].rm;
-				}
-				// ---- 12. accumulate (cpp:2145-2158) ----
-				if (rm[0] && rm[1]) { dst = (uint32_t)ix.nloci; status = DBT_ST_ASGN_REMOVED; }
-				else {
-					status = DBT_ST_COUNTED;
-					const int nr = 2 - rm[0] - rm[1];
-					if (lane == 0) {
-						atomicAdd(ix.nmapread + dst, (uint32_t)nr);
-						c_asgn += nr;
-						const int span = (mo[0].ei - mo[0].si) + (mo[1].ei - mo[1].si);
-						atomicAdd(reinterpret_cast<unsigned long long*>(ix.kmc + dst), (unsigned long long)(long long)span);
-					}
-					uint32_t inc_sum = 0;
-					for (uint32_t u = lane; u < U; u += 32) {
-						uint32_t inc = (rm[0] ? 0u : utf[u]) + (rm[1] ? 0u : utr[u]);
-						if (!inc) continue;
-						uint32_t ca = classify(ix, uval[u], uaux[u], dst0);
-						if ((ca >> AUX_CLASS_SHIFT) == 2) {
-							atomicAdd(reinterpret_cast<unsigned long long*>(ix.counts + (ca & AUX_IDX_MASK)), (unsigned long long)inc);
-							inc_sum += inc;
-						}
-					}
-					inc_sum = warp_sum(inc_sum);
-					if (lane == 0) c_inc += inc_sum;
-				}
-			}
-		}
-
-		// ---- 13. record ----
-		const bool emit = trace || (okam && status == DBT_ST_COUNTED);
-		if (!emit && okam && c < rp.max_records) {
-			// the slot of a candidate that prints no kam line must not keep a stale record
-			if (lane == 0) reinterpret_cast<dbt_pair_record*>(sv.records + (uint64_t)c * rp.rec_stride)->status = (uint8_t)status;
-		}
-		if (emit) {
-			const uint64_t slot = trace ? (uint64_t)p : (uint64_t)c;
-			if (!trace && slot >= rp.max_records) { if (lane == 0) atomicOr(sv.ncand + 1, ERR_RECORD_OVERFLOW); }
-			else {
-				uint8_t* rec = sv.records + slot * rp.rec_stride;
-				if (lane == 0) {
-					dbt_pair_record* h = reinterpret_cast<dbt_pair_record*>(rec);
-					const uint16_t nh0 = trace ? h->nhash0 : 0;       // left there by subfilter_kernel
-					h->pair_index = sv.first_pair_index + p;
-					const bool voted = status >= DBT_ST_UNASSIGNED;
-					h->dst = voted ? dst : (uint32_t)ix.nloci; h->dst0 = voted ? dst0 : NAN32;
-					h->fc = voted ? fc : 0; h->rc = voted ? rc : 0;
-					h->nhash0 = nh0; h->nhash1 = (uint16_t)nhash1; h->status = (uint8_t)status;
-					h->pad[0] = h->pad[1] = h->pad[2] = 0;
-#pragma unroll
-					for (int m = 0; m < 2; ++m) {
-						dbt_mate_record& o = h->mate[m];
-						o.si = (int16_t)mo[m].si; o.ei = (int16_t)mo[m].ei; o.si_ = (int16_t)mo[m].si_; o.ei_ = (int16_t)mo[m].ei_;
-						o.ti = (int16_t)mo[m].ti; o.nt = (int8_t)mo[m].nt; o.bs = (int8_t)mo[m].bs;
-						o.flags = (uint8_t)((kf[m] ? DBT_MF_KF : 0) | (hf[m] ? DBT_MF_HF : 0) | (mo[m].af ? DBT_MF_AF : 0) | (rm[m] ? DBT_MF_RM : 0));
-						o.pad = 0; o.nk = (uint16_t)nas[m];
-					}
-				}
-#pragma unroll
-				for (int m = 0; m < 2; ++m) {
-					uint8_t* dsta = rec + sizeof(dbt_pair_record) + (size_t)m * rp.as_stride;
-					for (uint32_t b = lane; b < rp.as_stride; b += 32) {
-						uint32_t v = 0;
-#pragma unroll
-						for (int q = 0; q < 4; ++q) { uint32_t i = 4 * b + q; if (i < nas[m]) v |= (uint32_t)as[m * NKP + i] << (2 * q); }
-						dsta[b] = (uint8_t)v;
-					}
-				}
-			}
-		}
-	}
-	ix.vote_epoch[gwarp] = epoch;
-	if (lane == 0) {
-		counter_add(sv.counters, DBT_C_NKMERFILTERED, c_kf);
-		counter_add(sv.counters, DBT_C_NLOCUSASSIGNFILTERED, c_laf);
-		counter_add(sv.counters, DBT_C_NQCFILTERED, c_qc);
-		counter_add(sv.counters, DBT_C_NTHREADINGREADS, c_thr);
-		counter_add(sv.counters, DBT_C_NFEASIBLEREADS, c_thr);
-		counter_add(sv.counters, DBT_C_NASGNREADS, c_asgn);
-		counter_add(sv.counters, DBT_C_NHASH1, c_h1);
-		counter_add(sv.counters, DBT_C_NINC, c_inc);
-	}
-}
+namespace dbt {
 
 // ============================================================================================
 // index build (A14 device half)
@@ -745,7 +307,7 @@ __global__ void random_gather_kernel(const uint4* __restrict__ table, uint64_t n
 // ============================================================================================
 // host-callable launchers (used by dbt_abi.cu)
 // ============================================================================================
-#define DISPATCH_B(B, ...) switch (B) { case 2: { constexpr int BB = 2; __VA_ARGS__; } break; case 4: { constexpr int BB = 4; __VA_ARGS__; } break; case 8: { constexpr int BB = 8; __VA_ARGS__; } break; default: return cudaErrorInvalidValue; }
+#define DISPATCH_B(B, ...) switch (B) { case 2: { constexpr int BB = 2; __VA_ARGS__; } break; case 4: { constexpr int BB = 4; __VA_ARGS__; } break; default: return cudaErrorInvalidValue; }
 
 cudaError_t launch_pack(cudaStream_t st, const uint8_t* ascii, const uint64_t* offsets, uint64_t npairs, const RunParams& rp,
                         uint64_t* p0, uint64_t* p1, uint16_t* m0, uint16_t* m1, uint32_t* err) {
@@ -776,20 +338,23 @@ cudaError_t launch_compact(cudaStream_t st, const SlotView& sv) {
 }
 
 template <int B, int MAXJ>
-static cudaError_t launch_candidate_t(cudaStream_t st, unsigned grid, size_t smem, const DevIndex& ix, const RunParams& rp, const SlotView& sv) {
-	cudaError_t e = cudaFuncSetAttribute(candidate_kernel<B, MAXJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+static cudaError_t launch_candidate_t(cudaStream_t st, unsigned grid_fast, unsigned grid_slow, size_t warp_smem, const DevIndex& ix, const RunParams& rp, const SlotView& sv) {
+	const size_t smem_fast = warp_smem * CAND_WARPS_FAST, smem_slow = warp_smem * CAND_WARPS_SLOW;
+	cudaError_t e = cudaFuncSetAttribute(candidate_kernel<B, MAXJ, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_fast);
 	if (e != cudaSuccess) return e;
-	candidate_kernel<B, MAXJ><<<grid, CAND_WARPS_PER_BLOCK * 32, smem, st>>>(ix, rp, sv);
+	e = cudaFuncSetAttribute(candidate_kernel<B, MAXJ, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_slow);
+	if (e != cudaSuccess) return e;
+	candidate_kernel<B, MAXJ, true><<<grid_fast, CAND_WARPS_FAST * 32, smem_fast, st>>>(ix, rp, sv);
+	candidate_kernel<B, MAXJ, false><<<grid_slow, CAND_WARPS_SLOW * 32, smem_slow, st>>>(ix, rp, sv);
 	return cudaGetLastError();
 }
 
-cudaError_t launch_candidate(cudaStream_t st, int B, unsigned grid, const DevIndex& ix, const RunParams& rp, const SlotView& sv) {
+cudaError_t launch_candidate(cudaStream_t st, int B, unsigned grid_fast, unsigned grid_slow, const DevIndex& ix, const RunParams& rp, const SlotView& sv) {
 	if (!sv.npairs) return cudaSuccess;
-	size_t smem = (size_t)rp.warp_smem * CAND_WARPS_PER_BLOCK;
 	int maxj = (int)(rp.nkp / 32);
-	if (maxj <= 5)      { DISPATCH_B(B, return launch_candidate_t<BB, 5>(st, grid, smem, ix, rp, sv)); }
-	else if (maxj <= 8) { DISPATCH_B(B, return launch_candidate_t<BB, 8>(st, grid, smem, ix, rp, sv)); }
-	else if (maxj <= 16){ DISPATCH_B(B, return launch_candidate_t<BB, 16>(st, grid, smem, ix, rp, sv)); }
+	if (maxj <= 5)      { DISPATCH_B(B, return launch_candidate_t<BB, 5>(st, grid_fast, grid_slow, rp.warp_smem, ix, rp, sv)); }
+	else if (maxj <= 8) { DISPATCH_B(B, return launch_candidate_t<BB, 8>(st, grid_fast, grid_slow, rp.warp_smem, ix, rp, sv)); }
+	else if (maxj <= 16){ DISPATCH_B(B, return launch_candidate_t<BB, 16>(st, grid_fast, grid_slow, rp.warp_smem, ix, rp, sv)); }
 	return cudaErrorInvalidValue;
 }
 

@@ -98,7 +98,7 @@ typedef struct {
   uint32_t max_batch_pairs;    /* largest npairs of one dbt_submit                              */
   uint32_t max_records;        /* record buffer capacity per slot; 0 = max_batch_pairs          */
   float    table_load;         /* hash table load factor; 0 = default                           */
-  uint32_t bucket_slots;       /* 16-byte slots per probe bucket: 2 (32 B sector) or 4 or 8; 0 = default */
+  uint32_t bucket_slots;       /* 16-byte slots per probe bucket: 2 (one 32 B sector) or 4; 0 = default (2) */
   uint32_t reserved[3];
 } dbt_params;
 

@@ -44,7 +44,7 @@ def test_no_cpu_fallback(lib):
 
 def test_bad_arguments(lib):
     h = C.c_void_p()
-    for k, v in (("k", 0), ("k", 28), ("max_read_len", 10), ("max_batch_pairs", 0), ("bucket_slots", 3)):
+    for k, v in (("k", 0), ("k", 28), ("max_read_len", 10), ("max_batch_pairs", 0), ("bucket_slots", 3), ("bucket_slots", 8)):
         p = abi.default_params()
         setattr(p, k, v)
         assert lib.dbt_create(C.byref(h), C.byref(p)) == -3, k

@@ -93,7 +93,7 @@ def oracle_vs_gpu(ix, seqs, p_gpu, p_oracle=None, batch=None):
     return recs, cnt
 
 
-@pytest.mark.parametrize("k,cth,flank,bucket", [(21, 45, 300, 2), (21, 10, 300, 4), (17, 30, 250, 2), (25, 20, 300, 8), (21, 45, 300, 4)])
+@pytest.mark.parametrize("k,cth,flank,bucket", [(21, 45, 300, 2), (21, 10, 300, 4), (17, 30, 250, 2), (25, 20, 300, 4), (21, 45, 300, 4)])
 def test_gpu_matches_oracle_seeded(k, cth, flank, bucket):
     """fresh synthetic RPGG with shared segments + chimeric/borderline/N/short reads; k = 17/21/25"""
     ix, seqs, _ = synthetic_case(nloci=60, seed=200 + k + cth, k=k, flank=flank, npairs=8000, read_seed=cth,
