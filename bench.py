@@ -329,25 +329,32 @@ def b200_arm(a, config, workdir, rank, world, local, dist):
     abi.check(L, L.dbt_wait(ctx.h, 0), "wait")
     cnt = dict(zip(abi.COUNTER_NAMES, list(res.counters)))
     kt = ktimes.mean(axis=0)
-    t_sub, t_cmp, t_cand = float(kt[1]), float(kt[2]), float(kt[3])
+    t_sub, t_cmp, t_cand, t_gen = float(kt[1]), float(kt[2]), float(kt[3]), float(kt[4])
 
-    # ---- roofline of the dominant kernel (algorithmic bytes: SURVEY.md §8(d)) ----
+    # ---- roofline of the dominant kernel (algorithmic bytes: SURVEY.md §8(d), DESIGN.md §5) ----
+    # one logical probe = one 32 B sector, one count increment = 64 B read-modify-write, bases at 2 bits
     nk = RLEN - K + 1
     ncand = cnt["ncandidates"]
     p_sub = cnt["nhash0"] + 2 * ncand                       # ++nhash skips the iteration that breaks (cpp:176)
-    p_as = cnt["nThreadingReads"] * nk                      # one classification probe per k-mer of pairs reaching assignTRkmc
     bytes_sub = P * 75 + 32 * p_sub
-    bytes_cand = 32 * (cnt["nhash1"] + p_as) + 64 * cnt["ninc"]
+    # candidate stage: kfilter probes (nhash1) + one classification probe per k-mer of pairs reaching assignTRkmc + increments,
+    # split between the closed-form kernel and the generic kernel by the generic kernel's own counters
+    g_h1, g_thr, g_inc = cnt["gen_nhash1"], cnt["gen_nThreadingReads"], cnt["gen_ninc"]
+    bytes_gen = 32 * (g_h1 + g_thr * nk) + 64 * g_inc
+    bytes_fast = 32 * ((cnt["nhash1"] - g_h1) + (cnt["nThreadingReads"] - g_thr) * nk) + 64 * (cnt["ninc"] - g_inc)
     peak, peak_src = peaks()
-    if t_cand >= t_sub:
-        dom, dom_ms, dom_bytes = "candidate_kernel", t_cand, bytes_cand
-    else:
-        dom, dom_ms, dom_bytes = "subfilter_kernel", t_sub, bytes_sub
+    kern = {"subfilter_kernel": (t_sub, bytes_sub), "candidate_fast_kernel": (t_cand, bytes_fast), "candidate_kernel(generic)": (t_gen, bytes_gen)}
+    dom = max(kern, key=lambda n: kern[n][0])
+    dom_ms, dom_bytes = kern[dom]
     ach = dom_bytes / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0
+    step_bytes = bytes_sub + bytes_fast + bytes_gen
     roofline = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
                 "kernel": dom, "kernel_ms": dom_ms, "algorithmic_bytes_per_launch": dom_bytes, "peak_source": peak_src,
-                "per_kernel_ms": {"subfilter": t_sub, "compaction": t_cmp, "candidate": t_cand},
-                "step_bytes": bytes_sub + bytes_cand, "step_GBps": (bytes_sub + bytes_cand) / (step_ms / 1e3) / 1e9}
+                "per_kernel_ms": {"subfilter": t_sub, "compaction": t_cmp, "candidate_fast": t_cand, "candidate_generic": t_gen},
+                "per_kernel_GBps": {n: (bb / (ms_ / 1e3) / 1e9 if ms_ > 0 else 0.0) for n, (ms_, bb) in kern.items()},
+                "per_kernel_bytes": {n: bb for n, (ms_, bb) in kern.items()},
+                "generic_path_pairs": cnt["gen_pairs"], "candidate_pairs": ncand,
+                "step_bytes": step_bytes, "step_GBps": step_bytes / (step_ms / 1e3) / 1e9, "step_frac": step_bytes / (step_ms / 1e3) / 1e9 / peak}
     if a.rrand and rank == 0:
         rr = {}
         for sect in (32, 64):

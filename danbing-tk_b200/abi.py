@@ -11,7 +11,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libdanbing_b200.so")
 
-DBT_N_COUNTERS = 16
+DBT_N_COUNTERS = 24
 DBT_N_SLOTS = 2
 DBT_NCCL_ID_BYTES = 128
 
@@ -20,7 +20,9 @@ ST_SHORT, ST_SUBFILTERED, ST_KFILTERED, ST_UNASSIGNED, ST_QCFILTERED, ST_ASGN_RE
 LAYOUT_ASCII, LAYOUT_PACKED = 0, 1
 COUNTER_NAMES = ["nReads", "nShort", "nSubFiltered", "nKmerFiltered", "nBaitFiltered", "nQualFiltered",
                  "nLocusAssignFiltered", "nQCFiltered", "nThreadingReads", "nFeasibleReads", "nAsgnReads",
-                 "nhash0", "nhash1", "ninc", "ncandidates", "nrecords"]
+                 "nhash0", "nhash1", "ninc", "ncandidates", "nrecords",
+                 "gen_pairs", "gen_nhash1", "gen_nThreadingReads", "gen_ninc"]
+MEASUREMENT_COUNTERS = ("nrecords", "gen_pairs", "gen_nhash1", "gen_nThreadingReads", "gen_ninc")   # no reference counterpart
 MF_KF, MF_HF, MF_BF, MF_QF, MF_AF, MF_RM = 1, 2, 4, 8, 16, 32
 
 u64p = C.POINTER(C.c_uint64)
@@ -147,6 +149,7 @@ def load_library(path=LIB_PATH):
     L.dbt_timer_stop.argtypes = [ctxp, C.c_int, C.POINTER(C.c_float)]
     L.dbt_kernel_times.argtypes = [ctxp, C.c_int, C.POINTER(C.c_float), u32p]
     L.dbt_table_stats.argtypes = [ctxp, u64p]
+    L.dbt_batch_stats.argtypes = [ctxp, C.c_int, u64p]
     L.dbt_random_gather_bench.argtypes = [C.c_int, C.c_uint64, C.c_uint32, C.c_uint64, C.c_int, C.POINTER(C.c_float)]
     L.dbt_host_alloc.argtypes = [C.c_size_t]
     L.dbt_host_alloc.restype = C.c_void_p
@@ -162,7 +165,7 @@ ABI_SYMBOLS = ["dbt_abi_version", "dbt_device_count", "dbt_default_params", "dbt
                "dbt_strerror", "dbt_last_error", "dbt_load_index", "dbt_upload", "dbt_process", "dbt_fetch",
                "dbt_submit", "dbt_wait", "dbt_download", "dbt_reset_counts", "dbt_nk_tr", "dbt_nloci",
                "dbt_record_stride", "dbt_record_as_stride", "dbt_nccl_unique_id", "dbt_comm_init", "dbt_allreduce",
-               "dbt_timer_start", "dbt_timer_stop", "dbt_kernel_times", "dbt_launch_count", "dbt_table_stats",
+               "dbt_timer_start", "dbt_timer_stop", "dbt_kernel_times", "dbt_launch_count", "dbt_table_stats", "dbt_batch_stats",
                "dbt_random_gather_bench", "dbt_host_alloc", "dbt_host_free", "dbt_packed_bytes", "dbt_pack_reads"]
 
 

@@ -298,16 +298,15 @@ __device__ __noinline__ uint3 vote_serial(const uint32_t* __restrict__ vv, const
 }
 
 // ------------------------------------------------------------------------------------------------
-// FAST = true : the common case, run phase-synchronously -- the warps of a block move through the
-//               phases of their pairs together (__syncthreads between phases), so that at any time
-//               an SM executes ONE phase's code (ncu showed the fused per-pair loop of ~8k SASS
-//               instructions to be instruction-fetch bound: stall_no_inst 55-58 %).  Pairs whose k-mers
-//               are not all unique to one locus are appended to sv.slow and left untouched.
-// FAST = false: the generic path (exact introsort replay + sequential vote) over sv.slow, free-running.
+// candidate_kernel: the GENERIC path -- exact countDupRemove / introsort replay / sequential vote.
+// It serves (a) the pairs candidate_fast_kernel (candidate_fast.cuh) defers to sv.slow: pairs whose
+// hits are not all unique to one locus, or whose accept/reject decision depends on the visiting
+// order, and (b) with all != 0 every candidate (DBT_F_TRACE: the records then carry the exact
+// top.fc/top.rc of the early stop).  Warps are free-running, one pair at a time.
 // ------------------------------------------------------------------------------------------------
-template <int B, int MAXJ, bool FAST>
-__global__ void __launch_bounds__((FAST ? CAND_WARPS_FAST : CAND_WARPS_SLOW) * 32, FAST ? 2 : 4) candidate_kernel(DevIndex ix, RunParams rp, SlotView sv) {
-	constexpr int WPB = FAST ? CAND_WARPS_FAST : CAND_WARPS_SLOW;
+template <int B, int MAXJ>
+__global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevIndex ix, RunParams rp, SlotView sv, int all) {
+	constexpr int WPB = CAND_WARPS_SLOW;
 	constexpr int E = (2 * MAXJ <= 16) ? 16 : 32;            // sort slots per lane: 32*E >= 2*nk_max, E >= 2*MAXJ
 	extern __shared__ __align__(16) uint8_t smem_raw[];
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -332,17 +331,17 @@ __global__ void __launch_bounds__((FAST ? CAND_WARPS_FAST : CAND_WARPS_SLOW) * 3
 	uint16_t* umid  = ustart + UMAX + 2;                                // first mate-1 element of the group
 	uint16_t* perm  = umid + UMAX;                                      // visiting order (cpp:320-327)
 
-	uint32_t c_kf = 0, c_laf = 0, c_qc = 0, c_thr = 0, c_asgn = 0, c_h1 = 0, c_inc = 0;   // lane-0 accumulators
+	uint32_t c_kf = 0, c_laf = 0, c_qc = 0, c_thr = 0, c_asgn = 0, c_h1 = 0, c_inc = 0, c_pairs = 0;   // lane-0 accumulators
 	uint32_t epoch = 0; uint64_t* scratch = nullptr;
-	if (!FAST) { epoch = ix.vote_epoch[gwarp]; scratch = ix.vote_scratch + (uint64_t)gwarp * (ix.nloci + 1); }
-	const uint32_t nwork = FAST ? sv.ncand[0] : sv.ncand[2];
-	const uint32_t stride = FAST ? gridDim.x * WPB : nwarps;
+	epoch = ix.vote_epoch[gwarp]; scratch = ix.vote_scratch + (uint64_t)gwarp * (ix.nloci + 1);
+	const uint32_t nwork = all ? sv.ncand[0] : sv.ncand[2];
+	const uint32_t stride = nwarps;
 
 #pragma unroll 1
-	for (uint32_t base = FAST ? blockIdx.x * WPB : gwarp; base < nwork; base += stride) {
-		const uint32_t w = FAST ? base + wib : base;
-		const bool active = w < nwork;                          // FAST: idle warps still meet the barriers
-		const uint32_t c = active ? (FAST ? w : sv.slow[w]) : 0;
+	for (uint32_t w = gwarp; w < nwork; w += stride) {
+		const bool active = true;
+		++c_pairs;
+		const uint32_t c = active ? (all ? w : sv.slow[w]) : 0;
 		const uint32_t p = active ? sv.cand[c] : 0;
 		uint32_t nk[2] = {0, 0};
 		uint32_t hitmask[2][MAXJ];            // ballot of "k-mer is in the index" per 32 positions
@@ -371,7 +370,7 @@ __global__ void __launch_bounds__((FAST ? CAND_WARPS_FAST : CAND_WARPS_SLOW) * 3
 				pk[i] = sv.packed[m][(uint64_t)p * W64 + (i - m * W64)];
 			}
 			nk[0] = (sv.meta[0][p] & META_LENMASK) - K + 1; nk[1] = (sv.meta[1][p] & META_LENMASK) - K + 1;
-			if (!FAST) for (uint32_t i = lane; i < 3 * VOTE_SMEM_SLOTS; i += 32) lkey[i] = 0;
+			for (uint32_t i = lane; i < 3 * VOTE_SMEM_SLOTS; i += 32) lkey[i] = 0;
 			__syncwarp();
 			// all canonical k-mers + ONE index probe each (A2 + the lookups of kfilter, cpp:207/218)
 #pragma unroll 1
@@ -462,7 +461,6 @@ __global__ void __launch_bounds__((FAST ? CAND_WARPS_FAST : CAND_WARPS_SLOW) * 3
 			}
 			if (rm[0] && rm[1]) status = DBT_ST_KFILTERED;
 		}
-		if (FAST) __syncthreads();
 
 		// =========================== phase 2: countDupRemove (cpp:257-296) ===========================
 		if (active && status < 0) {
@@ -516,7 +514,6 @@ __global__ void __launch_bounds__((FAST ? CAND_WARPS_FAST : CAND_WARPS_SLOW) * 3
 			}
 			__syncwarp();
 		}
-		if (FAST) __syncthreads();
 
 		// =========================== phase 3: fillstats + vote (cpp:308-453) ===========================
 		if (active && status < 0) {
@@ -535,17 +532,13 @@ __global__ void __launch_bounds__((FAST ? CAND_WARPS_FAST : CAND_WARPS_SLOW) * 3
 			any_odd = __any_sync(0xffffffffu, odd);
 			one_locus = !any_odd && !__any_sync(0xffffffffu, differs) && rp.nk_max <= 255;
 			total = warp_sum(wsum8);                                          // dupsum of countRemain (cpp:300)
-			if (FAST && !one_locus) {
-				deferred = true;                                              // generic path: leave the pair to the slow kernel
-				if (lane == 0) sv.slow[atomicAdd(sv.ncand + 2, 1u)] = c;
-			}
 		}
 		if (active && status < 0 && !deferred) {
 			// visiting order = std::sort by number of mapped loci (cpp:320-327)
 			if (!any_odd && U <= ix.permtab_maxU) {
 				const uint16_t* pt = ix.permtab + (size_t)U * (U - 1) / 2;
 				for (uint32_t u = lane; u < U; u += 32) perm[u] = pt[u];
-			} else if (!FAST) {
+			} else {
 				for (uint32_t u = lane; u < U; u += 32) perm[u] = (uint16_t)u;
 				__syncwarp();
 				if (lane == 0) perm_introsort(perm, unml, (int)U);
@@ -586,7 +579,7 @@ __global__ void __launch_bounds__((FAST ? CAND_WARPS_FAST : CAND_WARPS_SLOW) * 3
 					carryF = __shfl_sync(0xffffffffu, cf, 31); carryR = __shfl_sync(0xffffffffu, cr, 31);
 				}
 				dst0 = val0 >> 1;
-			} else if (!FAST) {
+			} else {
 				uint3 t3 = make_uint3(NAN32, 0, 0);
 				if (lane == 0) t3 = vote_serial(ix.vv, perm, uval, utf, utr, lkey, U, total, rp.cth, scratch, epoch + 1);
 				// the global fallback may have been written under epoch+1: retire that epoch
@@ -606,7 +599,6 @@ __global__ void __launch_bounds__((FAST ? CAND_WARPS_FAST : CAND_WARPS_SLOW) * 3
 			// QC gate (cpp:2059-2062)
 			if (status < 0 && (rp.flags & DBT_F_QC) && ix.qc && !ix.qc[dst]) { status = DBT_ST_QCFILTERED; if (lane == 0) c_qc += 2 - rm[0] - rm[1]; }
 		}
-		if (FAST) __syncthreads();
 
 		// =========================== phase 4: assignTRkmc, accumulate, record ===========================
 		if (active && !deferred) {
@@ -675,7 +667,7 @@ __global__ void __launch_bounds__((FAST ? CAND_WARPS_FAST : CAND_WARPS_SLOW) * 3
 						h->pair_index = sv.first_pair_index + p;
 						const bool voted = status >= DBT_ST_UNASSIGNED;
 						h->dst = voted ? dst : (uint32_t)ix.nloci; h->dst0 = voted ? dst0 : NAN32;
-						h->fc = voted ? fc : 0; h->rc = voted ? rc : 0;
+						h->fc = (voted && trace) ? fc : 0; h->rc = (voted && trace) ? rc : 0;   // exact only under DBT_F_TRACE (nm1/nm2 are unused downstream, cpp:2016)
 						h->nhash0 = nh0; h->nhash1 = (uint16_t)nhash1; h->status = (uint8_t)status;
 						h->pad[0] = h->pad[1] = h->pad[2] = 0;
 #pragma unroll
@@ -705,9 +697,8 @@ __global__ void __launch_bounds__((FAST ? CAND_WARPS_FAST : CAND_WARPS_SLOW) * 3
 				}
 			}
 		}
-		if (FAST) __syncthreads();
 	}
-	if (!FAST) ix.vote_epoch[gwarp] = epoch;
+	ix.vote_epoch[gwarp] = epoch;
 	if (lane == 0) {
 		counter_add(sv.counters, DBT_C_NKMERFILTERED, c_kf);
 		counter_add(sv.counters, DBT_C_NLOCUSASSIGNFILTERED, c_laf);
@@ -717,6 +708,10 @@ __global__ void __launch_bounds__((FAST ? CAND_WARPS_FAST : CAND_WARPS_SLOW) * 3
 		counter_add(sv.counters, DBT_C_NASGNREADS, c_asgn);
 		counter_add(sv.counters, DBT_C_NHASH1, c_h1);
 		counter_add(sv.counters, DBT_C_NINC, c_inc);
+		counter_add(sv.counters, DBT_C_GEN_PAIRS, c_pairs);
+		counter_add(sv.counters, DBT_C_GEN_NHASH1, c_h1);
+		counter_add(sv.counters, DBT_C_GEN_NTHREADINGREADS, c_thr);
+		counter_add(sv.counters, DBT_C_GEN_NINC, c_inc);
 	}
 }
 

@@ -1,0 +1,325 @@
+// candidate_fast_kernel: one warp per read pair that survived subfilter -- the common case, with no
+// sort and no shared-memory work arrays.
+//
+// The expensive part of the reference's locus vote (countDupRemove's sort by key, fillstats' unstable
+// std::sort, the sequential early-stopping walk; cpp:257-422) only decides
+//   (1) top.idx and (2) whether (top.fc, top.rc) at the stop pass the thresholds of cpp:439-440;
+// nm1/nm2 themselves are never used again (cpp:2016, 2056).  When EVERY index hit of the surviving
+// mates is a k-mer unique to one and the same locus A (all values even and equal), the walk is
+// degenerate: `second` stays {NAN32,0,0}, top = running sums, so top.idx = A, and with
+//   F, R = number of hit positions of mate 1 / mate 2 (>= cth for a mate that survived kfilter, cpp:190-224)
+// the exit state of the loops at cpp:383-417 is: counting continues while a threshold is still
+// reachable, i.e. until fc >= cth and rc >= cth (both mates alive: always reached -> accept), or,
+// with one mate removed (its side stays 0), until fc >= cth and remain < cth, where fc = F - remain:
+//   F <  2*cth       -> fc + 0 < 2*cth           -> reject, whatever the visiting order
+//   F >= 3*cth - 1   -> fc >= F - (cth-1) >= 2*cth -> accept, whatever the visiting order
+//   otherwise the outcome depends on the multiplicities met last -> generic kernel (exact replay).
+// Pairs with a multi-locus k-mer, hits in two loci, or that undecided band are appended to sv.slow and
+// left untouched for candidate_kernel.  Counts are accumulated per k-mer OCCURRENCE exactly as
+// cpp:2155-2158 does (one increment per position with as == 2), aggregated per warp with
+// __match_any_sync before the 64-bit atomic.
+#pragma once
+#include "candidate.cuh"
+
+namespace dbt {
+
+constexpr int CAND_FAST_WARPS = 8;
+
+// Per-warp shared-memory state.  Everything indexed by mate lives here rather than in registers so
+// that the per-mate stages are ROLLED loops: ncu showed the fully unrolled (2 mates x MAXJ) kernel,
+// ~4.4k SASS instructions = 70 KB, to be instruction-fetch bound (stall_no_instruction 5.0 per issue,
+// issue slots 29 % busy) -- its warps run free and the 32 KB L1.5 I-cache cannot hold the loop.
+template <int MAXJ>
+struct FastWarp {
+	uint64_t pk[2 * 16];                   // packed records of both mates (W64 <= 16 when nk_max <= 255)
+	uint32_t val[2][MAXJ * 32];            // index value per position
+	uint32_t aux[2][MAXJ * 32];            // aux word per position (AUX_MISS = not in the index); later: class word w.r.t. dst0
+	uint32_t hit[2][MAXJ], F[2][MAXJ], T[2][MAXJ];   // ballots: in the index / flank of dst0 / TR of dst0
+	dbt_mate_record mate[2];
+};
+
+template <int B, int MAXJ>
+__global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel(DevIndex ix, RunParams rp, SlotView sv) {
+	__shared__ __align__(16) FastWarp<MAXJ> wsm[CAND_FAST_WARPS];
+	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+	const uint32_t gwarp = blockIdx.x * CAND_FAST_WARPS + wib, nwarps = gridDim.x * CAND_FAST_WARPS;
+	const uint32_t W64 = rp.lay.W64, WB = rp.lay.WB, K = rp.k;
+	const bool okam = (rp.flags & DBT_F_KAM) != 0;
+	const uint32_t nloci = (uint32_t)ix.nloci, cth = rp.cth;
+	FastWarp<MAXJ>& W = wsm[wib];
+	uint32_t c_kf = 0, c_laf = 0, c_qc = 0, c_thr = 0, c_asgn = 0, c_h1 = 0, c_inc = 0;   // lane-0 accumulators
+	const uint32_t nwork = sv.ncand[0];
+
+#pragma unroll 1
+	for (uint32_t c = gwarp; c < nwork; c += nwarps) {
+		const uint32_t p = sv.cand[c];
+
+		// ---- packed records -> shared memory ----
+		__syncwarp();
+		for (uint32_t i = lane; i < 2 * W64; i += 32) {
+			const uint32_t m = i >= W64;
+			W.pk[i] = sv.packed[m][(uint64_t)p * W64 + (i - m * W64)];
+		}
+		const uint32_t nk0 = (sv.meta[0][p] & META_LENMASK) - K + 1, nk1 = (sv.meta[1][p] & META_LENMASK) - K + 1;
+		__syncwarp();
+
+		// ---- all canonical k-mers + ONE index probe each (A2 + the look-ups of kfilter, cpp:207/218) ----
+		// per mate: MAXJ independent bucket loads in flight per lane before any is inspected
+#pragma unroll 1
+		for (int m = 0; m < 2; ++m) {
+			const uint32_t nkm = m ? nk1 : nk0;
+			uint4 s[MAXJ][B];
+			uint64_t key[MAXJ];
+			const uint64_t* rec = W.pk + m * W64;
+			const uint32_t* mk32 = reinterpret_cast<const uint32_t*>(rec + WB);
+			const uint32_t sh = 2 * lane;
+			const uint64_t kmask = (1ull << (2 * K)) - 1, vmask = (1ull << K) - 1;
+			uint64_t wlo = rec[0];
+			uint32_t mlo = mk32[0];
+#pragma unroll
+			for (int j = 0; j < MAXJ; ++j) {
+				const uint32_t i = j * 32 + lane;
+				const uint64_t whi = (j + 1 < (int)WB) ? rec[j + 1] : 0ull;
+				const uint32_t mnx = ((uint32_t)(j + 1) < 2 * rp.lay.WM) ? mk32[j + 1] : 0xFFFFFFFFu;
+				const uint64_t wv = sh ? ((wlo >> sh) | (whi << (64 - sh))) : wlo;
+				const uint64_t mm = (((uint64_t)mnx << 32) | mlo) >> lane;
+				uint64_t kk = KMER_INVALID;
+				if (i < nkm && (mm & vmask) == 0) {
+					const uint64_t x = wv & kmask, rcx = (~wv) & kmask, fw = rev2(x) >> (64 - 2 * K);
+					kk = fw < rcx ? fw : rcx;
+				}
+				key[j] = kk;
+				wlo = whi; mlo = mnx;
+				if (kk != KMER_INVALID) {
+					const uint64_t hb = home_bucket(ix.table, kk);
+#pragma unroll
+					for (int q = 0; q < B; ++q) s[j][q] = ldg128(ix.table.slots + hb * B + q);
+				}
+			}
+#pragma unroll
+			for (int j = 0; j < MAXJ; ++j) {
+				uint32_t v = 0, a = AUX_MISS;
+				if (key[j] != KMER_INVALID) {
+					bool full = true, found = false;
+#pragma unroll
+					for (int q = 0; q < B; ++q) {
+						const uint64_t kk = slot_key(s[j][q]);
+						if (kk == SLOT_EMPTY) full = false;
+						else if ((kk & SLOT_KEYMASK) == key[j]) { v = s[j][q].z; a = s[j][q].w; found = true; }
+					}
+					if (!found && full && (slot_key(s[j][0]) & SLOT_OVF)) {
+						const uint2 r2 = probe_walk<B>(ix.table.slots, ix.table.nbuckets, key[j], home_bucket(ix.table, key[j]));
+						v = r2.x; a = r2.y;
+					}
+				}
+				W.val[m][j * 32 + lane] = v; W.aux[m][j * 32 + lane] = a;
+				const uint32_t hm = __ballot_sync(0xffffffffu, a != AUX_MISS);
+				if (lane == 0) W.hit[m][j] = hm;
+			}
+		}
+		__syncwarp();
+
+		// ---- kfilter (cpp:190-224): abort a mate at its (nk-cth+1)-th miss ----
+		uint32_t kfm = (nk0 < cth ? 1u : 0u) | (nk1 < cth ? 2u : 0u);      // bit m = kf[m]
+		uint32_t rmm = kfm;                                                // bit m = rm[m]
+		uint32_t nhash1 = 0;
+		uint32_t cnt0 = 0, cnt1 = 0;                                       // hit positions per mate
+		if (rmm != 3u) {
+#pragma unroll 1
+			for (int m = 0; m < 2; ++m) {
+				if ((rmm >> m) & 1u) continue;
+				const uint32_t nkm = m ? nk1 : nk0;
+				const uint32_t max_ns = nkm - cth;
+				uint32_t cum = 0, probes = nkm, aword = 0, abase = 0, arank = 0, hits = 0; bool aborted = false;
+#pragma unroll 1
+				for (int j = 0; j < MAXJ; ++j) {
+					const uint32_t inrange = (nkm >= (uint32_t)(j + 1) * 32) ? 0xFFFFFFFFu : ((nkm > (uint32_t)j * 32) ? ((1u << (nkm - j * 32)) - 1u) : 0u);
+					const uint32_t hm = W.hit[m][j];
+					const uint32_t mm = ~hm & inrange;
+					hits += __popc(hm);
+					if (!aborted && cum + __popc(mm) > max_ns) { aborted = true; aword = mm; abase = j * 32; arank = max_ns - cum; }
+					cum += __popc(mm);
+				}
+				if (aborted) {                                   // position of the (arank+1)-th miss of that word
+					uint32_t pos = 0, nn = arank;
+#pragma unroll
+					for (int shf = 16; shf >= 1; shf >>= 1) {
+						const uint32_t cn = __popc((aword >> pos) & ((1u << shf) - 1u));
+						if (nn >= cn) { nn -= cn; pos += shf; }
+					}
+					probes = abase + pos + 1;
+				}
+				nhash1 += probes;
+				if (aborted) { kfm |= 1u << m; rmm |= 1u << m; }
+				else if (m) cnt1 = hits; else cnt0 = hits;
+			}
+		}
+		if (rmm == 3u) {                                         // cpp:2054
+			if (lane == 0) {
+				c_kf += __popc(kfm); c_h1 += nhash1;
+				if (okam && c < rp.max_records) reinterpret_cast<dbt_pair_record*>(sv.records + (uint64_t)c * rp.rec_stride)->status = (uint8_t)DBT_ST_KFILTERED;
+			}
+			continue;
+		}
+
+		// ---- degenerate vote: every hit of the surviving mates unique to ONE locus? ----
+		uint32_t val0 = 0; bool have0 = false, differs = false;
+#pragma unroll 1
+		for (int m = 0; m < 2; ++m) {
+			if ((rmm >> m) & 1u) continue;
+#pragma unroll 1
+			for (int j = 0; j < MAXJ; ++j) {
+				const uint32_t hm = W.hit[m][j];
+				if (!hm) continue;
+				const uint32_t v = W.val[m][j * 32 + lane];
+				if (!have0) { val0 = __shfl_sync(0xffffffffu, v, __ffs(hm) - 1); have0 = true; }
+				if (((hm >> lane) & 1u) && v != val0) differs = true;
+			}
+		}
+		const bool one_locus = have0 && !(val0 & 1u) && !__any_sync(0xffffffffu, differs) && rp.nk_max <= 255;
+		int verdict = -1;                                        // 1 accept, 0 reject, -1 order-dependent
+		if (one_locus) {
+			if (rmm == 0u || cth == 0) verdict = 1;
+			else {
+				const uint32_t T = (rmm & 1u) ? cnt1 : cnt0;
+				if (T < 2 * cth) verdict = 0;
+				else if (T + 1 >= 3 * cth) verdict = 1;
+			}
+		}
+		if (verdict < 0) {                                       // generic path (nothing of this pair has been counted yet)
+			if (lane == 0) sv.slow[atomicAdd(sv.ncand + 2, 1u)] = c;
+			continue;
+		}
+		if (lane == 0) { c_kf += __popc(kfm); c_h1 += nhash1; }
+
+		// ---- countHit tail (cpp:436-452), QC gate (cpp:2059-2062) ----
+		const uint32_t dst0 = val0 >> 1;
+		uint32_t dst = dst0, hfm = 0;
+		int status = -1;
+		if (!verdict) {
+			hfm = ~rmm & 3u; rmm = 3u; dst = nloci; status = DBT_ST_UNASSIGNED;
+			if (lane == 0) c_laf += __popc(hfm);
+		} else if ((rp.flags & DBT_F_QC) && ix.qc && !ix.qc[dst]) {
+			status = DBT_ST_QCFILTERED;
+			if (lane == 0) c_qc += 2 - __popc(rmm);
+		}
+
+		if (status < 0) {
+			if (lane == 0) c_thr += 2;
+			int span = 0;
+			// ---- assignTRkmc (cpp:1450-1556) against the tables of destLocus0; the class comes with the index entry ----
+#pragma unroll 1
+			for (int m = 0; m < 2; ++m) {
+				const bool rmv = (rmm >> m) & 1u;
+				MateOut mo;
+				mo.si = mo.ei = mo.si_ = mo.ei_ = mo.ti = -1; mo.nt = 0; mo.bs = 0; mo.af = 0; mo.rm = rmv;
+				uint32_t nas = 0;
+				if (okam || !rmv) {                                 // cpp:1451
+					const uint32_t nkm = m ? nk1 : nk0;
+					nas = nkm;
+					MaskSet<MAXJ> Fs, Ts;
+					uint32_t ntr = 0;
+#pragma unroll
+					for (int j = 0; j < MAXJ; ++j) {
+						const uint32_t i = j * 32 + lane;
+						uint32_t cw = 0;
+						if (i < nkm) cw = classify2(ix, W.val[m][i], W.aux[m][i], dst0);
+						W.aux[m][i] = cw;                           // from here on: class word w.r.t. dst0
+						Fs.w[j] = __ballot_sync(0xffffffffu, (cw >> AUX_CLASS_SHIFT) == 1);
+						Ts.w[j] = __ballot_sync(0xffffffffu, (cw >> AUX_CLASS_SHIFT) == 2);
+						ntr += __popc(Ts.w[j]);
+						if (lane == 0) { W.F[m][j] = Fs.w[j]; W.T[m][j] = Ts.w[j]; }
+					}
+					if (rmv) { mo.nt = -1; mo.bs = -1; mo.ti = -1; }   // cpp:1470-1475
+					else mo = assign_masks<MAXJ>(Fs, Ts, (int)nkm, ntr & 0xFF, rp.nm_tr, mo);   // uint8_t ntr (cpp:1454)
+				} else if (lane == 0) {
+#pragma unroll
+					for (int j = 0; j < MAXJ; ++j) { W.F[m][j] = 0; W.T[m][j] = 0; }
+				}
+				if (mo.rm) rmm |= 1u << m;
+				span += mo.ei - mo.si;
+				if (lane == 0) {
+					dbt_mate_record& o = W.mate[m];
+					o.si = (int16_t)mo.si; o.ei = (int16_t)mo.ei; o.si_ = (int16_t)mo.si_; o.ei_ = (int16_t)mo.ei_;
+					o.ti = (int16_t)mo.ti; o.nt = (int8_t)mo.nt; o.bs = (int8_t)mo.bs;
+					o.flags = (uint8_t)((((kfm >> m) & 1u) ? DBT_MF_KF : 0) | (mo.af ? DBT_MF_AF : 0) | (mo.rm ? DBT_MF_RM : 0));
+					o.pad = 0; o.nk = (uint16_t)nas;
+				}
+			}
+			__syncwarp();
+			// ---- accumulate (cpp:2145-2158) ----
+			if (rmm == 3u) { dst = nloci; status = DBT_ST_ASGN_REMOVED; }
+			else {
+				status = DBT_ST_COUNTED;
+				const int nr = 2 - __popc(rmm);
+				if (lane == 0) {
+					atomicAdd(ix.nmapread + dst, (uint32_t)nr);
+					c_asgn += nr;
+					atomicAdd(reinterpret_cast<unsigned long long*>(ix.kmc + dst), (unsigned long long)(long long)span);
+				}
+				uint32_t inc_sum = 0;
+#pragma unroll 1
+				for (int m = 0; m < 2; ++m) {
+					if ((rmm >> m) & 1u) continue;
+#pragma unroll 1
+					for (int j = 0; j < MAXJ; ++j) {
+						const uint32_t tm = W.T[m][j];
+						if (!tm) continue;
+						inc_sum += __popc(tm);
+						if ((tm >> lane) & 1u) {                    // one atomic per distinct TR k-mer among these 32 positions
+							const uint32_t idx = W.aux[m][j * 32 + lane] & AUX_IDX_MASK;
+							const uint32_t peers = __match_any_sync(tm, idx);
+							if ((uint32_t)lane == (uint32_t)(__ffs(peers) - 1))
+								atomicAdd(reinterpret_cast<unsigned long long*>(ix.counts + idx), (unsigned long long)__popc(peers));
+						}
+					}
+				}
+				if (lane == 0) c_inc += inc_sum;
+			}
+		}
+
+		// ---- kam record (cpp:2169-2175); slot = candidate ordinal, compacted by dbt_wait ----
+		if (okam) {
+			if (c >= rp.max_records) { if (lane == 0 && status == DBT_ST_COUNTED) atomicOr(sv.ncand + 1, ERR_RECORD_OVERFLOW); }
+			else if (status != DBT_ST_COUNTED) {
+				if (lane == 0) reinterpret_cast<dbt_pair_record*>(sv.records + (uint64_t)c * rp.rec_stride)->status = (uint8_t)status;
+			} else {
+				uint8_t* rec = sv.records + (uint64_t)c * rp.rec_stride;
+				if (lane == 0) {
+					dbt_pair_record* h = reinterpret_cast<dbt_pair_record*>(rec);
+					h->pair_index = sv.first_pair_index + p;
+					h->dst = dst; h->dst0 = dst0; h->fc = 0; h->rc = 0;
+					h->nhash0 = 0; h->nhash1 = (uint16_t)nhash1; h->status = (uint8_t)status;
+					h->pad[0] = h->pad[1] = h->pad[2] = 0;
+					h->mate[0] = W.mate[0]; h->mate[1] = W.mate[1];
+				}
+				// 2-bit annotation (cpp:122): byte b = k-mers 4b..4b+3, from the flank/TR masks
+#pragma unroll 1
+				for (int m = 0; m < 2; ++m) {
+					uint8_t* dsta = rec + sizeof(dbt_pair_record) + (size_t)m * rp.as_stride;
+					for (uint32_t b = lane; b < rp.as_stride; b += 32) {
+						const uint32_t jw = b >> 3;
+						const uint32_t fw = jw < (uint32_t)MAXJ ? W.F[m][jw] : 0u, tw = jw < (uint32_t)MAXJ ? W.T[m][jw] : 0u;
+						const uint32_t fn = (fw >> ((b & 7) * 4)) & 0xF, tn = (tw >> ((b & 7) * 4)) & 0xF;
+						uint32_t v = 0;
+#pragma unroll
+						for (int q = 0; q < 4; ++q) v |= (((fn >> q) & 1u) | (((tn >> q) & 1u) << 1)) << (2 * q);
+						dsta[b] = (uint8_t)v;
+					}
+				}
+			}
+		}
+	}
+	if (lane == 0) {
+		counter_add(sv.counters, DBT_C_NKMERFILTERED, c_kf);
+		counter_add(sv.counters, DBT_C_NLOCUSASSIGNFILTERED, c_laf);
+		counter_add(sv.counters, DBT_C_NQCFILTERED, c_qc);
+		counter_add(sv.counters, DBT_C_NTHREADINGREADS, c_thr);
+		counter_add(sv.counters, DBT_C_NFEASIBLEREADS, c_thr);
+		counter_add(sv.counters, DBT_C_NASGNREADS, c_asgn);
+		counter_add(sv.counters, DBT_C_NHASH1, c_h1);
+		counter_add(sv.counters, DBT_C_NINC, c_inc);
+	}
+}
+
+}  // namespace dbt

@@ -61,7 +61,7 @@ extern "C" void dbt_default_params(dbt_params* p) {
 // ------------------------------------------------------------------------------------------
 // context
 // ------------------------------------------------------------------------------------------
-enum { KT_PACK = 0, KT_SUBFILTER, KT_COMPACT, KT_CANDIDATE, KT_N };
+enum { KT_PACK = 0, KT_SUBFILTER, KT_COMPACT, KT_CANDIDATE, KT_GENERIC, KT_N };   // KT_CANDIDATE = closed-form kernel, KT_GENERIC = generic kernel
 
 struct Slot {
 	bool ready = false;
@@ -71,7 +71,8 @@ struct Slot {
 	uint32_t* d_passmask = nullptr; uint32_t* d_blocksum = nullptr; uint32_t* d_cand = nullptr; uint32_t* d_ncand = nullptr; uint32_t* d_slow = nullptr;
 	uint8_t* d_records = nullptr; unsigned long long* d_counters = nullptr;
 	uint8_t* h_records = nullptr;            // pinned staging
-	uint64_t* h_counters = nullptr;          // pinned: DBT_N_COUNTERS u64 + 2 u32 (ncand, err)
+	uint64_t* h_counters = nullptr;          // pinned: DBT_N_COUNTERS u64 + 4 u32 (ncand, err, nslow, -)
+	uint64_t last_ncand = 0, last_nslow = 0;
 	uint64_t npairs = 0, first_pair_index = 0;
 	bool uploaded = false, processed = false, fetch_pending = false;
 	dbt_batch_result* result = nullptr;
@@ -167,7 +168,7 @@ extern "C" int dbt_create(dbt_ctx** out, const dbt_params* p) {
 	ws += (size_t)(rp.umax + 2) * 2;                 // ustart
 	ws += (size_t)2 * rp.umax * 2;                   // umid, perm
 	rp.warp_smem = round_up((uint32_t)ws, 16);
-	size_t block_smem = (size_t)rp.warp_smem * CAND_WARPS_FAST;
+	size_t block_smem = (size_t)rp.warp_smem * CAND_WARPS_SLOW;
 	if (block_smem > c->smem_optin) {
 		const size_t lim = c->smem_optin;
 		delete c;
@@ -176,8 +177,7 @@ extern "C" int dbt_create(dbt_ctx** out, const dbt_params* p) {
 	const size_t slow_smem = (size_t)rp.warp_smem * CAND_WARPS_SLOW;
 	unsigned blocks_per_sm = (unsigned)std::max<size_t>(1, std::min<size_t>(4, (size_t)(prop.sharedMemPerMultiprocessor - 1024) / (slow_smem + 1024)));
 	c->cand_grid = (unsigned)c->nsm * blocks_per_sm;
-	unsigned fast_per_sm = (unsigned)std::max<size_t>(1, std::min<size_t>(2, (size_t)(prop.sharedMemPerMultiprocessor - 1024) / (block_smem + 1024)));
-	c->cand_grid_fast = (unsigned)c->nsm * fast_per_sm;
+	c->cand_grid_fast = (unsigned)c->nsm * 3;            // candidate_fast_kernel: 3 blocks of 8 warps per SM (__launch_bounds__(256, 3))
 	*out = c;
 	return DBT_OK;
 }
@@ -237,7 +237,7 @@ static int ensure_slot(dbt_ctx* c, int si) {
 		cudaError_t e = cudaHostAlloc((void**)&s.h_records, std::max<size_t>((size_t)c->p.max_records * rp.rec_stride, 16), cudaHostAllocDefault);
 		if (e != cudaSuccess) { cudaGetLastError(); return fail(DBT_E_NOMEM, "cudaHostAlloc(records): %s", cudaGetErrorString(e)); }
 	}
-	CU(cudaHostAlloc((void**)&s.h_counters, (DBT_N_COUNTERS + 1) * sizeof(uint64_t), cudaHostAllocDefault));
+	CU(cudaHostAlloc((void**)&s.h_counters, (DBT_N_COUNTERS + 2) * sizeof(uint64_t), cudaHostAllocDefault));
 	for (auto& e : s.ev) CU(cudaEventCreate(&e));
 	CU(cudaEventCreate(&s.t0)); CU(cudaEventCreate(&s.t1));
 	s.ready = true;
@@ -485,12 +485,13 @@ extern "C" int dbt_process(dbt_ctx* c, int slot) {
 	CU(cudaMemsetAsync(s.d_ncand, 0, 4, s.st));
 	CU(cudaMemsetAsync(s.d_ncand + 2, 0, 4, s.st));
 	CU(cudaEventRecord(s.ev[1], s.st));
-	CU(launch_subfilter(s.st, c->B, c->nsm, c->ix, c->rp, sv)); ++c->launches;
+	CU(launch_subfilter(s.st, c->B, c->nsm, c->ix, c->rp, sv)); if (s.npairs) ++c->launches;
 	CU(cudaEventRecord(s.ev[2], s.st));
 	if (s.npairs) { CU(launch_compact(s.st, sv)); c->launches += 3; }
 	CU(cudaEventRecord(s.ev[3], s.st));
-	CU(launch_candidate(s.st, c->B, c->cand_grid_fast, c->cand_grid, c->ix, c->rp, sv)); c->launches += 2;
-	CU(cudaEventRecord(s.ev[4], s.st));
+	CU(launch_candidate(s.st, c->B, c->cand_grid_fast, c->cand_grid, c->ix, c->rp, sv, s.ev[4]));
+	if (s.npairs) c->launches += ((c->p.flags & DBT_F_TRACE) || c->rp.nk_max > 255) ? 1 : 2;   // generic kernel alone, or closed-form + generic
+	CU(cudaEventRecord(s.ev[5], s.st));
 	s.processed = true; s.ev_proc = true;
 	return DBT_OK;
 }
@@ -501,7 +502,7 @@ extern "C" int dbt_fetch(dbt_ctx* c, dbt_batch_result* r, int slot) {
 	if (!s.processed) return fail(DBT_E_STATE, "slot %d has not been processed", slot);
 	if (!r) return fail(DBT_E_BADARG, "null result");
 	CU(cudaMemcpyAsync(s.h_counters, s.d_counters, DBT_N_COUNTERS * 8, cudaMemcpyDeviceToHost, s.st));
-	CU(cudaMemcpyAsync(s.h_counters + DBT_N_COUNTERS, s.d_ncand, 8, cudaMemcpyDeviceToHost, s.st));
+	CU(cudaMemcpyAsync(s.h_counters + DBT_N_COUNTERS, s.d_ncand, 16, cudaMemcpyDeviceToHost, s.st));
 	s.result = r; s.fetch_pending = true;
 	return DBT_OK;
 }
@@ -521,6 +522,7 @@ extern "C" int dbt_wait(dbt_ctx* c, int slot) {
 	dbt_batch_result* r = s.result; s.result = nullptr;
 	const uint32_t* tail = reinterpret_cast<const uint32_t*>(s.h_counters + DBT_N_COUNTERS);
 	const uint32_t ncand = tail[0], err = tail[1];
+	s.last_ncand = ncand; s.last_nslow = tail[2];
 	if (err & ERR_READ_TOO_LONG) return fail(DBT_E_CAPACITY, "a read is longer than max_read_len=%u", c->p.max_read_len);
 	for (int i = 0; i < DBT_N_COUNTERS; ++i) r->counters[i] = s.h_counters[i];
 	r->counters[DBT_C_NREADS] = 2 * s.npairs;
@@ -604,8 +606,17 @@ extern "C" int dbt_kernel_times(dbt_ctx* c, int slot, float ms[8], uint32_t laun
 	if (s.ev_proc) {
 		CU(cudaEventElapsedTime(&ms[KT_SUBFILTER], s.ev[1], s.ev[2])); launches[KT_SUBFILTER] = 1;
 		CU(cudaEventElapsedTime(&ms[KT_COMPACT], s.ev[2], s.ev[3])); launches[KT_COMPACT] = 3;
-		CU(cudaEventElapsedTime(&ms[KT_CANDIDATE], s.ev[3], s.ev[4])); launches[KT_CANDIDATE] = 2;
+		const bool all = (c->p.flags & DBT_F_TRACE) || c->rp.nk_max > 255;
+		CU(cudaEventElapsedTime(&ms[KT_CANDIDATE], s.ev[3], s.ev[4])); launches[KT_CANDIDATE] = all ? 0 : 1;
+		CU(cudaEventElapsedTime(&ms[KT_GENERIC], s.ev[4], s.ev[5])); launches[KT_GENERIC] = 1;
 	}
+	return DBT_OK;
+}
+
+extern "C" int dbt_batch_stats(dbt_ctx* c, int slot, uint64_t stats[4]) {
+	if (!c || !stats) return fail(DBT_E_BADARG, "null argument");
+	if (slot < 0 || slot >= DBT_N_SLOTS) return fail(DBT_E_BADARG, "slot %d out of range", slot);
+	stats[0] = c->slot[slot].last_ncand; stats[1] = c->slot[slot].last_nslow; stats[2] = stats[3] = 0;
 	return DBT_OK;
 }
 

@@ -9,8 +9,7 @@ namespace dbt {
 
 constexpr uint32_t NAN32 = 0xFFFFFFFFu;
 constexpr int VOTE_SMEM_SLOTS = 64;          // per-pair shared-memory (locus -> hits1,hits2) entries
-constexpr int CAND_WARPS_FAST = 8;             // phase-synchronous kernel: warps per block (2 blocks / SM)
-constexpr int CAND_WARPS_SLOW = 4;             // generic kernel
+constexpr int CAND_WARPS_SLOW = 4;             // generic candidate_kernel: warps per block
 
 // resident RPGG index
 struct DevIndex {

@@ -221,7 +221,7 @@ __global__ void __launch_bounds__(256) compact_scatter_kernel(SlotView sv) {
 
 }  // namespace dbt
 
-#include "candidate.cuh"
+#include "candidate_fast.cuh"
 
 namespace dbt {
 
@@ -338,23 +338,27 @@ cudaError_t launch_compact(cudaStream_t st, const SlotView& sv) {
 }
 
 template <int B, int MAXJ>
-static cudaError_t launch_candidate_t(cudaStream_t st, unsigned grid_fast, unsigned grid_slow, size_t warp_smem, const DevIndex& ix, const RunParams& rp, const SlotView& sv) {
-	const size_t smem_fast = warp_smem * CAND_WARPS_FAST, smem_slow = warp_smem * CAND_WARPS_SLOW;
-	cudaError_t e = cudaFuncSetAttribute(candidate_kernel<B, MAXJ, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_fast);
+static cudaError_t launch_candidate_t(cudaStream_t st, unsigned grid_fast, unsigned grid_slow, size_t warp_smem, const DevIndex& ix, const RunParams& rp, const SlotView& sv, cudaEvent_t mid) {
+	const size_t smem_slow = warp_smem * CAND_WARPS_SLOW;
+	cudaError_t e = cudaFuncSetAttribute(candidate_kernel<B, MAXJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_slow);
 	if (e != cudaSuccess) return e;
-	e = cudaFuncSetAttribute(candidate_kernel<B, MAXJ, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_slow);
-	if (e != cudaSuccess) return e;
-	candidate_kernel<B, MAXJ, true><<<grid_fast, CAND_WARPS_FAST * 32, smem_fast, st>>>(ix, rp, sv);
-	candidate_kernel<B, MAXJ, false><<<grid_slow, CAND_WARPS_SLOW * 32, smem_slow, st>>>(ix, rp, sv);
+	// DBT_F_TRACE wants the exact (top.fc, top.rc) of every pair; reads with > 255 k-mers overflow the
+	// reference's uint8 multiplicities (cpp:42), which only the generic kernel reproduces
+	const bool all = (rp.flags & DBT_F_TRACE) != 0 || MAXJ > 8 || rp.nk_max > 255;
+	if constexpr (MAXJ <= 8) {
+		if (!all) candidate_fast_kernel<B, MAXJ><<<grid_fast, CAND_FAST_WARPS * 32, 0, st>>>(ix, rp, sv);
+	}
+	if (mid) { e = cudaEventRecord(mid, st); if (e != cudaSuccess) return e; }
+	candidate_kernel<B, MAXJ><<<grid_slow, CAND_WARPS_SLOW * 32, smem_slow, st>>>(ix, rp, sv, all ? 1 : 0);
 	return cudaGetLastError();
 }
 
-cudaError_t launch_candidate(cudaStream_t st, int B, unsigned grid_fast, unsigned grid_slow, const DevIndex& ix, const RunParams& rp, const SlotView& sv) {
-	if (!sv.npairs) return cudaSuccess;
+cudaError_t launch_candidate(cudaStream_t st, int B, unsigned grid_fast, unsigned grid_slow, const DevIndex& ix, const RunParams& rp, const SlotView& sv, cudaEvent_t mid) {
+	if (!sv.npairs) return mid ? cudaEventRecord(mid, st) : cudaSuccess;
 	int maxj = (int)(rp.nkp / 32);
-	if (maxj <= 5)      { DISPATCH_B(B, return launch_candidate_t<BB, 5>(st, grid_fast, grid_slow, rp.warp_smem, ix, rp, sv)); }
-	else if (maxj <= 8) { DISPATCH_B(B, return launch_candidate_t<BB, 8>(st, grid_fast, grid_slow, rp.warp_smem, ix, rp, sv)); }
-	else if (maxj <= 16){ DISPATCH_B(B, return launch_candidate_t<BB, 16>(st, grid_fast, grid_slow, rp.warp_smem, ix, rp, sv)); }
+	if (maxj <= 5)      { DISPATCH_B(B, return launch_candidate_t<BB, 5>(st, grid_fast, grid_slow, rp.warp_smem, ix, rp, sv, mid)); }
+	else if (maxj <= 8) { DISPATCH_B(B, return launch_candidate_t<BB, 8>(st, grid_fast, grid_slow, rp.warp_smem, ix, rp, sv, mid)); }
+	else if (maxj <= 16){ DISPATCH_B(B, return launch_candidate_t<BB, 16>(st, grid_fast, grid_slow, rp.warp_smem, ix, rp, sv, mid)); }
 	return cudaErrorInvalidValue;
 }
 

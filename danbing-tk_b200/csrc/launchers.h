@@ -6,7 +6,7 @@ cudaError_t launch_pack(cudaStream_t st, const uint8_t* ascii, const uint64_t* o
                         uint64_t* p0, uint64_t* p1, uint16_t* m0, uint16_t* m1, uint32_t* err);
 cudaError_t launch_subfilter(cudaStream_t st, int B, int nsm, const DevIndex& ix, const RunParams& rp, const SlotView& sv);
 cudaError_t launch_compact(cudaStream_t st, const SlotView& sv);
-cudaError_t launch_candidate(cudaStream_t st, int B, unsigned grid_fast, unsigned grid_slow, const DevIndex& ix, const RunParams& rp, const SlotView& sv);
+cudaError_t launch_candidate(cudaStream_t st, int B, unsigned grid_fast, unsigned grid_slow, const DevIndex& ix, const RunParams& rp, const SlotView& sv, cudaEvent_t mid);
 cudaError_t launch_insert(cudaStream_t st, int B, Table t, const uint64_t* keys, const uint32_t* vals, uint64_t n, uint32_t* err);
 cudaError_t launch_fill_aux(cudaStream_t st, int B, Table t, const uint32_t* vv, uint32_t* vv_aux, const uint64_t* kmers,
                             const uint32_t* locus_of, uint64_t n, uint32_t cls, uint32_t* err);

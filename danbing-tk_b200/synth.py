@@ -179,7 +179,7 @@ def random_read(rng, rlen=150):
 
 
 def sim_reads(loci, npairs, seed=1, frac_locus=0.5, frac_chimeric=0.1, frac_border=0.1, frac_n=0.05,
-              frac_short=0.01, frac_lower=0.01, err=0.0, rlen=150):
+              frac_short=0.01, frac_lower=0.01, err=0.0, rlen=150, frac_onemate=0.0, flen=500):
     """Mixed test workload: list of (title, mate_first, mate_second) in ARRIVAL order (/1 then /2).
     Includes the trap cases of SURVEY.md F4: chimeric two-locus pairs (trap 5), corrupted tails,
     N / lower-case bases (trap 1-2), short mates (trap 4), pure background."""
@@ -191,21 +191,32 @@ def sim_reads(loci, npairs, seed=1, frac_locus=0.5, frac_chimeric=0.1, frac_bord
         l = int(rng.integers(0, L))
         hap = loci[l][int(rng.integers(0, len(loci[l])))]
         if u < frac_locus:
-            a, b = sim_pair(hap, rng, rlen)
+            a, b = sim_pair(hap, rng, rlen, flen)
             kind = "loc%d" % l
         elif u < frac_locus + frac_chimeric and L > 1:
             l2 = int((l + 1 + rng.integers(0, L - 1)) % L)
             hap2 = loci[l2][int(rng.integers(0, len(loci[l2])))]
-            a1, b1 = sim_pair(hap, rng, rlen)
-            a2, b2 = sim_pair(hap2, rng, rlen)
+            a1, b1 = sim_pair(hap, rng, rlen, flen)
+            a2, b2 = sim_pair(hap2, rng, rlen, flen)
             c1, c2 = int(rng.integers(30, 121)), int(rng.integers(30, 121))
             a, b = a1[:c1] + a2[c1:], b1[:c2] + b2[c2:]
             kind = "chi%d_%d" % (l, l2)
         elif u < frac_locus + frac_chimeric + frac_border:
-            a, b = sim_pair(hap, rng, rlen)
+            a, b = sim_pair(hap, rng, rlen, flen)
             c1, c2 = int(rng.integers(40, 140)), int(rng.integers(40, 140))
             a, b = a[:c1] + random_read(rng, rlen - c1), b[:c2] + random_read(rng, rlen - c2)
             kind = "bor%d" % l
+        elif u < frac_locus + frac_chimeric + frac_border + frac_onemate:
+            # one mate keeps only a short locus prefix (passes subfilter at position 0, removed by kfilter), the
+            # other a locus prefix of random length: exercises the single-mate accept band
+            # 2*cth <= hits < 3*cth-1 of the locus vote (cpp:398, 439-440)
+            a, b = sim_pair(hap, rng, rlen, flen)
+            c1, c2 = int(rng.integers(40, rlen + 1)), int(rng.integers(25, 61))
+            a = a[:c1] + random_read(rng, rlen - c1)
+            b = b[:c2] + random_read(rng, rlen - c2)
+            if rng.random() < 0.5:
+                a, b = b, a
+            kind = "one%d" % l
         else:
             a, b = random_read(rng, rlen), random_read(rng, rlen)
             kind = "bg"

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define DBT_ABI_VERSION 1
+#define DBT_ABI_VERSION 2
 
 /* ---- error codes -------------------------------------------------------------------------- */
 #define DBT_OK            0
@@ -77,7 +77,12 @@ enum {
   DBT_C_NINC,                  /* TR k-mer occurrences incremented (= sum of counts delta)      */
   DBT_C_NCANDIDATES,           /* pairs that reached kfilter                                    */
   DBT_C_NRECORDS,              /* records emitted                                               */
-  DBT_N_COUNTERS = 16
+  /* measurement only (no reference counterpart): share of the work done by the generic candidate kernel */
+  DBT_C_GEN_PAIRS,             /* candidate pairs processed by the generic (exact replay) kernel */
+  DBT_C_GEN_NHASH1,            /* their part of DBT_C_NHASH1                                    */
+  DBT_C_GEN_NTHREADINGREADS,   /* their part of DBT_C_NTHREADINGREADS                           */
+  DBT_C_GEN_NINC,              /* their part of DBT_C_NINC                                      */
+  DBT_N_COUNTERS = 24
 };
 
 typedef struct dbt_ctx dbt_ctx;
@@ -219,6 +224,8 @@ int  dbt_timer_start(dbt_ctx*, int slot);
 int  dbt_timer_stop (dbt_ctx*, int slot, float* ms);          /* synchronises the slot           */
 int  dbt_kernel_times(dbt_ctx*, int slot, float ms[8], uint32_t launches[8]); /* last dbt_process */
 uint64_t dbt_launch_count(const dbt_ctx*);                    /* kernels launched since create   */
+/* after dbt_wait(slot): [0] candidate pairs, [1] pairs the closed-form kernel left to the generic one */
+int  dbt_batch_stats(dbt_ctx*, int slot, uint64_t stats[4]);
 int  dbt_table_stats(const dbt_ctx*, uint64_t stats[8]);      /* buckets, slots, keys, overflowed, bytes... */
 int  dbt_random_gather_bench(int device, uint64_t table_bytes, uint32_t sector_bytes,
                              uint64_t n_gathers, int iters, float* best_ms); /* R_rand roofline    */

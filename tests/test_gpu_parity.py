@@ -85,9 +85,11 @@ def oracle_vs_gpu(ix, seqs, p_gpu, p_oracle=None, batch=None):
         assert recs.tobytes() == orecs.tobytes()                       # record buffers byte-identical
     else:
         keep = orecs[orecs["h"]["status"] == 6].copy()
-        keep["h"]["nhash0"] = 0                                         # per-pair nhash0 is a trace-mode field
+        keep["h"]["nhash0"] = 0                                         # per-pair nhash0, top.fc/top.rc are trace-mode fields
+        keep["h"]["fc"] = 0
+        keep["h"]["rc"] = 0
         assert recs.tobytes() == keep.tobytes()
-    names = [n for n in abi.COUNTER_NAMES if n not in ("nrecords",)]
+    names = [n for n in abi.COUNTER_NAMES if n not in abi.MEASUREMENT_COUNTERS]
     assert {n: int(cnt[i]) for i, n in enumerate(abi.COUNTER_NAMES) if n in names} == \
            {n: int(ocnt[i]) for i, n in enumerate(abi.COUNTER_NAMES) if n in names}
     return recs, cnt
@@ -100,6 +102,27 @@ def test_gpu_matches_oracle_seeded(k, cth, flank, bucket):
                                  frac_locus=0.4, frac_chimeric=0.3, frac_border=0.15)
     p = abi.default_params(k=k, cth=cth, flags=abi.F_KAM | abi.F_TRACE, max_batch_pairs=8192)
     p.bucket_slots = bucket
+    oracle_vs_gpu(ix, seqs, p)
+
+
+@pytest.mark.parametrize("k,cth,bucket,err", [(21, 45, 2, 0.0), (21, 30, 4, 0.004), (17, 25, 2, 0.002), (25, 40, 2, 0.0), (21, 10, 2, 0.01)])
+def test_gpu_fast_path_matches_oracle(k, cth, bucket, err):
+    """production mode (no DBT_F_TRACE): candidate_fast_kernel decides one-locus pairs in closed form and defers the
+    rest to the generic kernel; one-mate pairs sweep the order-dependent band 2*cth <= hits < 3*cth-1"""
+    ix, seqs, _ = synthetic_case(nloci=60, seed=300 + k + cth, k=k, flank=300, npairs=12000, read_seed=cth + 1,
+                                 frac_locus=0.35, frac_chimeric=0.15, frac_border=0.1, frac_onemate=0.3, err=err)
+    p = abi.default_params(k=k, cth=cth, flags=abi.F_KAM, max_batch_pairs=12288)
+    p.bucket_slots = bucket
+    recs, cnt = oracle_vs_gpu(ix, seqs, p)
+    c = dict(zip(abi.COUNTER_NAMES, cnt.tolist()))
+    assert c["nLocusAssignFiltered"] > 0 and c["nKmerFiltered"] > 0 and c["nAsgnReads"] > 0
+
+
+def test_gpu_fast_path_long_reads():
+    """250 bp reads (MAXJ = 8 instantiation) through the fast path"""
+    ix, seqs, _ = synthetic_case(nloci=30, seed=77, k=21, flank=400, npairs=4000, read_seed=3, rlen=250, flen=600,
+                                 frac_locus=0.5, frac_chimeric=0.1, frac_border=0.1, frac_onemate=0.2)
+    p = abi.default_params(k=21, cth=45, flags=abi.F_KAM, max_read_len=250, max_batch_pairs=4096)
     oracle_vs_gpu(ix, seqs, p)
 
 
