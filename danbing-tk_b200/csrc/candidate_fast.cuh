@@ -14,8 +14,13 @@
 //   F <  2*cth       -> fc + 0 < 2*cth           -> reject, whatever the visiting order
 //   F >= 3*cth - 1   -> fc >= F - (cth-1) >= 2*cth -> accept, whatever the visiting order
 //   otherwise the outcome depends on the multiplicities met last -> generic kernel (exact replay).
-// Pairs with a multi-locus k-mer, hits in two loci, or that undecided band are appended to sv.slow and
-// left untouched for candidate_kernel.  Counts are accumulated per k-mer OCCURRENCE exactly as
+// The same holds with multi-locus k-mers present, as long as A is in the locus list of EVERY hit and the
+// hit positions unique to A (S1) are at least as many as those on shared k-mers (S2 >= the largest single
+// multiplicity): fillstats visits the unique k-mers first (ascending #loci, cpp:320), so when a shared
+// k-mer raises hits[B] to at most S2_before + d <= S1 + S2_before = hits[A], updatetop2's strict `>`
+// (cpp:332) never moves top away from A, and every later entry counts for top.idx (cpp:405-416).
+// Pairs with unique hits in two loci, a hit outside A, S1 < S2, or in that undecided band are appended to
+// sv.slow and left untouched for candidate_kernel.  Counts are accumulated per k-mer OCCURRENCE exactly as
 // cpp:2155-2158 does (one increment per position with as == 2), aggregated per warp with
 // __match_any_sync before the 64-bit atomic.
 #pragma once
@@ -162,28 +167,59 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 			continue;
 		}
 
-		// ---- degenerate vote: every hit of the surviving mates unique to ONE locus? ----
-		uint32_t val0 = 0; bool have0 = false, differs = false;
+		// ---- degenerate vote: one DOMINANT locus A? ----
+		// A = locus of the first hit that is unique to one locus (even value, kio:59-74)
+		uint32_t val0 = 0; bool have0 = false;
 #pragma unroll 1
-		for (int m = 0; m < 2; ++m) {
+		for (int m = 0; m < 2 && !have0; ++m) {
 			if ((rmm >> m) & 1u) continue;
 #pragma unroll 1
-			for (int j = 0; j < MAXJ; ++j) {
-				const uint32_t hm = W.hit[m][j];
-				if (!hm) continue;
+			for (int j = 0; j < MAXJ && !have0; ++j) {
 				const uint32_t v = W.val[m][j * 32 + lane];
-				if (!have0) { val0 = __shfl_sync(0xffffffffu, v, __ffs(hm) - 1); have0 = true; }
-				if (((hm >> lane) & 1u) && v != val0) differs = true;
+				const uint32_t em = W.hit[m][j] & __ballot_sync(0xffffffffu, !(v & 1u));
+				if (em) { val0 = __shfl_sync(0xffffffffu, v, __ffs(em) - 1); have0 = true; }
 			}
 		}
-		const bool one_locus = have0 && !(val0 & 1u) && !__any_sync(0xffffffffu, differs) && rp.nk_max <= 255;
+		const uint32_t dst0 = val0 >> 1;
+		// class of every k-mer w.r.t. A (= what assignTRkmc looks up, cpp:1464-1469); a hit belongs to A iff its class != 0
+		bool differs = false; uint32_t S2 = 0;                   // S2 = hit positions of surviving mates on multi-locus k-mers
+		if (have0) {
+#pragma unroll 1
+			for (int m = 0; m < 2; ++m) {
+				const bool rmv = (rmm >> m) & 1u;
+				if (rmv && !okam) {                                 // cpp:1451: a removed mate is only annotated for the kam line
+					if (lane == 0) {
+#pragma unroll
+						for (int j = 0; j < MAXJ; ++j) { W.F[m][j] = 0; W.T[m][j] = 0; }
+					}
+					continue;
+				}
+				const uint32_t nkm = m ? nk1 : nk0;
+#pragma unroll
+				for (int j = 0; j < MAXJ; ++j) {
+					const uint32_t i = j * 32 + lane;
+					const uint32_t v = W.val[m][i];
+					uint32_t cw = 0;
+					if (i < nkm) cw = classify2(ix, v, W.aux[m][i], dst0);
+					W.aux[m][i] = cw;                               // from here on: class word w.r.t. A
+					const uint32_t fm = __ballot_sync(0xffffffffu, (cw >> AUX_CLASS_SHIFT) == 1);
+					const uint32_t tm = __ballot_sync(0xffffffffu, (cw >> AUX_CLASS_SHIFT) == 2);
+					const uint32_t om = __ballot_sync(0xffffffffu, v & 1u);
+					const uint32_t hm = W.hit[m][j];
+					if (!rmv) { if (hm != (fm | tm)) differs = true; S2 += __popc(hm & om); }
+					if (lane == 0) { W.F[m][j] = fm; W.T[m][j] = tm; }
+				}
+			}
+		}
+		// Certain outcomes (see the header): every hit of the surviving mates lies in A, and the k-mers unique to A
+		// (visited first: fillstats sorts by #loci, cpp:320) outweigh any single shared k-mer, so top.idx never leaves A.
 		int verdict = -1;                                        // 1 accept, 0 reject, -1 order-dependent
-		if (one_locus) {
-			if (rmm == 0u || cth == 0) verdict = 1;
-			else {
-				const uint32_t T = (rmm & 1u) ? cnt1 : cnt0;
-				if (T < 2 * cth) verdict = 0;
-				else if (T + 1 >= 3 * cth) verdict = 1;
+		if (have0 && !differs && rp.nk_max <= 255) {
+			const uint32_t Tall = ((rmm & 1u) ? 0u : cnt0) + ((rmm & 2u) ? 0u : cnt1);
+			if (Tall - S2 >= S2) {
+				if (rmm == 0u || cth == 0) verdict = 1;
+				else if (Tall < 2 * cth) verdict = 0;
+				else if (Tall + 1 >= 3 * cth) verdict = 1;
 			}
 		}
 		if (verdict < 0) {                                       // generic path (nothing of this pair has been counted yet)
@@ -193,7 +229,6 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 		if (lane == 0) { c_kf += __popc(kfm); c_h1 += nhash1; }
 
 		// ---- countHit tail (cpp:436-452), QC gate (cpp:2059-2062) ----
-		const uint32_t dst0 = val0 >> 1;
 		uint32_t dst = dst0, hfm = 0;
 		int status = -1;
 		if (!verdict) {
@@ -207,7 +242,8 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 		if (status < 0) {
 			if (lane == 0) c_thr += 2;
 			int span = 0;
-			// ---- assignTRkmc (cpp:1450-1556) against the tables of destLocus0; the class comes with the index entry ----
+			__syncwarp();
+			// ---- assignTRkmc state machine (cpp:1470-1556) on the flank/TR masks ----
 #pragma unroll 1
 			for (int m = 0; m < 2; ++m) {
 				const bool rmv = (rmm >> m) & 1u;
@@ -217,24 +253,14 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 				if (okam || !rmv) {                                 // cpp:1451
 					const uint32_t nkm = m ? nk1 : nk0;
 					nas = nkm;
-					MaskSet<MAXJ> Fs, Ts;
-					uint32_t ntr = 0;
-#pragma unroll
-					for (int j = 0; j < MAXJ; ++j) {
-						const uint32_t i = j * 32 + lane;
-						uint32_t cw = 0;
-						if (i < nkm) cw = classify2(ix, W.val[m][i], W.aux[m][i], dst0);
-						W.aux[m][i] = cw;                           // from here on: class word w.r.t. dst0
-						Fs.w[j] = __ballot_sync(0xffffffffu, (cw >> AUX_CLASS_SHIFT) == 1);
-						Ts.w[j] = __ballot_sync(0xffffffffu, (cw >> AUX_CLASS_SHIFT) == 2);
-						ntr += __popc(Ts.w[j]);
-						if (lane == 0) { W.F[m][j] = Fs.w[j]; W.T[m][j] = Ts.w[j]; }
-					}
 					if (rmv) { mo.nt = -1; mo.bs = -1; mo.ti = -1; }   // cpp:1470-1475
-					else mo = assign_masks<MAXJ>(Fs, Ts, (int)nkm, ntr & 0xFF, rp.nm_tr, mo);   // uint8_t ntr (cpp:1454)
-				} else if (lane == 0) {
+					else {
+						MaskSet<MAXJ> Fs, Ts;
+						uint32_t ntr = 0;
 #pragma unroll
-					for (int j = 0; j < MAXJ; ++j) { W.F[m][j] = 0; W.T[m][j] = 0; }
+						for (int j = 0; j < MAXJ; ++j) { Fs.w[j] = W.F[m][j]; Ts.w[j] = W.T[m][j]; ntr += __popc(Ts.w[j]); }
+						mo = assign_masks<MAXJ>(Fs, Ts, (int)nkm, ntr & 0xFF, rp.nm_tr, mo);   // uint8_t ntr (cpp:1454)
+					}
 				}
 				if (mo.rm) rmm |= 1u << m;
 				span += mo.ei - mo.si;
