@@ -30,28 +30,41 @@ namespace dbt {
 
 constexpr int CAND_FAST_WARPS = 8;
 
-// Per-warp shared-memory state.  Everything indexed by mate lives here rather than in registers so
-// that the per-mate stages are ROLLED loops: ncu showed the fully unrolled (2 mates x MAXJ) kernel,
-// ~4.4k SASS instructions = 70 KB, to be instruction-fetch bound (stall_no_instruction 5.0 per issue,
-// issue slots 29 % busy) -- its warps run free and the 32 KB L1.5 I-cache cannot hold the loop.
-template <int MAXJ>
+// Per-warp shared-memory state.  Everything indexed by mate or by 32-position group lives here rather
+// than in registers so that the stages are ROLLED loops (2 mates x MAXJ groups): ncu showed the fully
+// unrolled kernel (~4.4k SASS instructions = 70 KB, each executed once per pair) to be instruction-fetch
+// bound (stall_no_instruction 5.0 per issue, issue slots 29 % busy).  Index buckets are staged through
+// shared memory with cp.async so that the probe loop can be rolled and still keep MAXJ x B 16-byte loads
+// per lane in flight.
+template <int B, int MAXJ>
 struct FastWarp {
+	uint4    slot[MAXJ][B][32];            // bucket staging: slot q of the bucket probed for position j*32+lane
 	uint64_t pk[2 * 16];                   // packed records of both mates (W64 <= 16 when nk_max <= 255)
-	uint32_t val[2][MAXJ * 32];            // index value per position
-	uint32_t aux[2][MAXJ * 32];            // aux word per position (AUX_MISS = not in the index); later: class word w.r.t. dst0
+	uint32_t val[2][MAXJ * 32];            // index value per position              (during the probe: k-mer, low half)
+	uint32_t aux[2][MAXJ * 32];            // aux word per position, AUX_MISS = not in the index (during the probe: k-mer, high half);
+	                                       // after classification: class word w.r.t. dst0
 	uint32_t hit[2][MAXJ], F[2][MAXJ], T[2][MAXJ];   // ballots: in the index / flank of dst0 / TR of dst0
 	dbt_mate_record mate[2];
 };
 
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+	const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+	asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
 template <int B, int MAXJ>
 __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel(DevIndex ix, RunParams rp, SlotView sv) {
-	__shared__ __align__(16) FastWarp<MAXJ> wsm[CAND_FAST_WARPS];
+	extern __shared__ __align__(16) uint8_t fast_smem[];
+	FastWarp<B, MAXJ>* wsm = reinterpret_cast<FastWarp<B, MAXJ>*>(fast_smem);
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
 	const uint32_t gwarp = blockIdx.x * CAND_FAST_WARPS + wib, nwarps = gridDim.x * CAND_FAST_WARPS;
 	const uint32_t W64 = rp.lay.W64, WB = rp.lay.WB, K = rp.k;
 	const bool okam = (rp.flags & DBT_F_KAM) != 0;
 	const uint32_t nloci = (uint32_t)ix.nloci, cth = rp.cth;
-	FastWarp<MAXJ>& W = wsm[wib];
+	FastWarp<B, MAXJ>& W = wsm[wib];
 	uint32_t c_kf = 0, c_laf = 0, c_qc = 0, c_thr = 0, c_asgn = 0, c_h1 = 0, c_inc = 0;   // lane-0 accumulators
 	const uint32_t nwork = sv.ncand[0];
 
@@ -69,23 +82,21 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 		__syncwarp();
 
 		// ---- all canonical k-mers + ONE index probe each (A2 + the look-ups of kfilter, cpp:207/218) ----
-		// per mate: MAXJ independent bucket loads in flight per lane before any is inspected
 #pragma unroll 1
 		for (int m = 0; m < 2; ++m) {
 			const uint32_t nkm = m ? nk1 : nk0;
-			uint4 s[MAXJ][B];
-			uint64_t key[MAXJ];
 			const uint64_t* rec = W.pk + m * W64;
 			const uint32_t* mk32 = reinterpret_cast<const uint32_t*>(rec + WB);
 			const uint32_t sh = 2 * lane;
 			const uint64_t kmask = (1ull << (2 * K)) - 1, vmask = (1ull << K) - 1;
-			uint64_t wlo = rec[0];
-			uint32_t mlo = mk32[0];
-#pragma unroll
+			// round 1: k-mer of position j*32+lane, home bucket -> shared memory (asynchronously)
+#pragma unroll 1
 			for (int j = 0; j < MAXJ; ++j) {
 				const uint32_t i = j * 32 + lane;
-				const uint64_t whi = (j + 1 < (int)WB) ? rec[j + 1] : 0ull;
-				const uint32_t mnx = ((uint32_t)(j + 1) < 2 * rp.lay.WM) ? mk32[j + 1] : 0xFFFFFFFFu;
+				// k-mers at positions lane+32j: same bit offset (2*lane) in consecutive base words, same bit
+				// offset (lane) in consecutive 32-bit halves of the invalid mask -> funnel shifts
+				const uint64_t wlo = rec[j], whi = (j + 1 < (int)WB) ? rec[j + 1] : 0ull;
+				const uint32_t mlo = mk32[j], mnx = ((uint32_t)(j + 1) < 2 * rp.lay.WM) ? mk32[j + 1] : 0xFFFFFFFFu;
 				const uint64_t wv = sh ? ((wlo >> sh) | (whi << (64 - sh))) : wlo;
 				const uint64_t mm = (((uint64_t)mnx << 32) | mlo) >> lane;
 				uint64_t kk = KMER_INVALID;
@@ -93,32 +104,75 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 					const uint64_t x = wv & kmask, rcx = (~wv) & kmask, fw = rev2(x) >> (64 - 2 * K);
 					kk = fw < rcx ? fw : rcx;
 				}
-				key[j] = kk;
-				wlo = whi; mlo = mnx;
+				W.val[m][i] = (uint32_t)kk; W.aux[m][i] = (uint32_t)(kk >> 32);
 				if (kk != KMER_INVALID) {
-					const uint64_t hb = home_bucket(ix.table, kk);
+					const uint4* bp = ix.table.slots + home_bucket(ix.table, kk) * B;
 #pragma unroll
-					for (int q = 0; q < B; ++q) s[j][q] = ldg128(ix.table.slots + hb * B + q);
+					for (int q = 0; q < B; ++q) cp_async16(&W.slot[j][q][lane], bp + q);
 				}
 			}
-#pragma unroll
+			cp_async_wait_all();
+			// inspect; a full bucket with the overflow flag sends the lane to the next bucket (round 2, again batched)
+			uint32_t need = 0;                                    // bit j: position j*32+lane continues in the next bucket
+#pragma unroll 1
 			for (int j = 0; j < MAXJ; ++j) {
+				const uint32_t i = j * 32 + lane;
+				const uint64_t key = ((uint64_t)W.aux[m][i] << 32) | W.val[m][i];
 				uint32_t v = 0, a = AUX_MISS;
-				if (key[j] != KMER_INVALID) {
-					bool full = true, found = false;
+				if (key != KMER_INVALID) {
+					bool full = true, found = false; uint64_t k0 = 0;
 #pragma unroll
 					for (int q = 0; q < B; ++q) {
-						const uint64_t kk = slot_key(s[j][q]);
+						const uint4 e = W.slot[j][q][lane];
+						const uint64_t kk = slot_key(e);
+						if (q == 0) k0 = kk;
 						if (kk == SLOT_EMPTY) full = false;
-						else if ((kk & SLOT_KEYMASK) == key[j]) { v = s[j][q].z; a = s[j][q].w; found = true; }
+						else if ((kk & SLOT_KEYMASK) == key) { v = e.z; a = e.w; found = true; }
 					}
-					if (!found && full && (slot_key(s[j][0]) & SLOT_OVF)) {
-						const uint2 r2 = probe_walk<B>(ix.table.slots, ix.table.nbuckets, key[j], home_bucket(ix.table, key[j]));
+					if (!found && full && (k0 & SLOT_OVF)) need |= 1u << j;
+				}
+				if (!((need >> j) & 1u)) { W.val[m][i] = v; W.aux[m][i] = a; }
+			}
+			if (__any_sync(0xffffffffu, need != 0)) {
+#pragma unroll 1
+				for (int j = 0; j < MAXJ; ++j) {
+					if (!((need >> j) & 1u)) continue;
+					const uint32_t i = j * 32 + lane;
+					const uint64_t key = ((uint64_t)W.aux[m][i] << 32) | W.val[m][i];
+					uint64_t b = home_bucket(ix.table, key) + 1;
+					if (b == ix.table.nbuckets) b = 0;
+					const uint4* bp = ix.table.slots + b * B;
+#pragma unroll
+					for (int q = 0; q < B; ++q) cp_async16(&W.slot[j][q][lane], bp + q);
+				}
+				cp_async_wait_all();
+#pragma unroll 1
+				for (int j = 0; j < MAXJ; ++j) {
+					if (!((need >> j) & 1u)) continue;
+					const uint32_t i = j * 32 + lane;
+					const uint64_t key = ((uint64_t)W.aux[m][i] << 32) | W.val[m][i];
+					uint32_t v = 0, a = AUX_MISS;
+					bool full = true, found = false; uint64_t k0 = 0;
+#pragma unroll
+					for (int q = 0; q < B; ++q) {
+						const uint4 e = W.slot[j][q][lane];
+						const uint64_t kk = slot_key(e);
+						if (q == 0) k0 = kk;
+						if (kk == SLOT_EMPTY) full = false;
+						else if ((kk & SLOT_KEYMASK) == key) { v = e.z; a = e.w; found = true; }
+					}
+					if (!found && full && (k0 & SLOT_OVF)) {           // third bucket and beyond: rare, divergent walk
+						uint64_t b = home_bucket(ix.table, key) + 1;
+						if (b == ix.table.nbuckets) b = 0;
+						const uint2 r2 = probe_walk<B>(ix.table.slots, ix.table.nbuckets, key, b);
 						v = r2.x; a = r2.y;
 					}
+					W.val[m][i] = v; W.aux[m][i] = a;
 				}
-				W.val[m][j * 32 + lane] = v; W.aux[m][j * 32 + lane] = a;
-				const uint32_t hm = __ballot_sync(0xffffffffu, a != AUX_MISS);
+			}
+#pragma unroll 1
+			for (int j = 0; j < MAXJ; ++j) {
+				const uint32_t hm = __ballot_sync(0xffffffffu, W.aux[m][j * 32 + lane] != AUX_MISS);
 				if (lane == 0) W.hit[m][j] = hm;
 			}
 		}

@@ -177,7 +177,7 @@ extern "C" int dbt_create(dbt_ctx** out, const dbt_params* p) {
 	const size_t slow_smem = (size_t)rp.warp_smem * CAND_WARPS_SLOW;
 	unsigned blocks_per_sm = (unsigned)std::max<size_t>(1, std::min<size_t>(4, (size_t)(prop.sharedMemPerMultiprocessor - 1024) / (slow_smem + 1024)));
 	c->cand_grid = (unsigned)c->nsm * blocks_per_sm;
-	c->cand_grid_fast = (unsigned)c->nsm * 3;            // candidate_fast_kernel: 3 blocks of 8 warps per SM (__launch_bounds__(256, 3))
+	c->cand_grid_fast = (unsigned)c->nsm;                // candidate_fast_kernel: the launcher multiplies by the resident blocks per SM
 	*out = c;
 	return DBT_OK;
 }

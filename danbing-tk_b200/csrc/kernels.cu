@@ -338,7 +338,7 @@ cudaError_t launch_compact(cudaStream_t st, const SlotView& sv) {
 }
 
 template <int B, int MAXJ>
-static cudaError_t launch_candidate_t(cudaStream_t st, unsigned grid_fast, unsigned grid_slow, size_t warp_smem, const DevIndex& ix, const RunParams& rp, const SlotView& sv, cudaEvent_t mid) {
+static cudaError_t launch_candidate_t(cudaStream_t st, unsigned nsm, unsigned grid_slow, size_t warp_smem, const DevIndex& ix, const RunParams& rp, const SlotView& sv, cudaEvent_t mid) {
 	const size_t smem_slow = warp_smem * CAND_WARPS_SLOW;
 	cudaError_t e = cudaFuncSetAttribute(candidate_kernel<B, MAXJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_slow);
 	if (e != cudaSuccess) return e;
@@ -346,7 +346,16 @@ static cudaError_t launch_candidate_t(cudaStream_t st, unsigned grid_fast, unsig
 	// reference's uint8 multiplicities (cpp:42), which only the generic kernel reproduces
 	const bool all = (rp.flags & DBT_F_TRACE) != 0 || MAXJ > 8 || rp.nk_max > 255;
 	if constexpr (MAXJ <= 8) {
-		if (!all) candidate_fast_kernel<B, MAXJ><<<grid_fast, CAND_FAST_WARPS * 32, 0, st>>>(ix, rp, sv);
+		if (!all) {
+			constexpr size_t smem_fast = sizeof(FastWarp<B, MAXJ>) * CAND_FAST_WARPS;
+			e = cudaFuncSetAttribute(candidate_fast_kernel<B, MAXJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_fast);
+			if (e != cudaSuccess) return e;
+			int per_sm = 0;
+			e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, candidate_fast_kernel<B, MAXJ>, CAND_FAST_WARPS * 32, smem_fast);
+			if (e != cudaSuccess) return e;
+			if (per_sm < 1) return cudaErrorInvalidConfiguration;
+			candidate_fast_kernel<B, MAXJ><<<nsm * (unsigned)per_sm, CAND_FAST_WARPS * 32, smem_fast, st>>>(ix, rp, sv);
+		}
 	}
 	if (mid) { e = cudaEventRecord(mid, st); if (e != cudaSuccess) return e; }
 	candidate_kernel<B, MAXJ><<<grid_slow, CAND_WARPS_SLOW * 32, smem_slow, st>>>(ix, rp, sv, all ? 1 : 0);
