@@ -451,7 +451,8 @@ def b200_arm(a, config, workdir, rank, world, local, dist):
                "roofline": roofline, "cpu_baseline": cpu,
                "counters_per_step_rank0": cnt, "tr_kmer_increments_per_step_all_ranks": total_inc,
                "index_table": {"buckets": int(stats[0]), "slots_per_bucket": int(stats[1]), "keys": int(stats[2]),
-                               "overflowed_buckets": int(stats[4]), "displaced_keys": int(stats[5]), "bytes": int(stats[6])}}
+                               "overflowed_buckets": int(stats[4]), "stash_keys": int(stats[5]), "bytes": int(stats[6]),
+                               "overflowed_stash_buckets": int(stats[7])}}
         print(json.dumps(out))
     ctx.close()
 

@@ -157,39 +157,46 @@ __device__ __forceinline__ int mw_prev_set(const uint32_t (&w)[MAXJ], int t) {
 
 template <int MAXJ> struct MaskSet { uint32_t w[MAXJ]; };
 
+// lowest set bit of w at a position >= from, or -1
+template <int MAXJ>
+__device__ __forceinline__ int mw_next_set(const uint32_t (&w)[MAXJ], int from) {
+	int best = -1;
+#pragma unroll
+	for (int j = MAXJ - 1; j >= 0; --j) {
+		uint32_t x = w[j];
+		if (j == (from >> 5)) x &= ~((1u << (from & 31)) - 1u);
+		else if (j < (from >> 5)) x = 0;
+		if (x) best = 32 * j + __ffs(x) - 1;
+	}
+	return best;
+}
+
 template <int MAXJ>
 __device__ __noinline__ MateOut assign_masks(const MaskSet<MAXJ> Fs, const MaskSet<MAXJ> Ts, int nk, uint32_t ntr8, uint32_t nm_tr, MateOut r) {
 	const uint32_t (&F)[MAXJ] = Fs.w;
 	const uint32_t (&T)[MAXJ] = Ts.w;
-	uint32_t NZ[MAXJ], TRANS[MAXJ];
-	// state of the latest non-zero k-mer at or before each position (segmented propagate), then
-	// TRANS = non-zero positions whose state differs from the previous non-zero one (cpp:1479-1481)
-	uint32_t carryKnown = 0, carryT = 0, prevKnownBit = 0, prevTBit = 0;
-	int p0 = -1;
+	uint32_t NZ[MAXJ];
 #pragma unroll
-	for (int j = 0; j < MAXJ; ++j) {
-		NZ[j] = F[j] | T[j];
-		if (p0 < 0 && NZ[j]) p0 = 32 * j + __ffs(NZ[j]) - 1;
-		uint32_t known = NZ[j], val = T[j];
-#pragma unroll
-		for (int d = 1; d < 32; d <<= 1) { val |= (val << d) & ~known; known |= known << d; }
-		val |= ~known & (carryT ? 0xFFFFFFFFu : 0u);
-		known |= carryKnown ? 0xFFFFFFFFu : 0u;
-		const uint32_t pK = (known << 1) | prevKnownBit, pT = (val << 1) | prevTBit;     // view of position i-1
-		TRANS[j] = NZ[j] & pK & (T[j] ^ pT);
-		prevKnownBit = known >> 31; prevTBit = val >> 31;
-		if (NZ[j]) { carryKnown = 1; carryT = val >> 31; }
-	}
-	r.bs = p0 < 0 ? 0 : (mw_bit<MAXJ>(T, p0) ? 2 : 1);                                 // cpp:1500
+	for (int j = 0; j < MAXJ; ++j) NZ[j] = F[j] | T[j];
+	// A transition (cpp:1479-1481) is a non-zero k-mer whose state differs from the previous non-zero one.
+	// States alternate, so transition n+1 is the first k-mer after transition n of the other class:
+	// p0 = first non-zero k-mer (state bs, cpp:1500), t1 = first k-mer of the other class after p0,
+	// t2 = first of class bs after t1, t3 = first of the other class after t2.
+	const int pF = mw_next_set<MAXJ>(F, 0), pT = mw_next_set<MAXJ>(T, 0);
+	const int p0 = (pF < 0) ? pT : (pT < 0 ? pF : (pF < pT ? pF : pT));
+	const bool bsT = p0 >= 0 && p0 == pT;
+	r.bs = p0 < 0 ? 0 : (bsT ? 2 : 1);
 	int t1 = -1, t2 = -1, ntrans = 0;
-#pragma unroll
-	for (int j = 0; j < MAXJ; ++j) {
-		uint32_t w = TRANS[j];
-		while (w && ntrans < 3) {
-			const int t = 32 * j + __ffs(w) - 1;
-			w &= w - 1;
-			if (ntrans == 0) t1 = t; else if (ntrans == 1) t2 = t;
-			++ntrans;
+	if (p0 >= 0) {
+		t1 = bsT ? mw_next_set<MAXJ>(F, p0) : mw_next_set<MAXJ>(T, p0);
+		if (t1 >= 0) {
+			ntrans = 1;
+			t2 = bsT ? mw_next_set<MAXJ>(T, t1) : mw_next_set<MAXJ>(F, t1);
+			if (t2 >= 0) {
+				ntrans = 2;
+				const int t3 = bsT ? mw_next_set<MAXJ>(F, t2) : mw_next_set<MAXJ>(T, t2);
+				if (t3 >= 0) ntrans = 3;
+			}
 		}
 	}
 	r.ti = t1;                                                                          // ti1 aliases r.ti (cpp:1457)
@@ -220,21 +227,21 @@ __device__ __noinline__ MateOut assign_masks(const MaskSet<MAXJ> Fs, const MaskS
 // ------------------------------------------------------------------------------------------------
 // out-of-line rare paths (kept out of the hot loop's instruction footprint)
 // ------------------------------------------------------------------------------------------------
-// continue a probe past a full home bucket that carries the overflow flag
+// continue a probe in the stash, starting with stash bucket b (home bucket full + overflow flag)
 template <int B>
-__device__ __noinline__ uint2 probe_walk(const uint4* slots, uint64_t nbuckets, uint64_t key, uint64_t b) {
+__device__ __noinline__ uint2 probe_walk(const Table t, uint64_t key, uint64_t b) {
 	for (;;) {
-		if (++b == nbuckets) b = 0;
 		bool full = true; uint64_t k0 = 0;
 #pragma unroll
 		for (int q = 0; q < B; ++q) {
-			const uint4 e = ldg128(slots + b * B + q);
+			const uint4 e = ldg128(t.slots + b * B + q);
 			const uint64_t kk = slot_key(e);
 			if (q == 0) k0 = kk;
 			if (kk == SLOT_EMPTY) full = false;
 			else if ((kk & SLOT_KEYMASK) == key) return make_uint2(e.z, e.w);
 		}
 		if (!full || !(k0 & SLOT_OVF)) return make_uint2(0u, AUX_MISS);
+		b = stash_next(t, b);
 	}
 }
 
@@ -419,7 +426,7 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 							if (kk == SLOT_EMPTY) full = false;
 							else if ((kk & SLOT_KEYMASK) == key[j]) { v = s[j][q].z; a = s[j][q].w; found = true; }
 						}
-						if (!found && full && (slot_key(s[j][0]) & SLOT_OVF)) { const uint2 r2 = probe_walk<B>(ix.table.slots, ix.table.nbuckets, key[j], hb[j]); v = r2.x; a = r2.y; }
+						if (!found && full && (slot_key(s[j][0]) & SLOT_OVF)) { const uint2 r2 = probe_walk<B>(ix.table, key[j], stash_bucket(ix.table, key[j])); v = r2.x; a = r2.y; }
 					}
 					pkey[m * NKP + i] = key[j]; pval[m * NKP + i] = v; paux[m * NKP + i] = a;
 				}

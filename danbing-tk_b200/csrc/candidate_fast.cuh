@@ -112,8 +112,8 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 				}
 			}
 			cp_async_wait_all();
-			// inspect; a full bucket with the overflow flag sends the lane to the next bucket (round 2, again batched)
-			uint32_t need = 0;                                    // bit j: position j*32+lane continues in the next bucket
+			// inspect; a full bucket with the overflow flag sends the lane to the stash (round 2, again batched)
+			uint32_t need = 0;                                    // bit j: position j*32+lane continues in the stash
 #pragma unroll 1
 			for (int j = 0; j < MAXJ; ++j) {
 				const uint32_t i = j * 32 + lane;
@@ -139,9 +139,7 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 					if (!((need >> j) & 1u)) continue;
 					const uint32_t i = j * 32 + lane;
 					const uint64_t key = ((uint64_t)W.aux[m][i] << 32) | W.val[m][i];
-					uint64_t b = home_bucket(ix.table, key) + 1;
-					if (b == ix.table.nbuckets) b = 0;
-					const uint4* bp = ix.table.slots + b * B;
+					const uint4* bp = ix.table.slots + stash_bucket(ix.table, key) * B;
 #pragma unroll
 					for (int q = 0; q < B; ++q) cp_async16(&W.slot[j][q][lane], bp + q);
 				}
@@ -161,10 +159,8 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 						if (kk == SLOT_EMPTY) full = false;
 						else if ((kk & SLOT_KEYMASK) == key) { v = e.z; a = e.w; found = true; }
 					}
-					if (!found && full && (k0 & SLOT_OVF)) {           // third bucket and beyond: rare, divergent walk
-						uint64_t b = home_bucket(ix.table, key) + 1;
-						if (b == ix.table.nbuckets) b = 0;
-						const uint2 r2 = probe_walk<B>(ix.table.slots, ix.table.nbuckets, key, b);
+					if (!found && full && (k0 & SLOT_OVF)) {           // second stash bucket and beyond: rare, divergent walk
+						const uint2 r2 = probe_walk<B>(ix.table, key, stash_next(ix.table, stash_bucket(ix.table, key)));
 						v = r2.x; a = r2.y;
 					}
 					W.val[m][i] = v; W.aux[m][i] = a;

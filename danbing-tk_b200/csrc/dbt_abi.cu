@@ -268,9 +268,12 @@ extern "C" int dbt_load_index(dbt_ctx* c, const dbt_index* in) {
 	uint64_t nslots_min = (uint64_t)((double)std::max<uint64_t>(in->nk_dbi, 1) / c->p.table_load) + B;
 	uint64_t nbuckets = (nslots_min + B - 1) / B;
 	if (nbuckets < 64) nbuckets = 64;
-	c->table_bytes = nbuckets * B * sizeof(uint4);
+	// stash: slots for half the keys, i.e. load ~0.15 at the default table_load (7 % of the keys overflow at B = 2)
+	uint64_t nstash = std::max<uint64_t>(64, (in->nk_dbi / 2 + B - 1) / B);
+	if (nbuckets >= (1ull << 32) || nstash >= (1ull << 32)) return fail(DBT_E_CAPACITY, "index table needs %llu buckets (limit 2^32)", (unsigned long long)nbuckets);
+	c->table_bytes = (nbuckets + nstash) * B * sizeof(uint4);
 	c->nkeys = in->nk_dbi;
-	TRY(dev_alloc(&c->d_slots, nbuckets * B, "index table"));
+	TRY(dev_alloc(&c->d_slots, (nbuckets + nstash) * B, "index table"));
 	CU(cudaMemsetAsync(c->d_slots, 0xFF, c->table_bytes, st));
 	TRY(dev_alloc(&c->d_vv, in->nvv + 1, "vv"));
 	TRY(dev_alloc(&c->d_vv_aux, in->nvv + 1, "vv_aux"));
@@ -278,7 +281,7 @@ extern "C" int dbt_load_index(dbt_ctx* c, const dbt_index* in) {
 	if (in->nvv) CU(cudaMemcpyAsync(c->d_vv, in->vv, in->nvv * 4, cudaMemcpyHostToDevice, st));
 	uint32_t* d_err; TRY(dev_alloc(&d_err, 1, "err"));
 	CU(cudaMemsetAsync(d_err, 0, 4, st));
-	Table t{c->d_slots, nbuckets};
+	Table t{c->d_slots, nbuckets, nstash};
 	{	// bulk insert of kmers.dbi (readBinaryIndex, h:671)
 		uint64_t* dk; uint32_t* dv;
 		TRY(dev_alloc(&dk, in->nk_dbi, "dbi keys")); TRY(dev_alloc(&dv, in->nk_dbi, "dbi vals"));
@@ -313,6 +316,7 @@ extern "C" int dbt_load_index(dbt_ctx* c, const dbt_index* in) {
 	CU(cudaMemcpy(&herr, d_err, 4, cudaMemcpyDeviceToHost));
 	cudaFree(d_err);
 	if (herr & ERR_INDEX_DUPKEY) return fail(DBT_E_INDEX, "duplicate key in kmers.dbi");
+	if (herr & ERR_INDEX_FULL) return fail(DBT_E_CAPACITY, "index table overflow: lower table_load");
 	if (herr & ERR_INDEX_MISSING) return fail(DBT_E_INDEX, "a tr/fl k-mer is missing from kmers.dbi for its locus (index files out of sync)");
 	if (herr & ERR_INDEX_DUPTR) return fail(DBT_E_INDEX, "duplicate TR k-mer within a locus");
 
@@ -632,7 +636,7 @@ extern "C" int dbt_table_stats(const dbt_ctx* cc, uint64_t stats[8]) {
 	CU(cudaMemcpy(h, d, 32, cudaMemcpyDeviceToHost));
 	cudaFree(d);
 	stats[0] = c->ix.table.nbuckets; stats[1] = (uint64_t)c->B; stats[2] = c->nkeys; stats[3] = h[0]; stats[4] = h[1]; stats[5] = h[2];
-	stats[6] = c->table_bytes; stats[7] = (uint64_t)c->rp.warp_smem;
+	stats[6] = c->table_bytes; stats[7] = h[3];
 	return DBT_OK;
 }
 

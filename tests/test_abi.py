@@ -29,7 +29,7 @@ def test_struct_sizes():
     assert C.sizeof(abi.Params) == 18 * 4
     assert C.sizeof(abi.Index) == 11 * 8
     assert C.sizeof(abi.Batch) == 40
-    assert C.sizeof(abi.BatchResult) == 24 + 16 * 8
+    assert C.sizeof(abi.BatchResult) == 24 + abi.DBT_N_COUNTERS * 8
     assert abi.RECORD_HEADER_DTYPE.itemsize == 64
 
 
