@@ -16,7 +16,7 @@ DBT_N_SLOTS = 2
 DBT_NCCL_ID_BYTES = 128
 
 F_KAM, F_QC, F_TRACE, F_THREADING, F_CORRECTION, F_ALN, F_ALN_MIN = 1, 2, 4, 8, 16, 32, 64
-ST_SHORT, ST_SUBFILTERED, ST_KFILTERED, ST_UNASSIGNED, ST_QCFILTERED, ST_ASGN_REMOVED, ST_COUNTED = range(7)
+ST_SHORT, ST_SUBFILTERED, ST_KFILTERED, ST_UNASSIGNED, ST_QCFILTERED, ST_ASGN_REMOVED, ST_COUNTED, ST_NOT_THREADED = range(8)
 LAYOUT_ASCII, LAYOUT_PACKED = 0, 1
 COUNTER_NAMES = ["nReads", "nShort", "nSubFiltered", "nKmerFiltered", "nBaitFiltered", "nQualFiltered",
                  "nLocusAssignFiltered", "nQCFiltered", "nThreadingReads", "nFeasibleReads", "nAsgnReads",

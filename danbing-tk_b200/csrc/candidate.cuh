@@ -338,7 +338,7 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 	uint16_t* umid  = ustart + UMAX + 2;                                // first mate-1 element of the group
 	uint16_t* perm  = umid + UMAX;                                      // visiting order (cpp:320-327)
 
-	uint32_t c_kf = 0, c_laf = 0, c_qc = 0, c_thr = 0, c_asgn = 0, c_h1 = 0, c_inc = 0, c_pairs = 0;   // lane-0 accumulators
+	uint32_t c_kf = 0, c_laf = 0, c_qc = 0, c_thr = 0, c_asgn = 0, c_h1 = 0, c_inc = 0, c_pairs = 0, c_thr0 = 0;   // lane-0 accumulators
 	uint32_t epoch = 0; uint64_t* scratch = nullptr;
 	epoch = ix.vote_epoch[gwarp]; scratch = ix.vote_scratch + (uint64_t)gwarp * (ix.nloci + 1);
 	const uint32_t nwork = all ? sv.ncand[0] : sv.ncand[2];
@@ -610,6 +610,7 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 		// =========================== phase 4: assignTRkmc, accumulate, record ===========================
 		if (active && !deferred) {
 			if (lane == 0) { c_kf += kf[0] + kf[1]; c_h1 += nhash1; }
+			if (status < 0 && (rp.flags & DBT_F_THREADING)) { status = DBT_ST_NOT_THREADED; if (lane == 0) c_thr0 += 2; }   // cpp:2070-2090 at HEAD
 			if (status < 0) {
 				if (lane == 0) c_thr += 2;
 				// assignTRkmc (cpp:1450-1556) against the tables of destLocus0
@@ -710,7 +711,7 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 		counter_add(sv.counters, DBT_C_NKMERFILTERED, c_kf);
 		counter_add(sv.counters, DBT_C_NLOCUSASSIGNFILTERED, c_laf);
 		counter_add(sv.counters, DBT_C_NQCFILTERED, c_qc);
-		counter_add(sv.counters, DBT_C_NTHREADINGREADS, c_thr);
+		counter_add(sv.counters, DBT_C_NTHREADINGREADS, c_thr + c_thr0);
 		counter_add(sv.counters, DBT_C_NFEASIBLEREADS, c_thr);
 		counter_add(sv.counters, DBT_C_NASGNREADS, c_asgn);
 		counter_add(sv.counters, DBT_C_NHASH1, c_h1);

@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 	const bool okam = (rp.flags & DBT_F_KAM) != 0;
 	const uint32_t nloci = (uint32_t)ix.nloci, cth = rp.cth;
 	FastWarp<B, MAXJ>& W = wsm[wib];
-	uint32_t c_kf = 0, c_laf = 0, c_qc = 0, c_thr = 0, c_asgn = 0, c_h1 = 0, c_inc = 0;   // lane-0 accumulators
+	uint32_t c_kf = 0, c_laf = 0, c_qc = 0, c_thr = 0, c_asgn = 0, c_h1 = 0, c_inc = 0, c_thr0 = 0;   // lane-0 accumulators
 	const uint32_t nwork = sv.ncand[0];
 
 #pragma unroll 1
@@ -289,6 +289,7 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 			if (lane == 0) c_qc += 2 - __popc(rmm);
 		}
 
+		if (status < 0 && (rp.flags & DBT_F_THREADING)) { status = DBT_ST_NOT_THREADED; if (lane == 0) c_thr0 += 2; }   // cpp:2070-2090 at HEAD
 		if (status < 0) {
 			if (lane == 0) c_thr += 2;
 			int span = 0;
@@ -390,7 +391,7 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 		counter_add(sv.counters, DBT_C_NKMERFILTERED, c_kf);
 		counter_add(sv.counters, DBT_C_NLOCUSASSIGNFILTERED, c_laf);
 		counter_add(sv.counters, DBT_C_NQCFILTERED, c_qc);
-		counter_add(sv.counters, DBT_C_NTHREADINGREADS, c_thr);
+		counter_add(sv.counters, DBT_C_NTHREADINGREADS, c_thr + c_thr0);
 		counter_add(sv.counters, DBT_C_NFEASIBLEREADS, c_thr);
 		counter_add(sv.counters, DBT_C_NASGNREADS, c_asgn);
 		counter_add(sv.counters, DBT_C_NHASH1, c_h1);

@@ -1,0 +1,116 @@
+// dbt-hostcheck: exercises the host-side pieces of the CLI without a GPU (used by tests/test_host.py).
+//   tr-order TR.kmers OUT.u64                      loader + libstdc++ iteration-order replay -> u64 nloci | n[nloci] | kmers[]
+//   index PREF [QCFILE]                            loads PREF.{tr.kmers,kmers.dbi,fl.kdb}; prints sizes
+//   pair FASTX isFastq minReadSize readsPerRefBatch pairsCap    reader/pairer -> "title\tseq1\tseq2[\tqual1\tqual2]" per pair
+//   kam RECORDS.bin stride as_stride FASTX isFastq minReadSize   formats records (e.g. from the CPU oracle) as kam lines
+//   args ...                                        parses a command line, prints the resolved options
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "options.hpp"
+#include "rpgg_files.hpp"
+#include "fastx_reader.hpp"
+#include "kam_writer.hpp"
+
+using namespace dbt_host;
+
+static bool alloc_batch(HostBatch& hb, uint64_t pairs, uint64_t bytes) {
+	hb.bases = (uint8_t*)malloc(bytes); hb.bases_cap = bytes;
+	hb.offsets = (uint64_t*)malloc((2 * pairs + 1) * 8); hb.pairs_cap = pairs;
+	return hb.bases && hb.offsets;
+}
+
+static int cmd_tr_order(const char* in, const char* out) {
+	Rpgg g; std::string err;
+	if (!read_tr_kmers_ordered(in, g, 4, err)) { fprintf(stderr, "%s\n", err.c_str()); return 1; }
+	FILE* f = fopen(out, "wb");
+	if (!f) return 1;
+	fwrite(&g.nloci, 8, 1, f); fwrite(g.tr_n.data(), 8, g.tr_n.size(), f); fwrite(g.tr_kmers.data(), 8, g.tr_kmers.size(), f);
+	fclose(f);
+	return 0;
+}
+
+static int cmd_index(const std::string& pref, const std::string& qcfn) {
+	Rpgg g; std::string err;
+	if (!load_rpgg(pref, pref + ".tr.kmers", qcfn, 4, g, err)) { fprintf(stderr, "%s\n", err.c_str()); return 1; }
+	printf("nloci %llu nk_dbi %zu nvv %zu ntr %zu nfl %zu nqc %zu\n", (unsigned long long)g.nloci, g.dbi_keys.size(), g.vv.size(),
+	       g.tr_kmers.size(), g.fl_kmers.size(), g.qc.size());
+	return 0;
+}
+
+static int cmd_pair(const char* fn, bool fq, uint64_t minlen, uint64_t refbatch, uint64_t cap) {
+	FastxReader rd(fq, minlen, refbatch);
+	if (!rd.open(fn)) { fprintf(stderr, "cannot open %s\n", fn); return 1; }
+	HostBatch hb;
+	if (!alloc_batch(hb, cap, cap * 2 * 400)) return 1;
+	uint64_t first = 0;
+	for (;;) {
+		hb.reset(first);
+		if (!rd.fill(hb)) break;
+		for (uint64_t i = 0; i < hb.npairs; ++i) {
+			fwrite(hb.names.data() + hb.name_off[i], 1, hb.name_off[i + 1] - hb.name_off[i], stdout); fputc('\t', stdout);
+			fwrite(hb.bases + hb.offsets[2 * i], 1, hb.offsets[2 * i + 1] - hb.offsets[2 * i], stdout); fputc('\t', stdout);
+			fwrite(hb.bases + hb.offsets[2 * i + 1], 1, hb.offsets[2 * i + 2] - hb.offsets[2 * i + 1], stdout);
+			if (fq) {
+				fputc('\t', stdout); fwrite(hb.quals.data() + hb.qual_off[2 * i], 1, hb.qual_off[2 * i + 1] - hb.qual_off[2 * i], stdout);
+				fputc('\t', stdout); fwrite(hb.quals.data() + hb.qual_off[2 * i + 1], 1, hb.qual_off[2 * i + 2] - hb.qual_off[2 * i + 1], stdout);
+			}
+			fputc('\n', stdout);
+		}
+		first += hb.npairs;
+	}
+	fprintf(stderr, "reads %llu unpaired %llu\n", (unsigned long long)rd.total_reads(), (unsigned long long)rd.unpaired());
+	return 0;
+}
+
+static int cmd_kam(const char* recfn, uint32_t stride, uint32_t as_stride, const char* fx, bool fq, uint64_t minlen) {
+	std::vector<char> recs; std::string err;
+	if (!read_whole_file(recfn, recs, err)) { fprintf(stderr, "%s\n", err.c_str()); return 1; }
+	FastxReader rd(fq, minlen, 300000);
+	if (!rd.open(fx)) { fprintf(stderr, "cannot open %s\n", fx); return 1; }
+	HostBatch hb;
+	if (!alloc_batch(hb, 1 << 16, (uint64_t)(1 << 16) * 2 * 400)) return 1;
+	uint64_t first = 0; size_t ri = 0; const size_t nrec = recs.size() / stride;
+	std::string out;
+	for (;;) {
+		hb.reset(first);
+		if (!rd.fill(hb)) break;
+		out.clear();
+		while (ri < nrec) {
+			const dbt_pair_record* h = reinterpret_cast<const dbt_pair_record*>(recs.data() + ri * stride);
+			if (h->pair_index >= first + hb.npairs) break;
+			append_kam_line(out, reinterpret_cast<const uint8_t*>(h), as_stride, hb, fq);
+			++ri;
+		}
+		fwrite(out.data(), 1, out.size(), stdout);
+		first += hb.npairs;
+	}
+	return ri == nrec ? 0 : 3;
+}
+
+static int cmd_args(int argc, char** argv) {
+	Options o;
+	std::string err = parse_args(argc, argv, o);
+	if (!err.empty()) { printf("error: %s\n", err.c_str()); return 1; }
+	printf("k=%llu kf=%llu,%llu cth=%llu c=%llu p=%llu r=%g threading=%d thread_cth=%llu maxnc=%llu tc=%d aln=%d alnmin=%d okam=%d qc=%d fq=%d named=%d tr=%s fx=%s out=%s qcfn=%s gpus=%d\n",
+	       (unsigned long long)o.ksize, (unsigned long long)o.N_FILTER, (unsigned long long)o.NM_FILTER, (unsigned long long)o.Cthreshold,
+	       (unsigned long long)o.NM_TR, (unsigned long long)o.nproc, o.readsPerBatchFactor, o.threading, (unsigned long long)o.thread_cth,
+	       (unsigned long long)o.maxncorrection, o.tc, o.aln, o.aln_minimal, o.okam, o.qc, o.isFastq, o.writeKmerName, o.trFname.c_str(),
+	       o.fastxFname.c_str(), o.outPrefix.c_str(), o.qcFn.c_str(), o.gpus);
+	report_parameters(o, stderr);
+	return 0;
+}
+
+int main(int argc, char** argv) {
+	if (argc < 2) { fprintf(stderr, "usage: dbt-hostcheck tr-order|index|pair|kam|args ...\n"); return 2; }
+	const std::string cmd = argv[1];
+	if (cmd == "tr-order" && argc == 4) return cmd_tr_order(argv[2], argv[3]);
+	if (cmd == "index" && argc >= 3) return cmd_index(argv[2], argc > 3 ? argv[3] : "");
+	if (cmd == "pair" && argc == 7) return cmd_pair(argv[2], atoi(argv[3]) != 0, strtoull(argv[4], nullptr, 10), strtoull(argv[5], nullptr, 10), strtoull(argv[6], nullptr, 10));
+	if (cmd == "kam" && argc == 8) return cmd_kam(argv[2], (uint32_t)atoi(argv[3]), (uint32_t)atoi(argv[4]), argv[5], atoi(argv[6]) != 0, strtoull(argv[7], nullptr, 10));
+	if (cmd == "args") return cmd_args(argc - 1, argv + 1);
+	fprintf(stderr, "bad arguments\n");
+	return 2;
+}

@@ -1,0 +1,69 @@
+// kam ("k-mer assignment") lines on stdout: writeKmerAssignments, src/aQueryFasta_thread.cpp:1646-1681,
+// with the run-length annotation of km_asgn_t::annot2str_ (cpp:121-138).  One line per dbt_pair_record
+// returned by dbt_wait, in pair order (= the order in which the reference pushes kams, cpp:2169-2175).
+// Columns: src dst dst0 span2 span1 header fields2 fields1 rle(as2) rle(as1) title seq2 qual2|. seq1 qual1|.
+// where "1"/"2" are the reference's internal slots: read 1 = the mate that arrived second (cpp:1972-1974).
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include "../../include/danbing_b200.h"
+#include "fastx_reader.hpp"
+
+namespace dbt_host {
+
+inline void append_int(std::string& o, long long v) {
+	char tmp[24]; int n = snprintf(tmp, sizeof tmp, "%lld", v); o.append(tmp, (size_t)n);
+}
+inline void append_na(std::string& o, int v) { if (v == -1) o.push_back('.'); else append_int(o, v); }
+
+inline void append_rle(std::string& o, const uint8_t* as2bit, uint32_t nk) {
+	static const char chs[3] = {'*', '.', '='};
+	if (!nk) { o.push_back('*'); return; }            // `string as1{'*'}` stays when the annotation is empty (cpp:1652)
+	auto st = [&](uint32_t i) { return (as2bit[i >> 2] >> (2 * (i & 3))) & 3u; };
+	uint32_t ct = 1, a0 = st(0);
+	for (uint32_t i = 1; i < nk; ++i) {
+		const uint32_t a1 = st(i);
+		if (a1 != a0) { append_int(o, ct); o.push_back(chs[a0]); ct = 1; } else ++ct;
+		a0 = a1;
+	}
+	append_int(o, ct); o.push_back(chs[a0]);
+}
+
+inline void append_fields(std::string& o, const dbt_mate_record& r) {
+	auto flag = [&](int bit) { o.push_back((r.flags & bit) ? '1' : '0'); o.push_back(':'); };
+	flag(DBT_MF_KF); flag(DBT_MF_HF); flag(DBT_MF_BF); flag(DBT_MF_QF); flag(DBT_MF_AF); flag(DBT_MF_RM);
+	o.append("0:0:");                                  // qn, qm: qfilter is disabled at HEAD (cpp:2129-2135)
+	append_na(o, r.si); o.push_back(':'); append_na(o, r.nt); o.push_back(':'); append_na(o, r.bs); o.push_back(':'); append_na(o, r.ti);
+}
+
+// rec: one record of dbt_record_stride bytes; hb: the batch it came from
+inline void append_kam_line(std::string& o, const uint8_t* rec, uint32_t as_stride, const HostBatch& hb, bool isFastq) {
+	const dbt_pair_record* h = reinterpret_cast<const dbt_pair_record*>(rec);
+	const dbt_mate_record& r1 = h->mate[0];
+	const dbt_mate_record& r2 = h->mate[1];
+	const uint64_t i = h->pair_index - hb.first_pair_index;
+	o.append(".\t");                                   // src: unknown without -s (cpp:1653)
+	append_int(o, h->dst); o.push_back('\t');
+	append_int(o, (h->dst0 != h->dst) ? (long long)(int)h->dst0 : -1); o.push_back('\t');   // km_asgn_t::assign (cpp:115-119), int fields
+	append_int(o, (int)r2.ei - (int)r2.si); o.push_back('\t');
+	append_int(o, (int)r1.ei - (int)r1.si); o.push_back('\t');
+	o.append("kf:hf:bf:qf:af:rm:qn:qm:si:nt:bs:ti\t");
+	append_fields(o, r2); o.push_back('\t');
+	append_fields(o, r1); o.push_back('\t');
+	append_rle(o, rec + sizeof(dbt_pair_record) + as_stride, r2.nk); o.push_back('\t');
+	append_rle(o, rec + sizeof(dbt_pair_record), r1.nk); o.push_back('\t');
+	const uint64_t n0 = hb.name_off[i], n1 = hb.name_off[i + 1];
+	if (n1 > n0 + 1) o.append(hb.names.data() + n0 + 1, n1 - n0 - 1);                      // titles[..].substr(1)
+	o.push_back('\t');
+	const uint64_t* off = hb.offsets + 2 * i;
+	o.append(reinterpret_cast<const char*>(hb.bases) + off[1], off[2] - off[1]); o.push_back('\t');     // read 2
+	if (isFastq) o.append(hb.quals.data() + hb.qual_off[2 * i + 1], hb.qual_off[2 * i + 2] - hb.qual_off[2 * i + 1]); else o.push_back('.');
+	o.push_back('\t');
+	o.append(reinterpret_cast<const char*>(hb.bases) + off[0], off[1] - off[0]); o.push_back('\t');     // read 1
+	if (isFastq) o.append(hb.quals.data() + hb.qual_off[2 * i], hb.qual_off[2 * i + 1] - hb.qual_off[2 * i]); else o.push_back('.');
+	o.push_back('\n');
+}
+
+}  // namespace dbt_host

@@ -1,0 +1,336 @@
+// danbing-tk (B200): drop-in for the reference's `danbing-tk` align CLI (src/aQueryFasta_thread.cpp:2286-2660).
+//
+// Same flags, same input files (PREF.tr.kmers / .kmers.dbi / .fl.kdb, -qc FILE, FASTA/FASTQ incl. /dev/stdin),
+// same outputs (OUT.trkmc.ar + OUT.tr.summary.txt, or OUT.tr.kmers with -on; kam lines on stdout; counters on
+// stderr).  What CountWords did per pair on pthreads (cpp:2002-2249) runs on the GPU(s) behind the C ABI of
+// include/danbing_b200.h; this file is the L3 driver around it:
+//
+//   reader thread      FASTA/FASTQ -> paired, pinned HostBatch (fastx_reader.hpp)          [cpp:1885-1986]
+//   one worker per GPU dbt_submit / dbt_wait on two slots, batch b -> GPU b mod G            [cpp:2002-2249]
+//                      + formatting of the returned records into kam lines                   [cpp:1646-1681]
+//   writer (main)      stdout in batch order, per-batch stderr line                          [cpp:2253-2279]
+//   end of run         NCCL sum of counts/kmc/nmapread/counters over the GPUs, outputs       [cpp:2617-2656]
+//
+// There is no CPU fallback: without a CUDA device the program fails.
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <deque>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/danbing_b200.h"
+#include "options.hpp"
+#include "rpgg_files.hpp"
+#include "fastx_reader.hpp"
+#include "kam_writer.hpp"
+
+using namespace dbt_host;
+
+namespace {
+
+template <typename T>
+class Channel {
+public:
+	void push(T v) { { std::lock_guard<std::mutex> l(m_); q_.push_back(std::move(v)); } cv_.notify_all(); }
+	bool pop(T& v) {
+		std::unique_lock<std::mutex> l(m_);
+		cv_.wait(l, [&] { return !q_.empty() || closed_; });
+		if (q_.empty()) return false;
+		v = std::move(q_.front()); q_.pop_front();
+		return true;
+	}
+	void close() { { std::lock_guard<std::mutex> l(m_); closed_ = true; } cv_.notify_all(); }
+private:
+	std::mutex m_; std::condition_variable cv_; std::deque<T> q_; bool closed_ = false;
+};
+
+struct BatchOut {                       // what a worker hands to the writer
+	uint64_t index = 0;
+	std::string text;                   // kam lines
+	uint64_t counters[DBT_N_COUNTERS] = {};
+	uint64_t npairs = 0, nreads_total = 0, unpaired = 0;
+	double seconds = 0;
+};
+
+struct Shared {
+	Options opt;
+	Rpgg rpgg;
+	dbt_index index{};
+	uint64_t batch_pairs = 0, bases_cap = 0;
+	std::atomic<bool> failed{false};
+	std::mutex err_mutex; std::string err;
+	void fail(const std::string& m) { std::lock_guard<std::mutex> l(err_mutex); if (!failed.exchange(true)) err = m; }
+};
+
+struct Worker {
+	int gpu = 0;
+	dbt_ctx* ctx = nullptr;
+	uint32_t ctx_len = 0;
+	Channel<HostBatch*> in;
+	std::vector<uint64_t> acc_tr, acc_kmc; std::vector<uint32_t> acc_nmap;      // counts of contexts retired by a rebuild
+	uint64_t acc_cnt[DBT_N_COUNTERS] = {};
+	std::thread th;
+};
+
+std::string dbt_err(const char* what, int rc) { return std::string(what) + ": " + dbt_strerror(rc) + ": " + dbt_last_error(); }
+
+bool make_ctx(Shared& S, Worker& w, uint32_t max_len) {
+	dbt_params p;
+	dbt_default_params(&p);
+	const Options& o = S.opt;
+	p.device = w.gpu; p.k = (uint32_t)o.ksize; p.n_filter = (uint32_t)o.N_FILTER; p.nm_filter = (uint32_t)o.NM_FILTER;
+	p.cth = (uint32_t)o.Cthreshold; p.nm_tr = (uint32_t)o.NM_TR; p.thread_cth = (uint32_t)o.thread_cth; p.max_ncorrection = (uint32_t)o.maxncorrection;
+	p.flags = (o.okam ? DBT_F_KAM : 0) | (o.qc ? DBT_F_QC : 0) | (o.threading ? DBT_F_THREADING : 0) | (o.threading && o.correction ? DBT_F_CORRECTION : 0) |
+	          (o.aln ? DBT_F_ALN : 0) | (o.aln_minimal ? DBT_F_ALN_MIN : 0);
+	p.max_read_len = max_len; p.max_batch_pairs = (uint32_t)S.batch_pairs; p.max_records = (uint32_t)S.batch_pairs;
+	p.table_load = o.table_load; p.bucket_slots = o.bucket_slots;
+	int rc = dbt_create(&w.ctx, &p);
+	if (rc) { S.fail(dbt_err("dbt_create", rc)); return false; }
+	rc = dbt_load_index(w.ctx, &S.index);
+	if (rc) { S.fail(dbt_err("dbt_load_index", rc)); return false; }
+	w.ctx_len = max_len;
+	return true;
+}
+
+// download the counts of the current context into the worker's host accumulators
+bool retire_ctx(Shared& S, Worker& w) {
+	if (!w.ctx) return true;
+	const uint64_t nk = dbt_nk_tr(w.ctx), nl = dbt_nloci(w.ctx);
+	std::vector<uint64_t> tr(std::max<uint64_t>(nk, 1)), kmc(std::max<uint64_t>(nl, 1)); std::vector<uint32_t> nm(std::max<uint64_t>(nl, 1));
+	uint64_t cnt[DBT_N_COUNTERS];
+	int rc = dbt_download(w.ctx, tr.data(), kmc.data(), nm.data(), cnt);
+	if (rc) { S.fail(dbt_err("dbt_download", rc)); return false; }
+	if (w.acc_tr.empty()) { w.acc_tr.assign(tr.size(), 0); w.acc_kmc.assign(kmc.size(), 0); w.acc_nmap.assign(nm.size(), 0); }
+	for (size_t i = 0; i < tr.size(); ++i) w.acc_tr[i] += tr[i];
+	for (size_t i = 0; i < kmc.size(); ++i) { w.acc_kmc[i] += kmc[i]; w.acc_nmap[i] += nm[i]; }
+	for (int i = 0; i < DBT_N_COUNTERS; ++i) w.acc_cnt[i] += cnt[i];
+	dbt_destroy(w.ctx); w.ctx = nullptr;
+	return true;
+}
+
+void worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<HostBatch*>& recycle) {
+	struct Inflight { HostBatch* hb = nullptr; dbt_batch_result res{}; std::vector<uint8_t> recs; std::chrono::steady_clock::time_point t0; };
+	Inflight fl[DBT_N_SLOTS];
+	auto finish = [&](int s) -> bool {
+		Inflight& f = fl[s];
+		if (!f.hb) return true;
+		int rc = dbt_wait(w.ctx, s);
+		if (rc) { S.fail(dbt_err("dbt_wait", rc)); return false; }
+		BatchOut bo;
+		bo.index = f.hb->first_pair_index;                    // batches are ordered by their first pair
+		bo.npairs = f.hb->npairs; bo.nreads_total = f.hb->nreads_total_after; bo.unpaired = f.hb->unpaired_after;
+		memcpy(bo.counters, f.res.counters, sizeof bo.counters);
+		if (S.opt.okam && f.res.n_records) {
+			const uint32_t stride = dbt_record_stride(w.ctx), as_stride = dbt_record_as_stride(w.ctx);
+			bo.text.reserve((size_t)f.res.n_records * 520);
+			for (uint64_t i = 0; i < f.res.n_records; ++i) append_kam_line(bo.text, f.recs.data() + i * stride, as_stride, *f.hb, S.opt.isFastq);
+		}
+		bo.seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - f.t0).count();
+		recycle.push(f.hb);
+		f.hb = nullptr;
+		out.push(std::move(bo));
+		return true;
+	};
+	HostBatch* hb = nullptr;
+	int k = 0;
+	while (!S.failed && w.in.pop(hb)) {
+		if (hb->max_len > w.ctx_len || !w.ctx) {              // first batch, or a read longer than the context was built for
+			for (int s = 0; s < DBT_N_SLOTS; ++s) if (!finish((k + s) & 1)) break;      // older slot first
+			if (S.failed || !retire_ctx(S, w)) break;
+			uint32_t L = std::max<uint32_t>({hb->max_len, S.opt.max_read_len, (uint32_t)S.opt.ksize, 150u});
+			if (w.ctx_len) L = std::max<uint32_t>(L, w.ctx_len + w.ctx_len / 4);
+			if (!make_ctx(S, w, L)) break;
+		}
+		const int s = k++ & 1;
+		if (!finish(s)) break;
+		Inflight& f = fl[s];
+		f.hb = hb; f.t0 = std::chrono::steady_clock::now();
+		const uint32_t stride = dbt_record_stride(w.ctx);
+		if (S.opt.okam) f.recs.resize((size_t)S.batch_pairs * stride);
+		f.res = dbt_batch_result{};
+		f.res.capacity = S.opt.okam ? S.batch_pairs : 0; f.res.records = S.opt.okam ? f.recs.data() : nullptr;
+		dbt_batch b{};
+		b.first_pair_index = hb->first_pair_index; b.npairs = hb->npairs; b.layout = DBT_LAYOUT_ASCII; b.bases = hb->bases; b.offsets = hb->offsets;
+		int rc = dbt_submit(w.ctx, &b, &f.res, s);
+		if (rc) { S.fail(dbt_err("dbt_submit", rc)); break; }
+	}
+	if (!S.failed) for (int s = 0; s < DBT_N_SLOTS; ++s) { const int ss = (k + s) & 1; if (!finish(ss)) break; }
+	if (S.failed) recycle.close();                           // unblock the reader
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+	if (argc < 2) { fputs(usage_text(), stderr); return 0; }
+	Shared S;
+	Options& o = S.opt;
+	std::string err = parse_args(argc, argv, o);
+	if (!err.empty()) { fprintf(stderr, "%s\n", err.c_str()); return 1; }
+	if (o.trPrefix.empty() || o.fastxFname.empty() || o.outPrefix.empty()) { fprintf(stderr, "-qs, -fa|-fq and -o|-on are required\n"); return 1; }
+	for (const char* unsupported : {o.bait ? "-b" : "", o.outputBubbles ? "-bu" : "", o.trackBait ? "-tb" : "", o.extractFastX ? "-e" : "",
+	                                o.simmode ? "-s" : "", o.g2pan ? "-m" : "", o.aug ? "-au" : "", o.trim ? "-t" : "", o.invkmer ? "-ik" : ""})
+		if (*unsupported) { fprintf(stderr, "option %s is not part of the B200 align path (SURVEY.md 8(f)); use the reference binary for it\n", unsupported); return 1; }
+	if (o.ksize < 1 || o.ksize > 27) { fprintf(stderr, "-k %llu unsupported (1..27)\n", (unsigned long long)o.ksize); return 1; }
+	report_parameters(o, stderr);
+	fprintf(stderr, "total number of loci in %s: ", o.trFname.c_str());
+
+	const int ndev = dbt_device_count();
+	if (ndev <= 0) { fprintf(stderr, "\nno CUDA device: %s (this build has no CPU path)\n", dbt_last_error()); return 1; }
+	const int G = std::max(1, o.gpus);
+	if (G > ndev) { fprintf(stderr, "\n--gpus %d but only %d CUDA device(s)\n", G, ndev); return 1; }
+
+	// ---- load the RPGG (cpp:2459-2504) ----
+	auto t_load = std::chrono::steady_clock::now();
+	const int hw = (int)std::max(1u, std::thread::hardware_concurrency());
+	if (!load_rpgg(o.trPrefix, o.trFname, o.qc ? o.qcFn : std::string(), std::max<int>((int)o.nproc, std::min(hw, 16)), S.rpgg, err)) { fprintf(stderr, "\n%s\n", err.c_str()); return 1; }
+	const Rpgg& g = S.rpgg;
+	fprintf(stderr, "%llu\n", (unsigned long long)g.nloci);
+	if (!g.nloci) { fprintf(stderr, "no loci in %s\n", o.trFname.c_str()); return 1; }
+	S.index.nloci = g.nloci; S.index.nk_dbi = g.dbi_keys.size(); S.index.dbi_keys = g.dbi_keys.data(); S.index.dbi_vals = g.dbi_vals.data();
+	S.index.nvv = g.vv.size(); S.index.vv = g.vv.empty() ? nullptr : g.vv.data();
+	S.index.tr_n = g.tr_n.data(); S.index.tr_kmers = g.tr_kmers.data(); S.index.fl_n = g.fl_n.data(); S.index.fl_kmers = g.fl_kmers.data();
+	S.index.qc = o.qc ? g.qc.data() : nullptr;
+	fprintf(stderr, "0 bait loci in baitDB\ndeserialized graph/index and read tr.kmers in %lld sec.\n# unique kmers in kmerDBi: %llu\n",
+	        (long long)std::chrono::duration_cast<std::chrono::seconds>(std::chrono::steady_clock::now() - t_load).count(), (unsigned long long)g.dbi_keys.size());
+
+	// ---- batches ----
+	const uint64_t readsPerRefBatch = (uint64_t)(300000 * o.readsPerBatchFactor);          // cpp:1835
+	S.batch_pairs = o.batch_pairs ? o.batch_pairs : (1ull << 20);
+	S.batch_pairs = std::max<uint64_t>(S.batch_pairs, readsPerRefBatch / 2 + 1);
+	if (S.batch_pairs >= (1ull << 31)) { fprintf(stderr, "--batch-pairs too large\n"); return 1; }
+	S.bases_cap = S.batch_pairs * 2 * 160;
+	const int NB = 2 * G + 2;
+	std::vector<std::unique_ptr<HostBatch>> pool;
+	Channel<HostBatch*> recycle;
+	for (int i = 0; i < NB; ++i) {
+		std::unique_ptr<HostBatch> hb(new HostBatch());
+		hb->bases = (uint8_t*)dbt_host_alloc(S.bases_cap); hb->bases_cap = S.bases_cap;
+		hb->offsets = (uint64_t*)dbt_host_alloc((2 * S.batch_pairs + 1) * 8); hb->pairs_cap = S.batch_pairs;
+		if (!hb->bases || !hb->offsets) { fprintf(stderr, "cannot allocate pinned batch buffers\n"); return 1; }
+		recycle.push(hb.get());
+		pool.push_back(std::move(hb));
+	}
+
+	fprintf(stderr, "creating data for each process...\n");
+	auto t_query = std::chrono::steady_clock::now();
+	std::vector<std::unique_ptr<Worker>> workers;
+	Channel<BatchOut> outq;
+	for (int i = 0; i < G; ++i) { workers.emplace_back(new Worker()); workers.back()->gpu = i; }
+	for (auto& w : workers) w->th = std::thread([&S, &outq, &recycle, wp = w.get()] { worker_main(S, *wp, outq, recycle); });
+
+	// ---- reader thread (the serial section of CountWords, cpp:1885-1986) ----
+	std::atomic<uint64_t> nbatches{0};
+	std::thread reader([&] {
+		FastxReader rd(o.isFastq, o.Cthreshold + o.ksize - 1, readsPerRefBatch);
+		if (!rd.open(o.fastxFname)) { S.fail("cannot open " + o.fastxFname); }
+		uint64_t first = 0, b = 0;
+		HostBatch* hb = nullptr;
+		while (!S.failed && recycle.pop(hb)) {
+			hb->reset(first);
+			if (!rd.fill(*hb)) { recycle.push(hb); break; }
+			if (hb->npairs == 0) {
+				if (hb->bases_cap < 2 * 1000000) { S.fail("a read pair does not fit the batch buffer"); recycle.push(hb); break; }
+				recycle.push(hb);
+				continue;
+			}
+			first += hb->npairs;
+			workers[b % G]->in.push(hb);
+			++b;
+			nbatches = b;
+		}
+		for (auto& w : workers) w->in.close();
+	});
+
+	// ---- writer: kam lines in batch order (cpp:2253-2279) ----
+	std::thread closer([&] { reader.join(); for (auto& w : workers) w->th.join(); outq.close(); });
+	std::map<uint64_t, BatchOut> held;
+	uint64_t next_first = 0;
+	std::vector<char> obuf(1 << 22);
+	setvbuf(stdout, obuf.data(), _IOFBF, obuf.size());
+	uint64_t tot[DBT_N_COUNTERS] = {};
+	BatchOut bo;
+	auto emit = [&](BatchOut& x) {
+		if (!x.text.empty()) fwrite(x.text.data(), 1, x.text.size(), stdout);
+		const uint64_t* c = x.counters;
+		const double nr = (double)(2 * x.npairs);
+		fprintf(stderr, "Buffered reading %llu\t%llu\t%llu\n", (unsigned long long)(2 * x.npairs), (unsigned long long)x.nreads_total, (unsigned long long)x.unpaired);
+		fprintf(stderr, "Batch query in %lld sec. %llu/%g/%g/%llu/%llu/%llu/%llu/%llu/%llu/%llu/%llu\n", (long long)x.seconds,
+		        (unsigned long long)c[DBT_C_NSHORT], (float)c[DBT_C_NHASH0] / nr, (float)c[DBT_C_NHASH1] / (nr - (double)c[DBT_C_NSUBFILTERED]),
+		        (unsigned long long)c[DBT_C_NSUBFILTERED], (unsigned long long)c[DBT_C_NKMERFILTERED], (unsigned long long)c[DBT_C_NLOCUSASSIGNFILTERED],
+		        (unsigned long long)c[DBT_C_NQCFILTERED], (unsigned long long)c[DBT_C_NTHREADINGREADS], (unsigned long long)c[DBT_C_NFEASIBLEREADS],
+		        (unsigned long long)c[DBT_C_NBAITFILTERED], (unsigned long long)c[DBT_C_NASGNREADS]);
+		for (int i = 0; i < DBT_N_COUNTERS; ++i) tot[i] += c[i];
+		next_first = x.index + x.npairs;
+	};
+	while (outq.pop(bo)) {
+		if (bo.index != next_first) { held.emplace(bo.index, std::move(bo)); continue; }
+		emit(bo);
+		for (auto it = held.find(next_first); it != held.end(); it = held.find(next_first)) { emit(it->second); held.erase(it); }
+	}
+	closer.join();
+	fflush(stdout);
+	if (S.failed) { fprintf(stderr, "danbing-tk: %s\n", S.err.c_str()); return 1; }
+
+	// ---- reduce over GPUs and collect ----
+	std::vector<uint64_t> counts(g.tr_kmers.size(), 0), kmc(g.nloci, 0); std::vector<uint32_t> nmap(g.nloci, 0);
+	{
+		std::vector<Worker*> live;
+		for (auto& w : workers) if (w->ctx) live.push_back(w.get());
+		if (live.size() > 1) {
+			uint8_t id[DBT_NCCL_ID_BYTES];
+			int rc = dbt_nccl_unique_id(id);
+			if (rc) { fprintf(stderr, "danbing-tk: %s\n", dbt_err("dbt_nccl_unique_id", rc).c_str()); return 1; }
+			std::vector<std::thread> th; std::atomic<int> bad{0};
+			for (size_t r = 0; r < live.size(); ++r) th.emplace_back([&, r] {
+				int rc2 = dbt_comm_init(live[r]->ctx, (int)live.size(), (int)r, id);
+				if (!rc2) rc2 = dbt_allreduce(live[r]->ctx);
+				if (rc2) { bad = rc2; S.fail(dbt_err("NCCL reduce", rc2)); }
+			});
+			for (auto& t : th) t.join();
+			if (bad) { fprintf(stderr, "danbing-tk: %s\n", S.err.c_str()); return 1; }
+		}
+		if (!live.empty()) {
+			std::vector<uint64_t> tr(std::max<size_t>(counts.size(), 1)), km(std::max<size_t>(kmc.size(), 1)); std::vector<uint32_t> nm(std::max<size_t>(nmap.size(), 1));
+			int rc = dbt_download(live[0]->ctx, tr.data(), km.data(), nm.data(), nullptr);
+			if (rc) { fprintf(stderr, "danbing-tk: %s\n", dbt_err("dbt_download", rc).c_str()); return 1; }
+			for (size_t i = 0; i < counts.size(); ++i) counts[i] += tr[i];
+			for (size_t i = 0; i < kmc.size(); ++i) { kmc[i] += km[i]; nmap[i] += nm[i]; }
+		}
+		for (auto& w : workers) {
+			for (size_t i = 0; i < w->acc_tr.size() && i < counts.size(); ++i) counts[i] += w->acc_tr[i];
+			for (size_t i = 0; i < w->acc_kmc.size() && i < kmc.size(); ++i) { kmc[i] += w->acc_kmc[i]; nmap[i] += w->acc_nmap[i]; }
+			if (w->ctx) { dbt_destroy(w->ctx); w->ctx = nullptr; }
+		}
+	}
+	for (auto& hb : pool) { dbt_host_free(hb->bases); dbt_host_free(hb->offsets); }
+
+	// ---- final counters (cpp:2617-2627) and outputs (cpp:2631-2656) ----
+	fprintf(stderr, "%llu reads processed in total.\n%llu reads removed by subsampled kmer-filter.\n%llu reads removed by kmer-filter.\n"
+	                "%llu reads removed by bait locus.\n%llu reads removed by qual filter.\n%llu reads removed during locus assignment.\n"
+	                "%llu reads removed by QC filter.\n%llu reads entered threading step.\n%llu reads passsed threading.\n"
+	                "%llu reads assigned to TR region.\nparallel query completed in %lld sec.\n",
+	        (unsigned long long)tot[DBT_C_NREADS], (unsigned long long)tot[DBT_C_NSUBFILTERED], (unsigned long long)tot[DBT_C_NKMERFILTERED],
+	        (unsigned long long)tot[DBT_C_NBAITFILTERED], (unsigned long long)tot[DBT_C_NQUALFILTERED], (unsigned long long)tot[DBT_C_NLOCUSASSIGNFILTERED],
+	        (unsigned long long)tot[DBT_C_NQCFILTERED], (unsigned long long)tot[DBT_C_NTHREADINGREADS], (unsigned long long)tot[DBT_C_NFEASIBLEREADS],
+	        (unsigned long long)tot[DBT_C_NASGNREADS],
+	        (long long)std::chrono::duration_cast<std::chrono::seconds>(std::chrono::steady_clock::now() - t_query).count());
+	fprintf(stderr, "writing kmers...\n");
+	bool ok;
+	if (o.writeKmerName) ok = write_kmers_with_name(o.outPrefix + ".tr.kmers", g, counts, err);
+	else {
+		fprintf(stderr, "# kmer skipped: 0\ndone\nserializing %s.trkmc.ar\n", o.outPrefix.c_str());
+		ok = write_trkmc_ar(o.outPrefix, counts, err) && write_tr_summary(o.outPrefix + ".tr.summary.txt", kmc, nmap, err);
+	}
+	if (!ok) { fprintf(stderr, "danbing-tk: %s\n", err.c_str()); return 1; }
+	fprintf(stderr, "all done!\n");
+	return 0;
+}

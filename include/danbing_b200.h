@@ -58,6 +58,9 @@ extern "C" {
 #define DBT_ST_QCFILTERED  4   /* locus fails QC                              (cpp:2059)       */
 #define DBT_ST_ASGN_REMOVED 5  /* both mates removed by assignTRkmc           (cpp:2145)       */
 #define DBT_ST_COUNTED     6   /* counts accumulated, kam line written        (cpp:2146-2175)  */
+#define DBT_ST_NOT_THREADED 7  /* DBT_F_THREADING at the reference's HEAD: the pair enters the threading step (cpp:2070)
+                                  and nothing passes it -- the only caller of isThreadFeasible is commented
+                                  out (cpp:2072-2088), so `alned` stays false and cpp:2090 skips counting and output */
 
 /* ---- counters (dbt_download / dbt_batch_result.counters); cpp:1820, 2617-2626 --------------- */
 enum {

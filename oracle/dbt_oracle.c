@@ -460,6 +460,9 @@ void dbo_run(const dbo_index* ix, const dbt_params* p, uint64_t first_pair_index
 			if (destLocus == nloci) status = DBT_ST_UNASSIGNED;
 		}
 		if (status < 0 && qc && !ix->qc[destLocus]) { counters[DBT_C_NQCFILTERED] += (uint64_t)(2 - r1.rm - r2.rm); status = DBT_ST_QCFILTERED; }
+		if (status < 0 && (p->flags & DBT_F_THREADING)) {                                           /* cpp:2070; 2072-2090: alned stays false */
+			counters[DBT_C_NTHREADINGREADS] += 2; status = DBT_ST_NOT_THREADED;
+		}
 		if (status < 0) {
 			counters[DBT_C_NTHREADINGREADS] += 2; counters[DBT_C_NFEASIBLEREADS] += 2;            /* cpp:2070, 2092 */
 			if (okam || !r1.rm || !r2.rm) {

@@ -1,0 +1,130 @@
+"""GPU tests of the drop-in CLI (danbing-tk_b200/bin/danbing-tk): byte-for-byte against the golden outputs of the
+unmodified reference binary, and -- where oracle/_ref travelled to the box -- against the reference run live."""
+import gzip
+import os
+import random
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from common import GOLDEN, golden_case, golden_outputs
+from oracle_abi import PKG_DIR, abi, ref_bin
+
+pytestmark = pytest.mark.gpu
+CLI = os.path.join(PKG_DIR, "bin", "danbing-tk")
+COUNTER_RE = re.compile(r"^(\d+) reads (.*)\.$", re.M)
+
+
+def stage_case(case_name, tmp_path):
+    d = os.path.join(GOLDEN, case_name)
+    for ext in ("tr.kmers", "kmers.dbi", "fl.kdb", "tre.kdb"):
+        with gzip.open(os.path.join(d, f"pan.{ext}.gz"), "rb") as f, open(tmp_path / f"pan.{ext}", "wb") as o:
+            o.write(f.read())
+    with gzip.open(os.path.join(d, "reads.fa.gz"), "rb") as f, open(tmp_path / "reads.fa", "wb") as o:
+        o.write(f.read())
+    return str(tmp_path / "pan"), str(tmp_path / "reads.fa")
+
+
+def run_cli(exe, args, cwd):
+    r = subprocess.run([exe, *map(str, args)], capture_output=True, cwd=cwd)
+    assert r.returncode == 0, r.stderr.decode()[-2000:]
+    return r.stdout, r.stderr.decode()
+
+
+def counters(stderr):
+    return {name: int(v) for v, name in COUNTER_RE.findall(stderr)}
+
+
+def flags_of(run):
+    return ["-k", run["k"], "-kf", run["kf"][0], run["kf"][1], "-cth", run["cth"], "-c", run["c"]]
+
+
+@pytest.mark.parametrize("case_name,run_name", [("s1", "cth45"), ("s1", "cth10"), ("multi", "cth45"), ("multi", "kf0")])
+def test_cli_matches_golden(case_name, run_name, tmp_path):
+    case = golden_case(case_name)
+    run = case["meta"]["runs"][run_name]
+    pref, fa = stage_case(case_name, tmp_path)
+    out, err = run_cli(CLI, flags_of(run) + ["-qs", pref, "-fa", fa, "-o", tmp_path / "out"], tmp_path)
+    exp = golden_outputs(case, run_name)
+    assert out.decode().splitlines() == exp["kam"]
+    assert np.array_equal(np.fromfile(tmp_path / "out.trkmc.ar", "<u8")[1:], exp["trkmc"])
+    assert open(tmp_path / "out.tr.summary.txt").read() == exp["summary"]
+    c = counters(err)
+    for name, v in run["counters"].items():
+        assert c[name[6:] if name.startswith("reads ") else name] == v, name
+
+
+def test_cli_small_batches_two_slots(tmp_path):
+    """many GPU submissions (reference batches of 600 reads, 512 pairs per submission): same bytes"""
+    case = golden_case("multi")
+    run = case["meta"]["runs"]["cth45"]
+    pref, fa = stage_case("multi", tmp_path)
+    out, err = run_cli(CLI, flags_of(run) + ["-r", 0.002, "--batch-pairs", 512, "-qs", pref, "-fa", fa, "-o", tmp_path / "out"], tmp_path)
+    exp = golden_outputs(case, "cth45")
+    assert out.decode().splitlines() == exp["kam"]
+    assert np.array_equal(np.fromfile(tmp_path / "out.trkmc.ar", "<u8")[1:], exp["trkmc"])
+    assert err.count("Batch query in") > 4
+
+
+needs_ref = pytest.mark.skipif(not ref_bin("danbing-tk"), reason="oracle/_ref/danbing-tk not present")
+
+
+def both(args, tmp_path):
+    a = run_cli(CLI, args + ["-o", tmp_path / "gpu"], tmp_path)
+    b = run_cli(ref_bin("danbing-tk"), args + ["-o", tmp_path / "ref"], tmp_path)
+    return a, b
+
+
+@needs_ref
+def test_cli_vs_reference_live_fastq_qc_and_stragglers(tmp_path):
+    """FASTQ input with shuffled mates, short mates, a trailing singleton (the reference pairs it with a stale mate,
+    cpp:1919-1948), -qc mask: stdout, .trkmc.ar, .tr.summary.txt and the final counters of both binaries"""
+    pref, fa = stage_case("multi", tmp_path)
+    rng = random.Random(5)
+    lines = open(fa).read().split("\n")[:-1]
+    recs = [(lines[i], lines[i + 1]) for i in range(0, len(lines), 2)]
+    for _ in range(len(recs) // 5):
+        i, j = rng.randrange(len(recs)), rng.randrange(len(recs))
+        recs[i], recs[j] = recs[j], recs[i]
+    recs.append((">lonely/1", recs[0][1]))
+    fq = tmp_path / "reads.fq"
+    with open(fq, "w") as f:
+        for t, s in recs:
+            f.write("@" + t[1:] + "\n" + s + "\n+\n" + "".join(chr(33 + rng.randrange(41)) for _ in s) + "\n")
+    nloci = golden_case("multi")["ix"]["nloci"]
+    with open(tmp_path / "qc.txt", "w") as f:
+        f.write("".join("0" if l % 4 == 1 else "1" for l in range(nloci)) + "\n")
+    args = ["-k", 21, "-kf", 4, 1, "-cth", 30, "-qc", tmp_path / "qc.txt", "-qs", pref, "-fq", fq]
+    (go, ge), (ro, re_) = both(args, tmp_path)
+    assert go == ro
+    assert open(tmp_path / "gpu.trkmc.ar", "rb").read() == open(tmp_path / "ref.trkmc.ar", "rb").read()
+    assert open(tmp_path / "gpu.tr.summary.txt").read() == open(tmp_path / "ref.tr.summary.txt").read()
+    assert counters(ge) == counters(re_) and counters(ge)["removed by QC filter"] > 0
+
+
+@needs_ref
+def test_cli_vs_reference_live_named_output_and_threading_flag(tmp_path):
+    """-on writes OUT.tr.kmers (k-mer names in the reference's hashtable order); -gc at HEAD counts nothing"""
+    pref, fa = stage_case("s1", tmp_path)
+    for exe, tag in ((CLI, "gpu"), (ref_bin("danbing-tk"), "ref")):
+        run_cli(exe, ["-k", 21, "-cth", 45, "-ka", "-qs", pref, "-fa", fa, "-on", tmp_path / tag], tmp_path)
+    assert open(tmp_path / "gpu.tr.kmers").read() == open(tmp_path / "ref.tr.kmers").read()
+    (go, ge), (ro, re_) = both(["-k", 21, "-gc", 85, 3, "-ae", "-kf", 4, 1, "-cth", 45, "-qs", pref, "-fa", fa], tmp_path)
+    assert go == ro == b""
+    assert open(tmp_path / "gpu.trkmc.ar", "rb").read() == open(tmp_path / "ref.trkmc.ar", "rb").read()
+    assert counters(ge) == counters(re_) and counters(ge)["passsed threading"] == 0 and counters(ge)["entered threading step"] > 0
+
+
+def test_cli_two_gpus_same_bytes(tmp_path, lib):
+    if lib.dbt_device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    case = golden_case("multi")
+    run = case["meta"]["runs"]["cth45"]
+    pref, fa = stage_case("multi", tmp_path)
+    out, err = run_cli(CLI, flags_of(run) + ["-r", 0.002, "--batch-pairs", 512, "--gpus", 2, "-qs", pref, "-fa", fa, "-o", tmp_path / "out"], tmp_path)
+    exp = golden_outputs(case, "cth45")
+    assert out.decode().splitlines() == exp["kam"]
+    assert np.array_equal(np.fromfile(tmp_path / "out.trkmc.ar", "<u8")[1:], exp["trkmc"])
+    assert open(tmp_path / "out.tr.summary.txt").read() == exp["summary"]

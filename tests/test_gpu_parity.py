@@ -150,6 +150,16 @@ def test_gpu_ka_and_qc_flags():
     assert np.array_equal(ctx.download()[0], o[2])
 
 
+@pytest.mark.parametrize("flags", [abi.F_KAM | abi.F_TRACE | abi.F_THREADING | abi.F_CORRECTION, abi.F_KAM | abi.F_THREADING])
+def test_gpu_threading_flag_head_semantics(flags):
+    """-g/-gc at the reference's HEAD: pairs enter the threading step and none passes (cpp:2070-2090)"""
+    ix, seqs, _ = synthetic_case(nloci=30, seed=8, npairs=3000, read_seed=12, frac_locus=0.5, frac_chimeric=0.2, frac_onemate=0.1)
+    p = abi.default_params(k=21, cth=30, flags=flags, max_batch_pairs=4096)
+    recs, cnt = oracle_vs_gpu(ix, seqs, p)
+    c = dict(zip(abi.COUNTER_NAMES, cnt.tolist()))
+    assert c["nThreadingReads"] > 0 and c["nFeasibleReads"] == 0 and c["nAsgnReads"] == 0 and c["ninc"] == 0
+
+
 def test_gpu_empty_and_degenerate_batches():
     ix, seqs, _ = synthetic_case(nloci=10, seed=7, npairs=50, read_seed=11)
     p = abi.default_params(k=21, cth=10, flags=abi.F_KAM | abi.F_TRACE, max_batch_pairs=64)
