@@ -355,6 +355,15 @@ def b200_arm(a, config, workdir, rank, world, local, dist):
                 "per_kernel_bytes": {n: bb for n, (ms_, bb) in kern.items()},
                 "generic_path_pairs": cnt["gen_pairs"], "candidate_pairs": ncand,
                 "step_bytes": step_bytes, "step_GBps": step_bytes / (step_ms / 1e3) / 1e9, "step_frac": step_bytes / (step_ms / 1e3) / 1e9 / peak}
+    # dram bytes per launch of the dominant kernel from the committed `ncu --set full` capture of this same workload
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        w = tj.get("workload", {})
+        if (w.get("pairs"), w.get("loci"), w.get("frac_locus")) == (P, a.loci, a.frac_locus) and dom in tj:
+            roofline["traffic"] = tj[dom]
+            roofline["traffic_source"] = "profiles/traffic.json (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum)"
+    except (OSError, ValueError):
+        pass
     if a.rrand and rank == 0:
         rr = {}
         for sect in (32, 64):
