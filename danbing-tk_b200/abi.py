@@ -16,7 +16,7 @@ DBT_N_SLOTS = 2
 DBT_NCCL_ID_BYTES = 128
 
 F_KAM, F_QC, F_TRACE, F_THREADING, F_CORRECTION, F_ALN, F_ALN_MIN = 1, 2, 4, 8, 16, 32, 64
-ST_SHORT, ST_SUBFILTERED, ST_KFILTERED, ST_UNASSIGNED, ST_QCFILTERED, ST_ASGN_REMOVED, ST_COUNTED, ST_NOT_THREADED = range(8)
+ST_SHORT, ST_SUBFILTERED, ST_KFILTERED, ST_UNASSIGNED, ST_QCFILTERED, ST_ASGN_REMOVED, ST_COUNTED, ST_NOT_THREADED, ST_THREAD_FAILED = range(9)
 LAYOUT_ASCII, LAYOUT_PACKED = 0, 1
 COUNTER_NAMES = ["nReads", "nShort", "nSubFiltered", "nKmerFiltered", "nBaitFiltered", "nQualFiltered",
                  "nLocusAssignFiltered", "nQCFiltered", "nThreadingReads", "nFeasibleReads", "nAsgnReads",
@@ -41,7 +41,7 @@ class Params(C.Structure):
 class Index(C.Structure):
     _fields_ = [("nloci", C.c_uint64), ("nk_dbi", C.c_uint64), ("dbi_keys", u64p), ("dbi_vals", u32p),
                 ("nvv", C.c_uint64), ("vv", u32p), ("tr_n", u64p), ("tr_kmers", u64p), ("fl_n", u64p),
-                ("fl_kmers", u64p), ("qc", u8p)]
+                ("fl_kmers", u64p), ("qc", u8p), ("g_n", u64p), ("g_kmers", u64p), ("g_masks", u8p)]
 
 
 class Batch(C.Structure):
@@ -64,6 +64,33 @@ assert MATE_DTYPE.itemsize == 16 and RECORD_HEADER_DTYPE.itemsize == 64
 
 def record_dtype(as_stride):
     return np.dtype([("h", RECORD_HEADER_DTYPE), ("as", "u1", (2, as_stride))])
+
+
+ALN_MATE_DTYPE = np.dtype([("alned", "u1"), ("err", "u1"), ("nes", "<u2"), ("ntr", "<u2"), ("nkm", "<u2"), ("kmers_hash", "<u8")])
+assert ALN_MATE_DTYPE.itemsize == 16
+ES_T = "*=XDI"          # dbt_aln_mate es byte: bits 0-2
+ES_G = "_ACGT*"         # bits 3-5 ('_' = none)
+TR_C = "*.="
+
+
+def aln_caps(max_read_len, k, max_ncorrection):
+    """(es_cap, tr_cap, aln_stride); must equal dbt_record_es_cap() / dbt_record_aln_stride()."""
+    grow = 2 * max_ncorrection + 8
+    es_cap = (max_read_len + grow + 7) // 8 * 8
+    tr_cap = (max(max_read_len - k + 1, 1) + grow + 7) // 8 * 8
+    return es_cap, tr_cap, 16 + es_cap + tr_cap
+
+
+def aln_record_dtype(es_cap, tr_cap):
+    m = np.dtype([("h", ALN_MATE_DTYPE), ("es", "u1", es_cap), ("tr", "u1", tr_cap)])
+    return np.dtype([("h", RECORD_HEADER_DTYPE), ("aln", m, 2)])
+
+
+def fnv1a_u64(kmers):
+    h = 0xcbf29ce484222325
+    for b in np.asarray(kmers, "<u8").tobytes():
+        h = ((h ^ b) * 0x100000001b3) & 0xFFFFFFFFFFFFFFFF
+    return h
 
 
 def as_stride_for(max_read_len, k):
@@ -90,6 +117,10 @@ def make_index_struct(ix):
     s.fl_n = ptr(ix["fl_n"], u64p)
     s.fl_kmers = ptr(ix["fl_kmers"], u64p)
     s.qc = ptr(ix.get("qc"), u8p) if ix.get("qc") is not None else None
+    if ix.get("g_n") is not None:                   # PREF.graph.kmers (restored threading)
+        s.g_n = ptr(ix["g_n"], u64p)
+        s.g_kmers = ptr(ix["g_kmers"], u64p)
+        s.g_masks = ptr(ix["g_masks"], u8p)
     s._keep = ix
     return s
 
@@ -139,7 +170,7 @@ def load_library(path=LIB_PATH):
     for f in (L.dbt_nk_tr, L.dbt_nloci, L.dbt_launch_count):
         f.argtypes = [ctxp]
         f.restype = C.c_uint64
-    for f in (L.dbt_record_stride, L.dbt_record_as_stride):
+    for f in (L.dbt_record_stride, L.dbt_record_as_stride, L.dbt_record_aln_stride, L.dbt_record_es_cap):
         f.argtypes = [ctxp]
         f.restype = C.c_uint32
     L.dbt_nccl_unique_id.argtypes = [u8p]
@@ -164,7 +195,7 @@ def load_library(path=LIB_PATH):
 ABI_SYMBOLS = ["dbt_abi_version", "dbt_device_count", "dbt_default_params", "dbt_create", "dbt_destroy",
                "dbt_strerror", "dbt_last_error", "dbt_load_index", "dbt_upload", "dbt_process", "dbt_fetch",
                "dbt_submit", "dbt_wait", "dbt_download", "dbt_reset_counts", "dbt_nk_tr", "dbt_nloci",
-               "dbt_record_stride", "dbt_record_as_stride", "dbt_nccl_unique_id", "dbt_comm_init", "dbt_allreduce",
+               "dbt_record_stride", "dbt_record_as_stride", "dbt_record_aln_stride", "dbt_record_es_cap", "dbt_nccl_unique_id", "dbt_comm_init", "dbt_allreduce",
                "dbt_timer_start", "dbt_timer_stop", "dbt_kernel_times", "dbt_launch_count", "dbt_table_stats", "dbt_batch_stats",
                "dbt_random_gather_bench", "dbt_host_alloc", "dbt_host_free", "dbt_packed_bytes", "dbt_pack_reads"]
 

@@ -367,6 +367,8 @@ extern "C" uint64_t dbt_nk_tr(const dbt_ctx* c) { return c ? c->ix.nk_tr : 0; }
 extern "C" uint64_t dbt_nloci(const dbt_ctx* c) { return c ? c->ix.nloci : 0; }
 extern "C" uint32_t dbt_record_stride(const dbt_ctx* c) { return c ? c->rp.rec_stride : 0; }
 extern "C" uint32_t dbt_record_as_stride(const dbt_ctx* c) { return c ? c->rp.as_stride : 0; }
+extern "C" uint32_t dbt_record_aln_stride(const dbt_ctx* c) { return c ? c->rp.aln_stride : 0; }
+extern "C" uint32_t dbt_record_es_cap(const dbt_ctx* c) { return c ? c->rp.es_cap : 0; }
 extern "C" uint64_t dbt_launch_count(const dbt_ctx* c) { return c ? c->launches.load() : 0; }
 
 // ------------------------------------------------------------------------------------------

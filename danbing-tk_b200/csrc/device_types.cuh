@@ -39,6 +39,10 @@ struct RunParams {
 	uint32_t as_stride, rec_stride;
 	uint32_t warp_smem;         // bytes of shared memory per warp in candidate_kernel
 	uint32_t max_records;
+	// restored graph threading (P1); all 0 unless DBT_F_THREADING and a graph is loaded
+	uint32_t thr_on;            // 1 = hand candidates to thread_kernel instead of the HEAD no-op
+	uint32_t thread_cth, max_ncorrection, correction;
+	uint32_t es_cap, tr_cap, aln_stride;   // record blob geometry (include/danbing_b200.h, dbt_aln_mate)
 };
 
 // one in-flight batch

@@ -135,6 +135,55 @@ def build_dbi(tr_n, tr_k, fl_n, fl_k):
     return keys.astype("<u8"), vals.astype("<u4"), np.array(vv, "<u4")
 
 
+def forward_kmers(codes, k):
+    """codes: u8 array of 0..3 -> strand-specific k-mers of every window (u64[len-k+1])."""
+    n = len(codes) - k + 1
+    if n <= 0:
+        return np.zeros(0, np.uint64)
+    f = np.zeros(n, np.uint64)
+    c = codes.astype(np.uint64)
+    for j in range(k):
+        f |= c[j:j + n] << np.uint64(2 * (k - 1 - j))
+    return f
+
+
+def locus_graph(haps, k):
+    """(nodes u64 sorted, masks u8) of one locus: fa2kmers -g == buildKmerGraph over the WHOLE haplotype
+    record, both strands, self-loops dropped (src/fa2kmers.cpp:158, src/aQueryFasta_thread.h:215-243).
+    Bit b of the mask: successor ((node & rmask) << 2) + b exists."""
+    ns, ms = [], []
+    for s in haps:
+        codes = _CODE[np.frombuffer(s, np.uint8)]
+        for c in (codes, (3 - codes[::-1]).astype(np.uint8)):
+            f = forward_kmers(c, k)
+            if not len(f):
+                continue
+            m = np.zeros(len(f), np.uint8)
+            nxt = c[k:].astype(np.uint8)
+            m[:-1] = np.where(f[:-1] != f[1:], np.uint8(1) << nxt, np.uint8(0))
+            ns.append(f)
+            ms.append(m)
+    if not ns:
+        return np.zeros(0, "<u8"), np.zeros(0, np.uint8)
+    ns, ms = np.concatenate(ns), np.concatenate(ms)
+    order = np.argsort(ns, kind="stable")
+    ns, ms = ns[order], ms[order]
+    nodes, start = np.unique(ns, return_index=True)
+    masks = np.bitwise_or.reduceat(ms, start)
+    return nodes.astype("<u8"), masks.astype(np.uint8)
+
+
+def build_graph(loci, k=21, pref=None):
+    """-> dict(g_n, g_kmers, g_masks); with pref also writes PREF.graph.kmers (text, `node<TAB>mask`)."""
+    gs = [locus_graph(h, k) for h in loci]
+    g_n = np.array([len(n) for n, _ in gs], "<u8")
+    g_k = np.concatenate([n for n, _ in gs]).astype("<u8") if gs else np.zeros(0, "<u8")
+    g_m = np.concatenate([m for _, m in gs]).astype(np.uint8) if gs else np.zeros(0, np.uint8)
+    if pref is not None:
+        rpgg_io.write_kmers_text(pref + ".graph.kmers", g_n, g_k, g_m)
+    return dict(g_n=g_n, g_kmers=g_k, g_masks=g_m)
+
+
 def build_rpgg(loci, pref, k=21, fsi=700, fso=700, write_text=True):
     """Writes PREF.tr.kmers, PREF.fl.kmers (text), PREF.kmers.dbi, PREF.fl.kdb, PREF.tre.kdb (valid, empty).
     Returns the host index dict (tr order = file order)."""
@@ -172,6 +221,25 @@ def mutate(s, rng, rate):
     m = rng.random(len(a)) < rate
     a[m] = _ASCII[rng.integers(0, 4, int(m.sum()))]
     return a.tobytes()
+
+
+def mutate_indel(s, rng, sub=0.0, ins=0.0, dele=0.0, rlen=None):
+    """substitutions (to a DIFFERENT base), insertions and deletions; result cut/padded back to rlen."""
+    a = np.frombuffer(s, np.uint8)
+    out = bytearray()
+    u = rng.random((len(a), 3))
+    for i, c in enumerate(a):
+        if u[i, 0] < dele:
+            continue
+        if u[i, 1] < ins:
+            out.append(int(_ASCII[rng.integers(0, 4)]))
+        if u[i, 2] < sub and c in b"ACGT":
+            c = b"ACGT"[(b"ACGT".index(c) + int(rng.integers(1, 4))) % 4]
+        out.append(int(c))
+    rlen = len(a) if rlen is None else rlen
+    while len(out) < rlen:
+        out.append(int(_ASCII[rng.integers(0, 4)]))
+    return bytes(out[:rlen])
 
 
 def random_read(rng, rlen=150):

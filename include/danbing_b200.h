@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define DBT_ABI_VERSION 2
+#define DBT_ABI_VERSION 3
 
 /* ---- error codes -------------------------------------------------------------------------- */
 #define DBT_OK            0
@@ -45,7 +45,9 @@ extern "C" {
 #define DBT_F_KAM        0x001u /* kam records wanted (reference default; `-ka` clears, cpp:2368) */
 #define DBT_F_QC         0x002u /* `-qc FILE` locus mask active (cpp:2381, 2059-2062)           */
 #define DBT_F_TRACE      0x004u /* test/diagnostic: emit a record for EVERY pair, not only kam   */
-#define DBT_F_THREADING  0x008u /* `-g/-gc/-gcc` (cpp:2360); dead at reference HEAD (cpp:2072)  */
+#define DBT_F_THREADING  0x008u /* `-g/-gc/-gcc` (cpp:2360).  With a graph in dbt_index: restored graph threading
+                                   (isThreadFeasible, cpp:1114-1260, pair glue = SURVEY.md §8(c) decision D1).
+                                   Without one: the reference's HEAD behaviour (caller commented out, cpp:2072) */
 #define DBT_F_CORRECTION 0x010u /* `-gc` error-correcting threading                            */
 #define DBT_F_ALN        0x020u /* `-a`                                                        */
 #define DBT_F_ALN_MIN    0x040u /* `-ae`                                                       */
@@ -58,6 +60,8 @@ extern "C" {
 #define DBT_ST_QCFILTERED  4   /* locus fails QC                              (cpp:2059)       */
 #define DBT_ST_ASGN_REMOVED 5  /* both mates removed by assignTRkmc           (cpp:2145)       */
 #define DBT_ST_COUNTED     6   /* counts accumulated, kam line written        (cpp:2146-2175)  */
+#define DBT_ST_THREAD_FAILED 8 /* restored threading: neither mate threads through graphDB[destLocus]
+                                  (commented cpp:2087 "removed by threading"); COUNTED = at least one does    */
 #define DBT_ST_NOT_THREADED 7  /* DBT_F_THREADING at the reference's HEAD: the pair enters the threading step (cpp:2070)
                                   and nothing passes it -- the only caller of isThreadFeasible is commented
                                   out (cpp:2072-2088), so `alned` stays false and cpp:2090 skips counting and output */
@@ -119,6 +123,9 @@ typedef struct {
  *                          reproduces it) -- counts[] comes back in exactly this order
  *   fl_n/fl_kmers        : PREF.fl.kdb     (readBinaryKmerSetDB, h:675-698)
  *   qc                   : -qc FILE after `- '0'` (readQCFile, kio:111-120); NULL unless DBT_F_QC
+ *   g_n/g_kmers/g_masks  : PREF.graph.kmers (readGraphKmers, h:549-575; GraphType h:32): per-locus node
+ *                          counts, strand-specific k-mers, 4-bit out-edge masks (bit b: successor
+ *                          ((node & rmask) << 2) + b exists, cpp:533-539).  NULL = no graph.
  * The caller may free everything once dbt_load_index returns.
  */
 typedef struct {
@@ -128,6 +135,7 @@ typedef struct {
   const uint64_t* tr_n;   const uint64_t* tr_kmers;
   const uint64_t* fl_n;   const uint64_t* fl_kmers;
   const uint8_t*  qc;
+  const uint64_t* g_n;    const uint64_t* g_kmers;  const uint8_t* g_masks;
 } dbt_index;
 
 #define DBT_LAYOUT_ASCII   0   /* concatenated ASCII read sequences + byte offsets               */
@@ -180,6 +188,24 @@ typedef struct {
   dbt_mate_record mate[2];
 } dbt_pair_record;
 
+/*
+ * Restored threading (DBT_F_THREADING with a graph): a record is the same 64-byte header (mate[].flags
+ * carry kf/hf/rm; the asgn fields stay at their defaults) followed, per mate, by one alignment blob of
+ * dbt_record_aln_stride(ctx) bytes == sam_t.r1 / sam_t.r2 (cpp:53-75):
+ *   dbt_aln_mate header, then es[nes] (CIGAR entries, one byte each: bits 0-2 type 0 '*' 1 '=' 2 'X'
+ *   3 'D' 4 'I' (edit_t.t, cpp:46-51), bits 3-5 graph base 0 none 1 'A' 2 'C' 3 'G' 4 'T' 5 '*' (edit_t.g)),
+ *   starting at byte sizeof(dbt_aln_mate); then tr[ntr] (k-mer annotation, 0 '*' 1 '.' 2 '=', cpp:60)
+ *   starting at byte sizeof(dbt_aln_mate) + dbt_record_es_cap(ctx).
+ * Records are emitted for the pairs the reference prints an .aln line for (cpp:2232-2239): with
+ * DBT_F_ALN every pair that entered threading, with DBT_F_ALN_MIN only threaded ones; DBT_F_TRACE: all.
+ */
+typedef struct {
+  uint8_t  alned;              /* isThreadFeasible's return: 0 infeasible, 1 threaded, 2 threaded with edits */
+  uint8_t  err;                /* 1 = the graph is not closed / capacity exceeded (reference: assert or UB) */
+  uint16_t nes, ntr, nkm;      /* lengths of es, tr and of the edited k-mer vector                        */
+  uint64_t kmers_hash;         /* FNV-1a over the edited k-mer vector (u64 little-endian), for parity tests */
+} dbt_aln_mate;
+
 typedef struct {
   uint64_t n_records;          /* out */
   uint64_t capacity;           /* in: records the buffer can hold                               */
@@ -215,6 +241,8 @@ uint64_t dbt_nk_tr(const dbt_ctx*);
 uint64_t dbt_nloci(const dbt_ctx*);
 uint32_t dbt_record_stride(const dbt_ctx*);
 uint32_t dbt_record_as_stride(const dbt_ctx*);
+uint32_t dbt_record_aln_stride(const dbt_ctx*);   /* 0 unless restored threading is active            */
+uint32_t dbt_record_es_cap(const dbt_ctx*);
 
 /* ---- multi-GPU: one context per GPU, reads sharded, one sum-reduce at the end --------------- */
 #define DBT_NCCL_ID_BYTES 128

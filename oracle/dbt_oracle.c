@@ -3,48 +3,8 @@
  * Every function cites the reference lines it follows ("cpp" = src/aQueryFasta_thread.cpp,
  * "h" = src/aQueryFasta_thread.h under /root/reference).  Written for clarity, not speed.
  */
-#include "dbt_oracle.h"
-#include <stdlib.h>
-#include <string.h>
+#include "dbt_oracle_int.h"
 
-#define NAN32 0xFFFFFFFFu
-#define NAN64 0xFFFFFFFFFFFFFFFFull
-
-/* ------------------------------------------------------------------------------------------ */
-/* tiny open-addressing maps (stand-ins for the reference's unordered_map / unordered_set)     */
-/* ------------------------------------------------------------------------------------------ */
-typedef struct { uint64_t cap; uint64_t* k; uint64_t* k2; uint32_t* v; uint8_t* used; } omap;
-
-static uint64_t mix64(uint64_t x) { x ^= x >> 33; x *= 0xff51afd7ed558ccdull; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ull; x ^= x >> 33; return x; }
-
-static int omap_init(omap* m, uint64_t n) {
-	uint64_t cap = 16; while (cap < 2*n + 2) cap <<= 1;
-	m->cap = cap;
-	m->k = (uint64_t*)malloc(cap*8); m->k2 = (uint64_t*)malloc(cap*8);
-	m->v = (uint32_t*)malloc(cap*4); m->used = (uint8_t*)calloc(cap, 1);
-	return m->k && m->k2 && m->v && m->used;
-}
-static void omap_free(omap* m) { free(m->k); free(m->k2); free(m->v); free(m->used); }
-/* last write wins, like operator[] assignment in the reference loaders */
-static void omap_put(omap* m, uint64_t key, uint64_t key2, uint32_t val) {
-	uint64_t i = mix64(key ^ mix64(key2 + 0x9e3779b97f4a7c15ull)) & (m->cap-1);
-	while (m->used[i]) { if (m->k[i] == key && m->k2[i] == key2) { m->v[i] = val; return; } i = (i+1) & (m->cap-1); }
-	m->used[i] = 1; m->k[i] = key; m->k2[i] = key2; m->v[i] = val;
-}
-static int omap_get(const omap* m, uint64_t key, uint64_t key2, uint32_t* val) {
-	uint64_t i = mix64(key ^ mix64(key2 + 0x9e3779b97f4a7c15ull)) & (m->cap-1);
-	while (m->used[i]) { if (m->k[i] == key && m->k2[i] == key2) { if (val) *val = m->v[i]; return 1; } i = (i+1) & (m->cap-1); }
-	return 0;
-}
-
-struct dbo_index {
-	uint64_t nloci, nk_tr, nvv;
-	omap dbi;        /* kmerDBi: k-mer -> val (h:35, kio:59-74)                                   */
-	uint32_t* vv;    /* kmerDBi_vv                                                               */
-	omap tr;         /* trResults[locus]: (k-mer, locus) -> position in the count array (h:31)    */
-	omap fl;         /* flankDB[locus]: (k-mer, locus) membership (h:47)                          */
-	uint8_t* qc;     /* qcFilter or NULL                                                         */
-};
 
 dbo_index* dbo_index_new(const dbt_index* in) {
 	dbo_index* ix = (dbo_index*)calloc(1, sizeof(*ix));
@@ -65,12 +25,25 @@ dbo_index* dbo_index_new(const dbt_index* in) {
 	for (uint64_t l = 0; l < in->nloci; ++l)
 		for (uint64_t i = 0; in->fl_n && i < in->fl_n[l]; ++i, ++j) omap_put(&ix->fl, in->fl_kmers[j], l, 1);
 	if (in->qc) { ix->qc = (uint8_t*)malloc(in->nloci); memcpy(ix->qc, in->qc, in->nloci); }
+	if (in->g_n && in->g_kmers && in->g_masks) {                 /* readGraphKmers, h:549-575: kmerDB[idx][kmer] |= c */
+		uint64_t ng = 0;
+		for (uint64_t l = 0; l < in->nloci; ++l) ng += in->g_n[l];
+		if (!omap_init(&ix->graph, ng)) return NULL;
+		j = 0;
+		for (uint64_t l = 0; l < in->nloci; ++l)
+			for (uint64_t i = 0; i < in->g_n[l]; ++i, ++j) {
+				uint32_t old = 0;
+				omap_get(&ix->graph, in->g_kmers[j], l, &old);
+				omap_put(&ix->graph, in->g_kmers[j], l, old | in->g_masks[j]);
+			}
+		ix->has_graph = 1;
+	}
 	return ix;
 }
 
 void dbo_index_free(dbo_index* ix) {
 	if (!ix) return;
-	omap_free(&ix->dbi); omap_free(&ix->tr); omap_free(&ix->fl); free(ix->vv); free(ix->qc); free(ix);
+	omap_free(&ix->dbi); omap_free(&ix->tr); omap_free(&ix->fl); if (ix->has_graph) omap_free(&ix->graph); free(ix->vv); free(ix->qc); free(ix);
 }
 
 /* ------------------------------------------------------------------------------------------ */

@@ -13,7 +13,18 @@
 //
 // Build (oracle/Makefile):  g++ -std=c++11 -O2 -w -pthread -I/root/reference/src ref_harness.cpp
 //
-// Usage: ref_harness PREF PAIRS.tsv OUT K CTH NFILTER NMFILTER NMTR OKAM [QCFILE]
+// Threading mode (P1; SURVEY.md §8(c) decision D1): the reference's isThreadFeasible and helpers
+// (aQueryFasta_thread.cpp:526-1260) compile but their only caller is commented out at HEAD
+// (cpp:2072-2088). With `thread=T` this harness re-creates that caller as GLUE (below, marked) --
+// the statements of the commented blocks cpp:2072-2088 / 2195-2209 / 2232-2248 with the variable
+// renames seq->seq1, seq1->seq2 -- and loads PREF.graph.kmers with the reference's readGraphKmers
+// (aQueryFasta_thread.h:549-575). Every algorithmic line that runs is still the reference's.
+//
+// Usage: ref_harness PREF PAIRS.tsv OUT K CTH NFILTER NMFILTER NMTR OKAM [QCFILE] [key=value ...]
+//   thread=T     -g T   (graph threading, thread_cth = T)
+//   corr=0|1     0 = -g (no error correction), 1 = -gc (default 1)
+//   maxnc=E      -gc T E (maxncorrection, default 4)
+//   aln=0|1|2    1 = -a, 2 = -ae: legacy .aln lines on stdout through the reference's writeAlignments
 //   PAIRS.tsv : one pair per line "seq1<TAB>seq2" in the reference's INTERNAL mate order
 //               (seq1 = seqs[2i] = the mate that arrived second, aQueryFasta_thread.cpp:1972-1974)
 //   writes OUT.trace.tsv, OUT.trkmc.ar, OUT.tr.summary.txt, OUT.counters.txt
@@ -38,7 +49,22 @@ int main(int argc, char* argv[]) {
 	NM_FILTER = stoul(argv[7]);
 	NM_TR = stoul(argv[8]);
 	bool okam = stoi(argv[9]);
-	bool qc = argc > 10;
+	bool threading = false, correction = true;
+	int aln = 0;
+	uint64_t thread_cth = 100;
+	string qcfile;
+	for (int i = 10; i < argc; ++i) {
+		string a = argv[i];
+		size_t eq = a.find('=');
+		if (eq == string::npos) { qcfile = a; continue; }
+		string key = a.substr(0, eq), val = a.substr(eq+1);
+		if      (key == "thread") { threading = true; thread_cth = stoul(val); }
+		else if (key == "corr")   { correction = stoi(val); }
+		else if (key == "maxnc")  { maxncorrection = stoul(val); }
+		else if (key == "aln")    { aln = stoi(val); }
+		else { cerr << "unknown option " << a << '\n'; return 2; }
+	}
+	bool qc = qcfile.size();
 
 	string trFname = pref + ".tr.kmers";
 	uint64_t nloci = countLoci(trFname);
@@ -52,9 +78,14 @@ int main(int argc, char* argv[]) {
 	readBinaryIndex(kmerDBi, kmerDBi_vv, pref);
 	readBinaryKmerSetDB(flankDB, pref+".fl");
 	readKmersWithZeroCount(trKmerDB, trFname);
-	if (qc) { readQCFile(qcFilter, argv[10]); }
+	if (qc) { readQCFile(qcFilter, qcfile); }
+	vector<GraphType> graphDB(nloci);
+	if (threading) { readGraphKmers(graphDB, pref + ".graph.kmers"); }
 
 	vector<uint32_t> hits1(nloci+1,0), hits2(nloci+1,0);
+	vector<string> seqs, titles;          // for writeAlignments (cpp:1742-1759)
+	vector<uint64_t> alnindices;
+	vector<sam_t> sams;
 	uint64_t nReads = 0, nShort = 0, nSub = 0, nKf = 0, nLaf = 0, nQC = 0, nThr = 0, nFea = 0, nAsgn = 0, nh0 = 0, nh1 = 0;
 
 	ifstream fin(pairsfn);
@@ -94,6 +125,59 @@ int main(int argc, char* argv[]) {
 			if (destLocus == nloci) { status = 3; }
 		}
 		if (status < 0 and qc and not qcFilter[destLocus]) { nQC += 2 - rm1 - rm2; status = 4; }
+		string thr_dump;
+		if (status < 0 and threading) {
+			// ---- GLUE (decision D1): the commented caller cpp:2072-2088, counting cpp:2195-2209
+			//      without the raw-k-mer double count, .aln selection cpp:2232-2239 (no simmode) ----
+			nThr += 2;
+			sam_t sam;
+			vector<uint64_t> nonca[2], ak[2];
+			int alned[2] = {0, 0};
+			string* ss[2] = { &s1, &s2 };
+			cigar_t* cgs[2] = { &sam.r1, &sam.r2 };
+			for (int m = 0; m < 2; ++m) {
+				cgs[m]->init(*ss[m]);
+				// a read without any valid k-mer leaves `kmers` empty and the reference then reads kmers[0]
+				// (cpp:1124): undefined behaviour. D1 defines such a mate as not threadable, k-mer vector empty.
+				bool anyvalid = false;
+				{ vector<uint64_t> t; read2kmers(t, *ss[m], ksize, 0, 0, false, true); anyvalid = t.size(); }
+				if (anyvalid) { alned[m] = isThreadFeasible(graphDB[destLocus], *ss[m], nonca[m], ak[m], thread_cth, correction, *cgs[m], trKmerDB[destLocus], log); }
+			}
+			uint64_t dst_before = destLocus;
+			if (alned[0] or alned[1]) {
+				nFea += 2;
+				kmer_aCount_umap& trKmers = trKmerDB[destLocus];
+				for (int m = 0; m < 2; ++m) {
+					for (uint64_t km : ak[m]) {
+						if (km == -1ULL) { continue; }
+						auto it = trKmers.find(toCaKmer(km, ksize));
+						if (it != trKmers.end()) { ++(it->second); }
+					}
+				}
+				status = 6;
+			}
+			else { destLocus = nloci; status = 5; }
+			if (aln == 1 or (aln == 2 and destLocus != nloci)) {
+				seqs.push_back(s1); seqs.push_back(s2);
+				titles.resize(seqs.size()/2, "p" + to_string(idx));
+				alnindices.push_back(seqs.size());
+				sam.src = -1;
+				sam.dst = destLocus;
+				sams.push_back(sam);
+			}
+			ostringstream td;
+			td << '\t' << dst_before;
+			for (int m = 0; m < 2; ++m) {
+				td << '\t' << alned[m] << '\t';
+				for (auto& e : cgs[m]->es) { td << (char)(e.t) << (char)(e.g ? e.g : '_'); }
+				td << '\t';
+				for (char c : cgs[m]->tr) { td << c; }
+				td << '\t';
+				for (size_t i = 0; i < ak[m].size(); ++i) { if (i) { td << ','; } td << (int64_t)ak[m][i]; }
+				if (not ak[m].size()) { td << '.'; }
+			}
+			thr_dump = td.str();
+		}
 		if (status < 0) {
 			// ---- glue: aQueryFasta_thread.cpp:2070-2175 (threading == false, no bait) ----
 			nThr += 2;
@@ -132,10 +216,11 @@ int main(int argc, char* argv[]) {
 			   << r.si << ':' << r.ei << ':' << r.si_ << ':' << r.ei_ << ':' << r.nt << ':' << r.bs << ':' << r.ti
 			   << '\t' << rle(r.as);
 		}
-		tr << '\n';
+		tr << thr_dump << '\n';
 		++idx;
 	}
 	tr.close();
+	if (aln) { writeAlignments(seqs, titles, alnindices, sams); }
 
 	dumpTRKmers(out, trKmerDB);
 	writeTRKmerSummary(out+".tr.summary.txt", kmc, nmapread);

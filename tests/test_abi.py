@@ -22,12 +22,12 @@ def test_header_and_python_mirror_agree():
 def test_library_exports_every_declared_symbol(lib):
     for s in declared_symbols():
         assert hasattr(lib, s), s
-    assert lib.dbt_abi_version() == 2
+    assert lib.dbt_abi_version() == 3
 
 
 def test_struct_sizes():
     assert C.sizeof(abi.Params) == 18 * 4
-    assert C.sizeof(abi.Index) == 11 * 8
+    assert C.sizeof(abi.Index) == 14 * 8
     assert C.sizeof(abi.Batch) == 40
     assert C.sizeof(abi.BatchResult) == 24 + abi.DBT_N_COUNTERS * 8
     assert abi.RECORD_HEADER_DTYPE.itemsize == 64
