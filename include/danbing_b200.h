@@ -199,6 +199,14 @@ typedef struct {
  * Records are emitted for the pairs the reference prints an .aln line for (cpp:2232-2239): with
  * DBT_F_ALN every pair that entered threading, with DBT_F_ALN_MIN only threaded ones; DBT_F_TRACE: all.
  */
+#define DBT_ES_TYPE(b)  ((b) & 7u)          /* index into "*=XDI"  */
+#define DBT_ES_BASE(b)  (((b) >> 3) & 7u)   /* index into "\0ACGT*" */
+static inline uint32_t dbt_es_cap_for(uint32_t max_read_len, uint32_t max_ncorrection) {
+  return (max_read_len + 2 * max_ncorrection + 8 + 7) / 8 * 8;
+}
+static inline uint32_t dbt_tr_cap_for(uint32_t max_read_len, uint32_t k, uint32_t max_ncorrection) {
+  return ((max_read_len >= k ? max_read_len - k + 1 : 1) + 2 * max_ncorrection + 8 + 7) / 8 * 8;
+}
 typedef struct {
   uint8_t  alned;              /* isThreadFeasible's return: 0 infeasible, 1 threaded, 2 threaded with edits */
   uint8_t  err;                /* 1 = the graph is not closed / capacity exceeded (reference: assert or UB) */

@@ -389,6 +389,32 @@ static void write_record(uint8_t* rec, uint32_t stride, uint32_t as_stride, uint
 	}
 }
 
+/* sam_t.r1 / r2 (cpp:53-75) of a pair that entered threading -> the two dbt_aln_mate blobs behind the header */
+static void write_aln_blobs(uint8_t* rec, uint32_t stride, const dbt_params* p, const dbo_thread_out* th) {
+	const uint32_t es_cap = dbt_es_cap_for(p->max_read_len, p->max_ncorrection);
+	const uint32_t aln_stride = (stride - (uint32_t)sizeof(dbt_pair_record)) / 2;
+	for (int m = 0; m < 2; ++m) {
+		uint8_t* b = rec + sizeof(dbt_pair_record) + (size_t)m * aln_stride;
+		memset(b, 0, aln_stride);
+		dbt_aln_mate* h = (dbt_aln_mate*)b;
+		h->alned = (uint8_t)th[m].rc; h->err = (uint8_t)th[m].err;
+		h->nes = (uint16_t)th[m].nes; h->ntr = (uint16_t)th[m].ntr; h->nkm = (uint16_t)th[m].nkm;
+		uint64_t hash = 0xcbf29ce484222325ull;
+		for (uint32_t i = 0; i < th[m].nkm; ++i)
+			for (int q = 0; q < 8; ++q) { hash ^= (th[m].kmers[i] >> (8*q)) & 0xFF; hash *= 0x100000001b3ull; }
+		h->kmers_hash = hash;
+		uint8_t* es = b + sizeof(dbt_aln_mate); uint8_t* tr = es + es_cap;
+		for (uint32_t i = 0; i < th[m].nes && i < es_cap; ++i) {
+			uint8_t t = th[m].es_t[i], g = th[m].es_g[i];
+			uint8_t tc = t == '*' ? 0 : t == '=' ? 1 : t == 'X' ? 2 : t == 'D' ? 3 : 4;
+			uint8_t gc = g == 0 ? 0 : g == 'A' ? 1 : g == 'C' ? 2 : g == 'G' ? 3 : g == 'T' ? 4 : 5;
+			es[i] = (uint8_t)(tc | (gc << 3));
+		}
+		for (uint32_t i = 0; i < th[m].ntr && sizeof(dbt_aln_mate) + es_cap + i < aln_stride; ++i)
+			tr[i] = th[m].tr[i] == '*' ? 0 : th[m].tr[i] == '.' ? 1 : 2;
+	}
+}
+
 /* The pair loop of CountWords, cpp:2002-2176 (asgn mode: threading off, no bait/bubbles/sim/extract). */
 void dbo_run(const dbo_index* ix, const dbt_params* p, uint64_t first_pair_index, uint64_t npairs,
              const uint8_t* bases, const uint64_t* offsets, uint8_t* records, uint32_t stride, uint32_t as_stride,
@@ -402,6 +428,7 @@ void dbo_run(const dbo_index* ix, const dbt_params* p, uint64_t first_pair_index
 	int64_t* kits1 = (int64_t*)malloc(maxlen * 8); int64_t* kits2 = (int64_t*)malloc(maxlen * 8);
 	int* as1 = (int*)malloc(maxlen * 4); int* as2 = (int*)malloc(maxlen * 4);
 	uint32_t* hits1 = (uint32_t*)calloc(nloci + 1, 4); uint32_t* hits2 = (uint32_t*)calloc(nloci + 1, 4);
+	dbo_thread_out* th = (dbo_thread_out*)calloc(2, sizeof(dbo_thread_out));
 
 	for (uint64_t pi = 0; pi < npairs; ++pi) {
 		const uint8_t* s1 = bases + offsets[2*pi]; uint32_t l1 = (uint32_t)(offsets[2*pi+1] - offsets[2*pi]);
@@ -433,8 +460,27 @@ void dbo_run(const dbo_index* ix, const dbt_params* p, uint64_t first_pair_index
 			if (destLocus == nloci) status = DBT_ST_UNASSIGNED;
 		}
 		if (status < 0 && qc && !ix->qc[destLocus]) { counters[DBT_C_NQCFILTERED] += (uint64_t)(2 - r1.rm - r2.rm); status = DBT_ST_QCFILTERED; }
-		if (status < 0 && (p->flags & DBT_F_THREADING)) {                                           /* cpp:2070; 2072-2090: alned stays false */
+		if (status < 0 && (p->flags & DBT_F_THREADING) && !ix->has_graph) {                         /* cpp:2070; 2072-2090: alned stays false */
 			counters[DBT_C_NTHREADINGREADS] += 2; status = DBT_ST_NOT_THREADED;
+		}
+		int threaded = 0;
+		if (status < 0 && (p->flags & DBT_F_THREADING)) {
+			/* restored caller (SURVEY.md §8(c) decision D1): commented blocks cpp:2072-2088 and 2195-2209 */
+			counters[DBT_C_NTHREADINGREADS] += 2;
+			threaded = 1;
+			dbo_thread_read(ix, destLocus, s1, l1, p, &th[0]);
+			dbo_thread_read(ix, destLocus, s2, l2, p, &th[1]);
+			if (th[0].rc || th[1].rc) {
+				counters[DBT_C_NFEASIBLEREADS] += 2;
+				for (int m = 0; m < 2; ++m)
+					for (uint32_t i = 0; i < th[m].nkm; ++i) {
+						uint64_t km = th[m].kmers[i]; uint32_t pos;
+						if (km == NAN64) continue;
+						uint64_t r = dbo_revcomp(km, k); if (r < km) km = r;
+						if (omap_get(&ix->tr, km, destLocus, &pos)) { ++trkmc[pos]; ++counters[DBT_C_NINC]; }
+					}
+				status = DBT_ST_COUNTED;
+			} else { destLocus = nloci; status = DBT_ST_THREAD_FAILED; }
 		}
 		if (status < 0) {
 			counters[DBT_C_NTHREADINGREADS] += 2; counters[DBT_C_NFEASIBLEREADS] += 2;            /* cpp:2070, 2092 */
@@ -457,8 +503,9 @@ void dbo_run(const dbo_index* ix, const dbt_params* p, uint64_t first_pair_index
 			write_record(records + pi * (uint64_t)stride, stride, as_stride, first_pair_index + pi, status,
 			             status >= DBT_ST_UNASSIGNED ? destLocus : nloci, status >= DBT_ST_UNASSIGNED ? destLocus0 : NAN32,
 			             status >= DBT_ST_UNASSIGNED ? fc : 0, status >= DBT_ST_UNASSIGNED ? rc : 0, nhash0, nhash1, &r1, &r2);
+			if (threaded) write_aln_blobs(records + pi * (uint64_t)stride, stride, p, th);
 			++counters[DBT_C_NRECORDS];
 		}
 	}
-	free(k1); free(k2); free(its1); free(its2); free(kits1); free(kits2); free(as1); free(as2); free(hits1); free(hits2);
+	free(k1); free(k2); free(its1); free(its2); free(kits1); free(kits2); free(as1); free(as2); free(hits1); free(hits2); free(th);
 }

@@ -378,10 +378,10 @@ static void edit_kmers_backward(thr_t* T, txt_t* x, uint64_t* ki_io, uint64_t* n
 			while (is_edit(t) && !T->err) { --e0; t = ES(T, e0-1)->t; }
 		}
 		/* merge edits if possible */
-		uint8_t ets[TCAP], rnts[TCAP], gnts[TCAP]; int nets = 0, nr = 0, ng = 0;
+		uint8_t rnts[TCAP], gnts[TCAP]; int nets = 0, nr = 0, ng = 0;
 		for (int i = e0; i < e1; ++i) {
 			edit_t* e = ES(T, i);
-			ets[nets++] = e->t;
+			++nets;                                                           /* ets.push_back(e.t) */
 			if (e->r) rnts[nr++] = e->r;
 			if (e->g) gnts[ng++] = e->g;
 		}

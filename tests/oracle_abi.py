@@ -92,6 +92,11 @@ class Oracle:
         max_len = int(np.max(np.diff(offsets.astype(np.int64)))) if npairs else 1
         as_stride = abi.as_stride_for(max(max_len, params.max_read_len), params.k)
         stride = 64 + 2 * as_stride
+        threading = bool(params.flags & abi.F_THREADING) and self.ix.get("g_n") is not None
+        if threading:                         # restored threading: header + two dbt_aln_mate blobs
+            assert max_len <= params.max_read_len
+            es_cap, tr_cap, aln_stride = abi.aln_caps(params.max_read_len, params.k, params.max_ncorrection)
+            stride = 64 + 2 * aln_stride
         rec = np.zeros(max(npairs, 1) * stride, np.uint8)
         if acc is None:
             trkmc = np.zeros(max(self.nk_tr, 1), np.uint64)
@@ -103,7 +108,7 @@ class Oracle:
         self.L.dbo_run(self.h, C.byref(params), first_pair_index, npairs, abi.ptr(bases, abi.u8p),
                        abi.ptr(offsets, abi.u64p), abi.ptr(rec, abi.u8p), stride, as_stride,
                        abi.ptr(trkmc, abi.u64p), abi.ptr(kmc, abi.u64p), abi.ptr(nmap, abi.u32p), abi.ptr(cnt, abi.u64p))
-        recs = rec[: npairs * stride].view(abi.record_dtype(as_stride))
+        recs = rec[: npairs * stride].view(abi.aln_record_dtype(es_cap, tr_cap) if threading else abi.record_dtype(as_stride))
         return recs, cnt, trkmc[: self.nk_tr], kmc[: self.nloci], nmap[: self.nloci]
 
 

@@ -69,3 +69,24 @@ def test_restatement_vs_golden_trace():
     rows = [l.rstrip("\n").split("\t") for l in gzip.open(os.path.join(GOLD, "harness.trace.tsv.gz"), "rt")]
     nread, hist = check_rows(rows, seqs, ix, p)
     assert nread == meta["threaded_reads"] and {str(k): v for k, v in hist.items()} == meta["rc_hist"]
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("ci", [0, 3, 4])
+def test_pair_level_D1_glue_vs_harness(ci, tmp_path):
+    """dbo_run in restored-threading mode: statuses, records, counters and per-locus counts equal the harness run."""
+    gk, pk = split_case(CASES[ci])
+    pref, ix, seqs, _ = tc.thread_case(outdir=str(tmp_path), frac_bg=0.2, **gk)
+    p = tc.thread_params(aln=1, **pk)
+    rows, _, ref_trkmc, ref_cnt = tc.run_ref_thread_harness(pref, seqs, str(tmp_path / "ref"), p)
+    # the harness dumps counts in the reference's unordered_map order: load the index in that order
+    ix2 = rpgg_io.load_index(pref, tr_order=tc.ref_tr_order(pref, str(tmp_path)))
+    ix2.update({k: ix[k] for k in ("g_n", "g_kmers", "g_masks")})
+    bases, off = rpgg_io.seqs_to_batch(seqs)
+    recs, cnt, trkmc, kmc, nmap = Oracle(ix2).run(p, bases, off)
+    assert tc.check_records_vs_harness(recs, rows, int(ix["nloci"])) > 50
+    assert np.array_equal(trkmc, ref_trkmc)
+    names = dict(zip(abi.COUNTER_NAMES, [int(x) for x in cnt]))
+    for key in ("nReads", "nShort", "nSubFiltered", "nKmerFiltered", "nLocusAssignFiltered", "nThreadingReads", "nFeasibleReads", "nhash0", "nhash1"):
+        assert names[key] == ref_cnt[key], key
+    assert kmc.sum() == 0 and nmap.sum() == 0

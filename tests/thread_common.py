@@ -93,3 +93,48 @@ def oracle_thread_read(o, locus, seq, p):
     es = "".join(chr(out.es_t[i]) + (chr(out.es_g[i]) if out.es_g[i] else "_") for i in range(out.nes))
     tr = bytes(out.tr[:out.ntr]).decode()
     return rc, out.err, es, tr, [int(out.kmers[i]) for i in range(out.nkm)]
+
+
+def es_string(es_bytes, n):
+    return "".join(abi.ES_T[b & 7] + abi.ES_G[(b >> 3) & 7] for b in es_bytes[:n])
+
+
+def tr_string(tr_bytes, n):
+    return "".join(abi.TR_C[b] for b in tr_bytes[:n])
+
+
+def check_records_vs_harness(recs, rows, nloci):
+    """Record-level parity of dbt_aln records (GPU or oracle, one per pair, input order) with the harness trace."""
+    n = 0
+    for f in rows:
+        idx, status, dst, mates = parse_thread_row(f)
+        r = recs[idx]
+        if mates is None:
+            assert int(r["h"]["status"]) == status, f"pair {idx}"
+            continue
+        want_status = abi.ST_COUNTED if status == 6 else abi.ST_THREAD_FAILED
+        assert int(r["h"]["status"]) == want_status, f"pair {idx}"
+        assert int(r["h"]["dst"]) == (dst if status == 6 else nloci), f"pair {idx}"
+        for m in range(2):
+            alned, es, tr, kms = mates[m]
+            a = r["aln"][m]
+            assert int(a["h"]["err"]) == 0
+            assert int(a["h"]["alned"]) == alned, f"pair {idx} mate {m}"
+            assert es_string(a["es"], int(a["h"]["nes"])) == es, f"pair {idx} mate {m}"
+            assert tr_string(a["tr"], int(a["h"]["ntr"])) == tr, f"pair {idx} mate {m}"
+            assert int(a["h"]["nkm"]) == len(kms) and int(a["h"]["kmers_hash"]) == abi.fnv1a_u64(kms), f"pair {idx} mate {m}"
+        n += 1
+    return n
+
+
+def ref_tr_order(pref, tmpdir, k=21):
+    """(tr_n, tr_kmers) in the reference's output order = libstdc++ unordered_map iteration order
+    (SURVEY.md F4 trap 6), read off a `-on` run of the unmodified reference binary on one dummy pair."""
+    from oracle_abi import run_ref_binary
+    fa = os.path.join(tmpdir, "dummy.fa")
+    with open(fa, "w") as f:
+        f.write(">d/1\n" + "A" * 60 + "\n>d/2\n" + "C" * 60 + "\n")
+    out = os.path.join(tmpdir, "order")
+    run_ref_binary(pref, fa, out, k=k, named=True)
+    tn, tk, _ = rpgg_io.read_kmers_text(out + ".tr.kmers")
+    return tn, tk
