@@ -245,6 +245,9 @@ class Context:
         self.nloci = self.L.dbt_nloci(self.h)
         self.stride = self.L.dbt_record_stride(self.h)
         self.as_stride = self.L.dbt_record_as_stride(self.h)
+        self.aln_stride = self.L.dbt_record_aln_stride(self.h)
+        self.es_cap = self.L.dbt_record_es_cap(self.h)
+        self.threading = self.stride == 64 + 2 * self.aln_stride      # restored threading is active (graph loaded)
 
     def close(self):
         if self.h:
@@ -278,7 +281,8 @@ class Context:
         check(self.L, self.L.dbt_submit(self.h, C.byref(b), C.byref(r), slot), "dbt_submit")
         check(self.L, self.L.dbt_wait(self.h, slot), "dbt_wait")
         n = int(r.n_records)
-        recs = rec[: n * self.stride].view(record_dtype(self.as_stride))
+        dt = aln_record_dtype(self.es_cap, self.aln_stride - 16 - self.es_cap) if self.threading else record_dtype(self.as_stride)
+        recs = rec[: n * self.stride].view(dt)
         return recs, np.array(list(r.counters), dtype=np.uint64)
 
     def download(self):

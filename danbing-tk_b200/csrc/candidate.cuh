@@ -320,7 +320,8 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 	const uint32_t gwarp = blockIdx.x * WPB + wib;
 	const uint32_t nwarps = gridDim.x * WPB;
 	const uint32_t W64 = rp.lay.W64, WB = rp.lay.WB, K = rp.k, NKP = rp.nkp, UMAX = rp.umax;
-	const bool okam = (rp.flags & DBT_F_KAM) != 0, trace = (rp.flags & DBT_F_TRACE) != 0;
+	const bool okam = (rp.flags & DBT_F_KAM) != 0 && !rp.thr_on, trace = (rp.flags & DBT_F_TRACE) != 0;   // no kam lines with threading (cpp:2110)
+	const bool wstat = okam || (rp.thr_on && (rp.flags & (DBT_F_ALN | DBT_F_ALN_MIN)));
 
 	// ---- shared-memory carve-up (per warp); dbt_create mirrors the sizes ----
 	uint8_t* ws = smem_raw + (size_t)wib * rp.warp_smem;
@@ -660,7 +661,7 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 			}
 			// record
 			const bool emit = trace || (okam && status == DBT_ST_COUNTED);
-			if (!emit && okam && c < rp.max_records) {
+			if (!emit && wstat && c < rp.max_records) {
 				// the slot of a candidate that prints no kam line must not keep a stale record
 				if (lane == 0) reinterpret_cast<dbt_pair_record*>(sv.records + (uint64_t)c * rp.rec_stride)->status = (uint8_t)status;
 			}

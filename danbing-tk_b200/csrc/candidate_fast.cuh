@@ -62,7 +62,8 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
 	const uint32_t gwarp = blockIdx.x * CAND_FAST_WARPS + wib, nwarps = gridDim.x * CAND_FAST_WARPS;
 	const uint32_t W64 = rp.lay.W64, WB = rp.lay.WB, K = rp.k;
-	const bool okam = (rp.flags & DBT_F_KAM) != 0;
+	const bool okam = (rp.flags & DBT_F_KAM) != 0 && !rp.thr_on;       // kam lines are only written without threading (cpp:2110)
+	const bool wstat = okam || (rp.thr_on && (rp.flags & (DBT_F_ALN | DBT_F_ALN_MIN)));   // record slots are keyed by candidate ordinal: keep their status current
 	const uint32_t nloci = (uint32_t)ix.nloci, cth = rp.cth;
 	FastWarp<B, MAXJ>& W = wsm[wib];
 	uint32_t c_kf = 0, c_laf = 0, c_qc = 0, c_thr = 0, c_asgn = 0, c_h1 = 0, c_inc = 0, c_thr0 = 0;   // lane-0 accumulators
@@ -212,7 +213,7 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 		if (rmm == 3u) {                                         // cpp:2054
 			if (lane == 0) {
 				c_kf += __popc(kfm); c_h1 += nhash1;
-				if (okam && c < rp.max_records) reinterpret_cast<dbt_pair_record*>(sv.records + (uint64_t)c * rp.rec_stride)->status = (uint8_t)DBT_ST_KFILTERED;
+				if (wstat && c < rp.max_records) reinterpret_cast<dbt_pair_record*>(sv.records + (uint64_t)c * rp.rec_stride)->status = (uint8_t)DBT_ST_KFILTERED;
 			}
 			continue;
 		}
@@ -289,7 +290,12 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 			if (lane == 0) c_qc += 2 - __popc(rmm);
 		}
 
-		if (status < 0 && (rp.flags & DBT_F_THREADING)) { status = DBT_ST_NOT_THREADED; if (lane == 0) c_thr0 += 2; }   // cpp:2070-2090 at HEAD
+		if (status < 0 && (rp.flags & DBT_F_THREADING)) {
+			if (rp.thr_on) {                                     // restored threading: hand the pair to thread_kernel (cpp:2070-2088)
+				status = DBT_ST_THREAD_PENDING;
+				if (lane == 0) { c_thr0 += 2; sv.thr_dst[c] = dst | (kfm << 28) | (rmm << 30); sv.thr[atomicAdd(sv.ncand + 3, 1u)] = c; }
+			} else { status = DBT_ST_NOT_THREADED; if (lane == 0) c_thr0 += 2; }   // cpp:2070-2090 at HEAD
+		}
 		if (status < 0) {
 			if (lane == 0) c_thr += 2;
 			int span = 0;
@@ -356,7 +362,7 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 		}
 
 		// ---- kam record (cpp:2169-2175); slot = candidate ordinal, compacted by dbt_wait ----
-		if (okam) {
+		if (wstat) {
 			if (c >= rp.max_records) { if (lane == 0 && status == DBT_ST_COUNTED) atomicOr(sv.ncand + 1, ERR_RECORD_OVERFLOW); }
 			else if (status != DBT_ST_COUNTED) {
 				if (lane == 0) reinterpret_cast<dbt_pair_record*>(sv.records + (uint64_t)c * rp.rec_stride)->status = (uint8_t)status;

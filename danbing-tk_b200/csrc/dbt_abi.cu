@@ -14,6 +14,7 @@
 #include <dlfcn.h>
 
 #include "launchers.h"
+#include "graph_table.cuh"
 
 using namespace dbt;
 
@@ -61,18 +62,18 @@ extern "C" void dbt_default_params(dbt_params* p) {
 // ------------------------------------------------------------------------------------------
 // context
 // ------------------------------------------------------------------------------------------
-enum { KT_PACK = 0, KT_SUBFILTER, KT_COMPACT, KT_CANDIDATE, KT_GENERIC, KT_N };   // KT_CANDIDATE = closed-form kernel, KT_GENERIC = generic kernel
+enum { KT_PACK = 0, KT_SUBFILTER, KT_COMPACT, KT_CANDIDATE, KT_GENERIC, KT_THREAD, KT_N };   // KT_CANDIDATE = closed-form kernel, KT_GENERIC = generic kernel
 
 struct Slot {
 	bool ready = false;
 	cudaStream_t st = nullptr;
 	uint8_t* d_ascii = nullptr; uint64_t* d_offsets = nullptr;
 	uint64_t* d_packed[2] = {nullptr, nullptr}; uint16_t* d_meta[2] = {nullptr, nullptr};
-	uint32_t* d_passmask = nullptr; uint32_t* d_blocksum = nullptr; uint32_t* d_cand = nullptr; uint32_t* d_ncand = nullptr; uint32_t* d_slow = nullptr;
+	uint32_t* d_passmask = nullptr; uint32_t* d_blocksum = nullptr; uint32_t* d_cand = nullptr; uint32_t* d_ncand = nullptr; uint32_t* d_slow = nullptr; uint32_t* d_thr = nullptr; uint32_t* d_thr_dst = nullptr;
 	uint8_t* d_records = nullptr; unsigned long long* d_counters = nullptr;
 	uint8_t* h_records = nullptr;            // pinned staging
 	uint64_t* h_counters = nullptr;          // pinned: DBT_N_COUNTERS u64 + 4 u32 (ncand, err, nslow, -)
-	uint64_t last_ncand = 0, last_nslow = 0;
+	uint64_t last_ncand = 0, last_nslow = 0, last_nthr = 0;
 	uint64_t npairs = 0, first_pair_index = 0;
 	bool uploaded = false, processed = false, fetch_pending = false;
 	dbt_batch_result* result = nullptr;
@@ -100,6 +101,7 @@ struct dbt_ctx {
 	bool index_loaded = false;
 	DevIndex ix{};
 	// owned device memory of the index
+	uint4* d_gslots = nullptr; uint64_t gtable_bytes = 0, gnodes = 0;   // graph table (restored threading)
 	uint4* d_slots = nullptr; uint32_t* d_vv = nullptr; uint32_t* d_vv_aux = nullptr;
 	uint64_t* d_counts = nullptr; uint64_t* d_kmc = nullptr; uint32_t* d_nmapread = nullptr; uint8_t* d_qc = nullptr;
 	uint16_t* d_permtab = nullptr; uint64_t* d_vote_scratch = nullptr; uint32_t* d_vote_epoch = nullptr;
@@ -157,6 +159,12 @@ extern "C" int dbt_create(dbt_ctx** out, const dbt_params* p) {
 	rp.as_stride = round_up((rp.nk_max + 3) / 4, 8);
 	rp.rec_stride = (uint32_t)sizeof(dbt_pair_record) + 2 * rp.as_stride;
 	rp.max_records = c->p.max_records;
+	// restored threading: geometry of the alignment blobs; switched on by dbt_load_index when the index carries a graph
+	rp.thr_on = 0; rp.thread_cth = p->thread_cth; rp.max_ncorrection = p->max_ncorrection; rp.correction = (p->flags & DBT_F_CORRECTION) ? 1u : 0u;
+	rp.es_cap = DBT_ES_CAP_FOR(p->max_read_len, p->max_ncorrection);
+	rp.tr_cap = DBT_TR_CAP_FOR(p->max_read_len, p->k, p->max_ncorrection);
+	rp.aln_stride = (uint32_t)sizeof(dbt_aln_mate) + rp.es_cap + rp.tr_cap;
+	if ((p->flags & DBT_F_THREADING) && rp.tr_cap > 16 * 32) { delete c; return fail(DBT_E_CAPACITY, "threading: read length + 2*max_ncorrection exceeds 512 k-mers"); }
 	// must mirror the carve-up in candidate_kernel
 	size_t ws = 0;
 	ws += (size_t)2 * rp.lay.W64 * 8;                // pk
@@ -186,7 +194,7 @@ static void free_slot(Slot& s) {
 	if (s.st) cudaStreamSynchronize(s.st);
 	cudaFree(s.d_ascii); cudaFree(s.d_offsets);
 	for (int m = 0; m < 2; ++m) { cudaFree(s.d_packed[m]); cudaFree(s.d_meta[m]); }
-	cudaFree(s.d_passmask); cudaFree(s.d_blocksum); cudaFree(s.d_cand); cudaFree(s.d_ncand); cudaFree(s.d_slow); cudaFree(s.d_records); cudaFree(s.d_counters);
+	cudaFree(s.d_passmask); cudaFree(s.d_blocksum); cudaFree(s.d_cand); cudaFree(s.d_ncand); cudaFree(s.d_slow); cudaFree(s.d_thr); cudaFree(s.d_thr_dst); cudaFree(s.d_records); cudaFree(s.d_counters);
 	if (s.h_records) cudaFreeHost(s.h_records);
 	if (s.h_counters) cudaFreeHost(s.h_counters);
 	for (auto& e : s.ev) if (e) cudaEventDestroy(e);
@@ -201,6 +209,7 @@ extern "C" void dbt_destroy(dbt_ctx* c) {
 	cudaSetDevice(c->p.device);
 	for (auto& s : c->slot) free_slot(s);
 	if (c->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
+	cudaFree(c->d_gslots);
 	cudaFree(c->d_slots); cudaFree(c->d_vv); cudaFree(c->d_vv_aux); cudaFree(c->d_counts); cudaFree(c->d_kmc); cudaFree(c->d_nmapread);
 	cudaFree(c->d_qc); cudaFree(c->d_permtab); cudaFree(c->d_vote_scratch); cudaFree(c->d_vote_epoch); cudaFree(c->d_totals);
 	delete c;
@@ -230,8 +239,9 @@ static int ensure_slot(dbt_ctx* c, int si) {
 	TRY(dev_alloc(&s.d_cand, P, "cand"));
 	TRY(dev_alloc(&s.d_ncand, 4, "ncand"));
 	TRY(dev_alloc(&s.d_slow, P, "slow list"));
+	if (rp.thr_on) { TRY(dev_alloc(&s.d_thr, P, "thread list")); TRY(dev_alloc(&s.d_thr_dst, P, "thread dst")); }
 	TRY(dev_alloc(&s.d_counters, DBT_N_COUNTERS, "counters"));
-	const bool want_records = (c->p.flags & (DBT_F_KAM | DBT_F_TRACE)) != 0;
+	const bool want_records = rp.thr_on ? (c->p.flags & (DBT_F_ALN | DBT_F_ALN_MIN | DBT_F_TRACE)) != 0 : (c->p.flags & (DBT_F_KAM | DBT_F_TRACE)) != 0;
 	if (want_records) {
 		TRY(dev_alloc(&s.d_records, (size_t)c->p.max_records * rp.rec_stride, "records"));
 		cudaError_t e = cudaHostAlloc((void**)&s.h_records, std::max<size_t>((size_t)c->p.max_records * rp.rec_stride, 16), cudaHostAllocDefault);
@@ -247,6 +257,63 @@ static int ensure_slot(dbt_ctx* c, int si) {
 // ------------------------------------------------------------------------------------------
 // index
 // ------------------------------------------------------------------------------------------
+// graphDB of all loci -> one device table (graph_table.cuh); replaces readGraphKmers (h:549-575) + cpp:2468
+static int load_graph(dbt_ctx* c, const dbt_index* in, uint64_t ntr) {
+	const uint64_t nloci = in->nloci;
+	if (nloci >= G_LOCUS_MASK) return fail(DBT_E_CAPACITY, "threading supports < %u loci", G_LOCUS_MASK);
+	uint64_t ng = 0;
+	for (uint64_t l = 0; l < nloci; ++l) ng += in->g_n[l];
+	if (ntr >= 0xFFFFFFFFull) return fail(DBT_E_CAPACITY, "too many TR k-mers");
+	const int B = c->B;
+	// entries <= canonical nodes (ng/2 when both strands are stored) + TR k-mers missing from the graph (normally none)
+	const uint64_t nent = ng / 2 + ng % 2 + 1024;
+	uint64_t nbuckets = (uint64_t)((double)nent / c->p.table_load) / B + 64;
+	uint64_t nstash = std::max<uint64_t>(64, (nent / 2 + ntr / 8 + B - 1) / B);
+	if (nbuckets >= (1ull << 32) || nstash >= (1ull << 32)) return fail(DBT_E_CAPACITY, "graph table needs %llu buckets (limit 2^32)", (unsigned long long)nbuckets);
+	c->gtable_bytes = (nbuckets + nstash) * B * sizeof(uint4); c->gnodes = ng;
+	cudaStream_t st; CU(cudaStreamCreate(&st));
+	TRY(dev_alloc(&c->d_gslots, (nbuckets + nstash) * B, "graph table"));
+	CU(cudaMemsetAsync(c->d_gslots, 0xFF, c->gtable_bytes, st));
+	Table t{c->d_gslots, nbuckets, nstash};
+	uint32_t* d_err; TRY(dev_alloc(&d_err, 1, "err")); CU(cudaMemsetAsync(d_err, 0, 4, st));
+	{
+		std::vector<uint32_t> loc(std::max<uint64_t>(ng, ntr));
+		uint64_t j = 0;
+		for (uint64_t l = 0; l < nloci; ++l) for (uint64_t i = 0; i < in->g_n[l]; ++i) loc[j++] = (uint32_t)l;
+		uint64_t* dk; uint8_t* dm; uint32_t* dl;
+		TRY(dev_alloc(&dk, std::max<uint64_t>(ng, ntr), "graph kmers")); TRY(dev_alloc(&dm, ng, "graph masks")); TRY(dev_alloc(&dl, std::max<uint64_t>(ng, ntr), "graph loci"));
+		if (ng) {
+			CU(cudaMemcpyAsync(dk, in->g_kmers, ng * 8, cudaMemcpyHostToDevice, st));
+			CU(cudaMemcpyAsync(dm, in->g_masks, ng, cudaMemcpyHostToDevice, st));
+			CU(cudaMemcpyAsync(dl, loc.data(), ng * 4, cudaMemcpyHostToDevice, st));
+			for (int pass = 0; pass < 2; ++pass) { CU(launch_graph_build(st, B, t, dk, dm, dl, ng, c->p.k, pass, d_err)); ++c->launches; }
+			CU(launch_graph_build(st, B, t, dk, dm, dl, ng, c->p.k, 3, d_err)); ++c->launches;
+			CU(cudaStreamSynchronize(st));
+		}
+		if (ntr) {                                     // TR k-mers attach their count-array position (trResults[locus], cpp:2465)
+			j = 0;
+			for (uint64_t l = 0; l < nloci; ++l) for (uint64_t i = 0; i < in->tr_n[l]; ++i) loc[j++] = (uint32_t)l;
+			CU(cudaMemcpyAsync(dk, in->tr_kmers, ntr * 8, cudaMemcpyHostToDevice, st));
+			CU(cudaMemcpyAsync(dl, loc.data(), ntr * 4, cudaMemcpyHostToDevice, st));
+			CU(launch_graph_build(st, B, t, dk, nullptr, dl, ntr, c->p.k, 2, d_err)); ++c->launches;
+			CU(cudaStreamSynchronize(st));
+		}
+		cudaFree(dk); cudaFree(dm); cudaFree(dl);
+	}
+	uint32_t herr = 0;
+	CU(cudaMemcpy(&herr, d_err, 4, cudaMemcpyDeviceToHost));
+	cudaFree(d_err);
+	CU(cudaStreamDestroy(st));
+	if (herr & ERR_INDEX_FULL) return fail(DBT_E_CAPACITY, "graph table overflow: lower table_load");
+	if (herr & ERR_INDEX_MISSING) return fail(DBT_E_INDEX, "graph.kmers holds a node that does not fit k=%u", c->p.k);
+	if (herr & ERR_INDEX_DUPKEY) return fail(DBT_E_INDEX, "duplicate node within a locus of the graph (merge masks before dbt_load_index, h:569)");
+	if (herr & ERR_INDEX_DUPTR) return fail(DBT_E_INDEX, "duplicate TR k-mer within a locus");
+	c->ix.gtable = t;
+	c->rp.thr_on = 1;
+	c->rp.rec_stride = (uint32_t)sizeof(dbt_pair_record) + 2 * c->rp.aln_stride;
+	return DBT_OK;
+}
+
 extern "C" int dbt_load_index(dbt_ctx* c, const dbt_index* in) {
 	if (!c || !in) return fail(DBT_E_BADARG, "null argument");
 	if (c->index_loaded) return fail(DBT_E_STATE, "index already loaded");
@@ -359,6 +426,8 @@ extern "C" int dbt_load_index(dbt_ctx* c, const dbt_index* in) {
 	c->ix.counts = c->d_counts; c->ix.kmc = c->d_kmc; c->ix.nmapread = c->d_nmapread; c->ix.qc = c->d_qc;
 	c->ix.permtab = c->d_permtab; c->ix.vote_scratch = c->d_vote_scratch; c->ix.vote_epoch = c->d_vote_epoch;
 	c->ix.nloci = nloci; c->ix.nk_tr = ntr;
+	c->ix.gtable = Table{nullptr, 0, 0};
+	if ((c->p.flags & DBT_F_THREADING) && in->g_n && in->g_kmers && in->g_masks) TRY(load_graph(c, in, ntr));
 	c->index_loaded = true;
 	return DBT_OK;
 }
@@ -433,7 +502,7 @@ extern "C" void dbt_host_free(void* p) { if (p) cudaFreeHost(p); }
 static SlotView slot_view(const dbt_ctx* c, const Slot& s) {
 	SlotView v;
 	v.packed[0] = s.d_packed[0]; v.packed[1] = s.d_packed[1]; v.meta[0] = s.d_meta[0]; v.meta[1] = s.d_meta[1];
-	v.passmask = s.d_passmask; v.blocksum = s.d_blocksum; v.cand = s.d_cand; v.ncand = s.d_ncand; v.slow = s.d_slow; v.records = s.d_records;
+	v.passmask = s.d_passmask; v.blocksum = s.d_blocksum; v.cand = s.d_cand; v.ncand = s.d_ncand; v.slow = s.d_slow; v.thr = s.d_thr; v.thr_dst = s.d_thr_dst; v.records = s.d_records;
 	v.counters = s.d_counters; v.npairs = s.npairs; v.first_pair_index = s.first_pair_index;
 	(void)c;
 	return v;
@@ -489,7 +558,9 @@ extern "C" int dbt_process(dbt_ctx* c, int slot) {
 	SlotView sv = slot_view(c, s);
 	CU(cudaMemsetAsync(s.d_counters, 0, DBT_N_COUNTERS * 8, s.st));
 	CU(cudaMemsetAsync(s.d_ncand, 0, 4, s.st));
-	CU(cudaMemsetAsync(s.d_ncand + 2, 0, 4, s.st));
+	CU(cudaMemsetAsync(s.d_ncand + 2, 0, 8, s.st));
+	if (c->rp.thr_on && (c->p.flags & DBT_F_TRACE) && s.d_records)      // blobs of pairs that never reach threading read as zeros
+		CU(cudaMemsetAsync(s.d_records, 0, (size_t)c->p.max_records * c->rp.rec_stride, s.st));
 	CU(cudaEventRecord(s.ev[1], s.st));
 	CU(launch_subfilter(s.st, c->B, c->nsm, c->ix, c->rp, sv)); if (s.npairs) ++c->launches;
 	CU(cudaEventRecord(s.ev[2], s.st));
@@ -498,6 +569,8 @@ extern "C" int dbt_process(dbt_ctx* c, int slot) {
 	CU(launch_candidate(s.st, c->B, c->cand_grid_fast, c->cand_grid, c->ix, c->rp, sv, s.ev[4]));
 	if (s.npairs) c->launches += ((c->p.flags & DBT_F_TRACE) || c->rp.nk_max > 255) ? 1 : 2;   // generic kernel alone, or closed-form + generic
 	CU(cudaEventRecord(s.ev[5], s.st));
+	if (c->rp.thr_on) { CU(launch_thread(s.st, c->B, c->nsm, c->ix, c->rp, sv)); if (s.npairs) ++c->launches; }
+	CU(cudaEventRecord(s.ev[6], s.st));
 	s.processed = true; s.ev_proc = true;
 	return DBT_OK;
 }
@@ -528,12 +601,14 @@ extern "C" int dbt_wait(dbt_ctx* c, int slot) {
 	dbt_batch_result* r = s.result; s.result = nullptr;
 	const uint32_t* tail = reinterpret_cast<const uint32_t*>(s.h_counters + DBT_N_COUNTERS);
 	const uint32_t ncand = tail[0], err = tail[1];
-	s.last_ncand = ncand; s.last_nslow = tail[2];
+	s.last_ncand = ncand; s.last_nslow = tail[2]; s.last_nthr = tail[3];
 	if (err & ERR_READ_TOO_LONG) return fail(DBT_E_CAPACITY, "a read is longer than max_read_len=%u", c->p.max_read_len);
 	for (int i = 0; i < DBT_N_COUNTERS; ++i) r->counters[i] = s.h_counters[i];
 	r->counters[DBT_C_NREADS] = 2 * s.npairs;
 	r->n_records = 0;
-	const bool trace = (c->p.flags & DBT_F_TRACE) != 0, okam = (c->p.flags & DBT_F_KAM) != 0;
+	const bool thr = c->rp.thr_on != 0;
+	const bool aln_min = (c->p.flags & DBT_F_ALN_MIN) != 0, aln = (c->p.flags & (DBT_F_ALN | DBT_F_ALN_MIN)) != 0;
+	const bool trace = (c->p.flags & DBT_F_TRACE) != 0, okam = thr ? aln : (c->p.flags & DBT_F_KAM) != 0;
 	int rc = DBT_OK;
 	if ((trace || okam) && r->records) {
 		if (err & ERR_RECORD_OVERFLOW) rc = fail(DBT_E_CAPACITY, "%u candidate pairs exceed max_records=%u", ncand, c->p.max_records);
@@ -546,7 +621,9 @@ extern "C" int dbt_wait(dbt_ctx* c, int slot) {
 		uint64_t n = 0;
 		for (uint64_t i = 0; i < nslots; ++i) {
 			const uint8_t* src = s.h_records + i * stride;
-			if (!trace && reinterpret_cast<const dbt_pair_record*>(src)->status != DBT_ST_COUNTED) continue;
+			const uint8_t stt = reinterpret_cast<const dbt_pair_record*>(src)->status;
+			// kam line / `-ae`: counted pairs only; `-a`: every pair that entered threading (cpp:2232-2239)
+			if (!trace && stt != DBT_ST_COUNTED && !(thr && !aln_min && stt == DBT_ST_THREAD_FAILED)) continue;
 			if (n >= r->capacity) { rc = fail(DBT_E_CAPACITY, "result buffer holds %llu records, more are pending", (unsigned long long)r->capacity); break; }
 			memcpy(r->records + n * stride, src, stride);
 			++n;
@@ -615,6 +692,7 @@ extern "C" int dbt_kernel_times(dbt_ctx* c, int slot, float ms[8], uint32_t laun
 		const bool all = (c->p.flags & DBT_F_TRACE) || c->rp.nk_max > 255;
 		CU(cudaEventElapsedTime(&ms[KT_CANDIDATE], s.ev[3], s.ev[4])); launches[KT_CANDIDATE] = all ? 0 : 1;
 		CU(cudaEventElapsedTime(&ms[KT_GENERIC], s.ev[4], s.ev[5])); launches[KT_GENERIC] = 1;
+		CU(cudaEventElapsedTime(&ms[KT_THREAD], s.ev[5], s.ev[6])); launches[KT_THREAD] = c->rp.thr_on ? 1 : 0;
 	}
 	return DBT_OK;
 }
@@ -622,7 +700,7 @@ extern "C" int dbt_kernel_times(dbt_ctx* c, int slot, float ms[8], uint32_t laun
 extern "C" int dbt_batch_stats(dbt_ctx* c, int slot, uint64_t stats[4]) {
 	if (!c || !stats) return fail(DBT_E_BADARG, "null argument");
 	if (slot < 0 || slot >= DBT_N_SLOTS) return fail(DBT_E_BADARG, "slot %d out of range", slot);
-	stats[0] = c->slot[slot].last_ncand; stats[1] = c->slot[slot].last_nslow; stats[2] = stats[3] = 0;
+	stats[0] = c->slot[slot].last_ncand; stats[1] = c->slot[slot].last_nslow; stats[2] = c->slot[slot].last_nthr; stats[3] = 0;
 	return DBT_OK;
 }
 

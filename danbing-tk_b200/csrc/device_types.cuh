@@ -26,6 +26,7 @@ struct DevIndex {
 	uint64_t* vote_scratch;     // per-warp epoch-tagged hits arrays [(nloci+1)] (fallback of the smem table)
 	uint32_t* vote_epoch;       // per-warp epoch
 	uint64_t nloci, nk_tr;
+	Table    gtable;            // graphDB of all loci (graph_table.cuh); slots == nullptr when no graph is loaded
 };
 
 struct RunParams {
@@ -52,13 +53,16 @@ struct SlotView {
 	uint32_t* passmask;         // bit per pair: passed subfilter
 	uint32_t* blocksum;         // compaction scratch
 	uint32_t* cand;             // candidate pair ids, ascending
-	uint32_t* ncand;            // [0] = number of candidates, [1] = error flags, [2] = length of slow[]
+	uint32_t* ncand;            // [0] = number of candidates, [1] = error flags, [2] = length of slow[], [3] = length of thr[]
 	uint32_t* slow;             // candidate ordinals left to the generic kernel
+	uint32_t* thr;              // candidate ordinals handed to thread_kernel (ncand[3] entries)
+	uint32_t* thr_dst;          // per candidate ordinal: dst | kf bits << 28 | rm bits << 30
 	uint8_t*  records;
 	unsigned long long* counters;   // DBT_N_COUNTERS
 	uint64_t npairs, first_pair_index;
 };
 
+constexpr int DBT_ST_THREAD_PENDING = 9;       // internal: handed to thread_kernel, which writes the final status
 constexpr uint32_t ERR_RECORD_OVERFLOW = 1u;
 constexpr uint32_t ERR_READ_TOO_LONG   = 2u;
 constexpr uint32_t ERR_INDEX_MISSING   = 4u;   // tr/fl k-mer not in kmers.dbi for its locus

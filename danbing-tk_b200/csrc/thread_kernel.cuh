@@ -1,0 +1,795 @@
+// thread_kernel: restored graph threading (decision D1 of §8(c)).
+// One warp per read pair that passed the locus vote and the QC gate; both mates are threaded through the de Bruijn
+// graph of the assigned locus (isThreadFeasible, cpp:1114-1260), the pair counts if either mate threads, and then
+// every k-mer of BOTH edited k-mer vectors that is a TR k-mer of the locus is incremented (commented caller
+// cpp:2072-2088 / 2195-2209).  "cpp" = src/aQueryFasta_thread.cpp of the reference.
+//
+// How the sequential walk is made parallel.  The reference advances one k-mer at a time, looking the CURRENT node's
+// out-edge mask up and comparing its successors with the next read k-mer (cpp:1167-1180).  Whenever that step is
+// reached the current node equals the previous read k-mer (it was just matched, anchored or corrected), so the
+// outcome of every step is a function of per-position data: the lanes probe the graph table once for ALL k-mers of
+// the read (one 32 B sector each, MAXJ independent probes in flight per lane), classify every position by ballot --
+// M match, N invalid window, H repeat of the previous k-mer (cpp:1152), A first valid k-mer after an N (cpp:1159),
+// E no matching edge -- and the warp then jumps from event to event with find-next-clear scans over the M mask,
+// filling `tr` / `es` for whole runs at once.  Only E events (sequencing errors) enter the correction code:
+//   * errorCorrection_forward/backward (cpp:898-1106): the 3-level graph expansion is 4 + 16 probes taken by
+//     lanes 0-3 / 0-15, the 4x4x4 reachability cube is one 64-bit mask, and the up to 62 extension walks of the
+//     eight edit families run one per lane (two rounds); thread_ext_t::get_edit's scan order is replayed on the
+//     score table (first maximum wins, cpp:628-647);
+//   * edit_kmers_forward/backward (cpp:649-862) -- vector inserts/erases and the CIGAR merge rules -- are literal
+//     and run on lane 0 over the shared-memory copies of kmers / cg.es / cg.tr.
+// After an edit the k-mer vector has changed (up to k rewritten k-mers, +-1 or 2 entries), so all positions are
+// probed and classified again; errors are a few per read, a refresh costs as much as the initial probe round.
+#pragma once
+#include "device_types.cuh"
+#include "graph_table.cuh"
+
+namespace dbt {
+
+constexpr int THR_WARPS = 4;
+constexpr uint64_t THR_MSC = 5;                    // min score for thread extension, cpp:1120
+
+// CIGAR entry codes (include/danbing_b200.h, dbt_aln_mate): type 0 '*' 1 '=' 2 'X' 3 'D' 4 'I'; base 0 none 1-4 ACGT 5 '*'
+enum : uint8_t { ET_STAR = 0, ET_EQ = 1, ET_X = 2, ET_D = 3, ET_I = 4 };
+constexpr uint8_t EG_STAR = 5, ER_INVALID = 6;     // read base that is not ACGT: equals no graph base
+__device__ __forceinline__ bool et_is_edit(uint8_t t) { return t >= ET_X; }
+__device__ __forceinline__ uint8_t eg_comp(uint8_t g) { return (g >= 1 && g <= 4) ? (uint8_t)(5 - g) : (uint8_t)127; }   // baseComplement on characters, h:71-87
+
+template <int MAXJ>
+struct ThreadWarp {
+	static constexpr int CAP = MAXJ * 32;          // k-mer vector / annotation capacity
+	static constexpr int ECAP = MAXJ * 32 + 32;    // CIGAR capacity (read length + deletions)
+	uint64_t km[2][CAP];                           // edited k-mer vectors of both mates (strand-specific, KMER_INVALID = -1)
+	uint32_t trx[2][CAP];                          // count-array position + 1 of each k-mer (0: not a TR k-mer of the locus)
+	uint32_t info[CAP];                            // GNode.bits of the mate being threaded
+	uint32_t cls[6][MAXJ];                         // ballots over positions: M, N, H, A, present, TR
+	uint64_t win[40];                              // k-mer window handed to the edit scorer
+	uint32_t score[64];                            // extension scores of the 62 candidate edits
+	uint8_t  es_t[ECAP], es_r[ECAP], es_g[ECAP];   // cigar_t.es (cpp:53-60)
+	uint8_t  tr[CAP];                              // cigar_t.tr: 0 '*' 1 '.' 2 '='
+	int      sc[12];                               // scalars published by lane 0
+};
+enum { CL_M = 0, CL_N, CL_H, CL_A, CL_P, CL_T };
+
+// lane-0 view of one read's threading state (thr_t of the oracle restatement)
+struct TState {
+	uint64_t* km; uint8_t *es_t, *es_r, *es_g, *tr;
+	int nkm, nes, ntr, ni, err;
+	int cap, ecap;
+	uint32_t k; uint64_t rmask;
+};
+
+struct Txt {                                       // thread_ext_t, cpp:596-625 (the part that outlives the scorer)
+	uint32_t score, nedits;
+	uint8_t et[2], eg[2];
+	uint32_t nm, nd, nins;
+	uint64_t nrk;
+	int a_lo, a_n;                                 // annotation range to fill from the refreshed TR bits
+};
+
+// ---- lane-0 vector primitives (bounds violations = undefined behaviour in the reference -> err) ----
+__device__ __forceinline__ void ts_km_insert(TState& T, int pos, uint64_t v) {
+	if (T.nkm + 1 > T.cap || pos < 0 || pos > T.nkm) { T.err = 1; return; }
+	for (int i = T.nkm; i > pos; --i) T.km[i] = T.km[i - 1];
+	T.km[pos] = v; ++T.nkm;
+}
+__device__ __forceinline__ void ts_km_erase(TState& T, int a, int b) {
+	if (a < 0 || b > T.nkm || a > b) { T.err = 1; return; }
+	for (int i = b; i < T.nkm; ++i) T.km[i - (b - a)] = T.km[i];
+	T.nkm -= (b - a);
+}
+__device__ __forceinline__ void ts_tr_insert(TState& T, int pos, uint8_t v) {
+	if (T.ntr + 1 > T.cap || pos < 0 || pos > T.ntr) { T.err = 1; return; }
+	for (int i = T.ntr; i > pos; --i) T.tr[i] = T.tr[i - 1];
+	T.tr[pos] = v; ++T.ntr;
+}
+__device__ __forceinline__ void ts_tr_erase(TState& T, int a, int b) {
+	if (a < 0 || b > T.ntr || a > b) { T.err = 1; return; }
+	for (int i = b; i < T.ntr; ++i) T.tr[i - (b - a)] = T.tr[i];
+	T.ntr -= (b - a);
+}
+__device__ __forceinline__ void ts_es_insert(TState& T, int pos, uint8_t t, uint8_t r, uint8_t g) {
+	if (T.nes + 1 > T.ecap || pos < 0 || pos > T.nes) { T.err = 1; return; }
+	for (int i = T.nes; i > pos; --i) { T.es_t[i] = T.es_t[i - 1]; T.es_r[i] = T.es_r[i - 1]; T.es_g[i] = T.es_g[i - 1]; }
+	T.es_t[pos] = t; T.es_r[pos] = r; T.es_g[pos] = g; ++T.nes;
+}
+__device__ __forceinline__ void ts_es_erase(TState& T, int pos) {
+	if (pos < 0 || pos >= T.nes) { T.err = 1; return; }
+	for (int i = pos + 1; i < T.nes; ++i) { T.es_t[i - 1] = T.es_t[i]; T.es_r[i - 1] = T.es_r[i]; T.es_g[i - 1] = T.es_g[i]; }
+	--T.nes;
+}
+__device__ __forceinline__ bool ts_es_ok(TState& T, int i) { if (i < 0 || i >= T.nes) { T.err = 1; return false; } return true; }
+__device__ __forceinline__ uint8_t ts_es_type(TState& T, int i) { return ts_es_ok(T, i) ? T.es_t[i] : (uint8_t)ET_EQ; }
+__device__ __forceinline__ uint64_t ts_km(TState& T, int i) { if (i < 0 || i >= T.nkm) { T.err = 1; return KMER_INVALID; } return T.km[i]; }
+
+// thread_ext_t::edit_kmers_forward, cpp:828-862 (lane 0).  The reference snapshots good[]/nts[] of the tail before
+// editing (cpp:829-832); element `dt_nti` of those snapshots is exactly the not-yet-rewritten k-mer that sits at
+// position i when it is consumed (cpp:842-845), so the tail is read in place.
+__device__ __noinline__ void edit_kmers_forward(TState& T, Txt& x, int& ki_io, uint64_t& ncorrection) {
+	const int ksize = (int)T.k;
+	int ki = ki_io;
+	x.nm = x.nd = x.nins = 0;
+	for (uint32_t e = 0; e < x.nedits; ++e) {
+		const uint8_t t = x.et[e];
+		if (t == ET_X)      {                             if (ki < 1 || ki >= T.nkm) { T.err = 1; return; } T.km[ki] = ((T.km[ki-1] & T.rmask) << 2) + (uint64_t)(x.eg[e] - 1); ++ki; ++x.nm; }
+		else if (t == ET_D) { ts_km_insert(T, ki, 0);     if (T.err || ki < 1) { T.err = 1; return; }       T.km[ki] = ((T.km[ki-1] & T.rmask) << 2) + (uint64_t)(x.eg[e] - 1); ++ki; ++x.nd; }
+		else if (t == ET_I) { ts_km_erase(T, ki, ki + 1); if (T.err) return;                                                                                               ++x.nins; }
+	}
+	const int dt_ki = (int)(x.nm + x.nd), dt_km = (int)x.nd - (int)x.nins;
+	for (int i = ki; i < min(T.nkm, ki + ksize); ++i) {
+		if (T.km[i] == KMER_INVALID) break;
+		T.km[i] = ((T.km[i-1] & T.rmask) << 2) + (T.km[i] & 3);
+	}
+	if (dt_km > 0) { for (int i = 0; i < dt_km; ++i) ts_tr_insert(T, T.ntr, 0); }          // cg.tr.resize(size + dt_km, '*')
+	else if (dt_km < 0) { ts_tr_erase(T, T.ntr + dt_km, T.ntr); }
+	for (uint32_t i = 0; i < x.nd; ++i) ts_es_insert(T, T.ni + ksize - 1 + (int)x.nm, ET_D, 0, EG_STAR);
+	x.a_lo = ki - dt_ki; x.a_n = dt_ki + (int)x.score;
+	if (x.a_lo < 0 || x.a_lo + x.a_n > T.ntr || x.a_lo + x.a_n > T.nkm) { T.err = 1; return; }
+	for (uint32_t i = 0; i < x.nedits; ++i, ++T.ni) {
+		const int q = T.ni + ksize - 1;
+		if (!ts_es_ok(T, q)) return;
+		T.es_t[q] = x.et[i]; T.es_g[q] = x.eg[i];
+	}
+	for (uint32_t i = 0; i < x.score; ++i, ++T.ni) {
+		const int q = T.ni + ksize - 1;
+		if (!ts_es_ok(T, q)) return;
+		T.es_t[q] = ET_EQ;
+	}
+	--T.ni;
+	ki += (int)x.score - 1;
+	ncorrection += x.nedits;
+	ki_io = ki;
+}
+
+// thread_ext_t::edit_kmers_backward, cpp:649-826 (lane 0).  good[]/nts[] (cpp:651-656) are read in place for the
+// same reason as above: position i-1 is still the original prefix k-mer when cpp:683-686 rewrites it.
+__device__ __noinline__ void edit_kmers_backward(TState& T, Txt& x, int& ki_io, uint64_t& ncorrection, uint64_t& nskip) {
+	const int ksize = (int)T.k;
+	int ki = ki_io;
+	const uint64_t lmask = 3ull << 2 * (ksize - 1), lbase = 1ull << 2 * (ksize - 1);
+	x.nm = x.nd = x.nins = 0; x.nrk = 0;
+	for (uint32_t e = 0; e < x.nedits; ++e) { const uint8_t t = x.et[e]; if (t == ET_X) ++x.nm; else if (t == ET_D) ++x.nd; else if (t == ET_I) ++x.nins; }
+	const int dt_km = (int)x.nd - (int)x.nins;
+	T.ni += (int)x.nd;
+	if (dt_km > 0) { for (int i = 0; i < dt_km; ++i) { ts_km_insert(T, ki, 0); ts_tr_insert(T, ki, 0); } }
+	else if (dt_km < 0) { ts_km_erase(T, ki + dt_km, ki); ts_tr_erase(T, ki + dt_km, ki); }
+	if (T.err) return;
+	ki += dt_km;
+	int ki_ = ki;
+	for (uint32_t e = 0; e < x.nedits; ++e) {                       // corrected k-mers, cpp:679-681
+		if (x.et[e] == ET_X || x.et[e] == ET_D) {
+			if (ki_ - 1 < 0 || ki_ >= T.nkm) { T.err = 1; return; }
+			T.km[ki_-1] = (T.km[ki_] >> 2) + (uint64_t)(3 - (x.eg[e] - 1)) * lbase;   // baseComplement[baseNumConversion[e.g]]
+			--ki_;
+		}
+	}
+	for (int i = ki_; i > max(0, ki_ - ksize); --i) {               // extended k-mers, cpp:683-686
+		if (T.km[i-1] == KMER_INVALID) break;
+		T.km[i-1] = (T.km[i] >> 2) + (T.km[i-1] & lmask);
+	}
+	const int lb = ki - (int)x.nm - (int)x.nd - (int)x.score;
+	if (lb < 0 || ki > T.ntr) { T.err = 1; return; }
+	for (int i = ki - 1; i >= lb; --i) if (T.tr[i] == 0) ++x.nrk;   // tr values themselves come from the refreshed TR bits
+	x.a_lo = lb; x.a_n = ki - lb;
+	x.nrk -= (x.nm + x.nd);
+	nskip -= x.nrk;
+	ncorrection += x.nedits;
+	{	// CIGAR, cpp:696-823
+		int cni = 0;
+		const int nti_ = ki - dt_km;
+		for (int i = 0; i < nti_ + cni; ++i) if (ts_es_type(T, i) == ET_I) ++cni;
+		int nti = nti_ + cni - 1;
+		for (uint32_t i = 0; i < x.nedits; ++i, --nti) {
+			const uint8_t t1 = x.et[i], g1 = x.eg[i];
+			if (t1 == ET_D) { ++nti; ts_es_insert(T, nti, ET_D, 0, EG_STAR); }
+			if (!ts_es_ok(T, nti)) return;
+			if (T.es_t[nti] == ET_D) {
+				if (t1 == ET_I) { ts_es_erase(T, nti); --T.ni; }
+				else T.es_g[nti] = eg_comp(g1);
+			} else {
+				while (ts_es_type(T, nti) == ET_I && !T.err) --nti;
+				if (!ts_es_ok(T, nti)) return;
+				T.es_t[nti] = t1;
+				T.es_g[nti] = g1 ? eg_comp(g1) : (uint8_t)0;
+			}
+		}
+		int e0 = nti + 1, e1 = e0;
+		for (uint32_t i = 0; i < x.score; ++i, --nti) {
+			const uint8_t t = ts_es_type(T, nti);
+			if (T.err) return;
+			if (t == ET_EQ) { }
+			else if (t == ET_STAR) T.es_t[nti] = ET_EQ;
+			else break;
+		}
+		{	// find the edit tract
+			uint8_t t = ts_es_type(T, e1);
+			while (et_is_edit(t) && !T.err) { ++e1; t = ts_es_type(T, e1); }
+			t = ts_es_type(T, e0 - 1);
+			while (et_is_edit(t) && !T.err) { --e0; t = ts_es_type(T, e0 - 1); }
+			if (T.err) return;
+		}
+		// merge edits if possible: rnts / gnts = the non-empty read / graph bases of the tract, in order
+		int nets = e1 - e0, nr = 0, ng = 0;
+		for (int i = e0; i < e1; ++i) { if (T.es_r[i]) ++nr; if (T.es_g[i]) ++ng; }
+		auto nth = [&](const uint8_t* a, int n) -> uint8_t {         // n-th non-empty base of the tract (as it was BEFORE the rewrite below)
+			for (int i = e0; i < e1; ++i) if (a[i]) { if (n == 0) return a[i]; --n; }
+			return 0;
+		};
+		if (nr == ng) {
+			bool no_edit = true;
+			{ int i = e0, j = e0;
+			  for (int q = 0; q < nr; ++q) { while (!T.es_r[i]) ++i; while (!T.es_g[j]) ++j; if (T.es_r[i] != T.es_g[j]) { no_edit = false; break; } ++i; ++j; } }
+			if (no_edit) {                                            // edits cancelled out, cpp:755-770
+				int dt_es = 0;
+				for (int i = e0; i < e1; ++i) {
+					const int q = i + dt_es;
+					if (!ts_es_ok(T, q)) return;
+					if (T.es_t[q] == ET_D) { ts_es_erase(T, q); --dt_es; }
+					else { T.es_t[q] = ET_EQ; T.es_g[q] = 0; }
+				}
+				T.ni += dt_es;
+				ncorrection -= (uint64_t)(e1 - e0);
+				nskip -= (uint64_t)(e1 - e0);
+			} else if (nets != nr) {                                  // D+I at one position -> X, cpp:772-798
+				// snapshot the base lists: the loop below rewrites the tract while consuming them
+				uint8_t rn[48], gn[48];
+				if (nr > 48) { T.err = 1; return; }
+				for (int q = 0; q < nr; ++q) { rn[q] = nth(T.es_r, q); gn[q] = nth(T.es_g, q); }
+				int dt_es = 0;
+				const int dt_es_ = nr - nets;
+				int j = 0, kk = 0;
+				for (int i = e0; i < e1; ++i) {
+					const int q = i + dt_es;
+					if (!ts_es_ok(T, q)) return;
+					if (T.es_t[q] == ET_D && dt_es != dt_es_) { ts_es_erase(T, q); --dt_es; }
+					else {
+						if (kk >= nr || j >= ng) { T.err = 1; return; }
+						if (rn[kk] == gn[kk]) { T.es_t[q] = ET_EQ; T.es_g[q] = 0; }
+						else { T.es_t[q] = ET_X; T.es_g[q] = gn[j]; }
+						++j; ++kk;
+					}
+				}
+				if (dt_es != dt_es_) { T.err = 1; return; }               // assert, cpp:794
+				T.ni += dt_es;
+				ncorrection += (uint64_t)(int64_t)dt_es;
+				nskip += (uint64_t)(int64_t)dt_es;
+			} else {                                                  // match / mismatch only, cpp:799-809: every entry has both bases
+				for (int i = 0; i < nr; ++i) {
+					const int q = e0 + i;
+					if (T.es_r[q] == T.es_g[q]) { T.es_t[q] = ET_EQ; T.es_g[q] = 0; --ncorrection; --nskip; }
+				}
+			}
+		} else {                                                      // cpp:812-822
+			for (int i = 0; i < nets; ++i) {
+				const int q = e0 + i;
+				if (T.es_r[q] == T.es_g[q]) { T.es_t[q] = ET_EQ; T.es_g[q] = 0; --ncorrection; --nskip; }
+			}
+		}
+	}
+	ki_io = ki;
+}
+
+// ---- warp-parallel edit scorer: errorCorrection_forward, cpp:898-1089 ----
+// W.win[j+1] holds kmers[ki+j] for j = -1 .. k+1 (KMER_INVALID beyond the vector), nrem = nkmers - ki.
+// Returns (warp-uniform) true when an edit was found; x.et/eg/score/nedits describe it.  err |= graph not closed.
+template <int B, int MAXJ>
+__device__ __noinline__ bool ec_score(const Table& gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ>& W,
+                                      uint32_t nrem, uint32_t mes, int lane, Txt& x, int& err) {
+	const uint64_t node = W.win[0];
+	// nts0 / nnds: getOutNodes(g, node), cpp:1170 / 1097
+	const GNode g0 = g_lookup<B>(gt, node, locus, K);
+	if (!(g0.bits & GN_PRESENT)) err = 1;
+	const uint32_t nts0 = gn_mask(g0.bits);
+	// level 1 (lanes 0-3) and level 2 (lanes 0-15) of the expansion, cpp:907-920
+	uint32_t m1 = 0; uint64_t n1 = 0; bool bad = false;
+	if (lane < 4 && ((nts0 >> lane) & 1u)) {
+		n1 = ((node & rmask) << 2) + (uint64_t)lane;
+		const GNode g = g_lookup<B>(gt, n1, locus, K);
+		if (!(g.bits & GN_PRESENT)) bad = true;
+		m1 = gn_mask(g.bits);
+	}
+	const uint32_t nts1 = __reduce_or_sync(0xffffffffu, m1);
+	uint32_t m2 = 0;
+	{
+		const int i = (lane >> 2) & 3, j = lane & 3;
+		const uint32_t m1i = __shfl_sync(0xffffffffu, m1, i);
+		if (lane < 16 && ((nts0 >> i) & 1u) && ((m1i >> j) & 1u)) {
+			const uint64_t n1i = ((node & rmask) << 2) + (uint64_t)i;
+			const uint64_t n2 = ((n1i & rmask) << 2) + (uint64_t)j;
+			const GNode g = g_lookup<B>(gt, n2, locus, K);
+			if (!(g.bits & GN_PRESENT)) bad = true;
+			m2 = gn_mask(g.bits);
+		}
+	}
+	if (__any_sync(0xffffffffu, bad)) err = 1;
+	const uint32_t nts2 = __reduce_or_sync(0xffffffffu, m2);
+	const uint32_t mlo = __reduce_or_sync(0xffffffffu, lane < 8 ? (m2 << (4 * lane)) : 0u);
+	const uint32_t mhi = __reduce_or_sync(0xffffffffu, (lane >= 8 && lane < 16) ? (m2 << (4 * (lane - 8))) : 0u);
+	const uint64_t mat = ((uint64_t)mhi << 32) | mlo;                 // bit nt0*16 + nt1*4 + nt2, graph_triplet_t cpp:865-875
+	auto nnts2 = [&](uint32_t i, uint32_t j) -> uint32_t { return (uint32_t)(mat >> (i * 16 + j * 4)) & 0xFu; };
+	auto nnts1 = [&](uint32_t i) -> uint32_t { uint32_t r = 0; for (uint32_t j = 0; j < 4; ++j) if (nnts2(i, j)) r |= 1u << j; return r; };
+
+	const uint32_t gl = nrem < K + 2 ? nrem : K + 2;                  // good[j], cpp:922-923
+	auto good = [&](uint32_t j) -> bool { return j < gl && W.win[j + 1] != KMER_INVALID; };
+	const uint64_t w1 = W.win[1], w2 = W.win[2], w3 = W.win[3];
+	const uint32_t oldnt = (uint32_t)(w1 & 3);
+	const bool g0k = good(0), g1k = good(1), g2k = good(2);
+	// family pre-conditions; the reference reads kmers[ki+j] % 4 before good[j], device code guards first
+	const bool c_m1 = g1k && ((nts1 >> (w2 & 3)) & 1u);
+	const bool c_m2 = !c_m1 && g2k && ((nts2 >> (w3 & 3)) & 1u) && mes >= 2;       // else-if, cpp:944
+	const bool c_mi = g2k && ((nts1 >> (w3 & 3)) & 1u) && mes >= 2;
+	const bool c_md = g1k && ((nts2 >> (w2 & 3)) & 1u) && mes >= 2;
+	const bool c_i1 = g1k && ((nts0 >> (w2 & 3)) & 1u);
+	const bool c_d1 = g0k && ((nts1 >> (w1 & 3)) & 1u);
+	const bool c_i2 = g2k && ((nts0 >> (w3 & 3)) & 1u) && mes >= 2;
+	const bool c_d2 = g0k && ((nts2 >> (w1 & 3)) & 1u) && mes >= 2;
+	const uint32_t e1 = nrem < K + 1 ? nrem : K + 1, e2 = nrem < K + 2 ? nrem : K + 2, e0 = nrem < K ? nrem : K;
+
+	// score slots in get_edit's scan order families: [0,4) nem1, [4,8) ned1, 8 nei1, [9,25) nem2, [25,41) nemd, [41,57) ned2, [57,61) nemi, 61 nei2
+#pragma unroll 1
+	for (int round = 0; round < 2; ++round) {
+		const uint32_t w = (uint32_t)lane + 32u * round;
+		bool act = false; uint64_t cr = 0; uint32_t nn = 0, jb = 0, je = 0;
+		if (w < 4)        { const uint32_t a = w;      act = c_m1 && ((nts0 >> a) & 1u); cr = w1 - oldnt + a; nn = nnts1(a); jb = 1; je = e1; }
+		else if (w < 8)   { const uint32_t a = w - 4;  act = c_d1 && ((nts0 >> a) & 1u); cr = w1 - oldnt + a; nn = nnts1(a); jb = 0; je = e0; }
+		else if (w == 8)  { act = c_i1; cr = node; nn = nts0; jb = 1; je = e1; }
+		else if (w < 57)  {
+			const uint32_t f = (w - 9) >> 4, q = (w - 9) & 15, a = q >> 2, b = q & 3;
+			const bool c = f == 0 ? c_m2 : (f == 1 ? c_md : c_d2);
+			act = c && ((nts0 >> a) & 1u) && ((nnts1(a) >> b) & 1u);
+			cr = (((w1 - oldnt + a) & rmask) << 2) + b; nn = nnts2(a, b);
+			jb = f == 0 ? 2 : (f == 1 ? 1 : 0); je = f == 0 ? e2 : (f == 1 ? e1 : e0);
+		}
+		else if (w < 61)  { const uint32_t a = w - 57; act = c_mi && ((nts0 >> a) & 1u); cr = w1 - oldnt + a; nn = nnts1(a); jb = 2; je = e2; }
+		else if (w == 61) { act = c_i2; cr = node; nn = nts0; jb = 2; je = e2; }
+		uint32_t n = 0;
+		if (act) {                                                    // extension walk, cpp:931-940 and siblings
+			for (uint32_t j = jb; j < je; ++j) {
+				if (!good(j)) break;
+				cr = ((cr & rmask) << 2) + (W.win[j + 1] & 3);
+				if (!((nn >> (cr & 3)) & 1u)) break;
+				++n;
+				const GNode g = g_lookup<B>(gt, cr, locus, K);          // getNextNucs, cpp:547-557: assigns only when the node exists
+				if (g.bits & GN_PRESENT) nn = gn_mask(g.bits);
+			}
+		}
+		if (w < 64) W.score[w] = n;
+	}
+	__syncwarp();
+	// thread_ext_t::get_edit, cpp:628-647 (every lane replays the same scan)
+	uint32_t best = 0, bw = 0xFFu;
+	const uint32_t ms1 = (uint32_t)THR_MSC, ms2 = 2 * (uint32_t)THR_MSC;
+	for (uint32_t w = 0; w < 9; ++w) { const uint32_t s = W.score[w]; if (s > best && s >= ms1) { best = s; bw = w; } }
+	if (mes > 1) {
+		for (uint32_t i = 0; i < 4; ++i) {
+			for (uint32_t j = 0; j < 4; ++j) {
+				for (uint32_t f = 0; f < 3; ++f) { const uint32_t w = 9 + 16 * f + 4 * i + j, s = W.score[w]; if (s > best && s >= ms2) { best = s; bw = w; } }
+			}
+			{ const uint32_t w = 57 + i, s = W.score[w]; if (s > best && s >= ms2) { best = s; bw = w; } }
+		}
+		{ const uint32_t s = W.score[61]; if (s > best && s >= ms2) { best = s; bw = 61; } }
+	}
+	__syncwarp();
+	x.score = best; x.nedits = 0;
+	if (best == 0) return false;
+	if (bw < 4)        { x.nedits = 1; x.et[0] = ET_X; x.eg[0] = (uint8_t)(bw + 1); }
+	else if (bw < 8)   { x.nedits = 1; x.et[0] = ET_D; x.eg[0] = (uint8_t)(bw - 4 + 1); }
+	else if (bw == 8)  { x.nedits = 1; x.et[0] = ET_I; x.eg[0] = 0; }
+	else if (bw < 57)  {
+		const uint32_t f = (bw - 9) >> 4, q = (bw - 9) & 15;
+		x.nedits = 2;
+		x.et[0] = f == 2 ? ET_D : ET_X; x.eg[0] = (uint8_t)((q >> 2) + 1);
+		x.et[1] = f == 0 ? ET_X : ET_D; x.eg[1] = (uint8_t)((q & 3) + 1);
+	}
+	else if (bw < 61)  { x.nedits = 2; x.et[0] = ET_X; x.eg[0] = (uint8_t)(bw - 57 + 1); x.et[1] = ET_I; x.eg[1] = 0; }
+	else               { x.nedits = 2; x.et[0] = ET_I; x.eg[0] = 0; x.et[1] = ET_I; x.eg[1] = 0; }
+	return true;
+}
+
+// ---- per-position probes + classification (the parallel replacement of the node-by-node walk) ----
+template <int B, int MAXJ>
+__device__ __forceinline__ void thr_refresh(const Table& gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ>& W,
+                                            int m, int nkm, int lane) {
+	__syncwarp();
+	constexpr int CH = 4;                                             // probes in flight per lane
+#pragma unroll 1
+	for (int j0 = 0; j0 < MAXJ; j0 += CH) {
+		uint4 s[CH][B]; uint64_t canon[CH]; bool isrc[CH], valid[CH];
+#pragma unroll
+		for (int c = 0; c < CH; ++c) {
+			const int i = (j0 + c) * 32 + lane;
+			valid[c] = (j0 + c) < MAXJ && i < nkm && W.km[m][i] != KMER_INVALID;
+			canon[c] = 0; isrc[c] = false;
+			if (valid[c]) {
+				const uint64_t fw = W.km[m][i], rc = kmer_rc(fw, K);
+				isrc[c] = rc < fw; canon[c] = isrc[c] ? rc : fw;
+				const uint4* bp = gt.slots + home_bucket(gt, g_hash_key(canon[c], locus)) * B;
+#pragma unroll
+				for (int q = 0; q < B; ++q) s[c][q] = ldg128(bp + q);
+			}
+		}
+#pragma unroll
+		for (int c = 0; c < CH; ++c) {
+			if ((j0 + c) >= MAXJ) continue;
+			const int i = (j0 + c) * 32 + lane;
+			uint32_t bits = 0, trp = 0;
+			if (valid[c]) {
+				bool full = true, found = false;
+#pragma unroll
+				for (int q = 0; q < B; ++q) {
+					const uint64_t kk = slot_key(s[c][q]);
+					if (kk == SLOT_EMPTY) full = false;
+					else if ((kk & SLOT_KEYMASK) == canon[c] && (s[c][q].z & G_LOCUS_MASK) == locus) {
+						const GNode n = g_decode(s[c][q].z, s[c][q].w, isrc[c]); bits = n.bits; trp = n.tr; found = true;
+					}
+				}
+				if (!found && full && (slot_key(s[c][0]) & SLOT_OVF)) {   // continues in the stash: rare
+					const GNode n = g_lookup<B>(gt, W.km[m][i], locus, K); bits = n.bits; trp = n.tr;
+				}
+			}
+			W.info[i] = bits; W.trx[m][i] = trp;
+		}
+	}
+	__syncwarp();
+#pragma unroll 1
+	for (int j = 0; j < MAXJ; ++j) {
+		const int i = j * 32 + lane;
+		const bool in = i < nkm;
+		const uint64_t f = in ? W.km[m][i] : KMER_INVALID;
+		const uint64_t pv = (in && i > 0) ? W.km[m][i - 1] : KMER_INVALID;
+		const uint32_t bi = in ? W.info[i] : 0u, bp = (in && i > 0) ? W.info[i - 1] : 0u;
+		const bool valid = in && f != KMER_INVALID;
+		const bool isN = in && f == KMER_INVALID;
+		const bool isH = valid && i > 0 && f == pv;                      // cpp:1152 (the N test comes first, cpp:1145)
+		const bool isA = valid && i > 0 && pv == KMER_INVALID;           // cpp:1159
+		const bool isM = valid && i > 0 && pv != KMER_INVALID && f != pv && (((pv & rmask) << 2) + (f & 3)) == f
+		                 && (bp & GN_PRESENT) && ((gn_mask(bp) >> (f & 3)) & 1u);   // cpp:1170-1178 with node == kmers[ki-1]
+		const uint32_t bm = __ballot_sync(0xffffffffu, isM), bn = __ballot_sync(0xffffffffu, isN), bh = __ballot_sync(0xffffffffu, isH);
+		const uint32_t ba = __ballot_sync(0xffffffffu, isA), bpz = __ballot_sync(0xffffffffu, valid && (bi & GN_PRESENT));
+		const uint32_t bt = __ballot_sync(0xffffffffu, valid && (bi & GN_TR));
+		if (lane == 0) { W.cls[CL_M][j] = bm; W.cls[CL_N][j] = bn; W.cls[CL_H][j] = bh; W.cls[CL_A][j] = ba; W.cls[CL_P][j] = bpz; W.cls[CL_T][j] = bt; }
+	}
+	__syncwarp();
+}
+
+// first position >= from whose bit in mask words w[] equals `want`, or n
+template <int MAXJ>
+__device__ __forceinline__ int thr_next(const uint32_t* w, int from, int n, bool want) {
+	if (from >= n) return n;
+	int j = from >> 5;
+	uint32_t v = (want ? w[j] : ~w[j]) & (0xFFFFFFFFu << (from & 31));
+	while (true) {
+		if (v) { const int p = j * 32 + __ffs(v) - 1; return p < n ? p : n; }
+		if (++j >= MAXJ || j * 32 >= n) return n;
+		v = want ? w[j] : ~w[j];
+	}
+}
+template <int MAXJ>
+__device__ __forceinline__ bool thr_bit(const uint32_t* w, int i) { return (w[i >> 5] >> (i & 31)) & 1u; }
+
+struct MateResult { int alned, err, nkm, nes, ntr; };
+
+// isThreadFeasible, cpp:1114-1260, for mate m of the pair held by warp state W.  Warp-uniform.
+template <int B, int MAXJ>
+__device__ __noinline__ MateResult thread_mate(const Table& gt, uint32_t locus, const RunParams& rp, ThreadWarp<MAXJ>& W, int m,
+                                               const uint64_t* __restrict__ rec, uint32_t len, int lane) {
+	constexpr int CAP = ThreadWarp<MAXJ>::CAP, ECAP = ThreadWarp<MAXJ>::ECAP;
+	const uint32_t K = rp.k;
+	const uint64_t rmask = (1ull << 2 * (K - 1)) - 1;
+	const uint64_t maxnc = rp.max_ncorrection;
+	const bool correction = rp.correction != 0;
+	MateResult R; R.alned = 0; R.err = 0;
+	int nkm = (int)len - (int)K + 1, nes = (int)len, ntr = nkm, ni = 0, err = 0;
+	if (nkm < 1 || nkm > CAP || nes > ECAP) { R.err = 1; R.nkm = 0; R.nes = 0; R.ntr = 0; return R; }
+	// cigar_t::init (cpp:62-67) and read2kmers(.., canonical=false, keepN=true) (h:246-271)
+	__syncwarp();
+	bool anyvalid = false;
+	for (int i = lane; i < nes; i += 32) {
+		const uint32_t code = (uint32_t)(rec[i >> 5] >> (2 * (i & 31))) & 3u;
+		const bool inv = (rec[rp.lay.WB + (i >> 6)] >> (i & 63)) & 1ull;
+		W.es_t[i] = ET_STAR; W.es_r[i] = inv ? ER_INVALID : (uint8_t)(code + 1); W.es_g[i] = 0;
+	}
+	for (int i = lane; i < nkm; i += 32) {
+		uint64_t f = KMER_INVALID;
+		if (extract_bits(rec + rp.lay.WB, (uint32_t)i, K) == 0) { f = rev2(extract_bits(rec, 2u * i, 2 * K)) >> (64 - 2 * K); anyvalid = true; }
+		W.km[m][i] = f; W.tr[i] = 0;
+	}
+	anyvalid = __any_sync(0xffffffffu, anyvalid);
+	__syncwarp();
+	if (!anyvalid) { R.nkm = 0; R.nes = nes; R.ntr = ntr; return R; }     // D1: a read without a valid k-mer is not threadable (cpp:1124 would be UB)
+	thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, nkm, lane);
+
+	const uint64_t nkm0 = (uint64_t)nkm;
+	const uint64_t maxnskip = nkm0 >= rp.thread_cth ? nkm0 - rp.thread_cth : 0;
+	int ki = 0;
+	uint64_t nskip = 0, ncorr = 0;
+	Txt x; x.score = 0; x.nedits = 0; x.nm = x.nd = x.nins = 0; x.nrk = 0; x.a_lo = 0; x.a_n = 0;
+	int result = -1;                                                   // -1: fall through to the final test (cpp:1259)
+
+	auto find_anchor = [&]() -> bool {                                  // cpp:878-888
+		const int a = thr_next<MAXJ>(W.cls[CL_P], ki, nkm, true);
+		nskip += (uint64_t)(a - ki); ni += a - ki; ki = a;
+		if (a >= nkm) return false;
+		if (lane == 0) W.tr[ki] = thr_bit<MAXJ>(W.cls[CL_T], ki) ? 2 : 1;
+		if (ni < 0 || ni + (int)K > nes) err = 1;
+		else for (int q = lane; q < (int)K; q += 32) if (W.es_t[ni + q] == ET_STAR) W.es_t[ni + q] = ET_EQ;
+		__syncwarp();
+		return true;
+	};
+	auto score_at = [&](bool backward, int kk, uint32_t mes) -> bool {  // errorCorrection_forward / _backward
+		__syncwarp();
+		uint32_t nrem;
+		if (!backward) {
+			nrem = (uint32_t)(nkm - kk);
+			for (int q = lane; q < (int)K + 3; q += 32) { const int i = kk - 1 + q; W.win[q] = (i >= 0 && i < nkm) ? W.km[m][i] : KMER_INVALID; }
+		} else {                                                         // kmers_rc, cpp:1098-1103
+			nrem = (uint32_t)kk;
+			for (int q = lane; q < (int)K + 3; q += 32) {
+				const int i = kk - q;
+				uint64_t v = KMER_INVALID;
+				if (i >= 0 && i < nkm && W.km[m][i] != KMER_INVALID) v = kmer_rc(W.km[m][i], K);
+				W.win[q] = v;
+			}
+		}
+		__syncwarp();
+		return ec_score<B, MAXJ>(gt, locus, K, rmask, W, nrem, mes, lane, x, err);
+	};
+	auto apply = [&](bool backward, int& kk) {                           // edit_kmers_forward / _backward on lane 0, then re-probe
+		__syncwarp();
+		if (lane == 0) {
+			TState T; T.km = W.km[m]; T.es_t = W.es_t; T.es_r = W.es_r; T.es_g = W.es_g; T.tr = W.tr;
+			T.nkm = nkm; T.nes = nes; T.ntr = ntr; T.ni = ni; T.err = err; T.cap = CAP; T.ecap = ECAP; T.k = K; T.rmask = rmask;
+			if (backward) edit_kmers_backward(T, x, kk, ncorr, nskip); else edit_kmers_forward(T, x, kk, ncorr);
+			nkm = T.nkm; nes = T.nes; ntr = T.ntr; ni = T.ni; err = T.err;
+		}
+		nkm = __shfl_sync(0xffffffffu, nkm, 0); nes = __shfl_sync(0xffffffffu, nes, 0); ntr = __shfl_sync(0xffffffffu, ntr, 0);
+		ni = __shfl_sync(0xffffffffu, ni, 0); err = __shfl_sync(0xffffffffu, err, 0); kk = __shfl_sync(0xffffffffu, kk, 0);
+		ncorr = __shfl_sync(0xffffffffu, ncorr, 0); nskip = __shfl_sync(0xffffffffu, nskip, 0);
+		x.nm = __shfl_sync(0xffffffffu, x.nm, 0); x.nd = __shfl_sync(0xffffffffu, x.nd, 0); x.nins = __shfl_sync(0xffffffffu, x.nins, 0);
+		x.a_lo = __shfl_sync(0xffffffffu, x.a_lo, 0); x.a_n = __shfl_sync(0xffffffffu, x.a_n, 0);
+		thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, nkm, lane);
+		if (!err) for (int q = lane; q < x.a_n; q += 32) W.tr[x.a_lo + q] = thr_bit<MAXJ>(W.cls[CL_T], x.a_lo + q) ? 2 : 1;   // cpp:850 / 690
+		__syncwarp();
+	};
+
+	if (!find_anchor()) result = 0;                                     // cpp:1129
+	else if (ki > 0 && correction && ncorr < maxnc && (uint64_t)ki >= THR_MSC + 1) {   // leading unaligned k-mers, cpp:1131-1141
+		const uint32_t mes = ((uint64_t)ki >= 2 * THR_MSC + 2) ? 2 : 1;
+		if (score_at(true, ki, mes)) apply(true, ki);
+	}
+	if (result < 0) { ++ki; ++ni; }
+	while (result < 0 && ki < nkm && !err) {                            // cpp:1144
+		{	// run of matching k-mers: cpp:1167-1180 for every position at once
+			const int e = thr_next<MAXJ>(W.cls[CL_M], ki, nkm, false);
+			if (e > ki) {
+				const int d = ni - ki + (int)K - 1;
+				if (d < 0 || e - 1 + d >= nes || e > ntr) { err = 1; break; }
+				for (int i = ki + lane; i < e; i += 32) { W.tr[i] = thr_bit<MAXJ>(W.cls[CL_T], i) ? 2 : 1; W.es_t[i + d] = ET_EQ; }
+				__syncwarp();
+				ni += e - ki; ki = e;
+			}
+			if (ki >= nkm) break;
+		}
+		if (thr_bit<MAXJ>(W.cls[CL_N], ki) || thr_bit<MAXJ>(W.cls[CL_H], ki)) {    // "N" in read / homopolymer run, cpp:1145-1158
+			int e = ki;
+			while (e < nkm && (thr_bit<MAXJ>(W.cls[CL_N], e) || thr_bit<MAXJ>(W.cls[CL_H], e))) ++e;
+			const uint64_t run = (uint64_t)(e - ki);
+			const uint64_t take = nskip > maxnskip ? 1 : (run < maxnskip - nskip + 1 ? run : maxnskip - nskip + 1);
+			const int d = ni - ki + (int)K - 1;
+			if (d < 0 || ki + (int)take - 1 + d >= nes || ki + (int)take > ntr) { err = 1; break; }
+			for (int i = ki + lane; i < ki + (int)take; i += 32) { W.tr[i] = 0; W.es_t[i + d] = ET_STAR; }
+			__syncwarp();
+			nskip += take;
+			if (nskip > maxnskip) { result = 0; break; }
+			ki += (int)take; ni += (int)take;
+			continue;
+		}
+		if (thr_bit<MAXJ>(W.cls[CL_A], ki)) {                               // after an N, cpp:1159-1165
+			if (!find_anchor()) break;
+			if (nskip > maxnskip) { result = 0; break; }
+			++ki; ++ni; continue;
+		}
+		// no matching node: error correction, cpp:1181-1257
+		if ((uint64_t)ki + THR_MSC >= nkm0) {                               // not enough info, cpp:1182-1185
+			nskip += (nkm0 - (uint64_t)ki);
+			result = nskip <= maxnskip ? (ncorr ? 2 : 1) : 0;
+			break;
+		}
+		if (correction && ncorr < maxnc) {
+			uint32_t mes = ((uint64_t)(nkm - ki) >= 2 * THR_MSC + 2) ? 2 : 1;
+			if (score_at(false, ki, mes)) {                                   // cpp:1192-1197
+				nskip += x.nedits;
+				if (nskip > maxnskip) { result = 0; break; }
+				apply(false, ki);
+			} else {                                                          // cpp:1198-1248
+				if (!find_anchor()) break;
+				bool skip = !score_at(true, ki, 2);
+				if (!skip) {
+					apply(true, ki);
+					++ncorr;
+					int64_t gap = (int64_t)min((int64_t)K, (int64_t)ki - (int64_t)x.nm - (int64_t)x.nd) - (int64_t)x.score;
+					int64_t ki1 = ki;
+					if (gap < 0) err = 1;
+					while (!skip && gap && !err) {                                // forward and backward threads not fully patched
+						const int64_t ki0 = ki1;
+						ki1 = ki0 - (int64_t)x.nm - (int64_t)x.nd - (int64_t)x.score;
+						if (ki1 < 0) { err = 1; break; }
+						mes = ((uint64_t)ki1 >= 2 * THR_MSC + 2) ? 2 : 1;
+						if ((uint64_t)ki1 < THR_MSC + 1) break;
+						if (ki1 >= nkm || !thr_bit<MAXJ>(W.cls[CL_P], (int)ki1)) { err = 1; break; }   // assert(g.count(node_)), cpp:1222
+						skip = !score_at(true, (int)ki1, mes);
+						if (!skip) {
+							int k1 = (int)ki1;
+							apply(true, k1);
+							ki1 = k1;
+							ki += (int)x.nd - (int)x.nins;
+							gap = (int64_t)min((int64_t)K, ki1 - (int64_t)x.nm - (int64_t)x.nd) - (int64_t)x.score;
+							if (gap < 0) err = 1;
+						}
+					}
+					if (gap > 0 && !err) {                                          // annot_gap, cpp:1108-1111
+						if (ki1 - gap < 0 || ki1 > ntr) err = 1;
+						else { for (int q = lane; q < (int)gap; q += 32) W.tr[ki1 - 1 - q] = 0; __syncwarp(); }
+						nskip -= (uint64_t)gap;
+					}
+					if (nskip > maxnskip) { result = 0; break; }
+				}
+				if (skip) {                                                       // cpp:1234-1243
+					if (!find_anchor()) break;
+					if (nskip > maxnskip) { result = 0; break; }
+					++ki; ++ni; continue;
+				}
+			}
+		} else {                                                              // cpp:1250-1256
+			if (!find_anchor()) break;
+			if (nskip > maxnskip) { result = 0; break; }
+			++ki; ++ni; continue;
+		}
+		++ki; ++ni;
+	}
+	if (result < 0) result = (nskip <= maxnskip && ncorr <= maxnc) ? (ncorr ? 2 : 1) : 0;   // cpp:1259
+	if (err) result = 0;
+	R.alned = result; R.err = err; R.nkm = nkm; R.nes = nes; R.ntr = ntr;
+	return R;
+}
+
+constexpr uint32_t THR_DST_MASK = (1u << G_LOCUS_BITS) - 1;           // sv.thr_dst[c] = dst | kf bits << 28 | rm bits << 30
+
+template <int B, int MAXJ>
+__global__ void __launch_bounds__(THR_WARPS * 32) thread_kernel(DevIndex ix, RunParams rp, SlotView sv) {
+	extern __shared__ __align__(16) uint8_t thr_smem[];
+	ThreadWarp<MAXJ>& W = reinterpret_cast<ThreadWarp<MAXJ>*>(thr_smem)[threadIdx.x >> 5];
+	const int lane = threadIdx.x & 31;
+	const uint32_t gwarp = blockIdx.x * THR_WARPS + (threadIdx.x >> 5), nwarps = gridDim.x * THR_WARPS;
+	const uint32_t nwork = sv.ncand[3];
+	const bool trace = (rp.flags & DBT_F_TRACE) != 0;
+	const bool aln_all = (rp.flags & DBT_F_ALN) && !(rp.flags & DBT_F_ALN_MIN), aln_min = (rp.flags & DBT_F_ALN_MIN) != 0;
+	const bool want_rec = trace || aln_all || aln_min;
+	const uint32_t W64 = rp.lay.W64;
+	uint32_t c_fea = 0, c_inc = 0;
+
+#pragma unroll 1
+	for (uint32_t t = gwarp; t < nwork; t += nwarps) {
+		const uint32_t c = sv.thr[t];
+		const uint32_t p = sv.cand[c];
+		const uint32_t dw = sv.thr_dst[c];
+		const uint32_t dst = dw & THR_DST_MASK;
+		const uint64_t slot = trace ? (uint64_t)p : (uint64_t)c;
+		const bool slot_ok = want_rec && (trace || slot < rp.max_records);
+		uint8_t* rec = sv.records + slot * rp.rec_stride;
+		MateResult r[2];
+#pragma unroll 1
+		for (int m = 0; m < 2; ++m) {
+			const uint32_t len = sv.meta[m][p] & META_LENMASK;
+			r[m] = thread_mate<B, MAXJ>(ix.gtable, dst, rp, W, m, sv.packed[m] + (uint64_t)p * W64, len, lane);
+			if (slot_ok) {                                              // sam_t.r1 / r2 -> dbt_aln_mate blob
+				uint8_t* b = rec + sizeof(dbt_pair_record) + (size_t)m * rp.aln_stride;
+				uint8_t* es = b + sizeof(dbt_aln_mate); uint8_t* trb = es + rp.es_cap;
+				const int nes = min(r[m].nes, (int)rp.es_cap), ntr = min(r[m].ntr, (int)rp.tr_cap);
+				if (r[m].nes > (int)rp.es_cap || r[m].ntr > (int)rp.tr_cap) r[m].err = 1;
+				for (int i = lane; i < (int)rp.es_cap; i += 32) es[i] = i < nes ? (uint8_t)(W.es_t[i] | (W.es_g[i] << 3)) : (uint8_t)0;
+				for (int i = lane; i < (int)rp.tr_cap; i += 32) trb[i] = i < ntr ? W.tr[i] : (uint8_t)0;
+				if (lane == 0) {
+					dbt_aln_mate* h = reinterpret_cast<dbt_aln_mate*>(b);
+					h->alned = (uint8_t)r[m].alned; h->err = (uint8_t)r[m].err;
+					h->nes = (uint16_t)r[m].nes; h->ntr = (uint16_t)r[m].ntr; h->nkm = (uint16_t)r[m].nkm;
+					uint64_t hash = 0;
+					if (trace) {                                            // FNV-1a over the edited k-mer vector (parity tests only)
+						hash = 0xcbf29ce484222325ull;
+						for (int i = 0; i < r[m].nkm; ++i) { const uint64_t v = W.km[m][i]; for (int q = 0; q < 8; ++q) { hash ^= (v >> (8 * q)) & 0xFF; hash *= 0x100000001b3ull; } }
+					}
+					h->kmers_hash = hash;
+				}
+			}
+			__syncwarp();
+		}
+		const bool alned = r[0].alned || r[1].alned;                       // commented caller, cpp:2082-2087
+		if (alned) {
+			if (lane == 0) c_fea += 2;
+			uint32_t inc_sum = 0;
+#pragma unroll 1
+			for (int m = 0; m < 2; ++m) {                                     // D1: every TR k-mer of both edited vectors, cpp:2203-2208
+#pragma unroll 1
+				for (int j = 0; j * 32 < r[m].nkm; ++j) {
+					const int i = j * 32 + lane;
+					const uint32_t tx = i < r[m].nkm ? W.trx[m][i] : 0u;
+					const uint32_t tm = __ballot_sync(0xffffffffu, tx != 0);
+					if (!tm) continue;
+					inc_sum += __popc(tm);
+					if (tx) {
+						const uint32_t peers = __match_any_sync(tm, tx);
+						if ((uint32_t)lane == (uint32_t)(__ffs(peers) - 1))
+							atomicAdd(reinterpret_cast<unsigned long long*>(ix.counts + (tx - 1)), (unsigned long long)__popc(peers));
+					}
+				}
+			}
+			if (lane == 0) c_inc += inc_sum;
+		}
+		const uint32_t status = alned ? DBT_ST_COUNTED : DBT_ST_THREAD_FAILED;
+		const uint32_t fdst = alned ? dst : (uint32_t)ix.nloci;
+		if (want_rec && !slot_ok) { if (lane == 0 && (aln_all || alned)) atomicOr(sv.ncand + 1, ERR_RECORD_OVERFLOW); }
+		else if (slot_ok && lane == 0) {
+			dbt_pair_record* h = reinterpret_cast<dbt_pair_record*>(rec);
+			if (!trace) {                                                     // under DBT_F_TRACE the generic candidate kernel left the full header
+				h->pair_index = sv.first_pair_index + p; h->dst0 = dst; h->fc = 0; h->rc = 0; h->nhash0 = 0; h->nhash1 = 0;
+				h->pad[0] = h->pad[1] = h->pad[2] = 0;
+				for (int m = 0; m < 2; ++m) {
+					dbt_mate_record& o = h->mate[m];
+					o.si = o.ei = o.si_ = o.ei_ = o.ti = -1; o.nt = 0; o.bs = 0; o.pad = 0; o.nk = 0;
+					o.flags = (uint8_t)((((dw >> (28 + m)) & 1u) ? DBT_MF_KF : 0) | (((dw >> (30 + m)) & 1u) ? DBT_MF_RM : 0));
+				}
+			}
+			h->dst = fdst; h->status = (uint8_t)status;
+		}
+	}
+	if (lane == 0) {
+		if (c_fea) atomicAdd(sv.counters + DBT_C_NFEASIBLEREADS, (unsigned long long)c_fea);
+		if (c_inc) atomicAdd(sv.counters + DBT_C_NINC, (unsigned long long)c_inc);
+	}
+}
+
+// ---- graph table build (load time) ----
+// pass 0: nodes in canonical orientation claim their entry; pass 1: reverse-complement orientation merges into it (or
+// claims one when the partner is absent from the file); pass 2: TR k-mers attach their count-array position.
+template <int B>
+__global__ void graph_insert_kernel(Table t, const uint64_t* __restrict__ kmers, const uint8_t* __restrict__ masks,
+                                    const uint32_t* __restrict__ locus_of, uint64_t n, uint32_t k, int pass, uint32_t* err) {
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const uint64_t fw = kmers[i]; const uint32_t loc = locus_of[i];
+	if (k < 32 && (fw >> (2 * k))) { atomicOr(err, ERR_INDEX_MISSING); return; }
+	const uint64_t rc = kmer_rc(fw, k);
+	if (pass == 2) {
+		if (rc < fw) return;                                            // not canonical: unreachable through toCaKmer (h:180-183)
+		uint4* s = g_find_slot<B>(t, fw, loc);
+		if (s) { uint32_t* w = reinterpret_cast<uint32_t*>(s); if (w[3]) atomicOr(err, ERR_INDEX_DUPTR); w[3] = (uint32_t)i + 1; }
+		else if (!g_claim<B>(t, fw, loc, loc, (uint32_t)i + 1)) atomicOr(err, ERR_INDEX_FULL);
+		return;
+	}
+	const uint32_t mk = masks[i] & 0xFu;
+	const bool is_rc = rc < fw;
+	if (pass == 0) {
+		if (is_rc) return;
+		uint32_t lw = loc | (mk << 22) | G_PRESENT_CA;
+		if (rc == fw) lw |= (mk << 26) | G_PRESENT_RC;                    // palindrome (even k): both orientations are this node
+		if (!g_claim<B>(t, fw, loc, lw, 0)) atomicOr(err, ERR_INDEX_FULL);
+	} else {
+		if (!is_rc) return;
+		uint4* s = g_find_slot<B>(t, rc, loc);
+		const uint32_t add = (mk << 26) | G_PRESENT_RC;
+		if (s) atomicOr(reinterpret_cast<uint32_t*>(s) + 2, add);
+		else if (!g_claim<B>(t, rc, loc, loc | add, 0)) atomicOr(err, ERR_INDEX_FULL);
+	}
+}
+
+// verification: every node must read back with its own mask (catches duplicate nodes within a locus)
+template <int B>
+__global__ void graph_verify_kernel(Table t, const uint64_t* __restrict__ kmers, const uint8_t* __restrict__ masks,
+                                    const uint32_t* __restrict__ locus_of, uint64_t n, uint32_t k, uint32_t* err) {
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const GNode g = g_lookup<B>(t, kmers[i], locus_of[i], k);
+	if (!(g.bits & GN_PRESENT) || gn_mask(g.bits) != (masks[i] & 0xFu)) atomicOr(err, ERR_INDEX_DUPKEY);
+}
+
+}  // namespace dbt

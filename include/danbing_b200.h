@@ -201,12 +201,10 @@ typedef struct {
  */
 #define DBT_ES_TYPE(b)  ((b) & 7u)          /* index into "*=XDI"  */
 #define DBT_ES_BASE(b)  (((b) >> 3) & 7u)   /* index into "\0ACGT*" */
-static inline uint32_t dbt_es_cap_for(uint32_t max_read_len, uint32_t max_ncorrection) {
-  return (max_read_len + 2 * max_ncorrection + 8 + 7) / 8 * 8;
-}
-static inline uint32_t dbt_tr_cap_for(uint32_t max_read_len, uint32_t k, uint32_t max_ncorrection) {
-  return ((max_read_len >= k ? max_read_len - k + 1 : 1) + 2 * max_ncorrection + 8 + 7) / 8 * 8;
-}
+/* capacities of es[] / tr[] inside a blob: the read plus what deletions can insert */
+#define DBT_ES_CAP_FOR(max_read_len, max_ncorrection) ((((uint32_t)(max_read_len) + 2u * (uint32_t)(max_ncorrection) + 8u + 7u) / 8u) * 8u)
+#define DBT_TR_CAP_FOR(max_read_len, k, max_ncorrection) \
+  (((((uint32_t)(max_read_len) >= (uint32_t)(k) ? (uint32_t)(max_read_len) - (uint32_t)(k) + 1u : 1u) + 2u * (uint32_t)(max_ncorrection) + 8u + 7u) / 8u) * 8u)
 typedef struct {
   uint8_t  alned;              /* isThreadFeasible's return: 0 infeasible, 1 threaded, 2 threaded with edits */
   uint8_t  err;                /* 1 = the graph is not closed / capacity exceeded (reference: assert or UB) */
@@ -263,7 +261,8 @@ int  dbt_timer_start(dbt_ctx*, int slot);
 int  dbt_timer_stop (dbt_ctx*, int slot, float* ms);          /* synchronises the slot           */
 int  dbt_kernel_times(dbt_ctx*, int slot, float ms[8], uint32_t launches[8]); /* last dbt_process */
 uint64_t dbt_launch_count(const dbt_ctx*);                    /* kernels launched since create   */
-/* after dbt_wait(slot): [0] candidate pairs, [1] pairs the closed-form kernel left to the generic one */
+/* after dbt_wait(slot): [0] candidate pairs, [1] pairs the closed-form kernel left to the generic one,
+   [2] pairs handed to the threading kernel */
 int  dbt_batch_stats(dbt_ctx*, int slot, uint64_t stats[4]);
 /* [0] main buckets [1] slots per bucket [2] keys [3] used slots [4] main buckets that overflowed
    [5] keys in the stash [6] table bytes [7] stash buckets that overflowed */

@@ -391,7 +391,7 @@ static void write_record(uint8_t* rec, uint32_t stride, uint32_t as_stride, uint
 
 /* sam_t.r1 / r2 (cpp:53-75) of a pair that entered threading -> the two dbt_aln_mate blobs behind the header */
 static void write_aln_blobs(uint8_t* rec, uint32_t stride, const dbt_params* p, const dbo_thread_out* th) {
-	const uint32_t es_cap = dbt_es_cap_for(p->max_read_len, p->max_ncorrection);
+	const uint32_t es_cap = DBT_ES_CAP_FOR(p->max_read_len, p->max_ncorrection);
 	const uint32_t aln_stride = (stride - (uint32_t)sizeof(dbt_pair_record)) / 2;
 	for (int m = 0; m < 2; ++m) {
 		uint8_t* b = rec + sizeof(dbt_pair_record) + (size_t)m * aln_stride;

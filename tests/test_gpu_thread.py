@@ -1,0 +1,126 @@
+"""GPU parity of restored graph threading (P1: thread_kernel through the C ABI) against the oracle restatement,
+the reference's own isThreadFeasible (oracle/_ref/ref_harness) and the committed golden trace."""
+import gzip
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle_abi import Oracle, abi, have_ref, rpgg_io
+import thread_common as tc
+from test_oracle_thread import CASES, GOLD, split_case
+
+pytestmark = pytest.mark.gpu
+
+
+def gpu_run(ix, p, seqs, batch=None):
+    bases, off = rpgg_io.seqs_to_batch(seqs)
+    ctx = abi.Context(p, abi.make_index_struct(ix))
+    assert ctx.threading
+    recs, cnt = ctx.run(bases, off)
+    trkmc, kmc, nmap, tot = ctx.download()
+    ctx.close()
+    return recs, cnt, trkmc, kmc, nmap
+
+
+def assert_same_as_oracle(ix, p, seqs):
+    bases, off = rpgg_io.seqs_to_batch(seqs)
+    orecs, ocnt, otr, okmc, onmap = Oracle(ix).run(p, bases, off)
+    recs, cnt, trkmc, kmc, nmap = gpu_run(ix, p, seqs)
+    assert len(recs) == len(orecs)
+    bad = [i for i in range(len(recs)) if recs[i].tobytes() != orecs[i].tobytes()]
+    if bad:
+        i = bad[0]
+        g, o = recs[i], orecs[i]
+        msg = [f"{len(bad)} records differ; first pair {i}: status gpu {g['h']['status']} oracle {o['h']['status']} dst {g['h']['dst']}/{o['h']['dst']}"]
+        for m in range(2):
+            ga, oa = g["aln"][m], o["aln"][m]
+            msg.append(f" mate {m}: alned {ga['h']['alned']}/{oa['h']['alned']} err {ga['h']['err']} nes {ga['h']['nes']}/{oa['h']['nes']} ntr {ga['h']['ntr']}/{oa['h']['ntr']} "
+                       f"nkm {ga['h']['nkm']}/{oa['h']['nkm']} hash_eq {ga['h']['kmers_hash'] == oa['h']['kmers_hash']}")
+            msg.append("  gpu es " + tc.es_string(ga["es"], int(ga["h"]["nes"])))
+            msg.append("  ora es " + tc.es_string(oa["es"], int(oa["h"]["nes"])))
+            msg.append("  gpu tr " + tc.tr_string(ga["tr"], int(ga["h"]["ntr"])))
+            msg.append("  ora tr " + tc.tr_string(oa["tr"], int(oa["h"]["ntr"])))
+        msg.append(" seqs " + seqs[2 * i] + " " + seqs[2 * i + 1])
+        raise AssertionError("\n".join(msg))
+    assert np.array_equal(trkmc, otr) and np.array_equal(kmc, okmc) and np.array_equal(nmap, onmap)
+    for i, name in enumerate(abi.COUNTER_NAMES):
+        if name not in abi.MEASUREMENT_COUNTERS:
+            assert int(cnt[i]) == int(ocnt[i]), name
+    return recs, cnt
+
+
+@pytest.mark.parametrize("ci", range(len(CASES)))
+def test_trace_records_counts_counters_vs_oracle(ci):
+    gk, pk = split_case(CASES[ci])
+    _, ix, seqs, _ = tc.thread_case(write_text=False, frac_bg=0.2, **gk)
+    p = tc.thread_params(extra_flags=abi.F_TRACE, max_batch_pairs=4096, **pk)
+    recs, cnt = assert_same_as_oracle(ix, p, seqs)
+    st = recs["h"]["status"]
+    assert (st == abi.ST_COUNTED).sum() > 50
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("ci", [0, 1, 3])
+def test_trace_records_vs_reference_harness(ci, tmp_path):
+    gk, pk = split_case(CASES[ci])
+    pref, ix, seqs, _ = tc.thread_case(outdir=str(tmp_path), frac_bg=0.2, **gk)
+    p = tc.thread_params(extra_flags=abi.F_TRACE, max_batch_pairs=4096, **pk)
+    rows, _, _, ref_cnt = tc.run_ref_thread_harness(pref, seqs, str(tmp_path / "ref"), p)
+    recs, cnt, trkmc, _, _ = gpu_run(ix, p, seqs)
+    assert tc.check_records_vs_harness(recs, rows, int(ix["nloci"])) > 50
+    names = dict(zip(abi.COUNTER_NAMES, [int(x) for x in cnt]))
+    for key in ("nThreadingReads", "nFeasibleReads", "nhash0", "nhash1", "nSubFiltered", "nKmerFiltered", "nLocusAssignFiltered"):
+        assert names[key] == ref_cnt[key], key
+
+
+def test_trace_records_vs_golden_trace():
+    meta = json.load(open(os.path.join(GOLD, "meta.json")))
+    gk, pk = split_case(meta["case"])
+    _, ix, seqs, _ = tc.thread_case(write_text=False, **gk)
+    p = tc.thread_params(extra_flags=abi.F_TRACE, max_batch_pairs=4096, **pk)
+    rows = [l.rstrip("\n").split("\t") for l in gzip.open(os.path.join(GOLD, "harness.trace.tsv.gz"), "rt")]
+    recs, cnt, trkmc, _, _ = gpu_run(ix, p, seqs)
+    assert tc.check_records_vs_harness(recs, rows, int(ix["nloci"])) * 2 == meta["threaded_reads"]
+    names = dict(zip(abi.COUNTER_NAMES, [int(x) for x in cnt]))
+    for key in ("nThreadingReads", "nFeasibleReads", "nhash0", "nhash1"):
+        assert names[key] == meta["counters"][key], key
+    gold = np.frombuffer(gzip.open(os.path.join(GOLD, "out.trkmc.ar.gz")).read(), "<u8")[1:]
+    assert int(trkmc.sum()) == int(gold.sum())
+
+
+@pytest.mark.parametrize("aln", [0, 1, 2])
+def test_record_selection_follows_a_and_ae(aln):
+    """-a: every pair that entered threading; -ae: threaded pairs only; neither: no records (cpp:2232-2239)."""
+    gk, pk = split_case(CASES[1])
+    _, ix, seqs, _ = tc.thread_case(write_text=False, frac_bg=0.2, **gk)
+    bases, off = rpgg_io.seqs_to_batch(seqs)
+    pt = tc.thread_params(extra_flags=abi.F_TRACE, max_batch_pairs=4096, **pk)
+    orecs, ocnt, otr, _, _ = Oracle(ix).run(pt, bases, off)
+    st = orecs["h"]["status"]
+    want = {0: np.zeros(len(st), bool), 1: (st == abi.ST_COUNTED) | (st == abi.ST_THREAD_FAILED), 2: st == abi.ST_COUNTED}[aln]
+    p = tc.thread_params(aln=aln, max_batch_pairs=4096, **pk)
+    recs, cnt, trkmc, _, _ = gpu_run(ix, p, seqs)
+    assert np.array_equal(trkmc, otr)
+    assert [int(x) for x in recs["h"]["pair_index"]] == [int(i) for i in np.nonzero(want)[0]]
+    for r in recs:
+        o = orecs[int(r["h"]["pair_index"])]
+        assert r["h"]["status"] == o["h"]["status"] and r["h"]["dst"] == o["h"]["dst"]
+        for m in range(2):
+            a, b = r["aln"][m], o["aln"][m]
+            assert a["h"]["alned"] == b["h"]["alned"] and a["es"].tobytes() == b["es"].tobytes() and a["tr"].tobytes() == b["tr"].tobytes()
+
+
+def test_threading_flag_without_graph_keeps_head_behaviour():
+    """No graph in the index: `-gc` behaves like the reference's HEAD (nothing passes, cpp:2072-2090)."""
+    gk, pk = split_case(CASES[0])
+    _, ix, seqs, _ = tc.thread_case(write_text=False, **gk)
+    ix = {k: v for k, v in ix.items() if not k.startswith("g_")}
+    p = tc.thread_params(extra_flags=abi.F_TRACE, max_batch_pairs=4096, **pk)
+    bases, off = rpgg_io.seqs_to_batch(seqs)
+    ctx = abi.Context(p, abi.make_index_struct(ix))
+    assert not ctx.threading
+    recs, cnt = ctx.run(bases, off)
+    trkmc, _, _, _ = ctx.download()
+    assert trkmc.sum() == 0 and (recs["h"]["status"] == abi.ST_NOT_THREADED).sum() > 50

@@ -48,9 +48,10 @@ def test_introsort_matches_libstdcxx():
     """device introsort (compiled for the host) and the oracle's, vs this toolchain's std::sort"""
     with tempfile.TemporaryDirectory() as tmp:
         exe = os.path.join(tmp, "introsort_check")
-        obj = os.path.join(tmp, "dbo.o")
+        obj, obj2 = os.path.join(tmp, "dbo.o"), os.path.join(tmp, "dbo_thread.o")
         subprocess.run(["gcc", "-O2", "-c", "-o", obj, os.path.join(ORACLE_DIR, "dbt_oracle.c")], check=True)
-        subprocess.run(["g++", "-O2", "-std=c++17", "-o", exe, os.path.join(ROOT, "tests/native/introsort_check.cpp"), obj], check=True)
+        subprocess.run(["gcc", "-O2", "-c", "-o", obj2, os.path.join(ORACLE_DIR, "dbt_oracle_thread.c")], check=True)
+        subprocess.run(["g++", "-O2", "-std=c++17", "-o", exe, os.path.join(ROOT, "tests/native/introsort_check.cpp"), obj, obj2], check=True)
         out = subprocess.run([exe], capture_output=True, text=True)
         assert out.returncode == 0 and out.stdout.startswith("OK"), out.stdout
         ncases, nheap = map(int, out.stdout.split()[1:3])
