@@ -611,7 +611,16 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 		// =========================== phase 4: assignTRkmc, accumulate, record ===========================
 		if (active && !deferred) {
 			if (lane == 0) { c_kf += kf[0] + kf[1]; c_h1 += nhash1; }
-			if (status < 0 && (rp.flags & DBT_F_THREADING)) { status = DBT_ST_NOT_THREADED; if (lane == 0) c_thr0 += 2; }   // cpp:2070-2090 at HEAD
+			if (status < 0 && (rp.flags & DBT_F_THREADING)) {
+				if (rp.thr_on) {                                     // restored threading: hand the pair to thread_kernel (cpp:2070-2088)
+					status = DBT_ST_THREAD_PENDING;
+					if (lane == 0) {
+						c_thr0 += 2;
+						sv.thr_dst[c] = dst | ((uint32_t)(kf[0] | (kf[1] << 1)) << 28) | ((uint32_t)(rm[0] | (rm[1] << 1)) << 30);
+						sv.thr[atomicAdd(sv.ncand + 3, 1u)] = c;
+					}
+				} else { status = DBT_ST_NOT_THREADED; if (lane == 0) c_thr0 += 2; }   // cpp:2070-2090 at HEAD
+			}
 			if (status < 0) {
 				if (lane == 0) c_thr += 2;
 				// assignTRkmc (cpp:1450-1556) against the tables of destLocus0

@@ -58,7 +58,7 @@ def test_trace_records_counts_counters_vs_oracle(ci):
     p = tc.thread_params(extra_flags=abi.F_TRACE, max_batch_pairs=4096, **pk)
     recs, cnt = assert_same_as_oracle(ix, p, seqs)
     st = recs["h"]["status"]
-    assert (st == abi.ST_COUNTED).sum() > 50
+    assert (st == abi.ST_COUNTED).sum() > 20
 
 
 @pytest.mark.skipif(not have_ref(), reason="oracle/_ref not built")
@@ -69,7 +69,7 @@ def test_trace_records_vs_reference_harness(ci, tmp_path):
     p = tc.thread_params(extra_flags=abi.F_TRACE, max_batch_pairs=4096, **pk)
     rows, _, _, ref_cnt = tc.run_ref_thread_harness(pref, seqs, str(tmp_path / "ref"), p)
     recs, cnt, trkmc, _, _ = gpu_run(ix, p, seqs)
-    assert tc.check_records_vs_harness(recs, rows, int(ix["nloci"])) > 50
+    assert tc.check_records_vs_harness(recs, rows, int(ix["nloci"])) > 20
     names = dict(zip(abi.COUNTER_NAMES, [int(x) for x in cnt]))
     for key in ("nThreadingReads", "nFeasibleReads", "nhash0", "nhash1", "nSubFiltered", "nKmerFiltered", "nLocusAssignFiltered"):
         assert names[key] == ref_cnt[key], key
@@ -124,3 +124,18 @@ def test_threading_flag_without_graph_keeps_head_behaviour():
     recs, cnt = ctx.run(bases, off)
     trkmc, _, _, _ = ctx.download()
     assert trkmc.sum() == 0 and (recs["h"]["status"] == abi.ST_NOT_THREADED).sum() > 50
+
+
+@pytest.mark.parametrize("cfg", [
+    dict(seed=41, rseed=1, sub=0.02, ins=0.004, dele=0.004, npairs=6000, thread=60, maxnc=4, nloci=30),
+    dict(seed=42, rseed=2, sub=0.06, ins=0.02, dele=0.02, npairs=6000, thread=15, maxnc=12, cth=15, nloci=12),
+    dict(seed=43, rseed=3, sub=0.01, ins=0.03, dele=0.03, npairs=6000, thread=25, maxnc=6, cth=20, frac_n=0.2, nloci=12, k=17),
+    dict(seed=44, rseed=4, sub=0.03, ins=0.01, dele=0.01, npairs=4000, thread=30, maxnc=5, cth=20, rlen=250, nloci=12),
+])
+def test_stress_vs_oracle(cfg):
+    """many reads, heavy error mixes, 250 bp reads (MAXJ = 8 instantiation): record-exact against the oracle"""
+    gk, pk = split_case(cfg)
+    _, ix, seqs, _ = tc.thread_case(write_text=False, frac_bg=0.1, **gk)
+    p = tc.thread_params(extra_flags=abi.F_TRACE, max_batch_pairs=8192, max_read_len=gk.get("rlen", 150), **pk)
+    recs, cnt = assert_same_as_oracle(ix, p, seqs)
+    assert (recs["h"]["status"] == abi.ST_COUNTED).sum() > 200
