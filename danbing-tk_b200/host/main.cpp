@@ -32,6 +32,7 @@
 #include "rpgg_files.hpp"
 #include "fastx_reader.hpp"
 #include "kam_writer.hpp"
+#include "aln_writer.hpp"
 
 using namespace dbt_host;
 
@@ -66,6 +67,8 @@ struct Shared {
 	Rpgg rpgg;
 	dbt_index index{};
 	uint64_t batch_pairs = 0, bases_cap = 0;
+	bool thr_graph = false;             // -g/-gc with PREF.graph.kmers loaded: restored graph threading
+	bool want_records = false;          // kam lines (no threading) or .aln lines (-a/-ae with threading)
 	std::atomic<bool> failed{false};
 	std::mutex err_mutex; std::string err;
 	void fail(const std::string& m) { std::lock_guard<std::mutex> l(err_mutex); if (!failed.exchange(true)) err = m; }
@@ -129,10 +132,14 @@ void worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<HostBatch
 		bo.index = f.hb->first_pair_index;                    // batches are ordered by their first pair
 		bo.npairs = f.hb->npairs; bo.nreads_total = f.hb->nreads_total_after; bo.unpaired = f.hb->unpaired_after;
 		memcpy(bo.counters, f.res.counters, sizeof bo.counters);
-		if (S.opt.okam && f.res.n_records) {
+		if (S.want_records && f.res.n_records) {
 			const uint32_t stride = dbt_record_stride(w.ctx), as_stride = dbt_record_as_stride(w.ctx);
 			bo.text.reserve((size_t)f.res.n_records * 520);
-			for (uint64_t i = 0; i < f.res.n_records; ++i) append_kam_line(bo.text, f.recs.data() + i * stride, as_stride, *f.hb, S.opt.isFastq);
+			if (S.thr_graph) {
+				const uint32_t aln_stride = dbt_record_aln_stride(w.ctx), es_cap = dbt_record_es_cap(w.ctx);
+				for (uint64_t i = 0; i < f.res.n_records; ++i) append_aln_line(bo.text, f.recs.data() + i * stride, aln_stride, es_cap, *f.hb);
+			} else
+				for (uint64_t i = 0; i < f.res.n_records; ++i) append_kam_line(bo.text, f.recs.data() + i * stride, as_stride, *f.hb, S.opt.isFastq);
 		}
 		bo.seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - f.t0).count();
 		recycle.push(f.hb);
@@ -155,9 +162,9 @@ void worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<HostBatch
 		Inflight& f = fl[s];
 		f.hb = hb; f.t0 = std::chrono::steady_clock::now();
 		const uint32_t stride = dbt_record_stride(w.ctx);
-		if (S.opt.okam) f.recs.resize((size_t)S.batch_pairs * stride);
+		if (S.want_records) f.recs.resize((size_t)S.batch_pairs * stride);
 		f.res = dbt_batch_result{};
-		f.res.capacity = S.opt.okam ? S.batch_pairs : 0; f.res.records = S.opt.okam ? f.recs.data() : nullptr;
+		f.res.capacity = S.want_records ? S.batch_pairs : 0; f.res.records = S.want_records ? f.recs.data() : nullptr;
 		dbt_batch b{};
 		b.first_pair_index = hb->first_pair_index; b.npairs = hb->npairs; b.layout = DBT_LAYOUT_ASCII; b.bases = hb->bases; b.offsets = hb->offsets;
 		int rc = dbt_submit(w.ctx, &b, &f.res, s);
@@ -199,6 +206,22 @@ int main(int argc, char** argv) {
 	S.index.nvv = g.vv.size(); S.index.vv = g.vv.empty() ? nullptr : g.vv.data();
 	S.index.tr_n = g.tr_n.data(); S.index.tr_kmers = g.tr_kmers.data(); S.index.fl_n = g.fl_n.data(); S.index.fl_kmers = g.fl_kmers.data();
 	S.index.qc = o.qc ? g.qc.data() : nullptr;
+	if (o.threading) {
+		// The reference's HEAD never loads a graph and its threading step passes nothing (cpp:2072-2090, 2468).  When the RPGG
+		// ships its graph (PREF.graph.kmers from `fa2kmers -g`, or a v1.3 PREF.graph.umap) the restored threading runs instead.
+		const std::string gk = o.trPrefix + ".graph.kmers", gu = o.trPrefix + ".graph.umap";
+		bool okg = true;
+		if (file_exists(gk)) okg = read_graph_kmers(gk, g.nloci, S.rpgg, std::max<int>((int)o.nproc, std::min(hw, 16)), err);
+		else if (file_exists(gu)) okg = read_graph_umap(gu, g.nloci, S.rpgg, err);
+		else fprintf(stderr, "[danbing-tk b200] no %s: -g/-gc behaves like the reference at HEAD (no read passes threading)\n", gk.c_str());
+		if (!okg) { fprintf(stderr, "\n%s\n", err.c_str()); return 1; }
+		if (!g.g_n.empty()) {
+			S.index.g_n = g.g_n.data(); S.index.g_kmers = g.g_kmers.data(); S.index.g_masks = g.g_masks.data();
+			S.thr_graph = true;
+			fprintf(stderr, "[danbing-tk b200] graph threading restored: %llu nodes\n", (unsigned long long)g.g_kmers.size());
+		}
+	}
+	S.want_records = S.thr_graph ? o.aln : o.okam;
 	fprintf(stderr, "0 bait loci in baitDB\ndeserialized graph/index and read tr.kmers in %lld sec.\n# unique kmers in kmerDBi: %llu\n",
 	        (long long)std::chrono::duration_cast<std::chrono::seconds>(std::chrono::steady_clock::now() - t_load).count(), (unsigned long long)g.dbi_keys.size());
 

@@ -39,6 +39,8 @@ struct Rpgg {
 	std::vector<uint64_t> tr_n, tr_kmers;      // per-locus sizes + keys in OUTPUT order
 	std::vector<uint64_t> fl_n, fl_kmers;
 	std::vector<uint8_t> qc;
+	std::vector<uint64_t> g_n, g_kmers;        // PREF.graph.kmers: per-locus node counts + strand-specific k-mers (sorted, unique)
+	std::vector<uint8_t> g_masks;              // 4-bit out-edge masks
 };
 
 inline bool read_whole_file(const std::string& fn, std::vector<char>& buf, std::string& err) {
@@ -149,6 +151,95 @@ inline bool read_tr_kmers_ordered(const std::string& fn, Rpgg& g, int nthreads, 
 	for (size_t l = 0; l < nloci; ++l) { if (!per[l].empty()) memcpy(g.tr_kmers.data() + o, per[l].data(), per[l].size() * 8); o += per[l].size(); }
 	return true;
 }
+
+// PREF.graph.kmers (text; readGraphKmers, src/aQueryFasta_thread.h:549-575: `kmerDB[idx][kmer] |= c`) -> per-locus nodes,
+// duplicate lines merged with OR like the reference's operator|=.  Loci are parsed on nthreads host threads.
+inline bool read_graph_kmers(const std::string& fn, uint64_t nloci, Rpgg& g, int nthreads, std::string& err) {
+	std::vector<char> b;
+	if (!read_whole_file(fn, b, err)) return false;
+	std::vector<size_t> start;
+	const char* p = b.data(); const char* e = p + b.size();
+	for (const char* q = p; q < e; ) {
+		const char* nl = (const char*)memchr(q, '\n', e - q);
+		const char* next = nl ? nl + 1 : e;
+		if (*q == '>') start.push_back(next - p);
+		else if (start.empty()) { err = fn + ": node line before the first '>' header"; return false; }
+		q = next;
+	}
+	if (start.size() != nloci) { err = fn + ": " + std::to_string(start.size()) + " loci, the RPGG has " + std::to_string(nloci); return false; }
+	std::vector<std::vector<std::pair<uint64_t, uint8_t>>> per(nloci);
+	std::atomic<size_t> nextl{0};
+	std::atomic<bool> ok{true};
+	auto work = [&]() {
+		for (;;) {
+			const size_t l = nextl.fetch_add(1);
+			if (l >= nloci) break;
+			auto& v = per[l];
+			const char* s = p + start[l];
+			const char* lim = (l + 1 < nloci) ? p + start[l + 1] : e;
+			while (s < lim) {
+				const char* nl = (const char*)memchr(s, '\n', lim - s);
+				const char* next = nl ? nl + 1 : lim;
+				if (*s == '>') { s = next; continue; }
+				char* e1 = nullptr; char* e2 = nullptr;
+				const unsigned long km = strtoul(s, &e1, 10);
+				if (e1 == s || *e1 != '\t') { ok = false; s = next; continue; }
+				const unsigned long mk = strtoul(e1 + 1, &e2, 10);
+				if (e2 == e1 + 1) { ok = false; s = next; continue; }
+				v.emplace_back((uint64_t)km, (uint8_t)mk);
+				s = next;
+			}
+			std::sort(v.begin(), v.end());
+			size_t w = 0;
+			for (size_t i = 0; i < v.size(); ++i) {
+				if (w && v[w - 1].first == v[i].first) v[w - 1].second |= v[i].second;
+				else v[w++] = v[i];
+			}
+			v.resize(w);
+		}
+	};
+	if (nthreads < 1) nthreads = 1;
+	std::vector<std::thread> th;
+	for (int t = 1; t < nthreads; ++t) th.emplace_back(work);
+	work();
+	for (auto& t : th) t.join();
+	if (!ok) { err = fn + ": malformed node line (expected `kmer<TAB>mask`)"; return false; }
+	size_t tot = 0;
+	g.g_n.assign(nloci, 0);
+	for (size_t l = 0; l < nloci; ++l) { g.g_n[l] = per[l].size(); tot += per[l].size(); }
+	g.g_kmers.resize(tot); g.g_masks.resize(tot);
+	size_t o = 0;
+	for (size_t l = 0; l < nloci; ++l) for (auto& kv : per[l]) { g.g_kmers[o] = kv.first; g.g_masks[o] = kv.second; ++o; }
+	return true;
+}
+
+// LEGACY v1.3 PREF.graph.umap: u64 nloci | per locus { u64 n | n x { u64 key, u8 mask } }
+inline bool read_graph_umap(const std::string& fn, uint64_t nloci, Rpgg& g, std::string& err) {
+	std::vector<char> b;
+	if (!read_whole_file(fn, b, err)) return false;
+	auto bad = [&]() { err = fn + ": truncated or malformed .graph.umap"; return false; };
+	size_t o = 0;
+	auto rd64 = [&](uint64_t& v) { if (o + 8 > b.size()) return false; memcpy(&v, b.data() + o, 8); o += 8; return true; };
+	uint64_t nl;
+	if (!rd64(nl)) return bad();
+	if (nl != nloci) { err = fn + ": " + std::to_string(nl) + " loci, the RPGG has " + std::to_string(nloci); return false; }
+	g.g_n.assign(nloci, 0); g.g_kmers.clear(); g.g_masks.clear();
+	for (uint64_t l = 0; l < nloci; ++l) {
+		uint64_t n;
+		if (!rd64(n) || n > (b.size() - o) / 9) return bad();
+		std::vector<std::pair<uint64_t, uint8_t>> v(n);
+		for (uint64_t i = 0; i < n; ++i) { memcpy(&v[i].first, b.data() + o, 8); v[i].second = (uint8_t)b[o + 8]; o += 9; }
+		std::sort(v.begin(), v.end());
+		size_t w = 0;
+		for (size_t i = 0; i < v.size(); ++i) { if (w && v[w - 1].first == v[i].first) v[w - 1].second |= v[i].second; else v[w++] = v[i]; }
+		g.g_n[l] = w;
+		for (size_t i = 0; i < w; ++i) { g.g_kmers.push_back(v[i].first); g.g_masks.push_back(v[i].second); }
+	}
+	if (o != b.size()) return bad();
+	return true;
+}
+
+inline bool file_exists(const std::string& fn) { FILE* f = fopen(fn.c_str(), "rb"); if (!f) return false; fclose(f); return true; }
 
 inline bool read_qc(const std::string& fn, uint64_t nloci, std::vector<uint8_t>& qc, std::string& err) {
 	std::vector<char> b;

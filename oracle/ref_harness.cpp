@@ -159,7 +159,7 @@ int main(int argc, char* argv[]) {
 			else { destLocus = nloci; status = 5; }
 			if (aln == 1 or (aln == 2 and destLocus != nloci)) {
 				seqs.push_back(s1); seqs.push_back(s2);
-				titles.resize(seqs.size()/2, "p" + to_string(idx));
+				titles.resize(seqs.size()/2, ">p" + to_string(idx));   // titles[] keep the leading '>' (cpp:1747 prints them whole)
 				alnindices.push_back(seqs.size());
 				sam.src = -1;
 				sam.dst = destLocus;

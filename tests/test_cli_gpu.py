@@ -128,3 +128,55 @@ def test_cli_two_gpus_same_bytes(tmp_path, lib):
     assert out.decode().splitlines() == exp["kam"]
     assert np.array_equal(np.fromfile(tmp_path / "out.trkmc.ar", "<u8")[1:], exp["trkmc"])
     assert open(tmp_path / "out.tr.summary.txt").read() == exp["summary"]
+
+
+# ---- restored graph threading (-g / -gc with PREF.graph.kmers): .aln lines and counts vs the reference harness golden ----
+def stage_thread_case(tmp_path):
+    import json
+    import thread_common as tc
+    from test_oracle_thread import GOLD, split_case
+    meta = json.load(open(os.path.join(GOLD, "meta.json")))
+    gk, pk = split_case(meta["case"])
+    pref, ix, seqs, _ = tc.thread_case(outdir=str(tmp_path), **gk)
+    fa = str(tmp_path / "reads.fa")
+    with open(fa, "w") as f:
+        for i in range(len(seqs) // 2):
+            f.write(f">p{i}/1\n{seqs[2 * i + 1]}\n>p{i}/2\n{seqs[2 * i]}\n")
+    flags = ["-k", 21, "-kf", 4, 1, "-cth", pk["cth"], "-gc", pk["thread"], pk["maxnc"]]
+    return pref, fa, flags, meta, GOLD
+
+
+@pytest.mark.parametrize("mode,gold", [("-a", "out.aln.gz"), ("-ae", "out.aln_min.gz")])
+def test_cli_threading_aln_lines_and_counts_match_reference_harness(mode, gold, tmp_path):
+    pref, fa, flags, meta, GOLD = stage_thread_case(tmp_path)
+    out, err = run_cli(CLI, flags + [mode, "-qs", pref, "-fa", fa, "-o", tmp_path / "out"], tmp_path)
+    exp = gzip.open(os.path.join(GOLD, gold), "rt").read()
+    assert out.decode() == exp
+    gold_tr = np.frombuffer(gzip.open(os.path.join(GOLD, "out.trkmc.ar.gz")).read(), "<u8")
+    assert np.array_equal(np.fromfile(tmp_path / "out.trkmc.ar", "<u8"), gold_tr)
+    c = counters(err)
+    assert c["entered threading step"] == meta["counters"]["nThreadingReads"]
+    assert c["passsed threading"] == meta["counters"]["nFeasibleReads"]
+    assert "graph threading restored" in err
+
+
+def test_cli_threading_without_alignment_output_and_legacy_graph_umap(tmp_path):
+    """no -a/-ae: empty stdout, same counts; the graph may also come as a v1.3 PREF.graph.umap"""
+    pref, fa, flags, meta, GOLD = stage_thread_case(tmp_path)
+    from oracle_abi import rpgg_io
+    n, k, v = rpgg_io.read_kmers_text(pref + ".graph.kmers")
+    with open(pref + ".graph.umap", "wb") as f:
+        f.write(np.uint64(len(n)).tobytes())
+        o = 0
+        for c in n:
+            c = int(c)
+            f.write(np.uint64(c).tobytes())
+            rec = np.zeros(c, dtype=[("k", "<u8"), ("m", "u1")])
+            rec["k"], rec["m"] = k[o:o + c], v[o:o + c].astype("u1")
+            f.write(rec.tobytes())
+            o += c
+    os.remove(pref + ".graph.kmers")
+    out, err = run_cli(CLI, flags + ["-qs", pref, "-fa", fa, "-o", tmp_path / "out"], tmp_path)
+    assert out == b""
+    gold_tr = np.frombuffer(gzip.open(os.path.join(GOLD, "out.trkmc.ar.gz")).read(), "<u8")
+    assert np.array_equal(np.fromfile(tmp_path / "out.trkmc.ar", "<u8"), gold_tr)
