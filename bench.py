@@ -13,9 +13,17 @@ Contract (driver): `python bench.py --gpus N --steps K --warmup W` prints ONE JS
               same workload on this box's host cores, outputs diffed against the GPU's (bit-exact gate)
 `--impl reference` times only that CPU reference arm.
 Workload = BASELINE.json configs[1]: synthetic 1k-locus RPGG, 10M simulated 150 bp pairs (5% locus
-reads, 95% background), flags -k 21 -kf 4 1 -cth 45 (+ -ae, an output-selection flag that is a no-op at
-the reference's HEAD; `-gc 85 3` threading has no caller there -- SURVEY.md F2/F3 -- so the live "asgn"
-path is what both arms run).
+reads, 95% background), flags -k 21 -gc 85 3 -kf 4 1 -cth 45 -ae.
+Two modes, both measured in the default run:
+  thread (HEADLINE)  restored graph threading (SURVEY.md §8(c) decision D1): locus reads carry 0.2 %
+              substitutions + 0.01 % indels (S2), every pair that passes the locus vote is threaded through
+              the locus graph with error correction, counts come from the edited k-mer vectors, `-ae`
+              alignment records come back.  CPU arm = the reference's own isThreadFeasible & helpers
+              compiled from /root/reference (oracle/_ref/ref_harness; the commented-out caller
+              cpp:2072-2088 restored as glue), one process per host core on shards of the sample.
+  asgn (block "asgn")  what the UNMODIFIED reference binary executes at HEAD for these flags minus -gc
+              (threading has no caller there): error-free reads, kam records.  CPU arm =
+              oracle/_ref/danbing-tk -p nproc.
 """
 import argparse
 import ctypes as C
@@ -51,25 +59,29 @@ def build_workload(nloci, seed, workdir):
     loci = synth.make_loci(nloci, seed=seed, nhap=8, flank=700, share_frac=0.05, share_len=200)
     pref = os.path.join(workdir, "pan")
     ix = synth.build_rpgg(loci, pref, k=K, fsi=700, fso=700, write_text=True)
+    ix.update(synth.build_graph(loci, K, pref))              # PREF.graph.kmers (fa2kmers -g) for the threading mode
     haps = [h for hs in loci for h in hs]
     hap_off = np.zeros(len(haps) + 1, np.uint64)
     hap_off[1:] = np.cumsum([len(h) for h in haps])
     pool = np.frombuffer(b"".join(haps), np.uint8).copy()
-    log(f"[bench] RPGG: {nloci} loci, {len(ix['dbi_keys'])} index k-mers, {len(ix['tr_kmers'])} TR k-mers, nvv={len(ix['vv'])} ({time.time()-t:.1f}s)")
+    log(f"[bench] RPGG: {nloci} loci, {len(ix['dbi_keys'])} index k-mers, {len(ix['tr_kmers'])} TR k-mers, nvv={len(ix['vv'])}, {len(ix['g_kmers'])} graph nodes ({time.time()-t:.1f}s)")
     return ix, pref, pool, hap_off
 
 
 _synth_lib = None
 
 
-def synth_reads(device, pool, hap_off, first_pair, npairs, seed, frac_locus, out):
+SUB_PPM, INDEL_PPM = 2000, 100          # S2 error model of the threading runs: 0.2 % substitutions, 0.01 % indels
+
+
+def synth_reads(device, pool, hap_off, first_pair, npairs, seed, frac_locus, out, sub_ppm=0, indel_ppm=0):
     global _synth_lib
     if _synth_lib is None:
         _synth_lib = C.CDLL(os.path.join(ROOT, "danbing-tk_b200", "libdbt_synth.so"))
-        _synth_lib.dbt_synth_reads.argtypes = [C.c_int, abi.u8p, abi.u64p, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint64,
-                                               C.c_double, C.c_uint32, C.c_uint32, abi.u8p]
-    rc = _synth_lib.dbt_synth_reads(device, abi.ptr(pool, abi.u8p), abi.ptr(hap_off, abi.u64p), len(hap_off) - 1, first_pair,
-                                    npairs, seed, frac_locus, RLEN, FLEN, abi.ptr(out, abi.u8p))
+        _synth_lib.dbt_synth_reads2.argtypes = [C.c_int, abi.u8p, abi.u64p, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint64,
+                                                C.c_double, C.c_uint32, C.c_uint32, abi.u8p, C.c_uint32, C.c_uint32]
+    rc = _synth_lib.dbt_synth_reads2(device, abi.ptr(pool, abi.u8p), abi.ptr(hap_off, abi.u64p), len(hap_off) - 1, first_pair,
+                                     npairs, seed, frac_locus, RLEN, FLEN, abi.ptr(out, abi.u8p), sub_ppm, indel_ppm)
     if rc:
         raise RuntimeError(f"dbt_synth_reads failed: {rc}")
 
@@ -149,6 +161,49 @@ def run_reference(pref, fasta, outpref, nproc):
     return max(t_all - t_load, 1e-9), t_all, t_load
 
 
+def write_pairs_tsv_sample(fn, ascii_reads, p0, p1):
+    """pairs [p0, p1) of the batch as `seq1<TAB>seq2` lines in the reference's internal mate order (= batch order)."""
+    a = ascii_reads[p0 * 2 * RLEN: p1 * 2 * RLEN].reshape(p1 - p0, 2, RLEN)
+    rec = np.empty((p1 - p0, 2 * RLEN + 2), np.uint8)
+    rec[:, :RLEN] = a[:, 0]
+    rec[:, RLEN] = ord("\t")
+    rec[:, RLEN + 1: 2 * RLEN + 1] = a[:, 1]
+    rec[:, 2 * RLEN + 1] = ord("\n")
+    rec.tofile(fn)
+
+
+def run_reference_thread(pref, ascii_reads, n, workdir, nproc):
+    """The reference's threading functions (oracle/_ref/ref_harness, thread=85 corr=1 maxnc=3 aln=2, no trace dump):
+    one process per core, each on a contiguous shard of the first n pairs.  -> (query s, wall s, load s, summed trkmc)."""
+    exe = ref_bin("ref_harness")
+    tail = [str(K), str(CTH), "4", "1", "40", "0", "thread=85", "corr=1", "maxnc=3", "aln=2", "trace=0"]
+    nproc = max(1, min(nproc, n // 1000 or 1))
+    bounds = [n * i // nproc for i in range(nproc + 1)]
+    empty = os.path.join(workdir, "thr.empty.tsv")
+    open(empty, "w").close()
+    for i in range(nproc):
+        write_pairs_tsv_sample(os.path.join(workdir, f"thr.{i}.tsv"), ascii_reads, bounds[i], bounds[i + 1])
+
+    def launch(tsvs):
+        t0 = time.perf_counter()
+        ps = [subprocess.Popen([exe, pref, tsv, tsv + ".out"] + tail, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL) for tsv in tsvs]
+        for q in ps:
+            if q.wait():
+                raise RuntimeError("ref_harness failed")
+        return time.perf_counter() - t0
+    # index load phase: the same nproc processes on empty inputs (they contend for memory bandwidth the same way)
+    empties = [f"{empty}.{i}" for i in range(nproc)]
+    for e in empties:
+        open(e, "w").close()
+    t_load = launch(empties)
+    t_all = launch([os.path.join(workdir, f"thr.{i}.tsv") for i in range(nproc)])
+    tot = None
+    for i in range(nproc):
+        c = rpgg_io.read_ar(os.path.join(workdir, f"thr.{i}.tsv.out.trkmc.ar"))
+        tot = c.astype(np.uint64) if tot is None else tot + c
+    return max(t_all - t_load, 1e-9), t_all, t_load, tot, nproc
+
+
 def peaks():
     fn = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(fn):
@@ -157,12 +212,18 @@ def peaks():
 
 
 # ------------------------------------------------------------------------------------------------
+METRIC = "read pairs/sec (k=21, -ae)"
+FLAGS_TXT = {"thread": "align -k 21 -gc 85 3 -kf 4 1 -cth 45 -ae (restored graph threading, SURVEY §8(c) D1)",
+             "asgn": "align -k 21 -kf 4 1 -cth 45 -ae (asgn path: what the unmodified reference runs at HEAD, SURVEY F2)"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--mode", default="both", choices=["both", "thread", "asgn"], help="headline = thread; 'both' adds the asgn block")
     ap.add_argument("--pairs", type=int, default=10_000_000, help="read pairs per GPU per step")
     ap.add_argument("--loci", type=int, default=1000)
     ap.add_argument("--frac-locus", type=float, default=0.05)
@@ -179,31 +240,45 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
     dist = None
-    if world > 1:
+    if world > 1 and a.impl != "reference":
         import torch.distributed as dist           # plumbing only: rendezvous, barrier, max over ranks
         dist.init_process_group("gloo", rank=rank, world_size=world)
-
-    config = {"workload": f"synthetic {a.loci}-locus RPGG (8 haplotypes, 700 bp flanks), {a.pairs} simulated 150bp read pairs per GPU "
-                          f"({a.frac_locus:.0%} locus reads / rest background), align -k 21 -kf 4 1 -cth 45 -ae (asgn path, SURVEY F2)",
-              "pairs_per_gpu": a.pairs, "loci": a.loci, "k": K, "cth": CTH, "kf": [4, 1],
-              "l2_policy": "inputs larger than L2 (packed reads 1.3 GB/step >> 126 MB); no explicit flush"}
 
     workdir = tempfile.mkdtemp(prefix="dbt_bench_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
     try:
         if a.impl == "reference":
             if rank != 0:
                 return
-            return reference_arm(a, config, workdir)
-        b200_arm(a, config, workdir, rank, world, local, dist)
+            return reference_arm(a, workdir)
+        ix, pref, pool, hap_off = build_workload(a.loci, 20261104, workdir)
+        head = "asgn" if a.mode == "asgn" else "thread"
+        out = b200_mode(head, a, ix, pref, pool, hap_off, workdir, rank, world, local, dist)
+        if a.mode == "both":
+            sec = b200_mode("asgn", a, ix, pref, pool, hap_off, workdir, rank, world, local, dist)
+            if rank == 0:
+                out["asgn"] = {k: sec[k] for k in ("value", "unit", "ms_per_step", "e2e", "gpu_launches", "roofline", "cpu_baseline",
+                                                   "config", "counters_per_step_rank0")}
+        if rank == 0:
+            print(json.dumps(out))
     finally:
         shutil.rmtree(workdir, ignore_errors=True)
         if dist is not None:
             dist.destroy_process_group()
 
 
-def reference_arm(a, config, workdir):
-    if not ref_bin("danbing-tk"):
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/danbing-tk not built (needs /root/reference at build time)"}))
+def make_config(a, mode):
+    err = f", locus reads with {SUB_PPM/1e4:.1f}% substitutions + {INDEL_PPM/1e4:.2f}% indels" if mode == "thread" else ", error-free"
+    return {"workload": f"synthetic {a.loci}-locus RPGG (8 haplotypes, 700 bp flanks), {a.pairs} simulated 150bp read pairs per GPU "
+                        f"({a.frac_locus:.0%} locus reads{err} / rest background), {FLAGS_TXT[mode]}",
+            "mode": mode, "pairs_per_gpu": a.pairs, "loci": a.loci, "k": K, "cth": CTH, "kf": [4, 1],
+            "l2_policy": "inputs larger than L2 (packed reads 1.3 GB/step >> 126 MB); no explicit flush"}
+
+
+def reference_arm(a, workdir):
+    mode = "asgn" if a.mode == "asgn" else "thread"
+    exe = ref_bin("ref_harness" if mode == "thread" else "danbing-tk")
+    if not exe:
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built (needs /root/reference at build time)"}))
         return
     L = abi.load_library()
     nproc = os.cpu_count() or 1
@@ -211,41 +286,64 @@ def reference_arm(a, config, workdir):
     n = min(a.cpu_sample, a.pairs)
     reads = np.empty(n * 2 * RLEN, np.uint8)
     if L.dbt_device_count() > 0:
-        synth_reads(0, pool, hap_off, 0, n, 777, a.frac_locus, reads)
-    else:                                                     # no GPU for the generator: numpy background + locus mix
+        e = (SUB_PPM, INDEL_PPM) if mode == "thread" else (0, 0)
+        synth_reads(0, pool, hap_off, 0, n, 777, a.frac_locus, reads, *e)
+    else:                                                     # no GPU for the generator: background only
         rng = np.random.default_rng(777)
         reads[:] = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, len(reads))]
-    fa = os.path.join(workdir, "sample.fa")
-    write_fasta_sample(fa, reads, n)
     times = []
+    if mode == "asgn":
+        fa = os.path.join(workdir, "sample.fa")
+        write_fasta_sample(fa, reads, n)
+    used = nproc
     for i in range(a.warmup + a.steps):
-        t_q, t_all, t_load = run_reference(pref, fa, os.path.join(workdir, "ref"), nproc)
+        if mode == "thread":
+            t_q, t_all, t_load, _, used = run_reference_thread(pref, reads, n, workdir, nproc)
+        else:
+            t_q, t_all, t_load = run_reference(pref, fa, os.path.join(workdir, "ref"), nproc)
         if i >= a.warmup:
             times.append(t_q)
     ms = 1e3 * sum(times) / len(times)
     v = n / (ms / 1e3)
-    print(json.dumps({"impl": "reference", "metric": "read pairs/sec (k=21, -ae)", "value": v, "unit": "read pairs/s", "n_gpus": a.gpus,
+    how = ("reference functions (isThreadFeasible & helpers) compiled from /root/reference as oracle/_ref/ref_harness, caller cpp:2072-2088 restored (D1), "
+           f"{used} processes on shards of the sample (pairs as TSV in /dev/shm)") if mode == "thread" else \
+          f"unmodified oracle/_ref/danbing-tk -p {nproc}, FASTA in /dev/shm"
+    print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": "read pairs/s", "n_gpus": a.gpus,
                       "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
-                      "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": config,
-                      "cpu_baseline": {"value": v, "unit": "read pairs/s", "cores": nproc, "kind": "reference",
-                                       "sample": f"first {n} pairs of the workload as FASTA in /dev/shm; query phase = wall minus a zero-read (index load) run"},
+                      "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": make_config(a, mode),
+                      "cpu_baseline": {"value": v, "unit": "read pairs/s", "cores": used, "kind": "reference",
+                                       "sample": f"first {n} pairs of the workload; {how}; query phase = wall minus a zero-read (index load) run"},
                       "e2e": {"value": v, "unit": "read pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
-def b200_arm(a, config, workdir, rank, world, local, dist):
+def per_locus_multiset_equal(ix, a, b):
+    ro = np.concatenate([[0], np.cumsum(ix["tr_n"]).astype(np.int64)])
+    for l in range(len(ix["tr_n"])):
+        if not np.array_equal(np.sort(a[ro[l]:ro[l + 1]]), np.sort(b[ro[l]:ro[l + 1]])):
+            return False
+    return True
+
+
+def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dist):
+    thr = mode == "thread"
     L = abi.load_library()
     if L.dbt_device_count() <= local:
         raise RuntimeError("bench.py needs a CUDA device per rank: libdanbing_b200 has no CPU fallback")
-    ix, pref, pool, hap_off = build_workload(a.loci, 20261104, workdir)
+    config = make_config(a, mode)
     P = a.pairs
-    p = abi.default_params(k=K, cth=CTH, n_filter=4, nm_filter=1, nm_tr=40, flags=abi.F_KAM, max_read_len=RLEN,
+    flags = (abi.F_THREADING | abi.F_CORRECTION | abi.F_ALN | abi.F_ALN_MIN) if thr else abi.F_KAM
+    p = abi.default_params(k=K, cth=CTH, n_filter=4, nm_filter=1, nm_tr=40, flags=flags, max_read_len=RLEN,
                            max_batch_pairs=P, device=local)
+    p.thread_cth, p.max_ncorrection = 85, 3
     p.max_records = max(int(P * a.frac_locus * 1.5) + 4096, 65536)
     p.bucket_slots = a.bucket_slots
     p.table_load = a.table_load
     t = time.time()
-    ctx = abi.Context(p, abi.make_index_struct(ix))
-    log(f"[bench r{rank}] index resident in HBM ({time.time()-t:.1f}s)")
+    ixm = ix if thr else {k: v for k, v in ix.items() if not k.startswith("g_")}
+    ctx = abi.Context(p, abi.make_index_struct(ixm))
+    if thr and not ctx.threading:
+        raise RuntimeError("threading mode requested but the context did not enable restored threading")
+    log(f"[bench r{rank}] {mode}: index resident in HBM ({time.time()-t:.1f}s)")
     stats = np.zeros(8, np.uint64)
     abi.check(L, L.dbt_table_stats(ctx.h, abi.ptr(stats, abi.u64p)), "table_stats")
     if world > 1:
@@ -263,32 +361,30 @@ def b200_arm(a, config, workdir, rank, world, local, dist):
     nbytes = P * 2 * RLEN
     host, owner = abi.pinned_array(L, nbytes)
     t = time.time()
-    synth_reads(local, pool, hap_off, rank * P, P, 777, a.frac_locus, host)
+    synth_reads(local, pool, hap_off, rank * P, P, 777, a.frac_locus, host, *((SUB_PPM, INDEL_PPM) if thr else (0, 0)))
     offsets_np = np.arange(2 * P + 1, dtype=np.uint64) * RLEN
     off_pin, off_owner = abi.pinned_array(L, offsets_np.nbytes)
     off_pin.view(np.uint64)[:] = offsets_np
     offsets = off_pin.view(np.uint64)
-    log(f"[bench r{rank}] {P} pairs generated ({time.time()-t:.1f}s)")
+    log(f"[bench r{rank}] {mode}: {P} pairs generated ({time.time()-t:.1f}s)")
 
     def barrier():
         if dist is not None:
             dist.barrier()
 
-    def allmax(x):
-        if dist is None:
-            return x
-        import torch
-        tt = torch.tensor([x], dtype=torch.float64)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        return float(tt[0])
-
-    def allsum(x):
+    def allred(x, op):
         if dist is None:
             return x
         import torch
         tt = torch.tensor([float(x)], dtype=torch.float64)
-        dist.all_reduce(tt, op=dist.ReduceOp.SUM)
+        dist.all_reduce(tt, op=op)
         return float(tt[0])
+
+    def allmax(x):
+        return allred(x, dist.ReduceOp.MAX) if dist is not None else x
+
+    def allsum(x):
+        return allred(x, dist.ReduceOp.SUM) if dist is not None else x
 
     # ---- 1. kernel-only: reads resident in HBM ----
     batch = ctx.make_batch(host, offsets)
@@ -329,7 +425,7 @@ def b200_arm(a, config, workdir, rank, world, local, dist):
     abi.check(L, L.dbt_wait(ctx.h, 0), "wait")
     cnt = dict(zip(abi.COUNTER_NAMES, list(res.counters)))
     kt = ktimes.mean(axis=0)
-    t_sub, t_cmp, t_cand, t_gen = float(kt[1]), float(kt[2]), float(kt[3]), float(kt[4])
+    t_sub, t_cmp, t_cand, t_gen, t_thr = float(kt[1]), float(kt[2]), float(kt[3]), float(kt[4]), float(kt[5])
 
     # ---- roofline of the dominant kernel (algorithmic bytes: SURVEY.md §8(d)) ----
     # one logical probe = one 32 B sector, one count increment = 64 B read-modify-write, bases at 2 bits
@@ -337,30 +433,49 @@ def b200_arm(a, config, workdir, rank, world, local, dist):
     ncand = cnt["ncandidates"]
     p_sub = cnt["nhash0"] + 2 * ncand                       # ++nhash skips the iteration that breaks (cpp:176)
     bytes_sub = P * 75 + 32 * p_sub
-    # candidate stage: kfilter probes (nhash1) + one classification probe per k-mer of pairs reaching assignTRkmc + increments,
-    # split between the closed-form kernel and the generic kernel by the generic kernel's own counters
     g_h1, g_thr, g_inc = cnt["gen_nhash1"], cnt["gen_nThreadingReads"], cnt["gen_ninc"]
-    bytes_gen = 32 * (g_h1 + g_thr * nk) + 64 * g_inc
-    bytes_fast = 32 * ((cnt["nhash1"] - g_h1) + (cnt["nThreadingReads"] - g_thr) * nk) + 64 * (cnt["ninc"] - g_inc)
+    if thr:
+        # candidate stage = kfilter + vote only (no assignTRkmc); threading: one node look-up per k-mer step of the walk
+        # (cpp:1170), the look-ups of the correction code, one trResults look-up per k-mer of the edited vectors of
+        # counted pairs (cpp:2203-2208) and the increments.  All four are the reference algorithm's own counts.
+        bytes_gen = 32 * g_h1
+        bytes_fast = 32 * (cnt["nhash1"] - g_h1)
+        bytes_thr = 32 * (cnt["thr_walk"] + cnt["thr_ec"] + cnt["thr_cls"]) + 64 * cnt["ninc"]
+    else:
+        # candidate stage: kfilter probes (nhash1) + one classification probe per k-mer of pairs reaching assignTRkmc + increments,
+        # split between the closed-form kernel and the generic kernel by the generic kernel's own counters
+        bytes_gen = 32 * (g_h1 + g_thr * nk) + 64 * g_inc
+        bytes_fast = 32 * ((cnt["nhash1"] - g_h1) + (cnt["nThreadingReads"] - g_thr) * nk) + 64 * (cnt["ninc"] - g_inc)
+        bytes_thr = 0
     peak, peak_src = peaks()
     kern = {"subfilter_kernel": (t_sub, bytes_sub), "candidate_fast_kernel": (t_cand, bytes_fast), "candidate_kernel(generic)": (t_gen, bytes_gen)}
+    if thr:
+        kern["thread_kernel"] = (t_thr, bytes_thr)
     dom = max(kern, key=lambda n: kern[n][0])
     dom_ms, dom_bytes = kern[dom]
     ach = dom_bytes / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0
-    step_bytes = bytes_sub + bytes_fast + bytes_gen
+    step_bytes = bytes_sub + bytes_fast + bytes_gen + bytes_thr
     roofline = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
                 "kernel": dom, "kernel_ms": dom_ms, "algorithmic_bytes_per_launch": dom_bytes, "peak_source": peak_src,
-                "per_kernel_ms": {"subfilter": t_sub, "compaction": t_cmp, "candidate_fast": t_cand, "candidate_generic": t_gen},
+                "per_kernel_ms": {"subfilter": t_sub, "compaction": t_cmp, "candidate_fast": t_cand, "candidate_generic": t_gen, "thread": t_thr},
                 "per_kernel_GBps": {n: (bb / (ms_ / 1e3) / 1e9 if ms_ > 0 else 0.0) for n, (ms_, bb) in kern.items()},
                 "per_kernel_bytes": {n: bb for n, (ms_, bb) in kern.items()},
                 "generic_path_pairs": cnt["gen_pairs"], "candidate_pairs": ncand,
                 "step_bytes": step_bytes, "step_GBps": step_bytes / (step_ms / 1e3) / 1e9, "step_frac": step_bytes / (step_ms / 1e3) / 1e9 / peak}
+    if thr:
+        nthr_pairs = max(cnt["nThreadingReads"] // 2, 1)
+        roofline["thread_kernel"] = {"pairs": cnt["nThreadingReads"] // 2, "us_per_pair_per_sm_warp": None,
+                                     "probes_algorithmic_per_pair": (cnt["thr_walk"] + cnt["thr_ec"] + cnt["thr_cls"]) / nthr_pairs,
+                                     "probes_issued_per_pair": (cnt["thr_refresh"] + cnt["thr_ec"]) / nthr_pairs,
+                                     "Gprobes_per_s": (cnt["thr_refresh"] + cnt["thr_ec"]) / (t_thr / 1e3) / 1e9 if t_thr > 0 else 0.0}
+        del roofline["thread_kernel"]["us_per_pair_per_sm_warp"]
     # dram bytes per launch of the dominant kernel from the committed `ncu --set full` capture of this same workload
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        w = tj.get("workload", {})
-        if (w.get("pairs"), w.get("loci"), w.get("frac_locus")) == (P, a.loci, a.frac_locus) and dom in tj:
-            roofline["traffic"] = tj[dom]
+        w = tj.get(mode, tj).get("workload", {})
+        tm = tj.get(mode, tj)
+        if (w.get("pairs"), w.get("loci"), w.get("frac_locus")) == (P, a.loci, a.frac_locus) and dom in tm:
+            roofline["traffic"] = tm[dom]
             roofline["traffic_source"] = "profiles/traffic.json (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum)"
     except (OSError, ValueError):
         pass
@@ -376,7 +491,8 @@ def b200_arm(a, config, workdir, rank, world, local, dist):
     sb = min(a.sub_batch, P)
     nsub = (P + sb - 1) // sb
     stride = ctx.stride
-    recbuf = [np.zeros(p.max_records * stride, np.uint8) for _ in range(2)]
+    cap_sb = min(p.max_records, int(sb * a.frac_locus * 1.5) + 4096)
+    recbuf = [np.zeros(cap_sb * stride, np.uint8) for _ in range(2)]
     results = [abi.BatchResult() for _ in range(2)]
     d2h = [0]
 
@@ -390,7 +506,7 @@ def b200_arm(a, config, workdir, rank, world, local, dist):
                 nrec += int(results[s].n_records)
             b0, b1 = j * sb, min(P, (j + 1) * sb)
             bb = ctx.make_batch(host, offsets[2 * b0: 2 * b1 + 1], first_pair_index=rank * P + b0)
-            results[s].capacity = p.max_records
+            results[s].capacity = cap_sb
             results[s].records = abi.ptr(recbuf[s], abi.u8p)
             abi.check(L, L.dbt_submit(ctx.h, C.byref(bb), C.byref(results[s]), s), "submit")
             pending[s] = True
@@ -414,56 +530,64 @@ def b200_arm(a, config, workdir, rank, world, local, dist):
     e2e_ms = allmax((time.perf_counter() - t0) * 1e3) / a.steps
     e2e_value = world * P / (e2e_ms / 1e3)
     e2e = {"value": e2e_value, "unit": "read pairs/s", "h2d_bytes_per_step": int(nbytes + offsets_np.nbytes),
-           "d2h_bytes_per_step": int(d2h[0]), "ms_per_step": e2e_ms, "kam_records_per_step": nrec,
+           "d2h_bytes_per_step": int(d2h[0]), "ms_per_step": e2e_ms, ("aln_records_per_step" if thr else "kam_records_per_step"): nrec,
+           "record_bytes": int(stride),
            "input": "pinned host ASCII reads + u64 offsets, packed to 2 bits on the device", "sub_batch_pairs": sb}
-    trkmc, kmc, nmap, tot = ctx.download()
 
     # ---- 3. CPU reference on a bounded sample of the same reads, outputs diffed against the GPU ----
     cpu = None
     if rank == 0 and not a.no_cpu:
-        if ref_bin("danbing-tk"):
-            n = min(a.cpu_sample, P)
-            fa = os.path.join(workdir, "sample.fa")
-            write_fasta_sample(fa, host, n)
-            nproc = os.cpu_count() or 1
-            t_q, t_all, t_load = run_reference(pref, fa, os.path.join(workdir, "ref"), nproc)
+        nproc = os.cpu_count() or 1
+        n = min(a.cpu_sample, P)
+        if ref_bin("ref_harness" if thr else "danbing-tk"):
             # GPU on the same sample, compared through the reference's own output files
-            p2 = abi.default_params(k=K, cth=CTH, flags=0, max_read_len=RLEN, max_batch_pairs=n, device=local)
-            ctx2 = abi.Context(p2, abi.make_index_struct(rpgg_io.load_index(pref)))
+            p2 = abi.default_params(k=K, cth=CTH, flags=(flags & ~(abi.F_ALN | abi.F_ALN_MIN | abi.F_KAM)), max_read_len=RLEN, max_batch_pairs=n, device=local)
+            p2.thread_cth, p2.max_ncorrection = 85, 3
+            if thr:
+                ix2 = ixm                      # file order == array order for the harness comparison below (multisets per locus)
+            else:
+                ix2 = rpgg_io.load_index(pref)
+            ctx2 = abi.Context(p2, abi.make_index_struct(ix2))
             ctx2.run(host, offsets[: 2 * n + 1], capacity=0)
-            g_tr, g_kmc, g_nmap, _ = ctx2.download()
+            g_tr, g_kmc, g_nmap, g_cnt = ctx2.download()
             ctx2.close()
-            ref_counts = rpgg_io.read_ar(os.path.join(workdir, "ref.trkmc.ar"))
-            # file-order GPU counts vs unordered_map-order reference dump: compare per locus as multisets via the text keys
-            same_sum = int(ref_counts.sum()) == int(g_tr.sum())
-            ref_summary = open(os.path.join(workdir, "ref.tr.summary.txt")).read()
-            g_summary = "".join(f"{int(x)}\t{int(y)}\n" for x, y in zip(g_nmap, g_kmc))
-            per_locus_ok = True
-            ro = np.concatenate([[0], np.cumsum(ix["tr_n"]).astype(np.int64)])
-            for l in range(len(ix["tr_n"])):
-                if not np.array_equal(np.sort(ref_counts[ro[l]:ro[l + 1]]), np.sort(g_tr[ro[l]:ro[l + 1]])):
-                    per_locus_ok = False
-                    break
-            cpu = {"value": n / t_q, "unit": "read pairs/s", "cores": nproc, "kind": "reference",
-                   "sample": f"first {n} pairs of rank 0's batch as FASTA in /dev/shm, `danbing-tk -k 21 -kf 4 1 -cth 45 -ae -p {nproc}` (kam lines to /dev/null); "
-                             f"query phase {t_q:.2f}s = wall {t_all:.2f}s minus zero-read index load {t_load:.2f}s",
-                   "parity_vs_gpu": {"tr_summary_identical": ref_summary == g_summary, "trkmc_total_identical": same_sum,
-                                     "trkmc_per_locus_multiset_identical": per_locus_ok}}
+            if thr:
+                t_q, t_all, t_load, ref_counts, used = run_reference_thread(pref, host, n, workdir, nproc)
+                gc = dict(zip(abi.COUNTER_NAMES, [int(x) for x in g_cnt]))
+                cpu = {"value": n / t_q, "unit": "read pairs/s", "cores": used, "kind": "reference",
+                       "sample": f"first {n} pairs of rank 0's batch; the reference's isThreadFeasible & helpers compiled from /root/reference "
+                                 f"(oracle/_ref/ref_harness thread=85 corr=1 maxnc=3 aln=2, caller cpp:2072-2088 restored as glue, D1), {used} processes on "
+                                 f"contiguous shards (TSV in /dev/shm); query phase {t_q:.2f}s = wall {t_all:.2f}s minus zero-read index load {t_load:.2f}s",
+                       "parity_vs_gpu": {"trkmc_total_identical": int(ref_counts.sum()) == int(g_tr.sum()),
+                                         "trkmc_per_locus_multiset_identical": per_locus_multiset_equal(ix, ref_counts, g_tr),
+                                         "gpu_sample_counters": {k: gc[k] for k in ("nThreadingReads", "nFeasibleReads", "ninc")}}}
+            else:
+                fa = os.path.join(workdir, "sample.fa")
+                write_fasta_sample(fa, host, n)
+                t_q, t_all, t_load = run_reference(pref, fa, os.path.join(workdir, "ref"), nproc)
+                ref_counts = rpgg_io.read_ar(os.path.join(workdir, "ref.trkmc.ar"))
+                ref_summary = open(os.path.join(workdir, "ref.tr.summary.txt")).read()
+                g_summary = "".join(f"{int(x)}\t{int(y)}\n" for x, y in zip(g_nmap, g_kmc))
+                cpu = {"value": n / t_q, "unit": "read pairs/s", "cores": nproc, "kind": "reference",
+                       "sample": f"first {n} pairs of rank 0's batch as FASTA in /dev/shm, `danbing-tk -k 21 -kf 4 1 -cth 45 -ae -p {nproc}` (kam lines to /dev/null); "
+                                 f"query phase {t_q:.2f}s = wall {t_all:.2f}s minus zero-read index load {t_load:.2f}s",
+                       "parity_vs_gpu": {"tr_summary_identical": ref_summary == g_summary, "trkmc_total_identical": int(ref_counts.sum()) == int(g_tr.sum()),
+                                         "trkmc_per_locus_multiset_identical": per_locus_multiset_equal(ix, ref_counts, g_tr)}}
         else:
             cpu = {"value": None, "unit": "read pairs/s", "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
 
     total_inc = allsum(cnt["ninc"])
-    if rank == 0:
-        out = {"metric": "read pairs/sec (k=21, -ae)", "value": value, "unit": "read pairs/s", "n_gpus": world, "steps": a.steps,
-               "warmup": a.warmup, "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-               "dtype": "u64", "data": "synthetic", "config": config, "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches,
-               "roofline": roofline, "cpu_baseline": cpu,
-               "counters_per_step_rank0": cnt, "tr_kmer_increments_per_step_all_ranks": total_inc,
-               "index_table": {"buckets": int(stats[0]), "slots_per_bucket": int(stats[1]), "keys": int(stats[2]),
-                               "overflowed_buckets": int(stats[4]), "stash_keys": int(stats[5]), "bytes": int(stats[6]),
-                               "overflowed_stash_buckets": int(stats[7])}}
-        print(json.dumps(out))
+    out = {"metric": METRIC, "value": value, "unit": "read pairs/s", "n_gpus": world, "steps": a.steps,
+           "warmup": a.warmup, "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "u64", "data": "synthetic", "config": config, "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches,
+           "roofline": roofline, "cpu_baseline": cpu,
+           "counters_per_step_rank0": cnt, "tr_kmer_increments_per_step_all_ranks": total_inc,
+           "index_table": {"buckets": int(stats[0]), "slots_per_bucket": int(stats[1]), "keys": int(stats[2]),
+                           "overflowed_buckets": int(stats[4]), "stash_keys": int(stats[5]), "bytes": int(stats[6]),
+                           "overflowed_stash_buckets": int(stats[7])}}
     ctx.close()
+    del host, owner, off_pin, off_owner, offsets
+    return out
 
 
 if __name__ == "__main__":

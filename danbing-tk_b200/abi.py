@@ -21,8 +21,10 @@ LAYOUT_ASCII, LAYOUT_PACKED = 0, 1
 COUNTER_NAMES = ["nReads", "nShort", "nSubFiltered", "nKmerFiltered", "nBaitFiltered", "nQualFiltered",
                  "nLocusAssignFiltered", "nQCFiltered", "nThreadingReads", "nFeasibleReads", "nAsgnReads",
                  "nhash0", "nhash1", "ninc", "ncandidates", "nrecords",
-                 "gen_pairs", "gen_nhash1", "gen_nThreadingReads", "gen_ninc"]
-MEASUREMENT_COUNTERS = ("nrecords", "gen_pairs", "gen_nhash1", "gen_nThreadingReads", "gen_ninc")   # no reference counterpart
+                 "gen_pairs", "gen_nhash1", "gen_nThreadingReads", "gen_ninc",
+                 "thr_walk", "thr_ec", "thr_cls", "thr_refresh"]
+MEASUREMENT_COUNTERS = ("nrecords", "gen_pairs", "gen_nhash1", "gen_nThreadingReads", "gen_ninc",
+                        "thr_walk", "thr_ec", "thr_cls", "thr_refresh")   # no reference counterpart
 MF_KF, MF_HF, MF_BF, MF_QF, MF_AF, MF_RM = 1, 2, 4, 8, 16, 32
 
 u64p = C.POINTER(C.c_uint64)

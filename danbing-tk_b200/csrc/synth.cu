@@ -5,6 +5,9 @@
 // complemented far end, like src/sim_reads.cpp:74-104 of the reference), the rest is iid-uniform
 // ACGT background.  Output = fixed-length ASCII reads in the ABI's batch order
 // (read 2i = late mate = "/2", read 2i+1 = "/1").
+// dbt_synth_reads2 adds sequencing errors to the locus reads for the threading (P1) runs of S2/S5:
+// per emitted base a substitution with probability sub_ppm/1e6 and an insertion or deletion with
+// probability indel_ppm/1e6 each half (counter-based as well: read = f(seed, pair, mate)).
 #include <cstdint>
 #include <cstdio>
 #include <cuda_runtime.h>
@@ -15,7 +18,8 @@ __device__ __forceinline__ uint64_t smix(uint64_t x) {
 
 __global__ void synth_reads_kernel(const uint8_t* __restrict__ pool, const uint64_t* __restrict__ hap_off, uint32_t nhap,
                                    uint64_t first_pair, uint64_t npairs, uint64_t seed, uint32_t locus_per_million,
-                                   uint32_t rlen, uint32_t flen, uint8_t* __restrict__ out) {
+                                   uint32_t rlen, uint32_t flen, uint8_t* __restrict__ out,
+                                   uint32_t sub_ppm, uint32_t indel_ppm) {
 	const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (p >= npairs) return;
 	const uint64_t g = first_pair + p;
@@ -29,10 +33,30 @@ __global__ void synth_reads_kernel(const uint8_t* __restrict__ pool, const uint6
 		uint64_t b = hap_off[h], len = hap_off[h + 1] - b;
 		uint64_t beg = (len > flen) ? smix(r1) % (len - flen + 1) : 0;
 		const uint8_t* s = pool + b + beg;
-		for (uint32_t i = 0; i < rlen; ++i) o1[i] = s[i];
-		for (uint32_t i = 0; i < rlen; ++i) {
-			uint8_t c = s[flen - 1 - i];
-			o2[i] = c == 'A' ? 'T' : c == 'C' ? 'G' : c == 'G' ? 'C' : c == 'T' ? 'A' : 'N';
+		if (sub_ppm == 0 && indel_ppm == 0) {
+			for (uint32_t i = 0; i < rlen; ++i) o1[i] = s[i];
+			for (uint32_t i = 0; i < rlen; ++i) {
+				uint8_t c = s[flen - 1 - i];
+				o2[i] = c == 'A' ? 'T' : c == 'C' ? 'G' : c == 'G' ? 'C' : c == 'T' ? 'A' : 'N';
+			}
+		} else {
+			const uint32_t span = len < flen ? (uint32_t)len : flen;       // source bases available to either mate
+			for (int m = 0; m < 2; ++m) {
+				uint8_t* o = m ? o2 : o1;
+				uint64_t x = smix(r1 ^ (0xA5A5ull + m));
+				uint32_t src = 0;
+				for (uint32_t i = 0; i < rlen; ) {
+					x = smix(x);
+					const uint32_t u = (uint32_t)(x % 1000000u), v = (uint32_t)(x >> 40) & 3u;
+					if (u < indel_ppm / 2 && src + 1 < span) { ++src; continue; }                 // deletion: skip a source base
+					if (u < indel_ppm) { o[i++] = ACGT[v]; continue; }                            // insertion
+					uint8_t c = src < span ? (m ? s[span - 1 - src] : s[src]) : (uint8_t)'N';
+					if (m) c = c == 'A' ? 'T' : c == 'C' ? 'G' : c == 'G' ? 'C' : c == 'T' ? 'A' : 'N';
+					++src;
+					if (u - indel_ppm < sub_ppm && c != 'N') { uint8_t d = ACGT[v]; if (d == c) d = ACGT[(v + 1) & 3]; c = d; }
+					o[i++] = c;
+				}
+			}
 		}
 	} else {
 		uint64_t x = r0;
@@ -44,8 +68,9 @@ __global__ void synth_reads_kernel(const uint8_t* __restrict__ pool, const uint6
 }
 
 // pool/hap_off: host pointers; out: host pointer (pinned or pageable) OR, when out_is_device != 0, a device pointer.
-extern "C" int dbt_synth_reads(int device, const uint8_t* pool, const uint64_t* hap_off, uint32_t nhap, uint64_t first_pair,
-                               uint64_t npairs, uint64_t seed, double frac_locus, uint32_t rlen, uint32_t flen, uint8_t* out) {
+extern "C" int dbt_synth_reads2(int device, const uint8_t* pool, const uint64_t* hap_off, uint32_t nhap, uint64_t first_pair,
+                                uint64_t npairs, uint64_t seed, double frac_locus, uint32_t rlen, uint32_t flen, uint8_t* out,
+                                uint32_t sub_ppm, uint32_t indel_ppm) {
 	if (cudaSetDevice(device) != cudaSuccess) return -1;
 	uint8_t* dpool = nullptr; uint64_t* doff = nullptr; uint8_t* dout = nullptr;
 	const uint64_t pool_bytes = hap_off[nhap];
@@ -58,9 +83,14 @@ extern "C" int dbt_synth_reads(int device, const uint8_t* pool, const uint64_t* 
 	for (uint64_t p0 = 0; p0 < npairs && !rc; p0 += chunk) {
 		uint64_t n = npairs - p0 < chunk ? npairs - p0 : chunk;
 		synth_reads_kernel<<<(unsigned)((n + 127) / 128), 128>>>(dpool, doff, nhap, first_pair + p0, n, seed,
-		                                                          (uint32_t)(frac_locus * 1e6 + 0.5), rlen, flen, dout);
+		                                                          (uint32_t)(frac_locus * 1e6 + 0.5), rlen, flen, dout, sub_ppm, indel_ppm);
 		if (cudaMemcpy(out + p0 * 2 * rlen, dout, n * 2 * rlen, cudaMemcpyDeviceToHost) != cudaSuccess) rc = -3;
 	}
 	cudaFree(dpool); cudaFree(doff); cudaFree(dout);
 	return rc;
+}
+
+extern "C" int dbt_synth_reads(int device, const uint8_t* pool, const uint64_t* hap_off, uint32_t nhap, uint64_t first_pair,
+                               uint64_t npairs, uint64_t seed, double frac_locus, uint32_t rlen, uint32_t flen, uint8_t* out) {
+	return dbt_synth_reads2(device, pool, hap_off, nhap, first_pair, npairs, seed, frac_locus, rlen, flen, out, 0, 0);
 }

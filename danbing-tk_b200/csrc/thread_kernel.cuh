@@ -274,8 +274,9 @@ __device__ __noinline__ void edit_kmers_backward(TState& T, Txt& x, int& ki_io, 
 // Returns (warp-uniform) true when an edit was found; x.et/eg/score/nedits describe it.  err |= graph not closed.
 template <int B, int MAXJ>
 __device__ __noinline__ bool ec_score(const Table& gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ>& W,
-                                      uint32_t nrem, uint32_t mes, int lane, Txt& x, int& err) {
+                                      uint32_t nrem, uint32_t mes, int lane, Txt& x, int& err, uint32_t& n_ec) {
 	const uint64_t node = W.win[0];
+	if (lane == 0) ++n_ec;
 	// nts0 / nnds: getOutNodes(g, node), cpp:1170 / 1097
 	const GNode g0 = g_lookup<B>(gt, node, locus, K);
 	if (!(g0.bits & GN_PRESENT)) err = 1;
@@ -284,6 +285,7 @@ __device__ __noinline__ bool ec_score(const Table& gt, uint32_t locus, uint32_t 
 	uint32_t m1 = 0; uint64_t n1 = 0; bool bad = false;
 	if (lane < 4 && ((nts0 >> lane) & 1u)) {
 		n1 = ((node & rmask) << 2) + (uint64_t)lane;
+		++n_ec;
 		const GNode g = g_lookup<B>(gt, n1, locus, K);
 		if (!(g.bits & GN_PRESENT)) bad = true;
 		m1 = gn_mask(g.bits);
@@ -296,6 +298,7 @@ __device__ __noinline__ bool ec_score(const Table& gt, uint32_t locus, uint32_t 
 		if (lane < 16 && ((nts0 >> i) & 1u) && ((m1i >> j) & 1u)) {
 			const uint64_t n1i = ((node & rmask) << 2) + (uint64_t)i;
 			const uint64_t n2 = ((n1i & rmask) << 2) + (uint64_t)j;
+			++n_ec;
 			const GNode g = g_lookup<B>(gt, n2, locus, K);
 			if (!(g.bits & GN_PRESENT)) bad = true;
 			m2 = gn_mask(g.bits);
@@ -348,7 +351,7 @@ __device__ __noinline__ bool ec_score(const Table& gt, uint32_t locus, uint32_t 
 				if (!good(j)) break;
 				cr = ((cr & rmask) << 2) + (W.win[j + 1] & 3);
 				if (!((nn >> (cr & 3)) & 1u)) break;
-				++n;
+				++n; ++n_ec;
 				const GNode g = g_lookup<B>(gt, cr, locus, K);          // getNextNucs, cpp:547-557: assigns only when the node exists
 				if (g.bits & GN_PRESENT) nn = gn_mask(g.bits);
 			}
@@ -389,7 +392,7 @@ __device__ __noinline__ bool ec_score(const Table& gt, uint32_t locus, uint32_t 
 // ---- per-position probes + classification (the parallel replacement of the node-by-node walk) ----
 template <int B, int MAXJ>
 __device__ __forceinline__ void thr_refresh(const Table& gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ>& W,
-                                            int m, int nkm, int lane) {
+                                            int m, int nkm, int lane, uint32_t& n_refresh) {
 	__syncwarp();
 	constexpr int CH = 4;                                             // probes in flight per lane
 #pragma unroll 1
@@ -403,6 +406,7 @@ __device__ __forceinline__ void thr_refresh(const Table& gt, uint32_t locus, uin
 			if (valid[c]) {
 				const uint64_t fw = W.km[m][i], rc = kmer_rc(fw, K);
 				isrc[c] = rc < fw; canon[c] = isrc[c] ? rc : fw;
+				++n_refresh;
 				const uint4* bp = gt.slots + home_bucket(gt, g_hash_key(canon[c], locus)) * B;
 #pragma unroll
 				for (int q = 0; q < B; ++q) s[c][q] = ldg128(bp + q);
@@ -472,7 +476,7 @@ struct MateResult { int alned, err, nkm, nes, ntr; };
 // isThreadFeasible, cpp:1114-1260, for mate m of the pair held by warp state W.  Warp-uniform.
 template <int B, int MAXJ>
 __device__ __noinline__ MateResult thread_mate(const Table& gt, uint32_t locus, const RunParams& rp, ThreadWarp<MAXJ>& W, int m,
-                                               const uint64_t* __restrict__ rec, uint32_t len, int lane) {
+                                               const uint64_t* __restrict__ rec, uint32_t len, int lane, uint32_t* ctr) {
 	constexpr int CAP = ThreadWarp<MAXJ>::CAP, ECAP = ThreadWarp<MAXJ>::ECAP;
 	const uint32_t K = rp.k;
 	const uint64_t rmask = (1ull << 2 * (K - 1)) - 1;
@@ -497,7 +501,8 @@ __device__ __noinline__ MateResult thread_mate(const Table& gt, uint32_t locus, 
 	anyvalid = __any_sync(0xffffffffu, anyvalid);
 	__syncwarp();
 	if (!anyvalid) { R.nkm = 0; R.nes = nes; R.ntr = ntr; return R; }     // D1: a read without a valid k-mer is not threadable (cpp:1124 would be UB)
-	thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, nkm, lane);
+	thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, nkm, lane, ctr[2]);
+	if (lane == 0) ctr[0] += (uint32_t)nkm;
 
 	const uint64_t nkm0 = (uint64_t)nkm;
 	const uint64_t maxnskip = nkm0 >= rp.thread_cth ? nkm0 - rp.thread_cth : 0;
@@ -532,7 +537,7 @@ __device__ __noinline__ MateResult thread_mate(const Table& gt, uint32_t locus, 
 			}
 		}
 		__syncwarp();
-		return ec_score<B, MAXJ>(gt, locus, K, rmask, W, nrem, mes, lane, x, err);
+		return ec_score<B, MAXJ>(gt, locus, K, rmask, W, nrem, mes, lane, x, err, ctr[1]);
 	};
 	auto apply = [&](bool backward, int& kk) {                           // edit_kmers_forward / _backward on lane 0, then re-probe
 		__syncwarp();
@@ -547,7 +552,7 @@ __device__ __noinline__ MateResult thread_mate(const Table& gt, uint32_t locus, 
 		ncorr = __shfl_sync(0xffffffffu, ncorr, 0); nskip = __shfl_sync(0xffffffffu, nskip, 0);
 		x.nm = __shfl_sync(0xffffffffu, x.nm, 0); x.nd = __shfl_sync(0xffffffffu, x.nd, 0); x.nins = __shfl_sync(0xffffffffu, x.nins, 0);
 		x.a_lo = __shfl_sync(0xffffffffu, x.a_lo, 0); x.a_n = __shfl_sync(0xffffffffu, x.a_n, 0);
-		thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, nkm, lane);
+		thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, nkm, lane, ctr[2]);
 		if (!err) for (int q = lane; q < x.a_n; q += 32) W.tr[x.a_lo + q] = thr_bit<MAXJ>(W.cls[CL_T], x.a_lo + q) ? 2 : 1;   // cpp:850 / 690
 		__syncwarp();
 	};
@@ -666,7 +671,8 @@ __global__ void __launch_bounds__(THR_WARPS * 32) thread_kernel(DevIndex ix, Run
 	const bool aln_all = (rp.flags & DBT_F_ALN) && !(rp.flags & DBT_F_ALN_MIN), aln_min = (rp.flags & DBT_F_ALN_MIN) != 0;
 	const bool want_rec = trace || aln_all || aln_min;
 	const uint32_t W64 = rp.lay.W64;
-	uint32_t c_fea = 0, c_inc = 0;
+	uint32_t c_fea = 0, c_inc = 0, c_cls = 0;
+	uint32_t ctr[3] = {0, 0, 0};                                       // per lane: walk, ec, refresh probes (measurement)
 
 #pragma unroll 1
 	for (uint32_t t = gwarp; t < nwork; t += nwarps) {
@@ -681,7 +687,7 @@ __global__ void __launch_bounds__(THR_WARPS * 32) thread_kernel(DevIndex ix, Run
 #pragma unroll 1
 		for (int m = 0; m < 2; ++m) {
 			const uint32_t len = sv.meta[m][p] & META_LENMASK;
-			r[m] = thread_mate<B, MAXJ>(ix.gtable, dst, rp, W, m, sv.packed[m] + (uint64_t)p * W64, len, lane);
+			r[m] = thread_mate<B, MAXJ>(ix.gtable, dst, rp, W, m, sv.packed[m] + (uint64_t)p * W64, len, lane, ctr);
 			if (slot_ok) {                                              // sam_t.r1 / r2 -> dbt_aln_mate blob
 				uint8_t* b = rec + sizeof(dbt_pair_record) + (size_t)m * rp.aln_stride;
 				uint8_t* es = b + sizeof(dbt_aln_mate); uint8_t* trb = es + rp.es_cap;
@@ -713,6 +719,7 @@ __global__ void __launch_bounds__(THR_WARPS * 32) thread_kernel(DevIndex ix, Run
 				for (int j = 0; j * 32 < r[m].nkm; ++j) {
 					const int i = j * 32 + lane;
 					const uint32_t tx = i < r[m].nkm ? W.trx[m][i] : 0u;
+					if (i < r[m].nkm && W.km[m][i] != KMER_INVALID) ++c_cls;
 					const uint32_t tm = __ballot_sync(0xffffffffu, tx != 0);
 					if (!tm) continue;
 					inc_sum += __popc(tm);
@@ -742,7 +749,13 @@ __global__ void __launch_bounds__(THR_WARPS * 32) thread_kernel(DevIndex ix, Run
 			h->dst = fdst; h->status = (uint8_t)status;
 		}
 	}
+	c_cls = __reduce_add_sync(0xffffffffu, c_cls);
+	for (int q = 0; q < 3; ++q) ctr[q] = __reduce_add_sync(0xffffffffu, ctr[q]);
 	if (lane == 0) {
+		if (ctr[0]) atomicAdd(sv.counters + DBT_C_THR_WALK, (unsigned long long)ctr[0]);
+		if (ctr[1]) atomicAdd(sv.counters + DBT_C_THR_EC, (unsigned long long)ctr[1]);
+		if (ctr[2]) atomicAdd(sv.counters + DBT_C_THR_REFRESH, (unsigned long long)ctr[2]);
+		if (c_cls) atomicAdd(sv.counters + DBT_C_THR_CLS, (unsigned long long)c_cls);
 		if (c_fea) atomicAdd(sv.counters + DBT_C_NFEASIBLEREADS, (unsigned long long)c_fea);
 		if (c_inc) atomicAdd(sv.counters + DBT_C_NINC, (unsigned long long)c_inc);
 	}

@@ -89,6 +89,11 @@ enum {
   DBT_C_GEN_NHASH1,            /* their part of DBT_C_NHASH1                                    */
   DBT_C_GEN_NTHREADINGREADS,   /* their part of DBT_C_NTHREADINGREADS                           */
   DBT_C_GEN_NINC,              /* their part of DBT_C_NINC                                      */
+  /* measurement only: graph probes of restored threading as the REFERENCE algorithm issues them      */
+  DBT_C_THR_WALK,              /* k-mers of the mates handed to isThreadFeasible (one node look-up per step, cpp:1170) */
+  DBT_C_THR_EC,                /* look-ups inside errorCorrection_forward/backward: expansion (cpp:907-920) + extension walks */
+  DBT_C_THR_CLS,               /* valid k-mers of the edited vectors looked up in trResults (cpp:2203-2208) */
+  DBT_C_THR_REFRESH,           /* implementation detail: per-position probes this kernel actually issued */
   DBT_N_COUNTERS = 24
 };
 

@@ -25,6 +25,7 @@
 //   corr=0|1     0 = -g (no error correction), 1 = -gc (default 1)
 //   maxnc=E      -gc T E (maxncorrection, default 4)
 //   aln=0|1|2    1 = -a, 2 = -ae: legacy .aln lines on stdout through the reference's writeAlignments
+//   trace=0      do not write OUT.trace.tsv (bench.py's timed runs: the dump is harness work, not the reference's)
 //   PAIRS.tsv : one pair per line "seq1<TAB>seq2" in the reference's INTERNAL mate order
 //               (seq1 = seqs[2i] = the mate that arrived second, aQueryFasta_thread.cpp:1972-1974)
 //   writes OUT.trace.tsv, OUT.trkmc.ar, OUT.tr.summary.txt, OUT.counters.txt
@@ -51,6 +52,7 @@ int main(int argc, char* argv[]) {
 	bool okam = stoi(argv[9]);
 	bool threading = false, correction = true;
 	int aln = 0;
+	bool dotrace = true;
 	uint64_t thread_cth = 100;
 	string qcfile;
 	for (int i = 10; i < argc; ++i) {
@@ -62,6 +64,7 @@ int main(int argc, char* argv[]) {
 		else if (key == "corr")   { correction = stoi(val); }
 		else if (key == "maxnc")  { maxncorrection = stoul(val); }
 		else if (key == "aln")    { aln = stoi(val); }
+		else if (key == "trace")  { dotrace = stoi(val); }
 		else { cerr << "unknown option " << a << '\n'; return 2; }
 	}
 	bool qc = qcfile.size();
@@ -166,6 +169,7 @@ int main(int argc, char* argv[]) {
 				sams.push_back(sam);
 			}
 			ostringstream td;
+			if (dotrace) {
 			td << '\t' << dst_before;
 			for (int m = 0; m < 2; ++m) {
 				td << '\t' << alned[m] << '\t';
@@ -175,6 +179,7 @@ int main(int argc, char* argv[]) {
 				td << '\t';
 				for (size_t i = 0; i < ak[m].size(); ++i) { if (i) { td << ','; } td << (int64_t)ak[m][i]; }
 				if (not ak[m].size()) { td << '.'; }
+			}
 			}
 			thr_dump = td.str();
 		}
@@ -205,6 +210,7 @@ int main(int argc, char* argv[]) {
 		nh0 += nhash0;
 		nh1 += nhash1;
 		// ---- dump ----
+		if (not dotrace) { ++idx; continue; }
 		tr << idx << '\t' << status << '\t' << nhash0 << '\t' << nhash1 << '\t'
 		   << (status >= 3 ? (int64_t)destLocus : -1) << '\t' << (status >= 3 ? (int64_t)destLocus0 : -1) << '\t'
 		   << (status >= 3 ? nm1 : 0) << '\t' << (status >= 3 ? nm2 : 0);
