@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libdanbing_b200.so")
+LIB_PATH = os.environ.get("DBT_LIB") or os.path.join(HERE, "libdanbing_b200.so")   # DBT_LIB: kernel-variant experiments only
 
 DBT_N_COUNTERS = 24
 DBT_N_SLOTS = 2

@@ -26,7 +26,16 @@
 
 namespace dbt {
 
-constexpr int THR_WARPS = 4;
+#ifndef THR_WARPS_N
+#define THR_WARPS_N 4
+#endif
+#ifndef THR_MINBLOCKS
+#define THR_MINBLOCKS 4
+#endif
+#ifndef THR_REFRESH_INLINE
+#define THR_REFRESH_INLINE __noinline__
+#endif
+constexpr int THR_WARPS = THR_WARPS_N;
 constexpr uint64_t THR_MSC = 5;                    // min score for thread extension, cpp:1120
 
 // CIGAR entry codes (include/danbing_b200.h, dbt_aln_mate): type 0 '*' 1 '=' 2 'X' 3 'D' 4 'I'; base 0 none 1-4 ACGT 5 '*'
@@ -41,7 +50,6 @@ struct ThreadWarp {
 	static constexpr int ECAP = MAXJ * 32 + 32;    // CIGAR capacity (read length + deletions)
 	uint64_t km[2][CAP];                           // edited k-mer vectors of both mates (strand-specific, KMER_INVALID = -1)
 	uint32_t trx[2][CAP];                          // count-array position + 1 of each k-mer (0: not a TR k-mer of the locus)
-	uint32_t info[CAP];                            // GNode.bits of the mate being threaded
 	uint32_t cls[6][MAXJ];                         // ballots over positions: M, N, H, A, present, TR
 	uint64_t win[40];                              // k-mer window handed to the edit scorer
 	uint32_t score[64];                            // extension scores of the 62 candidate edits
@@ -273,7 +281,7 @@ __device__ __noinline__ void edit_kmers_backward(TState& T, Txt& x, int& ki_io, 
 // W.win[j+1] holds kmers[ki+j] for j = -1 .. k+1 (KMER_INVALID beyond the vector), nrem = nkmers - ki.
 // Returns (warp-uniform) true when an edit was found; x.et/eg/score/nedits describe it.  err |= graph not closed.
 template <int B, int MAXJ>
-__device__ __noinline__ bool ec_score(const Table& gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ>& W,
+__device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ>& W,
                                       uint32_t nrem, uint32_t mes, int lane, Txt& x, int& err, uint32_t& n_ec) {
 	const uint64_t node = W.win[0];
 	if (lane == 0) ++n_ec;
@@ -328,6 +336,19 @@ __device__ __noinline__ bool ec_score(const Table& gt, uint32_t locus, uint32_t 
 	const bool c_d2 = g0k && ((nts2 >> (w1 & 3)) & 1u) && mes >= 2;
 	const uint32_t e1 = nrem < K + 1 ? nrem : K + 1, e2 = nrem < K + 2 ? nrem : K + 2, e0 = nrem < K ? nrem : K;
 
+	// parallel-walk set-up (k <= 29: the k+3 window entries fit one ballot): validity of win[q] and the last base of
+	// win[q] packed at bits 2*(31-q) of PB, q = 1..k+2
+	const bool par = K + 3 <= 32;
+	const uint64_t kmask = K < 32 ? (1ull << 2 * K) - 1 : ~0ull;
+	uint32_t vmask = 0; uint64_t PB = 0;
+	if (par) {
+		const bool inq = (uint32_t)lane < K + 3 && (uint32_t)lane < gl + 1;       // good(j): j = q-1 < gl
+		const uint64_t wq = inq ? W.win[lane] : KMER_INVALID;
+		const bool vq = wq != KMER_INVALID;
+		vmask = __ballot_sync(0xffffffffu, vq);
+		const uint64_t pb = (vq && lane >= 1) ? ((wq & 3) << (2 * (31 - lane))) : 0ull;
+		PB = ((uint64_t)__reduce_or_sync(0xffffffffu, (uint32_t)(pb >> 32)) << 32) | __reduce_or_sync(0xffffffffu, (uint32_t)pb);
+	}
 	// score slots in get_edit's scan order families: [0,4) nem1, [4,8) ned1, 8 nei1, [9,25) nem2, [25,41) nemd, [41,57) ned2, [57,61) nemi, 61 nei2
 #pragma unroll 1
 	for (int round = 0; round < 2; ++round) {
@@ -346,14 +367,57 @@ __device__ __noinline__ bool ec_score(const Table& gt, uint32_t locus, uint32_t 
 		else if (w < 61)  { const uint32_t a = w - 57; act = c_mi && ((nts0 >> a) & 1u); cr = w1 - oldnt + a; nn = nnts1(a); jb = 2; je = e2; }
 		else if (w == 61) { act = c_i2; cr = node; nn = nts0; jb = 2; je = e2; }
 		uint32_t n = 0;
-		if (act) {                                                    // extension walk, cpp:931-940 and siblings
-			for (uint32_t j = jb; j < je; ++j) {
-				if (!good(j)) break;
-				cr = ((cr & rmask) << 2) + (W.win[j + 1] & 3);
-				if (!((nn >> (cr & 3)) & 1u)) break;
-				++n; ++n_ec;
-				const GNode g = g_lookup<B>(gt, cr, locus, K);          // getNextNucs, cpp:547-557: assigns only when the node exists
-				if (g.bits & GN_PRESENT) nn = gn_mask(g.bits);
+		if (!par) {
+			if (act) {                                                  // extension walk, cpp:931-940 and siblings (k > 29: one lane per candidate)
+				for (uint32_t j = jb; j < je; ++j) {
+					if (!good(j)) break;
+					cr = ((cr & rmask) << 2) + (W.win[j + 1] & 3);
+					if (!((nn >> (cr & 3)) & 1u)) break;
+					++n; ++n_ec;
+					const GNode g = g_lookup<B>(gt, cr, locus, K);        // getNextNucs, cpp:547-557: assigns only when the node exists
+					if (g.bits & GN_PRESENT) nn = gn_mask(g.bits);
+				}
+			}
+		} else {
+			// One candidate at a time, its walk spread over the lanes: step t of the walk visits the k-mer made of the
+			// candidate's start k-mer followed by t+1 read bases, which does not depend on the earlier steps, so all
+			// steps are probed at once (one round of latency instead of up to k+2) and the walk length is read off a
+			// ballot.  The chain "mask of the previous node" is exact while every visited node exists; otherwise the
+			// reference keeps the stale mask (cpp:553) and the scan below replays that literally.
+			uint32_t amask = __ballot_sync(0xffffffffu, act);
+			while (amask) {
+				const int src = __ffs(amask) - 1; amask &= amask - 1;
+				const uint64_t cr0 = __shfl_sync(0xffffffffu, cr, src);
+				const uint32_t nn0 = __shfl_sync(0xffffffffu, nn, src), jb0 = __shfl_sync(0xffffffffu, jb, src), je0 = __shfl_sync(0xffffffffu, je, src);
+				const uint32_t T = je0 > jb0 ? je0 - jb0 : 0u, t = (uint32_t)lane;
+				const uint32_t need = (2u << t) - 1u;                                   // t+1 low bits
+				const bool in = t < T && ((~(vmask >> (jb0 + 1)) & need) == 0u);       // win[jb0+1 .. jb0+t+1] all valid (good(j), cpp:922)
+				uint32_t msk = 0; bool pres = false; uint32_t b = 0;
+				if (in) {
+					const uint32_t nb = t + 1;                                            // bases appended so far
+					const uint64_t low = (PB >> (2 * (31 - (jb0 + nb)))) & ((1ull << (2 * nb)) - 1);
+					const uint64_t c = ((cr0 << (2 * nb)) | low) & kmask;
+					b = (uint32_t)(c & 3);
+					const GNode g = g_lookup<B>(gt, c, locus, K);
+					pres = (g.bits & GN_PRESENT) != 0; msk = gn_mask(g.bits);
+				}
+				const uint32_t pm = __shfl_up_sync(0xffffffffu, msk, 1);
+				const uint32_t nnt = t == 0 ? nn0 : pm;
+				const uint32_t okb = __ballot_sync(0xffffffffu, in && ((nnt >> b) & 1u));
+				const uint32_t prb = __ballot_sync(0xffffffffu, pres);
+				uint32_t nw = (uint32_t)__ffs(~okb) - 1u;                               // leading ok steps (T <= 29 < 32: ~okb != 0)
+				if ((prb & ((1u << nw) - 1u)) != ((1u << nw) - 1u)) {                   // a visited node is missing: literal scan
+					uint32_t cur = nn0; nw = 0;
+					for (uint32_t q = 0; q < T; ++q) {
+						const bool inq = (__shfl_sync(0xffffffffu, (uint32_t)in, q)) != 0;
+						const uint32_t bq = __shfl_sync(0xffffffffu, b, q), mq = __shfl_sync(0xffffffffu, msk, q);
+						const bool pq = (__shfl_sync(0xffffffffu, (uint32_t)pres, q)) != 0;
+						if (!inq || !((cur >> bq) & 1u)) break;
+						++nw; if (pq) cur = mq;
+					}
+				}
+				if (lane == src) n = nw;
+				if (lane == 0) n_ec += nw;
 			}
 		}
 		if (w < 64) W.score[w] = n;
@@ -390,60 +454,28 @@ __device__ __noinline__ bool ec_score(const Table& gt, uint32_t locus, uint32_t 
 }
 
 // ---- per-position probes + classification (the parallel replacement of the node-by-node walk) ----
+// ONE rolled loop, one probe per lane and iteration: the kernel is instruction-fetch bound (hot code must stay within
+// the 32 KB L1.5 I-cache, profiles/r1 s5/s6), and 16-20 resident warps x 32 lanes already keep > 500 probes in flight
+// per SM.  The class of position i needs the node of position i-1: shuffled in from the neighbour lane, lane 0 takes
+// the carry of the previous iteration.
 template <int B, int MAXJ>
-__device__ __forceinline__ void thr_refresh(const Table& gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ>& W,
+__device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ>& W,
                                             int m, int nkm, int lane, uint32_t& n_refresh) {
 	__syncwarp();
-	constexpr int CH = 4;                                             // probes in flight per lane
-#pragma unroll 1
-	for (int j0 = 0; j0 < MAXJ; j0 += CH) {
-		uint4 s[CH][B]; uint64_t canon[CH]; bool isrc[CH], valid[CH];
-#pragma unroll
-		for (int c = 0; c < CH; ++c) {
-			const int i = (j0 + c) * 32 + lane;
-			valid[c] = (j0 + c) < MAXJ && i < nkm && W.km[m][i] != KMER_INVALID;
-			canon[c] = 0; isrc[c] = false;
-			if (valid[c]) {
-				const uint64_t fw = W.km[m][i], rc = kmer_rc(fw, K);
-				isrc[c] = rc < fw; canon[c] = isrc[c] ? rc : fw;
-				++n_refresh;
-				const uint4* bp = gt.slots + home_bucket(gt, g_hash_key(canon[c], locus)) * B;
-#pragma unroll
-				for (int q = 0; q < B; ++q) s[c][q] = ldg128(bp + q);
-			}
-		}
-#pragma unroll
-		for (int c = 0; c < CH; ++c) {
-			if ((j0 + c) >= MAXJ) continue;
-			const int i = (j0 + c) * 32 + lane;
-			uint32_t bits = 0, trp = 0;
-			if (valid[c]) {
-				bool full = true, found = false;
-#pragma unroll
-				for (int q = 0; q < B; ++q) {
-					const uint64_t kk = slot_key(s[c][q]);
-					if (kk == SLOT_EMPTY) full = false;
-					else if ((kk & SLOT_KEYMASK) == canon[c] && (s[c][q].z & G_LOCUS_MASK) == locus) {
-						const GNode n = g_decode(s[c][q].z, s[c][q].w, isrc[c]); bits = n.bits; trp = n.tr; found = true;
-					}
-				}
-				if (!found && full && (slot_key(s[c][0]) & SLOT_OVF)) {   // continues in the stash: rare
-					const GNode n = g_lookup<B>(gt, W.km[m][i], locus, K); bits = n.bits; trp = n.tr;
-				}
-			}
-			W.info[i] = bits; W.trx[m][i] = trp;
-		}
-	}
-	__syncwarp();
+	uint64_t carry_f = KMER_INVALID; uint32_t carry_b = 0;
 #pragma unroll 1
 	for (int j = 0; j < MAXJ; ++j) {
 		const int i = j * 32 + lane;
 		const bool in = i < nkm;
 		const uint64_t f = in ? W.km[m][i] : KMER_INVALID;
-		const uint64_t pv = (in && i > 0) ? W.km[m][i - 1] : KMER_INVALID;
-		const uint32_t bi = in ? W.info[i] : 0u, bp = (in && i > 0) ? W.info[i - 1] : 0u;
-		const bool valid = in && f != KMER_INVALID;
-		const bool isN = in && f == KMER_INVALID;
+		const bool valid = f != KMER_INVALID;
+		uint32_t bi = 0, trp = 0;
+		if (valid) { const GNode n = g_lookup<B>(gt, f, locus, K); bi = n.bits; trp = n.tr; ++n_refresh; }
+		if (in) W.trx[m][i] = trp;
+		uint64_t pv = __shfl_up_sync(0xffffffffu, f, 1); uint32_t bp = __shfl_up_sync(0xffffffffu, bi, 1);
+		if (lane == 0) { pv = carry_f; bp = carry_b; }
+		carry_f = __shfl_sync(0xffffffffu, f, 31); carry_b = __shfl_sync(0xffffffffu, bi, 31);
+		const bool isN = in && !valid;
 		const bool isH = valid && i > 0 && f == pv;                      // cpp:1152 (the N test comes first, cpp:1145)
 		const bool isA = valid && i > 0 && pv == KMER_INVALID;           // cpp:1159
 		const bool isM = valid && i > 0 && pv != KMER_INVALID && f != pv && (((pv & rmask) << 2) + (f & 3)) == f
@@ -473,9 +505,95 @@ __device__ __forceinline__ bool thr_bit(const uint32_t* w, int i) { return (w[i 
 
 struct MateResult { int alned, err, nkm, nes, ntr; };
 
+// Mutable state of one mate's walk.  It lives in local memory on purpose: find_anchor / score / apply are single
+// out-of-line functions working on it by reference.  ncu (profiles/r1, s5) showed the kernel instruction-fetch bound
+// (stall_no_instruction 9.6 cycles per issue, 255 KB of SASS) while insensitive to occupancy; every inlined copy of
+// these helpers removed bought more than the few local loads/stores cost.
+struct MS {
+	int nkm, nes, ntr, ni, err, ki;
+	uint64_t nskip, ncorr;
+	Txt x;
+};
+
+// find_anchor, cpp:878-888
+template <int MAXJ>
+__device__ __noinline__ bool ms_find_anchor(ThreadWarp<MAXJ>& W, MS& S, int K, int lane) {
+	const int a = thr_next<MAXJ>(W.cls[CL_P], S.ki, S.nkm, true);
+	S.nskip += (uint64_t)(a - S.ki); S.ni += a - S.ki; S.ki = a;
+	if (a >= S.nkm) return false;
+	if (lane == 0) W.tr[a] = thr_bit<MAXJ>(W.cls[CL_T], a) ? 2 : 1;
+	const int ni = S.ni;
+	if (ni < 0 || ni + K > S.nes) S.err = 1;
+	else {
+#pragma unroll 1
+		for (int q = lane; q < K; q += 32) if (W.es_t[ni + q] == ET_STAR) W.es_t[ni + q] = ET_EQ;
+	}
+	__syncwarp();
+	return true;
+}
+
+// errorCorrection_forward (backward = false) / errorCorrection_backward (cpp:1091-1106: the same scorer on kmers_rc)
+template <int B, int MAXJ>
+__device__ __noinline__ bool ms_score(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ>& W, int m, MS& S,
+                                      bool backward, int kk, uint32_t mes, int lane, uint32_t* ctr) {
+	__syncwarp();
+	const int nkm = S.nkm;
+	uint32_t nrem;
+	if (!backward) {
+		nrem = (uint32_t)(nkm - kk);
+#pragma unroll 1
+		for (int q = lane; q < (int)K + 3; q += 32) { const int i = kk - 1 + q; W.win[q] = (i >= 0 && i < nkm) ? W.km[m][i] : KMER_INVALID; }
+	} else {                                                         // kmers_rc, cpp:1098-1103
+		nrem = (uint32_t)kk;
+#pragma unroll 1
+		for (int q = lane; q < (int)K + 3; q += 32) {
+			const int i = kk - q;
+			uint64_t v = KMER_INVALID;
+			if (i >= 0 && i < nkm && W.km[m][i] != KMER_INVALID) v = kmer_rc(W.km[m][i], K);
+			W.win[q] = v;
+		}
+	}
+	__syncwarp();
+	int err = S.err;
+	const bool ok = ec_score<B, MAXJ>(gt, locus, K, rmask, W, nrem, mes, lane, S.x, err, ctr[1]);
+	S.err = err;
+	return ok;
+}
+
+// edit_kmers_forward / _backward on lane 0, then re-probe every position and fill the annotation range
+template <int B, int MAXJ>
+__device__ __noinline__ void ms_apply(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ>& W, int m, MS& S,
+                                      bool backward, int* kkp, int lane, uint32_t* ctr) {
+	constexpr int CAP = ThreadWarp<MAXJ>::CAP, ECAP = ThreadWarp<MAXJ>::ECAP;
+	__syncwarp();
+	int kk = *kkp;
+	int nkm = S.nkm, nes = S.nes, ntr = S.ntr, ni = S.ni, err = S.err;
+	uint64_t ncorr = S.ncorr, nskip = S.nskip;
+	Txt x = S.x;
+	if (lane == 0) {
+		TState T; T.km = W.km[m]; T.es_t = W.es_t; T.es_r = W.es_r; T.es_g = W.es_g; T.tr = W.tr;
+		T.nkm = nkm; T.nes = nes; T.ntr = ntr; T.ni = ni; T.err = err; T.cap = CAP; T.ecap = ECAP; T.k = K; T.rmask = rmask;
+		if (backward) edit_kmers_backward(T, x, kk, ncorr, nskip); else edit_kmers_forward(T, x, kk, ncorr);
+		nkm = T.nkm; nes = T.nes; ntr = T.ntr; ni = T.ni; err = T.err;
+	}
+	nkm = __shfl_sync(0xffffffffu, nkm, 0); nes = __shfl_sync(0xffffffffu, nes, 0); ntr = __shfl_sync(0xffffffffu, ntr, 0);
+	ni = __shfl_sync(0xffffffffu, ni, 0); err = __shfl_sync(0xffffffffu, err, 0); kk = __shfl_sync(0xffffffffu, kk, 0);
+	ncorr = __shfl_sync(0xffffffffu, ncorr, 0); nskip = __shfl_sync(0xffffffffu, nskip, 0);
+	x.nm = __shfl_sync(0xffffffffu, x.nm, 0); x.nd = __shfl_sync(0xffffffffu, x.nd, 0); x.nins = __shfl_sync(0xffffffffu, x.nins, 0);
+	x.a_lo = __shfl_sync(0xffffffffu, x.a_lo, 0); x.a_n = __shfl_sync(0xffffffffu, x.a_n, 0);
+	thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, nkm, lane, ctr[2]);
+	if (!err) {                                                        // cpp:850 / 690
+#pragma unroll 1
+		for (int q = lane; q < x.a_n; q += 32) W.tr[x.a_lo + q] = thr_bit<MAXJ>(W.cls[CL_T], x.a_lo + q) ? 2 : 1;
+	}
+	__syncwarp();
+	S.nkm = nkm; S.nes = nes; S.ntr = ntr; S.ni = ni; S.err = err; S.ncorr = ncorr; S.nskip = nskip; S.x = x;
+	*kkp = kk;
+}
+
 // isThreadFeasible, cpp:1114-1260, for mate m of the pair held by warp state W.  Warp-uniform.
 template <int B, int MAXJ>
-__device__ __noinline__ MateResult thread_mate(const Table& gt, uint32_t locus, const RunParams& rp, ThreadWarp<MAXJ>& W, int m,
+__device__ __noinline__ MateResult thread_mate(const Table gt, uint32_t locus, const RunParams& rp, ThreadWarp<MAXJ>& W, int m,
                                                const uint64_t* __restrict__ rec, uint32_t len, int lane, uint32_t* ctr) {
 	constexpr int CAP = ThreadWarp<MAXJ>::CAP, ECAP = ThreadWarp<MAXJ>::ECAP;
 	const uint32_t K = rp.k;
@@ -483,185 +601,144 @@ __device__ __noinline__ MateResult thread_mate(const Table& gt, uint32_t locus, 
 	const uint64_t maxnc = rp.max_ncorrection;
 	const bool correction = rp.correction != 0;
 	MateResult R; R.alned = 0; R.err = 0;
-	int nkm = (int)len - (int)K + 1, nes = (int)len, ntr = nkm, ni = 0, err = 0;
-	if (nkm < 1 || nkm > CAP || nes > ECAP) { R.err = 1; R.nkm = 0; R.nes = 0; R.ntr = 0; return R; }
+	MS S;
+	S.nkm = (int)len - (int)K + 1; S.nes = (int)len; S.ntr = S.nkm; S.ni = 0; S.err = 0; S.ki = 0; S.nskip = 0; S.ncorr = 0;
+	S.x.score = 0; S.x.nedits = 0; S.x.nm = S.x.nd = S.x.nins = 0; S.x.nrk = 0; S.x.a_lo = 0; S.x.a_n = 0;
+	if (S.nkm < 1 || S.nkm > CAP || S.nes > ECAP) { R.err = 1; R.nkm = 0; R.nes = 0; R.ntr = 0; return R; }
 	// cigar_t::init (cpp:62-67) and read2kmers(.., canonical=false, keepN=true) (h:246-271)
 	__syncwarp();
 	bool anyvalid = false;
-	for (int i = lane; i < nes; i += 32) {
+#pragma unroll 1
+	for (int i = lane; i < S.nes; i += 32) {
 		const uint32_t code = (uint32_t)(rec[i >> 5] >> (2 * (i & 31))) & 3u;
 		const bool inv = (rec[rp.lay.WB + (i >> 6)] >> (i & 63)) & 1ull;
 		W.es_t[i] = ET_STAR; W.es_r[i] = inv ? ER_INVALID : (uint8_t)(code + 1); W.es_g[i] = 0;
 	}
-	for (int i = lane; i < nkm; i += 32) {
+#pragma unroll 1
+	for (int i = lane; i < S.nkm; i += 32) {
 		uint64_t f = KMER_INVALID;
 		if (extract_bits(rec + rp.lay.WB, (uint32_t)i, K) == 0) { f = rev2(extract_bits(rec, 2u * i, 2 * K)) >> (64 - 2 * K); anyvalid = true; }
 		W.km[m][i] = f; W.tr[i] = 0;
 	}
 	anyvalid = __any_sync(0xffffffffu, anyvalid);
 	__syncwarp();
-	if (!anyvalid) { R.nkm = 0; R.nes = nes; R.ntr = ntr; return R; }     // D1: a read without a valid k-mer is not threadable (cpp:1124 would be UB)
-	thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, nkm, lane, ctr[2]);
-	if (lane == 0) ctr[0] += (uint32_t)nkm;
+	if (!anyvalid) { R.nkm = 0; R.nes = S.nes; R.ntr = S.ntr; return R; }     // D1: a read without a valid k-mer is not threadable (cpp:1124 would be UB)
+	thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, S.nkm, lane, ctr[2]);
+	if (lane == 0) ctr[0] += (uint32_t)S.nkm;
 
-	const uint64_t nkm0 = (uint64_t)nkm;
+	const uint64_t nkm0 = (uint64_t)S.nkm;
 	const uint64_t maxnskip = nkm0 >= rp.thread_cth ? nkm0 - rp.thread_cth : 0;
-	int ki = 0;
-	uint64_t nskip = 0, ncorr = 0;
-	Txt x; x.score = 0; x.nedits = 0; x.nm = x.nd = x.nins = 0; x.nrk = 0; x.a_lo = 0; x.a_n = 0;
 	int result = -1;                                                   // -1: fall through to the final test (cpp:1259)
+#define FIND_ANCHOR() ms_find_anchor<MAXJ>(W, S, (int)K, lane)
+#define SCORE_AT(bw, kk, mes) ms_score<B, MAXJ>(gt, locus, K, rmask, W, m, S, bw, kk, mes, lane, ctr)
+#define APPLY(bw, kkp) ms_apply<B, MAXJ>(gt, locus, K, rmask, W, m, S, bw, kkp, lane, ctr)
 
-	auto find_anchor = [&]() -> bool {                                  // cpp:878-888
-		const int a = thr_next<MAXJ>(W.cls[CL_P], ki, nkm, true);
-		nskip += (uint64_t)(a - ki); ni += a - ki; ki = a;
-		if (a >= nkm) return false;
-		if (lane == 0) W.tr[ki] = thr_bit<MAXJ>(W.cls[CL_T], ki) ? 2 : 1;
-		if (ni < 0 || ni + (int)K > nes) err = 1;
-		else for (int q = lane; q < (int)K; q += 32) if (W.es_t[ni + q] == ET_STAR) W.es_t[ni + q] = ET_EQ;
-		__syncwarp();
-		return true;
-	};
-	auto score_at = [&](bool backward, int kk, uint32_t mes) -> bool {  // errorCorrection_forward / _backward
-		__syncwarp();
-		uint32_t nrem;
-		if (!backward) {
-			nrem = (uint32_t)(nkm - kk);
-			for (int q = lane; q < (int)K + 3; q += 32) { const int i = kk - 1 + q; W.win[q] = (i >= 0 && i < nkm) ? W.km[m][i] : KMER_INVALID; }
-		} else {                                                         // kmers_rc, cpp:1098-1103
-			nrem = (uint32_t)kk;
-			for (int q = lane; q < (int)K + 3; q += 32) {
-				const int i = kk - q;
-				uint64_t v = KMER_INVALID;
-				if (i >= 0 && i < nkm && W.km[m][i] != KMER_INVALID) v = kmer_rc(W.km[m][i], K);
-				W.win[q] = v;
-			}
-		}
-		__syncwarp();
-		return ec_score<B, MAXJ>(gt, locus, K, rmask, W, nrem, mes, lane, x, err, ctr[1]);
-	};
-	auto apply = [&](bool backward, int& kk) {                           // edit_kmers_forward / _backward on lane 0, then re-probe
-		__syncwarp();
-		if (lane == 0) {
-			TState T; T.km = W.km[m]; T.es_t = W.es_t; T.es_r = W.es_r; T.es_g = W.es_g; T.tr = W.tr;
-			T.nkm = nkm; T.nes = nes; T.ntr = ntr; T.ni = ni; T.err = err; T.cap = CAP; T.ecap = ECAP; T.k = K; T.rmask = rmask;
-			if (backward) edit_kmers_backward(T, x, kk, ncorr, nskip); else edit_kmers_forward(T, x, kk, ncorr);
-			nkm = T.nkm; nes = T.nes; ntr = T.ntr; ni = T.ni; err = T.err;
-		}
-		nkm = __shfl_sync(0xffffffffu, nkm, 0); nes = __shfl_sync(0xffffffffu, nes, 0); ntr = __shfl_sync(0xffffffffu, ntr, 0);
-		ni = __shfl_sync(0xffffffffu, ni, 0); err = __shfl_sync(0xffffffffu, err, 0); kk = __shfl_sync(0xffffffffu, kk, 0);
-		ncorr = __shfl_sync(0xffffffffu, ncorr, 0); nskip = __shfl_sync(0xffffffffu, nskip, 0);
-		x.nm = __shfl_sync(0xffffffffu, x.nm, 0); x.nd = __shfl_sync(0xffffffffu, x.nd, 0); x.nins = __shfl_sync(0xffffffffu, x.nins, 0);
-		x.a_lo = __shfl_sync(0xffffffffu, x.a_lo, 0); x.a_n = __shfl_sync(0xffffffffu, x.a_n, 0);
-		thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, nkm, lane, ctr[2]);
-		if (!err) for (int q = lane; q < x.a_n; q += 32) W.tr[x.a_lo + q] = thr_bit<MAXJ>(W.cls[CL_T], x.a_lo + q) ? 2 : 1;   // cpp:850 / 690
-		__syncwarp();
-	};
-
-	if (!find_anchor()) result = 0;                                     // cpp:1129
-	else if (ki > 0 && correction && ncorr < maxnc && (uint64_t)ki >= THR_MSC + 1) {   // leading unaligned k-mers, cpp:1131-1141
-		const uint32_t mes = ((uint64_t)ki >= 2 * THR_MSC + 2) ? 2 : 1;
-		if (score_at(true, ki, mes)) apply(true, ki);
+	if (!FIND_ANCHOR()) result = 0;                                     // cpp:1129
+	else if (S.ki > 0 && correction && S.ncorr < maxnc && (uint64_t)S.ki >= THR_MSC + 1) {   // leading unaligned k-mers, cpp:1131-1141
+		const uint32_t mes = ((uint64_t)S.ki >= 2 * THR_MSC + 2) ? 2 : 1;
+		if (SCORE_AT(true, S.ki, mes)) APPLY(true, &S.ki);
 	}
-	if (result < 0) { ++ki; ++ni; }
-	while (result < 0 && ki < nkm && !err) {                            // cpp:1144
+	if (result < 0) { ++S.ki; ++S.ni; }
+	// what to do at the end of an iteration: 0 = step (++ki, ++ni), 1 = find_anchor then the skip test and step, 2 = stop
+	while (result < 0 && S.ki < S.nkm && !S.err) {                      // cpp:1144
+		int tail = 0;
 		{	// run of matching k-mers: cpp:1167-1180 for every position at once
-			const int e = thr_next<MAXJ>(W.cls[CL_M], ki, nkm, false);
+			const int ki = S.ki;
+			const int e = thr_next<MAXJ>(W.cls[CL_M], ki, S.nkm, false);
 			if (e > ki) {
-				const int d = ni - ki + (int)K - 1;
-				if (d < 0 || e - 1 + d >= nes || e > ntr) { err = 1; break; }
+				const int d = S.ni - ki + (int)K - 1;
+				if (d < 0 || e - 1 + d >= S.nes || e > S.ntr) { S.err = 1; break; }
+#pragma unroll 1
 				for (int i = ki + lane; i < e; i += 32) { W.tr[i] = thr_bit<MAXJ>(W.cls[CL_T], i) ? 2 : 1; W.es_t[i + d] = ET_EQ; }
 				__syncwarp();
-				ni += e - ki; ki = e;
+				S.ni += e - ki; S.ki = e;
 			}
-			if (ki >= nkm) break;
+			if (S.ki >= S.nkm) break;
 		}
+		const int ki = S.ki;
 		if (thr_bit<MAXJ>(W.cls[CL_N], ki) || thr_bit<MAXJ>(W.cls[CL_H], ki)) {    // "N" in read / homopolymer run, cpp:1145-1158
 			int e = ki;
-			while (e < nkm && (thr_bit<MAXJ>(W.cls[CL_N], e) || thr_bit<MAXJ>(W.cls[CL_H], e))) ++e;
+			while (e < S.nkm && (thr_bit<MAXJ>(W.cls[CL_N], e) || thr_bit<MAXJ>(W.cls[CL_H], e))) ++e;
 			const uint64_t run = (uint64_t)(e - ki);
-			const uint64_t take = nskip > maxnskip ? 1 : (run < maxnskip - nskip + 1 ? run : maxnskip - nskip + 1);
-			const int d = ni - ki + (int)K - 1;
-			if (d < 0 || ki + (int)take - 1 + d >= nes || ki + (int)take > ntr) { err = 1; break; }
+			const uint64_t take = S.nskip > maxnskip ? 1 : (run < maxnskip - S.nskip + 1 ? run : maxnskip - S.nskip + 1);
+			const int d = S.ni - ki + (int)K - 1;
+			if (d < 0 || ki + (int)take - 1 + d >= S.nes || ki + (int)take > S.ntr) { S.err = 1; break; }
+#pragma unroll 1
 			for (int i = ki + lane; i < ki + (int)take; i += 32) { W.tr[i] = 0; W.es_t[i + d] = ET_STAR; }
 			__syncwarp();
-			nskip += take;
-			if (nskip > maxnskip) { result = 0; break; }
-			ki += (int)take; ni += (int)take;
+			S.nskip += take;
+			if (S.nskip > maxnskip) { result = 0; break; }
+			S.ki += (int)take; S.ni += (int)take;
 			continue;
 		}
-		if (thr_bit<MAXJ>(W.cls[CL_A], ki)) {                               // after an N, cpp:1159-1165
-			if (!find_anchor()) break;
-			if (nskip > maxnskip) { result = 0; break; }
-			++ki; ++ni; continue;
-		}
-		// no matching node: error correction, cpp:1181-1257
-		if ((uint64_t)ki + THR_MSC >= nkm0) {                               // not enough info, cpp:1182-1185
-			nskip += (nkm0 - (uint64_t)ki);
-			result = nskip <= maxnskip ? (ncorr ? 2 : 1) : 0;
+		if (thr_bit<MAXJ>(W.cls[CL_A], ki)) tail = 1;                       // after an N, cpp:1159-1165
+		else if ((uint64_t)ki + THR_MSC >= nkm0) {                          // no matching node, not enough info: cpp:1182-1185
+			S.nskip += (nkm0 - (uint64_t)ki);
+			result = S.nskip <= maxnskip ? (S.ncorr ? 2 : 1) : 0;
 			break;
 		}
-		if (correction && ncorr < maxnc) {
-			uint32_t mes = ((uint64_t)(nkm - ki) >= 2 * THR_MSC + 2) ? 2 : 1;
-			if (score_at(false, ki, mes)) {                                   // cpp:1192-1197
-				nskip += x.nedits;
-				if (nskip > maxnskip) { result = 0; break; }
-				apply(false, ki);
+		else if (!(correction && S.ncorr < maxnc)) tail = 1;                // cpp:1250-1256
+		else {                                                             // error correction, cpp:1186-1248
+			uint32_t mes = ((uint64_t)(S.nkm - ki) >= 2 * THR_MSC + 2) ? 2 : 1;
+			if (SCORE_AT(false, ki, mes)) {                                   // cpp:1192-1197
+				S.nskip += S.x.nedits;
+				if (S.nskip > maxnskip) { result = 0; break; }
+				APPLY(false, &S.ki);
 			} else {                                                          // cpp:1198-1248
-				if (!find_anchor()) break;
-				bool skip = !score_at(true, ki, 2);
+				if (!FIND_ANCHOR()) break;
+				bool skip = !SCORE_AT(true, S.ki, 2);
 				if (!skip) {
-					apply(true, ki);
-					++ncorr;
-					int64_t gap = (int64_t)min((int64_t)K, (int64_t)ki - (int64_t)x.nm - (int64_t)x.nd) - (int64_t)x.score;
-					int64_t ki1 = ki;
-					if (gap < 0) err = 1;
-					while (!skip && gap && !err) {                                // forward and backward threads not fully patched
+					APPLY(true, &S.ki);
+					++S.ncorr;
+					int64_t gap = (int64_t)min((int64_t)K, (int64_t)S.ki - (int64_t)S.x.nm - (int64_t)S.x.nd) - (int64_t)S.x.score;
+					int64_t ki1 = S.ki;
+					if (gap < 0) S.err = 1;
+					while (!skip && gap && !S.err) {                              // forward and backward threads not fully patched
 						const int64_t ki0 = ki1;
-						ki1 = ki0 - (int64_t)x.nm - (int64_t)x.nd - (int64_t)x.score;
-						if (ki1 < 0) { err = 1; break; }
+						ki1 = ki0 - (int64_t)S.x.nm - (int64_t)S.x.nd - (int64_t)S.x.score;
+						if (ki1 < 0) { S.err = 1; break; }
 						mes = ((uint64_t)ki1 >= 2 * THR_MSC + 2) ? 2 : 1;
 						if ((uint64_t)ki1 < THR_MSC + 1) break;
-						if (ki1 >= nkm || !thr_bit<MAXJ>(W.cls[CL_P], (int)ki1)) { err = 1; break; }   // assert(g.count(node_)), cpp:1222
-						skip = !score_at(true, (int)ki1, mes);
+						if (ki1 >= S.nkm || !thr_bit<MAXJ>(W.cls[CL_P], (int)ki1)) { S.err = 1; break; }   // assert(g.count(node_)), cpp:1222
+						skip = !SCORE_AT(true, (int)ki1, mes);
 						if (!skip) {
 							int k1 = (int)ki1;
-							apply(true, k1);
+							APPLY(true, &k1);
 							ki1 = k1;
-							ki += (int)x.nd - (int)x.nins;
-							gap = (int64_t)min((int64_t)K, ki1 - (int64_t)x.nm - (int64_t)x.nd) - (int64_t)x.score;
-							if (gap < 0) err = 1;
+							S.ki += (int)S.x.nd - (int)S.x.nins;
+							gap = (int64_t)min((int64_t)K, ki1 - (int64_t)S.x.nm - (int64_t)S.x.nd) - (int64_t)S.x.score;
+							if (gap < 0) S.err = 1;
 						}
 					}
-					if (gap > 0 && !err) {                                          // annot_gap, cpp:1108-1111
-						if (ki1 - gap < 0 || ki1 > ntr) err = 1;
+					if (gap > 0 && !S.err) {                                        // annot_gap, cpp:1108-1111
+						if (ki1 - gap < 0 || ki1 > S.ntr) S.err = 1;
 						else { for (int q = lane; q < (int)gap; q += 32) W.tr[ki1 - 1 - q] = 0; __syncwarp(); }
-						nskip -= (uint64_t)gap;
+						S.nskip -= (uint64_t)gap;
 					}
-					if (nskip > maxnskip) { result = 0; break; }
+					if (S.nskip > maxnskip) { result = 0; break; }
 				}
-				if (skip) {                                                       // cpp:1234-1243
-					if (!find_anchor()) break;
-					if (nskip > maxnskip) { result = 0; break; }
-					++ki; ++ni; continue;
-				}
+				if (skip) tail = 1;                                               // cpp:1234-1243
 			}
-		} else {                                                              // cpp:1250-1256
-			if (!find_anchor()) break;
-			if (nskip > maxnskip) { result = 0; break; }
-			++ki; ++ni; continue;
 		}
-		++ki; ++ni;
+		if (tail == 1) {
+			if (!FIND_ANCHOR()) break;
+			if (S.nskip > maxnskip) { result = 0; break; }
+		}
+		++S.ki; ++S.ni;
 	}
-	if (result < 0) result = (nskip <= maxnskip && ncorr <= maxnc) ? (ncorr ? 2 : 1) : 0;   // cpp:1259
-	if (err) result = 0;
-	R.alned = result; R.err = err; R.nkm = nkm; R.nes = nes; R.ntr = ntr;
+#undef FIND_ANCHOR
+#undef SCORE_AT
+#undef APPLY
+	if (result < 0) result = (S.nskip <= maxnskip && S.ncorr <= maxnc) ? (S.ncorr ? 2 : 1) : 0;   // cpp:1259
+	if (S.err) result = 0;
+	R.alned = result; R.err = S.err; R.nkm = S.nkm; R.nes = S.nes; R.ntr = S.ntr;
 	return R;
 }
 
 constexpr uint32_t THR_DST_MASK = (1u << G_LOCUS_BITS) - 1;           // sv.thr_dst[c] = dst | kf bits << 28 | rm bits << 30
 
 template <int B, int MAXJ>
-__global__ void __launch_bounds__(THR_WARPS * 32) thread_kernel(DevIndex ix, RunParams rp, SlotView sv) {
+__global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(DevIndex ix, RunParams rp, SlotView sv) {
 	extern __shared__ __align__(16) uint8_t thr_smem[];
 	ThreadWarp<MAXJ>& W = reinterpret_cast<ThreadWarp<MAXJ>*>(thr_smem)[threadIdx.x >> 5];
 	const int lane = threadIdx.x & 31;
@@ -693,7 +770,9 @@ __global__ void __launch_bounds__(THR_WARPS * 32) thread_kernel(DevIndex ix, Run
 				uint8_t* es = b + sizeof(dbt_aln_mate); uint8_t* trb = es + rp.es_cap;
 				const int nes = min(r[m].nes, (int)rp.es_cap), ntr = min(r[m].ntr, (int)rp.tr_cap);
 				if (r[m].nes > (int)rp.es_cap || r[m].ntr > (int)rp.tr_cap) r[m].err = 1;
+#pragma unroll 1
 				for (int i = lane; i < (int)rp.es_cap; i += 32) es[i] = i < nes ? (uint8_t)(W.es_t[i] | (W.es_g[i] << 3)) : (uint8_t)0;
+#pragma unroll 1
 				for (int i = lane; i < (int)rp.tr_cap; i += 32) trb[i] = i < ntr ? W.tr[i] : (uint8_t)0;
 				if (lane == 0) {
 					dbt_aln_mate* h = reinterpret_cast<dbt_aln_mate*>(b);
@@ -702,6 +781,7 @@ __global__ void __launch_bounds__(THR_WARPS * 32) thread_kernel(DevIndex ix, Run
 					uint64_t hash = 0;
 					if (trace) {                                            // FNV-1a over the edited k-mer vector (parity tests only)
 						hash = 0xcbf29ce484222325ull;
+#pragma unroll 1
 						for (int i = 0; i < r[m].nkm; ++i) { const uint64_t v = W.km[m][i]; for (int q = 0; q < 8; ++q) { hash ^= (v >> (8 * q)) & 0xFF; hash *= 0x100000001b3ull; } }
 					}
 					h->kmers_hash = hash;
@@ -740,6 +820,7 @@ __global__ void __launch_bounds__(THR_WARPS * 32) thread_kernel(DevIndex ix, Run
 			if (!trace) {                                                     // under DBT_F_TRACE the generic candidate kernel left the full header
 				h->pair_index = sv.first_pair_index + p; h->dst0 = dst; h->fc = 0; h->rc = 0; h->nhash0 = 0; h->nhash1 = 0;
 				h->pad[0] = h->pad[1] = h->pad[2] = 0;
+#pragma unroll 1
 				for (int m = 0; m < 2; ++m) {
 					dbt_mate_record& o = h->mate[m];
 					o.si = o.ei = o.si_ = o.ei_ = o.ti = -1; o.nt = 0; o.bs = 0; o.pad = 0; o.nk = 0;
@@ -750,6 +831,7 @@ __global__ void __launch_bounds__(THR_WARPS * 32) thread_kernel(DevIndex ix, Run
 		}
 	}
 	c_cls = __reduce_add_sync(0xffffffffu, c_cls);
+#pragma unroll 1
 	for (int q = 0; q < 3; ++q) ctr[q] = __reduce_add_sync(0xffffffffu, ctr[q]);
 	if (lane == 0) {
 		if (ctr[0]) atomicAdd(sv.counters + DBT_C_THR_WALK, (unsigned long long)ctr[0]);
