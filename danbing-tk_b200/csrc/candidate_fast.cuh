@@ -47,13 +47,6 @@ struct FastWarp {
 	dbt_mate_record mate[2];
 };
 
-__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
-	const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
-	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(d), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all() {
-	asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
-}
 
 template <int B, int MAXJ>
 __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel(DevIndex ix, RunParams rp, SlotView sv) {

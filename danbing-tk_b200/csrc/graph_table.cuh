@@ -67,17 +67,19 @@ __device__ __forceinline__ GNode g_lookup(const Table& t, uint64_t fw, uint32_t 
 	bool home = true;
 	for (;;) {
 		const uint4* bp = t.slots + b * B;
-		uint4 s[B];
-#pragma unroll
-		for (int i = 0; i < B; ++i) s[i] = ldg128(bp + i);
-		bool full = true;
-#pragma unroll
-		for (int i = 0; i < B; ++i) {
-			const uint64_t kk = slot_key(s[i]);
-			if (kk == SLOT_EMPTY) full = false;
-			else if ((kk & SLOT_KEYMASK) == canon && (s[i].z & G_LOCUS_MASK) == locus) return g_decode(s[i].z, s[i].w, is_rc);
+		// named registers, not an array: inside divergent callers nvcc kept `uint4 s[B]` in local memory (ncu: 50 M LDL/STL)
+		const uint4 s0 = ldg128(bp), s1 = ldg128(bp + 1);
+		uint4 s2 = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0, 0), s3 = s2;
+		if (B == 4) { s2 = ldg128(bp + 2); s3 = ldg128(bp + 3); }
+		const uint64_t k0 = slot_key(s0), k1 = slot_key(s1), k2 = slot_key(s2), k3 = slot_key(s3);
+		if ((k0 & SLOT_KEYMASK) == canon && k0 != SLOT_EMPTY && (s0.z & G_LOCUS_MASK) == locus) return g_decode(s0.z, s0.w, is_rc);
+		if ((k1 & SLOT_KEYMASK) == canon && k1 != SLOT_EMPTY && (s1.z & G_LOCUS_MASK) == locus) return g_decode(s1.z, s1.w, is_rc);
+		if (B == 4) {
+			if ((k2 & SLOT_KEYMASK) == canon && k2 != SLOT_EMPTY && (s2.z & G_LOCUS_MASK) == locus) return g_decode(s2.z, s2.w, is_rc);
+			if ((k3 & SLOT_KEYMASK) == canon && k3 != SLOT_EMPTY && (s3.z & G_LOCUS_MASK) == locus) return g_decode(s3.z, s3.w, is_rc);
 		}
-		if (!full || !(slot_key(s[0]) & SLOT_OVF)) { GNode n; n.bits = 0; n.tr = 0; return n; }
+		const bool full = k0 != SLOT_EMPTY && k1 != SLOT_EMPTY && (B == 2 || (k2 != SLOT_EMPTY && k3 != SLOT_EMPTY));
+		if (!full || !(k0 & SLOT_OVF)) { GNode n; n.bits = 0; n.tr = 0; return n; }
 		b = home ? stash_bucket(t, hk) : stash_next(t, b);
 		home = false;
 	}

@@ -62,6 +62,16 @@ __device__ __forceinline__ uint64_t slot_key(const uint4& s) { return ((uint64_t
 // read-only 128-bit load through the non-coherent path (the table is immutable after load_index)
 __device__ __forceinline__ uint4 ldg128(const uint4* p) { return __ldg(p); }
 
+// bucket staging: 16-byte asynchronous copies HBM/L2 -> shared memory, so that probe loops can be ROLLED (small code,
+// the kernels are instruction-fetch sensitive) and still keep every probe of a read in flight at once
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+	const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+	asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
 // Looks key up. Returns true on hit and sets val/aux. key must be < 2^63 and != invalid.
 template <int B>
 __device__ __forceinline__ bool table_lookup(const Table& t, uint64_t key, uint32_t& val, uint32_t& aux) {

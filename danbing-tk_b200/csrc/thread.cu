@@ -8,7 +8,7 @@ namespace dbt {
 
 template <int B, int MAXJ>
 static cudaError_t launch_thread_t(cudaStream_t st, int nsm, const DevIndex& ix, const RunParams& rp, const SlotView& sv) {
-	constexpr size_t smem = sizeof(ThreadWarp<MAXJ>) * THR_WARPS;
+	constexpr size_t smem = sizeof(ThreadWarp<MAXJ, B>) * THR_WARPS;
 	cudaError_t e = cudaFuncSetAttribute(thread_kernel<B, MAXJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 	if (e != cudaSuccess) return e;
 	int per_sm = 0;

@@ -44,13 +44,14 @@ constexpr uint8_t EG_STAR = 5, ER_INVALID = 6;     // read base that is not ACGT
 __device__ __forceinline__ bool et_is_edit(uint8_t t) { return t >= ET_X; }
 __device__ __forceinline__ uint8_t eg_comp(uint8_t g) { return (g >= 1 && g <= 4) ? (uint8_t)(5 - g) : (uint8_t)127; }   // baseComplement on characters, h:71-87
 
-template <int MAXJ>
+template <int MAXJ, int SB>
 struct ThreadWarp {
 	static constexpr int CAP = MAXJ * 32;          // k-mer vector / annotation capacity
 	static constexpr int ECAP = MAXJ * 32 + 32;    // CIGAR capacity (read length + deletions)
 	uint64_t km[2][CAP];                           // edited k-mer vectors of both mates (strand-specific, KMER_INVALID = -1)
 	uint32_t trx[2][CAP];                          // count-array position + 1 of each k-mer (0: not a TR k-mer of the locus)
 	uint32_t cls[6][MAXJ];                         // ballots over positions: M, N, H, A, present, TR
+	uint4    stage[MAXJ][SB][32];                  // home buckets of every position of the mate being probed (cp.async)
 	uint64_t win[40];                              // k-mer window handed to the edit scorer
 	uint32_t score[64];                            // extension scores of the 62 candidate edits
 	uint8_t  es_t[ECAP], es_r[ECAP], es_g[ECAP];   // cigar_t.es (cpp:53-60)
@@ -113,7 +114,7 @@ __device__ __forceinline__ uint64_t ts_km(TState& T, int i) { if (i < 0 || i >= 
 // thread_ext_t::edit_kmers_forward, cpp:828-862 (lane 0).  The reference snapshots good[]/nts[] of the tail before
 // editing (cpp:829-832); element `dt_nti` of those snapshots is exactly the not-yet-rewritten k-mer that sits at
 // position i when it is consumed (cpp:842-845), so the tail is read in place.
-__device__ __noinline__ void edit_kmers_forward(TState& T, Txt& x, int& ki_io, uint64_t& ncorrection) {
+__device__ __forceinline__ void edit_kmers_forward(TState& T, Txt& x, int& ki_io, uint64_t& ncorrection) {
 	const int ksize = (int)T.k;
 	int ki = ki_io;
 	x.nm = x.nd = x.nins = 0;
@@ -151,7 +152,7 @@ __device__ __noinline__ void edit_kmers_forward(TState& T, Txt& x, int& ki_io, u
 
 // thread_ext_t::edit_kmers_backward, cpp:649-826 (lane 0).  good[]/nts[] (cpp:651-656) are read in place for the
 // same reason as above: position i-1 is still the original prefix k-mer when cpp:683-686 rewrites it.
-__device__ __noinline__ void edit_kmers_backward(TState& T, Txt& x, int& ki_io, uint64_t& ncorrection, uint64_t& nskip) {
+__device__ __forceinline__ void edit_kmers_backward(TState& T, Txt& x, int& ki_io, uint64_t& ncorrection, uint64_t& nskip) {
 	const int ksize = (int)T.k;
 	int ki = ki_io;
 	const uint64_t lmask = 3ull << 2 * (ksize - 1), lbase = 1ull << 2 * (ksize - 1);
@@ -281,10 +282,10 @@ __device__ __noinline__ void edit_kmers_backward(TState& T, Txt& x, int& ki_io, 
 // W.win[j+1] holds kmers[ki+j] for j = -1 .. k+1 (KMER_INVALID beyond the vector), nrem = nkmers - ki.
 // Returns (warp-uniform) true when an edit was found; x.et/eg/score/nedits describe it.  err |= graph not closed.
 template <int B, int MAXJ>
-__device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ>& W,
-                                      uint32_t nrem, uint32_t mes, int lane, Txt& x, int& err, uint32_t& n_ec) {
+__device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ, B>& W,
+                                      uint32_t nrem, uint32_t mes, int lane, Txt& x, int& err, uint32_t& n_ec_out) {
 	const uint64_t node = W.win[0];
-	if (lane == 0) ++n_ec;
+	uint32_t n_ec = lane == 0 ? 1u : 0u;
 	// nts0 / nnds: getOutNodes(g, node), cpp:1170 / 1097
 	const GNode g0 = g_lookup<B>(gt, node, locus, K);
 	if (!(g0.bits & GN_PRESENT)) err = 1;
@@ -437,6 +438,7 @@ __device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K
 		{ const uint32_t s = W.score[61]; if (s > best && s >= ms2) { best = s; bw = 61; } }
 	}
 	__syncwarp();
+	n_ec_out += n_ec;
 	x.score = best; x.nedits = 0;
 	if (best == 0) return false;
 	if (bw < 4)        { x.nedits = 1; x.et[0] = ET_X; x.eg[0] = (uint8_t)(bw + 1); }
@@ -454,15 +456,31 @@ __device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K
 }
 
 // ---- per-position probes + classification (the parallel replacement of the node-by-node walk) ----
-// ONE rolled loop, one probe per lane and iteration: the kernel is instruction-fetch bound (hot code must stay within
-// the 32 KB L1.5 I-cache, profiles/r1 s5/s6), and 16-20 resident warps x 32 lanes already keep > 500 probes in flight
-// per SM.  The class of position i needs the node of position i-1: shuffled in from the neighbour lane, lane 0 takes
-// the carry of the previous iteration.
+// Two ROLLED loops (the kernel is instruction-fetch sensitive: hot code must stay inside the 32 KB L1.5 I-cache,
+// profiles/r1 s5-s7): loop A computes the home bucket of every position and starts its 32-byte copy into shared
+// memory with cp.async -- all <= MAXJ*32 probes of the read are in flight together -- loop B matches the staged
+// slots and classifies.  The class of position i needs the node of position i-1: shuffled in from the neighbour
+// lane, lane 0 takes the carry of the previous iteration.
 template <int B, int MAXJ>
-__device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ>& W,
+__device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ, B>& W,
                                             int m, int nkm, int lane, uint32_t& n_refresh) {
 	__syncwarp();
-	uint64_t carry_f = KMER_INVALID; uint32_t carry_b = 0;
+	const uint64_t lmix = (uint64_t)locus * 0xC2B2AE3D27D4EB4Full;         // g_hash_key
+#pragma unroll 1
+	for (int j = 0; j * 32 < nkm; ++j) {
+		const int i = j * 32 + lane;
+		const uint64_t f = i < nkm ? W.km[m][i] : KMER_INVALID;
+		if (f != KMER_INVALID) {
+			const uint64_t rc = kmer_rc(f, K);
+			const uint64_t canon = rc < f ? rc : f;
+			const uint4* bp = gt.slots + home_bucket(gt, canon ^ lmix) * B;
+#pragma unroll
+			for (int q = 0; q < B; ++q) cp_async16(&W.stage[j][q][lane], bp + q);
+		}
+	}
+	cp_async_wait_all();
+	__syncwarp();
+	uint64_t carry_f = KMER_INVALID; uint32_t carry_b = 0, nprobe = 0;
 #pragma unroll 1
 	for (int j = 0; j < MAXJ; ++j) {
 		const int i = j * 32 + lane;
@@ -470,7 +488,23 @@ __device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, u
 		const uint64_t f = in ? W.km[m][i] : KMER_INVALID;
 		const bool valid = f != KMER_INVALID;
 		uint32_t bi = 0, trp = 0;
-		if (valid) { const GNode n = g_lookup<B>(gt, f, locus, K); bi = n.bits; trp = n.tr; ++n_refresh; }
+		if (valid) {
+			const uint64_t rc = kmer_rc(f, K);
+			const bool is_rc = rc < f;
+			const uint64_t canon = is_rc ? rc : f;
+			bool full = true, found = false;
+			uint64_t k0 = 0;
+#pragma unroll
+			for (int q = 0; q < B; ++q) {
+				const uint4 sl = W.stage[j][q][lane];
+				const uint64_t kk = slot_key(sl);
+				if (q == 0) k0 = kk;
+				if (kk == SLOT_EMPTY) full = false;
+				else if ((kk & SLOT_KEYMASK) == canon && (sl.z & G_LOCUS_MASK) == locus) { const GNode n = g_decode(sl.z, sl.w, is_rc); bi = n.bits; trp = n.tr; found = true; }
+			}
+			if (!found && full && (k0 & SLOT_OVF)) { const GNode n = g_lookup<B>(gt, f, locus, K); bi = n.bits; trp = n.tr; }   // continues in the stash: rare
+			++nprobe;
+		}
 		if (in) W.trx[m][i] = trp;
 		uint64_t pv = __shfl_up_sync(0xffffffffu, f, 1); uint32_t bp = __shfl_up_sync(0xffffffffu, bi, 1);
 		if (lane == 0) { pv = carry_f; bp = carry_b; }
@@ -485,6 +519,7 @@ __device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, u
 		const uint32_t bt = __ballot_sync(0xffffffffu, valid && (bi & GN_TR));
 		if (lane == 0) { W.cls[CL_M][j] = bm; W.cls[CL_N][j] = bn; W.cls[CL_H][j] = bh; W.cls[CL_A][j] = ba; W.cls[CL_P][j] = bpz; W.cls[CL_T][j] = bt; }
 	}
+	n_refresh += nprobe;
 	__syncwarp();
 }
 
@@ -516,8 +551,8 @@ struct MS {
 };
 
 // find_anchor, cpp:878-888
-template <int MAXJ>
-__device__ __noinline__ bool ms_find_anchor(ThreadWarp<MAXJ>& W, MS& S, int K, int lane) {
+template <int B, int MAXJ>
+__device__ __noinline__ bool ms_find_anchor(ThreadWarp<MAXJ, B>& W, MS& S, int K, int lane) {
 	const int a = thr_next<MAXJ>(W.cls[CL_P], S.ki, S.nkm, true);
 	S.nskip += (uint64_t)(a - S.ki); S.ni += a - S.ki; S.ki = a;
 	if (a >= S.nkm) return false;
@@ -534,7 +569,7 @@ __device__ __noinline__ bool ms_find_anchor(ThreadWarp<MAXJ>& W, MS& S, int K, i
 
 // errorCorrection_forward (backward = false) / errorCorrection_backward (cpp:1091-1106: the same scorer on kmers_rc)
 template <int B, int MAXJ>
-__device__ __noinline__ bool ms_score(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ>& W, int m, MS& S,
+__device__ __noinline__ bool ms_score(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ, B>& W, int m, MS& S,
                                       bool backward, int kk, uint32_t mes, int lane, uint32_t* ctr) {
 	__syncwarp();
 	const int nkm = S.nkm;
@@ -562,9 +597,9 @@ __device__ __noinline__ bool ms_score(const Table gt, uint32_t locus, uint32_t K
 
 // edit_kmers_forward / _backward on lane 0, then re-probe every position and fill the annotation range
 template <int B, int MAXJ>
-__device__ __noinline__ void ms_apply(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ>& W, int m, MS& S,
+__device__ __noinline__ void ms_apply(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ, B>& W, int m, MS& S,
                                       bool backward, int* kkp, int lane, uint32_t* ctr) {
-	constexpr int CAP = ThreadWarp<MAXJ>::CAP, ECAP = ThreadWarp<MAXJ>::ECAP;
+	constexpr int CAP = ThreadWarp<MAXJ, B>::CAP, ECAP = ThreadWarp<MAXJ, B>::ECAP;
 	__syncwarp();
 	int kk = *kkp;
 	int nkm = S.nkm, nes = S.nes, ntr = S.ntr, ni = S.ni, err = S.err;
@@ -593,13 +628,12 @@ __device__ __noinline__ void ms_apply(const Table gt, uint32_t locus, uint32_t K
 
 // isThreadFeasible, cpp:1114-1260, for mate m of the pair held by warp state W.  Warp-uniform.
 template <int B, int MAXJ>
-__device__ __noinline__ MateResult thread_mate(const Table gt, uint32_t locus, const RunParams& rp, ThreadWarp<MAXJ>& W, int m,
+__device__ __noinline__ MateResult thread_mate(const Table gt, uint32_t locus, uint32_t K, uint32_t WB, uint32_t thread_cth, uint32_t maxnc32,
+                                               bool correction, ThreadWarp<MAXJ, B>& W, int m,
                                                const uint64_t* __restrict__ rec, uint32_t len, int lane, uint32_t* ctr) {
-	constexpr int CAP = ThreadWarp<MAXJ>::CAP, ECAP = ThreadWarp<MAXJ>::ECAP;
-	const uint32_t K = rp.k;
+	constexpr int CAP = ThreadWarp<MAXJ, B>::CAP, ECAP = ThreadWarp<MAXJ, B>::ECAP;
 	const uint64_t rmask = (1ull << 2 * (K - 1)) - 1;
-	const uint64_t maxnc = rp.max_ncorrection;
-	const bool correction = rp.correction != 0;
+	const uint64_t maxnc = maxnc32;
 	MateResult R; R.alned = 0; R.err = 0;
 	MS S;
 	S.nkm = (int)len - (int)K + 1; S.nes = (int)len; S.ntr = S.nkm; S.ni = 0; S.err = 0; S.ki = 0; S.nskip = 0; S.ncorr = 0;
@@ -611,13 +645,13 @@ __device__ __noinline__ MateResult thread_mate(const Table gt, uint32_t locus, c
 #pragma unroll 1
 	for (int i = lane; i < S.nes; i += 32) {
 		const uint32_t code = (uint32_t)(rec[i >> 5] >> (2 * (i & 31))) & 3u;
-		const bool inv = (rec[rp.lay.WB + (i >> 6)] >> (i & 63)) & 1ull;
+		const bool inv = (rec[WB + (i >> 6)] >> (i & 63)) & 1ull;
 		W.es_t[i] = ET_STAR; W.es_r[i] = inv ? ER_INVALID : (uint8_t)(code + 1); W.es_g[i] = 0;
 	}
 #pragma unroll 1
 	for (int i = lane; i < S.nkm; i += 32) {
 		uint64_t f = KMER_INVALID;
-		if (extract_bits(rec + rp.lay.WB, (uint32_t)i, K) == 0) { f = rev2(extract_bits(rec, 2u * i, 2 * K)) >> (64 - 2 * K); anyvalid = true; }
+		if (extract_bits(rec + WB, (uint32_t)i, K) == 0) { f = rev2(extract_bits(rec, 2u * i, 2 * K)) >> (64 - 2 * K); anyvalid = true; }
 		W.km[m][i] = f; W.tr[i] = 0;
 	}
 	anyvalid = __any_sync(0xffffffffu, anyvalid);
@@ -627,9 +661,9 @@ __device__ __noinline__ MateResult thread_mate(const Table gt, uint32_t locus, c
 	if (lane == 0) ctr[0] += (uint32_t)S.nkm;
 
 	const uint64_t nkm0 = (uint64_t)S.nkm;
-	const uint64_t maxnskip = nkm0 >= rp.thread_cth ? nkm0 - rp.thread_cth : 0;
+	const uint64_t maxnskip = nkm0 >= thread_cth ? nkm0 - thread_cth : 0;
 	int result = -1;                                                   // -1: fall through to the final test (cpp:1259)
-#define FIND_ANCHOR() ms_find_anchor<MAXJ>(W, S, (int)K, lane)
+#define FIND_ANCHOR() ms_find_anchor<B, MAXJ>(W, S, (int)K, lane)
 #define SCORE_AT(bw, kk, mes) ms_score<B, MAXJ>(gt, locus, K, rmask, W, m, S, bw, kk, mes, lane, ctr)
 #define APPLY(bw, kkp) ms_apply<B, MAXJ>(gt, locus, K, rmask, W, m, S, bw, kkp, lane, ctr)
 
@@ -740,7 +774,7 @@ constexpr uint32_t THR_DST_MASK = (1u << G_LOCUS_BITS) - 1;           // sv.thr_
 template <int B, int MAXJ>
 __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(DevIndex ix, RunParams rp, SlotView sv) {
 	extern __shared__ __align__(16) uint8_t thr_smem[];
-	ThreadWarp<MAXJ>& W = reinterpret_cast<ThreadWarp<MAXJ>*>(thr_smem)[threadIdx.x >> 5];
+	ThreadWarp<MAXJ, B>& W = reinterpret_cast<ThreadWarp<MAXJ, B>*>(thr_smem)[threadIdx.x >> 5];
 	const int lane = threadIdx.x & 31;
 	const uint32_t gwarp = blockIdx.x * THR_WARPS + (threadIdx.x >> 5), nwarps = gridDim.x * THR_WARPS;
 	const uint32_t nwork = sv.ncand[3];
@@ -764,7 +798,7 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 #pragma unroll 1
 		for (int m = 0; m < 2; ++m) {
 			const uint32_t len = sv.meta[m][p] & META_LENMASK;
-			r[m] = thread_mate<B, MAXJ>(ix.gtable, dst, rp, W, m, sv.packed[m] + (uint64_t)p * W64, len, lane, ctr);
+			r[m] = thread_mate<B, MAXJ>(ix.gtable, dst, rp.k, rp.lay.WB, rp.thread_cth, rp.max_ncorrection, rp.correction != 0, W, m, sv.packed[m] + (uint64_t)p * W64, len, lane, ctr);
 			if (slot_ok) {                                              // sam_t.r1 / r2 -> dbt_aln_mate blob
 				uint8_t* b = rec + sizeof(dbt_pair_record) + (size_t)m * rp.aln_stride;
 				uint8_t* es = b + sizeof(dbt_aln_mate); uint8_t* trb = es + rp.es_cap;
