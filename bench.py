@@ -492,7 +492,8 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
     nsub = (P + sb - 1) // sb
     stride = ctx.stride
     cap_sb = min(p.max_records, int(sb * a.frac_locus * 1.5) + 4096)
-    recbuf = [np.zeros(cap_sb * stride, np.uint8) for _ in range(2)]
+    recpin = [abi.pinned_array(L, cap_sb * stride) for _ in range(2)]      # pinned result buffers (dbt_host_alloc): records arrive by DMA
+    recbuf = [x[0] for x in recpin]
     results = [abi.BatchResult() for _ in range(2)]
     d2h = [0]
 
@@ -586,7 +587,7 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
                            "overflowed_buckets": int(stats[4]), "stash_keys": int(stats[5]), "bytes": int(stats[6]),
                            "overflowed_stash_buckets": int(stats[7])}}
     ctx.close()
-    del host, owner, off_pin, off_owner, offsets
+    del host, owner, off_pin, off_owner, offsets, recbuf, recpin
     return out
 
 

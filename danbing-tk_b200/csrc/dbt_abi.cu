@@ -71,8 +71,11 @@ struct Slot {
 	uint64_t* d_packed[2] = {nullptr, nullptr}; uint16_t* d_meta[2] = {nullptr, nullptr};
 	uint32_t* d_passmask = nullptr; uint32_t* d_blocksum = nullptr; uint32_t* d_cand = nullptr; uint32_t* d_ncand = nullptr; uint32_t* d_slow = nullptr; uint32_t* d_thr = nullptr; uint32_t* d_thr_dst = nullptr;
 	uint8_t* d_records = nullptr; unsigned long long* d_counters = nullptr;
-	uint8_t* h_records = nullptr;            // pinned staging
-	uint64_t* h_counters = nullptr;          // pinned: DBT_N_COUNTERS u64 + 4 u32 (ncand, err, nslow, -)
+	uint8_t* h_records = nullptr;            // pinned staging (DBT_F_TRACE, or a pageable caller buffer)
+	// record emission: emit bitmap -> ordered list -> dense copy of the records that become kam / aln records
+	uint8_t* d_records_out = nullptr; uint32_t* d_emitmask = nullptr; uint32_t* d_emitsum = nullptr; uint32_t* d_emitlist = nullptr; uint32_t* d_nemit = nullptr;
+	bool emitted = false;
+	uint64_t* h_counters = nullptr;          // pinned: DBT_N_COUNTERS u64 + 4 u32 (ncand, err, nslow, nthr) + u32 nemit
 	uint64_t last_ncand = 0, last_nslow = 0, last_nthr = 0;
 	uint64_t npairs = 0, first_pair_index = 0;
 	bool uploaded = false, processed = false, fetch_pending = false;
@@ -195,6 +198,7 @@ static void free_slot(Slot& s) {
 	cudaFree(s.d_ascii); cudaFree(s.d_offsets);
 	for (int m = 0; m < 2; ++m) { cudaFree(s.d_packed[m]); cudaFree(s.d_meta[m]); }
 	cudaFree(s.d_passmask); cudaFree(s.d_blocksum); cudaFree(s.d_cand); cudaFree(s.d_ncand); cudaFree(s.d_slow); cudaFree(s.d_thr); cudaFree(s.d_thr_dst); cudaFree(s.d_records); cudaFree(s.d_counters);
+	cudaFree(s.d_records_out); cudaFree(s.d_emitmask); cudaFree(s.d_emitsum); cudaFree(s.d_emitlist); cudaFree(s.d_nemit);
 	if (s.h_records) cudaFreeHost(s.h_records);
 	if (s.h_counters) cudaFreeHost(s.h_counters);
 	for (auto& e : s.ev) if (e) cudaEventDestroy(e);
@@ -246,8 +250,16 @@ static int ensure_slot(dbt_ctx* c, int si) {
 		TRY(dev_alloc(&s.d_records, (size_t)c->p.max_records * rp.rec_stride, "records"));
 		cudaError_t e = cudaHostAlloc((void**)&s.h_records, std::max<size_t>((size_t)c->p.max_records * rp.rec_stride, 16), cudaHostAllocDefault);
 		if (e != cudaSuccess) { cudaGetLastError(); return fail(DBT_E_NOMEM, "cudaHostAlloc(records): %s", cudaGetErrorString(e)); }
+		if (!(c->p.flags & DBT_F_TRACE)) {
+			const uint64_t ew = ((uint64_t)c->p.max_records + 31) / 32;
+			TRY(dev_alloc(&s.d_records_out, (size_t)c->p.max_records * rp.rec_stride, "records (dense)"));
+			TRY(dev_alloc(&s.d_emitmask, ew + 8, "emit mask"));
+			TRY(dev_alloc(&s.d_emitsum, (ew + COMPACT_WORDS_H - 1) / COMPACT_WORDS_H + 1, "emit blocksum"));
+			TRY(dev_alloc(&s.d_emitlist, (size_t)c->p.max_records + 32, "emit list"));
+			TRY(dev_alloc(&s.d_nemit, 4, "nemit"));
+		}
 	}
-	CU(cudaHostAlloc((void**)&s.h_counters, (DBT_N_COUNTERS + 2) * sizeof(uint64_t), cudaHostAllocDefault));
+	CU(cudaHostAlloc((void**)&s.h_counters, (DBT_N_COUNTERS + 4) * sizeof(uint64_t), cudaHostAllocDefault));
 	for (auto& e : s.ev) CU(cudaEventCreate(&e));
 	CU(cudaEventCreate(&s.t0)); CU(cudaEventCreate(&s.t1));
 	s.ready = true;
@@ -580,6 +592,18 @@ extern "C" int dbt_fetch(dbt_ctx* c, dbt_batch_result* r, int slot) {
 	Slot& s = c->slot[slot];
 	if (!s.processed) return fail(DBT_E_STATE, "slot %d has not been processed", slot);
 	if (!r) return fail(DBT_E_BADARG, "null result");
+	s.emitted = false;
+	if (s.d_records_out && r->records && s.npairs) {          // kam / aln records: compact on the device, in slot (= pair) order
+		const bool thr = c->rp.thr_on != 0, aln_min = (c->p.flags & DBT_F_ALN_MIN) != 0;
+		const bool okam = thr ? (c->p.flags & (DBT_F_ALN | DBT_F_ALN_MIN)) != 0 : (c->p.flags & DBT_F_KAM) != 0;
+		if (okam) {
+			CU(launch_record_emit(s.st, c->nsm, s.d_records, c->rp.rec_stride, s.d_ncand, c->p.max_records, (thr && !aln_min) ? 1 : 0,
+			                      s.d_emitmask, s.d_emitsum, s.d_emitlist, s.d_nemit, s.d_records_out));
+			c->launches += 5;
+			CU(cudaMemcpyAsync(reinterpret_cast<uint32_t*>(s.h_counters + DBT_N_COUNTERS + 2), s.d_nemit, 4, cudaMemcpyDeviceToHost, s.st));
+			s.emitted = true;
+		}
+	}
 	CU(cudaMemcpyAsync(s.h_counters, s.d_counters, DBT_N_COUNTERS * 8, cudaMemcpyDeviceToHost, s.st));
 	CU(cudaMemcpyAsync(s.h_counters + DBT_N_COUNTERS, s.d_ncand, 16, cudaMemcpyDeviceToHost, s.st));
 	s.result = r; s.fetch_pending = true;
@@ -610,7 +634,23 @@ extern "C" int dbt_wait(dbt_ctx* c, int slot) {
 	const bool aln_min = (c->p.flags & DBT_F_ALN_MIN) != 0, aln = (c->p.flags & (DBT_F_ALN | DBT_F_ALN_MIN)) != 0;
 	const bool trace = (c->p.flags & DBT_F_TRACE) != 0, okam = thr ? aln : (c->p.flags & DBT_F_KAM) != 0;
 	int rc = DBT_OK;
-	if ((trace || okam) && r->records) {
+	if (s.emitted) {
+		// dense records are already in slot order on the device: one copy straight into the caller's buffer
+		// (DMA when it is pinned -- dbt_host_alloc -- else staged through this slot's pinned buffer)
+		if (err & ERR_RECORD_OVERFLOW) rc = fail(DBT_E_CAPACITY, "%u candidate pairs exceed max_records=%u", ncand, c->p.max_records);
+		uint64_t n = *reinterpret_cast<const uint32_t*>(s.h_counters + DBT_N_COUNTERS + 2);
+		if (n > r->capacity) { rc = fail(DBT_E_CAPACITY, "result buffer holds %llu records, more are pending", (unsigned long long)r->capacity); n = r->capacity; }
+		if (n) {
+			const size_t bytes = (size_t)n * c->rp.rec_stride;
+			cudaPointerAttributes pa{};
+			const bool pinned = cudaPointerGetAttributes(&pa, r->records) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+			if (!pinned) cudaGetLastError();
+			CU(cudaMemcpyAsync(pinned ? r->records : s.h_records, s.d_records_out, bytes, cudaMemcpyDeviceToHost, s.st));
+			CU(cudaStreamSynchronize(s.st));
+			if (!pinned) memcpy(r->records, s.h_records, bytes);
+		}
+		r->n_records = n;
+	} else if ((trace || okam) && r->records) {
 		if (err & ERR_RECORD_OVERFLOW) rc = fail(DBT_E_CAPACITY, "%u candidate pairs exceed max_records=%u", ncand, c->p.max_records);
 		const uint64_t nslots = trace ? s.npairs : std::min<uint64_t>(ncand, c->p.max_records);
 		const uint32_t stride = c->rp.rec_stride;

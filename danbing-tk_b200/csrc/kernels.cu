@@ -149,29 +149,31 @@ __global__ void __launch_bounds__(256) subfilter_kernel(DevIndex ix, RunParams r
 // ============================================================================================
 constexpr int COMPACT_WORDS = 1024;      // bitmap words per block (32768 pairs)
 
-__global__ void __launch_bounds__(256) compact_count_kernel(SlotView sv) {
+// generic over (bitmap, nbits): used for the pass bitmap -> candidate list and for the record emit bitmap -> emit list
+__global__ void __launch_bounds__(256) compact_count_kernel(const uint32_t* __restrict__ mask, uint64_t nbits, uint32_t* __restrict__ blocksum) {
 	__shared__ uint32_t ssum[8];
-	const uint64_t nwords = (sv.npairs + 31) / 32;
+	const uint64_t nwords = (nbits + 31) / 32;
 	uint32_t c = 0;
 	for (int i = threadIdx.x; i < COMPACT_WORDS; i += 256) {
 		uint64_t w = (uint64_t)blockIdx.x * COMPACT_WORDS + i;
-		if (w < nwords) c += __popc(sv.passmask[w]);
+		if (w < nwords) c += __popc(mask[w]);
 	}
 	c = warp_sum(c);
 	if ((threadIdx.x & 31) == 0) ssum[threadIdx.x >> 5] = c;
 	__syncthreads();
-	if (threadIdx.x == 0) { uint32_t t = 0; for (int i = 0; i < 8; ++i) t += ssum[i]; sv.blocksum[blockIdx.x] = t; }
+	if (threadIdx.x == 0) { uint32_t t = 0; for (int i = 0; i < 8; ++i) t += ssum[i]; blocksum[blockIdx.x] = t; }
 }
 
-__global__ void __launch_bounds__(1024) compact_scan_kernel(SlotView sv, uint32_t nblocks) {
-	// single block; nblocks is small (npairs / 32768)
+__global__ void __launch_bounds__(1024) compact_scan_kernel(uint32_t* __restrict__ blocksum, uint32_t nblocks, uint32_t* __restrict__ out_count,
+                                                           unsigned long long* __restrict__ counter) {
+	// single block; nblocks is small (nbits / 32768)
 	__shared__ uint32_t carry;
 	__shared__ uint32_t wsum[32];
 	if (threadIdx.x == 0) carry = 0;
 	__syncthreads();
 	for (uint32_t base = 0; base < nblocks; base += 1024) {
 		uint32_t i = base + threadIdx.x;
-		uint32_t v = i < nblocks ? sv.blocksum[i] : 0, x = v;
+		uint32_t v = i < nblocks ? blocksum[i] : 0, x = v;
 #pragma unroll
 		for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if ((threadIdx.x & 31) >= o) x += y; }
 		if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = x;
@@ -184,26 +186,27 @@ __global__ void __launch_bounds__(1024) compact_scan_kernel(SlotView sv, uint32_
 		}
 		__syncthreads();
 		uint32_t excl = carry + wsum[threadIdx.x >> 5] + x - v;
-		if (i < nblocks) sv.blocksum[i] = excl;
+		if (i < nblocks) blocksum[i] = excl;
 		__syncthreads();
 		if (threadIdx.x == 1023) carry = excl + v;
 		__syncthreads();
 	}
 	if (threadIdx.x == 0) {
-		sv.ncand[0] = carry;
-		atomicAdd(sv.counters + DBT_C_NCANDIDATES, (unsigned long long)carry);
+		*out_count = carry;
+		if (counter) atomicAdd(counter, (unsigned long long)carry);
 	}
 }
 
-__global__ void __launch_bounds__(256) compact_scatter_kernel(SlotView sv) {
+__global__ void __launch_bounds__(256) compact_scatter_kernel(const uint32_t* __restrict__ mask, uint64_t nbits, const uint32_t* __restrict__ blocksum,
+                                                             uint32_t* __restrict__ out) {
 	__shared__ uint32_t wbase[8];
 	__shared__ uint32_t run;
-	const uint64_t nwords = (sv.npairs + 31) / 32;
-	if (threadIdx.x == 0) run = sv.blocksum[blockIdx.x];
+	const uint64_t nwords = (nbits + 31) / 32;
+	if (threadIdx.x == 0) run = blocksum[blockIdx.x];
 	__syncthreads();
 	for (int i0 = 0; i0 < COMPACT_WORDS; i0 += 256) {
 		uint64_t w = (uint64_t)blockIdx.x * COMPACT_WORDS + i0 + threadIdx.x;
-		uint32_t bits = w < nwords ? sv.passmask[w] : 0;
+		uint32_t bits = w < nwords ? mask[w] : 0;
 		uint32_t c = __popc(bits), x = c;
 #pragma unroll
 		for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if ((threadIdx.x & 31) >= o) x += y; }
@@ -212,10 +215,40 @@ __global__ void __launch_bounds__(256) compact_scatter_kernel(SlotView sv) {
 		uint32_t pre = run;
 		for (int j = 0; j < (int)(threadIdx.x >> 5); ++j) pre += wbase[j];
 		uint32_t o = pre + x - c;
-		while (bits) { int b = __ffs(bits) - 1; bits &= bits - 1; sv.cand[o++] = (uint32_t)(w * 32 + b); }
+		while (bits) { int b = __ffs(bits) - 1; bits &= bits - 1; out[o++] = (uint32_t)(w * 32 + b); }
 		__syncthreads();
 		if (threadIdx.x == 0) { uint32_t t = 0; for (int j = 0; j < 8; ++j) t += wbase[j]; run += t; }
 		__syncthreads();
+	}
+}
+
+// ============================================================================================
+// record emission (dbt_fetch): which record slots become kam / aln records -> ordered emit list -> dense copy.
+// Replaces a per-record host memcpy loop in dbt_wait (360 MB per 10 M-pair step in threading mode).
+// ============================================================================================
+// slot i < min(*nslots, cap): emit iff COUNTED, or THREAD_FAILED when `emit_failed` (`-a`: every pair that entered threading, cpp:2232-2239)
+__global__ void __launch_bounds__(256) record_flag_kernel(const uint8_t* __restrict__ records, uint32_t stride, const uint32_t* __restrict__ nslots,
+                                                         uint32_t cap, int emit_failed, uint32_t* __restrict__ mask) {
+	const uint32_t n = min(*nslots, cap);
+	const uint32_t i = blockIdx.x * 256 + threadIdx.x;
+	bool e = false;
+	if (i < n) {
+		const uint8_t st = reinterpret_cast<const dbt_pair_record*>(records + (size_t)i * stride)->status;
+		e = st == DBT_ST_COUNTED || (emit_failed && st == DBT_ST_THREAD_FAILED);
+	}
+	const uint32_t b = __ballot_sync(0xffffffffu, e);
+	if ((threadIdx.x & 31) == 0 && i < ((cap + 31) / 32) * 32) mask[i >> 5] = b;
+}
+
+// one warp per emitted record: out[j] = records[list[j]]; strides are multiples of 8 bytes
+__global__ void __launch_bounds__(256) record_gather_kernel(const uint8_t* __restrict__ records, uint32_t stride, const uint32_t* __restrict__ list,
+                                                           const uint32_t* __restrict__ nemit, uint8_t* __restrict__ out) {
+	const uint32_t n = *nemit;
+	const uint32_t lane = threadIdx.x & 31, nw = stride / 8;
+	for (uint32_t j = blockIdx.x * 8 + (threadIdx.x >> 5); j < n; j += gridDim.x * 8) {
+		const uint64_t* src = reinterpret_cast<const uint64_t*>(records + (size_t)list[j] * stride);
+		uint64_t* dst = reinterpret_cast<uint64_t*>(out + (size_t)j * stride);
+		for (uint32_t q = lane; q < nw; q += 32) dst[q] = src[q];
 	}
 }
 
@@ -332,9 +365,25 @@ cudaError_t launch_compact(cudaStream_t st, const SlotView& sv) {
 	uint64_t nwords = (sv.npairs + 31) / 32;
 	unsigned nblocks = (unsigned)((nwords + COMPACT_WORDS - 1) / COMPACT_WORDS);
 	if (!nblocks) nblocks = 1;
-	compact_count_kernel<<<nblocks, 256, 0, st>>>(sv);
-	compact_scan_kernel<<<1, 1024, 0, st>>>(sv, nblocks);
-	compact_scatter_kernel<<<nblocks, 256, 0, st>>>(sv);
+	compact_count_kernel<<<nblocks, 256, 0, st>>>(sv.passmask, sv.npairs, sv.blocksum);
+	compact_scan_kernel<<<1, 1024, 0, st>>>(sv.blocksum, nblocks, sv.ncand, sv.counters + DBT_C_NCANDIDATES);
+	compact_scatter_kernel<<<nblocks, 256, 0, st>>>(sv.passmask, sv.npairs, sv.blocksum, sv.cand);
+	return cudaGetLastError();
+}
+
+// records[0 .. min(*nslots, cap)) -> out[0 .. *nemit) in slot order; 5 launches
+cudaError_t launch_record_emit(cudaStream_t st, int nsm, const uint8_t* records, uint32_t stride, const uint32_t* nslots, uint32_t cap, int emit_failed,
+                               uint32_t* mask, uint32_t* blocksum, uint32_t* list, uint32_t* nemit, uint8_t* out) {
+	if (!cap) return cudaSuccess;
+	const unsigned fb = (cap + 255) / 256;
+	record_flag_kernel<<<fb, 256, 0, st>>>(records, stride, nslots, cap, emit_failed, mask);
+	const uint64_t nwords = ((uint64_t)cap + 31) / 32;
+	unsigned nblocks = (unsigned)((nwords + COMPACT_WORDS - 1) / COMPACT_WORDS);
+	if (!nblocks) nblocks = 1;
+	compact_count_kernel<<<nblocks, 256, 0, st>>>(mask, cap, blocksum);
+	compact_scan_kernel<<<1, 1024, 0, st>>>(blocksum, nblocks, nemit, nullptr);
+	compact_scatter_kernel<<<nblocks, 256, 0, st>>>(mask, cap, blocksum, list);
+	record_gather_kernel<<<(unsigned)nsm * 8, 256, 0, st>>>(records, stride, list, nemit, out);
 	return cudaGetLastError();
 }
 

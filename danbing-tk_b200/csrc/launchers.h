@@ -6,6 +6,8 @@ cudaError_t launch_pack(cudaStream_t st, const uint8_t* ascii, const uint64_t* o
                         uint64_t* p0, uint64_t* p1, uint16_t* m0, uint16_t* m1, uint32_t* err);
 cudaError_t launch_subfilter(cudaStream_t st, int B, int nsm, const DevIndex& ix, const RunParams& rp, const SlotView& sv);
 cudaError_t launch_compact(cudaStream_t st, const SlotView& sv);
+cudaError_t launch_record_emit(cudaStream_t st, int nsm, const uint8_t* records, uint32_t stride, const uint32_t* nslots, uint32_t cap, int emit_failed,
+                               uint32_t* mask, uint32_t* blocksum, uint32_t* list, uint32_t* nemit, uint8_t* out);
 cudaError_t launch_candidate(cudaStream_t st, int B, unsigned grid_fast, unsigned grid_slow, const DevIndex& ix, const RunParams& rp, const SlotView& sv, cudaEvent_t mid);
 cudaError_t launch_insert(cudaStream_t st, int B, Table t, const uint64_t* keys, const uint32_t* vals, uint64_t n, uint32_t* err);
 cudaError_t launch_fill_aux(cudaStream_t st, int B, Table t, const uint32_t* vv, uint32_t* vv_aux, const uint64_t* kmers,
