@@ -47,11 +47,11 @@ __device__ __forceinline__ uint64_t kmer_rc(uint64_t x, uint32_t k) {
 }
 
 __device__ __forceinline__ GNode g_decode(uint32_t lw, uint32_t tr, bool is_rc) {
-	const uint32_t mca = (lw >> 22) & 0xFu, mrc = (lw >> 26) & 0xFu;
-	const bool pca = lw & G_PRESENT_CA, prc = lw & G_PRESENT_RC;
+	// x = [mask_ca(0-3) | mask_rc(4-7) | present_ca(8) | present_rc(9)]; for the rc orientation swap the two halves
+	uint32_t x = lw >> 22;
+	if (is_rc) x = ((x & 0x10Fu) << 4 & 0xF0u) | ((x >> 4) & 0xFu) | ((x & 0x100u) << 1) | ((x >> 1) & 0x100u);
 	GNode n;
-	n.bits = (is_rc ? (prc ? GN_PRESENT : 0u) : (pca ? GN_PRESENT : 0u)) | ((is_rc ? mrc : mca) << 1) | ((is_rc ? mca : mrc) << 5)
-	       | ((is_rc ? pca : prc) ? GN_RCPRESENT : 0u) | (tr ? GN_TR : 0u);
+	n.bits = ((x >> 8) & 1u) | ((x & 0xFFu) << 1) | (x & 0x200u) | (tr ? GN_TR : 0u);
 	n.tr = tr;
 	return n;
 }

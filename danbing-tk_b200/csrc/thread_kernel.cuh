@@ -50,6 +50,7 @@ struct ThreadWarp {
 	static constexpr int ECAP = MAXJ * 32 + 32;    // CIGAR capacity (read length + deletions)
 	uint64_t km[2][CAP];                           // edited k-mer vectors of both mates (strand-specific, KMER_INVALID = -1)
 	uint32_t trx[2][CAP];                          // count-array position + 1 of each k-mer (0: not a TR k-mer of the locus)
+	uint64_t rck[CAP];                             // reverse complement of km[m][i] of the mate being threaded (free at extraction, kmer.cuh)
 	uint32_t cls[6][MAXJ];                         // ballots over positions: M, N, H, A, present, TR
 	uint4    stage[MAXJ][SB][32];                  // home buckets of every position of the mate being probed (cp.async)
 	uint64_t win[40];                              // k-mer window handed to the edit scorer
@@ -471,7 +472,7 @@ __device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, u
 		const int i = j * 32 + lane;
 		const uint64_t f = i < nkm ? W.km[m][i] : KMER_INVALID;
 		if (f != KMER_INVALID) {
-			const uint64_t rc = kmer_rc(f, K);
+			const uint64_t rc = W.rck[i];
 			const uint64_t canon = rc < f ? rc : f;
 			const uint4* bp = gt.slots + home_bucket(gt, canon ^ lmix) * B;
 #pragma unroll
@@ -489,7 +490,7 @@ __device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, u
 		const bool valid = f != KMER_INVALID;
 		uint32_t bi = 0, trp = 0;
 		if (valid) {
-			const uint64_t rc = kmer_rc(f, K);
+			const uint64_t rc = W.rck[i];
 			const bool is_rc = rc < f;
 			const uint64_t canon = is_rc ? rc : f;
 			bool full = true, found = false;
@@ -616,6 +617,9 @@ __device__ __noinline__ void ms_apply(const Table gt, uint32_t locus, uint32_t K
 	ncorr = __shfl_sync(0xffffffffu, ncorr, 0); nskip = __shfl_sync(0xffffffffu, nskip, 0);
 	x.nm = __shfl_sync(0xffffffffu, x.nm, 0); x.nd = __shfl_sync(0xffffffffu, x.nd, 0); x.nins = __shfl_sync(0xffffffffu, x.nins, 0);
 	x.a_lo = __shfl_sync(0xffffffffu, x.a_lo, 0); x.a_n = __shfl_sync(0xffffffffu, x.a_n, 0);
+	__syncwarp();
+#pragma unroll 1
+	for (int i = lane; i < nkm; i += 32) { const uint64_t f = W.km[m][i]; W.rck[i] = f == KMER_INVALID ? KMER_INVALID : kmer_rc(f, K); }
 	thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, nkm, lane, ctr[2]);
 	if (!err) {                                                        // cpp:850 / 690
 #pragma unroll 1
@@ -650,9 +654,12 @@ __device__ __noinline__ MateResult thread_mate(const Table gt, uint32_t locus, u
 	}
 #pragma unroll 1
 	for (int i = lane; i < S.nkm; i += 32) {
-		uint64_t f = KMER_INVALID;
-		if (extract_bits(rec + WB, (uint32_t)i, K) == 0) { f = rev2(extract_bits(rec, 2u * i, 2 * K)) >> (64 - 2 * K); anyvalid = true; }
-		W.km[m][i] = f; W.tr[i] = 0;
+		uint64_t f = KMER_INVALID, rc = KMER_INVALID;
+		if (extract_bits(rec + WB, (uint32_t)i, K) == 0) {
+			const uint64_t w = extract_bits(rec, 2u * i, 2 * K);
+			f = rev2(w) >> (64 - 2 * K); rc = (~w) & (K < 32 ? (1ull << 2 * K) - 1 : ~0ull); anyvalid = true;
+		}
+		W.km[m][i] = f; W.rck[i] = rc; W.tr[i] = 0;
 	}
 	anyvalid = __any_sync(0xffffffffu, anyvalid);
 	__syncwarp();
@@ -805,9 +812,19 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 				const int nes = min(r[m].nes, (int)rp.es_cap), ntr = min(r[m].ntr, (int)rp.tr_cap);
 				if (r[m].nes > (int)rp.es_cap || r[m].ntr > (int)rp.tr_cap) r[m].err = 1;
 #pragma unroll 1
-				for (int i = lane; i < (int)rp.es_cap; i += 32) es[i] = i < nes ? (uint8_t)(W.es_t[i] | (W.es_g[i] << 3)) : (uint8_t)0;
+				// four entries per lane and store (caps are multiples of 8, blobs 8-byte aligned); entries >= nes / ntr read 0
+				for (int q = lane; q < (int)rp.es_cap / 4; q += 32) {
+					const int nb = nes - 4 * q;
+					const uint32_t keep = nb >= 4 ? 0xFFFFFFFFu : (nb <= 0 ? 0u : (1u << 8 * nb) - 1u);
+					const uint32_t v = reinterpret_cast<const uint32_t*>(W.es_t)[q] | ((reinterpret_cast<const uint32_t*>(W.es_g)[q] & 0x07070707u) << 3);
+					reinterpret_cast<uint32_t*>(es)[q] = v & keep;
+				}
 #pragma unroll 1
-				for (int i = lane; i < (int)rp.tr_cap; i += 32) trb[i] = i < ntr ? W.tr[i] : (uint8_t)0;
+				for (int q = lane; q < (int)rp.tr_cap / 4; q += 32) {
+					const int nb = ntr - 4 * q;
+					const uint32_t keep = nb >= 4 ? 0xFFFFFFFFu : (nb <= 0 ? 0u : (1u << 8 * nb) - 1u);
+					reinterpret_cast<uint32_t*>(trb)[q] = reinterpret_cast<const uint32_t*>(W.tr)[q] & keep;
+				}
 				if (lane == 0) {
 					dbt_aln_mate* h = reinterpret_cast<dbt_aln_mate*>(b);
 					h->alned = (uint8_t)r[m].alned; h->err = (uint8_t)r[m].err;
