@@ -236,6 +236,7 @@ def main():
     a = ap.parse_args()
     a.steps, a.warmup = max(a.steps, 1), max(a.warmup, 0)
 
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")      # keep stdout to the one JSON line (NCCL prints its version banner there)
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
