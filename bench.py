@@ -333,6 +333,8 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
     config = make_config(a, mode)
     P = a.pairs
     flags = (abi.F_THREADING | abi.F_CORRECTION | abi.F_ALN | abi.F_ALN_MIN) if thr else abi.F_KAM
+    if thr and os.environ.get("DBT_BENCH_NOCORR"):          # kernel experiments only: `-g 85` (exact threading, no error correction)
+        flags &= ~abi.F_CORRECTION
     p = abi.default_params(k=K, cth=CTH, n_filter=4, nm_filter=1, nm_tr=40, flags=flags, max_read_len=RLEN,
                            max_batch_pairs=P, device=local)
     p.thread_cth, p.max_ncorrection = 85, 3
