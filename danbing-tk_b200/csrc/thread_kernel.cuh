@@ -54,7 +54,7 @@ struct ThreadWarp {
 	uint32_t cls[6][MAXJ];                         // ballots over positions: M, N, H, A, present, TR
 	uint4    stage[MAXJ][SB][32];                  // home buckets of every position of the mate being probed (cp.async)
 	uint64_t win[40];                              // k-mer window handed to the edit scorer
-	uint32_t score[64];                            // extension scores of the 62 candidate edits
+	uint32_t info[CAP];                            // GNode.bits of every position of the mate being threaded (thr_refresh)
 	uint8_t  es_t[ECAP], es_r[ECAP], es_g[ECAP];   // cigar_t.es (cpp:53-60)
 	uint8_t  tr[CAP];                              // cigar_t.tr: 0 '*' 1 '.' 2 '='
 	int      sc[12];                               // scalars published by lane 0
@@ -284,13 +284,13 @@ __device__ __forceinline__ void edit_kmers_backward(TState& T, Txt& x, int& ki_i
 // Returns (warp-uniform) true when an edit was found; x.et/eg/score/nedits describe it.  err |= graph not closed.
 template <int B, int MAXJ>
 __device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ, B>& W,
-                                      uint32_t nrem, uint32_t mes, int lane, Txt& x, int& err, uint32_t& n_ec_out) {
+                                      uint32_t nrem, uint32_t mes, int lane, Txt& x, int& err, uint32_t& n_ec_out, uint32_t g0bits) {
 	const uint64_t node = W.win[0];
 	uint32_t n_ec = lane == 0 ? 1u : 0u;
-	// nts0 / nnds: getOutNodes(g, node), cpp:1170 / 1097
-	const GNode g0 = g_lookup<B>(gt, node, locus, K);
-	if (!(g0.bits & GN_PRESENT)) err = 1;
-	const uint32_t nts0 = gn_mask(g0.bits);
+	// nts0 / nnds: getOutNodes(g, node), cpp:1170 / 1097 -- the node is a k-mer of the read (or its reverse complement)
+	// that thr_refresh has already probed: g0bits = its GNode bits in the walk's orientation (W.info)
+	if (!(g0bits & GN_PRESENT)) err = 1;
+	const uint32_t nts0 = gn_mask(g0bits);
 	// level 1 (lanes 0-3) and level 2 (lanes 0-15) of the expansion, cpp:907-920
 	uint32_t m1 = 0; uint64_t n1 = 0; bool bad = false;
 	if (lane < 4 && ((nts0 >> lane) & 1u)) {
@@ -351,6 +351,8 @@ __device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K
 		const uint64_t pb = (vq && lane >= 1) ? ((wq & 3) << (2 * (31 - lane))) : 0ull;
 		PB = ((uint64_t)__reduce_or_sync(0xffffffffu, (uint32_t)(pb >> 32)) << 32) | __reduce_or_sync(0xffffffffu, (uint32_t)pb);
 	}
+	const uint32_t ms1 = (uint32_t)THR_MSC, ms2 = 2 * (uint32_t)THR_MSC;
+	uint32_t mykey = 0;
 	// score slots in get_edit's scan order families: [0,4) nem1, [4,8) ned1, 8 nei1, [9,25) nem2, [25,41) nemd, [41,57) ned2, [57,61) nemi, 61 nei2
 #pragma unroll 1
 	for (int round = 0; round < 2; ++round) {
@@ -422,22 +424,18 @@ __device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K
 				if (lane == 0) n_ec += nw;
 			}
 		}
-		if (w < 64) W.score[w] = n;
-	}
-	__syncwarp();
-	// thread_ext_t::get_edit, cpp:628-647 (every lane replays the same scan)
-	uint32_t best = 0, bw = 0xFFu;
-	const uint32_t ms1 = (uint32_t)THR_MSC, ms2 = 2 * (uint32_t)THR_MSC;
-	for (uint32_t w = 0; w < 9; ++w) { const uint32_t s = W.score[w]; if (s > best && s >= ms1) { best = s; bw = w; } }
-	if (mes > 1) {
-		for (uint32_t i = 0; i < 4; ++i) {
-			for (uint32_t j = 0; j < 4; ++j) {
-				for (uint32_t f = 0; f < 3; ++f) { const uint32_t w = 9 + 16 * f + 4 * i + j, s = W.score[w]; if (s > best && s >= ms2) { best = s; bw = w; } }
-			}
-			{ const uint32_t w = 57 + i, s = W.score[w]; if (s > best && s >= ms2) { best = s; bw = w; } }
+		// thread_ext_t::get_edit, cpp:628-647: a sequential scan with strict '>' = the FIRST maximum in scan order among the
+		// entries that reach their threshold.  key = score << 16 | (255 - scan rank) << 8 | slot, reduced with max.
+		if (w < 62 && n >= (w < 9 ? ms1 : ms2) && (w < 9 || mes > 1)) {
+			uint32_t rank = w;
+			if (w >= 9 && w < 57)  { const uint32_t f = (w - 9) >> 4, q = (w - 9) & 15; rank = 9 + (q >> 2) * 13 + (q & 3) * 3 + f; }
+			else if (w >= 57 && w < 61) rank = 9 + (w - 57) * 13 + 12;
+			const uint32_t key = (n << 16) | ((255u - rank) << 8) | w;
+			if (key > mykey) mykey = key;
 		}
-		{ const uint32_t s = W.score[61]; if (s > best && s >= ms2) { best = s; bw = 61; } }
 	}
+	const uint32_t bkey = __reduce_max_sync(0xffffffffu, mykey);
+	const uint32_t best = bkey >> 16, bw = bkey ? (bkey & 0xFFu) : 0xFFu;
 	__syncwarp();
 	n_ec_out += n_ec;
 	x.score = best; x.nedits = 0;
@@ -464,13 +462,17 @@ __device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K
 // lane, lane 0 takes the carry of the previous iteration.
 template <int B, int MAXJ>
 __device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ, B>& W,
-                                            int m, int nkm, int lane, uint32_t& n_refresh) {
+                                            int m, int nkm, int lo, int hi, int lane, uint32_t& n_refresh) {
+	// [lo, hi) = positions whose k-mer changed since the last refresh (0, nkm: all).  Only they are probed; the ballots are
+	// rebuilt for the 32-position groups that contain lo .. hi (position hi's match bit depends on node hi-1), from W.info
+	// for the untouched positions.
 	__syncwarp();
 	const uint64_t lmix = (uint64_t)locus * 0xC2B2AE3D27D4EB4Full;         // g_hash_key
+	const int j0 = lo >> 5, j1 = min(hi, nkm - 1) >> 5;                    // group range, inclusive
 #pragma unroll 1
-	for (int j = 0; j * 32 < nkm; ++j) {
+	for (int j = j0; j <= j1; ++j) {
 		const int i = j * 32 + lane;
-		const uint64_t f = i < nkm ? W.km[m][i] : KMER_INVALID;
+		const uint64_t f = (i >= lo && i < hi && i < nkm) ? W.km[m][i] : KMER_INVALID;
 		if (f != KMER_INVALID) {
 			const uint64_t rc = W.rck[i];
 			const uint64_t canon = rc < f ? rc : f;
@@ -482,14 +484,16 @@ __device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, u
 	cp_async_wait_all();
 	__syncwarp();
 	uint64_t carry_f = KMER_INVALID; uint32_t carry_b = 0, nprobe = 0;
+	if (j0 > 0) { carry_f = W.km[m][j0 * 32 - 1]; carry_b = W.info[j0 * 32 - 1]; }
 #pragma unroll 1
-	for (int j = 0; j < MAXJ; ++j) {
+	for (int j = j0; j <= j1; ++j) {
 		const int i = j * 32 + lane;
 		const bool in = i < nkm;
 		const uint64_t f = in ? W.km[m][i] : KMER_INVALID;
 		const bool valid = f != KMER_INVALID;
 		uint32_t bi = 0, trp = 0;
-		if (valid) {
+		if (valid && (i < lo || i >= hi)) { bi = W.info[i]; trp = W.trx[m][i]; }
+		else if (valid) {
 			const uint64_t rc = W.rck[i];
 			const bool is_rc = rc < f;
 			const uint64_t canon = is_rc ? rc : f;
@@ -506,7 +510,7 @@ __device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, u
 			if (!found && full && (k0 & SLOT_OVF)) { const GNode n = g_lookup<B>(gt, f, locus, K); bi = n.bits; trp = n.tr; }   // continues in the stash: rare
 			++nprobe;
 		}
-		if (in) W.trx[m][i] = trp;
+		if (in) { W.trx[m][i] = trp; W.info[i] = bi; }
 		uint64_t pv = __shfl_up_sync(0xffffffffu, f, 1); uint32_t bp = __shfl_up_sync(0xffffffffu, bi, 1);
 		if (lane == 0) { pv = carry_f; bp = carry_b; }
 		carry_f = __shfl_sync(0xffffffffu, f, 31); carry_b = __shfl_sync(0xffffffffu, bi, 31);
@@ -519,6 +523,10 @@ __device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, u
 		const uint32_t ba = __ballot_sync(0xffffffffu, isA), bpz = __ballot_sync(0xffffffffu, valid && (bi & GN_PRESENT));
 		const uint32_t bt = __ballot_sync(0xffffffffu, valid && (bi & GN_TR));
 		if (lane == 0) { W.cls[CL_M][j] = bm; W.cls[CL_N][j] = bn; W.cls[CL_H][j] = bh; W.cls[CL_A][j] = ba; W.cls[CL_P][j] = bpz; W.cls[CL_T][j] = bt; }
+	}
+	if (lo == 0 && hi >= nkm) {                                            // full refresh: groups past the vector read as empty
+#pragma unroll 1
+		for (int j = j1 + 1 + lane; j < MAXJ; j += 32) { W.cls[CL_M][j] = 0; W.cls[CL_N][j] = 0; W.cls[CL_H][j] = 0; W.cls[CL_A][j] = 0; W.cls[CL_P][j] = 0; W.cls[CL_T][j] = 0; }
 	}
 	n_refresh += nprobe;
 	__syncwarp();
@@ -591,7 +599,11 @@ __device__ __noinline__ bool ms_score(const Table gt, uint32_t locus, uint32_t K
 	}
 	__syncwarp();
 	int err = S.err;
-	const bool ok = ec_score<B, MAXJ>(gt, locus, K, rmask, W, nrem, mes, lane, S.x, err, ctr[1]);
+	// level-0 node of the expansion = kmers[kk-1] (forward) / reverse complement of kmers[kk] (backward): already probed
+	uint32_t g0 = 0;
+	if (!backward) { if (kk >= 1 && kk - 1 < nkm && W.km[m][kk - 1] != KMER_INVALID) g0 = W.info[kk - 1]; }
+	else if (kk >= 0 && kk < nkm && W.km[m][kk] != KMER_INVALID) { const uint32_t b = W.info[kk]; g0 = ((b & GN_RCPRESENT) ? GN_PRESENT : 0u) | (gn_rcmask(b) << 1); }
+	const bool ok = ec_score<B, MAXJ>(gt, locus, K, rmask, W, nrem, mes, lane, S.x, err, ctr[1], g0);
 	S.err = err;
 	return ok;
 }
@@ -603,6 +615,7 @@ __device__ __noinline__ void ms_apply(const Table gt, uint32_t locus, uint32_t K
 	constexpr int CAP = ThreadWarp<MAXJ, B>::CAP, ECAP = ThreadWarp<MAXJ, B>::ECAP;
 	__syncwarp();
 	int kk = *kkp;
+	const int kk0 = kk;
 	int nkm = S.nkm, nes = S.nes, ntr = S.ntr, ni = S.ni, err = S.err;
 	uint64_t ncorr = S.ncorr, nskip = S.nskip;
 	Txt x = S.x;
@@ -618,9 +631,18 @@ __device__ __noinline__ void ms_apply(const Table gt, uint32_t locus, uint32_t K
 	x.nm = __shfl_sync(0xffffffffu, x.nm, 0); x.nd = __shfl_sync(0xffffffffu, x.nd, 0); x.nins = __shfl_sync(0xffffffffu, x.nins, 0);
 	x.a_lo = __shfl_sync(0xffffffffu, x.a_lo, 0); x.a_n = __shfl_sync(0xffffffffu, x.a_n, 0);
 	__syncwarp();
+	// substitutions only (no k-mer inserted or erased): the rewritten k-mers are the <= nm + k positions after (forward,
+	// cpp:842-845) or before (backward, cpp:679-686) the edit point; anything else moved the tail -> everything is re-probed
+	int lo = 0, hi = nkm;
+	if (x.nd == 0 && x.nins == 0 && !err) {
+		if (!backward) { lo = kk0; hi = min(nkm, kk0 + (int)x.nm + (int)K); }
+		else           { lo = max(0, kk0 - (int)x.nm - (int)K); hi = kk0; }
+		if (lo >= hi) { lo = 0; hi = nkm; }
+	}
 #pragma unroll 1
-	for (int i = lane; i < nkm; i += 32) { const uint64_t f = W.km[m][i]; W.rck[i] = f == KMER_INVALID ? KMER_INVALID : kmer_rc(f, K); }
-	thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, nkm, lane, ctr[2]);
+	for (int i = lo + lane; i < hi; i += 32) { const uint64_t f = W.km[m][i]; W.rck[i] = f == KMER_INVALID ? KMER_INVALID : kmer_rc(f, K); }
+	__syncwarp();
+	thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, nkm, lo, hi, lane, ctr[2]);
 	if (!err) {                                                        // cpp:850 / 690
 #pragma unroll 1
 		for (int q = lane; q < x.a_n; q += 32) W.tr[x.a_lo + q] = thr_bit<MAXJ>(W.cls[CL_T], x.a_lo + q) ? 2 : 1;
@@ -664,7 +686,7 @@ __device__ __noinline__ MateResult thread_mate(const Table gt, uint32_t locus, u
 	anyvalid = __any_sync(0xffffffffu, anyvalid);
 	__syncwarp();
 	if (!anyvalid) { R.nkm = 0; R.nes = S.nes; R.ntr = S.ntr; return R; }     // D1: a read without a valid k-mer is not threadable (cpp:1124 would be UB)
-	thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, S.nkm, lane, ctr[2]);
+	thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, S.nkm, 0, S.nkm, lane, ctr[2]);
 	if (lane == 0) ctr[0] += (uint32_t)S.nkm;
 
 	const uint64_t nkm0 = (uint64_t)S.nkm;

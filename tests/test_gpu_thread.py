@@ -139,3 +139,50 @@ def test_stress_vs_oracle(cfg):
     p = tc.thread_params(extra_flags=abi.F_TRACE, max_batch_pairs=8192, max_read_len=gk.get("rlen", 150), **pk)
     recs, cnt = assert_same_as_oracle(ix, p, seqs)
     assert (recs["h"]["status"] == abi.ST_COUNTED).sum() > 200
+
+
+@pytest.mark.parametrize("aln", [1, 2])
+def test_pinned_result_buffer_gets_the_same_records(aln):
+    """dbt_wait copies the device-compacted records straight into a pinned caller buffer (dbt_host_alloc) and stages
+    them through its own pinned buffer otherwise; both must return the same records in pair order, over two slots,
+    for `-a` (every pair that entered threading) and `-ae` (threaded pairs only)."""
+    import ctypes as C
+    _, ix, seqs, _ = tc.thread_case(write_text=False, frac_bg=0.3, npairs=600, rseed=11, sub=0.02)
+    p = tc.thread_params(aln=aln, max_batch_pairs=1024)
+    bases, off = rpgg_io.seqs_to_batch(seqs)
+    ctx = abi.Context(p, abi.make_index_struct(ix))
+    L = ctx.L
+    want, _ = ctx.run(bases, off)                                   # pageable numpy buffer: staged path
+    want = want.copy()
+    pt = tc.thread_params(extra_flags=abi.F_TRACE, max_batch_pairs=1024)
+    st = Oracle(ix).run(pt, bases, off)[0]["h"]["status"]
+    sel = (st == abi.ST_COUNTED) | (st == abi.ST_THREAD_FAILED) if aln == 1 else st == abi.ST_COUNTED
+    assert [int(x) for x in want["h"]["pair_index"]] == [int(i) for i in np.nonzero(sel)[0]]
+    assert 0 < len(want) < len(seqs) // 2
+    ctx.reset()
+    cap = len(seqs) // 2
+    for slot in (0, 1):
+        buf, owner = abi.pinned_array(L, cap * ctx.stride)
+        buf[:] = 0xEE
+        r = abi.BatchResult()
+        r.capacity = cap
+        r.records = abi.ptr(buf, abi.u8p)
+        b = ctx.make_batch(bases, off)
+        abi.check(L, L.dbt_submit(ctx.h, C.byref(b), C.byref(r), slot), "submit")
+        abi.check(L, L.dbt_wait(ctx.h, slot), "wait")
+        n = int(r.n_records)
+        assert n == len(want)
+        assert buf[: n * ctx.stride].tobytes() == want.tobytes()
+        assert (buf[n * ctx.stride:] == 0xEE).all()                  # nothing written past the emitted records
+        del buf, owner
+    ctx.close()
+
+
+def test_result_capacity_overflow_is_reported():
+    _, ix, seqs, _ = tc.thread_case(write_text=False, npairs=300, rseed=12)
+    p = tc.thread_params(aln=1, max_batch_pairs=512)
+    bases, off = rpgg_io.seqs_to_batch(seqs)
+    ctx = abi.Context(p, abi.make_index_struct(ix))
+    with pytest.raises(abi.DbtError, match="result buffer holds 5 records"):
+        ctx.run(bases, off, capacity=5)
+    ctx.close()
