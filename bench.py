@@ -44,6 +44,7 @@ from oracle_abi import REF_DIR, abi, pkg, ref_bin, rpgg_io  # noqa: E402  (oracl
 
 synth = pkg.synth
 RLEN, FLEN, K, CTH = 150, 500, 21, 45
+CORR = 1                                   # 1: `-gc 85 3` (error-correcting threading), 0: `-g 85` (exact threading)
 
 
 def log(*a):
@@ -176,7 +177,7 @@ def run_reference_thread(pref, ascii_reads, n, workdir, nproc):
     """The reference's threading functions (oracle/_ref/ref_harness, thread=85 corr=1 maxnc=3 aln=2, no trace dump):
     one process per core, each on a contiguous shard of the first n pairs.  -> (query s, wall s, load s, summed trkmc)."""
     exe = ref_bin("ref_harness")
-    tail = [str(K), str(CTH), "4", "1", "40", "0", "thread=85", "corr=1", "maxnc=3", "aln=2", "trace=0"]
+    tail = [str(K), str(CTH), "4", "1", "40", "0", "thread=85", f"corr={CORR}", "maxnc=3", "aln=2", "trace=0"]
     nproc = max(1, min(nproc, n // 1000 or 1))
     bounds = [n * i // nproc for i in range(nproc + 1)]
     empty = os.path.join(workdir, "thr.empty.tsv")
@@ -213,8 +214,10 @@ def peaks():
 
 # ------------------------------------------------------------------------------------------------
 METRIC = "read pairs/sec (k=21, -ae)"
-FLAGS_TXT = {"thread": "align -k 21 -gc 85 3 -kf 4 1 -cth 45 -ae (restored graph threading, SURVEY §8(c) D1)",
-             "asgn": "align -k 21 -kf 4 1 -cth 45 -ae (asgn path: what the unmodified reference runs at HEAD, SURVEY F2)"}
+def flags_txt(mode):
+    if mode == "thread":
+        return f"align -k {K} {'-gc 85 3' if CORR else '-g 85'} -kf 4 1 -cth 45 -ae (restored graph threading, SURVEY §8(c) D1)"
+    return f"align -k {K} -kf 4 1 -cth 45 -ae (asgn path: what the unmodified reference runs at HEAD, SURVEY F2)"
 
 
 def main():
@@ -226,6 +229,8 @@ def main():
     ap.add_argument("--mode", default="both", choices=["both", "thread", "asgn"], help="headline = thread; 'both' adds the asgn block")
     ap.add_argument("--pairs", type=int, default=10_000_000, help="read pairs per GPU per step")
     ap.add_argument("--loci", type=int, default=1000)
+    ap.add_argument("--k", type=int, default=21, help="k-mer size (configs[3]: 17 / 25); the metric is quoted at the default 21")
+    ap.add_argument("--exact", action="store_true", help="threading mode with `-g 85` (no error correction, configs[4]) instead of `-gc 85 3`")
     ap.add_argument("--frac-locus", type=float, default=0.05)
     ap.add_argument("--cpu-sample", type=int, default=2_000_000, help="pairs given to the CPU reference")
     ap.add_argument("--sub-batch", type=int, default=2_500_000, help="pairs per dbt_submit in the e2e loop")
@@ -235,6 +240,8 @@ def main():
     ap.add_argument("--rrand", action="store_true", help="also measure the random-sector roofline R_rand")
     a = ap.parse_args()
     a.steps, a.warmup = max(a.steps, 1), max(a.warmup, 0)
+    global K, CORR
+    K, CORR = a.k, 0 if a.exact else 1
 
     os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")      # keep stdout to the one JSON line (NCCL prints its version banner there)
     rank = int(os.environ.get("RANK", 0))
@@ -270,7 +277,7 @@ def main():
 def make_config(a, mode):
     err = f", locus reads with {SUB_PPM/1e4:.1f}% substitutions + {INDEL_PPM/1e4:.2f}% indels" if mode == "thread" else ", error-free"
     return {"workload": f"synthetic {a.loci}-locus RPGG (8 haplotypes, 700 bp flanks), {a.pairs} simulated 150bp read pairs per GPU "
-                        f"({a.frac_locus:.0%} locus reads{err} / rest background), {FLAGS_TXT[mode]}",
+                        f"({a.frac_locus:.0%} locus reads{err} / rest background), {flags_txt(mode)}",
             "mode": mode, "pairs_per_gpu": a.pairs, "loci": a.loci, "k": K, "cth": CTH, "kf": [4, 1],
             "l2_policy": "inputs larger than L2 (packed reads 1.3 GB/step >> 126 MB); no explicit flush"}
 
@@ -333,7 +340,7 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
     config = make_config(a, mode)
     P = a.pairs
     flags = (abi.F_THREADING | abi.F_CORRECTION | abi.F_ALN | abi.F_ALN_MIN) if thr else abi.F_KAM
-    if thr and os.environ.get("DBT_BENCH_NOCORR"):          # kernel experiments only: `-g 85` (exact threading, no error correction)
+    if thr and not CORR:
         flags &= ~abi.F_CORRECTION
     p = abi.default_params(k=K, cth=CTH, n_filter=4, nm_filter=1, nm_tr=40, flags=flags, max_read_len=RLEN,
                            max_batch_pairs=P, device=local)
@@ -560,7 +567,7 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
                 gc = dict(zip(abi.COUNTER_NAMES, [int(x) for x in g_cnt]))
                 cpu = {"value": n / t_q, "unit": "read pairs/s", "cores": used, "kind": "reference",
                        "sample": f"first {n} pairs of rank 0's batch; the reference's isThreadFeasible & helpers compiled from /root/reference "
-                                 f"(oracle/_ref/ref_harness thread=85 corr=1 maxnc=3 aln=2, caller cpp:2072-2088 restored as glue, D1), {used} processes on "
+                                 f"(oracle/_ref/ref_harness thread=85 corr={CORR} maxnc=3 aln=2, caller cpp:2072-2088 restored as glue, D1), {used} processes on "
                                  f"contiguous shards (TSV in /dev/shm); query phase {t_q:.2f}s = wall {t_all:.2f}s minus zero-read index load {t_load:.2f}s",
                        "parity_vs_gpu": {"trkmc_total_identical": int(ref_counts.sum()) == int(g_tr.sum()),
                                          "trkmc_per_locus_multiset_identical": per_locus_multiset_equal(ix, ref_counts, g_tr),
@@ -573,7 +580,7 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
                 ref_summary = open(os.path.join(workdir, "ref.tr.summary.txt")).read()
                 g_summary = "".join(f"{int(x)}\t{int(y)}\n" for x, y in zip(g_nmap, g_kmc))
                 cpu = {"value": n / t_q, "unit": "read pairs/s", "cores": nproc, "kind": "reference",
-                       "sample": f"first {n} pairs of rank 0's batch as FASTA in /dev/shm, `danbing-tk -k 21 -kf 4 1 -cth 45 -ae -p {nproc}` (kam lines to /dev/null); "
+                       "sample": f"first {n} pairs of rank 0's batch as FASTA in /dev/shm, `danbing-tk -k {K} -kf 4 1 -cth 45 -ae -p {nproc}` (kam lines to /dev/null); "
                                  f"query phase {t_q:.2f}s = wall {t_all:.2f}s minus zero-read index load {t_load:.2f}s",
                        "parity_vs_gpu": {"tr_summary_identical": ref_summary == g_summary, "trkmc_total_identical": int(ref_counts.sum()) == int(g_tr.sum()),
                                          "trkmc_per_locus_multiset_identical": per_locus_multiset_equal(ix, ref_counts, g_tr)}}
