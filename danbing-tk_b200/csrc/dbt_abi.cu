@@ -12,8 +12,10 @@
 #include <thread>
 #include <vector>
 #include <dlfcn.h>
+#include <sched.h>
 
 #include "launchers.h"
+#include "host_pack.h"
 #include "graph_table.cuh"
 
 using namespace dbt;
@@ -460,16 +462,11 @@ extern "C" size_t dbt_packed_bytes(uint32_t max_read_len, uint64_t npairs) {
 	return (size_t)npairs * (2 * (size_t)l.W64 * 8 + 2 * 2);
 }
 
-static void pack_one(const uint8_t* s, uint32_t len, uint32_t k, const ReadLayout& lay, uint64_t* out, uint16_t* meta) {
-	for (uint32_t w = 0; w < lay.W64; ++w) out[w] = 0;
-	uint32_t run = 0; bool any = false;
-	const uint32_t nbits = lay.WM * 64;
-	for (uint32_t i = 0; i < nbits; ++i) {
-		uint32_t c = i < len ? base_code(s[i]) : 4;
-		if (c < 4) { out[i >> 5] |= (uint64_t)c << (2 * (i & 31)); if (++run >= k) any = true; }
-		else { out[lay.WB + (i >> 6)] |= 1ull << (i & 63); run = 0; }
-	}
-	*meta = (uint16_t)(len | (any ? 0 : META_NOVALID));
+// CPUs this thread may run on (affinity mask: what a NUMA-bound or cgroup-pinned process really has)
+static int usable_cpus() {
+	cpu_set_t set;
+	if (sched_getaffinity(0, sizeof(set), &set) == 0) { const int n = CPU_COUNT(&set); if (n > 0) return n; }
+	return (int)std::max(1u, std::thread::hardware_concurrency());
 }
 
 extern "C" int dbt_pack_reads(uint32_t k, uint32_t max_read_len, uint64_t npairs, const uint8_t* ascii,
@@ -480,15 +477,17 @@ extern "C" int dbt_pack_reads(uint32_t k, uint32_t max_read_len, uint64_t npairs
 	uint64_t* p1 = p0 + npairs * lay.W64;
 	uint16_t* m0 = reinterpret_cast<uint16_t*>(p1 + npairs * lay.W64);
 	uint16_t* m1 = m0 + npairs;
-	if (nthreads <= 0) nthreads = (int)std::max(1u, std::thread::hardware_concurrency());
+	const int impl = getenv("DBT_HOST_PACK_SWAR") ? HOST_PACK_SWAR : HOST_PACK_AUTO;   // test hook: force the non-AVX2 path
+	if (nthreads <= 0) nthreads = usable_cpus();
 	nthreads = (int)std::min<uint64_t>((uint64_t)nthreads, std::max<uint64_t>(1, npairs / 4096));
 	std::atomic<int> bad{0};
+	const uint64_t end = offsets[2 * npairs];
 	auto work = [&](uint64_t a, uint64_t b) {
 		for (uint64_t p = a; p < b; ++p) {
 			for (int m = 0; m < 2; ++m) {
 				uint64_t off = offsets[2 * p + m], len = offsets[2 * p + m + 1] - off;
 				if (len > max_read_len) { bad = 1; len = max_read_len; }
-				pack_one(ascii + off, (uint32_t)len, k, lay, (m ? p1 : p0) + p * lay.W64, (m ? m1 : m0) + p);
+				host_pack_read(ascii + off, (uint32_t)len, end - off, k, lay, (m ? p1 : p0) + p * lay.W64, (m ? m1 : m0) + p, impl);
 			}
 		}
 	};

@@ -32,6 +32,9 @@ namespace dbt {
 #ifndef THR_MINBLOCKS
 #define THR_MINBLOCKS 4
 #endif
+#ifndef THR_STAGE_GROUPS
+#define THR_STAGE_GROUPS 16                        // 32-position groups probed per round of thr_refresh (capped at MAXJ)
+#endif
 #ifndef THR_REFRESH_INLINE
 #define THR_REFRESH_INLINE __noinline__
 #endif
@@ -48,12 +51,14 @@ template <int MAXJ, int SB>
 struct ThreadWarp {
 	static constexpr int CAP = MAXJ * 32;          // k-mer vector / annotation capacity
 	static constexpr int ECAP = MAXJ * 32 + 32;    // CIGAR capacity (read length + deletions)
-	uint64_t km[2][CAP];                           // edited k-mer vectors of both mates (strand-specific, KMER_INVALID = -1)
-	uint32_t trx[2][CAP];                          // count-array position + 1 of each k-mer (0: not a TR k-mer of the locus)
+	static constexpr int SG = MAXJ < THR_STAGE_GROUPS ? MAXJ : THR_STAGE_GROUPS;   // groups whose buckets are in flight together
+	uint64_t km[CAP];                              // edited k-mer vector of the mate being threaded (strand-specific, KMER_INVALID = -1)
+	uint32_t trx[2][CAP];                          // count-array position + 1 of each k-mer of both edited vectors (0: not a TR k-mer of the locus)
 	uint64_t rck[CAP];                             // reverse complement of km[m][i] of the mate being threaded (free at extraction, kmer.cuh)
 	uint32_t cls[6][MAXJ];                         // ballots over positions: M, N, H, A, present, TR
-	uint4    stage[MAXJ][SB][32];                  // home buckets of every position of the mate being probed (cp.async)
-	uint64_t win[40];                              // k-mer window handed to the edit scorer
+	uint4    stage[SG][SB][32];                    // home buckets of SG*32 positions of the mate being probed (cp.async); between
+	                                               // refreshes its first 320 bytes are the k-mer window handed to the edit scorer
+	__device__ __forceinline__ uint64_t* win() { return reinterpret_cast<uint64_t*>(&stage[0][0][0]); }
 	uint32_t info[CAP];                            // GNode.bits of every position of the mate being threaded (thr_refresh)
 	uint8_t  es_t[ECAP], es_r[ECAP], es_g[ECAP];   // cigar_t.es (cpp:53-60)
 	uint8_t  tr[CAP];                              // cigar_t.tr: 0 '*' 1 '.' 2 '='
@@ -280,12 +285,12 @@ __device__ __forceinline__ void edit_kmers_backward(TState& T, Txt& x, int& ki_i
 }
 
 // ---- warp-parallel edit scorer: errorCorrection_forward, cpp:898-1089 ----
-// W.win[j+1] holds kmers[ki+j] for j = -1 .. k+1 (KMER_INVALID beyond the vector), nrem = nkmers - ki.
+// W.win()[j+1] holds kmers[ki+j] for j = -1 .. k+1 (KMER_INVALID beyond the vector), nrem = nkmers - ki.
 // Returns (warp-uniform) true when an edit was found; x.et/eg/score/nedits describe it.  err |= graph not closed.
 template <int B, int MAXJ>
 __device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ, B>& W,
                                       uint32_t nrem, uint32_t mes, int lane, Txt& x, int& err, uint32_t& n_ec_out, uint32_t g0bits) {
-	const uint64_t node = W.win[0];
+	const uint64_t node = W.win()[0];
 	uint32_t n_ec = lane == 0 ? 1u : 0u;
 	// nts0 / nnds: getOutNodes(g, node), cpp:1170 / 1097 -- the node is a k-mer of the read (or its reverse complement)
 	// that thr_refresh has already probed: g0bits = its GNode bits in the walk's orientation (W.info)
@@ -323,8 +328,8 @@ __device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K
 	auto nnts1 = [&](uint32_t i) -> uint32_t { uint32_t r = 0; for (uint32_t j = 0; j < 4; ++j) if (nnts2(i, j)) r |= 1u << j; return r; };
 
 	const uint32_t gl = nrem < K + 2 ? nrem : K + 2;                  // good[j], cpp:922-923
-	auto good = [&](uint32_t j) -> bool { return j < gl && W.win[j + 1] != KMER_INVALID; };
-	const uint64_t w1 = W.win[1], w2 = W.win[2], w3 = W.win[3];
+	auto good = [&](uint32_t j) -> bool { return j < gl && W.win()[j + 1] != KMER_INVALID; };
+	const uint64_t w1 = W.win()[1], w2 = W.win()[2], w3 = W.win()[3];
 	const uint32_t oldnt = (uint32_t)(w1 & 3);
 	const bool g0k = good(0), g1k = good(1), g2k = good(2);
 	// family pre-conditions; the reference reads kmers[ki+j] % 4 before good[j], device code guards first
@@ -340,12 +345,12 @@ __device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K
 
 	// parallel-walk set-up (k <= 29: the k+3 window entries fit one ballot): validity of win[q] and the last base of
 	// win[q] packed at bits 2*(31-q) of PB, q = 1..k+2
-	const bool par = K + 3 <= 32;
+	if (K + 3 > 32) { err = 1; x.score = 0; x.nedits = 0; return false; }   // dbt_create admits k <= 27
 	const uint64_t kmask = K < 32 ? (1ull << 2 * K) - 1 : ~0ull;
 	uint32_t vmask = 0; uint64_t PB = 0;
-	if (par) {
+	{
 		const bool inq = (uint32_t)lane < K + 3 && (uint32_t)lane < gl + 1;       // good(j): j = q-1 < gl
-		const uint64_t wq = inq ? W.win[lane] : KMER_INVALID;
+		const uint64_t wq = inq ? W.win()[lane] : KMER_INVALID;
 		const bool vq = wq != KMER_INVALID;
 		vmask = __ballot_sync(0xffffffffu, vq);
 		const uint64_t pb = (vq && lane >= 1) ? ((wq & 3) << (2 * (31 - lane))) : 0ull;
@@ -371,18 +376,7 @@ __device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K
 		else if (w < 61)  { const uint32_t a = w - 57; act = c_mi && ((nts0 >> a) & 1u); cr = w1 - oldnt + a; nn = nnts1(a); jb = 2; je = e2; }
 		else if (w == 61) { act = c_i2; cr = node; nn = nts0; jb = 2; je = e2; }
 		uint32_t n = 0;
-		if (!par) {
-			if (act) {                                                  // extension walk, cpp:931-940 and siblings (k > 29: one lane per candidate)
-				for (uint32_t j = jb; j < je; ++j) {
-					if (!good(j)) break;
-					cr = ((cr & rmask) << 2) + (W.win[j + 1] & 3);
-					if (!((nn >> (cr & 3)) & 1u)) break;
-					++n; ++n_ec;
-					const GNode g = g_lookup<B>(gt, cr, locus, K);        // getNextNucs, cpp:547-557: assigns only when the node exists
-					if (g.bits & GN_PRESENT) nn = gn_mask(g.bits);
-				}
-			}
-		} else {
+		{
 			// One candidate at a time, its walk spread over the lanes: step t of the walk visits the k-mer made of the
 			// candidate's start k-mer followed by t+1 read bases, which does not depend on the earlier steps, so all
 			// steps are probed at once (one round of latency instead of up to k+2) and the walk length is read off a
@@ -468,28 +462,32 @@ __device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, u
 	// for the untouched positions.
 	__syncwarp();
 	const uint64_t lmix = (uint64_t)locus * 0xC2B2AE3D27D4EB4Full;         // g_hash_key
+	constexpr int SG = ThreadWarp<MAXJ, B>::SG;
 	const int j0 = lo >> 5, j1 = min(hi, nkm - 1) >> 5;                    // group range, inclusive
+	uint64_t carry_f = KMER_INVALID; uint32_t carry_b = 0, nprobe = 0;
+	if (j0 > 0) { carry_f = W.km[j0 * 32 - 1]; carry_b = W.info[j0 * 32 - 1]; }
 #pragma unroll 1
-	for (int j = j0; j <= j1; ++j) {
+	for (int jc = j0; jc <= j1; jc += SG) {                                // SG groups per round (all of them when the stage holds MAXJ)
+	const int je = min(j1, jc + SG - 1);
+#pragma unroll 1
+	for (int j = jc; j <= je; ++j) {
 		const int i = j * 32 + lane;
-		const uint64_t f = (i >= lo && i < hi && i < nkm) ? W.km[m][i] : KMER_INVALID;
+		const uint64_t f = (i >= lo && i < hi && i < nkm) ? W.km[i] : KMER_INVALID;
 		if (f != KMER_INVALID) {
 			const uint64_t rc = W.rck[i];
 			const uint64_t canon = rc < f ? rc : f;
 			const uint4* bp = gt.slots + home_bucket(gt, canon ^ lmix) * B;
 #pragma unroll
-			for (int q = 0; q < B; ++q) cp_async16(&W.stage[j][q][lane], bp + q);
+			for (int q = 0; q < B; ++q) cp_async16(&W.stage[j - jc][q][lane], bp + q);
 		}
 	}
 	cp_async_wait_all();
 	__syncwarp();
-	uint64_t carry_f = KMER_INVALID; uint32_t carry_b = 0, nprobe = 0;
-	if (j0 > 0) { carry_f = W.km[m][j0 * 32 - 1]; carry_b = W.info[j0 * 32 - 1]; }
 #pragma unroll 1
-	for (int j = j0; j <= j1; ++j) {
+	for (int j = jc; j <= je; ++j) {
 		const int i = j * 32 + lane;
 		const bool in = i < nkm;
-		const uint64_t f = in ? W.km[m][i] : KMER_INVALID;
+		const uint64_t f = in ? W.km[i] : KMER_INVALID;
 		const bool valid = f != KMER_INVALID;
 		uint32_t bi = 0, trp = 0;
 		if (valid && (i < lo || i >= hi)) { bi = W.info[i]; trp = W.trx[m][i]; }
@@ -501,7 +499,7 @@ __device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, u
 			uint64_t k0 = 0;
 #pragma unroll
 			for (int q = 0; q < B; ++q) {
-				const uint4 sl = W.stage[j][q][lane];
+				const uint4 sl = W.stage[j - jc][q][lane];
 				const uint64_t kk = slot_key(sl);
 				if (q == 0) k0 = kk;
 				if (kk == SLOT_EMPTY) full = false;
@@ -523,6 +521,8 @@ __device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, u
 		const uint32_t ba = __ballot_sync(0xffffffffu, isA), bpz = __ballot_sync(0xffffffffu, valid && (bi & GN_PRESENT));
 		const uint32_t bt = __ballot_sync(0xffffffffu, valid && (bi & GN_TR));
 		if (lane == 0) { W.cls[CL_M][j] = bm; W.cls[CL_N][j] = bn; W.cls[CL_H][j] = bh; W.cls[CL_A][j] = ba; W.cls[CL_P][j] = bpz; W.cls[CL_T][j] = bt; }
+	}
+	__syncwarp();                                                          // the stage is rewritten by the next round
 	}
 	if (lo == 0 && hi >= nkm) {                                            // full refresh: groups past the vector read as empty
 #pragma unroll 1
@@ -586,23 +586,23 @@ __device__ __noinline__ bool ms_score(const Table gt, uint32_t locus, uint32_t K
 	if (!backward) {
 		nrem = (uint32_t)(nkm - kk);
 #pragma unroll 1
-		for (int q = lane; q < (int)K + 3; q += 32) { const int i = kk - 1 + q; W.win[q] = (i >= 0 && i < nkm) ? W.km[m][i] : KMER_INVALID; }
+		for (int q = lane; q < (int)K + 3; q += 32) { const int i = kk - 1 + q; W.win()[q] = (i >= 0 && i < nkm) ? W.km[i] : KMER_INVALID; }
 	} else {                                                         // kmers_rc, cpp:1098-1103
 		nrem = (uint32_t)kk;
 #pragma unroll 1
 		for (int q = lane; q < (int)K + 3; q += 32) {
 			const int i = kk - q;
 			uint64_t v = KMER_INVALID;
-			if (i >= 0 && i < nkm && W.km[m][i] != KMER_INVALID) v = kmer_rc(W.km[m][i], K);
-			W.win[q] = v;
+			if (i >= 0 && i < nkm && W.km[i] != KMER_INVALID) v = kmer_rc(W.km[i], K);
+			W.win()[q] = v;
 		}
 	}
 	__syncwarp();
 	int err = S.err;
 	// level-0 node of the expansion = kmers[kk-1] (forward) / reverse complement of kmers[kk] (backward): already probed
 	uint32_t g0 = 0;
-	if (!backward) { if (kk >= 1 && kk - 1 < nkm && W.km[m][kk - 1] != KMER_INVALID) g0 = W.info[kk - 1]; }
-	else if (kk >= 0 && kk < nkm && W.km[m][kk] != KMER_INVALID) { const uint32_t b = W.info[kk]; g0 = ((b & GN_RCPRESENT) ? GN_PRESENT : 0u) | (gn_rcmask(b) << 1); }
+	if (!backward) { if (kk >= 1 && kk - 1 < nkm && W.km[kk - 1] != KMER_INVALID) g0 = W.info[kk - 1]; }
+	else if (kk >= 0 && kk < nkm && W.km[kk] != KMER_INVALID) { const uint32_t b = W.info[kk]; g0 = ((b & GN_RCPRESENT) ? GN_PRESENT : 0u) | (gn_rcmask(b) << 1); }
 	const bool ok = ec_score<B, MAXJ>(gt, locus, K, rmask, W, nrem, mes, lane, S.x, err, ctr[1], g0);
 	S.err = err;
 	return ok;
@@ -620,7 +620,7 @@ __device__ __noinline__ void ms_apply(const Table gt, uint32_t locus, uint32_t K
 	uint64_t ncorr = S.ncorr, nskip = S.nskip;
 	Txt x = S.x;
 	if (lane == 0) {
-		TState T; T.km = W.km[m]; T.es_t = W.es_t; T.es_r = W.es_r; T.es_g = W.es_g; T.tr = W.tr;
+		TState T; T.km = W.km; T.es_t = W.es_t; T.es_r = W.es_r; T.es_g = W.es_g; T.tr = W.tr;
 		T.nkm = nkm; T.nes = nes; T.ntr = ntr; T.ni = ni; T.err = err; T.cap = CAP; T.ecap = ECAP; T.k = K; T.rmask = rmask;
 		if (backward) edit_kmers_backward(T, x, kk, ncorr, nskip); else edit_kmers_forward(T, x, kk, ncorr);
 		nkm = T.nkm; nes = T.nes; ntr = T.ntr; ni = T.ni; err = T.err;
@@ -640,7 +640,7 @@ __device__ __noinline__ void ms_apply(const Table gt, uint32_t locus, uint32_t K
 		if (lo >= hi) { lo = 0; hi = nkm; }
 	}
 #pragma unroll 1
-	for (int i = lo + lane; i < hi; i += 32) { const uint64_t f = W.km[m][i]; W.rck[i] = f == KMER_INVALID ? KMER_INVALID : kmer_rc(f, K); }
+	for (int i = lo + lane; i < hi; i += 32) { const uint64_t f = W.km[i]; W.rck[i] = f == KMER_INVALID ? KMER_INVALID : kmer_rc(f, K); }
 	__syncwarp();
 	thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, nkm, lo, hi, lane, ctr[2]);
 	if (!err) {                                                        // cpp:850 / 690
@@ -681,7 +681,7 @@ __device__ __noinline__ MateResult thread_mate(const Table gt, uint32_t locus, u
 			const uint64_t w = extract_bits(rec, 2u * i, 2 * K);
 			f = rev2(w) >> (64 - 2 * K); rc = (~w) & (K < 32 ? (1ull << 2 * K) - 1 : ~0ull); anyvalid = true;
 		}
-		W.km[m][i] = f; W.rck[i] = rc; W.tr[i] = 0;
+		W.km[i] = f; W.rck[i] = rc; W.tr[i] = 0;
 	}
 	anyvalid = __any_sync(0xffffffffu, anyvalid);
 	__syncwarp();
@@ -824,6 +824,7 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 		const bool slot_ok = want_rec && (trace || slot < rp.max_records);
 		uint8_t* rec = sv.records + slot * rp.rec_stride;
 		MateResult r[2];
+		uint32_t nvalid = 0;                                               // valid k-mers of both edited vectors (lane 0)
 #pragma unroll 1
 		for (int m = 0; m < 2; ++m) {
 			const uint32_t len = sv.meta[m][p] & META_LENMASK;
@@ -855,10 +856,16 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 					if (trace) {                                            // FNV-1a over the edited k-mer vector (parity tests only)
 						hash = 0xcbf29ce484222325ull;
 #pragma unroll 1
-						for (int i = 0; i < r[m].nkm; ++i) { const uint64_t v = W.km[m][i]; for (int q = 0; q < 8; ++q) { hash ^= (v >> (8 * q)) & 0xFF; hash *= 0x100000001b3ull; } }
+						for (int i = 0; i < r[m].nkm; ++i) { const uint64_t v = W.km[i]; for (int q = 0; q < 8; ++q) { hash ^= (v >> (8 * q)) & 0xFF; hash *= 0x100000001b3ull; } }
 					}
 					h->kmers_hash = hash;
 				}
+			}
+			if (r[m].nkm > 0) {                                          // the N ballots of the last refresh cover exactly [0, nkm)
+				uint32_t nn = 0;
+#pragma unroll 1
+				for (int j = lane; j < MAXJ; j += 32) nn += __popc(W.cls[CL_N][j]);
+				nvalid += (uint32_t)r[m].nkm - __reduce_add_sync(0xffffffffu, nn);
 			}
 			__syncwarp();
 		}
@@ -872,7 +879,6 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 				for (int j = 0; j * 32 < r[m].nkm; ++j) {
 					const int i = j * 32 + lane;
 					const uint32_t tx = i < r[m].nkm ? W.trx[m][i] : 0u;
-					if (i < r[m].nkm && W.km[m][i] != KMER_INVALID) ++c_cls;
 					const uint32_t tm = __ballot_sync(0xffffffffu, tx != 0);
 					if (!tm) continue;
 					inc_sum += __popc(tm);
@@ -883,7 +889,7 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 					}
 				}
 			}
-			if (lane == 0) c_inc += inc_sum;
+			if (lane == 0) { c_inc += inc_sum; c_cls += nvalid; }
 		}
 		const uint32_t status = alned ? DBT_ST_COUNTED : DBT_ST_THREAD_FAILED;
 		const uint32_t fdst = alned ? dst : (uint32_t)ix.nloci;
@@ -903,7 +909,6 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 			h->dst = fdst; h->status = (uint8_t)status;
 		}
 	}
-	c_cls = __reduce_add_sync(0xffffffffu, c_cls);
 #pragma unroll 1
 	for (int q = 0; q < 3; ++q) ctr[q] = __reduce_add_sync(0xffffffffu, ctr[q]);
 	if (lane == 0) {

@@ -76,3 +76,64 @@ def test_host_packer_layout(lib):
         assert (int(rec[5 + len(s) // 64]) >> (len(s) % 64)) & 1 == 1 or len(s) == 192
         assert int(meta[m, pair]) & 0x7FFF == len(s)
     assert [int(meta[r & 1, r >> 1]) >> 15 for r in range(4)] == [0, 1, 1, 0]
+
+
+def _numpy_pack(seqs, k, max_len):
+    """independent model of the packed record (csrc/kmer.cuh): every word, incl. the zero code under invalid bases"""
+    WB, WM = (max_len + 31) // 32, (max_len + 63) // 64
+    W = (WB + WM + 1) & ~1
+    recs = np.zeros((len(seqs), W), np.uint64)
+    meta = np.zeros(len(seqs), np.uint16)
+    lut = np.full(256, 4, np.uint8)
+    for i, ch in enumerate(b"ACGT"):
+        lut[ch] = i
+    for r, s in enumerate(seqs):
+        c = np.full(WM * 64, 4, np.uint8)
+        c[: len(s)] = lut[np.frombuffer(s, np.uint8)]
+        bad = c == 4
+        codes = np.where(bad, 0, c).astype(np.uint64)[: WB * 32].reshape(WB, 32)
+        recs[r, :WB] = (codes << (2 * np.arange(32, dtype=np.uint64))).sum(axis=1, dtype=np.uint64)
+        recs[r, WB:WB + WM] = (bad.reshape(WM, 64).astype(np.uint64) << np.arange(64, dtype=np.uint64)).sum(axis=1, dtype=np.uint64)
+        run, best = 0, 0
+        for b in bad[: len(s)]:
+            run = 0 if b else run + 1
+            best = max(best, run)
+        meta[r] = len(s) | (0 if best >= k else 0x8000)
+    return recs, meta
+
+
+def test_host_packer_random_vs_model(lib, monkeypatch):
+    """AVX2 and SWAR packers against the numpy model: all lengths 0..max, N / lower-case / arbitrary bytes, k = 17/21/25"""
+    rng = np.random.default_rng(7)
+    for max_len, k in ((150, 21), (250, 25), (96, 17), (64, 21)):
+        seqs = []
+        for L in list(range(0, max_len + 1)) + [max_len] * 50:
+            s = rng.choice(np.frombuffer(b"ACGT", np.uint8), L)
+            mode = rng.integers(0, 4)
+            if mode == 1 and L:
+                s[rng.integers(0, L, max(1, L // 30))] = ord("N")
+            elif mode == 2 and L:
+                s[rng.integers(0, L, max(1, L // 10))] = rng.integers(0, 256, max(1, L // 10))
+            elif mode == 3 and L:
+                s[rng.integers(0, L)] = ord("acgt"[rng.integers(0, 4)])
+            seqs.append(s.astype(np.uint8).tobytes())
+        if len(seqs) & 1:
+            seqs.append(b"")
+        npairs = len(seqs) // 2
+        want, wmeta = _numpy_pack(seqs, k, max_len)
+        bases = np.frombuffer(b"".join(seqs) + b"\0" * 64, np.uint8).copy()[: sum(map(len, seqs))]
+        off = np.zeros(len(seqs) + 1, np.uint64)
+        off[1:] = np.cumsum([len(s) for s in seqs])
+        W = want.shape[1]
+        for swar in (False, True):
+            if swar:
+                monkeypatch.setenv("DBT_HOST_PACK_SWAR", "1")
+            else:
+                monkeypatch.delenv("DBT_HOST_PACK_SWAR", raising=False)
+            out = np.full(lib.dbt_packed_bytes(max_len, npairs), 0xAB, np.uint8)
+            assert lib.dbt_pack_reads(k, max_len, npairs, abi.ptr(bases, abi.u8p), abi.ptr(off, abi.u64p), abi.ptr(out, abi.u8p), 3) == 0
+            p = out[: 2 * npairs * W * 8].view("<u8").reshape(2, npairs, W)
+            meta = out[2 * npairs * W * 8:].view("<u2").reshape(2, npairs)
+            for m in (0, 1):
+                assert np.array_equal(p[m], want[m::2]), (max_len, k, swar, m)
+                assert np.array_equal(meta[m], wmeta[m::2]), (max_len, k, swar, m)
