@@ -47,6 +47,27 @@ constexpr uint8_t EG_STAR = 5, ER_INVALID = 6;     // read base that is not ACGT
 __device__ __forceinline__ bool et_is_edit(uint8_t t) { return t >= ET_X; }
 __device__ __forceinline__ uint8_t eg_comp(uint8_t g) { return (g >= 1 && g <= 4) ? (uint8_t)(5 - g) : (uint8_t)127; }   // baseComplement on characters, h:71-87
 
+struct Txt {                                       // thread_ext_t, cpp:596-625 (the part that outlives the scorer)
+	uint32_t score, nedits;
+	uint8_t et[2], eg[2];
+	uint32_t nm, nd, nins;
+	uint64_t nrk;
+	int a_lo, a_n;                                 // annotation range to fill from the refreshed TR bits
+};
+
+struct MateResult { int alned, err, nkm, nes, ntr; };
+
+// Mutable state of one mate's walk (warp-uniform).  It lives in SHARED memory (ThreadWarp::S): find_anchor / score / apply
+// are single out-of-line functions working on it by reference (the kernel is instruction-fetch sensitive: every inlined
+// copy of them cost more than the calls, profiles/r1 s5-s7), and as a per-thread local struct it took 32 x the footprint in
+// an L1 that the 200 KB shared-memory carve-out leaves at ~56 KB -- ncu (s17): 55 % of the 87 M local loads/stores missed
+// L1, i.e. the walk's own loop variables came back from L2.
+struct MS {
+	int nkm, nes, ntr, ni, err, ki;
+	uint64_t nskip, ncorr;
+	Txt x;
+};
+
 template <int MAXJ, int SB>
 struct ThreadWarp {
 	static constexpr int CAP = MAXJ * 32;          // k-mer vector / annotation capacity
@@ -62,7 +83,10 @@ struct ThreadWarp {
 	uint32_t info[CAP];                            // GNode.bits of every position of the mate being threaded (thr_refresh)
 	uint8_t  es_t[ECAP], es_r[ECAP], es_g[ECAP];   // cigar_t.es (cpp:53-60)
 	uint8_t  tr[CAP];                              // cigar_t.tr: 0 '*' 1 '.' 2 '='
-	int      sc[12];                               // scalars published by lane 0
+	MS       S;                                    // walk state of the mate being threaded
+	MateResult res[2];                             // outcome of both mates
+	int      kk;                                   // k-mer index handed back by lane 0's edit (ms_apply)
+	uint32_t cnt[3];                               // this warp's probe counters: walk, ec, refresh (lane 0 adds; measurement)
 };
 enum { CL_M = 0, CL_N, CL_H, CL_A, CL_P, CL_T };
 
@@ -72,14 +96,6 @@ struct TState {
 	int nkm, nes, ntr, ni, err;
 	int cap, ecap;
 	uint32_t k; uint64_t rmask;
-};
-
-struct Txt {                                       // thread_ext_t, cpp:596-625 (the part that outlives the scorer)
-	uint32_t score, nedits;
-	uint8_t et[2], eg[2];
-	uint32_t nm, nd, nins;
-	uint64_t nrk;
-	int a_lo, a_n;                                 // annotation range to fill from the refreshed TR bits
 };
 
 // ---- lane-0 vector primitives (bounds violations = undefined behaviour in the reference -> err) ----
@@ -289,7 +305,7 @@ __device__ __forceinline__ void edit_kmers_backward(TState& T, Txt& x, int& ki_i
 // Returns (warp-uniform) true when an edit was found; x.et/eg/score/nedits describe it.  err |= graph not closed.
 template <int B, int MAXJ>
 __device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ, B>& W,
-                                      uint32_t nrem, uint32_t mes, int lane, Txt& x, int& err, uint32_t& n_ec_out, uint32_t g0bits) {
+                                      uint32_t nrem, uint32_t mes, int lane, Txt& x, int& err, uint32_t g0bits) {
 	const uint64_t node = W.win()[0];
 	uint32_t n_ec = lane == 0 ? 1u : 0u;
 	// nts0 / nnds: getOutNodes(g, node), cpp:1170 / 1097 -- the node is a k-mer of the read (or its reverse complement)
@@ -431,7 +447,8 @@ __device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K
 	const uint32_t bkey = __reduce_max_sync(0xffffffffu, mykey);
 	const uint32_t best = bkey >> 16, bw = bkey ? (bkey & 0xFFu) : 0xFFu;
 	__syncwarp();
-	n_ec_out += n_ec;
+	n_ec = __reduce_add_sync(0xffffffffu, n_ec);
+	if (lane == 0) W.cnt[1] += n_ec;
 	x.score = best; x.nedits = 0;
 	if (best == 0) return false;
 	if (bw < 4)        { x.nedits = 1; x.et[0] = ET_X; x.eg[0] = (uint8_t)(bw + 1); }
@@ -456,7 +473,7 @@ __device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K
 // lane, lane 0 takes the carry of the previous iteration.
 template <int B, int MAXJ>
 __device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ, B>& W,
-                                            int m, int nkm, int lo, int hi, int lane, uint32_t& n_refresh) {
+                                            int m, int nkm, int lo, int hi, int lane) {
 	// [lo, hi) = positions whose k-mer changed since the last refresh (0, nkm: all).  Only they are probed; the ballots are
 	// rebuilt for the 32-position groups that contain lo .. hi (position hi's match bit depends on node hi-1), from W.info
 	// for the untouched positions.
@@ -528,7 +545,8 @@ __device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, u
 #pragma unroll 1
 		for (int j = j1 + 1 + lane; j < MAXJ; j += 32) { W.cls[CL_M][j] = 0; W.cls[CL_N][j] = 0; W.cls[CL_H][j] = 0; W.cls[CL_A][j] = 0; W.cls[CL_P][j] = 0; W.cls[CL_T][j] = 0; }
 	}
-	n_refresh += nprobe;
+	nprobe = __reduce_add_sync(0xffffffffu, nprobe);
+	if (lane == 0) W.cnt[2] += nprobe;
 	__syncwarp();
 }
 
@@ -547,27 +565,20 @@ __device__ __forceinline__ int thr_next(const uint32_t* w, int from, int n, bool
 template <int MAXJ>
 __device__ __forceinline__ bool thr_bit(const uint32_t* w, int i) { return (w[i >> 5] >> (i & 31)) & 1u; }
 
-struct MateResult { int alned, err, nkm, nes, ntr; };
-
-// Mutable state of one mate's walk.  It lives in local memory on purpose: find_anchor / score / apply are single
-// out-of-line functions working on it by reference.  ncu (profiles/r1, s5) showed the kernel instruction-fetch bound
-// (stall_no_instruction 9.6 cycles per issue, 255 KB of SASS) while insensitive to occupancy; every inlined copy of
-// these helpers removed bought more than the few local loads/stores cost.
-struct MS {
-	int nkm, nes, ntr, ni, err, ki;
-	uint64_t nskip, ncorr;
-	Txt x;
-};
-
 // find_anchor, cpp:878-888
 template <int B, int MAXJ>
-__device__ __noinline__ bool ms_find_anchor(ThreadWarp<MAXJ, B>& W, MS& S, int K, int lane) {
-	const int a = thr_next<MAXJ>(W.cls[CL_P], S.ki, S.nkm, true);
-	S.nskip += (uint64_t)(a - S.ki); S.ni += a - S.ki; S.ki = a;
-	if (a >= S.nkm) return false;
+__device__ __noinline__ bool ms_find_anchor(ThreadWarp<MAXJ, B>& W, int K, int lane) {
+	__syncwarp();
+	MS& S = W.S;
+	const int ki = S.ki, nkm = S.nkm, ni0 = S.ni, nes = S.nes;
+	const uint64_t nskip = S.nskip;
+	const int a = thr_next<MAXJ>(W.cls[CL_P], ki, nkm, true);
+	const int ni = ni0 + (a - ki);
+	__syncwarp();
+	S.nskip = nskip + (uint64_t)(a - ki); S.ni = ni; S.ki = a;
+	if (a >= nkm) return false;
 	if (lane == 0) W.tr[a] = thr_bit<MAXJ>(W.cls[CL_T], a) ? 2 : 1;
-	const int ni = S.ni;
-	if (ni < 0 || ni + K > S.nes) S.err = 1;
+	if (ni < 0 || ni + K > nes) S.err = 1;
 	else {
 #pragma unroll 1
 		for (int q = lane; q < K; q += 32) if (W.es_t[ni + q] == ET_STAR) W.es_t[ni + q] = ET_EQ;
@@ -578,9 +589,10 @@ __device__ __noinline__ bool ms_find_anchor(ThreadWarp<MAXJ, B>& W, MS& S, int K
 
 // errorCorrection_forward (backward = false) / errorCorrection_backward (cpp:1091-1106: the same scorer on kmers_rc)
 template <int B, int MAXJ>
-__device__ __noinline__ bool ms_score(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ, B>& W, int m, MS& S,
-                                      bool backward, int kk, uint32_t mes, int lane, uint32_t* ctr) {
+__device__ __noinline__ bool ms_score(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ, B>& W, int m,
+                                      bool backward, int kk, uint32_t mes, int lane) {
 	__syncwarp();
+	MS& S = W.S;
 	const int nkm = S.nkm;
 	uint32_t nrem;
 	if (!backward) {
@@ -603,68 +615,67 @@ __device__ __noinline__ bool ms_score(const Table gt, uint32_t locus, uint32_t K
 	uint32_t g0 = 0;
 	if (!backward) { if (kk >= 1 && kk - 1 < nkm && W.km[kk - 1] != KMER_INVALID) g0 = W.info[kk - 1]; }
 	else if (kk >= 0 && kk < nkm && W.km[kk] != KMER_INVALID) { const uint32_t b = W.info[kk]; g0 = ((b & GN_RCPRESENT) ? GN_PRESENT : 0u) | (gn_rcmask(b) << 1); }
-	const bool ok = ec_score<B, MAXJ>(gt, locus, K, rmask, W, nrem, mes, lane, S.x, err, ctr[1], g0);
+	const bool ok = ec_score<B, MAXJ>(gt, locus, K, rmask, W, nrem, mes, lane, S.x, err, g0);
+	__syncwarp();
 	S.err = err;
 	return ok;
 }
 
-// edit_kmers_forward / _backward on lane 0, then re-probe every position and fill the annotation range
+// edit_kmers_forward / _backward on lane 0, then re-probe the rewritten positions and fill the annotation range.
+// Returns the new k-mer index (ki / ki_ of the caller).
 template <int B, int MAXJ>
-__device__ __noinline__ void ms_apply(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ, B>& W, int m, MS& S,
-                                      bool backward, int* kkp, int lane, uint32_t* ctr) {
+__device__ __noinline__ int ms_apply(const Table gt, uint32_t locus, uint32_t K, uint64_t rmask, ThreadWarp<MAXJ, B>& W, int m,
+                                     bool backward, int kk0, int lane) {
 	constexpr int CAP = ThreadWarp<MAXJ, B>::CAP, ECAP = ThreadWarp<MAXJ, B>::ECAP;
 	__syncwarp();
-	int kk = *kkp;
-	const int kk0 = kk;
-	int nkm = S.nkm, nes = S.nes, ntr = S.ntr, ni = S.ni, err = S.err;
-	uint64_t ncorr = S.ncorr, nskip = S.nskip;
-	Txt x = S.x;
+	MS& S = W.S;
 	if (lane == 0) {
+		int kk = kk0;
+		uint64_t ncorr = S.ncorr, nskip = S.nskip;
 		TState T; T.km = W.km; T.es_t = W.es_t; T.es_r = W.es_r; T.es_g = W.es_g; T.tr = W.tr;
-		T.nkm = nkm; T.nes = nes; T.ntr = ntr; T.ni = ni; T.err = err; T.cap = CAP; T.ecap = ECAP; T.k = K; T.rmask = rmask;
-		if (backward) edit_kmers_backward(T, x, kk, ncorr, nskip); else edit_kmers_forward(T, x, kk, ncorr);
-		nkm = T.nkm; nes = T.nes; ntr = T.ntr; ni = T.ni; err = T.err;
+		T.nkm = S.nkm; T.nes = S.nes; T.ntr = S.ntr; T.ni = S.ni; T.err = S.err; T.cap = CAP; T.ecap = ECAP; T.k = K; T.rmask = rmask;
+		if (backward) edit_kmers_backward(T, S.x, kk, ncorr, nskip); else edit_kmers_forward(T, S.x, kk, ncorr);
+		S.nkm = T.nkm; S.nes = T.nes; S.ntr = T.ntr; S.ni = T.ni; S.err = T.err; S.ncorr = ncorr; S.nskip = nskip;
+		W.kk = kk;
 	}
-	nkm = __shfl_sync(0xffffffffu, nkm, 0); nes = __shfl_sync(0xffffffffu, nes, 0); ntr = __shfl_sync(0xffffffffu, ntr, 0);
-	ni = __shfl_sync(0xffffffffu, ni, 0); err = __shfl_sync(0xffffffffu, err, 0); kk = __shfl_sync(0xffffffffu, kk, 0);
-	ncorr = __shfl_sync(0xffffffffu, ncorr, 0); nskip = __shfl_sync(0xffffffffu, nskip, 0);
-	x.nm = __shfl_sync(0xffffffffu, x.nm, 0); x.nd = __shfl_sync(0xffffffffu, x.nd, 0); x.nins = __shfl_sync(0xffffffffu, x.nins, 0);
-	x.a_lo = __shfl_sync(0xffffffffu, x.a_lo, 0); x.a_n = __shfl_sync(0xffffffffu, x.a_n, 0);
 	__syncwarp();
+	const int nkm = S.nkm, err = S.err, kk = W.kk;
+	const int xnm = (int)S.x.nm, xnd = (int)S.x.nd, xnins = (int)S.x.nins, a_lo = S.x.a_lo, a_n = S.x.a_n;
 	// substitutions only (no k-mer inserted or erased): the rewritten k-mers are the <= nm + k positions after (forward,
 	// cpp:842-845) or before (backward, cpp:679-686) the edit point; anything else moved the tail -> everything is re-probed
 	int lo = 0, hi = nkm;
-	if (x.nd == 0 && x.nins == 0 && !err) {
-		if (!backward) { lo = kk0; hi = min(nkm, kk0 + (int)x.nm + (int)K); }
-		else           { lo = max(0, kk0 - (int)x.nm - (int)K); hi = kk0; }
+	if (xnd == 0 && xnins == 0 && !err) {
+		if (!backward) { lo = kk0; hi = min(nkm, kk0 + xnm + (int)K); }
+		else           { lo = max(0, kk0 - xnm - (int)K); hi = kk0; }
 		if (lo >= hi) { lo = 0; hi = nkm; }
 	}
 #pragma unroll 1
 	for (int i = lo + lane; i < hi; i += 32) { const uint64_t f = W.km[i]; W.rck[i] = f == KMER_INVALID ? KMER_INVALID : kmer_rc(f, K); }
 	__syncwarp();
-	thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, nkm, lo, hi, lane, ctr[2]);
+	thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, nkm, lo, hi, lane);
 	if (!err) {                                                        // cpp:850 / 690
 #pragma unroll 1
-		for (int q = lane; q < x.a_n; q += 32) W.tr[x.a_lo + q] = thr_bit<MAXJ>(W.cls[CL_T], x.a_lo + q) ? 2 : 1;
+		for (int q = lane; q < a_n; q += 32) W.tr[a_lo + q] = thr_bit<MAXJ>(W.cls[CL_T], a_lo + q) ? 2 : 1;
 	}
 	__syncwarp();
-	S.nkm = nkm; S.nes = nes; S.ntr = ntr; S.ni = ni; S.err = err; S.ncorr = ncorr; S.nskip = nskip; S.x = x;
-	*kkp = kk;
+	return kk;
 }
 
 // isThreadFeasible, cpp:1114-1260, for mate m of the pair held by warp state W.  Warp-uniform.
 template <int B, int MAXJ>
-__device__ __noinline__ MateResult thread_mate(const Table gt, uint32_t locus, uint32_t K, uint32_t WB, uint32_t thread_cth, uint32_t maxnc32,
-                                               bool correction, ThreadWarp<MAXJ, B>& W, int m,
-                                               const uint64_t* __restrict__ rec, uint32_t len, int lane, uint32_t* ctr) {
+__device__ __noinline__ void thread_mate(const Table gt, uint32_t locus, uint32_t K, uint32_t WB, uint32_t thread_cth, uint32_t maxnc32,
+                                         bool correction, ThreadWarp<MAXJ, B>& W, int m,
+                                         const uint64_t* __restrict__ rec, uint32_t len, int lane) {
 	constexpr int CAP = ThreadWarp<MAXJ, B>::CAP, ECAP = ThreadWarp<MAXJ, B>::ECAP;
 	const uint64_t rmask = (1ull << 2 * (K - 1)) - 1;
 	const uint64_t maxnc = maxnc32;
-	MateResult R; R.alned = 0; R.err = 0;
-	MS S;
+	__syncwarp();
+	MateResult& R = W.res[m];                                          // W.res[m] and W.S: warp-uniform values, every lane stores the same
+	MS& S = W.S;
+	R.alned = 0; R.err = 0;
 	S.nkm = (int)len - (int)K + 1; S.nes = (int)len; S.ntr = S.nkm; S.ni = 0; S.err = 0; S.ki = 0; S.nskip = 0; S.ncorr = 0;
 	S.x.score = 0; S.x.nedits = 0; S.x.nm = S.x.nd = S.x.nins = 0; S.x.nrk = 0; S.x.a_lo = 0; S.x.a_n = 0;
-	if (S.nkm < 1 || S.nkm > CAP || S.nes > ECAP) { R.err = 1; R.nkm = 0; R.nes = 0; R.ntr = 0; return R; }
+	if (S.nkm < 1 || S.nkm > CAP || S.nes > ECAP) { R.err = 1; R.nkm = 0; R.nes = 0; R.ntr = 0; return; }
 	// cigar_t::init (cpp:62-67) and read2kmers(.., canonical=false, keepN=true) (h:246-271)
 	__syncwarp();
 	bool anyvalid = false;
@@ -685,21 +696,21 @@ __device__ __noinline__ MateResult thread_mate(const Table gt, uint32_t locus, u
 	}
 	anyvalid = __any_sync(0xffffffffu, anyvalid);
 	__syncwarp();
-	if (!anyvalid) { R.nkm = 0; R.nes = S.nes; R.ntr = S.ntr; return R; }     // D1: a read without a valid k-mer is not threadable (cpp:1124 would be UB)
-	thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, S.nkm, 0, S.nkm, lane, ctr[2]);
-	if (lane == 0) ctr[0] += (uint32_t)S.nkm;
+	if (!anyvalid) { R.nkm = 0; R.nes = S.nes; R.ntr = S.ntr; return; }     // D1: a read without a valid k-mer is not threadable (cpp:1124 would be UB)
+	thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, S.nkm, 0, S.nkm, lane);
+	if (lane == 0) W.cnt[0] += (uint32_t)S.nkm;
 
 	const uint64_t nkm0 = (uint64_t)S.nkm;
 	const uint64_t maxnskip = nkm0 >= thread_cth ? nkm0 - thread_cth : 0;
 	int result = -1;                                                   // -1: fall through to the final test (cpp:1259)
-#define FIND_ANCHOR() ms_find_anchor<B, MAXJ>(W, S, (int)K, lane)
-#define SCORE_AT(bw, kk, mes) ms_score<B, MAXJ>(gt, locus, K, rmask, W, m, S, bw, kk, mes, lane, ctr)
-#define APPLY(bw, kkp) ms_apply<B, MAXJ>(gt, locus, K, rmask, W, m, S, bw, kkp, lane, ctr)
+#define FIND_ANCHOR() ms_find_anchor<B, MAXJ>(W, (int)K, lane)
+#define SCORE_AT(bw, kk, mes) ms_score<B, MAXJ>(gt, locus, K, rmask, W, m, bw, kk, mes, lane)
+#define APPLY(bw, kkvar) { const int kk_new = ms_apply<B, MAXJ>(gt, locus, K, rmask, W, m, bw, kkvar, lane); kkvar = kk_new; }
 
 	if (!FIND_ANCHOR()) result = 0;                                     // cpp:1129
 	else if (S.ki > 0 && correction && S.ncorr < maxnc && (uint64_t)S.ki >= THR_MSC + 1) {   // leading unaligned k-mers, cpp:1131-1141
 		const uint32_t mes = ((uint64_t)S.ki >= 2 * THR_MSC + 2) ? 2 : 1;
-		if (SCORE_AT(true, S.ki, mes)) APPLY(true, &S.ki);
+		if (SCORE_AT(true, S.ki, mes)) APPLY(true, S.ki);
 	}
 	if (result < 0) { ++S.ki; ++S.ni; }
 	// what to do at the end of an iteration: 0 = step (++ki, ++ni), 1 = find_anchor then the skip test and step, 2 = stop
@@ -746,12 +757,12 @@ __device__ __noinline__ MateResult thread_mate(const Table gt, uint32_t locus, u
 			if (SCORE_AT(false, ki, mes)) {                                   // cpp:1192-1197
 				S.nskip += S.x.nedits;
 				if (S.nskip > maxnskip) { result = 0; break; }
-				APPLY(false, &S.ki);
+				APPLY(false, S.ki);
 			} else {                                                          // cpp:1198-1248
 				if (!FIND_ANCHOR()) break;
 				bool skip = !SCORE_AT(true, S.ki, 2);
 				if (!skip) {
-					APPLY(true, &S.ki);
+					APPLY(true, S.ki);
 					++S.ncorr;
 					int64_t gap = (int64_t)min((int64_t)K, (int64_t)S.ki - (int64_t)S.x.nm - (int64_t)S.x.nd) - (int64_t)S.x.score;
 					int64_t ki1 = S.ki;
@@ -766,7 +777,7 @@ __device__ __noinline__ MateResult thread_mate(const Table gt, uint32_t locus, u
 						skip = !SCORE_AT(true, (int)ki1, mes);
 						if (!skip) {
 							int k1 = (int)ki1;
-							APPLY(true, &k1);
+							APPLY(true, k1);
 							ki1 = k1;
 							S.ki += (int)S.x.nd - (int)S.x.nins;
 							gap = (int64_t)min((int64_t)K, ki1 - (int64_t)S.x.nm - (int64_t)S.x.nd) - (int64_t)S.x.score;
@@ -795,7 +806,7 @@ __device__ __noinline__ MateResult thread_mate(const Table gt, uint32_t locus, u
 	if (result < 0) result = (S.nskip <= maxnskip && S.ncorr <= maxnc) ? (S.ncorr ? 2 : 1) : 0;   // cpp:1259
 	if (S.err) result = 0;
 	R.alned = result; R.err = S.err; R.nkm = S.nkm; R.nes = S.nes; R.ntr = S.ntr;
-	return R;
+	__syncwarp();
 }
 
 constexpr uint32_t THR_DST_MASK = (1u << G_LOCUS_BITS) - 1;           // sv.thr_dst[c] = dst | kf bits << 28 | rm bits << 30
@@ -812,7 +823,8 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 	const bool want_rec = trace || aln_all || aln_min;
 	const uint32_t W64 = rp.lay.W64;
 	uint32_t c_fea = 0, c_inc = 0, c_cls = 0;
-	uint32_t ctr[3] = {0, 0, 0};                                       // per lane: walk, ec, refresh probes (measurement)
+	if (lane < 3) W.cnt[lane] = 0;                                     // walk, ec, refresh probes (measurement)
+	__syncwarp();
 
 #pragma unroll 1
 	for (uint32_t t = gwarp; t < nwork; t += nwarps) {
@@ -823,12 +835,12 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 		const uint64_t slot = trace ? (uint64_t)p : (uint64_t)c;
 		const bool slot_ok = want_rec && (trace || slot < rp.max_records);
 		uint8_t* rec = sv.records + slot * rp.rec_stride;
-		MateResult r[2];
+		MateResult* const r = W.res;
 		uint32_t nvalid = 0;                                               // valid k-mers of both edited vectors (lane 0)
 #pragma unroll 1
 		for (int m = 0; m < 2; ++m) {
 			const uint32_t len = sv.meta[m][p] & META_LENMASK;
-			r[m] = thread_mate<B, MAXJ>(ix.gtable, dst, rp.k, rp.lay.WB, rp.thread_cth, rp.max_ncorrection, rp.correction != 0, W, m, sv.packed[m] + (uint64_t)p * W64, len, lane, ctr);
+			thread_mate<B, MAXJ>(ix.gtable, dst, rp.k, rp.lay.WB, rp.thread_cth, rp.max_ncorrection, rp.correction != 0, W, m, sv.packed[m] + (uint64_t)p * W64, len, lane);
 			if (slot_ok) {                                              // sam_t.r1 / r2 -> dbt_aln_mate blob
 				uint8_t* b = rec + sizeof(dbt_pair_record) + (size_t)m * rp.aln_stride;
 				uint8_t* es = b + sizeof(dbt_aln_mate); uint8_t* trb = es + rp.es_cap;
@@ -909,12 +921,11 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 			h->dst = fdst; h->status = (uint8_t)status;
 		}
 	}
-#pragma unroll 1
-	for (int q = 0; q < 3; ++q) ctr[q] = __reduce_add_sync(0xffffffffu, ctr[q]);
+	__syncwarp();
 	if (lane == 0) {
-		if (ctr[0]) atomicAdd(sv.counters + DBT_C_THR_WALK, (unsigned long long)ctr[0]);
-		if (ctr[1]) atomicAdd(sv.counters + DBT_C_THR_EC, (unsigned long long)ctr[1]);
-		if (ctr[2]) atomicAdd(sv.counters + DBT_C_THR_REFRESH, (unsigned long long)ctr[2]);
+		if (W.cnt[0]) atomicAdd(sv.counters + DBT_C_THR_WALK, (unsigned long long)W.cnt[0]);
+		if (W.cnt[1]) atomicAdd(sv.counters + DBT_C_THR_EC, (unsigned long long)W.cnt[1]);
+		if (W.cnt[2]) atomicAdd(sv.counters + DBT_C_THR_REFRESH, (unsigned long long)W.cnt[2]);
 		if (c_cls) atomicAdd(sv.counters + DBT_C_THR_CLS, (unsigned long long)c_cls);
 		if (c_fea) atomicAdd(sv.counters + DBT_C_NFEASIBLEREADS, (unsigned long long)c_fea);
 		if (c_inc) atomicAdd(sv.counters + DBT_C_NINC, (unsigned long long)c_inc);
