@@ -10,8 +10,9 @@
 // (cpp:1091-1106, getOutNodes_rc) its reverse-strand mask from the probe the forward walk already made.
 //
 // Slot (16 B): { u64 key | bit63 = bucket-overflow flag (slot 0 only) ; u32 lw ; u32 tr }
-//   lw : locus (bits 0-21) | mask of the canonical orientation (22-25) | mask of the rc orientation (26-29)
-//        | present(canonical orientation) (30) | present(rc orientation) (31)
+//   lw : locus (bits 0-21) | canonical orientation: present (22), out-edge mask (23-26)
+//        | rc orientation: present (27), out-edge mask (28-31)
+//        -- the two 5-bit fields are what a probe hands out (GNode.bits), swapped for a k-mer met in its rc orientation
 //   tr : position in the output-ordered count array + 1 when the canonical k-mer is a TR k-mer of the locus, else 0.
 //        TR k-mers that are not graph nodes get an entry with both present bits clear, so that the annotation
 //        and the counting stay exact for arbitrary input files.
@@ -25,17 +26,18 @@ namespace dbt {
 
 constexpr uint32_t G_LOCUS_BITS = 22;
 constexpr uint32_t G_LOCUS_MASK = (1u << G_LOCUS_BITS) - 1;
-constexpr uint32_t G_PRESENT_CA = 1u << 30, G_PRESENT_RC = 1u << 31;
+constexpr uint32_t G_PRESENT_CA = 1u << 22, G_PRESENT_RC = 1u << 27;
+constexpr uint32_t G_MASK_CA_SHIFT = 23, G_MASK_RC_SHIFT = 28;
 
 // what one probe tells about a STRAND-SPECIFIC k-mer
 struct GNode {
-	uint32_t bits;    // bit0 present; bits 1-4 out-edge mask of this orientation; bits 5-8 mask of the opposite orientation;
-	                  // bit 9 opposite orientation present; bit 10 canonical k-mer is a TR k-mer of the locus
+	uint32_t bits;    // bit0 present; bits 1-4 out-edge mask of this orientation; bit 5 opposite orientation present;
+	                  // bits 6-9 mask of the opposite orientation; bit 10 canonical k-mer is a TR k-mer of the locus
 	uint32_t tr;      // count-array position + 1, or 0
 };
-constexpr uint32_t GN_PRESENT = 1u, GN_RCPRESENT = 1u << 9, GN_TR = 1u << 10;
+constexpr uint32_t GN_PRESENT = 1u, GN_RCPRESENT = 1u << 5, GN_TR = 1u << 10;
 __device__ __forceinline__ uint32_t gn_mask(uint32_t bits) { return (bits >> 1) & 0xFu; }
-__device__ __forceinline__ uint32_t gn_rcmask(uint32_t bits) { return (bits >> 5) & 0xFu; }
+__device__ __forceinline__ uint32_t gn_rcmask(uint32_t bits) { return (bits >> 6) & 0xFu; }
 
 __device__ __forceinline__ uint64_t g_hash_key(uint64_t canon, uint32_t locus) {
 	return canon ^ ((uint64_t)locus * 0xC2B2AE3D27D4EB4Full);
@@ -47,11 +49,11 @@ __device__ __forceinline__ uint64_t kmer_rc(uint64_t x, uint32_t k) {
 }
 
 __device__ __forceinline__ GNode g_decode(uint32_t lw, uint32_t tr, bool is_rc) {
-	// x = [mask_ca(0-3) | mask_rc(4-7) | present_ca(8) | present_rc(9)]; for the rc orientation swap the two halves
+	// x = [canonical orientation: present, mask | rc orientation: present, mask]; met in rc orientation: swap the halves
 	uint32_t x = lw >> 22;
-	if (is_rc) x = ((x & 0x10Fu) << 4 & 0xF0u) | ((x >> 4) & 0xFu) | ((x & 0x100u) << 1) | ((x >> 1) & 0x100u);
+	if (is_rc) x = ((x & 31u) << 5) | (x >> 5);
 	GNode n;
-	n.bits = ((x >> 8) & 1u) | ((x & 0xFFu) << 1) | (x & 0x200u) | (tr ? GN_TR : 0u);
+	n.bits = x | (tr ? GN_TR : 0u);
 	n.tr = tr;
 	return n;
 }

@@ -30,10 +30,10 @@ namespace dbt {
 #define THR_WARPS_N 4
 #endif
 #ifndef THR_MINBLOCKS
-#define THR_MINBLOCKS 4
+#define THR_MINBLOCKS 7                            // 72 registers; with THR_STAGE_GROUPS 2 the 7.4 KB of shared memory per warp admit 7 blocks per SM
 #endif
 #ifndef THR_STAGE_GROUPS
-#define THR_STAGE_GROUPS 16                        // 32-position groups probed per round of thr_refresh (capped at MAXJ)
+#define THR_STAGE_GROUPS 2                         // 32-position groups probed per round of thr_refresh (capped at MAXJ)
 #endif
 #ifndef THR_REFRESH_INLINE
 #define THR_REFRESH_INLINE __noinline__
@@ -312,29 +312,25 @@ __device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K
 	// that thr_refresh has already probed: g0bits = its GNode bits in the walk's orientation (W.info)
 	if (!(g0bits & GN_PRESENT)) err = 1;
 	const uint32_t nts0 = gn_mask(g0bits);
-	// level 1 (lanes 0-3) and level 2 (lanes 0-15) of the expansion, cpp:907-920
-	uint32_t m1 = 0; uint64_t n1 = 0; bool bad = false;
-	if (lane < 4 && ((nts0 >> lane) & 1u)) {
-		n1 = ((node & rmask) << 2) + (uint64_t)lane;
-		++n_ec;
-		const GNode g = g_lookup<B>(gt, n1, locus, K);
-		if (!(g.bits & GN_PRESENT)) bad = true;
-		m1 = gn_mask(g.bits);
-	}
-	const uint32_t nts1 = __reduce_or_sync(0xffffffffu, m1);
-	uint32_t m2 = 0;
+	// level 1 (lanes 16-19) and level 2 (lanes 0-15) of the expansion, cpp:907-920, probed in ONE round: the level-2 node
+	// ((n1_i & rmask) << 2) + j is known without the level-1 answer, only whether the reference would visit it (edge j of
+	// n1_i set) is not -- so it is probed speculatively and counted / checked / used only if that edge exists
+	uint32_t myb = 0; bool pres = false, probe = false; uint64_t nd = 0;
 	{
-		const int i = (lane >> 2) & 3, j = lane & 3;
-		const uint32_t m1i = __shfl_sync(0xffffffffu, m1, i);
-		if (lane < 16 && ((nts0 >> i) & 1u) && ((m1i >> j) & 1u)) {
-			const uint64_t n1i = ((node & rmask) << 2) + (uint64_t)i;
-			const uint64_t n2 = ((n1i & rmask) << 2) + (uint64_t)j;
-			++n_ec;
-			const GNode g = g_lookup<B>(gt, n2, locus, K);
-			if (!(g.bits & GN_PRESENT)) bad = true;
-			m2 = gn_mask(g.bits);
+		const uint32_t i = lane < 16 ? (uint32_t)(lane >> 2) : (uint32_t)(lane - 16);
+		if (lane < 20 && ((nts0 >> i) & 1u)) {
+			nd = ((node & rmask) << 2) + (uint64_t)i;
+			if (lane < 16) nd = ((nd & rmask) << 2) + (uint64_t)(lane & 3);
+			probe = true;
 		}
 	}
+	if (probe) { const GNode g = g_lookup<B>(gt, nd, locus, K); pres = (g.bits & GN_PRESENT) != 0; myb = gn_mask(g.bits); }
+	const uint32_t m1i = __shfl_sync(0xffffffffu, myb, 16 + ((lane >> 2) & 3));     // out-edges of n1_i, i = (lane >> 2) & 3
+	const uint32_t nts1 = __reduce_or_sync(0xffffffffu, (lane >= 16 && lane < 20) ? myb : 0u);
+	const bool real2 = lane < 16 && probe && ((m1i >> (lane & 3)) & 1u);
+	const uint32_t m2 = real2 ? myb : 0u;
+	if ((lane >= 16 && probe) || real2) ++n_ec;
+	const bool bad = ((lane >= 16 && probe) || real2) && !pres;
 	if (__any_sync(0xffffffffu, bad)) err = 1;
 	const uint32_t nts2 = __reduce_or_sync(0xffffffffu, m2);
 	const uint32_t mlo = __reduce_or_sync(0xffffffffu, lane < 8 ? (m2 << (4 * lane)) : 0u);
@@ -827,8 +823,18 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 	__syncwarp();
 
 #pragma unroll 1
+#ifdef THR_BLOCKSYNC
+	// experiment: the warps of a block start every mate together (block-uniform trip count, one barrier per mate), so that
+	// the warps sharing an SM sub-partition run the same probe/classify loops at the same time (instruction-cache locality)
+	for (uint32_t t0 = blockIdx.x * THR_WARPS; t0 < nwork; t0 += gridDim.x * THR_WARPS) {
+		const uint32_t t = t0 + (threadIdx.x >> 5);
+		const bool act = t < nwork;
+		const uint32_t c = sv.thr[act ? t : t0];
+#else
 	for (uint32_t t = gwarp; t < nwork; t += nwarps) {
+		const bool act = true;
 		const uint32_t c = sv.thr[t];
+#endif
 		const uint32_t p = sv.cand[c];
 		const uint32_t dw = sv.thr_dst[c];
 		const uint32_t dst = dw & THR_DST_MASK;
@@ -839,6 +845,10 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 		uint32_t nvalid = 0;                                               // valid k-mers of both edited vectors (lane 0)
 #pragma unroll 1
 		for (int m = 0; m < 2; ++m) {
+#ifdef THR_BLOCKSYNC
+			__syncthreads();
+#endif
+			if (!act) continue;
 			const uint32_t len = sv.meta[m][p] & META_LENMASK;
 			thread_mate<B, MAXJ>(ix.gtable, dst, rp.k, rp.lay.WB, rp.thread_cth, rp.max_ncorrection, rp.correction != 0, W, m, sv.packed[m] + (uint64_t)p * W64, len, lane);
 			if (slot_ok) {                                              // sam_t.r1 / r2 -> dbt_aln_mate blob
@@ -881,6 +891,7 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 			}
 			__syncwarp();
 		}
+		if (!act) continue;
 		const bool alned = r[0].alned || r[1].alned;                       // commented caller, cpp:2082-2087
 		if (alned) {
 			if (lane == 0) c_fea += 2;
@@ -954,13 +965,13 @@ __global__ void graph_insert_kernel(Table t, const uint64_t* __restrict__ kmers,
 	const bool is_rc = rc < fw;
 	if (pass == 0) {
 		if (is_rc) return;
-		uint32_t lw = loc | (mk << 22) | G_PRESENT_CA;
-		if (rc == fw) lw |= (mk << 26) | G_PRESENT_RC;                    // palindrome (even k): both orientations are this node
+		uint32_t lw = loc | (mk << G_MASK_CA_SHIFT) | G_PRESENT_CA;
+		if (rc == fw) lw |= (mk << G_MASK_RC_SHIFT) | G_PRESENT_RC;                    // palindrome (even k): both orientations are this node
 		if (!g_claim<B>(t, fw, loc, lw, 0)) atomicOr(err, ERR_INDEX_FULL);
 	} else {
 		if (!is_rc) return;
 		uint4* s = g_find_slot<B>(t, rc, loc);
-		const uint32_t add = (mk << 26) | G_PRESENT_RC;
+		const uint32_t add = (mk << G_MASK_RC_SHIFT) | G_PRESENT_RC;
 		if (s) atomicOr(reinterpret_cast<uint32_t*>(s) + 2, add);
 		else if (!g_claim<B>(t, rc, loc, loc | add, 0)) atomicOr(err, ERR_INDEX_FULL);
 	}
