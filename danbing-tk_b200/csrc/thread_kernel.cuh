@@ -698,6 +698,28 @@ __device__ __noinline__ void thread_mate(const Table gt, uint32_t locus, uint32_
 
 	const uint64_t nkm0 = (uint64_t)S.nkm;
 	const uint64_t maxnskip = nkm0 >= thread_cth ? nkm0 - thread_cth : 0;
+	{	// Error-free mate (three quarters of them): the first k-mer is a node and every later k-mer matches an out-edge of its
+		// predecessor.  The reference then anchors at 0 (cpp:1129, find_anchor marks es[0..k) '='), walks the whole read through
+		// cpp:1167-1180 (tr[i] = '=' / '.', es[i+k-1] = '=') and returns 1 (cpp:1259: no skip, no correction).  Written directly.
+		const int nkm = S.nkm, nes = S.nes;
+		bool ok = true;
+		if (lane < MAXJ && lane * 32 < nkm) {
+			const int n = min(32, nkm - lane * 32);
+			const uint32_t want = n == 32 ? 0xFFFFFFFFu : ((1u << n) - 1u);
+			const uint32_t mm = W.cls[CL_M][lane] | (lane == 0 ? (W.cls[CL_P][0] & 1u) : 0u);
+			ok = mm == want;
+		}
+		if (__all_sync(0xffffffffu, ok)) {
+#pragma unroll 1
+			for (int i = lane; i < nes; i += 32) W.es_t[i] = ET_EQ;
+#pragma unroll 1
+			for (int i = lane; i < nkm; i += 32) W.tr[i] = thr_bit<MAXJ>(W.cls[CL_T], i) ? 2 : 1;
+			__syncwarp();
+			R.alned = 1; R.err = 0; R.nkm = nkm; R.nes = nes; R.ntr = S.ntr;
+			__syncwarp();
+			return;
+		}
+	}
 	int result = -1;                                                   // -1: fall through to the final test (cpp:1259)
 #define FIND_ANCHOR() ms_find_anchor<B, MAXJ>(W, (int)K, lane)
 #define SCORE_AT(bw, kk, mes) ms_score<B, MAXJ>(gt, locus, K, rmask, W, m, bw, kk, mes, lane)
@@ -823,18 +845,8 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 	__syncwarp();
 
 #pragma unroll 1
-#ifdef THR_BLOCKSYNC
-	// experiment: the warps of a block start every mate together (block-uniform trip count, one barrier per mate), so that
-	// the warps sharing an SM sub-partition run the same probe/classify loops at the same time (instruction-cache locality)
-	for (uint32_t t0 = blockIdx.x * THR_WARPS; t0 < nwork; t0 += gridDim.x * THR_WARPS) {
-		const uint32_t t = t0 + (threadIdx.x >> 5);
-		const bool act = t < nwork;
-		const uint32_t c = sv.thr[act ? t : t0];
-#else
 	for (uint32_t t = gwarp; t < nwork; t += nwarps) {
-		const bool act = true;
 		const uint32_t c = sv.thr[t];
-#endif
 		const uint32_t p = sv.cand[c];
 		const uint32_t dw = sv.thr_dst[c];
 		const uint32_t dst = dw & THR_DST_MASK;
@@ -845,10 +857,6 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 		uint32_t nvalid = 0;                                               // valid k-mers of both edited vectors (lane 0)
 #pragma unroll 1
 		for (int m = 0; m < 2; ++m) {
-#ifdef THR_BLOCKSYNC
-			__syncthreads();
-#endif
-			if (!act) continue;
 			const uint32_t len = sv.meta[m][p] & META_LENMASK;
 			thread_mate<B, MAXJ>(ix.gtable, dst, rp.k, rp.lay.WB, rp.thread_cth, rp.max_ncorrection, rp.correction != 0, W, m, sv.packed[m] + (uint64_t)p * W64, len, lane);
 			if (slot_ok) {                                              // sam_t.r1 / r2 -> dbt_aln_mate blob
@@ -891,7 +899,6 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 			}
 			__syncwarp();
 		}
-		if (!act) continue;
 		const bool alned = r[0].alned || r[1].alned;                       // commented caller, cpp:2082-2087
 		if (alned) {
 			if (lane == 0) c_fea += 2;
