@@ -55,7 +55,7 @@ struct Txt {                                       // thread_ext_t, cpp:596-625 
 	int a_lo, a_n;                                 // annotation range to fill from the refreshed TR bits
 };
 
-struct MateResult { int alned, err, nkm, nes, ntr; };
+struct MateResult { int alned, err, nkm, nes, ntr, clean; };   // clean: error-free mate, es / tr not materialised (all '=', tr from the TR ballots)
 
 // Mutable state of one mate's walk (warp-uniform).  It lives in SHARED memory (ThreadWarp::S): find_anchor / score / apply
 // are single out-of-line functions working on it by reference (the kernel is instruction-fetch sensitive: every inlined
@@ -668,19 +668,13 @@ __device__ __noinline__ void thread_mate(const Table gt, uint32_t locus, uint32_
 	__syncwarp();
 	MateResult& R = W.res[m];                                          // W.res[m] and W.S: warp-uniform values, every lane stores the same
 	MS& S = W.S;
-	R.alned = 0; R.err = 0;
+	R.alned = 0; R.err = 0; R.clean = 0;
 	S.nkm = (int)len - (int)K + 1; S.nes = (int)len; S.ntr = S.nkm; S.ni = 0; S.err = 0; S.ki = 0; S.nskip = 0; S.ncorr = 0;
 	S.x.score = 0; S.x.nedits = 0; S.x.nm = S.x.nd = S.x.nins = 0; S.x.nrk = 0; S.x.a_lo = 0; S.x.a_n = 0;
 	if (S.nkm < 1 || S.nkm > CAP || S.nes > ECAP) { R.err = 1; R.nkm = 0; R.nes = 0; R.ntr = 0; return; }
-	// cigar_t::init (cpp:62-67) and read2kmers(.., canonical=false, keepN=true) (h:246-271)
+	// read2kmers(.., canonical=false, keepN=true) (h:246-271)
 	__syncwarp();
 	bool anyvalid = false;
-#pragma unroll 1
-	for (int i = lane; i < S.nes; i += 32) {
-		const uint32_t code = (uint32_t)(rec[i >> 5] >> (2 * (i & 31))) & 3u;
-		const bool inv = (rec[WB + (i >> 6)] >> (i & 63)) & 1ull;
-		W.es_t[i] = ET_STAR; W.es_r[i] = inv ? ER_INVALID : (uint8_t)(code + 1); W.es_g[i] = 0;
-	}
 #pragma unroll 1
 	for (int i = lane; i < S.nkm; i += 32) {
 		uint64_t f = KMER_INVALID, rc = KMER_INVALID;
@@ -688,20 +682,20 @@ __device__ __noinline__ void thread_mate(const Table gt, uint32_t locus, uint32_
 			const uint64_t w = extract_bits(rec, 2u * i, 2 * K);
 			f = rev2(w) >> (64 - 2 * K); rc = (~w) & (K < 32 ? (1ull << 2 * K) - 1 : ~0ull); anyvalid = true;
 		}
-		W.km[i] = f; W.rck[i] = rc; W.tr[i] = 0;
+		W.km[i] = f; W.rck[i] = rc;
 	}
 	anyvalid = __any_sync(0xffffffffu, anyvalid);
 	__syncwarp();
-	if (!anyvalid) { R.nkm = 0; R.nes = S.nes; R.ntr = S.ntr; return; }     // D1: a read without a valid k-mer is not threadable (cpp:1124 would be UB)
-	thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, S.nkm, 0, S.nkm, lane);
-	if (lane == 0) W.cnt[0] += (uint32_t)S.nkm;
-
 	const uint64_t nkm0 = (uint64_t)S.nkm;
 	const uint64_t maxnskip = nkm0 >= thread_cth ? nkm0 - thread_cth : 0;
-	{	// Error-free mate (three quarters of them): the first k-mer is a node and every later k-mer matches an out-edge of its
+	if (anyvalid) {
+		thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, S.nkm, 0, S.nkm, lane);
+		if (lane == 0) W.cnt[0] += (uint32_t)S.nkm;
+		// Error-free mate (three quarters of them): the first k-mer is a node and every later k-mer matches an out-edge of its
 		// predecessor.  The reference then anchors at 0 (cpp:1129, find_anchor marks es[0..k) '='), walks the whole read through
-		// cpp:1167-1180 (tr[i] = '=' / '.', es[i+k-1] = '=') and returns 1 (cpp:1259: no skip, no correction).  Written directly.
-		const int nkm = S.nkm, nes = S.nes;
+		// cpp:1167-1180 (tr[i] = '=' / '.', es[i+k-1] = '=') and returns 1 (cpp:1259: no skip, no correction): every CIGAR entry
+		// is '=' and tr follows the TR ballots -- the kernel writes the record from those, es / tr are not materialised.
+		const int nkm = S.nkm;
 		bool ok = true;
 		if (lane < MAXJ && lane * 32 < nkm) {
 			const int n = min(32, nkm - lane * 32);
@@ -710,16 +704,21 @@ __device__ __noinline__ void thread_mate(const Table gt, uint32_t locus, uint32_
 			ok = mm == want;
 		}
 		if (__all_sync(0xffffffffu, ok)) {
-#pragma unroll 1
-			for (int i = lane; i < nes; i += 32) W.es_t[i] = ET_EQ;
-#pragma unroll 1
-			for (int i = lane; i < nkm; i += 32) W.tr[i] = thr_bit<MAXJ>(W.cls[CL_T], i) ? 2 : 1;
-			__syncwarp();
-			R.alned = 1; R.err = 0; R.nkm = nkm; R.nes = nes; R.ntr = S.ntr;
+			R.alned = 1; R.err = 0; R.nkm = nkm; R.nes = S.nes; R.ntr = S.ntr; R.clean = 1;
 			__syncwarp();
 			return;
 		}
 	}
+	// cigar_t::init (cpp:62-67)
+#pragma unroll 1
+	for (int i = lane; i < S.nes; i += 32) {
+		const uint32_t code = (uint32_t)(rec[i >> 5] >> (2 * (i & 31))) & 3u;
+		const bool inv = (rec[WB + (i >> 6)] >> (i & 63)) & 1ull;
+		W.es_t[i] = ET_STAR; W.es_r[i] = inv ? ER_INVALID : (uint8_t)(code + 1); W.es_g[i] = 0;
+		if (i < S.nkm) W.tr[i] = 0;
+	}
+	__syncwarp();
+	if (!anyvalid) { R.nkm = 0; R.nes = S.nes; R.ntr = S.ntr; return; }     // D1: a read without a valid k-mer is not threadable (cpp:1124 would be UB)
 	int result = -1;                                                   // -1: fall through to the final test (cpp:1259)
 #define FIND_ANCHOR() ms_find_anchor<B, MAXJ>(W, (int)K, lane)
 #define SCORE_AT(bw, kk, mes) ms_score<B, MAXJ>(gt, locus, K, rmask, W, m, bw, kk, mes, lane)
@@ -869,14 +868,20 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 				for (int q = lane; q < (int)rp.es_cap / 4; q += 32) {
 					const int nb = nes - 4 * q;
 					const uint32_t keep = nb >= 4 ? 0xFFFFFFFFu : (nb <= 0 ? 0u : (1u << 8 * nb) - 1u);
-					const uint32_t v = reinterpret_cast<const uint32_t*>(W.es_t)[q] | ((reinterpret_cast<const uint32_t*>(W.es_g)[q] & 0x07070707u) << 3);
+					const uint32_t v = r[m].clean ? 0x01010101u * ET_EQ
+					                              : (reinterpret_cast<const uint32_t*>(W.es_t)[q] | ((reinterpret_cast<const uint32_t*>(W.es_g)[q] & 0x07070707u) << 3));
 					reinterpret_cast<uint32_t*>(es)[q] = v & keep;
 				}
 #pragma unroll 1
 				for (int q = lane; q < (int)rp.tr_cap / 4; q += 32) {
 					const int nb = ntr - 4 * q;
 					const uint32_t keep = nb >= 4 ? 0xFFFFFFFFu : (nb <= 0 ? 0u : (1u << 8 * nb) - 1u);
-					reinterpret_cast<uint32_t*>(trb)[q] = reinterpret_cast<const uint32_t*>(W.tr)[q] & keep;
+					uint32_t v;
+					if (r[m].clean) {                                       // tr[i] = '=' (2) for TR k-mers, '.' (1) otherwise: 4 TR ballot bits -> 4 bytes
+						const uint32_t bits = 4 * q < MAXJ * 32 ? (W.cls[CL_T][(4 * q) >> 5] >> ((4 * q) & 31)) & 0xFu : 0u;
+						v = 0x01010101u + ((bits & 1u) | ((bits & 2u) << 7) | ((bits & 4u) << 14) | ((bits & 8u) << 21));
+					} else v = reinterpret_cast<const uint32_t*>(W.tr)[q];
+					reinterpret_cast<uint32_t*>(trb)[q] = v & keep;
 				}
 				if (lane == 0) {
 					dbt_aln_mate* h = reinterpret_cast<dbt_aln_mate*>(b);
