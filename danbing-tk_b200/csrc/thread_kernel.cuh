@@ -30,10 +30,28 @@ namespace dbt {
 #define THR_WARPS_N 4
 #endif
 #ifndef THR_MINBLOCKS
-#define THR_MINBLOCKS 7                            // 72 registers; with THR_STAGE_GROUPS 2 the 7.4 KB of shared memory per warp admit 7 blocks per SM
+#define THR_MINBLOCKS 7                            // 72 registers; with THR_STAGE_GROUPS 1 the 6.4 KB of shared memory per warp admit 7 blocks per SM
 #endif
 #ifndef THR_STAGE_GROUPS
-#define THR_STAGE_GROUPS 2                         // 32-position groups probed per round of thr_refresh (capped at MAXJ)
+#define THR_STAGE_GROUPS 1                         // 32-position groups probed per round of thr_refresh (capped at MAXJ)
+#endif
+// inlining policy of the correction code, each measured on the GPU (profiles/r1/s17_thread_by_function.txt): out-of-line
+// edit_kmers_backward 8.80 -> 9.21 ms, + edit_kmers_forward 10.55 ms, out-of-line vector primitives 9.56 ms (the calls spill
+// through local memory, which misses an L1 squeezed by the shared-memory carve-out) -- all three stay inlined
+#ifdef THR_NI_BACK
+#define THR_BACK_INLINE __noinline__
+#else
+#define THR_BACK_INLINE __forceinline__
+#endif
+#ifdef THR_NI_FWD
+#define THR_FWD_INLINE __noinline__
+#else
+#define THR_FWD_INLINE __forceinline__
+#endif
+#ifdef THR_NI_TS
+#define THR_TS_INLINE __noinline__
+#else
+#define THR_TS_INLINE __forceinline__
 #endif
 #ifndef THR_REFRESH_INLINE
 #define THR_REFRESH_INLINE __noinline__
@@ -99,32 +117,32 @@ struct TState {
 };
 
 // ---- lane-0 vector primitives (bounds violations = undefined behaviour in the reference -> err) ----
-__device__ __forceinline__ void ts_km_insert(TState& T, int pos, uint64_t v) {
+__device__ THR_TS_INLINE void ts_km_insert(TState& T, int pos, uint64_t v) {
 	if (T.nkm + 1 > T.cap || pos < 0 || pos > T.nkm) { T.err = 1; return; }
 	for (int i = T.nkm; i > pos; --i) T.km[i] = T.km[i - 1];
 	T.km[pos] = v; ++T.nkm;
 }
-__device__ __forceinline__ void ts_km_erase(TState& T, int a, int b) {
+__device__ THR_TS_INLINE void ts_km_erase(TState& T, int a, int b) {
 	if (a < 0 || b > T.nkm || a > b) { T.err = 1; return; }
 	for (int i = b; i < T.nkm; ++i) T.km[i - (b - a)] = T.km[i];
 	T.nkm -= (b - a);
 }
-__device__ __forceinline__ void ts_tr_insert(TState& T, int pos, uint8_t v) {
+__device__ THR_TS_INLINE void ts_tr_insert(TState& T, int pos, uint8_t v) {
 	if (T.ntr + 1 > T.cap || pos < 0 || pos > T.ntr) { T.err = 1; return; }
 	for (int i = T.ntr; i > pos; --i) T.tr[i] = T.tr[i - 1];
 	T.tr[pos] = v; ++T.ntr;
 }
-__device__ __forceinline__ void ts_tr_erase(TState& T, int a, int b) {
+__device__ THR_TS_INLINE void ts_tr_erase(TState& T, int a, int b) {
 	if (a < 0 || b > T.ntr || a > b) { T.err = 1; return; }
 	for (int i = b; i < T.ntr; ++i) T.tr[i - (b - a)] = T.tr[i];
 	T.ntr -= (b - a);
 }
-__device__ __forceinline__ void ts_es_insert(TState& T, int pos, uint8_t t, uint8_t r, uint8_t g) {
+__device__ THR_TS_INLINE void ts_es_insert(TState& T, int pos, uint8_t t, uint8_t r, uint8_t g) {
 	if (T.nes + 1 > T.ecap || pos < 0 || pos > T.nes) { T.err = 1; return; }
 	for (int i = T.nes; i > pos; --i) { T.es_t[i] = T.es_t[i - 1]; T.es_r[i] = T.es_r[i - 1]; T.es_g[i] = T.es_g[i - 1]; }
 	T.es_t[pos] = t; T.es_r[pos] = r; T.es_g[pos] = g; ++T.nes;
 }
-__device__ __forceinline__ void ts_es_erase(TState& T, int pos) {
+__device__ THR_TS_INLINE void ts_es_erase(TState& T, int pos) {
 	if (pos < 0 || pos >= T.nes) { T.err = 1; return; }
 	for (int i = pos + 1; i < T.nes; ++i) { T.es_t[i - 1] = T.es_t[i]; T.es_r[i - 1] = T.es_r[i]; T.es_g[i - 1] = T.es_g[i]; }
 	--T.nes;
@@ -136,7 +154,7 @@ __device__ __forceinline__ uint64_t ts_km(TState& T, int i) { if (i < 0 || i >= 
 // thread_ext_t::edit_kmers_forward, cpp:828-862 (lane 0).  The reference snapshots good[]/nts[] of the tail before
 // editing (cpp:829-832); element `dt_nti` of those snapshots is exactly the not-yet-rewritten k-mer that sits at
 // position i when it is consumed (cpp:842-845), so the tail is read in place.
-__device__ __forceinline__ void edit_kmers_forward(TState& T, Txt& x, int& ki_io, uint64_t& ncorrection) {
+__device__ THR_FWD_INLINE void edit_kmers_forward(TState& T, Txt& x, int& ki_io, uint64_t& ncorrection) {
 	const int ksize = (int)T.k;
 	int ki = ki_io;
 	x.nm = x.nd = x.nins = 0;
@@ -174,7 +192,7 @@ __device__ __forceinline__ void edit_kmers_forward(TState& T, Txt& x, int& ki_io
 
 // thread_ext_t::edit_kmers_backward, cpp:649-826 (lane 0).  good[]/nts[] (cpp:651-656) are read in place for the
 // same reason as above: position i-1 is still the original prefix k-mer when cpp:683-686 rewrites it.
-__device__ __forceinline__ void edit_kmers_backward(TState& T, Txt& x, int& ki_io, uint64_t& ncorrection, uint64_t& nskip) {
+__device__ THR_BACK_INLINE void edit_kmers_backward(TState& T, Txt& x, int& ki_io, uint64_t& ncorrection, uint64_t& nskip) {
 	const int ksize = (int)T.k;
 	int ki = ki_io;
 	const uint64_t lmask = 3ull << 2 * (ksize - 1), lbase = 1ull << 2 * (ksize - 1);
@@ -300,6 +318,14 @@ __device__ __forceinline__ void edit_kmers_backward(TState& T, Txt& x, int& ki_i
 	ki_io = ki;
 }
 
+template <int B>
+__device__ __noinline__ GNode g_lookup_nl(const Table gt, uint64_t fw, uint32_t locus, uint32_t k) { return g_lookup<B>(gt, fw, locus, k); }
+#ifdef THR_INLINE_LOOKUP
+#define EC_LOOKUP g_lookup
+#else
+#define EC_LOOKUP g_lookup_nl                      // one out-of-line copy for the three look-up sites of the edit scorer: 8.80 -> 8.61 ms
+#endif
+
 // ---- warp-parallel edit scorer: errorCorrection_forward, cpp:898-1089 ----
 // W.win()[j+1] holds kmers[ki+j] for j = -1 .. k+1 (KMER_INVALID beyond the vector), nrem = nkmers - ki.
 // Returns (warp-uniform) true when an edit was found; x.et/eg/score/nedits describe it.  err |= graph not closed.
@@ -324,7 +350,7 @@ __device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K
 			probe = true;
 		}
 	}
-	if (probe) { const GNode g = g_lookup<B>(gt, nd, locus, K); pres = (g.bits & GN_PRESENT) != 0; myb = gn_mask(g.bits); }
+	if (probe) { const GNode g = EC_LOOKUP<B>(gt, nd, locus, K); pres = (g.bits & GN_PRESENT) != 0; myb = gn_mask(g.bits); }
 	const uint32_t m1i = __shfl_sync(0xffffffffu, myb, 16 + ((lane >> 2) & 3));     // out-edges of n1_i, i = (lane >> 2) & 3
 	const uint32_t nts1 = __reduce_or_sync(0xffffffffu, (lane >= 16 && lane < 20) ? myb : 0u);
 	const bool real2 = lane < 16 && probe && ((m1i >> (lane & 3)) & 1u);
@@ -408,7 +434,7 @@ __device__ __noinline__ bool ec_score(const Table gt, uint32_t locus, uint32_t K
 					const uint64_t low = (PB >> (2 * (31 - (jb0 + nb)))) & ((1ull << (2 * nb)) - 1);
 					const uint64_t c = ((cr0 << (2 * nb)) | low) & kmask;
 					b = (uint32_t)(c & 3);
-					const GNode g = g_lookup<B>(gt, c, locus, K);
+					const GNode g = EC_LOOKUP<B>(gt, c, locus, K);
 					pres = (g.bits & GN_PRESENT) != 0; msk = gn_mask(g.bits);
 				}
 				const uint32_t pm = __shfl_up_sync(0xffffffffu, msk, 1);
