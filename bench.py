@@ -7,7 +7,9 @@ Contract (driver): `python bench.py --gpus N --steps K --warmup W` prints ONE JS
               (weak scaling, RPGG replicated) and a step ends with the NCCL sum-reduce of the counts.
   value     = read pairs/s, whole job, packed reads already resident in HBM (CUDA events, max over ranks)
   e2e       = same metric through the C ABI with HOST buffers: pinned ASCII reads -> dbt_submit (H2D +
-              device 2-bit pack + kernels) -> dbt_wait (D2H of counters + kam records), double-buffered
+              device 2-bit pack + kernels) -> dbt_wait (D2H of counters + kam/aln records), double-buffered.
+              --e2e-input both (default) also times the host-packed and the hybrid input path from the same
+              ASCII reads (dbt_pack_reads inside the timed region) and reports the fastest, the rest in other_paths
   roofline  = dominant kernel's algorithmic HBM bytes / its CUDA-event time vs MEASURED_PEAKS.json
   cpu_baseline = the UNMODIFIED reference (oracle/_ref/danbing-tk -p nproc) on a bounded sample of the
               same workload on this box's host cores, outputs diffed against the GPU's (bit-exact gate)
