@@ -616,8 +616,7 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 					status = DBT_ST_THREAD_PENDING;
 					if (lane == 0) {
 						c_thr0 += 2;
-						sv.thr_dst[c] = dst | ((uint32_t)(kf[0] | (kf[1] << 1)) << 28) | ((uint32_t)(rm[0] | (rm[1] << 1)) << 30);
-						sv.thr[atomicAdd(sv.ncand + 3, 1u)] = c;
+						sv.thr[atomicAdd(sv.ncand + 3, 1u)] = make_uint4(c, p, dst | ((uint32_t)(kf[0] | (kf[1] << 1)) << 28) | ((uint32_t)(rm[0] | (rm[1] << 1)) << 30), 0u);
 					}
 				} else { status = DBT_ST_NOT_THREADED; if (lane == 0) c_thr0 += 2; }   // cpp:2070-2090 at HEAD
 			}

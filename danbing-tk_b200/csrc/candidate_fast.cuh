@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 		if (status < 0 && (rp.flags & DBT_F_THREADING)) {
 			if (rp.thr_on) {                                     // restored threading: hand the pair to thread_kernel (cpp:2070-2088)
 				status = DBT_ST_THREAD_PENDING;
-				if (lane == 0) { c_thr0 += 2; sv.thr_dst[c] = dst | (kfm << 28) | (rmm << 30); sv.thr[atomicAdd(sv.ncand + 3, 1u)] = c; }
+				if (lane == 0) { c_thr0 += 2; sv.thr[atomicAdd(sv.ncand + 3, 1u)] = make_uint4(c, p, dst | (kfm << 28) | (rmm << 30), 0u); }
 			} else { status = DBT_ST_NOT_THREADED; if (lane == 0) c_thr0 += 2; }   // cpp:2070-2090 at HEAD
 		}
 		if (status < 0) {

@@ -71,7 +71,7 @@ struct Slot {
 	cudaStream_t st = nullptr;
 	uint8_t* d_ascii = nullptr; uint64_t* d_offsets = nullptr;
 	uint64_t* d_packed[2] = {nullptr, nullptr}; uint16_t* d_meta[2] = {nullptr, nullptr};
-	uint32_t* d_passmask = nullptr; uint32_t* d_blocksum = nullptr; uint32_t* d_cand = nullptr; uint32_t* d_ncand = nullptr; uint32_t* d_slow = nullptr; uint32_t* d_thr = nullptr; uint32_t* d_thr_dst = nullptr;
+	uint32_t* d_passmask = nullptr; uint32_t* d_blocksum = nullptr; uint32_t* d_cand = nullptr; uint32_t* d_ncand = nullptr; uint32_t* d_slow = nullptr; uint4* d_thr = nullptr;
 	uint8_t* d_records = nullptr; unsigned long long* d_counters = nullptr;
 	uint8_t* h_records = nullptr;            // pinned staging (DBT_F_TRACE, or a pageable caller buffer)
 	// record emission: emit bitmap -> ordered list -> dense copy of the records that become kam / aln records
@@ -199,7 +199,7 @@ static void free_slot(Slot& s) {
 	if (s.st) cudaStreamSynchronize(s.st);
 	cudaFree(s.d_ascii); cudaFree(s.d_offsets);
 	for (int m = 0; m < 2; ++m) { cudaFree(s.d_packed[m]); cudaFree(s.d_meta[m]); }
-	cudaFree(s.d_passmask); cudaFree(s.d_blocksum); cudaFree(s.d_cand); cudaFree(s.d_ncand); cudaFree(s.d_slow); cudaFree(s.d_thr); cudaFree(s.d_thr_dst); cudaFree(s.d_records); cudaFree(s.d_counters);
+	cudaFree(s.d_passmask); cudaFree(s.d_blocksum); cudaFree(s.d_cand); cudaFree(s.d_ncand); cudaFree(s.d_slow); cudaFree(s.d_thr); cudaFree(s.d_records); cudaFree(s.d_counters);
 	cudaFree(s.d_records_out); cudaFree(s.d_emitmask); cudaFree(s.d_emitsum); cudaFree(s.d_emitlist); cudaFree(s.d_nemit);
 	if (s.h_records) cudaFreeHost(s.h_records);
 	if (s.h_counters) cudaFreeHost(s.h_counters);
@@ -245,7 +245,7 @@ static int ensure_slot(dbt_ctx* c, int si) {
 	TRY(dev_alloc(&s.d_cand, P, "cand"));
 	TRY(dev_alloc(&s.d_ncand, 4, "ncand"));
 	TRY(dev_alloc(&s.d_slow, P, "slow list"));
-	if (rp.thr_on) { TRY(dev_alloc(&s.d_thr, P, "thread list")); TRY(dev_alloc(&s.d_thr_dst, P, "thread dst")); }
+	if (rp.thr_on) { TRY(dev_alloc(&s.d_thr, P, "thread list")); }
 	TRY(dev_alloc(&s.d_counters, DBT_N_COUNTERS, "counters"));
 	const bool want_records = rp.thr_on ? (c->p.flags & (DBT_F_ALN | DBT_F_ALN_MIN | DBT_F_TRACE)) != 0 : (c->p.flags & (DBT_F_KAM | DBT_F_TRACE)) != 0;
 	if (want_records) {
@@ -513,7 +513,7 @@ extern "C" void dbt_host_free(void* p) { if (p) cudaFreeHost(p); }
 static SlotView slot_view(const dbt_ctx* c, const Slot& s) {
 	SlotView v;
 	v.packed[0] = s.d_packed[0]; v.packed[1] = s.d_packed[1]; v.meta[0] = s.d_meta[0]; v.meta[1] = s.d_meta[1];
-	v.passmask = s.d_passmask; v.blocksum = s.d_blocksum; v.cand = s.d_cand; v.ncand = s.d_ncand; v.slow = s.d_slow; v.thr = s.d_thr; v.thr_dst = s.d_thr_dst; v.records = s.d_records;
+	v.passmask = s.d_passmask; v.blocksum = s.d_blocksum; v.cand = s.d_cand; v.ncand = s.d_ncand; v.slow = s.d_slow; v.thr = s.d_thr; v.records = s.d_records;
 	v.counters = s.d_counters; v.npairs = s.npairs; v.first_pair_index = s.first_pair_index;
 	(void)c;
 	return v;

@@ -55,8 +55,8 @@ struct SlotView {
 	uint32_t* cand;             // candidate pair ids, ascending
 	uint32_t* ncand;            // [0] = number of candidates, [1] = error flags, [2] = length of slow[], [3] = length of thr[]
 	uint32_t* slow;             // candidate ordinals left to the generic kernel
-	uint32_t* thr;              // candidate ordinals handed to thread_kernel (ncand[3] entries)
-	uint32_t* thr_dst;          // per candidate ordinal: dst | kf bits << 28 | rm bits << 30
+	uint4*    thr;              // work items of thread_kernel (ncand[3] entries): x = candidate ordinal, y = pair index within the
+	                            // batch, z = dst | kf bits << 28 | rm bits << 30 -- one 16-byte load per pair instead of a chain of three
 	uint8_t*  records;
 	unsigned long long* counters;   // DBT_N_COUNTERS
 	uint64_t npairs, first_pair_index;

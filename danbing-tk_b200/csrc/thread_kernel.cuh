@@ -508,6 +508,7 @@ __device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, u
 #pragma unroll 1
 	for (int jc = j0; jc <= j1; jc += SG) {                                // SG groups per round (all of them when the stage holds MAXJ)
 	const int je = min(j1, jc + SG - 1);
+#ifndef THR_DIRECT_PROBE
 #pragma unroll 1
 	for (int j = jc; j <= je; ++j) {
 		const int i = j * 32 + lane;
@@ -522,6 +523,7 @@ __device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, u
 	}
 	cp_async_wait_all();
 	__syncwarp();
+#endif
 #pragma unroll 1
 	for (int j = jc; j <= je; ++j) {
 		const int i = j * 32 + lane;
@@ -536,9 +538,19 @@ __device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, u
 			const uint64_t canon = is_rc ? rc : f;
 			bool full = true, found = false;
 			uint64_t k0 = 0;
+#ifdef THR_DIRECT_PROBE
+			const uint4* bkt = gt.slots + home_bucket(gt, canon ^ lmix) * B;
+			uint4 slv[B];
+#pragma unroll
+			for (int q = 0; q < B; ++q) slv[q] = ldg128(bkt + q);
+#endif
 #pragma unroll
 			for (int q = 0; q < B; ++q) {
+#ifdef THR_DIRECT_PROBE
+				const uint4 sl = slv[q];
+#else
 				const uint4 sl = W.stage[j - jc][q][lane];
+#endif
 				const uint64_t kk = slot_key(sl);
 				if (q == 0) k0 = kk;
 				if (kk == SLOT_EMPTY) full = false;
@@ -852,7 +864,7 @@ __device__ __noinline__ void thread_mate(const Table gt, uint32_t locus, uint32_
 	__syncwarp();
 }
 
-constexpr uint32_t THR_DST_MASK = (1u << G_LOCUS_BITS) - 1;           // sv.thr_dst[c] = dst | kf bits << 28 | rm bits << 30
+constexpr uint32_t THR_DST_MASK = (1u << G_LOCUS_BITS) - 1;           // sv.thr[t].z = dst | kf bits << 28 | rm bits << 30
 
 template <int B, int MAXJ>
 __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(DevIndex ix, RunParams rp, SlotView sv) {
@@ -869,11 +881,11 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 	if (lane < 3) W.cnt[lane] = 0;                                     // walk, ec, refresh probes (measurement)
 	__syncwarp();
 
+	uint4 item = gwarp < nwork ? sv.thr[gwarp] : make_uint4(0, 0, 0, 0);
 #pragma unroll 1
 	for (uint32_t t = gwarp; t < nwork; t += nwarps) {
-		const uint32_t c = sv.thr[t];
-		const uint32_t p = sv.cand[c];
-		const uint32_t dw = sv.thr_dst[c];
+		const uint32_t c = item.x, p = item.y, dw = item.z;
+		if (t + nwarps < nwork) item = sv.thr[t + nwarps];              // next pair's work item: in flight while this pair is threaded
 		const uint32_t dst = dw & THR_DST_MASK;
 		const uint64_t slot = trace ? (uint64_t)p : (uint64_t)c;
 		const bool slot_ok = want_rec && (trace || slot < rp.max_records);
