@@ -60,13 +60,21 @@ __device__ __forceinline__ uint64_t stash_next(const Table& t, uint64_t b) {
 __device__ __forceinline__ uint64_t slot_key(const uint4& s) { return ((uint64_t)s.y << 32) | s.x; }
 
 // read-only 128-bit load through the non-coherent path (the table is immutable after load_index)
+#ifdef DBT_PROBE_LDCG
+__device__ __forceinline__ uint4 ldg128(const uint4* p) { return __ldcg(p); }   // L2 only: random probe sectors do not displace the L1 lines of the stack
+#else
 __device__ __forceinline__ uint4 ldg128(const uint4* p) { return __ldg(p); }
+#endif
 
 // bucket staging: 16-byte asynchronous copies HBM/L2 -> shared memory, so that probe loops can be ROLLED (small code,
 // the kernels are instruction-fetch sensitive) and still keep every probe of a read in flight at once
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
 	const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+#ifdef DBT_CPASYNC_CA
+	asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" :: "r"(d), "l"(gsrc) : "memory");   // allocates in L1: the correction code re-visits the read's own nodes
+#else
 	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(d), "l"(gsrc) : "memory");
+#endif
 }
 __device__ __forceinline__ void cp_async_wait_all() {
 	asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
