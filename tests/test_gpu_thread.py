@@ -186,3 +186,52 @@ def test_result_capacity_overflow_is_reported():
     with pytest.raises(abi.DbtError, match="result buffer holds 5 records"):
         ctx.run(bases, off, capacity=5)
     ctx.close()
+
+
+def test_mixed_packed_and_ascii_sub_batches_over_both_slots(lib=None):
+    """bench.py's hybrid input path: sub-batches alternate between host-packed (dbt_pack_reads + DBT_LAYOUT_PACKED) and ASCII
+    uploads on the two slots; records, counts and counters equal one ASCII submission (threading mode, reads with N / errors)."""
+    import ctypes as C
+    L = abi.load_library()
+    _, ix, seqs, _ = tc.thread_case(write_text=False, frac_bg=0.2, nloci=8, seed=21, npairs=1500, frac_n=0.2)
+    seqs[10] = seqs[10].lower()
+    p = tc.thread_params(aln=1, max_batch_pairs=4096)
+    bases, off = rpgg_io.seqs_to_batch(seqs)
+    npairs = len(seqs) // 2
+    ctx = abi.Context(p, abi.make_index_struct(ix))
+    r_all, c_all = ctx.run(bases, off)
+    r_all = r_all.copy()
+    t_all = [a.copy() for a in ctx.download()[:3]]
+    ctx.reset()
+    sb = 400
+    nsub = (npairs + sb - 1) // sb
+    res = [abi.BatchResult() for _ in range(2)]
+    bufs = [np.zeros(sb * ctx.stride, np.uint8) for _ in range(2)]
+    keep, got, pending = [], [], [None, None]
+    for j in range(nsub):
+        s = j & 1
+        if pending[s] is not None:
+            abi.check(L, L.dbt_wait(ctx.h, s), "wait")
+            got.append(bufs[s][: int(res[s].n_records) * ctx.stride].copy())
+        b0, b1 = j * sb, min(npairs, (j + 1) * sb)
+        o = off[2 * b0: 2 * b1 + 1]
+        if j % 2:
+            packed = np.zeros(L.dbt_packed_bytes(p.max_read_len, b1 - b0), np.uint8)
+            assert L.dbt_pack_reads(p.k, p.max_read_len, b1 - b0, abi.ptr(bases, abi.u8p), abi.ptr(o, abi.u64p), abi.ptr(packed, abi.u8p), 2) == 0
+            b = ctx.make_batch(packed, None, first_pair_index=b0, layout=abi.LAYOUT_PACKED, npairs=b1 - b0)
+            keep.append(packed)
+        else:
+            b = ctx.make_batch(bases, o, first_pair_index=b0)
+        keep.append(b)
+        res[s].capacity = sb
+        res[s].records = abi.ptr(bufs[s], abi.u8p)
+        abi.check(L, L.dbt_submit(ctx.h, C.byref(b), C.byref(res[s]), s), "submit")
+        pending[s] = j
+    order = sorted((j, s) for s, j in enumerate(pending) if j is not None)
+    for j, s in order:
+        abi.check(L, L.dbt_wait(ctx.h, s), "wait")
+        got.append(bufs[s][: int(res[s].n_records) * ctx.stride].copy())
+    assert np.concatenate(got).tobytes() == r_all.tobytes()
+    for a, b in zip(ctx.download()[:3], t_all):
+        assert np.array_equal(a, b)
+    ctx.close()
