@@ -556,7 +556,12 @@ __device__ THR_REFRESH_INLINE void thr_refresh(const Table gt, uint32_t locus, u
 				if (kk == SLOT_EMPTY) full = false;
 				else if ((kk & SLOT_KEYMASK) == canon && (sl.z & G_LOCUS_MASK) == locus) { const GNode n = g_decode(sl.z, sl.w, is_rc); bi = n.bits; trp = n.tr; found = true; }
 			}
+#ifdef THR_REFRESH_INLINE_STASH
 			if (!found && full && (k0 & SLOT_OVF)) { const GNode n = g_lookup<B>(gt, f, locus, K); bi = n.bits; trp = n.tr; }   // continues in the stash: rare
+#else
+			// continues in the stash: rare, and out of line -- inlined, the look-up made one iteration of this loop 5.3 KB of SASS, most of the 6 KB L0
+			if (!found && full && (k0 & SLOT_OVF)) { const GNode n = g_lookup_nl<B>(gt, f, locus, K); bi = n.bits; trp = n.tr; }
+#endif
 			++nprobe;
 		}
 		if (in) { W.trx[m][i] = trp; W.info[i] = bi; }
