@@ -244,7 +244,9 @@ def main():
     ap.add_argument("--bucket-slots", type=int, default=0)
     ap.add_argument("--table-load", type=float, default=0.0)
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--rrand", action="store_true", help="also measure the random-sector roofline R_rand")
+    ap.add_argument("--rrand", action=argparse.BooleanOptionalAction, default=True,
+                    help="also measure the random-sector roofline R_rand (32 B / 64 B gathers over an 8 GiB table, < 1 s) and report the "
+                         "probe rate of the dominant kernel as a fraction of it")
     a = ap.parse_args()
     a.steps, a.warmup = max(a.steps, 1), max(a.warmup, 0)
     global K, CORR
@@ -532,6 +534,15 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
             msr = C.c_float()
             abi.check(L, L.dbt_random_gather_bench(local, 8 << 30, sect, 1 << 28, 3, C.byref(msr)), "rrand")
             rr[f"{sect}B_Gsectors_per_s"] = (1 << 28) / (msr.value / 1e3) / 1e9
+        # the "HBM random-access roofline" of SURVEY.md 8(d): logical probes (one 32 B sector each) per second of the dominant
+        # kernel against the measured gather rate over a table far beyond L2.  At the default index size most probes hit L2, so
+        # this can exceed 1 -- it is the honest denominator for HBM-resident tables (--loci 20000 and up).
+        probes = {"thread_kernel": cnt["thr_walk"] + cnt["thr_ec"] + cnt["thr_cls"] if thr else 0,
+                  "candidate_fast_kernel": (cnt["nhash1"] - g_h1) + (0 if thr else (cnt["nThreadingReads"] - g_thr) * nk),
+                  "subfilter_kernel": p_sub}.get(dom)
+        if probes and dom_ms > 0:
+            rr["dominant_kernel_Gprobes_per_s"] = probes / (dom_ms / 1e3) / 1e9
+            rr["frac_of_r_rand_32B"] = rr["dominant_kernel_Gprobes_per_s"] / rr["32B_Gsectors_per_s"]
         roofline["r_rand"] = rr
 
     # ---- 2. end to end through the C ABI with host buffers (double-buffered sub-batches) ----

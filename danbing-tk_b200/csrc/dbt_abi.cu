@@ -16,6 +16,10 @@
 
 #include "launchers.h"
 #include "host_pack.h"
+
+#ifndef DBT_DEFAULT_L2_FETCH
+#define DBT_DEFAULT_L2_FETCH 0
+#endif
 #include "graph_table.cuh"
 
 using namespace dbt;
@@ -122,6 +126,15 @@ static NcclApi g_nccl;
 
 static int set_device(const dbt_ctx* c) { CU(cudaSetDevice(c->p.device)); return DBT_OK; }
 
+// L2 fetch granularity for this device.  The path is random 32-byte bucket probes; with the default granularity an L2 miss
+// pulls 128 bytes from HBM (ncu at 20 000 loci, profiles/r1/s41: 120 bytes of DRAM read per probe in all three kernels).
+// DBT_L2_FETCH_GRANULARITY = 32 | 64 | 128 overrides; 0 leaves the driver default.
+static void set_l2_fetch_granularity() {
+	size_t g = DBT_DEFAULT_L2_FETCH;
+	if (const char* e = getenv("DBT_L2_FETCH_GRANULARITY")) g = (size_t)atoi(e);
+	if (g == 32 || g == 64 || g == 128) { if (cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, g) != cudaSuccess) cudaGetLastError(); }
+}
+
 static uint32_t round_up(uint32_t v, uint32_t m) { return (v + m - 1) / m * m; }
 
 extern "C" int dbt_create(dbt_ctx** out, const dbt_params* p) {
@@ -145,6 +158,7 @@ extern "C" int dbt_create(dbt_ctx** out, const dbt_params* p) {
 	if (c->p.table_load <= 0.f || c->p.table_load > 0.9f) c->p.table_load = 0.4f;
 	c->B = c->p.bucket_slots ? (int)c->p.bucket_slots : 2;
 	cudaError_t e = cudaSetDevice(p->device);
+	if (e == cudaSuccess) set_l2_fetch_granularity();
 	cudaDeviceProp prop;
 	if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, p->device);
 	if (e != cudaSuccess) { delete c; return fail(DBT_E_CUDA, "cudaSetDevice/GetDeviceProperties: %s", cudaGetErrorString(e)); }
@@ -762,6 +776,7 @@ extern "C" int dbt_table_stats(const dbt_ctx* cc, uint64_t stats[8]) {
 extern "C" int dbt_random_gather_bench(int device, uint64_t table_bytes, uint32_t sector_bytes, uint64_t n_gathers, int iters, float* best_ms) {
 	if (!best_ms) return fail(DBT_E_BADARG, "null argument");
 	CU(cudaSetDevice(device));
+	set_l2_fetch_granularity();
 	cudaDeviceProp prop; CU(cudaGetDeviceProperties(&prop, device));
 	uint4* t; TRY(dev_alloc(&t, table_bytes / 16, "gather table"));
 	uint32_t* sink; TRY(dev_alloc(&sink, 1, "sink"));
