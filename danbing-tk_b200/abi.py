@@ -169,7 +169,7 @@ def load_library(path=LIB_PATH):
     L.dbt_wait.argtypes = [ctxp, C.c_int]
     L.dbt_download.argtypes = [ctxp, u64p, u64p, u32p, u64p]
     L.dbt_reset_counts.argtypes = [ctxp]
-    for f in (L.dbt_nk_tr, L.dbt_nloci, L.dbt_launch_count):
+    for f in (L.dbt_nk_tr, L.dbt_nloci, L.dbt_launch_count, L.dbt_graph_table_bytes):
         f.argtypes = [ctxp]
         f.restype = C.c_uint64
     for f in (L.dbt_record_stride, L.dbt_record_as_stride, L.dbt_record_aln_stride, L.dbt_record_es_cap):
@@ -198,7 +198,7 @@ ABI_SYMBOLS = ["dbt_abi_version", "dbt_device_count", "dbt_default_params", "dbt
                "dbt_strerror", "dbt_last_error", "dbt_load_index", "dbt_upload", "dbt_process", "dbt_fetch",
                "dbt_submit", "dbt_wait", "dbt_download", "dbt_reset_counts", "dbt_nk_tr", "dbt_nloci",
                "dbt_record_stride", "dbt_record_as_stride", "dbt_record_aln_stride", "dbt_record_es_cap", "dbt_nccl_unique_id", "dbt_comm_init", "dbt_allreduce",
-               "dbt_timer_start", "dbt_timer_stop", "dbt_kernel_times", "dbt_launch_count", "dbt_table_stats", "dbt_batch_stats",
+               "dbt_timer_start", "dbt_timer_stop", "dbt_kernel_times", "dbt_launch_count", "dbt_table_stats", "dbt_graph_table_bytes", "dbt_batch_stats",
                "dbt_random_gather_bench", "dbt_host_alloc", "dbt_host_free", "dbt_packed_bytes", "dbt_pack_reads"]
 
 

@@ -93,11 +93,34 @@ __device__ __forceinline__ void updatetop2(uint64_t cf, uint32_t ind, uint64_t c
 	}
 }
 
-// per-pair hits1/hits2 (cpp:432-434): small shared-memory table, falling back to a per-warp
-// epoch-tagged global array when a pair touches more than ~VOTE_SMEM_SLOTS loci
+// per-pair hits1/hits2 (cpp:432-434): small shared-memory table; a pair that touches more than ~VOTE_SMEM_SLOTS loci (k-mers
+// listed in hundreds of loci) spills into one array of a small POOL of epoch-tagged global arrays [nloci+1], taken under a
+// lock for the duration of this pair's vote.  The pool is shared by every warp of every in-flight kernel of the context
+// (both slots): holding a lock never waits on anything else, so there is no deadlock, and the arrays cost
+// VOTE_POOL x (nloci+1) x 8 B instead of one array per resident warp (1.5 GB at 80 000 loci).
 struct VoteHits {
 	uint32_t* lkey; uint32_t* lf; uint32_t* lr;    // shared memory, VOTE_SMEM_SLOTS entries, key = locus+1
-	uint64_t* scratch; uint32_t epoch; uint32_t used;
+	uint64_t* pool; uint32_t* lock; uint32_t* epochs; uint64_t nloci; uint32_t seed;
+	uint32_t used; int held; uint32_t epoch; volatile uint64_t* scratch;
+	__device__ __noinline__ void acquire() {
+		uint32_t i = seed % VOTE_POOL;
+		while (atomicCAS(lock + i, 0u, 1u) != 0u) i = (i + 1) % VOTE_POOL;
+		__threadfence();
+		held = (int)i;
+		scratch = pool + (uint64_t)i * (nloci + 1);
+		epoch = *(volatile uint32_t*)(epochs + i) + 1;
+		if (epoch >= 0xFFFFF0u) {                          // 24-bit tag about to wrap: clear the array
+			for (uint64_t q = 0; q < nloci + 1; ++q) scratch[q] = 0;
+			epoch = 1;
+		}
+	}
+	__device__ __forceinline__ void release() {
+		if (held < 0) return;
+		*(volatile uint32_t*)(epochs + held) = epoch;
+		__threadfence();
+		atomicExch(lock + held, 0u);
+		held = -1;
+	}
 	__device__ __forceinline__ void add(uint32_t locus, uint32_t df, uint32_t dr, uint32_t& f, uint32_t& r) {
 		uint32_t h = (locus * 2654435761u) >> 26;            // 6 bits
 		for (int probe = 0; probe < VOTE_SMEM_SLOTS; ++probe) {
@@ -105,10 +128,11 @@ struct VoteHits {
 			uint32_t kk = lkey[s];
 			if (kk == locus + 1) { f = (lf[s] += df); r = (lr[s] += dr); return; }
 			if (kk == 0) {
-				if (used >= VOTE_SMEM_SLOTS - 8) break;          // keep the table sparse; spill to global
+				if (used >= VOTE_SPILL_AT) break;                // keep the table sparse; spill to global
 				lkey[s] = locus + 1; lf[s] = df; lr[s] = dr; ++used; f = df; r = dr; return;
 			}
 		}
+		if (held < 0) acquire();
 		uint64_t e = scratch[locus];
 		uint32_t ef = 0, er = 0;
 		if ((uint32_t)(e >> 40) == epoch) { ef = (uint32_t)(e >> 20) & 0xFFFFF; er = (uint32_t)e & 0xFFFFF; }
@@ -265,9 +289,9 @@ __device__ __noinline__ void perm_introsort(uint16_t* perm, const uint32_t* unml
 // find_matching_locus, literal (cpp:364-422); one lane.  Returns top.idx / top.fc / top.rc.
 __device__ __noinline__ uint3 vote_serial(const uint32_t* __restrict__ vv, const uint16_t* perm, const uint32_t* uval, const uint16_t* utf,
                                           const uint16_t* utr, uint32_t* lkey, uint32_t U, uint32_t total, uint32_t cth32,
-                                          uint64_t* scratch, uint32_t epoch) {
+                                          const DevIndex& ix, uint32_t seed) {
 	Asgn top = {NAN32, 0, 0}, second = {NAN32, 0, 0};
-	VoteHits vh{lkey, lkey + VOTE_SMEM_SLOTS, lkey + 2 * VOTE_SMEM_SLOTS, scratch, epoch, 0};
+	VoteHits vh{lkey, lkey + VOTE_SMEM_SLOTS, lkey + 2 * VOTE_SMEM_SLOTS, ix.vote_pool, ix.vote_lock, ix.vote_epoch, ix.nloci, seed, 0, -1, 0, nullptr};
 	uint64_t rem = total;
 	const uint64_t cth = cth32;
 	for (uint32_t i = 0; i < U; ++i) {
@@ -301,6 +325,7 @@ __device__ __noinline__ uint3 vote_serial(const uint32_t* __restrict__ vv, const
 			break;
 		}
 	}
+	vh.release();
 	return make_uint3(top.idx, (uint32_t)top.fc, (uint32_t)top.rc);
 }
 
@@ -340,8 +365,6 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 	uint16_t* perm  = umid + UMAX;                                      // visiting order (cpp:320-327)
 
 	uint32_t c_kf = 0, c_laf = 0, c_qc = 0, c_thr = 0, c_asgn = 0, c_h1 = 0, c_inc = 0, c_pairs = 0, c_thr0 = 0;   // lane-0 accumulators
-	uint32_t epoch = 0; uint64_t* scratch = nullptr;
-	epoch = ix.vote_epoch[gwarp]; scratch = ix.vote_scratch + (uint64_t)gwarp * (ix.nloci + 1);
 	const uint32_t nwork = all ? sv.ncand[0] : sv.ncand[2];
 	const uint32_t stride = nwarps;
 
@@ -589,13 +612,7 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 				dst0 = val0 >> 1;
 			} else {
 				uint3 t3 = make_uint3(NAN32, 0, 0);
-				if (lane == 0) t3 = vote_serial(ix.vv, perm, uval, utf, utr, lkey, U, total, rp.cth, scratch, epoch + 1);
-				// the global fallback may have been written under epoch+1: retire that epoch
-				epoch += 1;
-				if (epoch >= 0xFFFFF0u) {                       // 24-bit tag about to wrap: clear this warp's scratch
-					for (uint64_t i = lane; i < ix.nloci + 1; i += 32) scratch[i] = 0;
-					epoch = 0;
-				}
+				if (lane == 0) t3 = vote_serial(ix.vv, perm, uval, utf, utr, lkey, U, total, rp.cth, ix, gwarp);
 				dst0 = __shfl_sync(0xffffffffu, t3.x, 0);
 				fc = __shfl_sync(0xffffffffu, t3.y, 0);
 				rc = __shfl_sync(0xffffffffu, t3.z, 0);
@@ -715,7 +732,6 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 			}
 		}
 	}
-	ix.vote_epoch[gwarp] = epoch;
 	if (lane == 0) {
 		counter_add(sv.counters, DBT_C_NKMERFILTERED, c_kf);
 		counter_add(sv.counters, DBT_C_NLOCUSASSIGNFILTERED, c_laf);

@@ -87,7 +87,7 @@ struct Slot {
 	bool uploaded = false, processed = false, fetch_pending = false;
 	dbt_batch_result* result = nullptr;
 	cudaEvent_t ev[KT_N + 1] = {};
-	cudaEvent_t t0 = nullptr, t1 = nullptr;
+	cudaEvent_t t0 = nullptr, t1 = nullptr, evp0 = nullptr, evp1 = nullptr;   // evp0/evp1 bracket pack_kernel (dbt_upload, ASCII layout)
 	bool ev_pack = false, ev_proc = false;
 };
 
@@ -98,6 +98,8 @@ struct NcclApi {
 	int (*CommInitRank)(void**, int, Id128, int) = nullptr;
 	int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
 	int (*CommDestroy)(void*) = nullptr;
+	int (*GroupStart)() = nullptr;
+	int (*GroupEnd)() = nullptr;
 	const char* (*GetErrorString)(int) = nullptr;
 };
 
@@ -112,9 +114,16 @@ struct dbt_ctx {
 	// owned device memory of the index
 	uint4* d_gslots = nullptr; uint64_t gtable_bytes = 0, gnodes = 0;   // graph table (restored threading)
 	uint4* d_slots = nullptr; uint32_t* d_vv = nullptr; uint32_t* d_vv_aux = nullptr;
+	// results: ONE allocation [counts nk_tr | kmc nloci | totals DBT_N_COUNTERS] u64 + [nmapread nloci] u32, so that the
+	// end-of-run exchange is one grouped collective (a u64 part and a u32 part); d_red = the same layout, filled by dbt_allreduce
+	uint64_t* d_results = nullptr; uint64_t* d_red = nullptr; uint64_t n_res64 = 0;
 	uint64_t* d_counts = nullptr; uint64_t* d_kmc = nullptr; uint32_t* d_nmapread = nullptr; uint8_t* d_qc = nullptr;
-	uint16_t* d_permtab = nullptr; uint64_t* d_vote_scratch = nullptr; uint32_t* d_vote_epoch = nullptr;
+	uint16_t* d_permtab = nullptr; uint64_t* d_vote_pool = nullptr; uint32_t* d_vote_lock = nullptr;
 	uint64_t* d_totals = nullptr;
+	uint64_t* h_totals = nullptr;            // pinned: local totals in, reduced totals out
+	bool reduced_valid = false;              // d_red holds the all-rank sums of the current local state
+	uint64_t totals_red[DBT_N_COUNTERS] = {};
+	cudaStream_t red_st = nullptr; cudaEvent_t red_ev = nullptr;
 	uint64_t table_bytes = 0, nkeys = 0;
 	Slot slot[DBT_N_SLOTS];
 	uint64_t totals[DBT_N_COUNTERS] = {};
@@ -220,6 +229,8 @@ static void free_slot(Slot& s) {
 	for (auto& e : s.ev) if (e) cudaEventDestroy(e);
 	if (s.t0) cudaEventDestroy(s.t0);
 	if (s.t1) cudaEventDestroy(s.t1);
+	if (s.evp0) cudaEventDestroy(s.evp0);
+	if (s.evp1) cudaEventDestroy(s.evp1);
 	if (s.st) cudaStreamDestroy(s.st);
 	s = Slot();
 }
@@ -230,8 +241,11 @@ extern "C" void dbt_destroy(dbt_ctx* c) {
 	for (auto& s : c->slot) free_slot(s);
 	if (c->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
 	cudaFree(c->d_gslots);
-	cudaFree(c->d_slots); cudaFree(c->d_vv); cudaFree(c->d_vv_aux); cudaFree(c->d_counts); cudaFree(c->d_kmc); cudaFree(c->d_nmapread);
-	cudaFree(c->d_qc); cudaFree(c->d_permtab); cudaFree(c->d_vote_scratch); cudaFree(c->d_vote_epoch); cudaFree(c->d_totals);
+	cudaFree(c->d_slots); cudaFree(c->d_vv); cudaFree(c->d_vv_aux); cudaFree(c->d_results); cudaFree(c->d_red);
+	cudaFree(c->d_qc); cudaFree(c->d_permtab); cudaFree(c->d_vote_pool); cudaFree(c->d_vote_lock);
+	if (c->h_totals) cudaFreeHost(c->h_totals);
+	if (c->red_ev) cudaEventDestroy(c->red_ev);
+	if (c->red_st) cudaStreamDestroy(c->red_st);
 	delete c;
 }
 
@@ -277,7 +291,7 @@ static int ensure_slot(dbt_ctx* c, int si) {
 	}
 	CU(cudaHostAlloc((void**)&s.h_counters, (DBT_N_COUNTERS + 4) * sizeof(uint64_t), cudaHostAllocDefault));
 	for (auto& e : s.ev) CU(cudaEventCreate(&e));
-	CU(cudaEventCreate(&s.t0)); CU(cudaEventCreate(&s.t1));
+	CU(cudaEventCreate(&s.t0)); CU(cudaEventCreate(&s.t1)); CU(cudaEventCreate(&s.evp0)); CU(cudaEventCreate(&s.evp1));
 	s.ready = true;
 	return DBT_OK;
 }
@@ -416,11 +430,11 @@ extern "C" int dbt_load_index(dbt_ctx* c, const dbt_index* in) {
 	if (herr & ERR_INDEX_DUPTR) return fail(DBT_E_INDEX, "duplicate TR k-mer within a locus");
 
 	// results
-	TRY(dev_alloc(&c->d_counts, ntr, "counts")); TRY(dev_alloc(&c->d_kmc, nloci, "kmc")); TRY(dev_alloc(&c->d_nmapread, nloci, "nmapread"));
-	TRY(dev_alloc(&c->d_totals, DBT_N_COUNTERS, "totals"));
-	CU(cudaMemsetAsync(c->d_counts, 0, std::max<uint64_t>(ntr, 1) * 8, st));
-	CU(cudaMemsetAsync(c->d_kmc, 0, nloci * 8, st));
-	CU(cudaMemsetAsync(c->d_nmapread, 0, nloci * 4, st));
+	c->n_res64 = ntr + nloci + DBT_N_COUNTERS;
+	TRY(dev_alloc(&c->d_results, c->n_res64 + (nloci + 1) / 2, "results"));
+	c->d_counts = c->d_results; c->d_kmc = c->d_counts + ntr; c->d_totals = c->d_kmc + nloci;
+	c->d_nmapread = reinterpret_cast<uint32_t*>(c->d_totals + DBT_N_COUNTERS);
+	CU(cudaMemsetAsync(c->d_results, 0, (c->n_res64 + (nloci + 1) / 2) * 8, st));
 	if (in->qc) { TRY(dev_alloc(&c->d_qc, nloci, "qc")); CU(cudaMemcpyAsync(c->d_qc, in->qc, nloci, cudaMemcpyHostToDevice, st)); }
 	// all-ties visiting orders: what std::sort does with a comparator that never says "less"
 	// (getSortedIndex on nmappedloci == 1 everywhere, cpp:247-250, 320-321).  Computed with the host's
@@ -441,18 +455,17 @@ extern "C" int dbt_load_index(dbt_ctx* c, const dbt_index* in) {
 		CU(cudaStreamSynchronize(st));
 		c->ix.permtab_maxU = maxU;
 	}
-	// vote fallback scratch: one epoch-tagged hits array per resident warp
-	const uint64_t nwarps = (uint64_t)c->cand_grid * CAND_WARPS_SLOW;
-	TRY(dev_alloc(&c->d_vote_scratch, nwarps * (nloci + 1), "vote scratch"));
-	TRY(dev_alloc(&c->d_vote_epoch, nwarps, "vote epoch"));
-	CU(cudaMemsetAsync(c->d_vote_scratch, 0, nwarps * (nloci + 1) * 8, st));
-	CU(cudaMemsetAsync(c->d_vote_epoch, 0, nwarps * 4, st));
+	// vote spill pool: VOTE_POOL epoch-tagged hits arrays + their locks and epochs (candidate.cuh, VoteHits)
+	TRY(dev_alloc(&c->d_vote_pool, (uint64_t)VOTE_POOL * (nloci + 1), "vote pool"));
+	TRY(dev_alloc(&c->d_vote_lock, 2 * VOTE_POOL, "vote locks"));
+	CU(cudaMemsetAsync(c->d_vote_pool, 0, (uint64_t)VOTE_POOL * (nloci + 1) * 8, st));
+	CU(cudaMemsetAsync(c->d_vote_lock, 0, 2 * VOTE_POOL * 4, st));
 	CU(cudaStreamSynchronize(st));
 	CU(cudaStreamDestroy(st));
 
 	c->ix.table = t; c->ix.vv = c->d_vv; c->ix.vv_aux = c->d_vv_aux; c->ix.nvv = in->nvv;
 	c->ix.counts = c->d_counts; c->ix.kmc = c->d_kmc; c->ix.nmapread = c->d_nmapread; c->ix.qc = c->d_qc;
-	c->ix.permtab = c->d_permtab; c->ix.vote_scratch = c->d_vote_scratch; c->ix.vote_epoch = c->d_vote_epoch;
+	c->ix.permtab = c->d_permtab; c->ix.vote_pool = c->d_vote_pool; c->ix.vote_lock = c->d_vote_lock; c->ix.vote_epoch = c->d_vote_lock + VOTE_POOL;
 	c->ix.nloci = nloci; c->ix.nk_tr = ntr;
 	c->ix.gtable = Table{nullptr, 0, 0};
 	if ((c->p.flags & DBT_F_THREADING) && in->g_n && in->g_kmers && in->g_masks) TRY(load_graph(c, in, ntr));
@@ -466,6 +479,7 @@ extern "C" uint32_t dbt_record_stride(const dbt_ctx* c) { return c ? c->rp.rec_s
 extern "C" uint32_t dbt_record_as_stride(const dbt_ctx* c) { return c ? c->rp.as_stride : 0; }
 extern "C" uint32_t dbt_record_aln_stride(const dbt_ctx* c) { return c ? c->rp.aln_stride : 0; }
 extern "C" uint32_t dbt_record_es_cap(const dbt_ctx* c) { return c ? c->rp.es_cap : 0; }
+extern "C" uint64_t dbt_graph_table_bytes(const dbt_ctx* c) { return c ? c->gtable_bytes : 0; }
 extern "C" uint64_t dbt_launch_count(const dbt_ctx* c) { return c ? c->launches.load() : 0; }
 
 // ------------------------------------------------------------------------------------------
@@ -559,7 +573,9 @@ extern "C" int dbt_upload(dbt_ctx* c, const dbt_batch* b, int slot) {
 			CU(cudaMemcpyAsync(s.d_ascii, b->bases + b->offsets[0], nbytes, cudaMemcpyHostToDevice, s.st));
 			CU(cudaMemcpyAsync(s.d_offsets, b->offsets, (2 * b->npairs + 1) * 8, cudaMemcpyHostToDevice, s.st));
 			// offsets are used relative to bases: shift by offsets[0] inside the kernel via pointer arithmetic
+			CU(cudaEventRecord(s.evp0, s.st));
 			CU(launch_pack(s.st, s.d_ascii - b->offsets[0], s.d_offsets, b->npairs, rp, s.d_packed[0], s.d_packed[1], s.d_meta[0], s.d_meta[1], s.d_ncand + 1)); ++c->launches;
+			CU(cudaEventRecord(s.evp1, s.st));
 			s.ev_pack = true;
 		} else if (b->layout == DBT_LAYOUT_PACKED) {
 			const uint64_t* p0 = reinterpret_cast<const uint64_t*>(b->bases);
@@ -580,6 +596,7 @@ extern "C" int dbt_process(dbt_ctx* c, int slot) {
 	TRY(check_slot(c, slot));
 	Slot& s = c->slot[slot];
 	if (!s.uploaded) return fail(DBT_E_STATE, "slot %d has no uploaded batch", slot);
+	c->reduced_valid = false;                  // the local arrays move on; dbt_download hands them out again until the next reduce
 	SlotView sv = slot_view(c, s);
 	CU(cudaMemsetAsync(s.d_counters, 0, DBT_N_COUNTERS * 8, s.st));
 	CU(cudaMemsetAsync(s.d_ncand, 0, 4, s.st));
@@ -700,10 +717,13 @@ extern "C" int dbt_download(dbt_ctx* c, uint64_t* trkmc, uint64_t* kmc, uint32_t
 	if (!c) return fail(DBT_E_BADARG, "null context");
 	if (!c->index_loaded) return fail(DBT_E_STATE, "no index");
 	TRY(set_device(c)); TRY(sync_all(c));
-	if (trkmc && c->ix.nk_tr) CU(cudaMemcpy(trkmc, c->d_counts, c->ix.nk_tr * 8, cudaMemcpyDeviceToHost));
-	if (kmc) CU(cudaMemcpy(kmc, c->d_kmc, c->ix.nloci * 8, cudaMemcpyDeviceToHost));
-	if (nmapread) CU(cudaMemcpy(nmapread, c->d_nmapread, c->ix.nloci * 4, cudaMemcpyDeviceToHost));
-	if (counters) for (int i = 0; i < DBT_N_COUNTERS; ++i) counters[i] = c->totals[i];
+	// after dbt_allreduce (and until the next dbt_process / dbt_reset_counts): the all-rank sums
+	const bool red = c->reduced_valid;
+	const uint64_t* base = red ? c->d_red : c->d_results;
+	if (trkmc && c->ix.nk_tr) CU(cudaMemcpy(trkmc, base, c->ix.nk_tr * 8, cudaMemcpyDeviceToHost));
+	if (kmc) CU(cudaMemcpy(kmc, base + c->ix.nk_tr, c->ix.nloci * 8, cudaMemcpyDeviceToHost));
+	if (nmapread) CU(cudaMemcpy(nmapread, base + c->n_res64, c->ix.nloci * 4, cudaMemcpyDeviceToHost));
+	if (counters) for (int i = 0; i < DBT_N_COUNTERS; ++i) counters[i] = red ? c->totals_red[i] : c->totals[i];
 	return DBT_OK;
 }
 
@@ -711,10 +731,9 @@ extern "C" int dbt_reset_counts(dbt_ctx* c) {
 	if (!c) return fail(DBT_E_BADARG, "null context");
 	if (!c->index_loaded) return fail(DBT_E_STATE, "no index");
 	TRY(set_device(c)); TRY(sync_all(c));
-	CU(cudaMemset(c->d_counts, 0, std::max<uint64_t>(c->ix.nk_tr, 1) * 8));
-	CU(cudaMemset(c->d_kmc, 0, c->ix.nloci * 8));
-	CU(cudaMemset(c->d_nmapread, 0, c->ix.nloci * 4));
+	CU(cudaMemset(c->d_results, 0, (c->n_res64 + (c->ix.nloci + 1) / 2) * 8));
 	memset(c->totals, 0, sizeof(c->totals));
+	c->reduced_valid = false;
 	return DBT_OK;
 }
 
@@ -739,6 +758,7 @@ extern "C" int dbt_kernel_times(dbt_ctx* c, int slot, float ms[8], uint32_t laun
 	Slot& s = c->slot[slot];
 	CU(cudaStreamSynchronize(s.st));
 	for (int i = 0; i < 8; ++i) { ms[i] = 0; launches[i] = 0; }
+	if (s.ev_pack) { CU(cudaEventElapsedTime(&ms[KT_PACK], s.evp0, s.evp1)); launches[KT_PACK] = 1; }   // the slot's last ASCII upload
 	if (s.ev_proc) {
 		CU(cudaEventElapsedTime(&ms[KT_SUBFILTER], s.ev[1], s.ev[2])); launches[KT_SUBFILTER] = 1;
 		CU(cudaEventElapsedTime(&ms[KT_COMPACT], s.ev[2], s.ev[3])); launches[KT_COMPACT] = 3;
@@ -809,6 +829,8 @@ static int nccl_load() {
 	g_nccl.AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(g_nccl.lib, "ncclAllReduce");
 	g_nccl.CommDestroy = (int (*)(void*))dlsym(g_nccl.lib, "ncclCommDestroy");
 	g_nccl.GetErrorString = (const char* (*)(int))dlsym(g_nccl.lib, "ncclGetErrorString");
+	g_nccl.GroupStart = (int (*)())dlsym(g_nccl.lib, "ncclGroupStart");
+	g_nccl.GroupEnd = (int (*)())dlsym(g_nccl.lib, "ncclGroupEnd");
 	if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce || !g_nccl.CommDestroy) return fail(DBT_E_NCCL, "libnccl lacks a required symbol");
 	return DBT_OK;
 }
@@ -832,21 +854,38 @@ extern "C" int dbt_comm_init(dbt_ctx* c, int nranks, int rank, const uint8_t id[
 }
 
 // One exchange step at the end of a run: integer sums are order-independent, so
-// N-GPU outputs are bit-identical to the single-GPU ones.
+// N-GPU outputs are bit-identical to the single-GPU ones.  OUT OF PLACE: the rank's own arrays stay as they are and
+// the sums land in a second block of the same layout, which dbt_download hands out until the next dbt_process /
+// dbt_reset_counts -- so a second call (or more batches followed by another call) reduces the local state afresh
+// instead of multiplying already-reduced counts by the number of ranks.  One grouped collective (u64 part + u32 part)
+// on the context's own stream; no blocking copies.
 extern "C" int dbt_allreduce(dbt_ctx* c) {
 	if (!c) return fail(DBT_E_BADARG, "null context");
 	if (!c->index_loaded) return fail(DBT_E_STATE, "no index");
-	TRY(set_device(c)); TRY(sync_all(c));
-	if (c->nranks == 1) return DBT_OK;
+	TRY(set_device(c));
+	if (c->nranks == 1) { TRY(sync_all(c)); return DBT_OK; }
 	if (!c->nccl_comm) return fail(DBT_E_STATE, "dbt_comm_init has not been called");
-	enum { ncclUint32 = 3, ncclUint64 = 5, ncclSum = 0 };
-	cudaStream_t st = 0;
-	CU(cudaMemcpy(c->d_totals, c->totals, sizeof(c->totals), cudaMemcpyHostToDevice));
-	if (c->ix.nk_tr) NC(g_nccl.AllReduce(c->d_counts, c->d_counts, c->ix.nk_tr, ncclUint64, ncclSum, c->nccl_comm, st));
-	NC(g_nccl.AllReduce(c->d_kmc, c->d_kmc, c->ix.nloci, ncclUint64, ncclSum, c->nccl_comm, st));
-	NC(g_nccl.AllReduce(c->d_nmapread, c->d_nmapread, c->ix.nloci, ncclUint32, ncclSum, c->nccl_comm, st));
-	NC(g_nccl.AllReduce(c->d_totals, c->d_totals, DBT_N_COUNTERS, ncclUint64, ncclSum, c->nccl_comm, st));
-	CU(cudaStreamSynchronize(st));
-	CU(cudaMemcpy(c->totals, c->d_totals, sizeof(c->totals), cudaMemcpyDeviceToHost));
+	enum { ncclUint32 = 3, ncclUint64 = 5, ncclSum = 0 };       // nccl.h: ncclDataType_t / ncclRedOp_t
+	const uint64_t nloci = c->ix.nloci;
+	if (!c->red_st) {
+		CU(cudaStreamCreateWithFlags(&c->red_st, cudaStreamNonBlocking));
+		CU(cudaEventCreateWithFlags(&c->red_ev, cudaEventDisableTiming));
+		TRY(dev_alloc(&c->d_red, c->n_res64 + (nloci + 1) / 2, "reduced results"));
+		CU(cudaHostAlloc((void**)&c->h_totals, 2 * sizeof(c->totals), cudaHostAllocDefault));
+	}
+	for (auto& s : c->slot) if (s.ready) { CU(cudaEventRecord(c->red_ev, s.st)); CU(cudaStreamWaitEvent(c->red_st, c->red_ev, 0)); }
+	// the host-side totals ride in the same u64 block (they are complete: dbt_wait adds a batch's counters before it returns)
+	for (auto& s : c->slot) if (s.fetch_pending) return fail(DBT_E_STATE, "dbt_allreduce with an unfinished fetch; call dbt_wait first");
+	memcpy(c->h_totals, c->totals, sizeof(c->totals));
+	CU(cudaMemcpyAsync(c->d_totals, c->h_totals, sizeof(c->totals), cudaMemcpyHostToDevice, c->red_st));
+	uint32_t* red32 = reinterpret_cast<uint32_t*>(c->d_red + c->n_res64);
+	if (g_nccl.GroupStart) NC(g_nccl.GroupStart());
+	NC(g_nccl.AllReduce(c->d_results, c->d_red, c->n_res64, ncclUint64, ncclSum, c->nccl_comm, c->red_st));
+	NC(g_nccl.AllReduce(c->d_nmapread, red32, nloci, ncclUint32, ncclSum, c->nccl_comm, c->red_st));
+	if (g_nccl.GroupEnd) NC(g_nccl.GroupEnd());
+	CU(cudaMemcpyAsync(c->h_totals + DBT_N_COUNTERS, c->d_red + (c->n_res64 - DBT_N_COUNTERS), sizeof(c->totals), cudaMemcpyDeviceToHost, c->red_st));
+	CU(cudaStreamSynchronize(c->red_st));
+	memcpy(c->totals_red, c->h_totals + DBT_N_COUNTERS, sizeof(c->totals));
+	c->reduced_valid = true;
 	return DBT_OK;
 }

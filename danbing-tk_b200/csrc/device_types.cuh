@@ -9,6 +9,11 @@ namespace dbt {
 
 constexpr uint32_t NAN32 = 0xFFFFFFFFu;
 constexpr int VOTE_SMEM_SLOTS = 64;          // per-pair shared-memory (locus -> hits1,hits2) entries
+#ifndef DBT_VOTE_SPILL_AT
+#define DBT_VOTE_SPILL_AT (VOTE_SMEM_SLOTS - 8)
+#endif
+constexpr uint32_t VOTE_SPILL_AT = DBT_VOTE_SPILL_AT;   // loci held in shared memory before a pair spills to the global pool (test builds lower it)
+constexpr uint32_t VOTE_POOL = 64;           // global spill arrays [nloci+1], shared under locks by all in-flight kernels of a context
 constexpr int CAND_WARPS_SLOW = 4;             // generic candidate_kernel: warps per block
 
 // resident RPGG index
@@ -23,8 +28,9 @@ struct DevIndex {
 	const uint8_t* qc;          // qcFilter (cpp:2471) or nullptr
 	const uint16_t* permtab;    // all-ties std::sort permutations, perm_U at offset U*(U-1)/2
 	uint32_t permtab_maxU;
-	uint64_t* vote_scratch;     // per-warp epoch-tagged hits arrays [(nloci+1)] (fallback of the smem table)
-	uint32_t* vote_epoch;       // per-warp epoch
+	uint64_t* vote_pool;        // VOTE_POOL epoch-tagged hits arrays [(nloci+1)] (spill target of the smem vote table)
+	uint32_t* vote_lock;        // [VOTE_POOL] 0 free / 1 held
+	uint32_t* vote_epoch;       // [VOTE_POOL] last epoch used in each array
 	uint64_t nloci, nk_tr;
 	Table    gtable;            // graphDB of all loci (graph_table.cuh); slots == nullptr when no graph is loaded
 };

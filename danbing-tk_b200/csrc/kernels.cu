@@ -9,7 +9,9 @@
 //                      with integer atomics (cpp:2145-2158) and the kam record (cpp:2169-2175)
 //   index build        A14     bulk insert + per-locus class fill
 // "cpp" = src/aQueryFasta_thread.cpp, "h" = src/aQueryFasta_thread.h of the reference.
+#include <algorithm>
 #include "device_types.cuh"
+#include "pack_read.cuh"
 
 namespace dbt {
 
@@ -37,26 +39,23 @@ __device__ void write_plain_record(uint8_t* rec, uint32_t stride, uint64_t pair_
 }
 
 // ============================================================================================
-// pack_kernel: one thread per read.  A1 (device half): 2 bits/base + invalid mask + "no valid window"
+// pack_kernel (A1, device half; north_star item 1): ASCII reads -> 2 bits/base + invalid mask + "no valid window".
+// One warp per TILE of 32 consecutive reads (16 pairs).  The tile's bytes -- one contiguous range of the ASCII stream --
+// are staged into shared memory with coalesced 128-bit asynchronous copies (cp.async, 16 B per lane); each lane then
+// packs one read out of shared memory four bases at a time with 32-bit SWAR arithmetic (alphabet test = exactly the
+// upper-case "ACGT" of h:52,297; code = ((c >> 1) ^ (c >> 2)) & 3 = encodeSeq's A0 C1 G2 T3, h:126-132) into a second
+// shared-memory tile, which the warp writes out with coalesced 128-bit stores: the 16 records of mate 0 and the 16 of
+// mate 1 are each one contiguous kilobyte of the SoA output.  HBM traffic = the algorithmic 150 B in + 64 B out per read.
 // ============================================================================================
-__global__ void pack_kernel(const uint8_t* __restrict__ ascii, const uint64_t* __restrict__ offsets, uint64_t nreads,
-                            uint32_t k, ReadLayout lay, uint32_t max_read_len, uint64_t npairs,
-                            uint64_t* __restrict__ packed0, uint64_t* __restrict__ packed1,
-                            uint16_t* __restrict__ meta0, uint16_t* __restrict__ meta1, uint32_t* __restrict__ err) {
-	uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (r >= nreads) return;
-	uint64_t pair = r >> 1; uint32_t mate = (uint32_t)(r & 1);
-	uint64_t off = offsets[r]; uint64_t len64 = offsets[r + 1] - off;
-	uint32_t len = (uint32_t)len64;
-	if (len64 > max_read_len) { atomicOr(err, ERR_READ_TOO_LONG); len = max_read_len; }
-	const uint8_t* s = ascii + off;
-	uint64_t* out = (mate ? packed1 : packed0) + pair * lay.W64;
+constexpr int PACK_WARPS = 4;
+
+// byte-wise fallback for a tile that holds a read longer than max_read_len (the batch is rejected: ERR_READ_TOO_LONG)
+__device__ __noinline__ void pack_read_slow(const uint8_t* __restrict__ s, uint32_t len, uint32_t k, ReadLayout lay, uint64_t* __restrict__ out, uint16_t* meta) {
 	uint32_t run = 0; bool any = false;
-	for (uint32_t w = 0; w < lay.WB; w += 2) {                 // two base words + one mask word per round
+	for (uint32_t w = 0; w < lay.WB; w += 2) {
 		uint64_t b0 = 0, b1 = 0, m = 0;
-#pragma unroll 4
 		for (uint32_t j = 0; j < 64; ++j) {
-			uint32_t i = w * 32 + j;
+			const uint32_t i = w * 32 + j;
 			uint32_t c = 4;
 			if (i < len) c = base_code(__ldg(s + i));
 			if (c < 4) { if (j < 32) b0 |= (uint64_t)c << (2 * j); else b1 |= (uint64_t)c << (2 * (j - 32)); ++run; if (run >= k) any = true; }
@@ -67,7 +66,63 @@ __global__ void pack_kernel(const uint8_t* __restrict__ ascii, const uint64_t* _
 		out[lay.WB + (w >> 1)] = m;
 	}
 	for (uint32_t w = lay.WB + lay.WM; w < lay.W64; ++w) out[w] = 0;
-	(mate ? meta1 : meta0)[pair] = (uint16_t)(len | (any ? 0 : META_NOVALID));
+	*meta = (uint16_t)(len | (any ? 0 : META_NOVALID));
+}
+
+// in_cap: bytes of one warp's input tile (multiple of 16, >= 32 * max_read_len + 15 alignment + 8 over-read)
+__global__ void __launch_bounds__(PACK_WARPS * 32) pack_kernel(const uint8_t* __restrict__ ascii, const uint64_t* __restrict__ offsets, uint64_t nreads,
+                                                             uint32_t k, ReadLayout lay, uint32_t max_read_len, uint32_t in_cap,
+                                                             uint64_t* __restrict__ packed0, uint64_t* __restrict__ packed1,
+                                                             uint16_t* __restrict__ meta0, uint16_t* __restrict__ meta1, uint32_t* __restrict__ err) {
+	extern __shared__ __align__(16) uint8_t pack_smem[];
+	const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+	const uint32_t W64 = lay.W64;
+	uint8_t* tin = pack_smem + (size_t)wib * (in_cap + 32 * W64 * 8);
+	uint64_t* tout = reinterpret_cast<uint64_t*>(tin + in_cap);                       // [mate][16 pairs][W64]
+	const uint64_t ntiles = (nreads + 31) / 32;
+#pragma unroll 1
+	for (uint64_t tile = (uint64_t)blockIdx.x * PACK_WARPS + wib; tile < ntiles; tile += (uint64_t)gridDim.x * PACK_WARPS) {
+		const uint64_t r = tile * 32 + lane;
+		const bool active = r < nreads;
+		const uint64_t off = active ? offsets[r] : 0, end = active ? offsets[r + 1] : 0;
+		const uint32_t nact = (uint32_t)min((uint64_t)32, nreads - tile * 32);
+		const uint64_t off0 = __shfl_sync(0xffffffffu, off, 0), endN = __shfl_sync(0xffffffffu, end, (int)nact - 1);
+		const uint64_t len64 = end - off;
+		const uint8_t* a0 = reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(ascii + off0) & ~(uintptr_t)15);
+		const uint64_t nbytes = ((uint64_t)((ascii + endN) - a0) + 15) & ~15ull;
+		const uint64_t pair = r >> 1; const uint32_t mate = (uint32_t)(r & 1);
+		if (__any_sync(0xffffffffu, active && len64 > max_read_len) || nbytes + 8 > in_cap) {
+			if (lane == 0) atomicOr(err, ERR_READ_TOO_LONG);
+			if (active) pack_read_slow(ascii + off, (uint32_t)min(len64, (uint64_t)max_read_len), k, lay, (mate ? packed1 : packed0) + pair * W64, (mate ? meta1 : meta0) + pair);
+			continue;
+		}
+		// ---- stage the tile: coalesced 16-byte asynchronous copies ----
+#pragma unroll 1
+		for (uint32_t c = lane; c < (uint32_t)(nbytes >> 4); c += 32) cp_async16(tin + 16 * c, a0 + 16 * (uint64_t)c);
+		cp_async_wait_all();
+		__syncwarp();
+		// ---- pack one read per lane ----
+		uint64_t* orec = tout + ((size_t)mate * 16 + (lane >> 1)) * W64;
+		if (active) {
+			const uint32_t so = (uint32_t)((ascii + off) - a0);                         // byte offset of the read inside the tile
+			(mate ? meta1 : meta0)[pair] = pack_read_swar(reinterpret_cast<const uint32_t*>(tin + (so & ~3u)), (so & 3u) * 8, (uint32_t)len64, k, lay, orec);
+		}
+		__syncwarp();
+		// ---- write the two record blocks out: coalesced 128-bit stores ----
+		{
+			const uint64_t pair0 = tile * 16;
+			const uint32_t npair_m[2] = {(nact + 1) / 2, nact / 2};
+#pragma unroll
+			for (int m = 0; m < 2; ++m) {
+				const uint4* src = reinterpret_cast<const uint4*>(tout + (size_t)m * 16 * W64);
+				uint4* dst = reinterpret_cast<uint4*>((m ? packed1 : packed0) + pair0 * W64);
+				const uint32_t n16 = npair_m[m] * W64 / 2;
+#pragma unroll 1
+				for (uint32_t q = lane; q < n16; q += 32) dst[q] = src[q];
+			}
+		}
+		__syncwarp();
+	}
 }
 
 // ============================================================================================
@@ -346,8 +401,18 @@ __global__ void random_gather_kernel(const uint4* __restrict__ table, uint64_t n
 cudaError_t launch_pack(cudaStream_t st, const uint8_t* ascii, const uint64_t* offsets, uint64_t npairs, const RunParams& rp,
                         uint64_t* p0, uint64_t* p1, uint16_t* m0, uint16_t* m1, uint32_t* err) {
 	if (!npairs) return cudaSuccess;
-	uint64_t nreads = 2 * npairs;
-	pack_kernel<<<(unsigned)((nreads + 127) / 128), 128, 0, st>>>(ascii, offsets, nreads, rp.k, rp.lay, rp.max_read_len, npairs, p0, p1, m0, m1, err);
+	const uint64_t nreads = 2 * npairs;
+	const uint32_t in_cap = (32u * rp.max_read_len + 15u + 8u + 15u) & ~15u;
+	const size_t smem = (size_t)PACK_WARPS * (in_cap + 32 * rp.lay.W64 * 8);
+	static bool attr_set = false;
+	if (!attr_set) {
+		cudaError_t e = cudaFuncSetAttribute(pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+		if (e != cudaSuccess) return e;
+		attr_set = true;
+	}
+	const uint64_t ntiles = (nreads + 31) / 32;
+	const unsigned grid = (unsigned)std::min<uint64_t>((ntiles + PACK_WARPS - 1) / PACK_WARPS, 148ull * 64);
+	pack_kernel<<<grid, PACK_WARPS * 32, smem, st>>>(ascii, offsets, nreads, rp.k, rp.lay, rp.max_read_len, in_cap, p0, p1, m0, m1, err);
 	return cudaGetLastError();
 }
 

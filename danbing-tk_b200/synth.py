@@ -173,21 +173,72 @@ def locus_graph(haps, k):
     return nodes.astype("<u8"), masks.astype(np.uint8)
 
 
-def build_graph(loci, k=21, pref=None):
+_PAR = {}
+
+
+def _par_sets(args):
+    l0, l1, k, fsi, fso = args
+    return [locus_kmer_sets(h, k, fsi, fso) for h in _PAR["loci"][l0:l1]]
+
+
+def _par_graph(args):
+    l0, l1, k = args
+    return [locus_graph(h, k) for h in _PAR["loci"][l0:l1]]
+
+
+def _pmap(fn, loci, extra, nproc):
+    """per-locus map over forked workers (the loci are inherited copy-on-write); serial below 4000 loci or with nproc <= 1"""
+    if nproc <= 1 or len(loci) < 4000:
+        _PAR["loci"] = loci
+        return fn((0, len(loci)) + extra)
+    import multiprocessing as mp
+    _PAR["loci"] = loci
+    step = max(64, len(loci) // (nproc * 8))
+    jobs = [(a, min(len(loci), a + step)) + extra for a in range(0, len(loci), step)]
+    with mp.get_context("fork").Pool(nproc) as pool:
+        parts = pool.map(fn, jobs)
+    return [x for p in parts for x in p]
+
+
+_wlib = None
+
+
+def write_kmers_text_fast(fn, n, ks, vs=None):
+    """rpgg_io.write_kmers_text through libdbt_synth.so's C writer when it is built (values: u8 masks or zeros)"""
+    global _wlib
+    so = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libdbt_synth.so")
+    if _wlib is None and os.path.exists(so):
+        import ctypes as C
+        _wlib = C.CDLL(so)
+        if not hasattr(_wlib, "dbt_write_kmers_text"):
+            _wlib = False
+        else:
+            _wlib.dbt_write_kmers_text.argtypes = [C.c_char_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
+    if not _wlib:
+        return rpgg_io.write_kmers_text(fn, n, ks, vs)
+    n = np.ascontiguousarray(n, "<u8")
+    ks = np.ascontiguousarray(ks, "<u8")
+    v = None if vs is None else np.ascontiguousarray(vs, np.uint8)
+    rc = _wlib.dbt_write_kmers_text(fn.encode(), len(n), n.ctypes.data, ks.ctypes.data, None if v is None else v.ctypes.data)
+    if rc:
+        raise OSError(f"dbt_write_kmers_text({fn}) failed: {rc}")
+
+
+def build_graph(loci, k=21, pref=None, nproc=1):
     """-> dict(g_n, g_kmers, g_masks); with pref also writes PREF.graph.kmers (text, `node<TAB>mask`)."""
-    gs = [locus_graph(h, k) for h in loci]
+    gs = _pmap(_par_graph, loci, (k,), nproc)
     g_n = np.array([len(n) for n, _ in gs], "<u8")
     g_k = np.concatenate([n for n, _ in gs]).astype("<u8") if gs else np.zeros(0, "<u8")
     g_m = np.concatenate([m for _, m in gs]).astype(np.uint8) if gs else np.zeros(0, np.uint8)
     if pref is not None:
-        rpgg_io.write_kmers_text(pref + ".graph.kmers", g_n, g_k, g_m)
+        write_kmers_text_fast(pref + ".graph.kmers", g_n, g_k, g_m)
     return dict(g_n=g_n, g_kmers=g_k, g_masks=g_m)
 
 
-def build_rpgg(loci, pref, k=21, fsi=700, fso=700, write_text=True):
+def build_rpgg(loci, pref, k=21, fsi=700, fso=700, write_text=True, nproc=1):
     """Writes PREF.tr.kmers, PREF.fl.kmers (text), PREF.kmers.dbi, PREF.fl.kdb, PREF.tre.kdb (valid, empty).
     Returns the host index dict (tr order = file order)."""
-    trs, fls = zip(*[locus_kmer_sets(h, k, fsi, fso) for h in loci])
+    trs, fls = zip(*_pmap(_par_sets, loci, (k, fsi, fso), nproc))
     tr_n = np.array([len(t) for t in trs], "<u8")
     fl_n = np.array([len(t) for t in fls], "<u8")
     tr_k = np.concatenate(trs).astype("<u8") if len(trs) else np.zeros(0, "<u8")
@@ -195,8 +246,8 @@ def build_rpgg(loci, pref, k=21, fsi=700, fso=700, write_text=True):
     keys, vals, vv = build_dbi(tr_n, tr_k, fl_n, fl_k)
     os.makedirs(os.path.dirname(os.path.abspath(pref)), exist_ok=True)
     if write_text:
-        rpgg_io.write_kmers_text(pref + ".tr.kmers", tr_n, tr_k)
-        rpgg_io.write_kmers_text(pref + ".fl.kmers", fl_n, fl_k)
+        write_kmers_text_fast(pref + ".tr.kmers", tr_n, tr_k)
+        write_kmers_text_fast(pref + ".fl.kmers", fl_n, fl_k)
     rpgg_io.write_dbi(pref + ".kmers.dbi", keys, vals, vv)
     rpgg_io.write_kdb(pref + ".fl.kdb", fl_n, fl_k)
     rpgg_io.write_kdb(pref + ".tre.kdb", np.zeros(len(tr_n), "<u8"), np.zeros(0, "<u8"))

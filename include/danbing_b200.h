@@ -259,7 +259,12 @@ uint32_t dbt_record_es_cap(const dbt_ctx*);
 #define DBT_NCCL_ID_BYTES 128
 int  dbt_nccl_unique_id(uint8_t id[DBT_NCCL_ID_BYTES]);
 int  dbt_comm_init(dbt_ctx*, int nranks, int rank, const uint8_t id[DBT_NCCL_ID_BYTES]);
-int  dbt_allreduce(dbt_ctx*);   /* in-place ncclAllReduce(sum) of counts, kmc, nmapread, counters */
+/* One grouped ncclAllReduce(sum) of counts, kmc, nmapread and the counters, OUT OF PLACE: the rank's own arrays are left
+   untouched; dbt_download hands out the all-rank sums until the next dbt_process / dbt_reset_counts.  Calling it again (or
+   after more batches) reduces the current local state afresh -- nothing is ever multiplied by the number of ranks.
+   Requires every dbt_fetch to have been finished with dbt_wait.  Replaces "one address space, one set of atomics" of
+   cpp:2598-2656. */
+int  dbt_allreduce(dbt_ctx*);
 
 /* ---- measurement helpers (CUDA events on the context's own streams) ------------------------- */
 int  dbt_timer_start(dbt_ctx*, int slot);
@@ -272,6 +277,7 @@ int  dbt_batch_stats(dbt_ctx*, int slot, uint64_t stats[4]);
 /* [0] main buckets [1] slots per bucket [2] keys [3] used slots [4] main buckets that overflowed
    [5] keys in the stash [6] table bytes [7] stash buckets that overflowed */
 int  dbt_table_stats(const dbt_ctx*, uint64_t stats[8]);
+uint64_t dbt_graph_table_bytes(const dbt_ctx*);                /* bytes of the graph table in HBM (0 without restored threading) */
 int  dbt_random_gather_bench(int device, uint64_t table_bytes, uint32_t sector_bytes,
                              uint64_t n_gathers, int iters, float* best_ms); /* R_rand roofline    */
 

@@ -137,3 +137,17 @@ def test_host_packer_random_vs_model(lib, monkeypatch):
             for m in (0, 1):
                 assert np.array_equal(p[m], want[m::2]), (max_len, k, swar, m)
                 assert np.array_equal(meta[m], wmeta[m::2]), (max_len, k, swar, m)
+
+
+def test_device_packer_body_matches_host_packer(tmp_path):
+    """csrc/pack_read.cuh (the per-lane SWAR body of pack_kernel, compiled for the host) == dbt_pack_reads' packer:
+    every length 0..max, every alignment inside a staged tile, N / lower-case / arbitrary bytes, k = 17/21/25"""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "pack_check")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-o", exe, os.path.join(root, "tests/native/pack_check.cpp"),
+                    os.path.join(root, "danbing-tk_b200/csrc/host_pack.cpp")], check=True)
+    out = subprocess.run([exe], capture_output=True, text=True)
+    assert out.returncode == 0 and out.stdout.startswith("OK"), out.stdout
+    ncase, nnovalid = map(int, out.stdout.split()[1:3])
+    assert ncase >= 50000 and 1000 < nnovalid < ncase - 1000
