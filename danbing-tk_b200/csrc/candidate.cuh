@@ -101,7 +101,7 @@ __device__ __forceinline__ void updatetop2(uint64_t cf, uint32_t ind, uint64_t c
 struct VoteHits {
 	uint32_t* lkey; uint32_t* lf; uint32_t* lr;    // shared memory, VOTE_SMEM_SLOTS entries, key = locus+1
 	uint64_t* pool; uint32_t* lock; uint32_t* epochs; uint64_t nloci; uint32_t seed;
-	uint32_t used; int held; uint32_t epoch; volatile uint64_t* scratch;
+	uint32_t used; int held; uint32_t epoch; volatile uint64_t* scratch; uint32_t spill_at;
 	__device__ __noinline__ void acquire() {
 		uint32_t i = seed % VOTE_POOL;
 		while (atomicCAS(lock + i, 0u, 1u) != 0u) i = (i + 1) % VOTE_POOL;
@@ -128,7 +128,7 @@ struct VoteHits {
 			uint32_t kk = lkey[s];
 			if (kk == locus + 1) { f = (lf[s] += df); r = (lr[s] += dr); return; }
 			if (kk == 0) {
-				if (used >= VOTE_SPILL_AT) break;                // keep the table sparse; spill to global
+				if (used >= spill_at) break;                // keep the table sparse; spill to global
 				lkey[s] = locus + 1; lf[s] = df; lr[s] = dr; ++used; f = df; r = dr; return;
 			}
 		}
@@ -289,9 +289,9 @@ __device__ __noinline__ void perm_introsort(uint16_t* perm, const uint32_t* unml
 // find_matching_locus, literal (cpp:364-422); one lane.  Returns top.idx / top.fc / top.rc.
 __device__ __noinline__ uint3 vote_serial(const uint32_t* __restrict__ vv, const uint16_t* perm, const uint32_t* uval, const uint16_t* utf,
                                           const uint16_t* utr, uint32_t* lkey, uint32_t U, uint32_t total, uint32_t cth32,
-                                          const DevIndex& ix, uint32_t seed) {
+                                          const DevIndex& ix, uint32_t seed, uint32_t spill_at) {
 	Asgn top = {NAN32, 0, 0}, second = {NAN32, 0, 0};
-	VoteHits vh{lkey, lkey + VOTE_SMEM_SLOTS, lkey + 2 * VOTE_SMEM_SLOTS, ix.vote_pool, ix.vote_lock, ix.vote_epoch, ix.nloci, seed, 0, -1, 0, nullptr};
+	VoteHits vh{lkey, lkey + VOTE_SMEM_SLOTS, lkey + 2 * VOTE_SMEM_SLOTS, ix.vote_pool, ix.vote_lock, ix.vote_epoch, ix.nloci, seed, 0, -1, 0, nullptr, spill_at};
 	uint64_t rem = total;
 	const uint64_t cth = cth32;
 	for (uint32_t i = 0; i < U; ++i) {
@@ -612,7 +612,7 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 				dst0 = val0 >> 1;
 			} else {
 				uint3 t3 = make_uint3(NAN32, 0, 0);
-				if (lane == 0) t3 = vote_serial(ix.vv, perm, uval, utf, utr, lkey, U, total, rp.cth, ix, gwarp);
+				if (lane == 0) t3 = vote_serial(ix.vv, perm, uval, utf, utr, lkey, U, total, rp.cth, ix, gwarp, rp.vote_spill_at);
 				dst0 = __shfl_sync(0xffffffffu, t3.x, 0);
 				fc = __shfl_sync(0xffffffffu, t3.y, 0);
 				rc = __shfl_sync(0xffffffffu, t3.z, 0);

@@ -187,6 +187,8 @@ extern "C" int dbt_create(dbt_ctx** out, const dbt_params* p) {
 	rp.as_stride = round_up((rp.nk_max + 3) / 4, 8);
 	rp.rec_stride = (uint32_t)sizeof(dbt_pair_record) + 2 * rp.as_stride;
 	rp.max_records = c->p.max_records;
+	rp.vote_spill_at = VOTE_SPILL_AT;
+	if (const char* e = getenv("DBT_VOTE_SPILL_AT")) { const int v = atoi(e); if (v >= 0 && v < (int)VOTE_SPILL_AT) rp.vote_spill_at = (uint32_t)v; }   // test hook
 	// restored threading: geometry of the alignment blobs; switched on by dbt_load_index when the index carries a graph
 	rp.thr_on = 0; rp.thread_cth = p->thread_cth; rp.max_ncorrection = p->max_ncorrection; rp.correction = (p->flags & DBT_F_CORRECTION) ? 1u : 0u;
 	rp.es_cap = DBT_ES_CAP_FOR(p->max_read_len, p->max_ncorrection);

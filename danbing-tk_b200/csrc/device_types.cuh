@@ -9,10 +9,8 @@ namespace dbt {
 
 constexpr uint32_t NAN32 = 0xFFFFFFFFu;
 constexpr int VOTE_SMEM_SLOTS = 64;          // per-pair shared-memory (locus -> hits1,hits2) entries
-#ifndef DBT_VOTE_SPILL_AT
-#define DBT_VOTE_SPILL_AT (VOTE_SMEM_SLOTS - 8)
-#endif
-constexpr uint32_t VOTE_SPILL_AT = DBT_VOTE_SPILL_AT;   // loci held in shared memory before a pair spills to the global pool (test builds lower it)
+constexpr uint32_t VOTE_SPILL_AT = VOTE_SMEM_SLOTS - 8;  // loci held in shared memory before a pair spills to the global pool
+                                                        // (RunParams::vote_spill_at; the DBT_VOTE_SPILL_AT environment variable lowers it in tests)
 constexpr uint32_t VOTE_POOL = 64;           // global spill arrays [nloci+1], shared under locks by all in-flight kernels of a context
 constexpr int CAND_WARPS_SLOW = 4;             // generic candidate_kernel: warps per block
 
@@ -45,6 +43,7 @@ struct RunParams {
 	uint32_t sortn;             // power of two >= 2*nk_max
 	uint32_t as_stride, rec_stride;
 	uint32_t warp_smem;         // bytes of shared memory per warp in candidate_kernel
+	uint32_t vote_spill_at;     // VOTE_SPILL_AT, or the test override
 	uint32_t max_records;
 	// restored graph threading (P1); all 0 unless DBT_F_THREADING and a graph is loaded
 	uint32_t thr_on;            // 1 = hand candidates to thread_kernel instead of the HEAD no-op

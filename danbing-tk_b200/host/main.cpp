@@ -260,10 +260,8 @@ int main(int argc, char** argv) {
 		while (!S.failed && recycle.pop(hb)) {
 			hb->reset(first);
 			if (!rd.fill(*hb)) { recycle.push(hb); break; }
-			if (hb->npairs == 0) {
-				if (hb->bases_cap < 2 * 1000000) { S.fail("a read pair does not fit the batch buffer"); recycle.push(hb); break; }
-				recycle.push(hb);
-				continue;
+			if (hb->npairs == 0) {                            // fill() made progress without emitting: the pending pair does not fit an EMPTY batch
+				S.fail("a read pair does not fit the batch buffer (raise --batch-pairs)"); recycle.push(hb); break;
 			}
 			first += hb->npairs;
 			workers[b % G]->in.push(hb);

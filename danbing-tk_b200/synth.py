@@ -36,9 +36,11 @@ def canonical_kmers(codes, k):
 
 
 def make_loci(nloci, seed=20261104, nhap=8, flank=700, share_frac=0.05, share_len=200, tr_median=300,
-              tr_min=50, tr_max=5000, sub_rate=0.02):
+              tr_min=50, tr_max=5000, sub_rate=0.02, multi_share=None):
     """Returns haps[locus][hap] = ASCII bytes (flank + TR + flank). A fraction of loci copy a segment
-    of another locus' TR/flank so that multi-locus k-mers (the vv path) occur."""
+    of another locus' TR/flank so that multi-locus k-mers (the vv path) occur.
+    multi_share = (n, seg_len): ONE random segment is additionally dropped into n loci, so that its k-mers are
+    listed in n loci (vv lists of hundreds of entries, as low-complexity k-mers are in real RPGGs)."""
     loci = []
     for l in range(nloci):
         rng = np.random.default_rng([seed, l])
@@ -67,6 +69,14 @@ def make_loci(nloci, seed=20261104, nhap=8, flank=700, share_frac=0.05, share_le
             # drop the shared segment into the TR/flank boundary region of locus a
             p0 = int(min(max(flank - share_len // 2, 0), len(d) - len(seg)))
             d[p0:p0 + len(seg)] = seg
+    if multi_share:
+        n, seg_len = multi_share
+        seg = rng.integers(0, 4, seg_len, dtype=np.uint8)
+        for a in rng.choice(nloci, min(n, nloci), replace=False):
+            for h in range(nhap):
+                d = loci[a][h]
+                p0 = int(min(max(flank + 10, 0), len(d) - len(seg)))
+                d[p0:p0 + len(seg)] = seg
     return [[_ASCII[h].tobytes() for h in haps] for haps in loci]
 
 

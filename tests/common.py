@@ -49,10 +49,10 @@ def summary_text(nmap, kmc):
     return "".join(f"{int(a)}\t{int(b)}\n" for a, b in zip(nmap, kmc))
 
 
-def synthetic_case(nloci=60, seed=21, k=21, nhap=4, flank=300, npairs=6000, read_seed=5, **simkw):
+def synthetic_case(nloci=60, seed=21, k=21, nhap=4, flank=300, npairs=6000, read_seed=5, multi_share=None, **simkw):
     """RPGG + mixed trap reads generated here (numpy), for oracle-vs-GPU parity beyond the goldens."""
     import tempfile
-    loci = synth.make_loci(nloci, seed=seed, nhap=nhap, flank=flank, share_frac=0.3, share_len=120, tr_median=200)
+    loci = synth.make_loci(nloci, seed=seed, nhap=nhap, flank=flank, share_frac=0.3, share_len=120, tr_median=200, multi_share=multi_share)
     tmp = tempfile.mkdtemp(prefix="dbt_syn_")
     ix = synth.build_rpgg(loci, os.path.join(tmp, "syn"), k=k, fsi=flank, fso=flank, write_text=False)
     reads = synth.sim_reads(loci, npairs, seed=read_seed, **simkw)

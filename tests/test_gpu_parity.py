@@ -211,3 +211,50 @@ def test_gpu_index_consistency_is_checked():
     p = abi.default_params(k=21, cth=10, max_batch_pairs=64)
     with pytest.raises(abi.DbtError, match="index"):
         abi.Context(p, abi.make_index_struct(bad))
+
+
+def _vv_max_list(ix):
+    vv, m, o = ix["vv"], 0, 0
+    while o < len(vv):
+        m = max(m, int(vv[o]))
+        o += int(vv[o]) + 1
+    return m
+
+
+@pytest.mark.parametrize("spill_at", [None, 2])
+def test_gpu_vote_spill_pool(spill_at, monkeypatch):
+    """k-mers listed in > 100 loci (one segment dropped into 130 loci): a pair's locus vote touches more loci than the
+    shared-memory table holds and spills into the locked global pool (candidate.cuh VoteHits).  Generic kernel for every
+    pair (TRACE) and fast + generic kernels (production), then BOTH slots in flight at once sharing the pool;
+    DBT_VOTE_SPILL_AT=2 makes nearly every multi-locus vote spill."""
+    if spill_at is not None:
+        monkeypatch.setenv("DBT_VOTE_SPILL_AT", str(spill_at))
+    ix, seqs, _ = synthetic_case(nloci=160, seed=91, npairs=6000, read_seed=17, multi_share=(130, 140),
+                                 frac_locus=0.5, frac_chimeric=0.25, frac_border=0.1)
+    assert _vv_max_list(ix) >= 100
+    for flags in (abi.F_KAM | abi.F_TRACE, abi.F_KAM):
+        p = abi.default_params(k=21, cth=30, flags=flags, max_batch_pairs=8192)
+        oracle_vs_gpu(ix, seqs, p)
+    # two batches in flight on the two slots (the CLI's worker loop): counts equal the oracle's on the concatenation
+    p = abi.default_params(k=21, cth=30, flags=abi.F_KAM | abi.F_TRACE, max_batch_pairs=4096)
+    bases, off = rpgg_io.seqs_to_batch(seqs)
+    _, _, otr, okmc, onmap = Oracle(ix).run(p, bases, off)
+    ctx = abi.Context(p, abi.make_index_struct(ix))
+    L = ctx.L
+    npairs, half = len(seqs) // 2, len(seqs) // 4
+    keep = []
+    for rep in range(3):
+        ctx.reset()
+        for s, (b0, b1) in enumerate(((0, half), (half, npairs))):
+            rec = np.zeros((b1 - b0) * ctx.stride, np.uint8)
+            r = abi.BatchResult()
+            r.capacity = b1 - b0
+            r.records = abi.ptr(rec, abi.u8p)
+            b = ctx.make_batch(bases, off[2 * b0: 2 * b1 + 1], first_pair_index=b0)
+            keep.append((rec, r, b))
+            abi.check(L, L.dbt_submit(ctx.h, C.byref(b), C.byref(r), s), "submit")
+        for s in (0, 1):
+            abi.check(L, L.dbt_wait(ctx.h, s), "wait")
+        trkmc, kmc, nmap, _ = ctx.download()
+        assert np.array_equal(trkmc, otr) and np.array_equal(kmc, okmc) and np.array_equal(nmap, onmap)
+    ctx.close()
