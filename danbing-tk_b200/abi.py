@@ -11,7 +11,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("DBT_LIB") or os.path.join(HERE, "libdanbing_b200.so")   # DBT_LIB: kernel-variant experiments only
 
-DBT_N_COUNTERS = 24
+DBT_N_COUNTERS = 32
 DBT_N_SLOTS = 2
 DBT_NCCL_ID_BYTES = 128
 
@@ -22,9 +22,11 @@ COUNTER_NAMES = ["nReads", "nShort", "nSubFiltered", "nKmerFiltered", "nBaitFilt
                  "nLocusAssignFiltered", "nQCFiltered", "nThreadingReads", "nFeasibleReads", "nAsgnReads",
                  "nhash0", "nhash1", "ninc", "ncandidates", "nrecords",
                  "gen_pairs", "gen_nhash1", "gen_nThreadingReads", "gen_ninc",
-                 "thr_walk", "thr_ec", "thr_cls", "thr_refresh"]
+                 "thr_walk", "thr_ec", "thr_cls", "thr_refresh",
+                 "thr2_pairs", "thr2_mates", "thr2_walk", "thr2_cls", "thr2_ninc", "thr2_refresh", "reserved30", "reserved31"]
 MEASUREMENT_COUNTERS = ("nrecords", "gen_pairs", "gen_nhash1", "gen_nThreadingReads", "gen_ninc",
-                        "thr_walk", "thr_ec", "thr_cls", "thr_refresh")   # no reference counterpart
+                        "thr_walk", "thr_ec", "thr_cls", "thr_refresh",
+                        "thr2_pairs", "thr2_mates", "thr2_walk", "thr2_cls", "thr2_ninc", "thr2_refresh", "reserved30", "reserved31")   # no reference counterpart
 MF_KF, MF_HF, MF_BF, MF_QF, MF_AF, MF_RM = 1, 2, 4, 8, 16, 32
 
 u64p = C.POINTER(C.c_uint64)

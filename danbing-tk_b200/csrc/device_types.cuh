@@ -58,15 +58,18 @@ struct SlotView {
 	uint32_t* passmask;         // bit per pair: passed subfilter
 	uint32_t* blocksum;         // compaction scratch
 	uint32_t* cand;             // candidate pair ids, ascending
-	uint32_t* ncand;            // [0] = number of candidates, [1] = error flags, [2] = length of slow[], [3] = length of thr[]
+	uint32_t* ncand;            // [0] = number of candidates, [1] = error flags, [2] = length of slow[], [3] = length of thr[], [4] = length of thr2[]
 	uint32_t* slow;             // candidate ordinals left to the generic kernel
 	uint4*    thr;              // work items of thread_kernel (ncand[3] entries): x = candidate ordinal, y = pair index within the
 	                            // batch, z = dst | kf bits << 28 | rm bits << 30 -- one 16-byte load per pair instead of a chain of three
+	uint4*    thr2;             // work items of thread_kernel (ncand[4] entries), appended by thread_fast_kernel: x, y, z as thr,
+	                            // w = mates to thread (THR2_MATE0 | THR2_MATE1) | THR2_ALNED: the other mate threaded cleanly, the pair already counts
 	uint8_t*  records;
 	unsigned long long* counters;   // DBT_N_COUNTERS
 	uint64_t npairs, first_pair_index;
 };
 
+constexpr uint32_t THR2_MATE0 = 1u, THR2_MATE1 = 2u, THR2_ALNED = 4u;
 constexpr int DBT_ST_THREAD_PENDING = 9;       // internal: handed to thread_kernel, which writes the final status
 constexpr uint32_t ERR_RECORD_OVERFLOW = 1u;
 constexpr uint32_t ERR_READ_TOO_LONG   = 2u;

@@ -1,0 +1,306 @@
+// thread_fast_kernel: the first of the two threading kernels (SURVEY.md §8(a) rows T1-T3, T6 + decision D1 of §8(c)).
+//
+// Three quarters of the mates handed to isThreadFeasible (cpp:1114-1260) carry no sequencing error: their first k-mer is
+// a node of the locus graph and every later k-mer sits on an out-edge of its predecessor.  The reference then anchors at
+// k-mer 0 (cpp:1129; find_anchor marks es[0..k) '=', cpp:878-888), walks the whole read through cpp:1167-1180
+// (tr[i] = '=' for TR k-mers, '.' otherwise; es[i+k-1] = '=') and returns 1 (cpp:1259: no skip, no correction).  Whether a
+// mate is of that kind is a function of per-position data only, so this kernel decides it for BOTH mates of every pair
+// with one probe round per mate and nothing else: no walk state, no CIGAR arrays, no correction code -- about 1.5 k warp
+// instructions per pair where the all-in-one kernel of round 1 spent 7 k (profiles/r1/s28: instruction-fetch bound, every
+// warp of a scheduler in different code).  A clean mate is finished here: its TR k-mers are counted (D1: both edited
+// vectors of a pair that threads are counted, cpp:2203-2208 -- a clean mate makes the pair thread) and its half of the
+// aln record is written from the ballots.  Mates with an error go to a work list for thread_kernel (thread_kernel.cuh),
+// which owns find_anchor / errorCorrection_* / edit_kmers_*; a pair with one clean mate is already known to count, a
+// pair with two dirty mates is decided there.
+//
+// Per mate, ROLLED loops over the 32-position groups (small code; every warp of the SM runs these same loops):
+//   A   k-mer of position j*32+lane straight from the packed words (funnel shifts; the little-endian packing makes the
+//       reverse complement a NOT + mask, kmer.cuh), canonical form, home bucket of (canonical k-mer, locus) -> 32-byte
+//       asynchronous copy into shared memory; all groups of the mate are in flight together.  Also here, from the packed
+//       words alone: "window i equals window i+1" (the homopolymer repeat of cpp:1152) -- such mates are not clean;
+//   B1  match the staged slots -> node bits + count-array position per position; keys that continue in the stash (7 % at
+//       load 0.4) take a second, again batched, round;
+//   B2  "on an out-edge of its predecessor" (cpp:1170-1178 with node == kmers[ki-1]) and "TR k-mer" ballots.
+#pragma once
+#include "thread_kernel.cuh"          // CIGAR codes, kmer_rc, THR2_* work-item bits
+
+namespace dbt {
+
+#ifndef THRF_WARPS_N
+#define THRF_WARPS_N 4
+#endif
+#ifndef THRF_MINBLOCKS
+#define THRF_MINBLOCKS 7
+#endif
+constexpr int THRF_WARPS = THRF_WARPS_N;
+constexpr uint64_t THRF_RCFLAG = 1ull << 62;       // W.key: the read meets the k-mer in its reverse-complement orientation (k <= 27: bits 54.. are free)
+constexpr uint32_t THRF_F3_SHIFT = 60;             // W.key bits 60-61: last base of the strand-specific k-mer
+
+// continuation of a look-up behind the first stash bucket (rare): out of line
+template <int B>
+__device__ __noinline__ GNode g_lookup_canon_nl(const Table gt, uint64_t canon, bool is_rc, uint32_t locus, uint64_t b) {
+	const uint64_t hk = g_hash_key(canon, locus);
+	(void)hk;
+	for (;;) {
+		const uint4* bp = gt.slots + b * B;
+		bool full = true; uint64_t k0 = 0;
+#pragma unroll
+		for (int q = 0; q < B; ++q) {
+			const uint4 sl = ldg128(bp + q);
+			const uint64_t kk = slot_key(sl);
+			if (q == 0) k0 = kk;
+			if (kk == SLOT_EMPTY) full = false;
+			else if ((kk & SLOT_KEYMASK) == canon && (sl.z & G_LOCUS_MASK) == locus) return g_decode(sl.z, sl.w, is_rc);
+		}
+		if (!full || !(k0 & SLOT_OVF)) { GNode n; n.bits = 0; n.tr = 0; return n; }
+		b = stash_next(gt, b);
+	}
+}
+
+template <int B, int MAXJ>
+struct FastThreadWarp {
+	uint4    stage[MAXJ][B][32];               // home (then stash) buckets of every position of the mate being probed
+	uint64_t key[MAXJ * 32];                   // canonical k-mer | last base << 60 | THRF_RCFLAG; KMER_INVALID for an invalid window
+	uint32_t trx[MAXJ * 32];                   // count-array position + 1 of TR k-mers, else 0
+	uint8_t  nb[MAXJ * 32 + 32];               // nb[i + 1] = present | out-edge mask << 1 of position i (nb[0]: unused)
+	uint64_t pk[2 * MAXJ + 6];                 // packed record of the mate (W64 <= 1.5 MAXJ + 4 for reads of <= MAXJ*32 k-mers)
+	uint32_t T[MAXJ];                          // TR ballots
+};
+
+template <int B, int MAXJ>
+__global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_kernel(DevIndex ix, RunParams rp, SlotView sv) {
+	extern __shared__ __align__(16) uint8_t thrf_smem[];
+	FastThreadWarp<B, MAXJ>& W = reinterpret_cast<FastThreadWarp<B, MAXJ>*>(thrf_smem)[threadIdx.x >> 5];
+	const int lane = threadIdx.x & 31;
+	const uint32_t gwarp = blockIdx.x * THRF_WARPS + (threadIdx.x >> 5), nwarps = gridDim.x * THRF_WARPS;
+	const uint32_t nwork = sv.ncand[3];
+	const bool trace = (rp.flags & DBT_F_TRACE) != 0;
+	const bool aln_all = (rp.flags & DBT_F_ALN) && !(rp.flags & DBT_F_ALN_MIN), aln_min = (rp.flags & DBT_F_ALN_MIN) != 0;
+	const bool want_rec = trace || aln_all || aln_min;
+	const uint32_t W64 = rp.lay.W64, WB = rp.lay.WB, K = rp.k;
+	const Table gt = ix.gtable;
+	const uint64_t kmask = (1ull << (2 * K)) - 1, vmask = (1ull << K) - 1;
+	uint32_t c_fea = 0, c_inc = 0, c_cls = 0, c_walk = 0, c_probe = 0, c_items = 0;   // lane-0 accumulators (c_probe: per lane, reduced at the end)
+
+	uint4 item = gwarp < nwork ? sv.thr[gwarp] : make_uint4(0, 0, 0, 0);
+#pragma unroll 1
+	for (uint32_t t = gwarp; t < nwork; t += nwarps) {
+		const uint32_t c = item.x, p = item.y, dw = item.z;
+		if (t + nwarps < nwork) item = sv.thr[t + nwarps];                   // next work item: in flight while this pair is probed
+		const uint32_t dst = dw & G_LOCUS_MASK;
+		const uint64_t lmix = (uint64_t)dst * 0xC2B2AE3D27D4EB4Full;         // g_hash_key
+		const uint64_t slot = trace ? (uint64_t)p : (uint64_t)c;
+		const bool slot_ok = want_rec && (trace || slot < rp.max_records);
+		uint8_t* rec = sv.records + slot * rp.rec_stride;
+		uint32_t dirty = 0;                                                  // bit m: mate m goes to thread_kernel
+
+#pragma unroll 1
+		for (int m = 0; m < 2; ++m) {
+			const uint32_t len = sv.meta[m][p] & META_LENMASK;
+			const int nkm = (int)len - (int)K + 1;
+			__syncwarp();
+			for (uint32_t q = lane; q < W64 && q < 2 * MAXJ + 6; q += 32) W.pk[q] = sv.packed[m][(uint64_t)p * W64 + q];
+			__syncwarp();
+			if (nkm < 1 || nkm > MAXJ * 32 || W64 > 2 * MAXJ + 6) { dirty |= 1u << m; continue; }   // thread_kernel handles (and reports) the odd ones
+			const uint32_t* mk32 = reinterpret_cast<const uint32_t*>(W.pk + WB);
+			const uint32_t sh = 2 * lane;
+			const int ng = (nkm + 31) >> 5;
+			// ---- A: k-mers + home-bucket copies ----
+			bool plain = true, anyvalid = false;                               // plain: every window valid, none equal to its successor
+#pragma unroll 1
+			for (int j = 0; j < ng; ++j) {
+				const int i = j * 32 + lane;
+				const uint64_t wlo = W.pk[j], whi = (j + 1 < (int)WB) ? W.pk[j + 1] : 0ull;
+				const uint32_t mlo = mk32[j], mnx = ((uint32_t)(j + 1) < 2 * rp.lay.WM) ? mk32[j + 1] : 0xFFFFFFFFu;
+				const uint64_t wv = sh ? ((wlo >> sh) | (whi << (64 - sh))) : wlo;
+				const uint64_t mm = (((uint64_t)mnx << 32) | mlo) >> lane;
+				uint64_t kk = KMER_INVALID;
+				if (i < nkm) {
+					if ((mm & vmask) == 0) {
+						const uint64_t x = wv & kmask, rcx = (~wv) & kmask, fw = rev2(x) >> (64 - 2 * K);   // read2kmers(canonical = false), h:246-271
+						const bool is_rc = rcx < fw;
+						const uint64_t canon = is_rc ? rcx : fw;
+						kk = canon | ((fw & 3) << THRF_F3_SHIFT) | (is_rc ? THRF_RCFLAG : 0ull);
+						const uint4* bp = gt.slots + home_bucket(gt, canon ^ lmix) * B;
+#pragma unroll
+						for (int q = 0; q < B; ++q) cp_async16(&W.stage[j][q][lane], bp + q);
+						++c_probe;
+						anyvalid = true;
+						if (i + 1 < nkm && ((wv >> 2) & kmask) == x) plain = false;   // kmers[i+1] == kmers[i]: cpp:1152 is thread_kernel's
+					} else plain = false;
+				}
+				W.key[i] = kk;
+			}
+			cp_async_wait_all();
+			__syncwarp();
+			anyvalid = __any_sync(0xffffffffu, anyvalid);
+			plain = __all_sync(0xffffffffu, plain);
+			if (lane == 0 && anyvalid) c_walk += (uint32_t)nkm;               // the reference's walk: one node look-up per k-mer (cpp:1170)
+			if (!plain) { dirty |= 1u << m; continue; }
+			// ---- B1: match the home buckets ----
+			uint32_t need = 0;                                               // bit j: position j*32+lane continues in the stash
+#pragma unroll 1
+			for (int j = 0; j < ng; ++j) {
+				const int i = j * 32 + lane;
+				uint32_t bi = 0, trp = 0;
+				if (i < nkm) {
+					const uint64_t kw = W.key[i];
+					const uint64_t canon = kw & kmask;
+					const bool is_rc = (kw & THRF_RCFLAG) != 0;
+					bool full = true, found = false; uint64_t k0 = 0;
+#pragma unroll
+					for (int q = 0; q < B; ++q) {
+						const uint4 sl = W.stage[j][q][lane];
+						const uint64_t kk = slot_key(sl);
+						if (q == 0) k0 = kk;
+						if (kk == SLOT_EMPTY) full = false;
+						else if ((kk & SLOT_KEYMASK) == canon && (sl.z & G_LOCUS_MASK) == dst) { const GNode n = g_decode(sl.z, sl.w, is_rc); bi = n.bits; trp = n.tr; found = true; }
+					}
+					if (!found && full && (k0 & SLOT_OVF)) need |= 1u << j;
+				}
+				W.nb[i + 1] = (uint8_t)(bi & 0x1Fu); W.trx[i] = trp;
+			}
+			if (__any_sync(0xffffffffu, need != 0)) {                        // second round: first stash bucket, batched like the first
+				__syncwarp();
+#pragma unroll 1
+				for (int j = 0; j < ng; ++j) {
+					if (!((need >> j) & 1u)) continue;
+					const uint64_t canon = W.key[j * 32 + lane] & kmask;
+					const uint4* bp = gt.slots + stash_bucket(gt, canon ^ lmix) * B;
+#pragma unroll
+					for (int q = 0; q < B; ++q) cp_async16(&W.stage[j][q][lane], bp + q);
+					++c_probe;
+				}
+				cp_async_wait_all();
+#pragma unroll 1
+				for (int j = 0; j < ng; ++j) {
+					if (!((need >> j) & 1u)) continue;
+					const int i = j * 32 + lane;
+					const uint64_t kw = W.key[i];
+					const uint64_t canon = kw & kmask;
+					const bool is_rc = (kw & THRF_RCFLAG) != 0;
+					uint32_t bi = 0, trp = 0;
+					bool full = true, found = false; uint64_t k0 = 0;
+#pragma unroll
+					for (int q = 0; q < B; ++q) {
+						const uint4 sl = W.stage[j][q][lane];
+						const uint64_t kk = slot_key(sl);
+						if (q == 0) k0 = kk;
+						if (kk == SLOT_EMPTY) full = false;
+						else if ((kk & SLOT_KEYMASK) == canon && (sl.z & G_LOCUS_MASK) == dst) { const GNode n = g_decode(sl.z, sl.w, is_rc); bi = n.bits; trp = n.tr; found = true; }
+					}
+					if (!found && full && (k0 & SLOT_OVF)) {
+						const GNode n = g_lookup_canon_nl<B>(gt, canon, is_rc, dst, stash_next(gt, stash_bucket(gt, canon ^ lmix)));
+						bi = n.bits; trp = n.tr;
+					}
+					W.nb[i + 1] = (uint8_t)(bi & 0x1Fu); W.trx[i] = trp;
+				}
+			}
+			__syncwarp();
+			// ---- B2: every k-mer on an out-edge of its predecessor, the first one a node? ----
+			bool clean = true;
+#pragma unroll 1
+			for (int j = 0; j < ng; ++j) {
+				const int i = j * 32 + lane;
+				bool ok = true, tr = false;
+				if (i < nkm) {
+					const uint32_t f3 = (uint32_t)(W.key[i] >> THRF_F3_SHIFT) & 3u;
+					const uint32_t pb = W.nb[i];                                 // node of position i-1 (i == 0: unused)
+					ok = i == 0 ? (W.nb[1] & 1u) != 0 : ((pb & 1u) && ((pb >> (1 + f3)) & 1u));
+					tr = W.trx[i] != 0;
+				}
+				if (!__all_sync(0xffffffffu, ok)) clean = false;
+				const uint32_t bt = __ballot_sync(0xffffffffu, tr);
+				if (lane == 0) W.T[j] = bt;
+			}
+			__syncwarp();
+			if (!clean) { dirty |= 1u << m; continue; }
+
+			// ---- clean mate: alned = 1, es all '=', tr from the TR ballots; count its TR k-mers (D1) ----
+			{
+				uint32_t inc_sum = 0;
+#pragma unroll 1
+				for (int j = 0; j < ng; ++j) {
+					const int i = j * 32 + lane;
+					const uint32_t tx = i < nkm ? W.trx[i] : 0u;
+					const uint32_t tm = W.T[j];
+					if (!tm) continue;
+					inc_sum += __popc(tm);
+					if (tx) {
+						const uint32_t peers = __match_any_sync(tm, tx);
+						if ((uint32_t)lane == (uint32_t)(__ffs(peers) - 1))
+							atomicAdd(reinterpret_cast<unsigned long long*>(ix.counts + (tx - 1)), (unsigned long long)__popc(peers));
+					}
+				}
+				if (lane == 0) { c_inc += inc_sum; c_cls += (uint32_t)nkm; }
+			}
+			if (slot_ok) {                                                   // sam_t.r1 / r2 -> dbt_aln_mate blob
+				uint8_t* b = rec + sizeof(dbt_pair_record) + (size_t)m * rp.aln_stride;
+				uint8_t* es = b + sizeof(dbt_aln_mate); uint8_t* trb = es + rp.es_cap;
+				const int nes = min((int)len, (int)rp.es_cap), ntr = min(nkm, (int)rp.tr_cap);
+#pragma unroll 1
+				for (int q = lane; q < (int)rp.es_cap / 4; q += 32) {         // four entries per lane and store; entries >= nes read 0
+					const int nbb = nes - 4 * q;
+					const uint32_t keep = nbb >= 4 ? 0xFFFFFFFFu : (nbb <= 0 ? 0u : (1u << 8 * nbb) - 1u);
+					reinterpret_cast<uint32_t*>(es)[q] = (0x01010101u * ET_EQ) & keep;
+				}
+#pragma unroll 1
+				for (int q = lane; q < (int)rp.tr_cap / 4; q += 32) {         // tr[i] = '=' (2) for TR k-mers, '.' (1) otherwise: 4 TR ballot bits -> 4 bytes
+					const int nbb = ntr - 4 * q;
+					const uint32_t keep = nbb >= 4 ? 0xFFFFFFFFu : (nbb <= 0 ? 0u : (1u << 8 * nbb) - 1u);
+					const uint32_t bits = 4 * q < ng * 32 ? (W.T[(4 * q) >> 5] >> ((4 * q) & 31)) & 0xFu : 0u;
+					const uint32_t v = 0x01010101u + ((bits & 1u) | ((bits & 2u) << 7) | ((bits & 4u) << 14) | ((bits & 8u) << 21));
+					reinterpret_cast<uint32_t*>(trb)[q] = v & keep;
+				}
+				if (lane == 0) {
+					dbt_aln_mate* h = reinterpret_cast<dbt_aln_mate*>(b);
+					h->alned = 1; h->err = (uint8_t)((int)len > (int)rp.es_cap || nkm > (int)rp.tr_cap);
+					h->nes = (uint16_t)len; h->ntr = (uint16_t)nkm; h->nkm = (uint16_t)nkm;
+					uint64_t hash = 0;
+					if (trace) {                                                // FNV-1a over the k-mer vector (parity tests only)
+						hash = 0xcbf29ce484222325ull;
+#pragma unroll 1
+						for (int i = 0; i < nkm; ++i) {
+							const uint64_t kw = W.key[i];
+							const uint64_t v = (kw & THRF_RCFLAG) ? kmer_rc(kw & kmask, K) : (kw & kmask);
+							for (int q = 0; q < 8; ++q) { hash ^= (v >> (8 * q)) & 0xFF; hash *= 0x100000001b3ull; }
+						}
+					}
+					h->kmers_hash = hash;
+				}
+			}
+		}
+
+		// ---- pair level: a clean mate makes the pair thread (commented caller, cpp:2082-2087) ----
+		if (dirty != 3u) {
+			if (lane == 0) c_fea += 2;
+			if (want_rec && !slot_ok) { if (lane == 0) atomicOr(sv.ncand + 1, ERR_RECORD_OVERFLOW); }
+			else if (slot_ok && lane == 0) {
+				dbt_pair_record* h = reinterpret_cast<dbt_pair_record*>(rec);
+				if (!trace) {                                                   // under DBT_F_TRACE the generic candidate kernel left the full header
+					h->pair_index = sv.first_pair_index + p; h->dst0 = dst; h->fc = 0; h->rc = 0; h->nhash0 = 0; h->nhash1 = 0;
+					h->pad[0] = h->pad[1] = h->pad[2] = 0;
+#pragma unroll 1
+					for (int m = 0; m < 2; ++m) {
+						dbt_mate_record& o = h->mate[m];
+						o.si = o.ei = o.si_ = o.ei_ = o.ti = -1; o.nt = 0; o.bs = 0; o.pad = 0; o.nk = 0;
+						o.flags = (uint8_t)((((dw >> (28 + m)) & 1u) ? DBT_MF_KF : 0) | (((dw >> (30 + m)) & 1u) ? DBT_MF_RM : 0));
+					}
+				}
+				h->dst = dst; h->status = (uint8_t)DBT_ST_COUNTED;
+			}
+		}
+		if (dirty && lane == 0) { sv.thr2[atomicAdd(sv.ncand + 4, 1u)] = make_uint4(c, p, dw, dirty | (dirty != 3u ? THR2_ALNED : 0u)); ++c_items; }
+	}
+	c_probe = __reduce_add_sync(0xffffffffu, c_probe);
+	if (lane == 0) {
+		if (c_walk) atomicAdd(sv.counters + DBT_C_THR_WALK, (unsigned long long)c_walk);
+		if (c_probe) atomicAdd(sv.counters + DBT_C_THR_REFRESH, (unsigned long long)c_probe);
+		if (c_cls) atomicAdd(sv.counters + DBT_C_THR_CLS, (unsigned long long)c_cls);
+		if (c_fea) atomicAdd(sv.counters + DBT_C_NFEASIBLEREADS, (unsigned long long)c_fea);
+		if (c_inc) atomicAdd(sv.counters + DBT_C_NINC, (unsigned long long)c_inc);
+		if (c_items) atomicAdd(sv.counters + DBT_C_THR2_PAIRS, (unsigned long long)c_items);
+	}
+}
+
+}  // namespace dbt

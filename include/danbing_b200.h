@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define DBT_ABI_VERSION 3
+#define DBT_ABI_VERSION 4
 
 /* ---- error codes -------------------------------------------------------------------------- */
 #define DBT_OK            0
@@ -93,8 +93,15 @@ enum {
   DBT_C_THR_WALK,              /* k-mers of the mates handed to isThreadFeasible (one node look-up per step, cpp:1170) */
   DBT_C_THR_EC,                /* look-ups inside errorCorrection_forward/backward: expansion (cpp:907-920) + extension walks */
   DBT_C_THR_CLS,               /* valid k-mers of the edited vectors looked up in trResults (cpp:2203-2208) */
-  DBT_C_THR_REFRESH,           /* implementation detail: per-position probes this kernel actually issued */
-  DBT_N_COUNTERS = 24
+  DBT_C_THR_REFRESH,           /* implementation detail: per-position probes the two threading kernels actually issued */
+  /* measurement only: the part of the above that belongs to thread_kernel (mates with errors); the rest is thread_fast_kernel's */
+  DBT_C_THR2_PAIRS,            /* pairs with at least one mate handed to thread_kernel            */
+  DBT_C_THR2_MATES,            /* mates threaded by thread_kernel                                 */
+  DBT_C_THR2_WALK,             /* their part of DBT_C_THR_WALK                                    */
+  DBT_C_THR2_CLS,              /* thread_kernel's part of DBT_C_THR_CLS                           */
+  DBT_C_THR2_NINC,             /* thread_kernel's part of DBT_C_NINC                              */
+  DBT_C_THR2_REFRESH,          /* thread_kernel's part of DBT_C_THR_REFRESH                       */
+  DBT_N_COUNTERS = 32
 };
 
 typedef struct dbt_ctx dbt_ctx;
