@@ -563,7 +563,7 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
                       "pre-reduce trkmc / kmc / nmapread / counters; MIN over ranks of the per-rank verdict"}
         ctx.reset()
     kt = ktimes.mean(axis=0)
-    t_sub, t_cmp, t_cand, t_gen, t_thr = float(kt[1]), float(kt[2]), float(kt[3]), float(kt[4]), float(kt[5])
+    t_sub, t_cmp, t_cand, t_gen, t_thr, t_thr2 = float(kt[1]), float(kt[2]), float(kt[3]), float(kt[4]), float(kt[5]), float(kt[6])
 
     # ---- roofline of the dominant kernel (algorithmic bytes: SURVEY.md §8(d)) ----
     # one logical probe = one 32 B sector, one count increment = 64 B read-modify-write, bases at 2 bits
@@ -578,24 +578,28 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
         # counted pairs (cpp:2203-2208) and the increments.  All four are the reference algorithm's own counts.
         bytes_gen = 32 * g_h1
         bytes_fast = 32 * (cnt["nhash1"] - g_h1)
-        bytes_thr = 32 * (cnt["thr_walk"] + cnt["thr_ec"] + cnt["thr_cls"]) + 64 * cnt["ninc"]
+        # split between the two threading kernels by thread_kernel's own counters (thr2_*): thread_fast_kernel walks and
+        # classifies every error-free mate, thread_kernel the mates with errors (+ the correction look-ups)
+        bytes_thr2 = 32 * (cnt["thr2_walk"] + cnt["thr_ec"] + cnt["thr2_cls"]) + 64 * cnt["thr2_ninc"]
+        bytes_thr = 32 * (cnt["thr_walk"] + cnt["thr_ec"] + cnt["thr_cls"]) + 64 * cnt["ninc"] - bytes_thr2
     else:
         # candidate stage: kfilter probes (nhash1) + one classification probe per k-mer of pairs reaching assignTRkmc + increments,
         # split between the closed-form kernel and the generic kernel by the generic kernel's own counters
         bytes_gen = 32 * (g_h1 + g_thr * nk) + 64 * g_inc
         bytes_fast = 32 * ((cnt["nhash1"] - g_h1) + (cnt["nThreadingReads"] - g_thr) * nk) + 64 * (cnt["ninc"] - g_inc)
-        bytes_thr = 0
+        bytes_thr = bytes_thr2 = 0
     peak, peak_src = peaks()
     kern = {"subfilter_kernel": (t_sub, bytes_sub), "candidate_fast_kernel": (t_cand, bytes_fast), "candidate_kernel(generic)": (t_gen, bytes_gen)}
     if thr:
-        kern["thread_kernel"] = (t_thr, bytes_thr)
+        kern["thread_fast_kernel"] = (t_thr, bytes_thr)
+        kern["thread_kernel"] = (t_thr2, bytes_thr2)
     dom = max(kern, key=lambda n: kern[n][0])
     dom_ms, dom_bytes = kern[dom]
     ach = dom_bytes / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0
-    step_bytes = bytes_sub + bytes_fast + bytes_gen + bytes_thr
+    step_bytes = bytes_sub + bytes_fast + bytes_gen + bytes_thr + bytes_thr2
     roofline = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
                 "kernel": dom, "kernel_ms": dom_ms, "algorithmic_bytes_per_launch": dom_bytes, "peak_source": peak_src,
-                "per_kernel_ms": {"subfilter": t_sub, "compaction": t_cmp, "candidate_fast": t_cand, "candidate_generic": t_gen, "thread": t_thr,
+                "per_kernel_ms": {"subfilter": t_sub, "compaction": t_cmp, "candidate_fast": t_cand, "candidate_generic": t_gen, "thread_fast": t_thr, "thread": t_thr2,
                                   "pack(e2e upload only, 2P reads)": t_pack},
                 "per_kernel_GBps": dict({n: (bb / (ms_ / 1e3) / 1e9 if ms_ > 0 else 0.0) for n, (ms_, bb) in kern.items()},
                                         pack_kernel=(bytes_pack / (t_pack / 1e3) / 1e9 if t_pack > 0 else 0.0)),
@@ -607,11 +611,15 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
                 "step_bytes": step_bytes, "step_GBps": step_bytes / (step_ms / 1e3) / 1e9, "step_frac": step_bytes / (step_ms / 1e3) / 1e9 / peak}
     if thr:
         nthr_pairs = max(cnt["nThreadingReads"] // 2, 1)
-        roofline["thread_kernel"] = {"pairs": cnt["nThreadingReads"] // 2, "us_per_pair_per_sm_warp": None,
-                                     "probes_algorithmic_per_pair": (cnt["thr_walk"] + cnt["thr_ec"] + cnt["thr_cls"]) / nthr_pairs,
-                                     "probes_issued_per_pair": (cnt["thr_refresh"] + cnt["thr_ec"]) / nthr_pairs,
-                                     "Gprobes_per_s": (cnt["thr_refresh"] + cnt["thr_ec"]) / (t_thr / 1e3) / 1e9 if t_thr > 0 else 0.0}
-        del roofline["thread_kernel"]["us_per_pair_per_sm_warp"]
+        t_stage = t_thr + t_thr2
+        roofline["thread_stage"] = {"kernels": "thread_fast_kernel + thread_kernel (= round 1's single thread_kernel)", "ms": t_stage,
+                                    "algorithmic_bytes": bytes_thr + bytes_thr2,
+                                    "GBps": (bytes_thr + bytes_thr2) / (t_stage / 1e3) / 1e9 if t_stage > 0 else 0.0,
+                                    "frac": (bytes_thr + bytes_thr2) / (t_stage / 1e3) / 1e9 / peak if t_stage > 0 else 0.0,
+                                    "pairs": cnt["nThreadingReads"] // 2, "pairs_with_an_error_mate": cnt["thr2_pairs"], "mates_with_errors": cnt["thr2_mates"],
+                                    "probes_algorithmic_per_pair": (cnt["thr_walk"] + cnt["thr_ec"] + cnt["thr_cls"]) / nthr_pairs,
+                                    "probes_issued_per_pair": (cnt["thr_refresh"] + cnt["thr_ec"]) / nthr_pairs,
+                                    "Gprobes_per_s": (cnt["thr_refresh"] + cnt["thr_ec"]) / (t_stage / 1e3) / 1e9 if t_stage > 0 else 0.0}
     # dram bytes per launch of the dominant kernel from the committed `ncu --set full` capture of this same workload
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
@@ -633,10 +641,12 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
         # this can exceed 1 -- it is the honest denominator for HBM-resident tables (--loci 20000 and up).
         # logical = the probes the REFERENCE algorithm makes (SURVEY §8(d) unit of work); issued = the bucket fetches the kernel
         # really starts (one graph probe answers walk + classification; kfilter and assignTRkmc share one index probe)
-        logical = {"thread_kernel": cnt["thr_walk"] + cnt["thr_ec"] + cnt["thr_cls"] if thr else 0,
+        logical = {"thread_fast_kernel": (cnt["thr_walk"] - cnt["thr2_walk"]) + (cnt["thr_cls"] - cnt["thr2_cls"]) if thr else 0,
+                   "thread_kernel": cnt["thr2_walk"] + cnt["thr_ec"] + cnt["thr2_cls"] if thr else 0,
                    "candidate_fast_kernel": (cnt["nhash1"] - g_h1) + (0 if thr else (cnt["nThreadingReads"] - g_thr) * nk),
                    "subfilter_kernel": p_sub}
-        issued = {"thread_kernel": cnt["thr_refresh"] + cnt["thr_ec"] if thr else 0,
+        issued = {"thread_fast_kernel": cnt["thr_refresh"] - cnt["thr2_refresh"] if thr else 0,
+                  "thread_kernel": cnt["thr2_refresh"] + cnt["thr_ec"] if thr else 0,
                   "candidate_fast_kernel": cnt["nhash1"] - g_h1,
                   "subfilter_kernel": p_sub}
         if logical.get(dom) and dom_ms > 0:
@@ -644,7 +654,7 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
             rr["frac_of_r_rand_32B"] = rr["dominant_kernel_Gprobes_per_s"] / rr["32B_Gsectors_per_s"]
             rr["dominant_kernel_issued_Gprobes_per_s"] = issued[dom] / (dom_ms / 1e3) / 1e9
             rr["frac_of_r_rand_32B_issued"] = rr["dominant_kernel_issued_Gprobes_per_s"] / rr["32B_Gsectors_per_s"]
-        tk = {"thread_kernel": t_thr, "candidate_fast_kernel": t_cand, "subfilter_kernel": t_sub}
+        tk = {"thread_fast_kernel": t_thr, "thread_kernel": t_thr2, "candidate_fast_kernel": t_cand, "subfilter_kernel": t_sub}
         rr["per_kernel"] = {n: {"logical_Gprobes_per_s": logical[n] / (tk[n] / 1e3) / 1e9, "issued_Gprobes_per_s": issued[n] / (tk[n] / 1e3) / 1e9,
                                 "frac_logical": logical[n] / (tk[n] / 1e3) / 1e9 / rr["32B_Gsectors_per_s"],
                                 "frac_issued": issued[n] / (tk[n] / 1e3) / 1e9 / rr["32B_Gsectors_per_s"]}

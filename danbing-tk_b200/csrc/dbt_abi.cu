@@ -68,14 +68,15 @@ extern "C" void dbt_default_params(dbt_params* p) {
 // ------------------------------------------------------------------------------------------
 // context
 // ------------------------------------------------------------------------------------------
-enum { KT_PACK = 0, KT_SUBFILTER, KT_COMPACT, KT_CANDIDATE, KT_GENERIC, KT_THREAD, KT_N };   // KT_CANDIDATE = closed-form kernel, KT_GENERIC = generic kernel
+enum { KT_PACK = 0, KT_SUBFILTER, KT_COMPACT, KT_CANDIDATE, KT_GENERIC, KT_THREAD, KT_THREAD2, KT_N };   // KT_CANDIDATE = closed-form kernel, KT_GENERIC = generic kernel,
+                                                                                                   // KT_THREAD = thread_fast_kernel, KT_THREAD2 = thread_kernel (mates with errors)
 
 struct Slot {
 	bool ready = false;
 	cudaStream_t st = nullptr;
 	uint8_t* d_ascii = nullptr; uint64_t* d_offsets = nullptr;
 	uint64_t* d_packed[2] = {nullptr, nullptr}; uint16_t* d_meta[2] = {nullptr, nullptr};
-	uint32_t* d_passmask = nullptr; uint32_t* d_blocksum = nullptr; uint32_t* d_cand = nullptr; uint32_t* d_ncand = nullptr; uint32_t* d_slow = nullptr; uint4* d_thr = nullptr;
+	uint32_t* d_passmask = nullptr; uint32_t* d_blocksum = nullptr; uint32_t* d_cand = nullptr; uint32_t* d_ncand = nullptr; uint32_t* d_slow = nullptr; uint4* d_thr = nullptr; uint4* d_thr2 = nullptr;
 	uint8_t* d_records = nullptr; unsigned long long* d_counters = nullptr;
 	uint8_t* h_records = nullptr;            // pinned staging (DBT_F_TRACE, or a pageable caller buffer)
 	// record emission: emit bitmap -> ordered list -> dense copy of the records that become kam / aln records
@@ -224,7 +225,7 @@ static void free_slot(Slot& s) {
 	if (s.st) cudaStreamSynchronize(s.st);
 	cudaFree(s.d_ascii); cudaFree(s.d_offsets);
 	for (int m = 0; m < 2; ++m) { cudaFree(s.d_packed[m]); cudaFree(s.d_meta[m]); }
-	cudaFree(s.d_passmask); cudaFree(s.d_blocksum); cudaFree(s.d_cand); cudaFree(s.d_ncand); cudaFree(s.d_slow); cudaFree(s.d_thr); cudaFree(s.d_records); cudaFree(s.d_counters);
+	cudaFree(s.d_passmask); cudaFree(s.d_blocksum); cudaFree(s.d_cand); cudaFree(s.d_ncand); cudaFree(s.d_slow); cudaFree(s.d_thr); cudaFree(s.d_thr2); cudaFree(s.d_records); cudaFree(s.d_counters);
 	cudaFree(s.d_records_out); cudaFree(s.d_emitmask); cudaFree(s.d_emitsum); cudaFree(s.d_emitlist); cudaFree(s.d_nemit);
 	if (s.h_records) cudaFreeHost(s.h_records);
 	if (s.h_counters) cudaFreeHost(s.h_counters);
@@ -273,9 +274,9 @@ static int ensure_slot(dbt_ctx* c, int si) {
 	TRY(dev_alloc(&s.d_passmask, nwords, "passmask"));
 	TRY(dev_alloc(&s.d_blocksum, (nwords + COMPACT_WORDS_H - 1) / COMPACT_WORDS_H + 1, "blocksum"));
 	TRY(dev_alloc(&s.d_cand, P, "cand"));
-	TRY(dev_alloc(&s.d_ncand, 4, "ncand"));
+	TRY(dev_alloc(&s.d_ncand, 8, "ncand"));
 	TRY(dev_alloc(&s.d_slow, P, "slow list"));
-	if (rp.thr_on) { TRY(dev_alloc(&s.d_thr, P, "thread list")); }
+	if (rp.thr_on) { TRY(dev_alloc(&s.d_thr, P, "thread list")); TRY(dev_alloc(&s.d_thr2, P, "thread list 2")); }
 	TRY(dev_alloc(&s.d_counters, DBT_N_COUNTERS, "counters"));
 	const bool want_records = rp.thr_on ? (c->p.flags & (DBT_F_ALN | DBT_F_ALN_MIN | DBT_F_TRACE)) != 0 : (c->p.flags & (DBT_F_KAM | DBT_F_TRACE)) != 0;
 	if (want_records) {
@@ -543,7 +544,7 @@ extern "C" void dbt_host_free(void* p) { if (p) cudaFreeHost(p); }
 static SlotView slot_view(const dbt_ctx* c, const Slot& s) {
 	SlotView v;
 	v.packed[0] = s.d_packed[0]; v.packed[1] = s.d_packed[1]; v.meta[0] = s.d_meta[0]; v.meta[1] = s.d_meta[1];
-	v.passmask = s.d_passmask; v.blocksum = s.d_blocksum; v.cand = s.d_cand; v.ncand = s.d_ncand; v.slow = s.d_slow; v.thr = s.d_thr; v.records = s.d_records;
+	v.passmask = s.d_passmask; v.blocksum = s.d_blocksum; v.cand = s.d_cand; v.ncand = s.d_ncand; v.slow = s.d_slow; v.thr = s.d_thr; v.thr2 = s.d_thr2; v.records = s.d_records;
 	v.counters = s.d_counters; v.npairs = s.npairs; v.first_pair_index = s.first_pair_index;
 	(void)c;
 	return v;
@@ -565,7 +566,7 @@ extern "C" int dbt_upload(dbt_ctx* c, const dbt_batch* b, int slot) {
 	if (b->npairs > c->p.max_batch_pairs) return fail(DBT_E_CAPACITY, "npairs=%llu > max_batch_pairs=%u", (unsigned long long)b->npairs, c->p.max_batch_pairs);
 	s.npairs = b->npairs; s.first_pair_index = b->first_pair_index; s.processed = false; s.ev_pack = false;
 	const RunParams& rp = c->rp;
-	CU(cudaMemsetAsync(s.d_ncand, 0, 16, s.st));
+	CU(cudaMemsetAsync(s.d_ncand, 0, 32, s.st));
 	if (b->npairs) {
 		if (!b->bases) return fail(DBT_E_BADARG, "null bases");
 		if (b->layout == DBT_LAYOUT_ASCII) {
@@ -602,7 +603,7 @@ extern "C" int dbt_process(dbt_ctx* c, int slot) {
 	SlotView sv = slot_view(c, s);
 	CU(cudaMemsetAsync(s.d_counters, 0, DBT_N_COUNTERS * 8, s.st));
 	CU(cudaMemsetAsync(s.d_ncand, 0, 4, s.st));
-	CU(cudaMemsetAsync(s.d_ncand + 2, 0, 8, s.st));
+	CU(cudaMemsetAsync(s.d_ncand + 2, 0, 12, s.st));
 	if (c->rp.thr_on && (c->p.flags & DBT_F_TRACE) && s.d_records)      // blobs of pairs that never reach threading read as zeros
 		CU(cudaMemsetAsync(s.d_records, 0, (size_t)c->p.max_records * c->rp.rec_stride, s.st));
 	CU(cudaEventRecord(s.ev[1], s.st));
@@ -613,8 +614,9 @@ extern "C" int dbt_process(dbt_ctx* c, int slot) {
 	CU(launch_candidate(s.st, c->B, c->cand_grid_fast, c->cand_grid, c->ix, c->rp, sv, s.ev[4]));
 	if (s.npairs) c->launches += ((c->p.flags & DBT_F_TRACE) || c->rp.nk_max > 255) ? 1 : 2;   // generic kernel alone, or closed-form + generic
 	CU(cudaEventRecord(s.ev[5], s.st));
-	if (c->rp.thr_on) { CU(launch_thread(s.st, c->B, c->nsm, c->ix, c->rp, sv)); if (s.npairs) ++c->launches; }
-	CU(cudaEventRecord(s.ev[6], s.st));
+	if (c->rp.thr_on) { CU(launch_thread(s.st, c->B, c->nsm, c->ix, c->rp, sv, s.ev[6])); if (s.npairs) c->launches += 2; }
+	else CU(cudaEventRecord(s.ev[6], s.st));
+	CU(cudaEventRecord(s.ev[7], s.st));
 	s.processed = true; s.ev_proc = true;
 	return DBT_OK;
 }
@@ -768,6 +770,7 @@ extern "C" int dbt_kernel_times(dbt_ctx* c, int slot, float ms[8], uint32_t laun
 		CU(cudaEventElapsedTime(&ms[KT_CANDIDATE], s.ev[3], s.ev[4])); launches[KT_CANDIDATE] = all ? 0 : 1;
 		CU(cudaEventElapsedTime(&ms[KT_GENERIC], s.ev[4], s.ev[5])); launches[KT_GENERIC] = 1;
 		CU(cudaEventElapsedTime(&ms[KT_THREAD], s.ev[5], s.ev[6])); launches[KT_THREAD] = c->rp.thr_on ? 1 : 0;
+		CU(cudaEventElapsedTime(&ms[KT_THREAD2], s.ev[6], s.ev[7])); launches[KT_THREAD2] = c->rp.thr_on ? 1 : 0;
 	}
 	return DBT_OK;
 }

@@ -12,7 +12,7 @@ cudaError_t launch_candidate(cudaStream_t st, int B, unsigned grid_fast, unsigne
 cudaError_t launch_insert(cudaStream_t st, int B, Table t, const uint64_t* keys, const uint32_t* vals, uint64_t n, uint32_t* err);
 cudaError_t launch_fill_aux(cudaStream_t st, int B, Table t, const uint32_t* vv, uint32_t* vv_aux, const uint64_t* kmers,
                             const uint32_t* locus_of, uint64_t n, uint32_t cls, uint32_t* err);
-cudaError_t launch_thread(cudaStream_t st, int B, int nsm, const DevIndex& ix, const RunParams& rp, const SlotView& sv);
+cudaError_t launch_thread(cudaStream_t st, int B, int nsm, const DevIndex& ix, const RunParams& rp, const SlotView& sv, cudaEvent_t mid);   // thread_fast_kernel, event `mid`, thread_kernel
 // pass 0/1: graph nodes (canonical / reverse-complement orientation), pass 2: TR k-mers (masks == nullptr), pass 3: verify
 cudaError_t launch_graph_build(cudaStream_t st, int B, Table t, const uint64_t* kmers, const uint8_t* masks, const uint32_t* locus_of,
                                uint64_t n, uint32_t k, int pass, uint32_t* err);

@@ -96,10 +96,10 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 
 #pragma unroll 1
 		for (int m = 0; m < 2; ++m) {
-			const uint32_t len = sv.meta[m][p] & META_LENMASK;
+			const uint32_t len = (m ? sv.meta[1] : sv.meta[0])[p] & META_LENMASK;           // (no dynamic index into the parameter struct: it would be copied to local memory)
 			const int nkm = (int)len - (int)K + 1;
 			__syncwarp();
-			for (uint32_t q = lane; q < W64 && q < 2 * MAXJ + 6; q += 32) W.pk[q] = sv.packed[m][(uint64_t)p * W64 + q];
+			for (uint32_t q = lane; q < W64 && q < 2 * MAXJ + 6; q += 32) W.pk[q] = (m ? sv.packed[1] : sv.packed[0])[(uint64_t)p * W64 + q];
 			__syncwarp();
 			if (nkm < 1 || nkm > MAXJ * 32 || W64 > 2 * MAXJ + 6) { dirty |= 1u << m; continue; }   // thread_kernel handles (and reports) the odd ones
 			const uint32_t* mk32 = reinterpret_cast<const uint32_t*>(W.pk + WB);

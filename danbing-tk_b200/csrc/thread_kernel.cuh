@@ -1,8 +1,10 @@
-// thread_kernel: restored graph threading (decision D1 of §8(c)).
-// One warp per read pair that passed the locus vote and the QC gate; both mates are threaded through the de Bruijn
-// graph of the assigned locus (isThreadFeasible, cpp:1114-1260), the pair counts if either mate threads, and then
-// every k-mer of BOTH edited k-mer vectors that is a TR k-mer of the locus is incremented (commented caller
-// cpp:2072-2088 / 2195-2209).  "cpp" = src/aQueryFasta_thread.cpp of the reference.
+// thread_kernel: restored graph threading (decision D1 of §8(c)) for the mates that carry an
+// error.  thread_fast_kernel (thread_fast.cuh) has already finished every error-free mate of the pairs that passed the locus
+// vote and the QC gate; its work list sv.thr2 names, per pair, the mates left over and whether the other mate threaded.
+// One warp per work item: the listed mates are threaded through the de Bruijn graph of the assigned locus
+// (isThreadFeasible, cpp:1114-1260), the pair counts if either mate threads, and then every k-mer of the edited k-mer
+// vectors that is a TR k-mer of the locus is incremented (commented caller cpp:2072-2088 / 2195-2209; the clean mate's
+// share was counted by thread_fast_kernel).  "cpp" = src/aQueryFasta_thread.cpp of the reference.
 //
 // How the sequential walk is made parallel.  The reference advances one k-mer at a time, looking the CURRENT node's
 // out-edge mask up and comparing its successors with the next read k-mer (cpp:1167-1180).  Whenever that step is
@@ -733,7 +735,7 @@ __device__ __noinline__ void thread_mate(const Table gt, uint32_t locus, uint32_
 	const uint64_t maxnskip = nkm0 >= thread_cth ? nkm0 - thread_cth : 0;
 	if (anyvalid) {
 		thr_refresh<B, MAXJ>(gt, locus, K, rmask, W, m, S.nkm, 0, S.nkm, lane);
-		if (lane == 0) W.cnt[0] += (uint32_t)S.nkm;
+		if (lane == 0) W.cnt[0] += (uint32_t)S.nkm;                       // DBT_C_THR2_WALK (the walk itself was counted by thread_fast_kernel)
 		// Error-free mate (three quarters of them): the first k-mer is a node and every later k-mer matches an out-edge of its
 		// predecessor.  The reference then anchors at 0 (cpp:1129, find_anchor marks es[0..k) '='), walks the whole read through
 		// cpp:1167-1180 (tr[i] = '=' / '.', es[i+k-1] = '=') and returns 1 (cpp:1259: no skip, no correction): every CIGAR entry
@@ -877,30 +879,33 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 	ThreadWarp<MAXJ, B>& W = reinterpret_cast<ThreadWarp<MAXJ, B>*>(thr_smem)[threadIdx.x >> 5];
 	const int lane = threadIdx.x & 31;
 	const uint32_t gwarp = blockIdx.x * THR_WARPS + (threadIdx.x >> 5), nwarps = gridDim.x * THR_WARPS;
-	const uint32_t nwork = sv.ncand[3];
+	const uint32_t nwork = sv.ncand[4];
 	const bool trace = (rp.flags & DBT_F_TRACE) != 0;
 	const bool aln_all = (rp.flags & DBT_F_ALN) && !(rp.flags & DBT_F_ALN_MIN), aln_min = (rp.flags & DBT_F_ALN_MIN) != 0;
 	const bool want_rec = trace || aln_all || aln_min;
 	const uint32_t W64 = rp.lay.W64;
-	uint32_t c_fea = 0, c_inc = 0, c_cls = 0;
+	uint32_t c_fea = 0, c_inc = 0, c_cls = 0, c_mates = 0;
 	if (lane < 3) W.cnt[lane] = 0;                                     // walk, ec, refresh probes (measurement)
 	__syncwarp();
 
-	uint4 item = gwarp < nwork ? sv.thr[gwarp] : make_uint4(0, 0, 0, 0);
+	uint4 item = gwarp < nwork ? sv.thr2[gwarp] : make_uint4(0, 0, 0, 0);
 #pragma unroll 1
 	for (uint32_t t = gwarp; t < nwork; t += nwarps) {
-		const uint32_t c = item.x, p = item.y, dw = item.z;
-		if (t + nwarps < nwork) item = sv.thr[t + nwarps];              // next pair's work item: in flight while this pair is threaded
+		const uint32_t c = item.x, p = item.y, dw = item.z, mw = item.w;
+		if (t + nwarps < nwork) item = sv.thr2[t + nwarps];             // next work item: in flight while this one is threaded
 		const uint32_t dst = dw & THR_DST_MASK;
+		const bool pre = (mw & THR2_ALNED) != 0;                           // the other mate threaded cleanly: the pair counts whatever happens here
 		const uint64_t slot = trace ? (uint64_t)p : (uint64_t)c;
 		const bool slot_ok = want_rec && (trace || slot < rp.max_records);
 		uint8_t* rec = sv.records + slot * rp.rec_stride;
 		MateResult* const r = W.res;
-		uint32_t nvalid = 0;                                               // valid k-mers of both edited vectors (lane 0)
+		uint32_t nvalid = 0;                                               // valid k-mers of the edited vectors threaded here (lane 0)
 #pragma unroll 1
 		for (int m = 0; m < 2; ++m) {
-			const uint32_t len = sv.meta[m][p] & META_LENMASK;
-			thread_mate<B, MAXJ>(ix.gtable, dst, rp.k, rp.lay.WB, rp.thread_cth, rp.max_ncorrection, rp.correction != 0, W, m, sv.packed[m] + (uint64_t)p * W64, len, lane);
+			if (!((mw >> m) & 1u)) { r[m].alned = 0; r[m].err = 0; r[m].nkm = 0; r[m].nes = 0; r[m].ntr = 0; r[m].clean = 0; __syncwarp(); continue; }
+			if (lane == 0) ++c_mates;
+			const uint32_t len = (m ? sv.meta[1] : sv.meta[0])[p] & META_LENMASK;       // (no dynamic index into the parameter struct)
+			thread_mate<B, MAXJ>(ix.gtable, dst, rp.k, rp.lay.WB, rp.thread_cth, rp.max_ncorrection, rp.correction != 0, W, m, (m ? sv.packed[1] : sv.packed[0]) + (uint64_t)p * W64, len, lane);
 			if (slot_ok) {                                              // sam_t.r1 / r2 -> dbt_aln_mate blob
 				uint8_t* b = rec + sizeof(dbt_pair_record) + (size_t)m * rp.aln_stride;
 				uint8_t* es = b + sizeof(dbt_aln_mate); uint8_t* trb = es + rp.es_cap;
@@ -947,12 +952,13 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 			}
 			__syncwarp();
 		}
-		const bool alned = r[0].alned || r[1].alned;                       // commented caller, cpp:2082-2087
+		const bool alned = pre || r[0].alned || r[1].alned;                // commented caller, cpp:2082-2087
 		if (alned) {
-			if (lane == 0) c_fea += 2;
+			if (lane == 0 && !pre) c_fea += 2;                                // (a pair with a clean mate was counted as feasible by thread_fast_kernel)
 			uint32_t inc_sum = 0;
 #pragma unroll 1
-			for (int m = 0; m < 2; ++m) {                                     // D1: every TR k-mer of both edited vectors, cpp:2203-2208
+			for (int m = 0; m < 2; ++m) {                                     // D1: every TR k-mer of the edited vectors, cpp:2203-2208
+				if (!((mw >> m) & 1u)) continue;
 #pragma unroll 1
 				for (int j = 0; j * 32 < r[m].nkm; ++j) {
 					const int i = j * 32 + lane;
@@ -969,6 +975,7 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 			}
 			if (lane == 0) { c_inc += inc_sum; c_cls += nvalid; }
 		}
+		if (pre) continue;                                                 // header, status and the overflow flag were thread_fast_kernel's
 		const uint32_t status = alned ? DBT_ST_COUNTED : DBT_ST_THREAD_FAILED;
 		const uint32_t fdst = alned ? dst : (uint32_t)ix.nloci;
 		if (want_rec && !slot_ok) { if (lane == 0 && (aln_all || alned)) atomicOr(sv.ncand + 1, ERR_RECORD_OVERFLOW); }
@@ -989,12 +996,13 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 	}
 	__syncwarp();
 	if (lane == 0) {
-		if (W.cnt[0]) atomicAdd(sv.counters + DBT_C_THR_WALK, (unsigned long long)W.cnt[0]);
+		if (W.cnt[0]) atomicAdd(sv.counters + DBT_C_THR2_WALK, (unsigned long long)W.cnt[0]);
 		if (W.cnt[1]) atomicAdd(sv.counters + DBT_C_THR_EC, (unsigned long long)W.cnt[1]);
-		if (W.cnt[2]) atomicAdd(sv.counters + DBT_C_THR_REFRESH, (unsigned long long)W.cnt[2]);
-		if (c_cls) atomicAdd(sv.counters + DBT_C_THR_CLS, (unsigned long long)c_cls);
+		if (W.cnt[2]) { atomicAdd(sv.counters + DBT_C_THR_REFRESH, (unsigned long long)W.cnt[2]); atomicAdd(sv.counters + DBT_C_THR2_REFRESH, (unsigned long long)W.cnt[2]); }
+		if (c_cls) { atomicAdd(sv.counters + DBT_C_THR_CLS, (unsigned long long)c_cls); atomicAdd(sv.counters + DBT_C_THR2_CLS, (unsigned long long)c_cls); }
 		if (c_fea) atomicAdd(sv.counters + DBT_C_NFEASIBLEREADS, (unsigned long long)c_fea);
-		if (c_inc) atomicAdd(sv.counters + DBT_C_NINC, (unsigned long long)c_inc);
+		if (c_inc) { atomicAdd(sv.counters + DBT_C_NINC, (unsigned long long)c_inc); atomicAdd(sv.counters + DBT_C_THR2_NINC, (unsigned long long)c_inc); }
+		if (c_mates) atomicAdd(sv.counters + DBT_C_THR2_MATES, (unsigned long long)c_mates);
 	}
 }
 

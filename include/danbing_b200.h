@@ -276,6 +276,8 @@ int  dbt_allreduce(dbt_ctx*);
 /* ---- measurement helpers (CUDA events on the context's own streams) ------------------------- */
 int  dbt_timer_start(dbt_ctx*, int slot);
 int  dbt_timer_stop (dbt_ctx*, int slot, float* ms);          /* synchronises the slot           */
+/* [0] pack (the slot's last ASCII upload) [1] subfilter [2] compaction [3] candidate_fast [4] candidate (generic)
+   [5] thread_fast [6] thread (mates with errors); the rest 0 */
 int  dbt_kernel_times(dbt_ctx*, int slot, float ms[8], uint32_t launches[8]); /* last dbt_process */
 uint64_t dbt_launch_count(const dbt_ctx*);                    /* kernels launched since create   */
 /* after dbt_wait(slot): [0] candidate pairs, [1] pairs the closed-form kernel left to the generic one,

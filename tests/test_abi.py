@@ -22,7 +22,7 @@ def test_header_and_python_mirror_agree():
 def test_library_exports_every_declared_symbol(lib):
     for s in declared_symbols():
         assert hasattr(lib, s), s
-    assert lib.dbt_abi_version() == 3
+    assert lib.dbt_abi_version() == 4
 
 
 def test_struct_sizes():
