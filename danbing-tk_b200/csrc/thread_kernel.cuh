@@ -891,6 +891,9 @@ __global__ void __launch_bounds__(THR_WARPS * 32, THR_MINBLOCKS) thread_kernel(D
 	uint4 item = gwarp < nwork ? sv.thr2[gwarp] : make_uint4(0, 0, 0, 0);
 #pragma unroll 1
 	for (uint32_t t = gwarp; t < nwork; t += nwarps) {
+#ifdef THR_BLOCKSYNC
+		__syncthreads();                                                   // experiment: the warps of a block start every work item together (instruction-cache locality)
+#endif
 		const uint32_t c = item.x, p = item.y, dw = item.z, mw = item.w;
 		if (t + nwarps < nwork) item = sv.thr2[t + nwarps];             // next work item: in flight while this one is threaded
 		const uint32_t dst = dw & THR_DST_MASK;

@@ -10,7 +10,7 @@
 #include <string>
 #include <vector>
 #include "options.hpp"
-#include "rpgg_files.hpp"
+#include "serialize.hpp"
 #include "fastx_reader.hpp"
 #include "kam_writer.hpp"
 
@@ -37,6 +37,20 @@ static int cmd_index(const std::string& pref, const std::string& qcfn) {
 	if (!load_rpgg(pref, pref + ".tr.kmers", qcfn, 4, g, err)) { fprintf(stderr, "%s\n", err.c_str()); return 1; }
 	printf("nloci %llu nk_dbi %zu nvv %zu ntr %zu nfl %zu nqc %zu\n", (unsigned long long)g.nloci, g.dbi_keys.size(), g.vv.size(),
 	       g.tr_kmers.size(), g.fl_kmers.size(), g.qc.size());
+	return 0;
+}
+
+// order-independent digest of the loaded index (legacy-container tests: the same index must come out of either file set)
+static int cmd_index_sum(const std::string& pref) {
+	Rpgg g; std::string err;
+	if (!load_rpgg(pref, pref + ".tr.kmers", "", 4, g, err)) { fprintf(stderr, "%s\n", err.c_str()); return 1; }
+	uint64_t keysum = 0, kvsum = 0, vvsum = 0, flsum = 0;
+	for (size_t i = 0; i < g.dbi_keys.size(); ++i) { keysum += g.dbi_keys[i]; kvsum += g.dbi_keys[i] * (uint64_t)(g.dbi_vals[i] + 1u); }
+	for (size_t i = 0; i < g.vv.size(); ++i) vvsum = vvsum * 1000003u + g.vv[i];
+	size_t o = 0;
+	for (size_t l = 0; l < g.fl_n.size(); ++l) for (uint64_t i = 0; i < g.fl_n[l]; ++i) flsum += g.fl_kmers[o++] * (uint64_t)(l + 1);
+	printf("nloci %llu nk_dbi %zu nvv %zu ntr %zu nfl %zu keysum %llu kvsum %llu vvsum %llu flsum %llu\n", (unsigned long long)g.nloci, g.dbi_keys.size(),
+	       g.vv.size(), g.tr_kmers.size(), g.fl_kmers.size(), (unsigned long long)keysum, (unsigned long long)kvsum, (unsigned long long)vvsum, (unsigned long long)flsum);
 	return 0;
 }
 
@@ -108,6 +122,7 @@ int main(int argc, char** argv) {
 	const std::string cmd = argv[1];
 	if (cmd == "tr-order" && argc == 4) return cmd_tr_order(argv[2], argv[3]);
 	if (cmd == "index" && argc >= 3) return cmd_index(argv[2], argc > 3 ? argv[3] : "");
+	if (cmd == "index-sum" && argc == 3) return cmd_index_sum(argv[2]);
 	if (cmd == "pair" && argc == 7) return cmd_pair(argv[2], atoi(argv[3]) != 0, strtoull(argv[4], nullptr, 10), strtoull(argv[5], nullptr, 10), strtoull(argv[6], nullptr, 10));
 	if (cmd == "kam" && argc == 8) return cmd_kam(argv[2], (uint32_t)atoi(argv[3]), (uint32_t)atoi(argv[4]), argv[5], atoi(argv[6]) != 0, strtoull(argv[7], nullptr, 10));
 	if (cmd == "args") return cmd_args(argc - 1, argv + 1);

@@ -29,7 +29,7 @@
 
 #include "../../include/danbing_b200.h"
 #include "options.hpp"
-#include "rpgg_files.hpp"
+#include "serialize.hpp"
 #include "fastx_reader.hpp"
 #include "kam_writer.hpp"
 #include "aln_writer.hpp"

@@ -250,15 +250,6 @@ inline bool read_qc(const std::string& fn, uint64_t nloci, std::vector<uint8_t>&
 	return true;
 }
 
-inline bool load_rpgg(const std::string& pref, const std::string& trFname, const std::string& qcFn, int nthreads, Rpgg& g, std::string& err) {
-	if (!read_tr_kmers_ordered(trFname, g, nthreads, err)) return false;
-	if (!read_dbi(pref + ".kmers.dbi", g, err)) return false;
-	if (!read_kdb(pref + ".fl.kdb", g.fl_n, g.fl_kmers, err)) return false;
-	if (g.fl_n.size() != g.nloci) { err = pref + ".fl.kdb: " + std::to_string(g.fl_n.size()) + " loci, " + trFname + " has " + std::to_string(g.nloci); return false; }
-	if (!qcFn.empty() && !read_qc(qcFn, g.nloci, g.qc, err)) return false;
-	return true;
-}
-
 // ---- writers ----
 inline bool write_trkmc_ar(const std::string& pref, const std::vector<uint64_t>& counts, std::string& err) {
 	const std::string fn = pref + ".trkmc.ar";

@@ -24,7 +24,7 @@ for ln in lines:
     m = re.search(r'//## File "([^"]+)", line (\d+)', ln)
     if m: curline = os.path.basename(m.group(1)) + ":" + m.group(2); continue
     if re.match(r"\s+/\*[0-9a-f]{4,}\*/", ln): seq.append((curfn,curline))
-raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"] + (["-k", "regex:" + sys.argv[4]] if len(sys.argv) > 4 else []), capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hi = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
 h = rows[hi]
