@@ -53,6 +53,18 @@ class Batch(C.Structure):
                 ("bases", u8p), ("offsets", u64p)]
 
 
+class RawInfo(C.Structure):
+    _fields_ = [(n, C.c_uint32) for n in ("nlines", "nrecords", "npairs", "nsingle", "nshort_pairs", "flags", "max_read_len", "max_record_bytes")]
+
+
+class RawBatch(C.Structure):
+    _fields_ = [("first_pair_index", C.c_uint64), ("text", u8p), ("nbytes", C.c_uint64), ("is_fastq", C.c_int32), ("min_read_len", C.c_uint32),
+                ("pair_offset", u32p), ("pair_hash", u64p), ("single_offset", u32p), ("single_cap", C.c_uint32)]
+
+
+RAW_SLOWPATH, RAW_OVERFLOW = 1, 2
+
+
 class BatchResult(C.Structure):
     _fields_ = [("n_records", C.c_uint64), ("capacity", C.c_uint64), ("records", u8p),
                 ("counters", C.c_uint64 * DBT_N_COUNTERS)]
@@ -165,6 +177,10 @@ def load_library(path=LIB_PATH):
     L.dbt_last_error.restype = C.c_char_p
     L.dbt_load_index.argtypes = [ctxp, C.POINTER(Index)]
     L.dbt_upload.argtypes = [ctxp, C.POINTER(Batch), C.c_int]
+    L.dbt_upload_raw.argtypes = [ctxp, C.POINTER(RawBatch), C.POINTER(RawInfo), C.c_int]
+    L.dbt_title_hash.argtypes = [C.c_char_p, C.c_size_t]
+    L.dbt_title_hash.restype = C.c_uint64
+    L.dbt_raw_times.argtypes = [ctxp, C.c_int, C.POINTER(C.c_float)]
     L.dbt_process.argtypes = [ctxp, C.c_int]
     L.dbt_fetch.argtypes = [ctxp, C.POINTER(BatchResult), C.c_int]
     L.dbt_submit.argtypes = [ctxp, C.POINTER(Batch), C.POINTER(BatchResult), C.c_int]
@@ -196,7 +212,7 @@ def load_library(path=LIB_PATH):
     return L
 
 
-ABI_SYMBOLS = ["dbt_abi_version", "dbt_device_count", "dbt_default_params", "dbt_create", "dbt_destroy",
+ABI_SYMBOLS = ["dbt_upload_raw", "dbt_title_hash", "dbt_raw_times", "dbt_abi_version", "dbt_device_count", "dbt_default_params", "dbt_create", "dbt_destroy",
                "dbt_strerror", "dbt_last_error", "dbt_load_index", "dbt_upload", "dbt_process", "dbt_fetch",
                "dbt_submit", "dbt_wait", "dbt_download", "dbt_reset_counts", "dbt_nk_tr", "dbt_nloci",
                "dbt_record_stride", "dbt_record_as_stride", "dbt_record_aln_stride", "dbt_record_es_cap", "dbt_nccl_unique_id", "dbt_comm_init", "dbt_allreduce",
@@ -288,6 +304,32 @@ class Context:
         dt = aln_record_dtype(self.es_cap, self.aln_stride - 16 - self.es_cap) if self.threading else record_dtype(self.as_stride)
         recs = rec[: n * self.stride].view(dt)
         return recs, np.array(list(r.counters), dtype=np.uint64)
+
+    def run_raw(self, text, is_fastq, min_read_len, first_pair_index=0, slot=0, single_cap=1 << 16):
+        """dbt_upload_raw + process + fetch + wait on raw FASTA/FASTQ text (bytes).
+        -> (info dict, pair_offset, pair_hash, single_offset, records, counters); records None when info['flags'] != 0."""
+        t = np.frombuffer(text, dtype=np.uint8)
+        P = int(self.params.max_batch_pairs)
+        po, ph, so = np.zeros(P, "<u4"), np.zeros(P, "<u8"), np.zeros(single_cap, "<u4")
+        b = RawBatch()
+        b.first_pair_index, b.text, b.nbytes, b.is_fastq, b.min_read_len = first_pair_index, ptr(t, u8p), len(t), int(is_fastq), min_read_len
+        b.pair_offset, b.pair_hash, b.single_offset, b.single_cap = ptr(po, u32p), ptr(ph, u64p), ptr(so, u32p), single_cap
+        info = RawInfo()
+        check(self.L, self.L.dbt_upload_raw(self.h, C.byref(b), C.byref(info), slot), "dbt_upload_raw")
+        d = {n: int(getattr(info, n)) for n, _ in RawInfo._fields_}
+        if d["flags"]:
+            return d, None, None, None, None, None
+        n = d["npairs"]
+        rec = np.zeros(max(n, 1) * self.stride, dtype=np.uint8)
+        r = BatchResult()
+        r.capacity = n
+        r.records = ptr(rec, u8p)
+        check(self.L, self.L.dbt_process(self.h, slot), "dbt_process")
+        check(self.L, self.L.dbt_fetch(self.h, C.byref(r), slot), "dbt_fetch")
+        check(self.L, self.L.dbt_wait(self.h, slot), "dbt_wait")
+        dt = aln_record_dtype(self.es_cap, self.aln_stride - 16 - self.es_cap) if self.threading else record_dtype(self.as_stride)
+        recs = rec[: int(r.n_records) * self.stride].view(dt)
+        return d, po[:n].copy(), ph[:n].copy(), so[:d["nsingle"]].copy(), recs, np.array(list(r.counters), dtype=np.uint64)
 
     def download(self):
         trkmc = np.zeros(max(self.nk_tr, 1), dtype=np.uint64)

@@ -90,6 +90,16 @@ struct Slot {
 	cudaEvent_t ev[KT_N + 1] = {};
 	cudaEvent_t t0 = nullptr, t1 = nullptr, evp0 = nullptr, evp1 = nullptr;   // evp0/evp1 bracket pack_kernel (dbt_upload, ASCII layout)
 	bool ev_pack = false, ev_proc = false;
+	// raw FASTA/FASTQ ingestion (dbt_upload_raw): device text + splitter buffers, grown on demand
+	uint8_t* d_raw = nullptr; uint64_t raw_cap = 0;
+	uint32_t *d_nlmask = nullptr, *d_rblocksum = nullptr, *d_nl = nullptr, *d_rhdr = nullptr, *d_tlen = nullptr, *d_slen = nullptr;
+	uint64_t* d_rhash = nullptr; uint8_t* d_eq = nullptr;
+	uint32_t *d_pairmask = nullptr, *d_singlemask = nullptr, *d_pairlist = nullptr, *d_singlelist = nullptr, *d_pairoff = nullptr, *d_singleoff = nullptr;
+	uint64_t *d_rstart = nullptr, *d_rend = nullptr, *d_pairhash = nullptr;
+	uint32_t raw_max_lines = 0, raw_max_recs = 0, raw_max_single = 0;
+	uint32_t* h_rhdr = nullptr;              // pinned: dbt_raw_info
+	cudaEvent_t evr0 = nullptr, evr1 = nullptr;
+	bool ev_raw = false;
 };
 
 struct Id128 { char b[128]; };       // ncclUniqueId is passed BY VALUE to ncclCommInitRank
@@ -227,6 +237,12 @@ static void free_slot(Slot& s) {
 	for (int m = 0; m < 2; ++m) { cudaFree(s.d_packed[m]); cudaFree(s.d_meta[m]); }
 	cudaFree(s.d_passmask); cudaFree(s.d_blocksum); cudaFree(s.d_cand); cudaFree(s.d_ncand); cudaFree(s.d_slow); cudaFree(s.d_thr); cudaFree(s.d_thr2); cudaFree(s.d_records); cudaFree(s.d_counters);
 	cudaFree(s.d_records_out); cudaFree(s.d_emitmask); cudaFree(s.d_emitsum); cudaFree(s.d_emitlist); cudaFree(s.d_nemit);
+	cudaFree(s.d_raw); cudaFree(s.d_nlmask); cudaFree(s.d_rblocksum); cudaFree(s.d_nl); cudaFree(s.d_rhdr); cudaFree(s.d_tlen); cudaFree(s.d_slen);
+	cudaFree(s.d_rhash); cudaFree(s.d_eq); cudaFree(s.d_pairmask); cudaFree(s.d_singlemask); cudaFree(s.d_pairlist); cudaFree(s.d_singlelist);
+	cudaFree(s.d_pairoff); cudaFree(s.d_singleoff); cudaFree(s.d_rstart); cudaFree(s.d_rend); cudaFree(s.d_pairhash);
+	if (s.h_rhdr) cudaFreeHost(s.h_rhdr);
+	if (s.evr0) cudaEventDestroy(s.evr0);
+	if (s.evr1) cudaEventDestroy(s.evr1);
 	if (s.h_records) cudaFreeHost(s.h_records);
 	if (s.h_counters) cudaFreeHost(s.h_counters);
 	for (auto& e : s.ev) if (e) cudaEventDestroy(e);
@@ -577,7 +593,7 @@ extern "C" int dbt_upload(dbt_ctx* c, const dbt_batch* b, int slot) {
 			CU(cudaMemcpyAsync(s.d_offsets, b->offsets, (2 * b->npairs + 1) * 8, cudaMemcpyHostToDevice, s.st));
 			// offsets are used relative to bases: shift by offsets[0] inside the kernel via pointer arithmetic
 			CU(cudaEventRecord(s.evp0, s.st));
-			CU(launch_pack(s.st, s.d_ascii - b->offsets[0], s.d_offsets, b->npairs, rp, s.d_packed[0], s.d_packed[1], s.d_meta[0], s.d_meta[1], s.d_ncand + 1)); ++c->launches;
+			CU(launch_pack(s.st, s.d_ascii - b->offsets[0], s.d_offsets, s.d_offsets + 1, b->npairs, rp, 0, s.d_packed[0], s.d_packed[1], s.d_meta[0], s.d_meta[1], s.d_ncand + 1)); ++c->launches;
 			CU(cudaEventRecord(s.evp1, s.st));
 			s.ev_pack = true;
 		} else if (b->layout == DBT_LAYOUT_PACKED) {
@@ -592,6 +608,108 @@ extern "C" int dbt_upload(dbt_ctx* c, const dbt_batch* b, int slot) {
 		} else return fail(DBT_E_BADARG, "unknown layout %d", b->layout);
 	}
 	s.uploaded = true;
+	return DBT_OK;
+}
+
+// ---- raw FASTA/FASTQ text: split into records and pair neighbours on the device (fastx.cu), then pack ----
+static int ensure_raw(dbt_ctx* c, Slot& s, uint64_t nbytes) {
+	if (!s.h_rhdr) {
+		CU(cudaHostAlloc((void**)&s.h_rhdr, 64, cudaHostAllocDefault));
+		CU(cudaEventCreate(&s.evr0)); CU(cudaEventCreate(&s.evr1));
+		TRY(dev_alloc(&s.d_rhdr, 16, "raw header"));
+		const uint64_t P = c->p.max_batch_pairs;
+		TRY(dev_alloc(&s.d_rstart, 2 * P, "raw read starts")); TRY(dev_alloc(&s.d_rend, 2 * P, "raw read ends"));
+		TRY(dev_alloc(&s.d_pairoff, P, "raw pair offsets")); TRY(dev_alloc(&s.d_pairhash, P, "raw pair hashes"));
+		s.raw_max_single = (uint32_t)std::min<uint64_t>(std::max<uint64_t>(P / 8, 1024), 1u << 22);
+		TRY(dev_alloc(&s.d_singleoff, s.raw_max_single, "raw singleton offsets"));
+	}
+	if (nbytes <= s.raw_cap) return DBT_OK;
+	CU(cudaStreamSynchronize(s.st));
+	cudaFree(s.d_raw); cudaFree(s.d_nlmask); cudaFree(s.d_rblocksum); cudaFree(s.d_nl); cudaFree(s.d_tlen); cudaFree(s.d_slen); cudaFree(s.d_rhash); cudaFree(s.d_eq);
+	cudaFree(s.d_pairmask); cudaFree(s.d_singlemask); cudaFree(s.d_pairlist); cudaFree(s.d_singlelist);
+	s.d_raw = nullptr; s.d_nlmask = s.d_rblocksum = s.d_nl = s.d_tlen = s.d_slen = s.d_pairmask = s.d_singlemask = s.d_pairlist = s.d_singlelist = nullptr;
+	s.d_rhash = nullptr; s.d_eq = nullptr; s.raw_cap = 0;
+	const uint64_t cap = (std::max<uint64_t>(nbytes + nbytes / 8, 1 << 20) + 31) & ~31ull;
+	// a record is at least two lines; lines of real read files are tens of bytes: room for one line per 8 bytes, one record per 16
+	const uint64_t max_lines = cap / 8, max_recs = cap / 16;
+	TRY(dev_alloc(&s.d_raw, cap + 64, "raw text"));
+	TRY(dev_alloc(&s.d_nlmask, cap / 32 + 8, "newline bitmap"));
+	TRY(dev_alloc(&s.d_rblocksum, cap / 32 / COMPACT_WORDS_H + 8, "raw compaction scratch"));
+	TRY(dev_alloc(&s.d_nl, max_lines + 8, "newline offsets"));
+	TRY(dev_alloc(&s.d_rhash, max_recs + 8, "record hashes")); TRY(dev_alloc(&s.d_tlen, max_recs + 8, "title lengths")); TRY(dev_alloc(&s.d_slen, max_recs + 8, "sequence lengths"));
+	TRY(dev_alloc(&s.d_eq, max_recs + 8, "record equality"));
+	TRY(dev_alloc(&s.d_pairmask, max_recs / 32 + 8, "pair bitmap")); TRY(dev_alloc(&s.d_singlemask, max_recs / 32 + 8, "singleton bitmap"));
+	TRY(dev_alloc(&s.d_pairlist, max_recs + 8, "pair list")); TRY(dev_alloc(&s.d_singlelist, max_recs + 8, "singleton list"));
+	s.raw_cap = cap; s.raw_max_lines = (uint32_t)max_lines; s.raw_max_recs = (uint32_t)max_recs;
+	return DBT_OK;
+}
+
+extern "C" uint64_t dbt_title_hash(const uint8_t* t, size_t len) {
+	if (len >= 2 && t[len - 2] == '/' && (t[len - 1] == '1' || t[len - 1] == '2')) len -= 2;
+	uint64_t h = 0xcbf29ce484222325ull;
+	for (size_t i = 0; i < len; ++i) { h ^= t[i]; h *= 0x100000001b3ull; }
+	return h;
+}
+
+extern "C" int dbt_upload_raw(dbt_ctx* c, const dbt_raw_batch* b, dbt_raw_info* info, int slot) {
+	TRY(check_slot(c, slot));
+	if (!b || !info) return fail(DBT_E_BADARG, "null argument");
+	Slot& s = c->slot[slot];
+	if (s.fetch_pending) return fail(DBT_E_STATE, "slot %d has an unfinished fetch; call dbt_wait", slot);
+	memset(info, 0, sizeof *info);
+	s.uploaded = false; s.processed = false; s.ev_pack = false; s.ev_raw = false; s.npairs = 0; s.first_pair_index = b->first_pair_index;
+	if (b->nbytes >= (1ull << 32) - 64) return fail(DBT_E_CAPACITY, "raw text of %llu bytes: a batch must stay below 4 GiB", (unsigned long long)b->nbytes);
+	if (b->nbytes && (!b->text || b->text[b->nbytes - 1] != '\n')) return fail(DBT_E_BADARG, "raw text must hold whole lines (last byte '\\n')");
+	CU(cudaMemsetAsync(s.d_ncand, 0, 32, s.st));
+	if (!b->nbytes) { s.uploaded = true; return DBT_OK; }
+	if (!b->pair_offset || (!b->single_offset && b->single_cap)) return fail(DBT_E_BADARG, "null output array");
+	TRY(ensure_raw(c, s, b->nbytes));
+	const RunParams& rp = c->rp;
+	RawView v{};
+	v.raw = s.d_raw; v.nlmask = s.d_nlmask; v.blocksum = s.d_rblocksum; v.nl = s.d_nl; v.hdr = s.d_rhdr; v.hash = s.d_rhash; v.tlen = s.d_tlen; v.slen = s.d_slen; v.eq = s.d_eq;
+	v.pairmask = s.d_pairmask; v.singlemask = s.d_singlemask; v.pairlist = s.d_pairlist; v.singlelist = s.d_singlelist;
+	v.rstart = s.d_rstart; v.rend = s.d_rend; v.pairoff = s.d_pairoff; v.pairhash = s.d_pairhash; v.singleoff = s.d_singleoff;
+	v.max_lines = s.raw_max_lines; v.max_recs = s.raw_max_recs; v.max_pairs = c->p.max_batch_pairs; v.max_single = std::min(s.raw_max_single, b->single_cap);
+	CU(cudaEventRecord(s.evr0, s.st));
+	CU(cudaMemcpyAsync(s.d_raw, b->text, b->nbytes, cudaMemcpyHostToDevice, s.st));
+	CU(cudaMemsetAsync(s.d_raw + b->nbytes, 0, 64 + (32 - b->nbytes % 32) % 32, s.st));      // nl_mask_kernel reads 32-byte words, pack_kernel stages 16-byte words
+	CU(launch_fastx_split(s.st, c->nsm, v, b->nbytes, b->is_fastq ? 4u : 2u, b->min_read_len)); c->launches += 14;
+	CU(cudaMemcpyAsync(s.h_rhdr, s.d_rhdr, 32, cudaMemcpyDeviceToHost, s.st));
+	CU(cudaEventRecord(s.evr1, s.st));
+	CU(cudaStreamSynchronize(s.st));
+	s.ev_raw = true;
+	memcpy(info, s.h_rhdr, sizeof *info);
+	if (info->flags) return DBT_OK;                          // the caller takes the host path for this text
+	if (info->npairs > c->p.max_batch_pairs) return fail(DBT_E_CAPACITY, "raw text holds %u pairs > max_batch_pairs=%u", info->npairs, c->p.max_batch_pairs);
+	const uint64_t P = info->npairs;
+	if (P) {
+		CU(cudaMemcpyAsync(b->pair_offset, s.d_pairoff, P * 4, cudaMemcpyDeviceToHost, s.st));
+		if (b->pair_hash) CU(cudaMemcpyAsync(b->pair_hash, s.d_pairhash, P * 8, cudaMemcpyDeviceToHost, s.st));
+	}
+	if (info->nsingle) CU(cudaMemcpyAsync(b->single_offset, s.d_singleoff, (size_t)info->nsingle * 4, cudaMemcpyDeviceToHost, s.st));
+	// a pair shorter than min_read_len never reaches here; a pair LONGER than the context was built for is the caller's to handle
+	if (P && info->max_read_len > rp.max_read_len) {
+		CU(cudaStreamSynchronize(s.st));
+		return fail(DBT_E_CAPACITY, "a read of %u bases is longer than max_read_len=%u", info->max_read_len, rp.max_read_len);
+	}
+	if (P) {
+		CU(cudaEventRecord(s.evp0, s.st));
+		CU(launch_pack(s.st, s.d_raw, s.d_rstart, s.d_rend, P, rp, 32u * info->max_record_bytes, s.d_packed[0], s.d_packed[1], s.d_meta[0], s.d_meta[1], s.d_ncand + 1)); ++c->launches;
+		CU(cudaEventRecord(s.evp1, s.st));
+		s.ev_pack = true;
+	}
+	CU(cudaStreamSynchronize(s.st));                         // pair_offset / single_offset are the caller's to read now
+	s.npairs = P; s.uploaded = true;
+	return DBT_OK;
+}
+
+extern "C" int dbt_raw_times(dbt_ctx* c, int slot, float ms[2]) {
+	TRY(check_slot(c, slot));
+	Slot& s = c->slot[slot];
+	ms[0] = ms[1] = 0.f;
+	CU(cudaStreamSynchronize(s.st));
+	if (s.ev_raw) CU(cudaEventElapsedTime(&ms[0], s.evr0, s.evr1));
+	if (s.ev_pack) CU(cudaEventElapsedTime(&ms[1], s.evp0, s.evp1));
 	return DBT_OK;
 }
 

@@ -69,6 +69,20 @@ struct SlotView {
 	uint64_t npairs, first_pair_index;
 };
 
+// device buffers of the raw FASTA/FASTQ splitter (fastx.cu), one set per slot
+struct RawView {
+	const uint8_t* raw;         // the text (padded to a multiple of 32 bytes + 64)
+	uint32_t* nlmask;           // bit per byte: '\n'
+	uint32_t* blocksum;         // compaction scratch
+	uint32_t* nl;               // newline offsets, ascending (max_lines)
+	uint32_t* hdr;              // dbt_raw_info in the making: nlines, nrecords, npairs, nsingle, nshort_pairs, flags, max_read_len, max_record_bytes
+	uint64_t* hash; uint32_t* tlen; uint32_t* slen; uint8_t* eq;       // per record (max_recs, eq: +2)
+	uint32_t* pairmask; uint32_t* singlemask; uint32_t* pairlist; uint32_t* singlelist;
+	uint64_t* rstart; uint64_t* rend;                                   // per read of the pairs formed: [start, end) of the sequence in raw
+	uint32_t* pairoff; uint64_t* pairhash; uint32_t* singleoff;
+	uint32_t max_lines, max_recs, max_pairs, max_single;
+};
+
 constexpr uint32_t THR2_MATE0 = 1u, THR2_MATE1 = 2u, THR2_ALNED = 4u;
 constexpr int DBT_ST_THREAD_PENDING = 9;       // internal: handed to thread_kernel, which writes the final status
 constexpr uint32_t ERR_RECORD_OVERFLOW = 1u;

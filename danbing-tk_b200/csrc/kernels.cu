@@ -70,7 +70,9 @@ __device__ __noinline__ void pack_read_slow(const uint8_t* __restrict__ s, uint3
 }
 
 // in_cap: bytes of one warp's input tile (multiple of 16, >= 32 * max_read_len + 15 alignment + 8 over-read)
-__global__ void __launch_bounds__(PACK_WARPS * 32) pack_kernel(const uint8_t* __restrict__ ascii, const uint64_t* __restrict__ offsets, uint64_t nreads,
+// read r = ascii[starts[r], ends[r]): one u64 offsets array (starts = offsets, ends = offsets + 1) for concatenated reads, or
+// the two arrays the FASTA/FASTQ record splitter fills (fastx.cu) when the reads sit between title lines of the raw text
+__global__ void __launch_bounds__(PACK_WARPS * 32) pack_kernel(const uint8_t* __restrict__ ascii, const uint64_t* __restrict__ starts, const uint64_t* __restrict__ ends, uint64_t nreads,
                                                              uint32_t k, ReadLayout lay, uint32_t max_read_len, uint32_t in_cap,
                                                              uint64_t* __restrict__ packed0, uint64_t* __restrict__ packed1,
                                                              uint16_t* __restrict__ meta0, uint16_t* __restrict__ meta1, uint32_t* __restrict__ err) {
@@ -84,16 +86,18 @@ __global__ void __launch_bounds__(PACK_WARPS * 32) pack_kernel(const uint8_t* __
 	for (uint64_t tile = (uint64_t)blockIdx.x * PACK_WARPS + wib; tile < ntiles; tile += (uint64_t)gridDim.x * PACK_WARPS) {
 		const uint64_t r = tile * 32 + lane;
 		const bool active = r < nreads;
-		const uint64_t off = active ? offsets[r] : 0, end = active ? offsets[r + 1] : 0;
+		const uint64_t off = active ? starts[r] : ~0ull, end = active ? ends[r] : 0;
 		const uint32_t nact = (uint32_t)min((uint64_t)32, nreads - tile * 32);
-		const uint64_t off0 = __shfl_sync(0xffffffffu, off, 0), endN = __shfl_sync(0xffffffffu, end, (int)nact - 1);
+		uint64_t off0 = off, endN = end;                                              // byte range of the tile: min start, max end
+#pragma unroll
+		for (int o = 16; o; o >>= 1) { off0 = min(off0, __shfl_xor_sync(0xffffffffu, off0, o)); endN = max(endN, __shfl_xor_sync(0xffffffffu, endN, o)); }
 		const uint64_t len64 = end - off;
 		const uint8_t* a0 = reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(ascii + off0) & ~(uintptr_t)15);
 		const uint64_t nbytes = ((uint64_t)((ascii + endN) - a0) + 15) & ~15ull;
 		const uint64_t pair = r >> 1; const uint32_t mate = (uint32_t)(r & 1);
-		if (__any_sync(0xffffffffu, active && len64 > max_read_len) || nbytes + 8 > in_cap) {
-			if (lane == 0) atomicOr(err, ERR_READ_TOO_LONG);
-			if (active) pack_read_slow(ascii + off, (uint32_t)min(len64, (uint64_t)max_read_len), k, lay, (mate ? packed1 : packed0) + pair * W64, (mate ? meta1 : meta0) + pair);
+		if (__any_sync(0xffffffffu, active && (len64 > max_read_len || end < off)) || nbytes + 8 > in_cap) {
+			if (__any_sync(0xffffffffu, active && (len64 > max_read_len || end < off)) && lane == 0) atomicOr(err, ERR_READ_TOO_LONG);
+			if (active) pack_read_slow(ascii + off, end < off ? 0u : (uint32_t)min(len64, (uint64_t)max_read_len), k, lay, (mate ? packed1 : packed0) + pair * W64, (mate ? meta1 : meta0) + pair);
 			continue;
 		}
 		// ---- stage the tile: coalesced 16-byte asynchronous copies ----
@@ -253,7 +257,7 @@ __global__ void __launch_bounds__(1024) compact_scan_kernel(uint32_t* __restrict
 }
 
 __global__ void __launch_bounds__(256) compact_scatter_kernel(const uint32_t* __restrict__ mask, uint64_t nbits, const uint32_t* __restrict__ blocksum,
-                                                             uint32_t* __restrict__ out) {
+                                                             uint32_t* __restrict__ out, uint32_t cap = 0xFFFFFFFFu) {
 	__shared__ uint32_t wbase[8];
 	__shared__ uint32_t run;
 	const uint64_t nwords = (nbits + 31) / 32;
@@ -270,7 +274,7 @@ __global__ void __launch_bounds__(256) compact_scatter_kernel(const uint32_t* __
 		uint32_t pre = run;
 		for (int j = 0; j < (int)(threadIdx.x >> 5); ++j) pre += wbase[j];
 		uint32_t o = pre + x - c;
-		while (bits) { int b = __ffs(bits) - 1; bits &= bits - 1; out[o++] = (uint32_t)(w * 32 + b); }
+		while (bits) { int b = __ffs(bits) - 1; bits &= bits - 1; if (o < cap) out[o] = (uint32_t)(w * 32 + b); ++o; }
 		__syncthreads();
 		if (threadIdx.x == 0) { uint32_t t = 0; for (int j = 0; j < 8; ++j) t += wbase[j]; run += t; }
 		__syncthreads();
@@ -398,11 +402,14 @@ __global__ void random_gather_kernel(const uint4* __restrict__ table, uint64_t n
 // ============================================================================================
 #define DISPATCH_B(B, ...) switch (B) { case 2: { constexpr int BB = 2; __VA_ARGS__; } break; case 4: { constexpr int BB = 4; __VA_ARGS__; } break; default: return cudaErrorInvalidValue; }
 
-cudaError_t launch_pack(cudaStream_t st, const uint8_t* ascii, const uint64_t* offsets, uint64_t npairs, const RunParams& rp,
-                        uint64_t* p0, uint64_t* p1, uint16_t* m0, uint16_t* m1, uint32_t* err) {
+cudaError_t launch_pack(cudaStream_t st, const uint8_t* ascii, const uint64_t* starts, const uint64_t* ends, uint64_t npairs, const RunParams& rp,
+                        uint32_t tile_bytes, uint64_t* p0, uint64_t* p1, uint16_t* m0, uint16_t* m1, uint32_t* err) {
 	if (!npairs) return cudaSuccess;
 	const uint64_t nreads = 2 * npairs;
-	const uint32_t in_cap = (32u * rp.max_read_len + 15u + 8u + 15u) & ~15u;
+	// tile_bytes: the byte range 32 consecutive reads span (0: concatenated reads); capped so that four warps fit a block --
+	// a tile that does not fit its stage takes the byte-wise per-lane path
+	const uint32_t want = std::max(32u * rp.max_read_len, std::min(tile_bytes, 40u * 1024u));
+	const uint32_t in_cap = (want + 15u + 8u + 15u) & ~15u;
 	const size_t smem = (size_t)PACK_WARPS * (in_cap + 32 * rp.lay.W64 * 8);
 	static bool attr_set = false;
 	if (!attr_set) {
@@ -412,7 +419,7 @@ cudaError_t launch_pack(cudaStream_t st, const uint8_t* ascii, const uint64_t* o
 	}
 	const uint64_t ntiles = (nreads + 31) / 32;
 	const unsigned grid = (unsigned)std::min<uint64_t>((ntiles + PACK_WARPS - 1) / PACK_WARPS, 148ull * 64);
-	pack_kernel<<<grid, PACK_WARPS * 32, smem, st>>>(ascii, offsets, nreads, rp.k, rp.lay, rp.max_read_len, in_cap, p0, p1, m0, m1, err);
+	pack_kernel<<<grid, PACK_WARPS * 32, smem, st>>>(ascii, starts, ends, nreads, rp.k, rp.lay, rp.max_read_len, in_cap, p0, p1, m0, m1, err);
 	return cudaGetLastError();
 }
 
@@ -437,6 +444,17 @@ cudaError_t launch_compact(cudaStream_t st, const SlotView& sv) {
 }
 
 // records[0 .. min(*nslots, cap)) -> out[0 .. *nemit) in slot order; 5 launches
+// generic: set bits of mask[0, nbits) -> ascending positions in list (at most cap are written), their number in *count
+cudaError_t launch_compact_bits(cudaStream_t st, const uint32_t* mask, uint64_t nbits, uint32_t* blocksum, uint32_t* list, uint32_t* count, uint32_t cap) {
+	const uint64_t nwords = (nbits + 31) / 32;
+	unsigned nblocks = (unsigned)((nwords + COMPACT_WORDS - 1) / COMPACT_WORDS);
+	if (!nblocks) nblocks = 1;
+	compact_count_kernel<<<nblocks, 256, 0, st>>>(mask, nbits, blocksum);
+	compact_scan_kernel<<<1, 1024, 0, st>>>(blocksum, nblocks, count, nullptr);
+	compact_scatter_kernel<<<nblocks, 256, 0, st>>>(mask, nbits, blocksum, list, cap);
+	return cudaGetLastError();
+}
+
 cudaError_t launch_record_emit(cudaStream_t st, int nsm, const uint8_t* records, uint32_t stride, const uint32_t* nslots, uint32_t cap, int emit_failed,
                                uint32_t* mask, uint32_t* blocksum, uint32_t* list, uint32_t* nemit, uint8_t* out) {
 	if (!cap) return cudaSuccess;

@@ -2,8 +2,12 @@
 #pragma once
 #include "device_types.cuh"
 namespace dbt {
-cudaError_t launch_pack(cudaStream_t st, const uint8_t* ascii, const uint64_t* offsets, uint64_t npairs, const RunParams& rp,
-                        uint64_t* p0, uint64_t* p1, uint16_t* m0, uint16_t* m1, uint32_t* err);
+// read r = ascii[starts[r], ends[r]); tile_bytes: span of 32 consecutive reads in the text (0 = concatenated reads)
+cudaError_t launch_pack(cudaStream_t st, const uint8_t* ascii, const uint64_t* starts, const uint64_t* ends, uint64_t npairs, const RunParams& rp,
+                        uint32_t tile_bytes, uint64_t* p0, uint64_t* p1, uint16_t* m0, uint16_t* m1, uint32_t* err);
+cudaError_t launch_compact_bits(cudaStream_t st, const uint32_t* mask, uint64_t nbits, uint32_t* blocksum, uint32_t* list, uint32_t* count, uint32_t cap);
+// raw FASTA/FASTQ text -> newline list, records, adjacent-mate pairs (fastx.cu)
+cudaError_t launch_fastx_split(cudaStream_t st, int nsm, const RawView& v, uint64_t nbytes, uint32_t lines_per_record, uint32_t min_len);
 cudaError_t launch_subfilter(cudaStream_t st, int B, int nsm, const DevIndex& ix, const RunParams& rp, const SlotView& sv);
 cudaError_t launch_compact(cudaStream_t st, const SlotView& sv);
 cudaError_t launch_record_emit(cudaStream_t st, int nsm, const uint8_t* records, uint32_t stride, const uint32_t* nslots, uint32_t cap, int emit_failed,

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define DBT_ABI_VERSION 4
+#define DBT_ABI_VERSION 5
 
 /* ---- error codes -------------------------------------------------------------------------- */
 #define DBT_OK            0
@@ -250,6 +250,39 @@ int  dbt_fetch  (dbt_ctx*, dbt_batch_result*, int slot);      /* async D2H of re
 int  dbt_submit (dbt_ctx*, const dbt_batch*, dbt_batch_result*, int slot); /* upload+process+fetch */
 int  dbt_wait   (dbt_ctx*, int slot);                         /* blocks; finalises dbt_batch_result */
 #define DBT_N_SLOTS 2
+
+/* ---- raw FASTA/FASTQ ingestion ----------------------------------------
+ * Replaces, for name-collated input, the serial read loop of CountWords (cpp:1918-1976: four / two getline calls per
+ * record, prunePEinfo cpp:455-462, pairing through a hash map, the late mate = read 1, pairs with a mate shorter than
+ * min_read_len forgotten).  `text` = whole records of the file as they are (FASTA: title line + sequence line; FASTQ: four
+ * lines), last byte '\n', < 4 GiB.  The device finds the lines, pairs every record with the record before it when their
+ * pruned titles are equal, packs the sequences and leaves the slot in the state dbt_upload leaves it in: dbt_process /
+ * dbt_fetch / dbt_wait follow.  Pair i of the batch = the i-th such pair in stream order (the reference's order).
+ * The call returns after the split (it synchronises the slot's stream; the other slot keeps running):
+ *   info            counts, flags, the longest read
+ *   pair_offset[i]  byte offset in `text` of the first record of pair i (its mate is the next record) -- kam / aln
+ *                   lines are formatted from the text itself
+ *   pair_hash[i]    dbt_title_hash of the pair's pruned title (may be NULL)
+ *   single_offset[] byte offsets of the records left unpaired, ascending: the caller keeps the reference's map for them
+ * flags != 0 (three or more equal titles in a row, or more lines / pairs / singletons than the capacities): nothing was
+ * uploaded, the caller pairs this text on the host and submits it with dbt_upload.  DBT_E_CAPACITY with info filled: a read
+ * is longer than max_read_len, or more pairs than max_batch_pairs. */
+#define DBT_RAW_SLOWPATH 1u
+#define DBT_RAW_OVERFLOW 2u
+typedef struct {
+  uint32_t nlines, nrecords, npairs, nsingle, nshort_pairs, flags, max_read_len, max_record_bytes;
+} dbt_raw_info;
+typedef struct {
+  uint64_t first_pair_index;
+  const uint8_t* text; uint64_t nbytes;
+  int32_t  is_fastq; uint32_t min_read_len;     /* Cthreshold + k - 1 (cpp:1892) */
+  uint32_t* pair_offset; uint64_t* pair_hash;   /* [max_batch_pairs] */
+  uint32_t* single_offset; uint32_t single_cap;
+} dbt_raw_batch;
+int  dbt_upload_raw(dbt_ctx*, const dbt_raw_batch*, dbt_raw_info* info, int slot);
+uint64_t dbt_title_hash(const uint8_t* title, size_t len);     /* FNV-1a 64 of the pruned title, as the device computes it */
+/* [0] H2D + split kernels [1] pack_kernel of the slot's last dbt_upload_raw, milliseconds */
+int  dbt_raw_times(dbt_ctx*, int slot, float ms[2]);
 
 /* ---- results (replaces dumpTRKmers/writeTRKmerSummary inputs, cpp:2631-2641) ---------------- */
 int  dbt_download(dbt_ctx*, uint64_t* trkmc /*[nk_tr]*/, uint64_t* kmc /*[nloci]*/,

@@ -38,7 +38,7 @@ for ln in lines:
         continue
     if re.match(r"\s+/\*[0-9a-f]{4,}\*/", ln):
         seq.append(curline)
-raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"] + (["-k", "regex:" + os.environ["NCU_K"]] if os.environ.get("NCU_K") else []), capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hi = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
 h = rows[hi]

@@ -56,7 +56,7 @@ def test_index_loader_sizes_and_errors(tmp_path):
     assert run("index", tmp_path / "pan").returncode == 1
 
 
-def ref_pairing(lines, is_fastq, min_read_size, reads_per_batch):
+def ref_pairing(lines, is_fastq, min_read_size, reads_per_batch, return_db=False):
     """Python restatement of the read loop of CountWords (cpp:1869-1981), incl. std::getline leaving the string
     untouched at EOF and the FASTQ branch lacking the `se and EOF` break."""
     pos = [0]
@@ -100,7 +100,7 @@ def ref_pairing(lines, is_fastq, min_read_size, reads_per_batch):
                 break
             out.append((title, seq1, seq2, qual1, qual2))
             n += 2
-    return out, len(db)
+    return (out, db) if return_db else (out, len(db))
 
 
 def make_fastx(rng, npairs, is_fastq, shuffle, singletons):
