@@ -60,15 +60,13 @@ inline void append_annot(std::string& o, const uint8_t* tr, uint32_t n) {
 }
 
 // rec: one record of dbt_record_stride bytes in the threading layout (header + two dbt_aln_mate blobs)
-inline void append_aln_line(std::string& o, const uint8_t* rec, uint32_t aln_stride, uint32_t es_cap, const HostBatch& hb) {
+inline void append_aln_line(std::string& o, const uint8_t* rec, uint32_t aln_stride, uint32_t es_cap, const PairText& t) {
 	const dbt_pair_record* h = reinterpret_cast<const dbt_pair_record*>(rec);
-	const uint64_t i = h->pair_index - hb.first_pair_index;
 	o.append(".\t");                                   // src: -1 without -s (cpp:1744)
 	append_int(o, (int)h->dst); o.push_back('\t');
-	o.append(hb.names.data() + hb.name_off[i], hb.name_off[i + 1] - hb.name_off[i]); o.push_back('\t');
-	const uint64_t* off = hb.offsets + 2 * i;
-	o.append(reinterpret_cast<const char*>(hb.bases) + off[1], off[2] - off[1]); o.push_back('\t');     // read 2
-	o.append(reinterpret_cast<const char*>(hb.bases) + off[0], off[1] - off[0]); o.push_back('\t');     // read 1
+	o.append(t.title, t.title_len); o.push_back('\t');
+	o.append(t.seq[1], t.seq_len[1]); o.push_back('\t');     // read 2
+	o.append(t.seq[0], t.seq_len[0]); o.push_back('\t');     // read 1
 	for (int m = 1; m >= 0; --m) {                      // r2 first (cpp:1750-1756)
 		const uint8_t* b = rec + sizeof(dbt_pair_record) + (size_t)m * aln_stride;
 		const dbt_aln_mate* a = reinterpret_cast<const dbt_aln_mate*>(b);
@@ -76,6 +74,10 @@ inline void append_aln_line(std::string& o, const uint8_t* rec, uint32_t aln_str
 		append_annot(o, b + sizeof(dbt_aln_mate) + es_cap, a->ntr);
 		o.push_back(m ? '\t' : '\n');
 	}
+}
+inline void append_aln_line(std::string& o, const uint8_t* rec, uint32_t aln_stride, uint32_t es_cap, const HostBatch& hb) {
+	const uint64_t i = reinterpret_cast<const dbt_pair_record*>(rec)->pair_index - hb.first_pair_index;
+	append_aln_line(o, rec, aln_stride, es_cap, pair_text(hb, i, false));
 }
 
 }  // namespace dbt_host

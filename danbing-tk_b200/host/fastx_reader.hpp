@@ -25,6 +25,7 @@ namespace dbt_host {
 
 struct HostBatch {
 	uint64_t first_pair_index = 0, npairs = 0;
+	uint64_t seq = 0;                                         // ordinal of the batch in the stream
 	uint8_t* bases = nullptr; uint64_t bases_cap = 0;       // caller-provided (pinned) buffer
 	uint64_t* offsets = nullptr; uint64_t pairs_cap = 0;    // caller-provided (pinned), 2*pairs_cap+1 entries
 	std::vector<char> names; std::vector<uint64_t> name_off;    // title of pair i = names[name_off[i], name_off[i+1]) incl. leading '>'/'@'
@@ -38,6 +39,23 @@ struct HostBatch {
 	}
 	bool room_for(uint64_t l1, uint64_t l2) const { return npairs < pairs_cap && offsets[2 * npairs] + l1 + l2 <= bases_cap; }
 };
+
+// ---- a pair's text, wherever it lives ----
+struct PairText {
+	const char* title = nullptr; size_t title_len = 0;       // pruned, with its leading '>' / '@'
+	const char* seq[2] = {nullptr, nullptr}; size_t seq_len[2] = {0, 0};    // [0] = read 1 (late mate), [1] = read 2
+	const char* qual[2] = {nullptr, nullptr}; size_t qual_len[2] = {0, 0};
+};
+
+inline PairText pair_text(const HostBatch& hb, uint64_t i, bool fq) {
+	PairText t;
+	t.title = hb.names.data() + hb.name_off[i]; t.title_len = hb.name_off[i + 1] - hb.name_off[i];
+	for (int m = 0; m < 2; ++m) {
+		t.seq[m] = (const char*)hb.bases + hb.offsets[2 * i + m]; t.seq_len[m] = hb.offsets[2 * i + m + 1] - hb.offsets[2 * i + m];
+		if (fq) { t.qual[m] = hb.quals.data() + hb.qual_off[2 * i + m]; t.qual_len[m] = hb.qual_off[2 * i + m + 1] - hb.qual_off[2 * i + m]; }
+	}
+	return t;
+}
 
 class FastxReader {
 public:

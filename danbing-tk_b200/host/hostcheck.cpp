@@ -13,6 +13,7 @@
 #include "serialize.hpp"
 #include "fastx_reader.hpp"
 #include "kam_writer.hpp"
+#include "raw_ingest.hpp"
 
 using namespace dbt_host;
 
@@ -51,6 +52,54 @@ static int cmd_index_sum(const std::string& pref) {
 	for (size_t l = 0; l < g.fl_n.size(); ++l) for (uint64_t i = 0; i < g.fl_n[l]; ++i) flsum += g.fl_kmers[o++] * (uint64_t)(l + 1);
 	printf("nloci %llu nk_dbi %zu nvv %zu ntr %zu nfl %zu keysum %llu kvsum %llu vvsum %llu flsum %llu\n", (unsigned long long)g.nloci, g.dbi_keys.size(),
 	       g.vv.size(), g.tr_kmers.size(), g.fl_kmers.size(), (unsigned long long)keysum, (unsigned long long)kvsum, (unsigned long long)vvsum, (unsigned long long)flsum);
+	return 0;
+}
+
+// RawReader + StreamPairer with the GPU's record split (csrc/fastx.cu) restated on the host for the test: neighbours with
+// equal pruned titles pair up, runs of three raise the slow-path flag, the rest are singletons.  Prints the pairs in output order.
+static int cmd_pair_raw(const char* fn, bool fq, uint64_t minlen, uint64_t refbatch, uint64_t target) {
+	RawReader rd(fq);
+	if (!rd.open(fn)) { fprintf(stderr, "cannot open %s\n", fn); return 1; }
+	RawChunk c;
+	c.cap = RawReader::HEADROOM + target + 4096;
+	std::vector<uint8_t> buf(c.cap + 64);
+	c.buf = buf.data();
+	StreamPairer pr(fq, minlen, refbatch);
+	StreamPairer::Extra ex;
+	const uint32_t L = fq ? 4 : 2;
+	uint64_t nfast = 0, nslow = 0;
+	while (rd.fill(c, target)) {
+		// ---- the device split, on the host ----
+		const uint8_t* t = c.text(); const uint64_t n = c.nbytes();
+		std::vector<uint32_t> rec;                              // record start offsets
+		{ uint64_t p = 0; while (p < n) { rec.push_back((uint32_t)p); for (uint32_t i = 0; i < L; ++i) p = (uint64_t)((const uint8_t*)rawmemchr(t + p, '\n') - t) + 1; } }
+		auto title = [&](uint32_t r) { const uint8_t* a = t + rec[r]; const uint8_t* e = (const uint8_t*)rawmemchr(a, '\n'); return std::string((const char*)a, pruned_len(a, (size_t)(e - a))); };
+		auto slen = [&](uint32_t r) { const uint8_t* a = (const uint8_t*)rawmemchr(t + rec[r], '\n') + 1; return (uint64_t)((const uint8_t*)rawmemchr(a, '\n') - a); };
+		const uint32_t nr = (uint32_t)rec.size();
+		std::vector<uint8_t> eq(nr + 2, 0);
+		for (uint32_t r = 1; r < nr; ++r) eq[r] = title(r) == title(r - 1);
+		std::vector<uint32_t> po, so; std::vector<uint64_t> ph; uint32_t flags = 0, nshort = 0;
+		for (uint32_t r = 0; r < nr; ++r) {
+			const bool e0 = r ? eq[r - 1] : false, e1 = eq[r], e2 = eq[r + 1];
+			if (e1 && (e0 || e2)) flags |= DBT_RAW_SLOWPATH;
+			else if (e1) { if (slen(r) >= minlen && slen(r - 1) >= minlen) { po.push_back(rec[r - 1]); const std::string tt = title(r); uint64_t h = 0xcbf29ce484222325ull; for (unsigned char ch : tt) { h ^= ch; h *= 0x100000001b3ull; } ph.push_back(h); } else ++nshort; }
+			else if (!e2) so.push_back(rec[r]);
+		}
+		c.pair_offset = po.data(); c.pair_hash = ph.data(); c.single_offset = so.data();
+		const bool fast = pr.chunk(c, true, flags, (uint32_t)po.size(), (uint32_t)so.size(), nshort, ex);
+		(fast ? nfast : nslow) += 1;
+		// ---- merged output: GPU pairs (key = pair_offset) and host pairs (key) ascending ----
+		size_t i = 0, j = 0; const size_t ng = fast ? po.size() : 0, nh = ex.key.size();
+		while (i < ng || j < nh) {
+			PairText p;
+			if (j >= nh || (i < ng && (uint64_t)po[i] < ex.key[j])) p = pair_text_raw(t, po[i++], fq); else p = pair_text(ex.hb, j++, fq);
+			fwrite(p.title, 1, p.title_len, stdout); putchar('\t'); fwrite(p.seq[0], 1, p.seq_len[0], stdout); putchar('\t'); fwrite(p.seq[1], 1, p.seq_len[1], stdout);
+			if (fq) { putchar('\t'); fwrite(p.qual[0], 1, p.qual_len[0], stdout); putchar('\t'); fwrite(p.qual[1], 1, p.qual_len[1], stdout); }
+			putchar('\n');
+		}
+	}
+	if (!rd.error().empty()) { fprintf(stderr, "%s\n", rd.error().c_str()); return 1; }
+	fprintf(stderr, "reads %llu unpaired %llu fast %llu slow %llu\n", (unsigned long long)(2 * pr.total_pairs()), (unsigned long long)pr.unpaired(), (unsigned long long)nfast, (unsigned long long)nslow);
 	return 0;
 }
 
@@ -123,6 +172,7 @@ int main(int argc, char** argv) {
 	if (cmd == "tr-order" && argc == 4) return cmd_tr_order(argv[2], argv[3]);
 	if (cmd == "index" && argc >= 3) return cmd_index(argv[2], argc > 3 ? argv[3] : "");
 	if (cmd == "index-sum" && argc == 3) return cmd_index_sum(argv[2]);
+	if (cmd == "pair-raw" && argc == 7) return cmd_pair_raw(argv[2], atoi(argv[3]) != 0, strtoull(argv[4], nullptr, 10), strtoull(argv[5], nullptr, 10), strtoull(argv[6], nullptr, 10));
 	if (cmd == "pair" && argc == 7) return cmd_pair(argv[2], atoi(argv[3]) != 0, strtoull(argv[4], nullptr, 10), strtoull(argv[5], nullptr, 10), strtoull(argv[6], nullptr, 10));
 	if (cmd == "kam" && argc == 8) return cmd_kam(argv[2], (uint32_t)atoi(argv[3]), (uint32_t)atoi(argv[4]), argv[5], atoi(argv[6]) != 0, strtoull(argv[7], nullptr, 10));
 	if (cmd == "args") return cmd_args(argc - 1, argv + 1);

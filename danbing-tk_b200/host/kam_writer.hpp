@@ -38,12 +38,11 @@ inline void append_fields(std::string& o, const dbt_mate_record& r) {
 	append_na(o, r.si); o.push_back(':'); append_na(o, r.nt); o.push_back(':'); append_na(o, r.bs); o.push_back(':'); append_na(o, r.ti);
 }
 
-// rec: one record of dbt_record_stride bytes; hb: the batch it came from
-inline void append_kam_line(std::string& o, const uint8_t* rec, uint32_t as_stride, const HostBatch& hb, bool isFastq) {
+// rec: one record of dbt_record_stride bytes; t: the text of its pair (HostBatch, or the raw chunk the GPU split)
+inline void append_kam_line(std::string& o, const uint8_t* rec, uint32_t as_stride, const PairText& t, bool isFastq) {
 	const dbt_pair_record* h = reinterpret_cast<const dbt_pair_record*>(rec);
 	const dbt_mate_record& r1 = h->mate[0];
 	const dbt_mate_record& r2 = h->mate[1];
-	const uint64_t i = h->pair_index - hb.first_pair_index;
 	o.append(".\t");                                   // src: unknown without -s (cpp:1653)
 	append_int(o, h->dst); o.push_back('\t');
 	append_int(o, (h->dst0 != h->dst) ? (long long)(int)h->dst0 : -1); o.push_back('\t');   // km_asgn_t::assign (cpp:115-119), int fields
@@ -54,16 +53,18 @@ inline void append_kam_line(std::string& o, const uint8_t* rec, uint32_t as_stri
 	append_fields(o, r1); o.push_back('\t');
 	append_rle(o, rec + sizeof(dbt_pair_record) + as_stride, r2.nk); o.push_back('\t');
 	append_rle(o, rec + sizeof(dbt_pair_record), r1.nk); o.push_back('\t');
-	const uint64_t n0 = hb.name_off[i], n1 = hb.name_off[i + 1];
-	if (n1 > n0 + 1) o.append(hb.names.data() + n0 + 1, n1 - n0 - 1);                      // titles[..].substr(1)
+	if (t.title_len > 1) o.append(t.title + 1, t.title_len - 1);                          // titles[..].substr(1)
 	o.push_back('\t');
-	const uint64_t* off = hb.offsets + 2 * i;
-	o.append(reinterpret_cast<const char*>(hb.bases) + off[1], off[2] - off[1]); o.push_back('\t');     // read 2
-	if (isFastq) o.append(hb.quals.data() + hb.qual_off[2 * i + 1], hb.qual_off[2 * i + 2] - hb.qual_off[2 * i + 1]); else o.push_back('.');
+	o.append(t.seq[1], t.seq_len[1]); o.push_back('\t');                                  // read 2
+	if (isFastq) o.append(t.qual[1], t.qual_len[1]); else o.push_back('.');
 	o.push_back('\t');
-	o.append(reinterpret_cast<const char*>(hb.bases) + off[0], off[1] - off[0]); o.push_back('\t');     // read 1
-	if (isFastq) o.append(hb.quals.data() + hb.qual_off[2 * i], hb.qual_off[2 * i + 1] - hb.qual_off[2 * i]); else o.push_back('.');
+	o.append(t.seq[0], t.seq_len[0]); o.push_back('\t');                                  // read 1
+	if (isFastq) o.append(t.qual[0], t.qual_len[0]); else o.push_back('.');
 	o.push_back('\n');
+}
+inline void append_kam_line(std::string& o, const uint8_t* rec, uint32_t as_stride, const HostBatch& hb, bool isFastq) {
+	const uint64_t i = reinterpret_cast<const dbt_pair_record*>(rec)->pair_index - hb.first_pair_index;
+	append_kam_line(o, rec, as_stride, pair_text(hb, i, isFastq), isFastq);
 }
 
 }  // namespace dbt_host

@@ -20,6 +20,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <deque>
+#include <functional>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -31,6 +32,7 @@
 #include "options.hpp"
 #include "serialize.hpp"
 #include "fastx_reader.hpp"
+#include "raw_ingest.hpp"
 #include "kam_writer.hpp"
 #include "aln_writer.hpp"
 
@@ -55,15 +57,22 @@ private:
 };
 
 struct BatchOut {                       // what a worker hands to the writer
-	uint64_t index = 0;
+	uint64_t index = 0;                 // ordinal of the batch / chunk in the stream: stdout and the per-batch stderr lines go out in this order
 	std::string text;                   // kam lines
 	uint64_t counters[DBT_N_COUNTERS] = {};
 	uint64_t npairs = 0, nreads_total = 0, unpaired = 0;
 	double seconds = 0;
 };
 
+struct PairTurn {                       // raw ingestion: chunks meet the host pairer (one map, like the reference's) in stream order
+	std::mutex m; std::condition_variable cv; uint64_t next = 0;
+};
+
 struct Shared {
 	Options opt;
+	std::unique_ptr<StreamPairer> pairer; PairTurn turn;
+	uint64_t chunk_target = 0;          // raw text bytes per GPU submission
+	std::atomic<uint64_t> t_split_us{0}, t_pair_us{0}, t_wait_us{0}, t_format_us{0}, t_read_us{0}, n_slow_chunks{0}, n_chunks{0};
 	Rpgg rpgg;
 	dbt_index index{};
 	uint64_t batch_pairs = 0, bases_cap = 0;
@@ -79,6 +88,7 @@ struct Worker {
 	dbt_ctx* ctx = nullptr;
 	uint32_t ctx_len = 0;
 	Channel<HostBatch*> in;
+	Channel<RawChunk*> rin;
 	std::vector<uint64_t> acc_tr, acc_kmc; std::vector<uint32_t> acc_nmap;      // counts of contexts retired by a rebuild
 	uint64_t acc_cnt[DBT_N_COUNTERS] = {};
 	std::thread th;
@@ -129,7 +139,7 @@ void worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<HostBatch
 		int rc = dbt_wait(w.ctx, s);
 		if (rc) { S.fail(dbt_err("dbt_wait", rc)); return false; }
 		BatchOut bo;
-		bo.index = f.hb->first_pair_index;                    // batches are ordered by their first pair
+		bo.index = f.hb->seq;
 		bo.npairs = f.hb->npairs; bo.nreads_total = f.hb->nreads_total_after; bo.unpaired = f.hb->unpaired_after;
 		memcpy(bo.counters, f.res.counters, sizeof bo.counters);
 		if (S.want_records && f.res.n_records) {
@@ -172,6 +182,166 @@ void worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<HostBatch
 	}
 	if (!S.failed) for (int s = 0; s < DBT_N_SLOTS; ++s) { const int ss = (k + s) & 1; if (!finish(ss)) break; }
 	if (S.failed) recycle.close();                           // unblock the reader
+}
+
+using Clock = std::chrono::steady_clock;
+static uint64_t us_since(Clock::time_point t0) { return (uint64_t)std::chrono::duration_cast<std::chrono::microseconds>(Clock::now() - t0).count(); }
+
+// One GPU's share of the raw chunks: dbt_upload_raw (H2D + record split + neighbour pairing + 2-bit pack on the device),
+// the chunk's turn at the host pairer (singletons, end-of-stream rules; whole chunks the device hands back), the pair
+// loop on the device, and -- when the pairer formed pairs of its own -- one more ordinary ASCII submission whose lines
+// are merged into the chunk's output by the position of the late mate.
+void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawChunk*>& recycle) {
+	struct Inflight {
+		RawChunk* ch = nullptr; bool gpu = false; dbt_raw_info info{}; dbt_batch_result res{};
+		uint8_t* recs = nullptr; StreamPairer::Extra ex;
+		uint64_t nreads_total = 0, unpaired = 0; Clock::time_point t0;
+	};
+	Inflight fl[DBT_N_SLOTS];
+	const bool fq = S.opt.isFastq;
+	std::vector<uint8_t> recs2;
+	std::function<bool(int)> finish;
+	auto rebuild = [&](uint32_t need_len, int keep_slot) -> bool {       // a read longer than the context was built for
+		for (int s = 0; s < DBT_N_SLOTS; ++s) if (s != keep_slot && !finish(s)) return false;
+		if (!retire_ctx(S, w)) return false;
+		uint32_t L = std::max<uint32_t>({need_len, S.opt.max_read_len, (uint32_t)S.opt.ksize, 150u});
+		if (w.ctx_len) L = std::max<uint32_t>(L, w.ctx_len + w.ctx_len / 4);
+		for (auto& g : fl) if (g.recs) { dbt_host_free(g.recs); g.recs = nullptr; }   // sized for the old record stride
+		return make_ctx(S, w, L);
+	};
+	auto ensure_recs = [&](Inflight& f) -> bool {
+		if (!S.want_records || f.recs) return true;
+		f.recs = (uint8_t*)dbt_host_alloc((size_t)S.batch_pairs * dbt_record_stride(w.ctx));
+		if (!f.recs) { S.fail("cannot allocate pinned record buffer"); return false; }
+		return true;
+	};
+	finish = [&](int s) -> bool {
+		Inflight& f = fl[s];
+		if (!f.ch) return true;
+		RawChunk* ch = f.ch; f.ch = nullptr;
+		BatchOut bo;
+		bo.index = ch->seq; bo.nreads_total = f.nreads_total; bo.unpaired = f.unpaired;
+		uint64_t ngpu = 0;
+		if (f.gpu) {
+			auto tw = Clock::now();
+			int rc = dbt_wait(w.ctx, s);
+			S.t_wait_us += us_since(tw);
+			if (rc) { S.fail(dbt_err("dbt_wait", rc)); return false; }
+			for (int i = 0; i < DBT_N_COUNTERS; ++i) bo.counters[i] += f.res.counters[i];
+			bo.npairs += f.info.npairs; ngpu = f.res.n_records;
+		}
+		const HostBatch& xb = f.ex.hb;
+		auto format = [&](std::string& o, const uint8_t* rec, bool from_gpu) {
+			const uint64_t pi = reinterpret_cast<const dbt_pair_record*>(rec)->pair_index;
+			const PairText t = from_gpu ? pair_text_raw(ch->text(), ch->pair_offset[pi], fq) : pair_text(xb, pi, fq);
+			if (S.thr_graph) append_aln_line(o, rec, dbt_record_aln_stride(w.ctx), dbt_record_es_cap(w.ctx), t);
+			else append_kam_line(o, rec, dbt_record_as_stride(w.ctx), t, fq);
+		};
+		auto tf = Clock::now();
+		if (!xb.npairs) {
+			if (S.want_records && ngpu) {
+				const uint32_t stride = dbt_record_stride(w.ctx);
+				bo.text.reserve((size_t)ngpu * 520);
+				for (uint64_t i = 0; i < ngpu; ++i) format(bo.text, f.recs + i * stride, true);
+			}
+		} else {
+			// Pairs the host pairer formed for this chunk: an ordinary ASCII batch on the same slot, its lines merged into the
+			// chunk's by the position of the late mate.  The device pairs are formatted first: the context may have to be
+			// rebuilt for a longer read, which changes the record stride.
+			std::vector<std::pair<uint64_t, std::string>> lines;
+			if (S.want_records && ngpu) {
+				const uint32_t stride = dbt_record_stride(w.ctx);
+				lines.reserve(ngpu + xb.npairs);
+				for (uint64_t i = 0; i < ngpu; ++i) {
+					const uint8_t* rec = f.recs + i * stride;
+					lines.emplace_back((uint64_t)ch->pair_offset[reinterpret_cast<const dbt_pair_record*>(rec)->pair_index], std::string());
+					format(lines.back().second, rec, true);
+				}
+			}
+			if (!w.ctx || xb.max_len > w.ctx_len) { if (!rebuild(xb.max_len, s)) return false; }
+			const uint32_t stride = dbt_record_stride(w.ctx);
+			dbt_batch_result res2{};
+			if (S.want_records) recs2.resize((size_t)xb.npairs * stride);
+			res2.capacity = S.want_records ? xb.npairs : 0; res2.records = S.want_records ? recs2.data() : nullptr;
+			dbt_batch b{};
+			b.first_pair_index = 0; b.npairs = xb.npairs; b.layout = DBT_LAYOUT_ASCII; b.bases = xb.bases; b.offsets = xb.offsets;
+			int rc = dbt_submit(w.ctx, &b, &res2, s);
+			if (!rc) rc = dbt_wait(w.ctx, s);
+			if (rc) { S.fail(dbt_err("dbt_submit (host-paired reads)", rc)); return false; }
+			for (int i = 0; i < DBT_N_COUNTERS; ++i) bo.counters[i] += res2.counters[i];
+			bo.npairs += xb.npairs;
+			for (uint64_t j = 0; j < res2.n_records; ++j) {
+				const uint8_t* rec = recs2.data() + j * stride;
+				lines.emplace_back(f.ex.key[reinterpret_cast<const dbt_pair_record*>(rec)->pair_index], std::string());
+				format(lines.back().second, rec, false);
+			}
+			std::stable_sort(lines.begin(), lines.end(), [](const auto& a, const auto& b2) { return a.first < b2.first; });
+			for (auto& l : lines) bo.text += l.second;
+		}
+		S.t_format_us += us_since(tf);
+		bo.seconds = std::chrono::duration<double>(Clock::now() - f.t0).count();
+		recycle.push(ch);
+		out.push(std::move(bo));
+		return true;
+	};
+	RawChunk* ch = nullptr;
+	int k = 0;
+	const uint32_t minlen = (uint32_t)(S.opt.Cthreshold + S.opt.ksize - 1);
+	while (!S.failed && w.rin.pop(ch)) {
+		const int s = k++ & 1;
+		if (!finish(s)) break;
+		Inflight& f = fl[s];
+		f.t0 = Clock::now(); f.gpu = false; f.info = dbt_raw_info{};
+		bool use_gpu = ch->nbytes() > 0, ok = true;
+		if (use_gpu) {
+			if (!w.ctx && !make_ctx(S, w, std::max<uint32_t>({S.opt.max_read_len, (uint32_t)S.opt.ksize, 150u}))) break;
+			if (!ensure_recs(f)) break;
+			auto ts = Clock::now();
+			for (int attempt = 0; attempt < 2; ++attempt) {
+				dbt_raw_batch rb{};
+				rb.first_pair_index = 0; rb.text = ch->text(); rb.nbytes = ch->nbytes(); rb.is_fastq = fq ? 1 : 0; rb.min_read_len = minlen;
+				rb.pair_offset = ch->pair_offset; rb.pair_hash = ch->pair_hash; rb.single_offset = ch->single_offset; rb.single_cap = ch->single_cap;
+				const int rc = dbt_upload_raw(w.ctx, &rb, &f.info, s);
+				if (rc == DBT_OK) break;
+				if (rc == DBT_E_CAPACITY && f.info.max_read_len > w.ctx_len && attempt == 0) {
+					if (!rebuild(f.info.max_read_len, s) || !ensure_recs(f)) { ok = false; break; }
+					continue;
+				}
+				S.fail(dbt_err("dbt_upload_raw", rc)); ok = false; break;
+			}
+			S.t_split_us += us_since(ts);
+		}
+		// the chunk's turn at the pairer (stream order over all GPUs)
+		{
+			std::unique_lock<std::mutex> l(S.turn.m);
+			S.turn.cv.wait(l, [&] { return S.turn.next == ch->seq || S.failed; });
+			if (ok && !S.failed) {
+				auto tp = Clock::now();
+				const bool fast = S.pairer->chunk(*ch, use_gpu, f.info.flags, f.info.npairs, f.info.nsingle, f.info.nshort_pairs, f.ex);
+				f.gpu = fast && f.info.npairs > 0;
+				if (!fast) f.info.npairs = 0;
+				if (use_gpu && !fast) ++S.n_slow_chunks;
+				++S.n_chunks;
+				f.nreads_total = 2 * S.pairer->total_pairs(); f.unpaired = S.pairer->unpaired();
+				S.t_pair_us += us_since(tp);
+			}
+			++S.turn.next;
+			S.turn.cv.notify_all();
+		}
+		if (!ok || S.failed) { recycle.push(ch); break; }
+		f.ch = ch;
+		if (f.gpu) {
+			if (!ensure_recs(f)) break;
+			f.res = dbt_batch_result{};
+			f.res.capacity = S.want_records ? S.batch_pairs : 0; f.res.records = S.want_records ? f.recs : nullptr;
+			int rc = dbt_process(w.ctx, s);
+			if (!rc) rc = dbt_fetch(w.ctx, &f.res, s);
+			if (rc) { S.fail(dbt_err("dbt_process", rc)); break; }
+		}
+	}
+	if (!S.failed) for (int s = 0; s < DBT_N_SLOTS; ++s) { const int ss = (k + s) & 1; if (!finish(ss)) break; }
+	for (auto& f : fl) if (f.recs) dbt_host_free(f.recs);
+	if (S.failed) { recycle.close(); S.turn.cv.notify_all(); }
 }
 
 }  // namespace
@@ -227,20 +397,46 @@ int main(int argc, char** argv) {
 
 	// ---- batches ----
 	const uint64_t readsPerRefBatch = (uint64_t)(300000 * o.readsPerBatchFactor);          // cpp:1835
-	S.batch_pairs = o.batch_pairs ? o.batch_pairs : (1ull << 20);
-	S.batch_pairs = std::max<uint64_t>(S.batch_pairs, readsPerRefBatch / 2 + 1);
-	if (S.batch_pairs >= (1ull << 31)) { fprintf(stderr, "--batch-pairs too large\n"); return 1; }
-	S.bases_cap = S.batch_pairs * 2 * 160;
+	const uint64_t minlen = o.Cthreshold + o.ksize - 1;
+	const bool raw = !o.host_reader;
 	const int NB = 2 * G + 2;
 	std::vector<std::unique_ptr<HostBatch>> pool;
+	std::vector<std::unique_ptr<RawChunk>> rpool;
 	Channel<HostBatch*> recycle;
-	for (int i = 0; i < NB; ++i) {
-		std::unique_ptr<HostBatch> hb(new HostBatch());
-		hb->bases = (uint8_t*)dbt_host_alloc(S.bases_cap); hb->bases_cap = S.bases_cap;
-		hb->offsets = (uint64_t*)dbt_host_alloc((2 * S.batch_pairs + 1) * 8); hb->pairs_cap = S.batch_pairs;
-		if (!hb->bases || !hb->offsets) { fprintf(stderr, "cannot allocate pinned batch buffers\n"); return 1; }
-		recycle.push(hb.get());
-		pool.push_back(std::move(hb));
+	Channel<RawChunk*> rrecycle;
+	if (raw) {
+		// a submission = a chunk of raw text; it cannot hold more pairs than bytes / (two reads of the minimum length + their lines' overhead)
+		const uint64_t per_pair = 2 * (minlen + 4);
+		if (o.batch_pairs) { S.batch_pairs = o.batch_pairs; S.chunk_target = std::max<uint64_t>(o.batch_pairs * per_pair, 4096); }
+		else { S.chunk_target = (o.chunk_mb ? o.chunk_mb : 128) << 20; S.batch_pairs = S.chunk_target / per_pair + 16; }
+		if (o.batch_pairs && o.chunk_mb) S.chunk_target = o.chunk_mb << 20;
+		S.batch_pairs = std::max<uint64_t>(S.batch_pairs, (S.chunk_target + RawReader::HEADROOM) / per_pair + 16);
+		if (S.chunk_target >= (3ull << 30) || S.batch_pairs >= (1ull << 31)) { fprintf(stderr, "--chunk-mb / --batch-pairs too large (a submission stays below 3 GiB)\n"); return 1; }
+		S.pairer.reset(new StreamPairer(o.isFastq, minlen, readsPerRefBatch));
+		const uint32_t single_cap = (uint32_t)std::min<uint64_t>(std::max<uint64_t>(S.batch_pairs / 8, 1024), 1u << 22);
+		for (int i = 0; i < NB; ++i) {
+			std::unique_ptr<RawChunk> c(new RawChunk());
+			c->cap = RawReader::HEADROOM + S.chunk_target + 4096;
+			c->buf = (uint8_t*)dbt_host_alloc(c->cap + 64);
+			c->pair_offset = (uint32_t*)dbt_host_alloc(S.batch_pairs * 4); c->pair_hash = (uint64_t*)dbt_host_alloc(S.batch_pairs * 8);
+			c->single_offset = (uint32_t*)dbt_host_alloc((size_t)single_cap * 4); c->pairs_cap = (uint32_t)S.batch_pairs; c->single_cap = single_cap;
+			if (!c->buf || !c->pair_offset || !c->pair_hash || !c->single_offset) { fprintf(stderr, "cannot allocate pinned chunk buffers\n"); return 1; }
+			rrecycle.push(c.get());
+			rpool.push_back(std::move(c));
+		}
+	} else {
+		S.batch_pairs = o.batch_pairs ? o.batch_pairs : (1ull << 20);
+		S.batch_pairs = std::max<uint64_t>(S.batch_pairs, readsPerRefBatch / 2 + 1);
+		if (S.batch_pairs >= (1ull << 31)) { fprintf(stderr, "--batch-pairs too large\n"); return 1; }
+		S.bases_cap = S.batch_pairs * 2 * 160;
+		for (int i = 0; i < NB; ++i) {
+			std::unique_ptr<HostBatch> hb(new HostBatch());
+			hb->bases = (uint8_t*)dbt_host_alloc(S.bases_cap); hb->bases_cap = S.bases_cap;
+			hb->offsets = (uint64_t*)dbt_host_alloc((2 * S.batch_pairs + 1) * 8); hb->pairs_cap = S.batch_pairs;
+			if (!hb->bases || !hb->offsets) { fprintf(stderr, "cannot allocate pinned batch buffers\n"); return 1; }
+			recycle.push(hb.get());
+			pool.push_back(std::move(hb));
+		}
 	}
 
 	fprintf(stderr, "creating data for each process...\n");
@@ -248,12 +444,29 @@ int main(int argc, char** argv) {
 	std::vector<std::unique_ptr<Worker>> workers;
 	Channel<BatchOut> outq;
 	for (int i = 0; i < G; ++i) { workers.emplace_back(new Worker()); workers.back()->gpu = i; }
-	for (auto& w : workers) w->th = std::thread([&S, &outq, &recycle, wp = w.get()] { worker_main(S, *wp, outq, recycle); });
+	for (auto& w : workers) {
+		if (raw) w->th = std::thread([&S, &outq, &rrecycle, wp = w.get()] { raw_worker_main(S, *wp, outq, rrecycle); });
+		else w->th = std::thread([&S, &outq, &recycle, wp = w.get()] { worker_main(S, *wp, outq, recycle); });
+	}
 
 	// ---- reader thread (the serial section of CountWords, cpp:1885-1986) ----
-	std::atomic<uint64_t> nbatches{0};
 	std::thread reader([&] {
-		FastxReader rd(o.isFastq, o.Cthreshold + o.ksize - 1, readsPerRefBatch);
+		if (raw) {
+			// raw text in whole records; the GPU splits and pairs it (dbt_upload_raw), the StreamPairer takes what is left over
+			RawReader rd(o.isFastq);
+			if (!rd.open(o.fastxFname)) { S.fail("cannot open " + o.fastxFname); }
+			RawChunk* ch = nullptr;
+			while (!S.failed && rrecycle.pop(ch)) {
+				auto tr = Clock::now();
+				const bool got = rd.fill(*ch, S.chunk_target);
+				S.t_read_us += us_since(tr);
+				if (!got) { if (!rd.error().empty()) S.fail(o.fastxFname + ": " + rd.error()); rrecycle.push(ch); break; }
+				workers[ch->seq % G]->rin.push(ch);
+			}
+			for (auto& w : workers) w->rin.close();
+			return;
+		}
+		FastxReader rd(o.isFastq, minlen, readsPerRefBatch);
 		if (!rd.open(o.fastxFname)) { S.fail("cannot open " + o.fastxFname); }
 		uint64_t first = 0, b = 0;
 		HostBatch* hb = nullptr;
@@ -263,10 +476,10 @@ int main(int argc, char** argv) {
 			if (hb->npairs == 0) {                            // fill() made progress without emitting: the pending pair does not fit an EMPTY batch
 				S.fail("a read pair does not fit the batch buffer (raise --batch-pairs)"); recycle.push(hb); break;
 			}
+			hb->seq = b;
 			first += hb->npairs;
 			workers[b % G]->in.push(hb);
 			++b;
-			nbatches = b;
 		}
 		for (auto& w : workers) w->in.close();
 	});
@@ -274,7 +487,7 @@ int main(int argc, char** argv) {
 	// ---- writer: kam lines in batch order (cpp:2253-2279) ----
 	std::thread closer([&] { reader.join(); for (auto& w : workers) w->th.join(); outq.close(); });
 	std::map<uint64_t, BatchOut> held;
-	uint64_t next_first = 0;
+	uint64_t next_seq = 0;
 	std::vector<char> obuf(1 << 22);
 	setvbuf(stdout, obuf.data(), _IOFBF, obuf.size());
 	uint64_t tot[DBT_N_COUNTERS] = {};
@@ -290,12 +503,12 @@ int main(int argc, char** argv) {
 		        (unsigned long long)c[DBT_C_NQCFILTERED], (unsigned long long)c[DBT_C_NTHREADINGREADS], (unsigned long long)c[DBT_C_NFEASIBLEREADS],
 		        (unsigned long long)c[DBT_C_NBAITFILTERED], (unsigned long long)c[DBT_C_NASGNREADS]);
 		for (int i = 0; i < DBT_N_COUNTERS; ++i) tot[i] += c[i];
-		next_first = x.index + x.npairs;
+		next_seq = x.index + 1;
 	};
 	while (outq.pop(bo)) {
-		if (bo.index != next_first) { held.emplace(bo.index, std::move(bo)); continue; }
+		if (bo.index != next_seq) { held.emplace(bo.index, std::move(bo)); continue; }
 		emit(bo);
-		for (auto it = held.find(next_first); it != held.end(); it = held.find(next_first)) { emit(it->second); held.erase(it); }
+		for (auto it = held.find(next_seq); it != held.end(); it = held.find(next_seq)) { emit(it->second); held.erase(it); }
 	}
 	closer.join();
 	fflush(stdout);
@@ -333,6 +546,12 @@ int main(int argc, char** argv) {
 		}
 	}
 	for (auto& hb : pool) { dbt_host_free(hb->bases); dbt_host_free(hb->offsets); }
+	for (auto& c : rpool) { dbt_host_free(c->buf); dbt_host_free(c->pair_offset); dbt_host_free(c->pair_hash); dbt_host_free(c->single_offset); }
+	if (o.timing) {
+		fprintf(stderr, "[danbing-tk b200 timing] query wall %.3f s; reader %.3f s; upload+split (sync) %.3f s; pairer %.3f s; wait %.3f s; format %.3f s; chunks %llu (%llu paired on the host)\n",
+		        std::chrono::duration<double>(std::chrono::steady_clock::now() - t_query).count(), S.t_read_us / 1e6, S.t_split_us / 1e6, S.t_pair_us / 1e6, S.t_wait_us / 1e6, S.t_format_us / 1e6,
+		        (unsigned long long)S.n_chunks.load(), (unsigned long long)S.n_slow_chunks.load());
+	}
 
 	// ---- final counters (cpp:2617-2627) and outputs (cpp:2631-2656) ----
 	fprintf(stderr, "%llu reads processed in total.\n%llu reads removed by subsampled kmer-filter.\n%llu reads removed by kmer-filter.\n"

@@ -31,6 +31,9 @@ struct Options {
 	uint32_t max_read_len = 0;         // 0 = longest read of the first batch (the context is rebuilt if a longer one shows up)
 	float table_load = 0.f;
 	uint32_t bucket_slots = 0;
+	bool host_reader = false;          // --host-reader: parse and pair every record on the host (the line reader) instead of on the GPU
+	uint64_t chunk_mb = 0;             // --chunk-mb: raw text per GPU submission; 0 = auto
+	bool timing = false;               // --timing: per-phase wall times on stderr
 };
 
 inline bool file_readable(const std::string& fn) { std::ifstream f(fn); return (bool)f; }
@@ -116,6 +119,9 @@ inline std::string parse_args(int argc, char** argv, Options& o) {
 			else if (a == "--max-read-len") { if (!need(1)) return "missing value for --max-read-len"; o.max_read_len = (uint32_t)std::stoul(args[++argi]); }
 			else if (a == "--table-load") { if (!need(1)) return "missing value for --table-load"; o.table_load = std::stof(args[++argi]); }
 			else if (a == "--bucket-slots") { if (!need(1)) return "missing value for --bucket-slots"; o.bucket_slots = (uint32_t)std::stoul(args[++argi]); }
+			else if (a == "--host-reader") o.host_reader = true;
+			else if (a == "--timing") o.timing = true;
+			else if (a == "--chunk-mb") { if (!need(1)) return "missing value for --chunk-mb"; o.chunk_mb = std::stoull(args[++argi]); }
 			else return "invalid option: " + a;
 			++argi;
 		}
@@ -166,7 +172,10 @@ inline const char* usage_text() {
 	       "-B200:\n"
 	       "  --gpus <INT>          GPUs to shard the reads over (index replicated, NCCL sum at the end) [1]\n"
 	       "  --batch-pairs <INT>   read pairs per GPU submission [auto]\n"
-	       "  --max-read-len <INT>  longest read to expect [auto]\n\n";
+	       "  --max-read-len <INT>  longest read to expect [auto]\n"
+	       "  --chunk-mb <INT>      raw FASTA/FASTQ text per GPU submission, MiB [128]\n"
+	       "  --host-reader         parse and pair the reads on the host instead of on the GPU\n"
+	       "  --timing              per-phase wall times on stderr\n\n";
 }
 
 }  // namespace dbt_host

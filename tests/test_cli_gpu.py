@@ -41,12 +41,16 @@ def flags_of(run):
     return ["-k", run["k"], "-kf", run["kf"][0], run["kf"][1], "-cth", run["cth"], "-c", run["c"]]
 
 
+READERS = [pytest.param([], id="gpu-reader"), pytest.param(["--host-reader"], id="host-reader")]   # raw text split on the GPU (default) / line reader on the host
+
+
+@pytest.mark.parametrize("reader", READERS)
 @pytest.mark.parametrize("case_name,run_name", [("s1", "cth45"), ("s1", "cth10"), ("multi", "cth45"), ("multi", "kf0")])
-def test_cli_matches_golden(case_name, run_name, tmp_path):
+def test_cli_matches_golden(case_name, run_name, reader, tmp_path):
     case = golden_case(case_name)
     run = case["meta"]["runs"][run_name]
     pref, fa = stage_case(case_name, tmp_path)
-    out, err = run_cli(CLI, flags_of(run) + ["-qs", pref, "-fa", fa, "-o", tmp_path / "out"], tmp_path)
+    out, err = run_cli(CLI, flags_of(run) + reader + ["-qs", pref, "-fa", fa, "-o", tmp_path / "out"], tmp_path)
     exp = golden_outputs(case, run_name)
     assert out.decode().splitlines() == exp["kam"]
     assert np.array_equal(np.fromfile(tmp_path / "out.trkmc.ar", "<u8")[1:], exp["trkmc"])
@@ -56,12 +60,13 @@ def test_cli_matches_golden(case_name, run_name, tmp_path):
         assert c[name[6:] if name.startswith("reads ") else name] == v, name
 
 
-def test_cli_small_batches_two_slots(tmp_path):
+@pytest.mark.parametrize("reader", READERS)
+def test_cli_small_batches_two_slots(reader, tmp_path):
     """many GPU submissions (reference batches of 600 reads, 512 pairs per submission): same bytes"""
     case = golden_case("multi")
     run = case["meta"]["runs"]["cth45"]
     pref, fa = stage_case("multi", tmp_path)
-    out, err = run_cli(CLI, flags_of(run) + ["-r", 0.002, "--batch-pairs", 512, "-qs", pref, "-fa", fa, "-o", tmp_path / "out"], tmp_path)
+    out, err = run_cli(CLI, flags_of(run) + reader + ["-r", 0.002, "--batch-pairs", 512, "-qs", pref, "-fa", fa, "-o", tmp_path / "out"], tmp_path)
     exp = golden_outputs(case, "cth45")
     assert out.decode().splitlines() == exp["kam"]
     assert np.array_equal(np.fromfile(tmp_path / "out.trkmc.ar", "<u8")[1:], exp["trkmc"])
@@ -71,14 +76,16 @@ def test_cli_small_batches_two_slots(tmp_path):
 needs_ref = pytest.mark.skipif(not ref_bin("danbing-tk"), reason="oracle/_ref/danbing-tk not present")
 
 
-def both(args, tmp_path):
-    a = run_cli(CLI, args + ["-o", tmp_path / "gpu"], tmp_path)
+def both(args, tmp_path, extra=()):
+    a = run_cli(CLI, args + list(extra) + ["-o", tmp_path / "gpu"], tmp_path)
     b = run_cli(ref_bin("danbing-tk"), args + ["-o", tmp_path / "ref"], tmp_path)
     return a, b
 
 
 @needs_ref
-def test_cli_vs_reference_live_fastq_qc_and_stragglers(tmp_path):
+@pytest.mark.parametrize("extra", [pytest.param([], id="gpu-reader"), pytest.param(["--batch-pairs", 300], id="gpu-reader-small-chunks"),
+                                   pytest.param(["--host-reader"], id="host-reader")])
+def test_cli_vs_reference_live_fastq_qc_and_stragglers(extra, tmp_path):
     """FASTQ input with shuffled mates, short mates, a trailing singleton (the reference pairs it with a stale mate,
     cpp:1919-1948), -qc mask: stdout, .trkmc.ar, .tr.summary.txt and the final counters of both binaries"""
     pref, fa = stage_case("multi", tmp_path)
@@ -97,11 +104,41 @@ def test_cli_vs_reference_live_fastq_qc_and_stragglers(tmp_path):
     with open(tmp_path / "qc.txt", "w") as f:
         f.write("".join("0" if l % 4 == 1 else "1" for l in range(nloci)) + "\n")
     args = ["-k", 21, "-kf", 4, 1, "-cth", 30, "-qc", tmp_path / "qc.txt", "-qs", pref, "-fq", fq]
-    (go, ge), (ro, re_) = both(args, tmp_path)
+    (go, ge), (ro, re_) = both(args, tmp_path, extra)
     assert go == ro
     assert open(tmp_path / "gpu.trkmc.ar", "rb").read() == open(tmp_path / "ref.trkmc.ar", "rb").read()
     assert open(tmp_path / "gpu.tr.summary.txt").read() == open(tmp_path / "ref.tr.summary.txt").read()
     assert counters(ge) == counters(re_) and counters(ge)["removed by QC filter"] > 0
+
+
+@needs_ref
+@pytest.mark.parametrize("is_fastq", [False, True])
+def test_cli_vs_reference_live_collated_reads_on_the_gpu_reader(is_fastq, tmp_path):
+    """name-collated input (mates are neighbours) in many small chunks: every pair is formed on the GPU; a run of three
+    equal titles, a short last pair and a chunk border inside a pair must not change a byte"""
+    pref, fa = stage_case("multi", tmp_path)
+    lines = open(fa).read().split("\n")[:-1]
+    recs = [(lines[i], lines[i + 1]) for i in range(0, len(lines), 2)]
+    recs.insert(40, (recs[38][0][:-2] + "/1", recs[38][1]))                   # a third record of one title
+    recs += [(">tail/1", recs[0][1]), (">tail/2", recs[1][1][:20])]          # the stream ends on a pair with a short mate
+    rng = random.Random(3)
+    fx = tmp_path / ("reads.fq" if is_fastq else "reads2.fa")
+    with open(fx, "w") as f:
+        for t, s in recs:
+            if is_fastq:
+                f.write("@" + t[1:] + "\n" + s + "\n+\n" + "".join(chr(33 + rng.randrange(41)) for _ in s) + "\n")
+            else:
+                f.write(t + "\n" + s + "\n")
+    args = ["-k", 21, "-kf", 4, 1, "-cth", 30, "-qs", pref, "-fq" if is_fastq else "-fa", fx]
+    for extra in (["--batch-pairs", 256, "--timing"], []):
+        (go, ge), (ro, re_) = both(args, tmp_path, extra)
+        assert go == ro
+        assert open(tmp_path / "gpu.trkmc.ar", "rb").read() == open(tmp_path / "ref.trkmc.ar", "rb").read()
+        assert open(tmp_path / "gpu.tr.summary.txt").read() == open(tmp_path / "ref.tr.summary.txt").read()
+        assert counters(ge) == counters(re_)
+        if "--timing" in extra:
+            m = re.search(r"chunks (\d+) \((\d+) paired on the host\)", ge)
+            assert m and int(m.group(1)) > 4 and 1 <= int(m.group(2)) < int(m.group(1))   # only the chunk with the run of three left the GPU path
 
 
 @needs_ref

@@ -180,3 +180,79 @@ def test_flag_scanner(tmp_path):
     assert "thread_cth=100 maxnc=4" in r.stdout.decode() and "okam=0" in r.stdout.decode() and "fq=1 named=1" in r.stdout.decode()
     assert run("args", "-zz").stdout.startswith(b"error: invalid option: -zz")
     assert run("args", "-qs", str(tmp_path / "missing")).returncode == 1
+
+
+# ---- raw ingestion: RawReader + StreamPairer around the GPU's neighbour pairing ----
+def run_pair_raw(tmp_path, lines, is_fastq, ref_batch, target, trailing_newline=True, minlen=55):
+    fn = str(tmp_path / "reads.fx")
+    with open(fn, "w") as f:
+        f.write("\n".join(lines) + ("\n" if trailing_newline and lines else ""))
+    exp, ndb = ref_pairing(lines, bool(is_fastq), minlen, ref_batch)
+    r = run("pair-raw", fn, int(is_fastq), minlen, ref_batch, target)
+    assert r.returncode == 0, r.stderr
+    got = [tuple(l.split("\t")) for l in r.stdout.decode().split("\n")[:-1]]
+    want = [(t, s1, s2) + ((q1, q2) if is_fastq else ()) for t, s1, s2, q1, q2 in exp]
+    assert got == want, (ref_batch, target)
+    st = r.stderr.decode().split()
+    assert st[:4] == ["reads", str(2 * len(exp)), "unpaired", str(ndb)]
+    return dict(fast=int(st[5]), slow=int(st[7]))
+
+
+@pytest.mark.parametrize("is_fastq", [0, 1])
+@pytest.mark.parametrize("shuffle,singletons,trailing_newline", [(False, 0, True), (True, 3, True), (True, 1, False), (False, 1, True)])
+def test_raw_reader_and_pairer_like_the_reference(tmp_path, is_fastq, shuffle, singletons, trailing_newline):
+    """same inputs as the line reader's test, cut into chunks of 64 KB / 3 KB / 700 B so that mates, stragglers and the
+    end-of-file rules meet chunk borders"""
+    rng = random.Random(7 * is_fastq + 3 * shuffle + singletons)
+    lines = make_fastx(rng, 400, is_fastq, shuffle, singletons)
+    for ref_batch, target in ((300000, 1 << 16), (64, 3000), (64, 700), (2, 1200)):
+        st = run_pair_raw(tmp_path, lines, is_fastq, ref_batch, target, trailing_newline)
+        if not shuffle and not singletons:
+            assert st["slow"] == 0          # name-collated input never leaves the GPU path
+        # no mate is "short" at this threshold: stragglers are then paired by the host map beside the GPU's neighbour pairs
+        st = run_pair_raw(tmp_path, lines, is_fastq, ref_batch, target, trailing_newline, minlen=10)
+        assert st["slow"] == 0 and st["fast"] >= 1
+
+
+@pytest.mark.parametrize("is_fastq", [0, 1])
+def test_raw_pairer_runs_of_equal_titles_and_third_mates(tmp_path, is_fastq):
+    """three and four records with one title, a neighbour pair whose title a straggler is waiting for, duplicated pairs:
+    the order of arrival decides in the reference's map -- such chunks must come back from the host pairer identical"""
+    rng = random.Random(99 + is_fastq)
+    lines = make_fastx(rng, 120, is_fastq, False, 0)
+    L = 4 if is_fastq else 2
+    recs = [lines[i:i + L] for i in range(0, len(lines), L)]
+
+    def retitle(r, t):
+        return [r[0][0] + t] + r[1:]
+    out = []
+    for i in range(0, len(recs), 2):
+        a, b = recs[i], recs[i + 1]
+        if i % 40 == 6:
+            out += [a, b, retitle(a, b[0][1:-2] + "/1")]                     # three in a row
+        elif i % 40 == 14:
+            out += [a, b, retitle(a, b[0][1:-2] + "/1"), retitle(b, b[0][1:-2] + "/2")]   # four in a row
+        elif i % 40 == 22:
+            out += [retitle(a, "late%d/1" % i)] + recs[i + 2:i + 4] + [retitle(a, "late%d/2" % i), retitle(b, "late%d/1" % i)]   # straggler, then a neighbour pair of its title
+        else:
+            out += [a, b]
+    flat = [l for r in out for l in r]
+    for ref_batch, target in ((300000, 1 << 16), (10, 2000), (4, 900)):
+        st = run_pair_raw(tmp_path, flat, is_fastq, ref_batch, target)
+        assert st["slow"] >= 1
+
+
+@pytest.mark.parametrize("is_fastq", [0, 1])
+@pytest.mark.parametrize("drop", [1, 2, 3])
+def test_raw_reader_truncated_last_record_and_empty_input(tmp_path, is_fastq, drop):
+    """a file that ends in the middle of a record: std::getline leaves the reference's strings alone at end of file"""
+    rng = random.Random(5 + drop)
+    lines = make_fastx(rng, 30, is_fastq, False, 0)
+    L = 4 if is_fastq else 2
+    if drop >= L:
+        pytest.skip("a FASTA record has two lines")
+    for ref_batch, target in ((300000, 1 << 16), (6, 800)):
+        run_pair_raw(tmp_path, lines[:-drop], is_fastq, ref_batch, target)
+        run_pair_raw(tmp_path, lines[:L * 7 - drop], is_fastq, ref_batch, target)     # the truncated record's mate is missing
+    run_pair_raw(tmp_path, [], is_fastq, 300000, 1 << 16)
+    run_pair_raw(tmp_path, lines[:1], is_fastq, 300000, 1 << 16, trailing_newline=False)
