@@ -30,6 +30,7 @@ Two modes, both measured in the default run:
 import argparse
 import ctypes as C
 import json
+import re
 import os
 import shutil
 import subprocess
@@ -261,6 +262,8 @@ def main():
                     "as block `hbm_resident`; 0 = off")
     ap.add_argument("--hbm-pairs", type=int, default=2_000_000)
     ap.add_argument("--hbm-cpu-sample", type=int, default=200_000)
+    ap.add_argument("--file-pairs", type=int, default=2_000_000, help="block `e2e_file` (N=1): FASTA of this many pairs in /dev/shm -> the drop-in CLI -> "
+                    "outputs in /dev/shm, beside the reference binary on the same file; 0 = off")
     ap.add_argument("--rrand", action=argparse.BooleanOptionalAction, default=True,
                     help="also measure the random-sector roofline R_rand (32 B / 64 B gathers over an 8 GiB table, < 1 s) and report the "
                          "probe rate of the dominant kernel as a fraction of it")
@@ -294,12 +297,73 @@ def main():
                                                    "config", "counters_per_step_rank0")}
         if rank == 0 and world == 1 and a.hbm_loci > 0 and a.hbm_loci != a.loci and a.mode != "asgn":
             out["hbm_resident"] = hbm_resident_block(a, workdir)
+        if rank == 0 and world == 1 and a.file_pairs > 0 and a.loci == 1000:
+            out["e2e_file"] = e2e_file_block(a, pref, pool, hap_off, workdir, local)
         if rank == 0:
             print(json.dumps(out))
     finally:
         shutil.rmtree(workdir, ignore_errors=True)
         if dist is not None:
             dist.destroy_process_group()
+
+
+def e2e_file_block(a, pref, pool, hap_off, workdir, device):
+    """File to file (SURVEY §8(d) "end-to-end": FASTA bytes in the page cache -> outputs on disk): the drop-in CLI
+    (danbing-tk_b200/bin/danbing-tk: raw text -> GPU record split + pairing -> pair loop -> kam / aln lines) on a FASTA of
+    --file-pairs pairs in /dev/shm, and the unmodified reference binary on the same file with the same flags and all host cores.
+    Query phase of both = wall time minus a zero-read run (index load); the CLI's own `--timing` query wall is reported beside it."""
+    cli = os.path.join(ROOT, "danbing-tk_b200", "bin", "danbing-tk")
+    n = a.file_pairs
+    reads = np.empty(n * 2 * RLEN, np.uint8)
+    synth_reads(device, pool, hap_off, 0, n, 4242, a.frac_locus, reads, SUB_PPM, INDEL_PPM)
+    fa = os.path.join(workdir, "file.fa")
+    write_fasta_sample(fa, reads, n)
+    del reads
+    empty = os.path.join(workdir, "file.empty.fa")
+    open(empty, "w").close()
+    nproc = os.cpu_count() or 1
+    blk = {"pairs": n, "fasta_bytes": os.path.getsize(fa), "host_cores": nproc,
+           "what": "FASTA in /dev/shm -> CLI -> stdout file + OUT.trkmc.ar + OUT.tr.summary.txt in /dev/shm; query phase = wall minus a zero-read run"}
+
+    def timed(cmd, out_fn):
+        t0 = time.perf_counter()
+        with open(out_fn, "wb") as so:
+            r = subprocess.run(cmd, stdout=so, stderr=subprocess.PIPE)
+        if r.returncode:
+            raise RuntimeError(f"{cmd[0]} failed: {r.stderr.decode()[-500:]}")
+        return time.perf_counter() - t0, r.stderr.decode()
+
+    def cli_run(flags, tag):
+        base = [cli] + flags + ["-p", str(nproc), "--timing", "-qs", pref]
+        t_load, _ = timed(base + ["-fa", empty, "-o", os.path.join(workdir, tag + ".e")], os.path.join(workdir, tag + ".e.out"))
+        t_all, err = timed(base + ["-fa", fa, "-o", os.path.join(workdir, tag)], os.path.join(workdir, tag + ".out"))
+        m = re.search(r"query wall ([0-9.]+) s; reader ([0-9.]+) s; upload\+split \(sync\) ([0-9.]+) s; pairer ([0-9.]+) s; wait ([0-9.]+) s; format ([0-9.]+) s; chunks (\d+) \((\d+) paired", err)
+        q = float(m.group(1)) if m else None
+        d = {"pairs_per_s": n / max(t_all - t_load, 1e-9), "wall_s": t_all, "load_s": t_load, "query_wall_s_cli": q,
+             "pairs_per_s_cli_query_wall": (n / q) if q else None, "stdout_bytes": os.path.getsize(os.path.join(workdir, tag + ".out"))}
+        if m:
+            d["phases_s"] = dict(zip(("reader", "upload+split", "pairer", "wait", "format"), map(float, m.groups()[1:6])))
+            d["chunks"], d["chunks_paired_on_host"] = int(m.group(7)), int(m.group(8))
+        return d
+    asgn = ["-k", str(K), "-kf", "4", "1", "-cth", str(CTH)]
+    blk["asgn"] = cli_run(asgn, "f_asgn")
+    blk["thread"] = cli_run(asgn + (["-gc", "85", "3"] if CORR else ["-g", "85"]) + ["-ae"], "f_thr")
+    blk["asgn_host_reader"] = cli_run(asgn + ["--host-reader"], "f_asgn_hr")
+    exe = ref_bin("danbing-tk")
+    if exe and not a.no_cpu:
+        base = [exe] + asgn + ["-p", str(nproc), "-qs", pref]
+        t_load, _ = timed(base + ["-fa", empty, "-o", os.path.join(workdir, "f_ref.e")], os.path.join(workdir, "f_ref.e.out"))
+        t_all, _ = timed(base + ["-fa", fa, "-o", os.path.join(workdir, "f_ref")], os.path.join(workdir, "f_ref.out"))
+        ref_rate = n / max(t_all - t_load, 1e-9)
+        same = all(open(os.path.join(workdir, "f_asgn" + e), "rb").read() == open(os.path.join(workdir, "f_ref" + e), "rb").read()
+                   for e in (".trkmc.ar", ".tr.summary.txt"))
+        # stdout: the reference's threads print their kam lines in completion order; compare as sorted lines
+        same_kam = sorted(open(os.path.join(workdir, "f_asgn.out"), "rb").read().split(b"\n")) == sorted(open(os.path.join(workdir, "f_ref.out"), "rb").read().split(b"\n"))
+        blk["reference_binary"] = {"pairs_per_s": ref_rate, "wall_s": t_all, "load_s": t_load, "threads": nproc,
+                                   "flags": "same as `asgn` (graph threading is dead code in the unmodified binary, SURVEY F2)",
+                                   "outputs_identical": {"trkmc_ar_and_summary": same, "kam_lines_as_multiset": same_kam}}
+        blk["speedup_vs_reference_binary"] = blk["asgn"]["pairs_per_s"] / ref_rate
+    return blk
 
 
 def hbm_resident_block(a, workdir):

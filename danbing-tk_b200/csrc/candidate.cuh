@@ -345,7 +345,7 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 	const uint32_t gwarp = blockIdx.x * WPB + wib;
 	const uint32_t nwarps = gridDim.x * WPB;
 	const uint32_t W64 = rp.lay.W64, WB = rp.lay.WB, K = rp.k, NKP = rp.nkp, UMAX = rp.umax;
-	const bool okam = (rp.flags & DBT_F_KAM) != 0 && !rp.thr_on, trace = (rp.flags & DBT_F_TRACE) != 0;   // no kam lines with threading (cpp:2110)
+	const bool okam = (rp.flags & (DBT_F_KAM | DBT_F_EXTRACT)) != 0 && !rp.thr_on, trace = (rp.flags & DBT_F_TRACE) != 0;   // no kam lines with threading (cpp:2110)
 	const bool wstat = okam || (rp.thr_on && (rp.flags & (DBT_F_ALN | DBT_F_ALN_MIN)));
 
 	// ---- shared-memory carve-up (per warp); dbt_create mirrors the sizes ----
@@ -637,6 +637,10 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 					}
 				} else { status = DBT_ST_NOT_THREADED; if (lane == 0) c_thr0 += 2; }   // cpp:2070-2090 at HEAD
 			}
+			if (status < 0 && (rp.flags & DBT_F_EXTRACT)) {       // `-e`: the pair is handed out as it is, nothing is counted (cpp:2094-2099)
+				if (lane == 0) c_thr += 2;
+				status = DBT_ST_COUNTED;
+			}
 			if (status < 0) {
 				if (lane == 0) c_thr += 2;
 				// assignTRkmc (cpp:1450-1556) against the tables of destLocus0
@@ -685,7 +689,7 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 				}
 			}
 			// record
-			const bool emit = trace || (okam && status == DBT_ST_COUNTED);
+			const bool emit = trace || (okam && (status == DBT_ST_COUNTED || ((rp.flags & DBT_F_SIM) && status == DBT_ST_ASGN_REMOVED)));
 			if (!emit && wstat && c < rp.max_records) {
 				// the slot of a candidate that prints no kam line must not keep a stale record
 				if (lane == 0) reinterpret_cast<dbt_pair_record*>(sv.records + (uint64_t)c * rp.rec_stride)->status = (uint8_t)status;

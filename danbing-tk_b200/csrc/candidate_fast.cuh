@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
 	const uint32_t gwarp = blockIdx.x * CAND_FAST_WARPS + wib, nwarps = gridDim.x * CAND_FAST_WARPS;
 	const uint32_t W64 = rp.lay.W64, WB = rp.lay.WB, K = rp.k;
-	const bool okam = (rp.flags & DBT_F_KAM) != 0 && !rp.thr_on;       // kam lines are only written without threading (cpp:2110)
+	const bool okam = (rp.flags & (DBT_F_KAM | DBT_F_EXTRACT)) != 0 && !rp.thr_on;   // kam lines are only written without threading (cpp:2110); `-e` records ride the same slots
 	const bool wstat = okam || (rp.thr_on && (rp.flags & (DBT_F_ALN | DBT_F_ALN_MIN)));   // record slots are keyed by candidate ordinal: keep their status current
 	const uint32_t nloci = (uint32_t)ix.nloci, cth = rp.cth;
 	FastWarp<B, MAXJ>& W = wsm[wib];
@@ -289,6 +289,19 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 				if (lane == 0) { c_thr0 += 2; sv.thr[atomicAdd(sv.ncand + 3, 1u)] = make_uint4(c, p, dst | (kfm << 28) | (rmm << 30), 0u); }
 			} else { status = DBT_ST_NOT_THREADED; if (lane == 0) c_thr0 += 2; }   // cpp:2070-2090 at HEAD
 		}
+		if (status < 0 && (rp.flags & DBT_F_EXTRACT)) {           // `-e`: the pair is handed out as it is, nothing is counted (cpp:2094-2099)
+			if (lane == 0) {
+				c_thr += 2;
+#pragma unroll 1
+				for (int m = 0; m < 2; ++m) {
+					dbt_mate_record& o = W.mate[m];
+					o.si = o.ei = o.si_ = o.ei_ = o.ti = -1; o.nt = 0; o.bs = 0; o.pad = 0; o.nk = 0;
+					o.flags = (uint8_t)((((kfm >> m) & 1u) ? DBT_MF_KF : 0) | (((rmm >> m) & 1u) ? DBT_MF_RM : 0));
+				}
+			}
+			__syncwarp();
+			status = DBT_ST_COUNTED;
+		}
 		if (status < 0) {
 			if (lane == 0) c_thr += 2;
 			int span = 0;
@@ -356,8 +369,8 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 
 		// ---- kam record (cpp:2169-2175); slot = candidate ordinal, compacted by dbt_wait ----
 		if (wstat) {
-			if (c >= rp.max_records) { if (lane == 0 && status == DBT_ST_COUNTED) atomicOr(sv.ncand + 1, ERR_RECORD_OVERFLOW); }
-			else if (status != DBT_ST_COUNTED) {
+			if (c >= rp.max_records) { if (lane == 0 && (status == DBT_ST_COUNTED || ((rp.flags & DBT_F_SIM) && status == DBT_ST_ASGN_REMOVED))) atomicOr(sv.ncand + 1, ERR_RECORD_OVERFLOW); }
+			else if (status != DBT_ST_COUNTED && !((rp.flags & DBT_F_SIM) && status == DBT_ST_ASGN_REMOVED)) {
 				if (lane == 0) reinterpret_cast<dbt_pair_record*>(sv.records + (uint64_t)c * rp.rec_stride)->status = (uint8_t)status;
 			} else {
 				uint8_t* rec = sv.records + (uint64_t)c * rp.rec_stride;

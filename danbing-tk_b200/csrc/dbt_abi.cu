@@ -283,8 +283,6 @@ static int ensure_slot(dbt_ctx* c, int si) {
 	const RunParams& rp = c->rp;
 	const uint64_t P = c->p.max_batch_pairs;
 	CU(cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking));
-	TRY(dev_alloc(&s.d_ascii, (size_t)2 * P * rp.max_read_len + 16, "ascii"));
-	TRY(dev_alloc(&s.d_offsets, 2 * P + 1, "offsets"));
 	for (int m = 0; m < 2; ++m) { TRY(dev_alloc(&s.d_packed[m], P * rp.lay.W64, "packed")); TRY(dev_alloc(&s.d_meta[m], P, "meta")); }
 	const uint64_t nwords = (P + 31) / 32;
 	TRY(dev_alloc(&s.d_passmask, nwords, "passmask"));
@@ -294,11 +292,9 @@ static int ensure_slot(dbt_ctx* c, int si) {
 	TRY(dev_alloc(&s.d_slow, P, "slow list"));
 	if (rp.thr_on) { TRY(dev_alloc(&s.d_thr, P, "thread list")); TRY(dev_alloc(&s.d_thr2, P, "thread list 2")); }
 	TRY(dev_alloc(&s.d_counters, DBT_N_COUNTERS, "counters"));
-	const bool want_records = rp.thr_on ? (c->p.flags & (DBT_F_ALN | DBT_F_ALN_MIN | DBT_F_TRACE)) != 0 : (c->p.flags & (DBT_F_KAM | DBT_F_TRACE)) != 0;
+	const bool want_records = rp.thr_on ? (c->p.flags & (DBT_F_ALN | DBT_F_ALN_MIN | DBT_F_TRACE)) != 0 : (c->p.flags & (DBT_F_KAM | DBT_F_EXTRACT | DBT_F_TRACE)) != 0;
 	if (want_records) {
 		TRY(dev_alloc(&s.d_records, (size_t)c->p.max_records * rp.rec_stride, "records"));
-		cudaError_t e = cudaHostAlloc((void**)&s.h_records, std::max<size_t>((size_t)c->p.max_records * rp.rec_stride, 16), cudaHostAllocDefault);
-		if (e != cudaSuccess) { cudaGetLastError(); return fail(DBT_E_NOMEM, "cudaHostAlloc(records): %s", cudaGetErrorString(e)); }
 		if (!(c->p.flags & DBT_F_TRACE)) {
 			const uint64_t ew = ((uint64_t)c->p.max_records + 31) / 32;
 			TRY(dev_alloc(&s.d_records_out, (size_t)c->p.max_records * rp.rec_stride, "records (dense)"));
@@ -566,6 +562,14 @@ static SlotView slot_view(const dbt_ctx* c, const Slot& s) {
 	return v;
 }
 
+// pinned staging for records: only a pageable caller buffer or DBT_F_TRACE needs it
+static int ensure_h_records(dbt_ctx* c, Slot& s) {
+	if (s.h_records) return DBT_OK;
+	cudaError_t e = cudaHostAlloc((void**)&s.h_records, std::max<size_t>((size_t)c->p.max_records * c->rp.rec_stride, 16), cudaHostAllocDefault);
+	if (e != cudaSuccess) { cudaGetLastError(); return fail(DBT_E_NOMEM, "cudaHostAlloc(records): %s", cudaGetErrorString(e)); }
+	return DBT_OK;
+}
+
 static int check_slot(dbt_ctx* c, int slot) {
 	if (!c) return fail(DBT_E_BADARG, "null context");
 	if (slot < 0 || slot >= DBT_N_SLOTS) return fail(DBT_E_BADARG, "slot %d out of range", slot);
@@ -589,6 +593,10 @@ extern "C" int dbt_upload(dbt_ctx* c, const dbt_batch* b, int slot) {
 			if (!b->offsets) return fail(DBT_E_BADARG, "null offsets");
 			const uint64_t nbytes = b->offsets[2 * b->npairs] - b->offsets[0];
 			if (nbytes > (uint64_t)2 * c->p.max_batch_pairs * rp.max_read_len) return fail(DBT_E_CAPACITY, "batch holds %llu bases, more than max_batch_pairs*2*max_read_len", (unsigned long long)nbytes);
+			if (!s.d_ascii) {                                   // first ASCII batch of the slot (raw-text submissions never need these)
+				TRY(dev_alloc(&s.d_ascii, (size_t)2 * c->p.max_batch_pairs * rp.max_read_len + 16, "ascii"));
+				TRY(dev_alloc(&s.d_offsets, 2 * (size_t)c->p.max_batch_pairs + 1, "offsets"));
+			}
 			CU(cudaMemcpyAsync(s.d_ascii, b->bases + b->offsets[0], nbytes, cudaMemcpyHostToDevice, s.st));
 			CU(cudaMemcpyAsync(s.d_offsets, b->offsets, (2 * b->npairs + 1) * 8, cudaMemcpyHostToDevice, s.st));
 			// offsets are used relative to bases: shift by offsets[0] inside the kernel via pointer arithmetic
@@ -641,6 +649,15 @@ static int ensure_raw(dbt_ctx* c, Slot& s, uint64_t nbytes) {
 	TRY(dev_alloc(&s.d_pairmask, max_recs / 32 + 8, "pair bitmap")); TRY(dev_alloc(&s.d_singlemask, max_recs / 32 + 8, "singleton bitmap"));
 	TRY(dev_alloc(&s.d_pairlist, max_recs + 8, "pair list")); TRY(dev_alloc(&s.d_singlelist, max_recs + 8, "singleton list"));
 	s.raw_cap = cap; s.raw_max_lines = (uint32_t)max_lines; s.raw_max_recs = (uint32_t)max_recs;
+	return DBT_OK;
+}
+
+extern "C" int dbt_prepare(dbt_ctx* c, uint64_t raw_bytes) {
+	if (!c) return fail(DBT_E_BADARG, "null context");
+	for (int i = 0; i < DBT_N_SLOTS; ++i) {
+		TRY(check_slot(c, i));
+		if (raw_bytes) TRY(ensure_raw(c, c->slot[i], raw_bytes));
+	}
 	return DBT_OK;
 }
 
@@ -747,9 +764,9 @@ extern "C" int dbt_fetch(dbt_ctx* c, dbt_batch_result* r, int slot) {
 	s.emitted = false;
 	if (s.d_records_out && r->records && s.npairs) {          // kam / aln records: compact on the device, in slot (= pair) order
 		const bool thr = c->rp.thr_on != 0, aln_min = (c->p.flags & DBT_F_ALN_MIN) != 0;
-		const bool okam = thr ? (c->p.flags & (DBT_F_ALN | DBT_F_ALN_MIN)) != 0 : (c->p.flags & DBT_F_KAM) != 0;
+		const bool okam = thr ? (c->p.flags & (DBT_F_ALN | DBT_F_ALN_MIN)) != 0 : (c->p.flags & (DBT_F_KAM | DBT_F_EXTRACT)) != 0;
 		if (okam) {
-			CU(launch_record_emit(s.st, c->nsm, s.d_records, c->rp.rec_stride, s.d_ncand, c->p.max_records, (thr && !aln_min) ? 1 : 0,
+			CU(launch_record_emit(s.st, c->nsm, s.d_records, c->rp.rec_stride, s.d_ncand, c->p.max_records, ((thr && !aln_min) ? 1 : 0) | ((!thr && (c->p.flags & DBT_F_SIM)) ? 2 : 0),
 			                      s.d_emitmask, s.d_emitsum, s.d_emitlist, s.d_nemit, s.d_records_out));
 			c->launches += 5;
 			CU(cudaMemcpyAsync(reinterpret_cast<uint32_t*>(s.h_counters + DBT_N_COUNTERS + 2), s.d_nemit, 4, cudaMemcpyDeviceToHost, s.st));
@@ -784,7 +801,7 @@ extern "C" int dbt_wait(dbt_ctx* c, int slot) {
 	r->n_records = 0;
 	const bool thr = c->rp.thr_on != 0;
 	const bool aln_min = (c->p.flags & DBT_F_ALN_MIN) != 0, aln = (c->p.flags & (DBT_F_ALN | DBT_F_ALN_MIN)) != 0;
-	const bool trace = (c->p.flags & DBT_F_TRACE) != 0, okam = thr ? aln : (c->p.flags & DBT_F_KAM) != 0;
+	const bool trace = (c->p.flags & DBT_F_TRACE) != 0, okam = thr ? aln : (c->p.flags & (DBT_F_KAM | DBT_F_EXTRACT)) != 0;
 	int rc = DBT_OK;
 	if (s.emitted) {
 		// dense records are already in slot order on the device: one copy straight into the caller's buffer
@@ -797,6 +814,7 @@ extern "C" int dbt_wait(dbt_ctx* c, int slot) {
 			cudaPointerAttributes pa{};
 			const bool pinned = cudaPointerGetAttributes(&pa, r->records) == cudaSuccess && pa.type == cudaMemoryTypeHost;
 			if (!pinned) cudaGetLastError();
+			if (!pinned) TRY(ensure_h_records(c, s));
 			CU(cudaMemcpyAsync(pinned ? r->records : s.h_records, s.d_records_out, bytes, cudaMemcpyDeviceToHost, s.st));
 			CU(cudaStreamSynchronize(s.st));
 			if (!pinned) memcpy(r->records, s.h_records, bytes);
@@ -807,6 +825,7 @@ extern "C" int dbt_wait(dbt_ctx* c, int slot) {
 		const uint64_t nslots = trace ? s.npairs : std::min<uint64_t>(ncand, c->p.max_records);
 		const uint32_t stride = c->rp.rec_stride;
 		if (nslots) {
+			TRY(ensure_h_records(c, s));
 			CU(cudaMemcpyAsync(s.h_records, s.d_records, nslots * stride, cudaMemcpyDeviceToHost, s.st));
 			CU(cudaStreamSynchronize(s.st));
 		}
@@ -815,7 +834,7 @@ extern "C" int dbt_wait(dbt_ctx* c, int slot) {
 			const uint8_t* src = s.h_records + i * stride;
 			const uint8_t stt = reinterpret_cast<const dbt_pair_record*>(src)->status;
 			// kam line / `-ae`: counted pairs only; `-a`: every pair that entered threading (cpp:2232-2239)
-			if (!trace && stt != DBT_ST_COUNTED && !(thr && !aln_min && stt == DBT_ST_THREAD_FAILED)) continue;
+			if (!trace && stt != DBT_ST_COUNTED && !(thr && !aln_min && stt == DBT_ST_THREAD_FAILED) && !(!thr && (c->p.flags & DBT_F_SIM) && stt == DBT_ST_ASGN_REMOVED)) continue;
 			if (n >= r->capacity) { rc = fail(DBT_E_CAPACITY, "result buffer holds %llu records, more are pending", (unsigned long long)r->capacity); break; }
 			memcpy(r->records + n * stride, src, stride);
 			++n;

@@ -285,7 +285,8 @@ __global__ void __launch_bounds__(256) compact_scatter_kernel(const uint32_t* __
 // record emission (dbt_fetch): which record slots become kam / aln records -> ordered emit list -> dense copy.
 // Replaces a per-record host memcpy loop in dbt_wait (360 MB per 10 M-pair step in threading mode).
 // ============================================================================================
-// slot i < min(*nslots, cap): emit iff COUNTED, or THREAD_FAILED when `emit_failed` (`-a`: every pair that entered threading, cpp:2232-2239)
+// slot i < min(*nslots, cap): emit iff COUNTED, or THREAD_FAILED when `emit_failed` & 1 (`-a`: every pair that entered threading,
+// cpp:2232-2239), or ASGN_REMOVED when `emit_failed` & 2 (`-s`: kam lines of removed pairs with a known source locus, cpp:2169)
 __global__ void __launch_bounds__(256) record_flag_kernel(const uint8_t* __restrict__ records, uint32_t stride, const uint32_t* __restrict__ nslots,
                                                          uint32_t cap, int emit_failed, uint32_t* __restrict__ mask) {
 	const uint32_t n = min(*nslots, cap);
@@ -293,7 +294,7 @@ __global__ void __launch_bounds__(256) record_flag_kernel(const uint8_t* __restr
 	bool e = false;
 	if (i < n) {
 		const uint8_t st = reinterpret_cast<const dbt_pair_record*>(records + (size_t)i * stride)->status;
-		e = st == DBT_ST_COUNTED || (emit_failed && st == DBT_ST_THREAD_FAILED);
+		e = st == DBT_ST_COUNTED || ((emit_failed & 1) && st == DBT_ST_THREAD_FAILED) || ((emit_failed & 2) && st == DBT_ST_ASGN_REMOVED);
 	}
 	const uint32_t b = __ballot_sync(0xffffffffu, e);
 	if ((threadIdx.x & 31) == 0 && i < ((cap + 31) / 32) * 32) mask[i >> 5] = b;

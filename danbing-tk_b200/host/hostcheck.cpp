@@ -58,7 +58,7 @@ static int cmd_index_sum(const std::string& pref) {
 // RawReader + StreamPairer with the GPU's record split (csrc/fastx.cu) restated on the host for the test: neighbours with
 // equal pruned titles pair up, runs of three raise the slow-path flag, the rest are singletons.  Prints the pairs in output order.
 static int cmd_pair_raw(const char* fn, bool fq, uint64_t minlen, uint64_t refbatch, uint64_t target) {
-	RawReader rd(fq);
+	RawReader rd(fq, target >= (4u << 20) ? 4 : 1);
 	if (!rd.open(fn)) { fprintf(stderr, "cannot open %s\n", fn); return 1; }
 	RawChunk c;
 	c.cap = RawReader::HEADROOM + target + 4096;

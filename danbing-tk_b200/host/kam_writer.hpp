@@ -39,11 +39,31 @@ inline void append_fields(std::string& o, const dbt_mate_record& r) {
 }
 
 // rec: one record of dbt_record_stride bytes; t: the text of its pair (HostBatch, or the raw chunk the GPU split)
-inline void append_kam_line(std::string& o, const uint8_t* rec, uint32_t as_stride, const PairText& t, bool isFastq) {
+// `-s 1|2`: the source locus a simulated read carries in its (pruned) title.  simmode 1: ">LOCUS.rest" (parseReadName,
+// cpp:477-489); simmode 2: ">CHR:START-END:LOCUS", LOCUS "." = not from a locus = nloci (cpp:492-506).  -2: malformed.
+inline long long sim_source_locus(const PairText& t, int simmode, uint64_t nloci) {
+	const std::string title(t.title, t.title_len);
+	char* e = nullptr;
+	if (simmode == 1) {
+		if (title.size() < 2) return -2;
+		const unsigned long v = strtoul(title.c_str() + 1, &e, 10);
+		return e == title.c_str() + 1 ? -2 : (long long)v;
+	}
+	const size_t p1 = title.find(':');
+	const size_t p2 = p1 == std::string::npos ? p1 : title.find(':', p1 + 1);
+	if (p2 == std::string::npos || p2 + 1 >= title.size()) return -2;
+	if (title[p2 + 1] == '.') return (long long)nloci;
+	const unsigned long long v = strtoull(title.c_str() + p2 + 1, &e, 10);
+	return e == title.c_str() + p2 + 1 ? -2 : (long long)(int)v;          // meta holds it as int (cpp:492)
+}
+
+// src < 0: no `-s` (the column reads "."); with `-s` the caller drops a record unless src != nloci or dst != nloci (cpp:2169)
+inline void append_kam_line(std::string& o, const uint8_t* rec, uint32_t as_stride, const PairText& t, bool isFastq, long long src = -1) {
 	const dbt_pair_record* h = reinterpret_cast<const dbt_pair_record*>(rec);
 	const dbt_mate_record& r1 = h->mate[0];
 	const dbt_mate_record& r2 = h->mate[1];
-	o.append(".\t");                                   // src: unknown without -s (cpp:1653)
+	if (src < 0) o.push_back('.'); else append_int(o, src);   // cpp:1653
+	o.push_back('\t');
 	append_int(o, h->dst); o.push_back('\t');
 	append_int(o, (h->dst0 != h->dst) ? (long long)(int)h->dst0 : -1); o.push_back('\t');   // km_asgn_t::assign (cpp:115-119), int fields
 	append_int(o, (int)r2.ei - (int)r2.si); o.push_back('\t');
@@ -62,6 +82,18 @@ inline void append_kam_line(std::string& o, const uint8_t* rec, uint32_t as_stri
 	if (isFastq) o.append(t.qual[0], t.qual_len[0]); else o.push_back('.');
 	o.push_back('\n');
 }
+// `-e 1|2`: writeExtractedReads, cpp:1618-1644 -- read 2 first, then read 1, both under the pair's title; `-e 2` appends ":<locus>"
+inline void append_extracted(std::string& o, const uint8_t* rec, const PairText& t, bool isFastq, int mode) {
+	const dbt_pair_record* h = reinterpret_cast<const dbt_pair_record*>(rec);
+	for (int m = 1; m >= 0; --m) {
+		o.append(t.title, t.title_len);
+		if (mode == 2) { o.push_back(':'); append_int(o, h->dst); }
+		o.push_back('\n');
+		o.append(t.seq[m], t.seq_len[m]); o.push_back('\n');
+		if (isFastq) { o.append("+\n"); o.append(t.qual[m], t.qual_len[m]); o.push_back('\n'); }
+	}
+}
+
 inline void append_kam_line(std::string& o, const uint8_t* rec, uint32_t as_stride, const HostBatch& hb, bool isFastq) {
 	const uint64_t i = reinterpret_cast<const dbt_pair_record*>(rec)->pair_index - hb.first_pair_index;
 	append_kam_line(o, rec, as_stride, pair_text(hb, i, isFastq), isFastq);

@@ -89,10 +89,24 @@ struct Worker {
 	uint32_t ctx_len = 0;
 	Channel<HostBatch*> in;
 	Channel<RawChunk*> rin;
+	uint8_t* recs[DBT_N_SLOTS] = {};                                             // raw path: pinned record buffers of the two slots
 	std::vector<uint64_t> acc_tr, acc_kmc; std::vector<uint32_t> acc_nmap;      // counts of contexts retired by a rebuild
 	uint64_t acc_cnt[DBT_N_COUNTERS] = {};
 	std::thread th;
 };
+
+// one kam line, or none: with `-s` a record is printed when its read name carries a source locus or the pair was assigned (cpp:2169)
+bool append_kam_checked(Shared& S, std::string& o, const uint8_t* rec, uint32_t as_stride, const PairText& t) {
+	long long src = -1;
+	if (S.opt.simmode) {
+		src = sim_source_locus(t, S.opt.simmode, S.rpgg.nloci);
+		if (src == -2) { S.fail("-s " + std::to_string(S.opt.simmode) + ": cannot read the source locus from read name " + std::string(t.title, t.title_len)); return false; }
+		const dbt_pair_record* h = reinterpret_cast<const dbt_pair_record*>(rec);
+		if (!(src != (long long)S.rpgg.nloci || h->dst != S.rpgg.nloci)) return true;
+	}
+	append_kam_line(o, rec, as_stride, t, S.opt.isFastq, src);
+	return true;
+}
 
 std::string dbt_err(const char* what, int rc) { return std::string(what) + ": " + dbt_strerror(rc) + ": " + dbt_last_error(); }
 
@@ -102,7 +116,7 @@ bool make_ctx(Shared& S, Worker& w, uint32_t max_len) {
 	const Options& o = S.opt;
 	p.device = w.gpu; p.k = (uint32_t)o.ksize; p.n_filter = (uint32_t)o.N_FILTER; p.nm_filter = (uint32_t)o.NM_FILTER;
 	p.cth = (uint32_t)o.Cthreshold; p.nm_tr = (uint32_t)o.NM_TR; p.thread_cth = (uint32_t)o.thread_cth; p.max_ncorrection = (uint32_t)o.maxncorrection;
-	p.flags = (o.okam ? DBT_F_KAM : 0) | (o.qc ? DBT_F_QC : 0) | (o.threading ? DBT_F_THREADING : 0) | (o.threading && o.correction ? DBT_F_CORRECTION : 0) |
+	p.flags = (o.extractFastX ? DBT_F_EXTRACT : (o.okam ? DBT_F_KAM : 0)) | (o.simmode ? DBT_F_SIM : 0) | (o.qc ? DBT_F_QC : 0) | (o.threading ? DBT_F_THREADING : 0) | (o.threading && o.correction ? DBT_F_CORRECTION : 0) |
 	          (o.aln ? DBT_F_ALN : 0) | (o.aln_minimal ? DBT_F_ALN_MIN : 0);
 	p.max_read_len = max_len; p.max_batch_pairs = (uint32_t)S.batch_pairs; p.max_records = (uint32_t)S.batch_pairs;
 	p.table_load = o.table_load; p.bucket_slots = o.bucket_slots;
@@ -110,6 +124,8 @@ bool make_ctx(Shared& S, Worker& w, uint32_t max_len) {
 	if (rc) { S.fail(dbt_err("dbt_create", rc)); return false; }
 	rc = dbt_load_index(w.ctx, &S.index);
 	if (rc) { S.fail(dbt_err("dbt_load_index", rc)); return false; }
+	rc = dbt_prepare(w.ctx, S.chunk_target ? S.chunk_target + RawReader::HEADROOM : 0);     // slot and splitter buffers now, not inside the first batches
+	if (rc) { S.fail(dbt_err("dbt_prepare", rc)); return false; }
 	w.ctx_len = max_len;
 	return true;
 }
@@ -145,11 +161,19 @@ void worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<HostBatch
 		if (S.want_records && f.res.n_records) {
 			const uint32_t stride = dbt_record_stride(w.ctx), as_stride = dbt_record_as_stride(w.ctx);
 			bo.text.reserve((size_t)f.res.n_records * 520);
-			if (S.thr_graph) {
+			if (S.opt.extractFastX) {
+				for (uint64_t i = 0; i < f.res.n_records; ++i) {
+					const uint8_t* rec = f.recs.data() + i * stride;
+					append_extracted(bo.text, rec, pair_text(*f.hb, reinterpret_cast<const dbt_pair_record*>(rec)->pair_index - f.hb->first_pair_index, S.opt.isFastq), S.opt.isFastq, S.opt.extractFastX);
+				}
+			} else if (S.thr_graph) {
 				const uint32_t aln_stride = dbt_record_aln_stride(w.ctx), es_cap = dbt_record_es_cap(w.ctx);
 				for (uint64_t i = 0; i < f.res.n_records; ++i) append_aln_line(bo.text, f.recs.data() + i * stride, aln_stride, es_cap, *f.hb);
 			} else
-				for (uint64_t i = 0; i < f.res.n_records; ++i) append_kam_line(bo.text, f.recs.data() + i * stride, as_stride, *f.hb, S.opt.isFastq);
+				for (uint64_t i = 0; i < f.res.n_records; ++i) {
+					const uint8_t* rec = f.recs.data() + i * stride;
+					if (!append_kam_checked(S, bo.text, rec, as_stride, pair_text(*f.hb, reinterpret_cast<const dbt_pair_record*>(rec)->pair_index - f.hb->first_pair_index, S.opt.isFastq))) return false;
+				}
 		}
 		bo.seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - f.t0).count();
 		recycle.push(f.hb);
@@ -194,7 +218,7 @@ static uint64_t us_since(Clock::time_point t0) { return (uint64_t)std::chrono::d
 void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawChunk*>& recycle) {
 	struct Inflight {
 		RawChunk* ch = nullptr; bool gpu = false; dbt_raw_info info{}; dbt_batch_result res{};
-		uint8_t* recs = nullptr; StreamPairer::Extra ex;
+		StreamPairer::Extra ex;
 		uint64_t nreads_total = 0, unpaired = 0; Clock::time_point t0;
 	};
 	Inflight fl[DBT_N_SLOTS];
@@ -206,13 +230,13 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 		if (!retire_ctx(S, w)) return false;
 		uint32_t L = std::max<uint32_t>({need_len, S.opt.max_read_len, (uint32_t)S.opt.ksize, 150u});
 		if (w.ctx_len) L = std::max<uint32_t>(L, w.ctx_len + w.ctx_len / 4);
-		for (auto& g : fl) if (g.recs) { dbt_host_free(g.recs); g.recs = nullptr; }   // sized for the old record stride
+		for (auto& r : w.recs) if (r) { dbt_host_free(r); r = nullptr; }             // sized for the old record stride
 		return make_ctx(S, w, L);
 	};
-	auto ensure_recs = [&](Inflight& f) -> bool {
-		if (!S.want_records || f.recs) return true;
-		f.recs = (uint8_t*)dbt_host_alloc((size_t)S.batch_pairs * dbt_record_stride(w.ctx));
-		if (!f.recs) { S.fail("cannot allocate pinned record buffer"); return false; }
+	auto ensure_recs = [&](int s) -> bool {
+		if (!S.want_records || w.recs[s]) return true;
+		w.recs[s] = (uint8_t*)dbt_host_alloc((size_t)S.batch_pairs * dbt_record_stride(w.ctx));
+		if (!w.recs[s]) { S.fail("cannot allocate pinned record buffer"); return false; }
 		return true;
 	};
 	finish = [&](int s) -> bool {
@@ -234,15 +258,16 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 		auto format = [&](std::string& o, const uint8_t* rec, bool from_gpu) {
 			const uint64_t pi = reinterpret_cast<const dbt_pair_record*>(rec)->pair_index;
 			const PairText t = from_gpu ? pair_text_raw(ch->text(), ch->pair_offset[pi], fq) : pair_text(xb, pi, fq);
-			if (S.thr_graph) append_aln_line(o, rec, dbt_record_aln_stride(w.ctx), dbt_record_es_cap(w.ctx), t);
-			else append_kam_line(o, rec, dbt_record_as_stride(w.ctx), t, fq);
+			if (S.opt.extractFastX) append_extracted(o, rec, t, fq, S.opt.extractFastX);
+			else if (S.thr_graph) append_aln_line(o, rec, dbt_record_aln_stride(w.ctx), dbt_record_es_cap(w.ctx), t);
+			else append_kam_checked(S, o, rec, dbt_record_as_stride(w.ctx), t);
 		};
 		auto tf = Clock::now();
 		if (!xb.npairs) {
 			if (S.want_records && ngpu) {
 				const uint32_t stride = dbt_record_stride(w.ctx);
 				bo.text.reserve((size_t)ngpu * 520);
-				for (uint64_t i = 0; i < ngpu; ++i) format(bo.text, f.recs + i * stride, true);
+				for (uint64_t i = 0; i < ngpu; ++i) format(bo.text, w.recs[s] + i * stride, true);
 			}
 		} else {
 			// Pairs the host pairer formed for this chunk: an ordinary ASCII batch on the same slot, its lines merged into the
@@ -253,7 +278,7 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 				const uint32_t stride = dbt_record_stride(w.ctx);
 				lines.reserve(ngpu + xb.npairs);
 				for (uint64_t i = 0; i < ngpu; ++i) {
-					const uint8_t* rec = f.recs + i * stride;
+					const uint8_t* rec = w.recs[s] + i * stride;
 					lines.emplace_back((uint64_t)ch->pair_offset[reinterpret_cast<const dbt_pair_record*>(rec)->pair_index], std::string());
 					format(lines.back().second, rec, true);
 				}
@@ -295,7 +320,7 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 		bool use_gpu = ch->nbytes() > 0, ok = true;
 		if (use_gpu) {
 			if (!w.ctx && !make_ctx(S, w, std::max<uint32_t>({S.opt.max_read_len, (uint32_t)S.opt.ksize, 150u}))) break;
-			if (!ensure_recs(f)) break;
+			if (!ensure_recs(s)) break;
 			auto ts = Clock::now();
 			for (int attempt = 0; attempt < 2; ++attempt) {
 				dbt_raw_batch rb{};
@@ -304,7 +329,7 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 				const int rc = dbt_upload_raw(w.ctx, &rb, &f.info, s);
 				if (rc == DBT_OK) break;
 				if (rc == DBT_E_CAPACITY && f.info.max_read_len > w.ctx_len && attempt == 0) {
-					if (!rebuild(f.info.max_read_len, s) || !ensure_recs(f)) { ok = false; break; }
+					if (!rebuild(f.info.max_read_len, s) || !ensure_recs(s)) { ok = false; break; }
 					continue;
 				}
 				S.fail(dbt_err("dbt_upload_raw", rc)); ok = false; break;
@@ -331,16 +356,16 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 		if (!ok || S.failed) { recycle.push(ch); break; }
 		f.ch = ch;
 		if (f.gpu) {
-			if (!ensure_recs(f)) break;
+			if (!ensure_recs(s)) break;
 			f.res = dbt_batch_result{};
-			f.res.capacity = S.want_records ? S.batch_pairs : 0; f.res.records = S.want_records ? f.recs : nullptr;
+			f.res.capacity = S.want_records ? S.batch_pairs : 0; f.res.records = S.want_records ? w.recs[s] : nullptr;
 			int rc = dbt_process(w.ctx, s);
 			if (!rc) rc = dbt_fetch(w.ctx, &f.res, s);
 			if (rc) { S.fail(dbt_err("dbt_process", rc)); break; }
 		}
 	}
 	if (!S.failed) for (int s = 0; s < DBT_N_SLOTS; ++s) { const int ss = (k + s) & 1; if (!finish(ss)) break; }
-	for (auto& f : fl) if (f.recs) dbt_host_free(f.recs);
+	for (auto& r : w.recs) if (r) { dbt_host_free(r); r = nullptr; }
 	if (S.failed) { recycle.close(); S.turn.cv.notify_all(); }
 }
 
@@ -353,8 +378,8 @@ int main(int argc, char** argv) {
 	std::string err = parse_args(argc, argv, o);
 	if (!err.empty()) { fprintf(stderr, "%s\n", err.c_str()); return 1; }
 	if (o.trPrefix.empty() || o.fastxFname.empty() || o.outPrefix.empty()) { fprintf(stderr, "-qs, -fa|-fq and -o|-on are required\n"); return 1; }
-	for (const char* unsupported : {o.bait ? "-b" : "", o.outputBubbles ? "-bu" : "", o.trackBait ? "-tb" : "", o.extractFastX ? "-e" : "",
-	                                o.simmode ? "-s" : "", o.g2pan ? "-m" : "", o.aug ? "-au" : "", o.trim ? "-t" : "", o.invkmer ? "-ik" : ""})
+	for (const char* unsupported : {o.bait ? "-b" : "", o.outputBubbles ? "-bu" : "", o.trackBait ? "-tb" : "",
+	                                o.g2pan ? "-m" : "", o.aug ? "-au" : "", o.trim ? "-t" : "", o.invkmer ? "-ik" : ""})
 		if (*unsupported) { fprintf(stderr, "option %s is not part of the B200 align path (SURVEY.md 8(f)); use the reference binary for it\n", unsupported); return 1; }
 	if (o.ksize < 1 || o.ksize > 27) { fprintf(stderr, "-k %llu unsupported (1..27)\n", (unsigned long long)o.ksize); return 1; }
 	report_parameters(o, stderr);
@@ -391,7 +416,9 @@ int main(int argc, char** argv) {
 			fprintf(stderr, "[danbing-tk b200] graph threading restored: %llu nodes\n", (unsigned long long)g.g_kmers.size());
 		}
 	}
-	S.want_records = S.thr_graph ? o.aln : o.okam;
+	if (o.extractFastX && S.thr_graph) { fprintf(stderr, "\n-e with a graph in the RPGG (restored threading) is outside the reference's behaviour; drop -g/-gc or the graph file\n"); return 1; }
+	if (o.extractFastX && o.extractFastX != 1 && o.extractFastX != 2) { fprintf(stderr, "\n-e takes 1 or 2\n"); return 1; }
+	S.want_records = o.extractFastX ? true : (S.thr_graph ? o.aln : o.okam);
 	fprintf(stderr, "0 bait loci in baitDB\ndeserialized graph/index and read tr.kmers in %lld sec.\n# unique kmers in kmerDBi: %llu\n",
 	        (long long)std::chrono::duration_cast<std::chrono::seconds>(std::chrono::steady_clock::now() - t_load).count(), (unsigned long long)g.dbi_keys.size());
 
@@ -440,10 +467,22 @@ int main(int argc, char** argv) {
 	}
 
 	fprintf(stderr, "creating data for each process...\n");
-	auto t_query = std::chrono::steady_clock::now();
 	std::vector<std::unique_ptr<Worker>> workers;
 	Channel<BatchOut> outq;
 	for (int i = 0; i < G; ++i) { workers.emplace_back(new Worker()); workers.back()->gpu = i; }
+	{	// the device-resident index of every GPU is part of loading the RPGG (cpp:2484-2504), not of the query phase
+		auto t_ctx = std::chrono::steady_clock::now();
+		const uint32_t L0 = std::max<uint32_t>({o.max_read_len, (uint32_t)o.ksize, 150u});
+		std::vector<std::thread> th;
+		for (auto& w : workers) th.emplace_back([&S, L0, raw, wp = w.get()] {
+			if (!make_ctx(S, *wp, L0) || !raw || !S.want_records) return;
+			for (auto& r : wp->recs) { r = (uint8_t*)dbt_host_alloc((size_t)S.batch_pairs * dbt_record_stride(wp->ctx)); if (!r) S.fail("cannot allocate pinned record buffer"); }
+		});
+		for (auto& t : th) t.join();
+		if (S.failed) { fprintf(stderr, "danbing-tk: %s\n", S.err.c_str()); return 1; }
+		if (o.timing) fprintf(stderr, "[danbing-tk b200 timing] device index built on %d GPU(s) in %.3f s\n", G, std::chrono::duration<double>(std::chrono::steady_clock::now() - t_ctx).count());
+	}
+	auto t_query = std::chrono::steady_clock::now();
 	for (auto& w : workers) {
 		if (raw) w->th = std::thread([&S, &outq, &rrecycle, wp = w.get()] { raw_worker_main(S, *wp, outq, rrecycle); });
 		else w->th = std::thread([&S, &outq, &recycle, wp = w.get()] { worker_main(S, *wp, outq, recycle); });
@@ -453,7 +492,7 @@ int main(int argc, char** argv) {
 	std::thread reader([&] {
 		if (raw) {
 			// raw text in whole records; the GPU splits and pairs it (dbt_upload_raw), the StreamPairer takes what is left over
-			RawReader rd(o.isFastq);
+			RawReader rd(o.isFastq, (int)std::min<uint64_t>(std::max<uint64_t>(o.nproc, 1), 16));
 			if (!rd.open(o.fastxFname)) { S.fail("cannot open " + o.fastxFname); }
 			RawChunk* ch = nullptr;
 			while (!S.failed && rrecycle.pop(ch)) {
@@ -563,6 +602,7 @@ int main(int argc, char** argv) {
 	        (unsigned long long)tot[DBT_C_NQCFILTERED], (unsigned long long)tot[DBT_C_NTHREADINGREADS], (unsigned long long)tot[DBT_C_NFEASIBLEREADS],
 	        (unsigned long long)tot[DBT_C_NASGNREADS],
 	        (long long)std::chrono::duration_cast<std::chrono::seconds>(std::chrono::steady_clock::now() - t_query).count());
+	if (o.extractFastX) { fprintf(stderr, "all done!\n"); return 0; }      // cpp:2631: extraction writes no count files
 	fprintf(stderr, "writing kmers...\n");
 	bool ok;
 	if (o.writeKmerName) ok = write_kmers_with_name(o.outPrefix + ".tr.kmers", g, counts, err);

@@ -22,7 +22,9 @@
 #include <vector>
 #include <fcntl.h>
 #include <unistd.h>
+#include <sys/stat.h>
 #include <algorithm>
+#include <thread>
 #if defined(__x86_64__)
 #include <immintrin.h>
 #endif
@@ -69,9 +71,15 @@ struct RawChunk {
 class RawReader {
 public:
 	static constexpr uint64_t HEADROOM = 1 << 20;     // carried records are copied in front of the freshly read bytes
-	explicit RawReader(bool isFastq) : L_(isFastq ? 4 : 2) {}
+	explicit RawReader(bool isFastq, int nthreads = 1) : L_(isFastq ? 4 : 2), nthreads_(std::max(1, nthreads)) {}
 	~RawReader() { if (fd_ > 0) close(fd_); }
-	bool open(const std::string& fn) { fd_ = ::open(fn.c_str(), O_RDONLY); return fd_ >= 0; }
+	bool open(const std::string& fn) {
+		fd_ = ::open(fn.c_str(), O_RDONLY);
+		if (fd_ < 0) return false;
+		struct stat st;
+		if (fstat(fd_, &st) == 0 && S_ISREG(st.st_mode)) { regular_ = true; size_ = (uint64_t)st.st_size; }   // pipes / stdin: one sequential read
+		return true;
+	}
 	const std::string& error() const { return err_; }
 
 	// Fills c with the next chunk (about `target` fresh bytes).  false: nothing more (or error(): non-empty).
@@ -83,15 +91,41 @@ public:
 		const uint64_t start = HEADROOM - carry_.size();
 		memcpy(c.buf + start, carry_.data(), carry_.size());
 		uint64_t have = HEADROOM;                     // bytes [start, have) are valid
-		while (have - HEADROOM < target && !src_eof_) {
-			const ssize_t r = ::read(fd_, c.buf + have, (size_t)std::min<uint64_t>(target - (have - HEADROOM), 1u << 30));
-			if (r < 0) { err_ = "read error"; done_ = true; return false; }
-			if (r == 0) { src_eof_ = true; break; }
-			have += (uint64_t)r;
+		uint64_t nl = 0;
+		if (regular_ && nthreads_ > 1) {
+			// a regular file: the chunk's byte range is read by nthreads_ threads at once (pread), each counting its newlines
+			const uint64_t want = std::min<uint64_t>(target, size_ - std::min(size_, off_));
+			const int T = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)nthreads_, want >> 20));
+			const uint64_t part = (want + T - 1) / T;
+			std::vector<uint64_t> cnt(T, 0); std::vector<int> bad(T, 0);
+			auto work = [&](int i) {
+				uint64_t a = std::min(want, part * i), b = std::min(want, part * (i + 1));
+				while (a < b) {
+					const ssize_t r = ::pread(fd_, c.buf + HEADROOM + a, (size_t)std::min<uint64_t>(b - a, 1u << 30), (off_t)(off_ + a));
+					if (r <= 0) { bad[i] = 1; return; }
+					cnt[i] += count_nl(c.buf + HEADROOM + a, (size_t)r);
+					a += (uint64_t)r;
+				}
+			};
+			std::vector<std::thread> th;
+			for (int i = 1; i < T; ++i) th.emplace_back(work, i);
+			work(0);
+			for (auto& t : th) t.join();
+			for (int i = 0; i < T; ++i) { if (bad[i]) { err_ = "read error (file truncated while reading?)"; done_ = true; return false; } nl += cnt[i]; }
+			have += want; off_ += want;
+			if (off_ >= size_) src_eof_ = true;
+			nl += count_nl(c.buf + start, HEADROOM - start);
+		} else {
+			while (have - HEADROOM < target && !src_eof_) {
+				const ssize_t r = ::read(fd_, c.buf + have, (size_t)std::min<uint64_t>(target - (have - HEADROOM), 1u << 30));
+				if (r < 0) { err_ = "read error"; done_ = true; return false; }
+				if (r == 0) { src_eof_ = true; break; }
+				have += (uint64_t)r;
+			}
+			nl = count_nl(c.buf + start, have - start);
 		}
-		if (src_eof_ && have > start && c.buf[have - 1] != '\n') c.buf[have++] = '\n';   // std::getline hands out an unterminated last line too
+		if (src_eof_ && have > start && c.buf[have - 1] != '\n') { c.buf[have++] = '\n'; ++nl; }   // std::getline hands out an unterminated last line too
 		c.seq = seq_++; c.eof = false; c.tail.clear(); c.begin = start;
-		const uint64_t nl = count_nl(c.buf + start, have - start);
 		const uint64_t nrec = nl / L_;
 		const uint64_t rec_end = back_lines(c.buf, start, have, nl % L_);   // end of the last complete record
 		if (src_eof_) {
@@ -115,7 +149,8 @@ public:
 	}
 
 private:
-	uint32_t L_;
+	uint32_t L_; int nthreads_;
+	bool regular_ = false; uint64_t size_ = 0, off_ = 0;
 	int fd_ = -1; bool src_eof_ = false, done_ = false;
 	std::string carry_; uint64_t seq_ = 0;
 	std::string err_;

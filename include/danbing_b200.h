@@ -51,6 +51,10 @@ extern "C" {
 #define DBT_F_CORRECTION 0x010u /* `-gc` error-correcting threading                            */
 #define DBT_F_ALN        0x020u /* `-a`                                                        */
 #define DBT_F_ALN_MIN    0x040u /* `-ae`                                                       */
+#define DBT_F_SIM        0x100u /* `-s 1|2` (cpp:2169): kam records also for pairs whose both mates assignTRkmc removed (dst = nloci); the
+                                   caller prints them when the read name carries a source locus */
+#define DBT_F_EXTRACT    0x080u /* `-e 1|2` (cpp:2094-2099, 1618-1644): a pair that passes the locus vote and the QC gate is
+                                   handed out as a record (status COUNTED, dst = its locus, no annotation) and NOTHING is counted */
 
 /* ---- per-pair status (dbt_pair_record.status); order = the order of the exits in cpp:2035-2145 */
 #define DBT_ST_SHORT       0   /* a mate has no valid k-mer window            (cpp:2037)       */
@@ -280,6 +284,8 @@ typedef struct {
   uint32_t* single_offset; uint32_t single_cap;
 } dbt_raw_batch;
 int  dbt_upload_raw(dbt_ctx*, const dbt_raw_batch*, dbt_raw_info* info, int slot);
+/* optional: allocate both slots (and, raw_bytes > 0, the splitter's buffers for texts of that size) now instead of on first use */
+int  dbt_prepare(dbt_ctx*, uint64_t raw_bytes);
 uint64_t dbt_title_hash(const uint8_t* title, size_t len);     /* FNV-1a 64 of the pruned title, as the device computes it */
 /* [0] H2D + split kernels [1] pack_kernel of the slot's last dbt_upload_raw, milliseconds */
 int  dbt_raw_times(dbt_ctx*, int slot, float ms[2]);

@@ -217,3 +217,56 @@ def test_cli_threading_without_alignment_output_and_legacy_graph_umap(tmp_path):
     assert out == b""
     gold_tr = np.frombuffer(gzip.open(os.path.join(GOLD, "out.trkmc.ar.gz")).read(), "<u8")
     assert np.array_equal(np.fromfile(tmp_path / "out.trkmc.ar", "<u8"), gold_tr)
+
+
+# ---- the remaining align flags, byte for byte against the live reference ----
+def retitled(fa, tmp_path, title_of, is_fastq=False, name="reads_t"):
+    lines = open(fa).read().split("\n")[:-1]
+    rng = random.Random(17)
+    fx = tmp_path / (name + (".fq" if is_fastq else ".fa"))
+    with open(fx, "w") as f:
+        for i in range(0, len(lines), 4):                          # two records = one pair
+            t = title_of(i // 4)
+            for m, (s, tag) in enumerate(((lines[i + 1], "/1"), (lines[i + 3], "/2"))):
+                if is_fastq:
+                    f.write("@" + t + tag + "\n" + s + "\n+\n" + "".join(chr(33 + rng.randrange(41)) for _ in s) + "\n")
+                else:
+                    f.write(">" + t + tag + "\n" + s + "\n")
+    return fx
+
+
+@needs_ref
+@pytest.mark.parametrize("mode", [1, 2])
+@pytest.mark.parametrize("is_fastq", [False, True])
+def test_cli_vs_reference_live_extract_reads(mode, is_fastq, tmp_path):
+    """`-e 1|2` (cpp:2094-2099, 1618-1644): pairs that pass the locus vote are written out as FASTA/FASTQ, nothing is counted"""
+    pref, fa = stage_case("multi", tmp_path)
+    fx = retitled(fa, tmp_path, lambda i: f"frag{i}", is_fastq)
+    args = ["-k", 21, "-kf", 4, 1, "-cth", 30, "-e", mode, "-qs", pref, "-fq" if is_fastq else "-fa", fx]
+    for extra in ([], ["--batch-pairs", 300], ["--host-reader"]):
+        (go, ge), (ro, re_) = both(args, tmp_path, extra)
+        assert go == ro and len(go) > 10000
+        assert counters(ge) == counters(re_) and counters(ge)["passsed threading"] > 0
+        assert not os.path.exists(tmp_path / "gpu.tr.summary.txt")
+
+
+@needs_ref
+@pytest.mark.parametrize("simmode", [1, 2])
+def test_cli_vs_reference_live_simulation_truth_in_kam(simmode, tmp_path):
+    """`-s 1|2` (cpp:476-524, 2169): the source locus read off the read name fills the first kam column, and pairs that
+    assignTRkmc removed are printed too when their source locus is known"""
+    pref, fa = stage_case("multi", tmp_path)
+    nloci = golden_case("multi")["ix"]["nloci"]
+    if simmode == 1:
+        title_of = lambda i: f"{(i // 7) % nloci}.frag{i}"
+    else:
+        title_of = lambda i: f"chr1:{i}-{i + 150}:" + ("." if (i // 5) % 4 == 3 else str((i // 5) % nloci))
+    fx = retitled(fa, tmp_path, title_of)
+    args = ["-k", 21, "-kf", 4, 1, "-cth", 30, "-c", 1000, "-s", simmode, "-qs", pref, "-fa", fx]   # -c 1000: spanning reads are removed by assignTRkmc
+    for extra in ([], ["--batch-pairs", 300], ["--host-reader"]):
+        (go, ge), (ro, re_) = both(args, tmp_path, extra)
+        assert go == ro and len(go) > 10000
+        assert open(tmp_path / "gpu.trkmc.ar", "rb").read() == open(tmp_path / "ref.trkmc.ar", "rb").read()
+        assert counters(ge) == counters(re_)
+    removed = [l for l in go.decode().splitlines() if l.split("\t")[1] == str(nloci)]
+    assert removed, "no removed pair with a known source locus in this input: the test does not exercise cpp:2169"

@@ -256,3 +256,10 @@ def test_raw_reader_truncated_last_record_and_empty_input(tmp_path, is_fastq, dr
         run_pair_raw(tmp_path, lines[:L * 7 - drop], is_fastq, ref_batch, target)     # the truncated record's mate is missing
     run_pair_raw(tmp_path, [], is_fastq, 300000, 1 << 16)
     run_pair_raw(tmp_path, lines[:1], is_fastq, 300000, 1 << 16, trailing_newline=False)
+
+
+def test_raw_reader_parallel_pread(tmp_path):
+    """a regular file is read by several threads at once (pread): same chunks, same pairs"""
+    rng = random.Random(31)
+    lines = make_fastx(rng, 30000, 0, False, 0)
+    run_pair_raw(tmp_path, lines, 0, 300000, 5 << 20)
