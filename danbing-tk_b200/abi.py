@@ -23,10 +23,10 @@ COUNTER_NAMES = ["nReads", "nShort", "nSubFiltered", "nKmerFiltered", "nBaitFilt
                  "nhash0", "nhash1", "ninc", "ncandidates", "nrecords",
                  "gen_pairs", "gen_nhash1", "gen_nThreadingReads", "gen_ninc",
                  "thr_walk", "thr_ec", "thr_cls", "thr_refresh",
-                 "thr2_pairs", "thr2_mates", "thr2_walk", "thr2_cls", "thr2_ninc", "thr2_refresh", "reserved30", "reserved31"]
+                 "thr2_pairs", "thr2_mates", "thr2_walk", "thr2_cls", "thr2_ninc", "thr2_refresh", "thr1_fixed", "reserved31"]
 MEASUREMENT_COUNTERS = ("nrecords", "gen_pairs", "gen_nhash1", "gen_nThreadingReads", "gen_ninc",
                         "thr_walk", "thr_ec", "thr_cls", "thr_refresh",
-                        "thr2_pairs", "thr2_mates", "thr2_walk", "thr2_cls", "thr2_ninc", "thr2_refresh", "reserved30", "reserved31")   # no reference counterpart
+                        "thr2_pairs", "thr2_mates", "thr2_walk", "thr2_cls", "thr2_ninc", "thr2_refresh", "thr1_fixed", "reserved31")   # no reference counterpart
 MF_KF, MF_HF, MF_BF, MF_QF, MF_AF, MF_RM = 1, 2, 4, 8, 16, 32
 
 u64p = C.POINTER(C.c_uint64)

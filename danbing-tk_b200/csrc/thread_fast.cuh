@@ -57,6 +57,9 @@ __device__ __noinline__ GNode g_lookup_canon_nl(const Table gt, uint64_t canon, 
 	}
 }
 
+template <int B>
+__device__ __noinline__ GNode g_lookup_fast_nl(const Table gt, uint64_t fw, uint32_t locus, uint32_t k) { return g_lookup<B>(gt, fw, locus, k); }
+
 template <int B, int MAXJ>
 struct FastThreadWarp {
 	uint4    stage[MAXJ][B][32];               // home (then stash) buckets of every position of the mate being probed
@@ -65,6 +68,7 @@ struct FastThreadWarp {
 	uint8_t  nb[MAXJ * 32 + 32];               // nb[i + 1] = present | out-edge mask << 1 of position i (nb[0]: unused)
 	uint64_t pk[2 * MAXJ + 6];                 // packed record of the mate (W64 <= 1.5 MAXJ + 4 for reads of <= MAXJ*32 k-mers)
 	uint32_t T[MAXJ];                          // TR ballots
+	uint32_t ok[MAXJ];                         // "on an out-edge of its predecessor" ballots (position 0: is a node)
 };
 
 template <int B, int MAXJ>
@@ -80,7 +84,8 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 	const uint32_t W64 = rp.lay.W64, WB = rp.lay.WB, K = rp.k;
 	const Table gt = ix.gtable;
 	const uint64_t kmask = (1ull << (2 * K)) - 1, vmask = (1ull << K) - 1;
-	uint32_t c_fea = 0, c_inc = 0, c_cls = 0, c_walk = 0, c_probe = 0, c_items = 0;   // lane-0 accumulators (c_probe: per lane, reduced at the end)
+	uint32_t c_fea = 0, c_inc = 0, c_cls = 0, c_walk = 0, c_probe = 0, c_items = 0, c_fix = 0, c_ec = 0;   // lane-0 accumulators (c_probe: per lane, reduced at the end)
+	const bool correction1 = rp.correction != 0 && rp.max_ncorrection >= 1;
 
 	uint4 item = gwarp < nwork ? sv.thr[gwarp] : make_uint4(0, 0, 0, 0);
 #pragma unroll 1
@@ -209,11 +214,77 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 					ok = i == 0 ? (W.nb[1] & 1u) != 0 : ((pb & 1u) && ((pb >> (1 + f3)) & 1u));
 					tr = W.trx[i] != 0;
 				}
-				if (!__all_sync(0xffffffffu, ok)) clean = false;
+				const uint32_t bo = __ballot_sync(0xffffffffu, ok);
+				if (bo != 0xffffffffu) clean = false;
 				const uint32_t bt = __ballot_sync(0xffffffffu, tr);
-				if (lane == 0) W.T[j] = bt;
+				if (lane == 0) { W.T[j] = bt; W.ok[j] = bo; }
 			}
 			__syncwarp();
+			int xpos = -1; uint32_t xbase = 0;                                // fixed mate: CIGAR entry xpos is 'X' with graph base xbase (1-4)
+			if (!clean && correction1) {
+				// ---- one substitution in the interior of the read, graph without a branch there ----
+				// The walk (cpp:1167-1180) stops at the first k-mer ki that is not on an out-edge of its predecessor.  If that
+				// predecessor has ONE out-edge a, the k-mer with its last base replaced by a is a node whose one out-edge is the
+				// next read base, and the k following k-mers with that base replaced (the last of them is the read's own k-mer
+				// ki+k) form a path, then errorCorrection_forward (cpp:898-1089) scores the 1-mismatch edit `a` with the full
+				// extension k: no other edit can score more (every family's walk is at most k steps long here) and this one comes
+				// first in thread_ext_t::get_edit's scan (cpp:628-647).  edit_kmers_forward (cpp:828-862) rewrites exactly those
+				// k k-mers and one CIGAR entry; if every k-mer after them was already on an out-edge of its predecessor the read
+				// threads with one correction (isThreadFeasible returns 2).  Everything else is thread_kernel's.
+				int ki = nkm;
+#pragma unroll 1
+				for (int j = ng - 1; j >= 0; --j) { const uint32_t z = ~W.ok[j]; if (z) ki = j * 32 + __ffs(z) - 1; }
+				bool cand = ki >= 1 && ki + (int)K + 2 <= nkm && (uint32_t)nkm > rp.thread_cth;   // anchored at 0; k+2 k-mers remain; one skip allowed (cpp:1194)
+				if (cand) {
+#pragma unroll 1
+					for (int j = (ki + (int)K + 1) >> 5; j < ng && cand; ++j) {       // every k-mer past the rewritten ones matches already
+						const int lo = max(ki + (int)K + 1 - j * 32, 0), n = min(32, nkm - j * 32);
+						const uint32_t want = (n == 32 ? 0xFFFFFFFFu : (1u << n) - 1u) & (0xFFFFFFFFu << lo);
+						if ((W.ok[j] & want) != want) cand = false;
+					}
+				}
+				const uint32_t pm = cand ? (uint32_t)(W.nb[ki] >> 1) & 0xFu : 0u;   // out-edges of k-mer ki-1
+				if (cand && __popc(pm) == 1) {
+					const uint32_t a = (uint32_t)__ffs(pm) - 1u;
+					const int t = lane;                                           // lane t < k: k-mer ki+t with the wrong base (2t bits up) replaced
+					uint64_t c = 0; uint32_t bits = 0, trp = 0, f3n = 0;
+					if (t < (int)K) {
+						const uint64_t kw = W.key[ki + t];
+						const uint64_t cn = kw & kmask;
+						const uint64_t fw = (kw & THRF_RCFLAG) ? kmer_rc(cn, K) : cn;
+						c = (fw & ~(3ull << (2 * t))) | ((uint64_t)a << (2 * t));
+						const GNode g = g_lookup_fast_nl<B>(gt, c, dst, K);
+						bits = g.bits; trp = g.tr;
+						++c_probe;
+						f3n = (uint32_t)(W.key[ki + t + 1] >> THRF_F3_SHIFT) & 3u;   // last base of the next k-mer (ki + t + 1 < nkm)
+					}
+					// lane t (< k): present, and the next k-mer's last base is an out-edge (lane 0: its ONLY out-edge, the level-2
+					// expansion of the scorer then holds just that base, cpp:907-920)
+					bool good = true;
+					if (t < (int)K) {
+						const uint32_t mk = gn_mask(bits);
+						good = (bits & GN_PRESENT) && ((mk >> f3n) & 1u) && (t != 0 || __popc(mk) == 1);
+					}
+					if (__all_sync(0xffffffffu, good)) {
+						if (t < (int)K) {
+							const uint64_t rc = kmer_rc(c, K);
+							const bool is_rc = rc < c;
+							W.key[ki + t] = (is_rc ? rc : c) | ((c & 3) << THRF_F3_SHIFT) | (is_rc ? THRF_RCFLAG : 0ull);
+							W.trx[ki + t] = trp;
+						}
+						__syncwarp();
+#pragma unroll 1
+						for (int j = ki >> 5; j <= (ki + (int)K - 1) >> 5; ++j) {     // TR ballots of the groups that changed
+							const int i = j * 32 + lane;
+							const uint32_t bt = __ballot_sync(0xffffffffu, i < nkm && W.trx[i] != 0);
+							if (lane == 0) W.T[j] = bt;
+						}
+						__syncwarp();
+						clean = true; xpos = ki + (int)K - 1; xbase = a + 1;
+						if (lane == 0) { ++c_fix; c_ec += K + 2; }               // look-ups of the scorer's winning path: 1 + 1 expansion nodes + k walk steps
+					}
+				}
+			}
 			if (!clean) { dirty |= 1u << m; continue; }
 
 			// ---- clean mate: alned = 1, es all '=', tr from the TR ballots; count its TR k-mers (D1) ----
@@ -242,7 +313,9 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 				for (int q = lane; q < (int)rp.es_cap / 4; q += 32) {         // four entries per lane and store; entries >= nes read 0
 					const int nbb = nes - 4 * q;
 					const uint32_t keep = nbb >= 4 ? 0xFFFFFFFFu : (nbb <= 0 ? 0u : (1u << 8 * nbb) - 1u);
-					reinterpret_cast<uint32_t*>(es)[q] = (0x01010101u * ET_EQ) & keep;
+					uint32_t v = 0x01010101u * ET_EQ;
+					if (xpos >= 0 && (xpos >> 2) == q) v = (v & ~(0xFFu << (8 * (xpos & 3)))) | ((uint32_t)(ET_X | (xbase << 3)) << (8 * (xpos & 3)));
+					reinterpret_cast<uint32_t*>(es)[q] = v & keep;
 				}
 #pragma unroll 1
 				for (int q = lane; q < (int)rp.tr_cap / 4; q += 32) {         // tr[i] = '=' (2) for TR k-mers, '.' (1) otherwise: 4 TR ballot bits -> 4 bytes
@@ -254,7 +327,7 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 				}
 				if (lane == 0) {
 					dbt_aln_mate* h = reinterpret_cast<dbt_aln_mate*>(b);
-					h->alned = 1; h->err = (uint8_t)((int)len > (int)rp.es_cap || nkm > (int)rp.tr_cap);
+					h->alned = xpos >= 0 ? 2 : 1; h->err = (uint8_t)((int)len > (int)rp.es_cap || nkm > (int)rp.tr_cap);
 					h->nes = (uint16_t)len; h->ntr = (uint16_t)nkm; h->nkm = (uint16_t)nkm;
 					uint64_t hash = 0;
 					if (trace) {                                                // FNV-1a over the k-mer vector (parity tests only)
@@ -300,6 +373,8 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 		if (c_fea) atomicAdd(sv.counters + DBT_C_NFEASIBLEREADS, (unsigned long long)c_fea);
 		if (c_inc) atomicAdd(sv.counters + DBT_C_NINC, (unsigned long long)c_inc);
 		if (c_items) atomicAdd(sv.counters + DBT_C_THR2_PAIRS, (unsigned long long)c_items);
+		if (c_fix) atomicAdd(sv.counters + DBT_C_THR1_FIXED, (unsigned long long)c_fix);
+		if (c_ec) atomicAdd(sv.counters + DBT_C_THR_EC, (unsigned long long)c_ec);
 	}
 }
 

@@ -73,6 +73,7 @@ struct Shared {
 	std::unique_ptr<StreamPairer> pairer; PairTurn turn;
 	uint64_t chunk_target = 0;          // raw text bytes per GPU submission
 	std::atomic<uint64_t> t_split_us{0}, t_pair_us{0}, t_wait_us{0}, t_format_us{0}, t_read_us{0}, n_slow_chunks{0}, n_chunks{0};
+	std::atomic<uint64_t> t_launch_us{0}, t_write_us{0}, t_reader_blocked_us{0}, t_worker_idle_us{0}, t_turn_us{0};
 	Rpgg rpgg;
 	dbt_index index{};
 	uint64_t batch_pairs = 0, bases_cap = 0;
@@ -266,8 +267,24 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 		if (!xb.npairs) {
 			if (S.want_records && ngpu) {
 				const uint32_t stride = dbt_record_stride(w.ctx);
-				bo.text.reserve((size_t)ngpu * 520);
-				for (uint64_t i = 0; i < ngpu; ++i) format(bo.text, w.recs[s] + i * stride, true);
+				const int T = (int)std::min<uint64_t>(std::min<uint64_t>(std::max<uint64_t>(S.opt.nproc, 1), 16), ngpu / 8192 + 1);   // -p host threads format the lines
+				if (T <= 1) {
+					bo.text.reserve((size_t)ngpu * 520);
+					for (uint64_t i = 0; i < ngpu; ++i) format(bo.text, w.recs[s] + i * stride, true);
+				} else {
+					std::vector<std::string> part(T);
+					std::vector<std::thread> th;
+					for (int t = 0; t < T; ++t) th.emplace_back([&, t] {
+						const uint64_t a = ngpu * t / T, b = ngpu * (t + 1) / T;
+						part[t].reserve((size_t)(b - a) * 520);
+						for (uint64_t i = a; i < b; ++i) format(part[t], w.recs[s] + i * stride, true);
+					});
+					for (auto& x : th) x.join();
+					size_t tot = 0;
+					for (auto& x : part) tot += x.size();
+					bo.text.reserve(tot);
+					for (auto& x : part) bo.text += x;
+				}
 			}
 		} else {
 			// Pairs the host pairer formed for this chunk: an ordinary ASCII batch on the same slot, its lines merged into the
@@ -312,7 +329,10 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 	RawChunk* ch = nullptr;
 	int k = 0;
 	const uint32_t minlen = (uint32_t)(S.opt.Cthreshold + S.opt.ksize - 1);
-	while (!S.failed && w.rin.pop(ch)) {
+	for (;;) {
+		auto ti = Clock::now();
+		if (S.failed || !w.rin.pop(ch)) break;
+		S.t_worker_idle_us += us_since(ti);
 		const int s = k++ & 1;
 		if (!finish(s)) break;
 		Inflight& f = fl[s];
@@ -338,8 +358,10 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 		}
 		// the chunk's turn at the pairer (stream order over all GPUs)
 		{
+			auto tt = Clock::now();
 			std::unique_lock<std::mutex> l(S.turn.m);
 			S.turn.cv.wait(l, [&] { return S.turn.next == ch->seq || S.failed; });
+			S.t_turn_us += us_since(tt);
 			if (ok && !S.failed) {
 				auto tp = Clock::now();
 				const bool fast = S.pairer->chunk(*ch, use_gpu, f.info.flags, f.info.npairs, f.info.nsingle, f.info.nshort_pairs, f.ex);
@@ -359,8 +381,10 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 			if (!ensure_recs(s)) break;
 			f.res = dbt_batch_result{};
 			f.res.capacity = S.want_records ? S.batch_pairs : 0; f.res.records = S.want_records ? w.recs[s] : nullptr;
+			auto tl = Clock::now();
 			int rc = dbt_process(w.ctx, s);
 			if (!rc) rc = dbt_fetch(w.ctx, &f.res, s);
+			S.t_launch_us += us_since(tl);
 			if (rc) { S.fail(dbt_err("dbt_process", rc)); break; }
 		}
 	}
@@ -495,7 +519,10 @@ int main(int argc, char** argv) {
 			RawReader rd(o.isFastq, (int)std::min<uint64_t>(std::max<uint64_t>(o.nproc, 1), 16));
 			if (!rd.open(o.fastxFname)) { S.fail("cannot open " + o.fastxFname); }
 			RawChunk* ch = nullptr;
-			while (!S.failed && rrecycle.pop(ch)) {
+			for (;;) {
+				auto tb = Clock::now();
+				if (S.failed || !rrecycle.pop(ch)) break;
+				S.t_reader_blocked_us += us_since(tb);
 				auto tr = Clock::now();
 				const bool got = rd.fill(*ch, S.chunk_target);
 				S.t_read_us += us_since(tr);
@@ -532,7 +559,9 @@ int main(int argc, char** argv) {
 	uint64_t tot[DBT_N_COUNTERS] = {};
 	BatchOut bo;
 	auto emit = [&](BatchOut& x) {
+		auto tw = Clock::now();
 		if (!x.text.empty()) fwrite(x.text.data(), 1, x.text.size(), stdout);
+		S.t_write_us += us_since(tw);
 		const uint64_t* c = x.counters;
 		const double nr = (double)(2 * x.npairs);
 		fprintf(stderr, "Buffered reading %llu\t%llu\t%llu\n", (unsigned long long)(2 * x.npairs), (unsigned long long)x.nreads_total, (unsigned long long)x.unpaired);
@@ -551,6 +580,7 @@ int main(int argc, char** argv) {
 	}
 	closer.join();
 	fflush(stdout);
+	const double query_wall = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_query).count();
 	if (S.failed) { fprintf(stderr, "danbing-tk: %s\n", S.err.c_str()); return 1; }
 
 	// ---- reduce over GPUs and collect ----
@@ -587,9 +617,10 @@ int main(int argc, char** argv) {
 	for (auto& hb : pool) { dbt_host_free(hb->bases); dbt_host_free(hb->offsets); }
 	for (auto& c : rpool) { dbt_host_free(c->buf); dbt_host_free(c->pair_offset); dbt_host_free(c->pair_hash); dbt_host_free(c->single_offset); }
 	if (o.timing) {
-		fprintf(stderr, "[danbing-tk b200 timing] query wall %.3f s; reader %.3f s; upload+split (sync) %.3f s; pairer %.3f s; wait %.3f s; format %.3f s; chunks %llu (%llu paired on the host)\n",
-		        std::chrono::duration<double>(std::chrono::steady_clock::now() - t_query).count(), S.t_read_us / 1e6, S.t_split_us / 1e6, S.t_pair_us / 1e6, S.t_wait_us / 1e6, S.t_format_us / 1e6,
-		        (unsigned long long)S.n_chunks.load(), (unsigned long long)S.n_slow_chunks.load());
+		fprintf(stderr, "[danbing-tk b200 timing] query wall %.3f s; reader %.3f s; upload+split (sync) %.3f s; pairer %.3f s; wait %.3f s; format %.3f s; chunks %llu (%llu paired on the host); launch %.3f s; pairer turn wait %.3f s; worker idle %.3f s; reader blocked %.3f s; stdout write %.3f s\n",
+		        query_wall, S.t_read_us / 1e6, S.t_split_us / 1e6, S.t_pair_us / 1e6, S.t_wait_us / 1e6, S.t_format_us / 1e6,
+		        (unsigned long long)S.n_chunks.load(), (unsigned long long)S.n_slow_chunks.load(), S.t_launch_us / 1e6, S.t_turn_us / 1e6, S.t_worker_idle_us / 1e6,
+		        S.t_reader_blocked_us / 1e6, S.t_write_us / 1e6);
 	}
 
 	// ---- final counters (cpp:2617-2627) and outputs (cpp:2631-2656) ----

@@ -105,6 +105,7 @@ enum {
   DBT_C_THR2_CLS,              /* thread_kernel's part of DBT_C_THR_CLS                           */
   DBT_C_THR2_NINC,             /* thread_kernel's part of DBT_C_NINC                              */
   DBT_C_THR2_REFRESH,          /* thread_kernel's part of DBT_C_THR_REFRESH                       */
+  DBT_C_THR1_FIXED,            /* mates with one substitution that thread_fast_kernel corrected itself (alned = 2) */
   DBT_N_COUNTERS = 32
 };
 
