@@ -220,31 +220,34 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 				if (lane == 0) { W.T[j] = bt; W.ok[j] = bo; }
 			}
 			__syncwarp();
-			int xpos = -1; uint32_t xbase = 0;                                // fixed mate: CIGAR entry xpos is 'X' with graph base xbase (1-4)
+			uint64_t xlist = 0; int nfix = 0;                                 // corrected mate: 'X' entries of the CIGAR, 16 bits each: position | graph base (1-4) << 13
 			if (!clean && correction1) {
-				// ---- one substitution in the interior of the read, graph without a branch there ----
+				// ---- substitutions in the interior of the read, graph without a branch there ----
 				// The walk (cpp:1167-1180) stops at the first k-mer ki that is not on an out-edge of its predecessor.  If that
 				// predecessor has ONE out-edge a, the k-mer with its last base replaced by a is a node whose one out-edge is the
 				// next read base, and the k following k-mers with that base replaced (the last of them is the read's own k-mer
 				// ki+k) form a path, then errorCorrection_forward (cpp:898-1089) scores the 1-mismatch edit `a` with the full
 				// extension k: no other edit can score more (every family's walk is at most k steps long here) and this one comes
 				// first in thread_ext_t::get_edit's scan (cpp:628-647).  edit_kmers_forward (cpp:828-862) rewrites exactly those
-				// k k-mers and one CIGAR entry; if every k-mer after them was already on an out-edge of its predecessor the read
-				// threads with one correction (isThreadFeasible returns 2).  Everything else is thread_kernel's.
-				int ki = nkm;
+				// k k-mers and one CIGAR entry, and the walk resumes behind them: the next stop, if any, is handled the same way
+				// while corrections (cpp:1186) and skips (cpp:1194) are left.  If every other k-mer is on an out-edge of its
+				// predecessor the read threads with nfix corrections (isThreadFeasible returns 2).  Anything else -- an error
+				// near an end, an indel, a branch, a missing node -- is thread_kernel's, which starts over from the packed read.
+				const uint32_t maxskip = (uint32_t)nkm > rp.thread_cth ? (uint32_t)nkm - rp.thread_cth : 0u;
+				int from = 0; bool fail = false;
 #pragma unroll 1
-				for (int j = ng - 1; j >= 0; --j) { const uint32_t z = ~W.ok[j]; if (z) ki = j * 32 + __ffs(z) - 1; }
-				bool cand = ki >= 1 && ki + (int)K + 2 <= nkm && (uint32_t)nkm > rp.thread_cth;   // anchored at 0; k+2 k-mers remain; one skip allowed (cpp:1194)
-				if (cand) {
+				for (;;) {
+					int ki = nkm;
 #pragma unroll 1
-					for (int j = (ki + (int)K + 1) >> 5; j < ng && cand; ++j) {       // every k-mer past the rewritten ones matches already
-						const int lo = max(ki + (int)K + 1 - j * 32, 0), n = min(32, nkm - j * 32);
-						const uint32_t want = (n == 32 ? 0xFFFFFFFFu : (1u << n) - 1u) & (0xFFFFFFFFu << lo);
-						if ((W.ok[j] & want) != want) cand = false;
+					for (int j = ng - 1; j >= (from >> 5); --j) {
+						uint32_t z = ~W.ok[j];
+						if (j == (from >> 5)) z &= 0xFFFFFFFFu << (from & 31);
+						if (z) ki = j * 32 + __ffs(z) - 1;
 					}
-				}
-				const uint32_t pm = cand ? (uint32_t)(W.nb[ki] >> 1) & 0xFu : 0u;   // out-edges of k-mer ki-1
-				if (cand && __popc(pm) == 1) {
+					if (ki >= nkm) break;                                         // nothing stops the walk any more
+					if (nfix >= 4 || (uint32_t)nfix >= rp.max_ncorrection || (uint32_t)nfix + 1 > maxskip || ki < 1 || ki + (int)K + 2 > nkm) { fail = true; break; }
+					const uint32_t pm = (uint32_t)(W.nb[ki] >> 1) & 0xFu;        // out-edges of k-mer ki-1 (never a rewritten one: ki-1 >= from-1)
+					if (__popc(pm) != 1) { fail = true; break; }
 					const uint32_t a = (uint32_t)__ffs(pm) - 1u;
 					const int t = lane;                                           // lane t < k: k-mer ki+t with the wrong base (2t bits up) replaced
 					uint64_t c = 0; uint32_t bits = 0, trp = 0, f3n = 0;
@@ -265,24 +268,30 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 						const uint32_t mk = gn_mask(bits);
 						good = (bits & GN_PRESENT) && ((mk >> f3n) & 1u) && (t != 0 || __popc(mk) == 1);
 					}
-					if (__all_sync(0xffffffffu, good)) {
-						if (t < (int)K) {
-							const uint64_t rc = kmer_rc(c, K);
-							const bool is_rc = rc < c;
-							W.key[ki + t] = (is_rc ? rc : c) | ((c & 3) << THRF_F3_SHIFT) | (is_rc ? THRF_RCFLAG : 0ull);
-							W.trx[ki + t] = trp;
-						}
-						__syncwarp();
-#pragma unroll 1
-						for (int j = ki >> 5; j <= (ki + (int)K - 1) >> 5; ++j) {     // TR ballots of the groups that changed
-							const int i = j * 32 + lane;
-							const uint32_t bt = __ballot_sync(0xffffffffu, i < nkm && W.trx[i] != 0);
-							if (lane == 0) W.T[j] = bt;
-						}
-						__syncwarp();
-						clean = true; xpos = ki + (int)K - 1; xbase = a + 1;
-						if (lane == 0) { ++c_fix; c_ec += K + 2; }               // look-ups of the scorer's winning path: 1 + 1 expansion nodes + k walk steps
+					if (!__all_sync(0xffffffffu, good)) { fail = true; break; }
+					__syncwarp();
+					if (t < (int)K) {
+						const uint64_t rc = kmer_rc(c, K);
+						const bool is_rc = rc < c;
+						W.key[ki + t] = (is_rc ? rc : c) | ((c & 3) << THRF_F3_SHIFT) | (is_rc ? THRF_RCFLAG : 0ull);
+						W.trx[ki + t] = trp;
 					}
+					__syncwarp();
+					xlist |= (uint64_t)((uint32_t)(ki + (int)K - 1) | ((a + 1) << 13)) << (16 * nfix);
+					++nfix;
+					from = ki + (int)K + 1;                                       // the walk resumes here (cpp:1197: ki += score - 1, then the loop's ++ki)
+					if (lane == 0) c_ec += K + 2;                                 // look-ups of the scorer's winning path: 1 + 1 expansion nodes + k walk steps
+				}
+				if (!fail && nfix) {
+#pragma unroll 1
+					for (int j = 0; j < ng; ++j) {                                 // TR ballots again: the rewritten k-mers have their own
+						const int i = j * 32 + lane;
+						const uint32_t bt = __ballot_sync(0xffffffffu, i < nkm && W.trx[i] != 0);
+						if (lane == 0) W.T[j] = bt;
+					}
+					__syncwarp();
+					clean = true;
+					if (lane == 0) ++c_fix;
 				}
 			}
 			if (!clean) { dirty |= 1u << m; continue; }
@@ -314,7 +323,11 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 					const int nbb = nes - 4 * q;
 					const uint32_t keep = nbb >= 4 ? 0xFFFFFFFFu : (nbb <= 0 ? 0u : (1u << 8 * nbb) - 1u);
 					uint32_t v = 0x01010101u * ET_EQ;
-					if (xpos >= 0 && (xpos >> 2) == q) v = (v & ~(0xFFu << (8 * (xpos & 3)))) | ((uint32_t)(ET_X | (xbase << 3)) << (8 * (xpos & 3)));
+#pragma unroll 1
+					for (int f = 0; f < nfix; ++f) {
+						const uint32_t e = (uint32_t)(xlist >> (16 * f)) & 0xFFFFu, xp = e & 0x1FFFu, xb = e >> 13;
+						if ((int)(xp >> 2) == q) v = (v & ~(0xFFu << (8 * (xp & 3)))) | ((uint32_t)(ET_X | (xb << 3)) << (8 * (xp & 3)));
+					}
 					reinterpret_cast<uint32_t*>(es)[q] = v & keep;
 				}
 #pragma unroll 1
@@ -327,7 +340,7 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 				}
 				if (lane == 0) {
 					dbt_aln_mate* h = reinterpret_cast<dbt_aln_mate*>(b);
-					h->alned = xpos >= 0 ? 2 : 1; h->err = (uint8_t)((int)len > (int)rp.es_cap || nkm > (int)rp.tr_cap);
+					h->alned = nfix ? 2 : 1; h->err = (uint8_t)((int)len > (int)rp.es_cap || nkm > (int)rp.tr_cap);
 					h->nes = (uint16_t)len; h->ntr = (uint16_t)nkm; h->nkm = (uint16_t)nkm;
 					uint64_t hash = 0;
 					if (trace) {                                                // FNV-1a over the k-mer vector (parity tests only)

@@ -59,6 +59,7 @@ private:
 struct BatchOut {                       // what a worker hands to the writer
 	uint64_t index = 0;                 // ordinal of the batch / chunk in the stream: stdout and the per-batch stderr lines go out in this order
 	std::string text;                   // kam lines
+	std::vector<std::string> parts;     // ... or several pieces in order (formatted by several threads); the strings come from and return to Shared::strings
 	uint64_t counters[DBT_N_COUNTERS] = {};
 	uint64_t npairs = 0, nreads_total = 0, unpaired = 0;
 	double seconds = 0;
@@ -68,8 +69,15 @@ struct PairTurn {                       // raw ingestion: chunks meet the host p
 	std::mutex m; std::condition_variable cv; uint64_t next = 0;
 };
 
+struct StringPool {                     // output buffers circulate between the formatting threads and the writer: no fresh pages per chunk
+	std::mutex m; std::vector<std::string> free_;
+	std::string get() { std::lock_guard<std::mutex> l(m); if (free_.empty()) return std::string(); std::string s = std::move(free_.back()); free_.pop_back(); return s; }
+	void put(std::string&& s) { s.clear(); std::lock_guard<std::mutex> l(m); if (free_.size() < 64) free_.push_back(std::move(s)); }
+};
+
 struct Shared {
 	Options opt;
+	StringPool strings;
 	std::unique_ptr<StreamPairer> pairer; PairTurn turn;
 	uint64_t chunk_target = 0;          // raw text bytes per GPU submission
 	std::atomic<uint64_t> t_split_us{0}, t_pair_us{0}, t_wait_us{0}, t_format_us{0}, t_read_us{0}, n_slow_chunks{0}, n_chunks{0};
@@ -269,21 +277,17 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 				const uint32_t stride = dbt_record_stride(w.ctx);
 				const int T = (int)std::min<uint64_t>(std::min<uint64_t>(std::max<uint64_t>(S.opt.nproc, 1), 16), ngpu / 8192 + 1);   // -p host threads format the lines
 				if (T <= 1) {
-					bo.text.reserve((size_t)ngpu * 520);
-					for (uint64_t i = 0; i < ngpu; ++i) format(bo.text, w.recs[s] + i * stride, true);
+					bo.parts.resize(1); bo.parts[0] = S.strings.get();
+					for (uint64_t i = 0; i < ngpu; ++i) format(bo.parts[0], w.recs[s] + i * stride, true);
 				} else {
-					std::vector<std::string> part(T);
+					bo.parts.resize(T);
+					for (auto& x : bo.parts) x = S.strings.get();
 					std::vector<std::thread> th;
 					for (int t = 0; t < T; ++t) th.emplace_back([&, t] {
 						const uint64_t a = ngpu * t / T, b = ngpu * (t + 1) / T;
-						part[t].reserve((size_t)(b - a) * 520);
-						for (uint64_t i = a; i < b; ++i) format(part[t], w.recs[s] + i * stride, true);
+						for (uint64_t i = a; i < b; ++i) format(bo.parts[t], w.recs[s] + i * stride, true);
 					});
 					for (auto& x : th) x.join();
-					size_t tot = 0;
-					for (auto& x : part) tot += x.size();
-					bo.text.reserve(tot);
-					for (auto& x : part) bo.text += x;
 				}
 			}
 		} else {
@@ -450,7 +454,7 @@ int main(int argc, char** argv) {
 	const uint64_t readsPerRefBatch = (uint64_t)(300000 * o.readsPerBatchFactor);          // cpp:1835
 	const uint64_t minlen = o.Cthreshold + o.ksize - 1;
 	const bool raw = !o.host_reader;
-	const int NB = 2 * G + 2;
+	const int NB = 2 * G + 4;
 	std::vector<std::unique_ptr<HostBatch>> pool;
 	std::vector<std::unique_ptr<RawChunk>> rpool;
 	Channel<HostBatch*> recycle;
@@ -561,6 +565,7 @@ int main(int argc, char** argv) {
 	auto emit = [&](BatchOut& x) {
 		auto tw = Clock::now();
 		if (!x.text.empty()) fwrite(x.text.data(), 1, x.text.size(), stdout);
+		for (auto& part : x.parts) { if (!part.empty()) fwrite(part.data(), 1, part.size(), stdout); S.strings.put(std::move(part)); }
 		S.t_write_us += us_since(tw);
 		const uint64_t* c = x.counters;
 		const double nr = (double)(2 * x.npairs);
