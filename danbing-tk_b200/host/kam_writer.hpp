@@ -4,6 +4,7 @@
 // Columns: src dst dst0 span2 span1 header fields2 fields1 rle(as2) rle(as1) title seq2 qual2|. seq1 qual1|.
 // where "1"/"2" are the reference's internal slots: read 1 = the mate that arrived second (cpp:1972-1974).
 #pragma once
+#include <charconv>
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
@@ -14,7 +15,9 @@
 namespace dbt_host {
 
 inline void append_int(std::string& o, long long v) {
-	char tmp[24]; int n = snprintf(tmp, sizeof tmp, "%lld", v); o.append(tmp, (size_t)n);
+	char tmp[24];
+	const auto r = std::to_chars(tmp, tmp + sizeof tmp, v);      // (snprintf was two thirds of the formatting time of a kam line)
+	o.append(tmp, (size_t)(r.ptr - tmp));
 }
 inline void append_na(std::string& o, int v) { if (v == -1) o.push_back('.'); else append_int(o, v); }
 
