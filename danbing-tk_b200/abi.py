@@ -16,6 +16,7 @@ DBT_N_SLOTS = 2
 DBT_NCCL_ID_BYTES = 128
 
 F_KAM, F_QC, F_TRACE, F_THREADING, F_CORRECTION, F_ALN, F_ALN_MIN = 1, 2, 4, 8, 16, 32, 64
+F_EXTRACT, F_SIM, F_BUBBLES = 128, 256, 512
 ST_SHORT, ST_SUBFILTERED, ST_KFILTERED, ST_UNASSIGNED, ST_QCFILTERED, ST_ASGN_REMOVED, ST_COUNTED, ST_NOT_THREADED, ST_THREAD_FAILED = range(9)
 LAYOUT_ASCII, LAYOUT_PACKED = 0, 1
 COUNTER_NAMES = ["nReads", "nShort", "nSubFiltered", "nKmerFiltered", "nBaitFiltered", "nQualFiltered",
@@ -45,7 +46,7 @@ class Params(C.Structure):
 class Index(C.Structure):
     _fields_ = [("nloci", C.c_uint64), ("nk_dbi", C.c_uint64), ("dbi_keys", u64p), ("dbi_vals", u32p),
                 ("nvv", C.c_uint64), ("vv", u32p), ("tr_n", u64p), ("tr_kmers", u64p), ("fl_n", u64p),
-                ("fl_kmers", u64p), ("qc", u8p), ("g_n", u64p), ("g_kmers", u64p), ("g_masks", u8p)]
+                ("fl_kmers", u64p), ("qc", u8p), ("g_n", u64p), ("g_kmers", u64p), ("g_masks", u8p), ("tre_n", u64p), ("tre_kmers", u64p)]
 
 
 class Batch(C.Structure):
@@ -137,6 +138,9 @@ def make_index_struct(ix):
         s.g_n = ptr(ix["g_n"], u64p)
         s.g_kmers = ptr(ix["g_kmers"], u64p)
         s.g_masks = ptr(ix["g_masks"], u8p)
+    if ix.get("tre_n") is not None:                 # PREF.tre.kdb (`-bu`)
+        s.tre_n = ptr(ix["tre_n"], u64p)
+        s.tre_kmers = ptr(ix["tre_kmers"], u64p)
     s._keep = ix
     return s
 
@@ -179,6 +183,7 @@ def load_library(path=LIB_PATH):
     L.dbt_upload.argtypes = [ctxp, C.POINTER(Batch), C.c_int]
     L.dbt_upload_raw.argtypes = [ctxp, C.POINTER(RawBatch), C.POINTER(RawInfo), C.c_int]
     L.dbt_prepare.argtypes = [ctxp, C.c_uint64]
+    L.dbt_bubble_events.argtypes = [ctxp, C.c_int, u64p, u64p, u32p, C.c_uint64, u64p]
     L.dbt_title_hash.argtypes = [C.c_char_p, C.c_size_t]
     L.dbt_title_hash.restype = C.c_uint64
     L.dbt_raw_times.argtypes = [ctxp, C.c_int, C.POINTER(C.c_float)]
@@ -213,7 +218,7 @@ def load_library(path=LIB_PATH):
     return L
 
 
-ABI_SYMBOLS = ["dbt_prepare", "dbt_upload_raw", "dbt_title_hash", "dbt_raw_times", "dbt_abi_version", "dbt_device_count", "dbt_default_params", "dbt_create", "dbt_destroy",
+ABI_SYMBOLS = ["dbt_bubble_events", "dbt_prepare", "dbt_upload_raw", "dbt_title_hash", "dbt_raw_times", "dbt_abi_version", "dbt_device_count", "dbt_default_params", "dbt_create", "dbt_destroy",
                "dbt_strerror", "dbt_last_error", "dbt_load_index", "dbt_upload", "dbt_process", "dbt_fetch",
                "dbt_submit", "dbt_wait", "dbt_download", "dbt_reset_counts", "dbt_nk_tr", "dbt_nloci",
                "dbt_record_stride", "dbt_record_as_stride", "dbt_record_aln_stride", "dbt_record_es_cap", "dbt_nccl_unique_id", "dbt_comm_init", "dbt_allreduce",

@@ -345,7 +345,7 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 	const uint32_t gwarp = blockIdx.x * WPB + wib;
 	const uint32_t nwarps = gridDim.x * WPB;
 	const uint32_t W64 = rp.lay.W64, WB = rp.lay.WB, K = rp.k, NKP = rp.nkp, UMAX = rp.umax;
-	const bool okam = (rp.flags & (DBT_F_KAM | DBT_F_EXTRACT)) != 0 && !rp.thr_on, trace = (rp.flags & DBT_F_TRACE) != 0;   // no kam lines with threading (cpp:2110)
+	const bool okam = (rp.flags & (DBT_F_KAM | DBT_F_EXTRACT | DBT_F_BUBBLES)) != 0 && !rp.thr_on, trace = (rp.flags & DBT_F_TRACE) != 0;   // no kam lines with threading (cpp:2110)
 	const bool wstat = okam || (rp.thr_on && (rp.flags & (DBT_F_ALN | DBT_F_ALN_MIN)));
 
 	// ---- shared-memory carve-up (per warp); dbt_create mirrors the sizes ----

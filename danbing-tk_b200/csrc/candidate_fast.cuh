@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
 	const uint32_t gwarp = blockIdx.x * CAND_FAST_WARPS + wib, nwarps = gridDim.x * CAND_FAST_WARPS;
 	const uint32_t W64 = rp.lay.W64, WB = rp.lay.WB, K = rp.k;
-	const bool okam = (rp.flags & (DBT_F_KAM | DBT_F_EXTRACT)) != 0 && !rp.thr_on;   // kam lines are only written without threading (cpp:2110); `-e` records ride the same slots
+	const bool okam = (rp.flags & (DBT_F_KAM | DBT_F_EXTRACT | DBT_F_BUBBLES)) != 0 && !rp.thr_on;   // kam lines are only written without threading (cpp:2110); `-e` records ride the same slots
 	const bool wstat = okam || (rp.thr_on && (rp.flags & (DBT_F_ALN | DBT_F_ALN_MIN)));   // record slots are keyed by candidate ordinal: keep their status current
 	const uint32_t nloci = (uint32_t)ix.nloci, cth = rp.cth;
 	FastWarp<B, MAXJ>& W = wsm[wib];

@@ -100,6 +100,9 @@ struct Slot {
 	uint32_t* h_rhdr = nullptr;              // pinned: dbt_raw_info
 	cudaEvent_t evr0 = nullptr, evr1 = nullptr;
 	bool ev_raw = false;
+	// `-bu`: novel-edge events of the batch
+	uint64_t *d_evkey = nullptr, *d_evedge = nullptr; uint32_t *d_evlocus = nullptr, *d_nev = nullptr; uint32_t ev_cap = 0;
+	uint32_t* h_nev = nullptr; bool ev_pending = false;
 };
 
 struct Id128 { char b[128]; };       // ncclUniqueId is passed BY VALUE to ncclCommInitRank
@@ -124,6 +127,7 @@ struct dbt_ctx {
 	DevIndex ix{};
 	// owned device memory of the index
 	uint4* d_gslots = nullptr; uint64_t gtable_bytes = 0, gnodes = 0;   // graph table (restored threading)
+	uint4* d_tslots = nullptr; Table ttable{}; bool bubbles = false;    // TR edge table (`-bu`)
 	uint4* d_slots = nullptr; uint32_t* d_vv = nullptr; uint32_t* d_vv_aux = nullptr;
 	// results: ONE allocation [counts nk_tr | kmc nloci | totals DBT_N_COUNTERS] u64 + [nmapread nloci] u32, so that the
 	// end-of-run exchange is one grouped collective (a u64 part and a u32 part); d_red = the same layout, filled by dbt_allreduce
@@ -240,6 +244,8 @@ static void free_slot(Slot& s) {
 	cudaFree(s.d_raw); cudaFree(s.d_nlmask); cudaFree(s.d_rblocksum); cudaFree(s.d_nl); cudaFree(s.d_rhdr); cudaFree(s.d_tlen); cudaFree(s.d_slen);
 	cudaFree(s.d_rhash); cudaFree(s.d_eq); cudaFree(s.d_pairmask); cudaFree(s.d_singlemask); cudaFree(s.d_pairlist); cudaFree(s.d_singlelist);
 	cudaFree(s.d_pairoff); cudaFree(s.d_singleoff); cudaFree(s.d_rstart); cudaFree(s.d_rend); cudaFree(s.d_pairhash);
+	cudaFree(s.d_evkey); cudaFree(s.d_evedge); cudaFree(s.d_evlocus); cudaFree(s.d_nev);
+	if (s.h_nev) cudaFreeHost(s.h_nev);
 	if (s.h_rhdr) cudaFreeHost(s.h_rhdr);
 	if (s.evr0) cudaEventDestroy(s.evr0);
 	if (s.evr1) cudaEventDestroy(s.evr1);
@@ -259,7 +265,7 @@ extern "C" void dbt_destroy(dbt_ctx* c) {
 	cudaSetDevice(c->p.device);
 	for (auto& s : c->slot) free_slot(s);
 	if (c->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
-	cudaFree(c->d_gslots);
+	cudaFree(c->d_gslots); cudaFree(c->d_tslots);
 	cudaFree(c->d_slots); cudaFree(c->d_vv); cudaFree(c->d_vv_aux); cudaFree(c->d_results); cudaFree(c->d_red);
 	cudaFree(c->d_qc); cudaFree(c->d_permtab); cudaFree(c->d_vote_pool); cudaFree(c->d_vote_lock);
 	if (c->h_totals) cudaFreeHost(c->h_totals);
@@ -292,7 +298,7 @@ static int ensure_slot(dbt_ctx* c, int si) {
 	TRY(dev_alloc(&s.d_slow, P, "slow list"));
 	if (rp.thr_on) { TRY(dev_alloc(&s.d_thr, P, "thread list")); TRY(dev_alloc(&s.d_thr2, P, "thread list 2")); }
 	TRY(dev_alloc(&s.d_counters, DBT_N_COUNTERS, "counters"));
-	const bool want_records = rp.thr_on ? (c->p.flags & (DBT_F_ALN | DBT_F_ALN_MIN | DBT_F_TRACE)) != 0 : (c->p.flags & (DBT_F_KAM | DBT_F_EXTRACT | DBT_F_TRACE)) != 0;
+	const bool want_records = rp.thr_on ? (c->p.flags & (DBT_F_ALN | DBT_F_ALN_MIN | DBT_F_TRACE)) != 0 : (c->p.flags & (DBT_F_KAM | DBT_F_EXTRACT | DBT_F_BUBBLES | DBT_F_TRACE)) != 0;
 	if (want_records) {
 		TRY(dev_alloc(&s.d_records, (size_t)c->p.max_records * rp.rec_stride, "records"));
 		if (!(c->p.flags & DBT_F_TRACE)) {
@@ -303,6 +309,12 @@ static int ensure_slot(dbt_ctx* c, int si) {
 			TRY(dev_alloc(&s.d_emitlist, (size_t)c->p.max_records + 32, "emit list"));
 			TRY(dev_alloc(&s.d_nemit, 4, "nemit"));
 		}
+	}
+	if (c->bubbles) {
+		s.ev_cap = (uint32_t)std::min<uint64_t>(4 * P + (1u << 20), 0xFFFFFFF0ull);
+		TRY(dev_alloc(&s.d_evkey, s.ev_cap, "bubble event keys")); TRY(dev_alloc(&s.d_evedge, s.ev_cap, "bubble event edges"));
+		TRY(dev_alloc(&s.d_evlocus, s.ev_cap, "bubble event loci")); TRY(dev_alloc(&s.d_nev, 1, "bubble event count"));
+		CU(cudaHostAlloc((void**)&s.h_nev, 16, cudaHostAllocDefault));
 	}
 	CU(cudaHostAlloc((void**)&s.h_counters, (DBT_N_COUNTERS + 4) * sizeof(uint64_t), cudaHostAllocDefault));
 	for (auto& e : s.ev) CU(cudaEventCreate(&e));
@@ -368,6 +380,43 @@ static int load_graph(dbt_ctx* c, const dbt_index* in, uint64_t ntr) {
 	c->ix.gtable = t;
 	c->rp.thr_on = 1;
 	c->rp.rec_stride = (uint32_t)sizeof(dbt_pair_record) + 2 * c->rp.aln_stride;
+	return DBT_OK;
+}
+
+// trEdgeDB of all loci (PREF.tre.kdb, cpp:2492) -> one device table keyed (canonical (k+1)-mer, locus)
+static int load_edges(dbt_ctx* c, const dbt_index* in) {
+	const uint64_t nloci = in->nloci;
+	if (nloci >= G_LOCUS_MASK) return fail(DBT_E_CAPACITY, "-bu supports < %u loci", G_LOCUS_MASK);
+	if (c->p.k + 1 > 31) return fail(DBT_E_CAPACITY, "-bu: (k+1)-mers must fit 62 bits");
+	uint64_t ne = 0;
+	for (uint64_t l = 0; l < nloci; ++l) ne += in->tre_n[l];
+	const int B = c->B;
+	const uint64_t nbuckets = (uint64_t)((double)(ne + 1024) / c->p.table_load) / B + 64, nstash = std::max<uint64_t>(64, ((ne + 1024) / 2 + B - 1) / B);
+	if (nbuckets >= (1ull << 32) || nstash >= (1ull << 32)) return fail(DBT_E_CAPACITY, "edge table needs %llu buckets (limit 2^32)", (unsigned long long)nbuckets);
+	cudaStream_t st; CU(cudaStreamCreate(&st));
+	TRY(dev_alloc(&c->d_tslots, (nbuckets + nstash) * B, "edge table"));
+	CU(cudaMemsetAsync(c->d_tslots, 0xFF, (nbuckets + nstash) * B * sizeof(uint4), st));
+	Table t{c->d_tslots, nbuckets, nstash};
+	uint32_t* d_err; TRY(dev_alloc(&d_err, 1, "err")); CU(cudaMemsetAsync(d_err, 0, 4, st));
+	uint32_t herr = 0;
+	if (ne) {
+		std::vector<uint32_t> loc(ne);
+		uint64_t j = 0;
+		for (uint64_t l = 0; l < nloci; ++l) for (uint64_t i = 0; i < in->tre_n[l]; ++i) loc[j++] = (uint32_t)l;
+		uint64_t* dk; uint32_t* dl;
+		TRY(dev_alloc(&dk, ne, "edges")); TRY(dev_alloc(&dl, ne, "edge loci"));
+		CU(cudaMemcpyAsync(dk, in->tre_kmers, ne * 8, cudaMemcpyHostToDevice, st));
+		CU(cudaMemcpyAsync(dl, loc.data(), ne * 4, cudaMemcpyHostToDevice, st));
+		CU(launch_edge_insert(st, B, t, dk, dl, ne, c->p.k + 1, d_err)); ++c->launches;
+		CU(cudaMemcpyAsync(&herr, d_err, 4, cudaMemcpyDeviceToHost, st));
+		CU(cudaStreamSynchronize(st));
+		cudaFree(dk); cudaFree(dl);
+	}
+	cudaFree(d_err);
+	CU(cudaStreamDestroy(st));
+	if (herr & ERR_INDEX_FULL) return fail(DBT_E_CAPACITY, "edge table overflow: lower table_load");
+	if (herr & ERR_INDEX_MISSING) return fail(DBT_E_INDEX, "tre.kdb holds an edge that does not fit k+1=%u bases", c->p.k + 1);
+	c->ttable = t; c->bubbles = true;
 	return DBT_OK;
 }
 
@@ -484,6 +533,11 @@ extern "C" int dbt_load_index(dbt_ctx* c, const dbt_index* in) {
 	c->ix.nloci = nloci; c->ix.nk_tr = ntr;
 	c->ix.gtable = Table{nullptr, 0, 0};
 	if ((c->p.flags & DBT_F_THREADING) && in->g_n && in->g_kmers && in->g_masks) TRY(load_graph(c, in, ntr));
+	if (c->p.flags & DBT_F_BUBBLES) {
+		if (c->rp.thr_on) return fail(DBT_E_BADARG, "DBT_F_BUBBLES with graph threading: the reference counts bubbles only without threading (cpp:2110, 2160)");
+		if (!in->tre_n || (!in->tre_kmers && nloci)) return fail(DBT_E_BADARG, "DBT_F_BUBBLES needs tre_n / tre_kmers (PREF.tre.kdb)");
+		TRY(load_edges(c, in));
+	}
 	c->index_loaded = true;
 	return DBT_OK;
 }
@@ -720,6 +774,27 @@ extern "C" int dbt_upload_raw(dbt_ctx* c, const dbt_raw_batch* b, dbt_raw_info* 
 	return DBT_OK;
 }
 
+extern "C" int dbt_bubble_events(dbt_ctx* c, int slot, uint64_t* key, uint64_t* edge, uint32_t* locus, uint64_t cap, uint64_t* n) {
+	TRY(check_slot(c, slot));
+	if (!n) return fail(DBT_E_BADARG, "null argument");
+	*n = 0;
+	if (!c->bubbles) return fail(DBT_E_STATE, "the context was not created with DBT_F_BUBBLES");
+	Slot& s = c->slot[slot];
+	if (s.fetch_pending) return fail(DBT_E_STATE, "slot %d has an unfinished fetch; call dbt_wait", slot);
+	CU(cudaStreamSynchronize(s.st));
+	const uint64_t nev = s.ev_pending ? *s.h_nev : 0;
+	if (nev > s.ev_cap) return fail(DBT_E_CAPACITY, "%llu novel-edge events in one batch, the slot holds %u: submit smaller batches", (unsigned long long)nev, s.ev_cap);
+	if (nev > cap) return fail(DBT_E_CAPACITY, "%llu novel-edge events, the caller's arrays hold %llu", (unsigned long long)nev, (unsigned long long)cap);
+	if (nev) {
+		if (!key || !edge || !locus) return fail(DBT_E_BADARG, "null output array");
+		CU(cudaMemcpy(key, s.d_evkey, nev * 8, cudaMemcpyDeviceToHost));
+		CU(cudaMemcpy(edge, s.d_evedge, nev * 8, cudaMemcpyDeviceToHost));
+		CU(cudaMemcpy(locus, s.d_evlocus, nev * 4, cudaMemcpyDeviceToHost));
+	}
+	*n = nev;
+	return DBT_OK;
+}
+
 extern "C" int dbt_raw_times(dbt_ctx* c, int slot, float ms[2]) {
 	TRY(check_slot(c, slot));
 	Slot& s = c->slot[slot];
@@ -748,6 +823,10 @@ extern "C" int dbt_process(dbt_ctx* c, int slot) {
 	CU(cudaEventRecord(s.ev[3], s.st));
 	CU(launch_candidate(s.st, c->B, c->cand_grid_fast, c->cand_grid, c->ix, c->rp, sv, s.ev[4]));
 	if (s.npairs) c->launches += ((c->p.flags & DBT_F_TRACE) || c->rp.nk_max > 255) ? 1 : 2;   // generic kernel alone, or closed-form + generic
+	if (c->bubbles && s.npairs) {
+		CU(cudaMemsetAsync(s.d_nev, 0, 4, s.st));
+		CU(launch_bubbles(s.st, c->B, c->nsm, c->ttable, c->rp, sv, (uint32_t)c->ix.nloci, s.d_evkey, s.d_evedge, s.d_evlocus, s.d_nev, s.ev_cap)); ++c->launches;
+	}
 	CU(cudaEventRecord(s.ev[5], s.st));
 	if (c->rp.thr_on) { CU(launch_thread(s.st, c->B, c->nsm, c->ix, c->rp, sv, s.ev[6])); if (s.npairs) c->launches += 2; }
 	else CU(cudaEventRecord(s.ev[6], s.st));
@@ -773,6 +852,8 @@ extern "C" int dbt_fetch(dbt_ctx* c, dbt_batch_result* r, int slot) {
 			s.emitted = true;
 		}
 	}
+	s.ev_pending = false;
+	if (c->bubbles) { *s.h_nev = 0; if (s.npairs) { CU(cudaMemcpyAsync(s.h_nev, s.d_nev, 4, cudaMemcpyDeviceToHost, s.st)); s.ev_pending = true; } }
 	CU(cudaMemcpyAsync(s.h_counters, s.d_counters, DBT_N_COUNTERS * 8, cudaMemcpyDeviceToHost, s.st));
 	CU(cudaMemcpyAsync(s.h_counters + DBT_N_COUNTERS, s.d_ncand, 16, cudaMemcpyDeviceToHost, s.st));
 	s.result = r; s.fetch_pending = true;

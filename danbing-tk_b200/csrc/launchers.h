@@ -23,5 +23,9 @@ cudaError_t launch_graph_build(cudaStream_t st, int B, Table t, const uint64_t* 
 cudaError_t launch_table_stats(cudaStream_t st, int B, Table t, unsigned long long* out);
 cudaError_t launch_random_gather(cudaStream_t st, int nsm, const uint4* table, uint64_t table_bytes, uint32_t sector_bytes,
                                  uint64_t ngathers, uint64_t seed, uint32_t* sink);
+// `-bu` (bubbles.cu): PREF.tre.kdb -> edge table; novel-edge events of the COUNTED records of a batch
+cudaError_t launch_edge_insert(cudaStream_t st, int B, Table t, const uint64_t* edges, const uint32_t* locus_of, uint64_t n, uint32_t k1, uint32_t* err);
+cudaError_t launch_bubbles(cudaStream_t st, int B, int nsm, Table tt, const RunParams& rp, const SlotView& sv, uint32_t nloci,
+                           uint64_t* ev_key, uint64_t* ev_edge, uint32_t* ev_locus, uint32_t* nev, uint32_t cap);
 constexpr int COMPACT_WORDS_H = 1024;
 }

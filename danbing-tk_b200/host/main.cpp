@@ -35,6 +35,7 @@
 #include "raw_ingest.hpp"
 #include "kam_writer.hpp"
 #include "aln_writer.hpp"
+#include "bubbles.hpp"
 
 using namespace dbt_host;
 
@@ -59,6 +60,7 @@ private:
 struct BatchOut {                       // what a worker hands to the writer
 	uint64_t index = 0;                 // ordinal of the batch / chunk in the stream: stdout and the per-batch stderr lines go out in this order
 	std::string text;                   // kam lines
+	std::vector<BubbleEvent> events;    // `-bu`: novel edges of the batch, ascending (pair, mate, position)
 	std::vector<std::string> parts;     // ... or several pieces in order (formatted by several threads); the strings come from and return to Shared::strings
 	uint64_t counters[DBT_N_COUNTERS] = {};
 	uint64_t npairs = 0, nreads_total = 0, unpaired = 0;
@@ -79,6 +81,7 @@ struct Shared {
 	Options opt;
 	StringPool strings;
 	std::unique_ptr<StreamPairer> pairer; PairTurn turn;
+	std::unique_ptr<BubbleAcc> bubbles;                                          // `-bu`: replayed by the writer thread in stream order
 	uint64_t chunk_target = 0;          // raw text bytes per GPU submission
 	std::atomic<uint64_t> t_split_us{0}, t_pair_us{0}, t_wait_us{0}, t_format_us{0}, t_read_us{0}, n_slow_chunks{0}, n_chunks{0};
 	std::atomic<uint64_t> t_launch_us{0}, t_write_us{0}, t_reader_blocked_us{0}, t_worker_idle_us{0}, t_turn_us{0};
@@ -119,13 +122,27 @@ bool append_kam_checked(Shared& S, std::string& o, const uint8_t* rec, uint32_t 
 
 std::string dbt_err(const char* what, int rc) { return std::string(what) + ": " + dbt_strerror(rc) + ": " + dbt_last_error(); }
 
+// `-bu`: the novel-edge events of the submission that just finished on `slot`; ordinal(p) = global ordinal of pair p of the submission
+template <typename F>
+bool fetch_bubbles(Shared& S, Worker& w, int slot, uint64_t npairs, F&& ordinal, std::vector<BubbleEvent>& out) {
+	if (!S.opt.outputBubbles || !npairs) return true;
+	const uint64_t cap = 4 * npairs + (1u << 20);
+	std::vector<uint64_t> key(cap), edge(cap); std::vector<uint32_t> loc(cap);
+	uint64_t n = 0;
+	const int rc = dbt_bubble_events(w.ctx, slot, key.data(), edge.data(), loc.data(), cap, &n);
+	if (rc) { S.fail(dbt_err("dbt_bubble_events", rc)); return false; }
+	out.reserve(out.size() + n);
+	for (uint64_t i = 0; i < n; ++i) out.push_back(BubbleEvent{(ordinal(key[i] >> 10) << 10) | (key[i] & 1023), edge[i], loc[i]});
+	return true;
+}
+
 bool make_ctx(Shared& S, Worker& w, uint32_t max_len) {
 	dbt_params p;
 	dbt_default_params(&p);
 	const Options& o = S.opt;
 	p.device = w.gpu; p.k = (uint32_t)o.ksize; p.n_filter = (uint32_t)o.N_FILTER; p.nm_filter = (uint32_t)o.NM_FILTER;
 	p.cth = (uint32_t)o.Cthreshold; p.nm_tr = (uint32_t)o.NM_TR; p.thread_cth = (uint32_t)o.thread_cth; p.max_ncorrection = (uint32_t)o.maxncorrection;
-	p.flags = (o.extractFastX ? DBT_F_EXTRACT : (o.okam ? DBT_F_KAM : 0)) | (o.simmode ? DBT_F_SIM : 0) | (o.qc ? DBT_F_QC : 0) | (o.threading ? DBT_F_THREADING : 0) | (o.threading && o.correction ? DBT_F_CORRECTION : 0) |
+	p.flags = (o.extractFastX ? DBT_F_EXTRACT : (o.okam ? DBT_F_KAM : 0)) | (o.simmode ? DBT_F_SIM : 0) | (o.outputBubbles ? DBT_F_BUBBLES : 0) | (o.qc ? DBT_F_QC : 0) | (o.threading ? DBT_F_THREADING : 0) | (o.threading && o.correction ? DBT_F_CORRECTION : 0) |
 	          (o.aln ? DBT_F_ALN : 0) | (o.aln_minimal ? DBT_F_ALN_MIN : 0);
 	p.max_read_len = max_len; p.max_batch_pairs = (uint32_t)S.batch_pairs; p.max_records = (uint32_t)S.batch_pairs;
 	p.table_load = o.table_load; p.bucket_slots = o.bucket_slots;
@@ -167,6 +184,8 @@ void worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<HostBatch
 		bo.index = f.hb->seq;
 		bo.npairs = f.hb->npairs; bo.nreads_total = f.hb->nreads_total_after; bo.unpaired = f.hb->unpaired_after;
 		memcpy(bo.counters, f.res.counters, sizeof bo.counters);
+		if (!fetch_bubbles(S, w, s, f.hb->npairs, [&](uint64_t p) { return f.hb->first_pair_index + p; }, bo.events)) return false;
+		std::sort(bo.events.begin(), bo.events.end(), [](const BubbleEvent& a, const BubbleEvent& b) { return a.key < b.key; });
 		if (S.want_records && f.res.n_records) {
 			const uint32_t stride = dbt_record_stride(w.ctx), as_stride = dbt_record_as_stride(w.ctx);
 			bo.text.reserve((size_t)f.res.n_records * 520);
@@ -228,7 +247,7 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 	struct Inflight {
 		RawChunk* ch = nullptr; bool gpu = false; dbt_raw_info info{}; dbt_batch_result res{};
 		StreamPairer::Extra ex;
-		uint64_t nreads_total = 0, unpaired = 0; Clock::time_point t0;
+		uint64_t nreads_total = 0, unpaired = 0, first_pair = 0; Clock::time_point t0;
 	};
 	Inflight fl[DBT_N_SLOTS];
 	const bool fq = S.opt.isFastq;
@@ -262,7 +281,11 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 			if (rc) { S.fail(dbt_err("dbt_wait", rc)); return false; }
 			for (int i = 0; i < DBT_N_COUNTERS; ++i) bo.counters[i] += f.res.counters[i];
 			bo.npairs += f.info.npairs; ngpu = f.res.n_records;
+			// global ordinal of device pair p = pairs before the chunk + p + the host-formed pairs of the chunk that come before it
+			if (!fetch_bubbles(S, w, s, f.info.npairs, [&](uint64_t p) {
+				return f.first_pair + p + (uint64_t)(std::lower_bound(f.ex.key.begin(), f.ex.key.end(), (uint64_t)ch->pair_offset[p]) - f.ex.key.begin()); }, bo.events)) return false;
 		}
+		const uint32_t np_gpu = f.gpu ? f.info.npairs : 0;
 		const HostBatch& xb = f.ex.hb;
 		auto format = [&](std::string& o, const uint8_t* rec, bool from_gpu) {
 			const uint64_t pi = reinterpret_cast<const dbt_pair_record*>(rec)->pair_index;
@@ -316,6 +339,9 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 			if (rc) { S.fail(dbt_err("dbt_submit (host-paired reads)", rc)); return false; }
 			for (int i = 0; i < DBT_N_COUNTERS; ++i) bo.counters[i] += res2.counters[i];
 			bo.npairs += xb.npairs;
+			if (!fetch_bubbles(S, w, s, xb.npairs, [&](uint64_t j) {
+				const uint64_t kj = f.ex.key[j];
+				return f.first_pair + j + (uint64_t)(kj > 0xFFFFFFFFull ? np_gpu : std::lower_bound(ch->pair_offset, ch->pair_offset + np_gpu, (uint32_t)kj) - ch->pair_offset); }, bo.events)) return false;
 			for (uint64_t j = 0; j < res2.n_records; ++j) {
 				const uint8_t* rec = recs2.data() + j * stride;
 				lines.emplace_back(f.ex.key[reinterpret_cast<const dbt_pair_record*>(rec)->pair_index], std::string());
@@ -325,6 +351,7 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 			for (auto& l : lines) bo.text += l.second;
 		}
 		S.t_format_us += us_since(tf);
+		std::sort(bo.events.begin(), bo.events.end(), [](const BubbleEvent& a, const BubbleEvent& b) { return a.key < b.key; });
 		bo.seconds = std::chrono::duration<double>(Clock::now() - f.t0).count();
 		recycle.push(ch);
 		out.push(std::move(bo));
@@ -374,6 +401,7 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 				if (use_gpu && !fast) ++S.n_slow_chunks;
 				++S.n_chunks;
 				f.nreads_total = 2 * S.pairer->total_pairs(); f.unpaired = S.pairer->unpaired();
+				f.first_pair = S.pairer->total_pairs() - (f.gpu ? f.info.npairs : 0) - f.ex.hb.npairs;
 				S.t_pair_us += us_since(tp);
 			}
 			++S.turn.next;
@@ -406,7 +434,7 @@ int main(int argc, char** argv) {
 	std::string err = parse_args(argc, argv, o);
 	if (!err.empty()) { fprintf(stderr, "%s\n", err.c_str()); return 1; }
 	if (o.trPrefix.empty() || o.fastxFname.empty() || o.outPrefix.empty()) { fprintf(stderr, "-qs, -fa|-fq and -o|-on are required\n"); return 1; }
-	for (const char* unsupported : {o.bait ? "-b" : "", o.outputBubbles ? "-bu" : "", o.trackBait ? "-tb" : "",
+	for (const char* unsupported : {o.bait ? "-b" : "", o.trackBait ? "-tb" : "",
 	                                o.g2pan ? "-m" : "", o.aug ? "-au" : "", o.trim ? "-t" : "", o.invkmer ? "-ik" : ""})
 		if (*unsupported) { fprintf(stderr, "option %s is not part of the B200 align path (SURVEY.md 8(f)); use the reference binary for it\n", unsupported); return 1; }
 	if (o.ksize < 1 || o.ksize > 27) { fprintf(stderr, "-k %llu unsupported (1..27)\n", (unsigned long long)o.ksize); return 1; }
@@ -446,6 +474,13 @@ int main(int argc, char** argv) {
 	}
 	if (o.extractFastX && S.thr_graph) { fprintf(stderr, "\n-e with a graph in the RPGG (restored threading) is outside the reference's behaviour; drop -g/-gc or the graph file\n"); return 1; }
 	if (o.extractFastX && o.extractFastX != 1 && o.extractFastX != 2) { fprintf(stderr, "\n-e takes 1 or 2\n"); return 1; }
+	if (o.outputBubbles) {
+		if (S.thr_graph) { fprintf(stderr, "\n-bu with a graph in the RPGG (restored threading): the reference counts bubbles only without threading\n"); return 1; }
+		if (o.extractFastX) { fprintf(stderr, "\n-bu with -e: extraction counts nothing\n"); return 1; }
+		if (!read_kdb(o.trPrefix + ".tre.kdb", S.rpgg.tre_n, S.rpgg.tre_kmers, err) || S.rpgg.tre_n.size() != g.nloci) { fprintf(stderr, "\n%s\n", err.empty() ? (o.trPrefix + ".tre.kdb: locus count differs").c_str() : err.c_str()); return 1; }
+		S.index.tre_n = S.rpgg.tre_n.data(); S.index.tre_kmers = S.rpgg.tre_kmers.data();
+		S.bubbles.reset(new BubbleAcc(g.nloci, (uint64_t)(300000 * o.readsPerBatchFactor)));
+	}
 	S.want_records = o.extractFastX ? true : (S.thr_graph ? o.aln : o.okam);
 	fprintf(stderr, "0 bait loci in baitDB\ndeserialized graph/index and read tr.kmers in %lld sec.\n# unique kmers in kmerDBi: %llu\n",
 	        (long long)std::chrono::duration_cast<std::chrono::seconds>(std::chrono::steady_clock::now() - t_load).count(), (unsigned long long)g.dbi_keys.size());
@@ -575,6 +610,7 @@ int main(int argc, char** argv) {
 		        (unsigned long long)c[DBT_C_NSUBFILTERED], (unsigned long long)c[DBT_C_NKMERFILTERED], (unsigned long long)c[DBT_C_NLOCUSASSIGNFILTERED],
 		        (unsigned long long)c[DBT_C_NQCFILTERED], (unsigned long long)c[DBT_C_NTHREADINGREADS], (unsigned long long)c[DBT_C_NFEASIBLEREADS],
 		        (unsigned long long)c[DBT_C_NBAITFILTERED], (unsigned long long)c[DBT_C_NASGNREADS]);
+		if (S.bubbles) S.bubbles->replay(x.events);
 		for (int i = 0; i < DBT_N_COUNTERS; ++i) tot[i] += c[i];
 		next_seq = x.index + 1;
 	};
@@ -645,6 +681,12 @@ int main(int argc, char** argv) {
 	else {
 		fprintf(stderr, "# kmer skipped: 0\ndone\nserializing %s.trkmc.ar\n", o.outPrefix.c_str());
 		ok = write_trkmc_ar(o.outPrefix, counts, err) && write_tr_summary(o.outPrefix + ".tr.summary.txt", kmc, nmap, err);
+	}
+	if (ok && S.bubbles) {                                                       // cpp:2648-2651
+		fprintf(stderr, "writing bubbles...\n");
+		uint64_t nskip = 0;
+		ok = S.bubbles->write(o.outPrefix, nskip, err);
+		fprintf(stderr, "# kmer skipped: %llu\nserializing %s.bub.kmdb\n", (unsigned long long)nskip, o.outPrefix.c_str());
 	}
 	if (!ok) { fprintf(stderr, "danbing-tk: %s\n", err.c_str()); return 1; }
 	fprintf(stderr, "all done!\n");

@@ -41,6 +41,7 @@ struct Rpgg {
 	std::vector<uint8_t> qc;
 	std::vector<uint64_t> g_n, g_kmers;        // PREF.graph.kmers: per-locus node counts + strand-specific k-mers (sorted, unique)
 	std::vector<uint8_t> g_masks;              // 4-bit out-edge masks
+	std::vector<uint64_t> tre_n, tre_kmers;    // PREF.tre.kdb (`-bu`): per-locus TR (k+1)-mer edges
 };
 
 inline bool read_whole_file(const std::string& fn, std::vector<char>& buf, std::string& err) {

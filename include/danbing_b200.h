@@ -53,6 +53,8 @@ extern "C" {
 #define DBT_F_ALN_MIN    0x040u /* `-ae`                                                       */
 #define DBT_F_SIM        0x100u /* `-s 1|2` (cpp:2169): kam records also for pairs whose both mates assignTRkmc removed (dst = nloci); the
                                    caller prints them when the read name carries a source locus */
+#define DBT_F_BUBBLES    0x200u /* `-bu` (cpp:1559-1606): novel (k+1)-mer edges inside the observed TR segment of every kept mate of a counted
+                                   pair are handed back as events (dbt_bubble_events); needs tre_n / tre_kmers in dbt_index; not with threading */
 #define DBT_F_EXTRACT    0x080u /* `-e 1|2` (cpp:2094-2099, 1618-1644): a pair that passes the locus vote and the QC gate is
                                    handed out as a record (status COUNTED, dst = its locus, no annotation) and NOTHING is counted */
 
@@ -153,6 +155,7 @@ typedef struct {
   const uint64_t* fl_n;   const uint64_t* fl_kmers;
   const uint8_t*  qc;
   const uint64_t* g_n;    const uint64_t* g_kmers;  const uint8_t* g_masks;
+  const uint64_t* tre_n;  const uint64_t* tre_kmers;  /* PREF.tre.kdb: per-locus TR (k+1)-mer edges (readBinaryKmerSetDB, h:675-698); NULL unless DBT_F_BUBBLES */
 } dbt_index;
 
 #define DBT_LAYOUT_ASCII   0   /* concatenated ASCII read sequences + byte offsets               */
@@ -288,6 +291,10 @@ int  dbt_upload_raw(dbt_ctx*, const dbt_raw_batch*, dbt_raw_info* info, int slot
 /* optional: allocate both slots (and, raw_bytes > 0, the splitter's buffers for texts of that size) now instead of on first use */
 int  dbt_prepare(dbt_ctx*, uint64_t raw_bytes);
 uint64_t dbt_title_hash(const uint8_t* title, size_t len);     /* FNV-1a 64 of the pruned title, as the device computes it */
+/* `-bu`: after dbt_wait(slot), the novel edges of the batch (unordered; the caller sorts by key and replays them into the reference's
+   containers, cpp:1565, 1599-1606).  key = pair index within the batch << 10 | mate << 9 | k-mer position; locus = the pair's locus.
+   Returns DBT_E_CAPACITY when the batch produced more events than the slot holds (4 per pair + 2^20): submit smaller batches. */
+int  dbt_bubble_events(dbt_ctx*, int slot, uint64_t* key, uint64_t* edge, uint32_t* locus, uint64_t cap, uint64_t* n);
 /* [0] H2D + split kernels [1] pack_kernel of the slot's last dbt_upload_raw, milliseconds */
 int  dbt_raw_times(dbt_ctx*, int slot, float ms[2]);
 

@@ -270,3 +270,40 @@ def test_cli_vs_reference_live_simulation_truth_in_kam(simmode, tmp_path):
         assert counters(ge) == counters(re_)
     removed = [l for l in go.decode().splitlines() if l.split("\t")[1] == str(nloci)]
     assert removed, "no removed pair with a known source locus in this input: the test does not exercise cpp:2169"
+
+
+@needs_ref
+@pytest.mark.parametrize("extra", [pytest.param([], id="gpu-reader"), pytest.param(["--batch-pairs", 300], id="gpu-reader-small-chunks"),
+                                   pytest.param(["--host-reader", "-r", 0.004], id="host-reader-small-ref-batches")])
+def test_cli_vs_reference_live_bubbles(extra, tmp_path):
+    """`-bu` (cpp:1559-1606): reads that carry a recurring variant absent from the graph -> OUT.bub.kmdb (edges seen >= 5 times, in the
+    reference's hashtable order) byte for byte; the reference runs with -p 1 (its batches merge in completion order otherwise)"""
+    pref, fa = stage_case("multi", tmp_path)
+    lines = open(fa).read().split("\n")[:-1]
+    seqs = lines[1::2]
+    rng = random.Random(23)
+    comp = {"A": "C", "C": "G", "G": "T", "T": "A"}
+    for _ in range(150):                                   # a variant = the middle base of a 31-mer of some read, changed in every read that has it
+        s = seqs[rng.randrange(len(seqs))]
+        if len(s) < 80:
+            continue
+        o = rng.randrange(20, len(s) - 51)
+        seed = s[o:o + 31]
+        var = seed[:15] + comp.get(seed[15], "A") + seed[16:]
+        seqs = [x.replace(seed, var) for x in seqs]
+    fx = tmp_path / "reads_var.fa"
+    with open(fx, "w") as f:
+        for t, s in zip(lines[0::2], seqs):
+            f.write(t + "\n" + s + "\n")
+    rflag = [x for x in extra if x in ("-r", 0.004)]
+    args = ["-k", 21, "-kf", 4, 1, "-cth", 30, "-bu", "-p", 1] + rflag + ["-qs", pref, "-fa", fx]
+    a = run_cli(CLI, args + [x for x in extra if x not in rflag] + ["-o", tmp_path / "gpu"], tmp_path)
+    b = run_cli(ref_bin("danbing-tk"), args + ["-o", tmp_path / "ref"], tmp_path)
+    assert a[0] == b[0]
+    assert open(tmp_path / "gpu.trkmc.ar", "rb").read() == open(tmp_path / "ref.trkmc.ar", "rb").read()
+    bub = open(tmp_path / "ref.bub.kmdb", "rb").read()
+    assert open(tmp_path / "gpu.bub.kmdb", "rb").read() == bub
+    nloci = golden_case("multi")["ix"]["nloci"]
+    nk = int(np.frombuffer(bub, "<u8", 1, 8 + 8 * nloci)[0])
+    assert nk >= 10, "the input produced too few recurring novel edges to test anything"
+    assert counters(a[1]) == counters(b[1])
