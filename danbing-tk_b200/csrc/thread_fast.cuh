@@ -220,6 +220,7 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 				if (lane == 0) { W.T[j] = bt; W.ok[j] = bo; }
 			}
 			__syncwarp();
+			int es_end = (int)len, tr_end = nkm;                              // a walk that ends early (cpp:1182-1185) leaves the entries from here on '*'
 			uint64_t xlist = 0; int nfix = 0;                                 // corrected mate: 'X' entries of the CIGAR, 16 bits each: position | graph base (1-4) << 13
 			if (!clean && correction1) {
 				// ---- substitutions in the interior of the read, graph without a branch there ----
@@ -235,6 +236,11 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 				// near an end, an indel, a branch, a missing node -- is thread_kernel's, which starts over from the packed read.
 				const uint32_t maxskip = (uint32_t)nkm > rp.thread_cth ? (uint32_t)nkm - rp.thread_cth : 0u;
 				int from = 0; bool fail = false;
+				// Stops near the end of the read.  With nrem = nkm - ki k-mers left: nrem <= 5 ends the walk (cpp:1182-1185: the rest is
+				// skipped, no correction); nrem = k+1 is the interior case (every family's walk is still at most k steps); 6 <= nrem <= k:
+				// the 1-mismatch walk is nrem-1 steps long and only the two deletion families walk one step further (jb = 0, cpp:961,
+				// 1040) -- they are not tried at all unless the wrong base is an out-edge of the corrected k-mer (1 deletion, cpp:957)
+				// or of its successor (2 deletions, cpp:1036, needs >= 12 k-mers left), and then the pair is left to thread_kernel.
 #pragma unroll 1
 				for (;;) {
 					int ki = nkm;
@@ -245,13 +251,20 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 						if (z) ki = j * 32 + __ffs(z) - 1;
 					}
 					if (ki >= nkm) break;                                         // nothing stops the walk any more
-					if (nfix >= 4 || (uint32_t)nfix >= rp.max_ncorrection || (uint32_t)nfix + 1 > maxskip || ki < 1 || ki + (int)K + 2 > nkm) { fail = true; break; }
+					const int nrem = nkm - ki;
+					if (ki >= 1 && nrem <= (int)THR_MSC) {                           // cpp:1182-1185
+						if ((uint32_t)(nfix + nrem) > maxskip) { fail = true; break; }   // the read does not thread: thread_kernel reports it
+						es_end = ki + (int)K - 1; tr_end = ki;
+						break;
+					}
+					if (nfix >= 4 || (uint32_t)nfix >= rp.max_ncorrection || (uint32_t)nfix + 1 > maxskip || ki < 1) { fail = true; break; }
+					const int nrw = min(nrem, (int)K);                            // k-mers the edit rewrites: ki .. ki+nrw-1
 					const uint32_t pm = (uint32_t)(W.nb[ki] >> 1) & 0xFu;        // out-edges of k-mer ki-1 (never a rewritten one: ki-1 >= from-1)
 					if (__popc(pm) != 1) { fail = true; break; }
 					const uint32_t a = (uint32_t)__ffs(pm) - 1u;
 					const int t = lane;                                           // lane t < k: k-mer ki+t with the wrong base (2t bits up) replaced
 					uint64_t c = 0; uint32_t bits = 0, trp = 0, f3n = 0;
-					if (t < (int)K) {
+					if (t < nrw) {
 						const uint64_t kw = W.key[ki + t];
 						const uint64_t cn = kw & kmask;
 						const uint64_t fw = (kw & THRF_RCFLAG) ? kmer_rc(cn, K) : cn;
@@ -259,18 +272,24 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 						const GNode g = g_lookup_fast_nl<B>(gt, c, dst, K);
 						bits = g.bits; trp = g.tr;
 						++c_probe;
-						f3n = (uint32_t)(W.key[ki + t + 1] >> THRF_F3_SHIFT) & 3u;   // last base of the next k-mer (ki + t + 1 < nkm)
+						if (ki + t + 1 < nkm) f3n = (uint32_t)(W.key[ki + t + 1] >> THRF_F3_SHIFT) & 3u;   // last base of the next k-mer
 					}
 					// lane t (< k): present, and the next k-mer's last base is an out-edge (lane 0: its ONLY out-edge, the level-2
 					// expansion of the scorer then holds just that base, cpp:907-920)
 					bool good = true;
-					if (t < (int)K) {
+					if (t < nrw && ki + t + 1 < nkm) {                             // (the last k-mer of the read is only visited, cpp:553)
 						const uint32_t mk = gn_mask(bits);
 						good = (bits & GN_PRESENT) && ((mk >> f3n) & 1u) && (t != 0 || __popc(mk) == 1);
 					}
-					if (!__all_sync(0xffffffffu, good)) { fail = true; break; }
+					if (nrem <= (int)K) {                                         // deletion families must not be in play (see above)
+						const uint32_t oldnt = (uint32_t)(W.key[ki] >> THRF_F3_SHIFT) & 3u;
+						const uint32_t m0 = __shfl_sync(0xffffffffu, gn_mask(bits), 0), m1 = __shfl_sync(0xffffffffu, gn_mask(bits), 1);
+						if (((m0 >> oldnt) & 1u) || (nrem >= 2 * (int)THR_MSC + 2 && ((m1 >> oldnt) & 1u))) good = false;
+					}
+					const bool allgood = __all_sync(0xffffffffu, good);
+					if (!allgood) { fail = true; break; }
 					__syncwarp();
-					if (t < (int)K) {
+					if (t < nrw) {
 						const uint64_t rc = kmer_rc(c, K);
 						const bool is_rc = rc < c;
 						W.key[ki + t] = (is_rc ? rc : c) | ((c & 3) << THRF_F3_SHIFT) | (is_rc ? THRF_RCFLAG : 0ull);
@@ -282,7 +301,7 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 					from = ki + (int)K + 1;                                       // the walk resumes here (cpp:1197: ki += score - 1, then the loop's ++ki)
 					if (lane == 0) c_ec += K + 2;                                 // look-ups of the scorer's winning path: 1 + 1 expansion nodes + k walk steps
 				}
-				if (!fail && nfix) {
+				if (!fail && (nfix || tr_end < nkm)) {
 #pragma unroll 1
 					for (int j = 0; j < ng; ++j) {                                 // TR ballots again: the rewritten k-mers have their own
 						const int i = j * 32 + lane;
@@ -320,7 +339,7 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 				const int nes = min((int)len, (int)rp.es_cap), ntr = min(nkm, (int)rp.tr_cap);
 #pragma unroll 1
 				for (int q = lane; q < (int)rp.es_cap / 4; q += 32) {         // four entries per lane and store; entries >= nes read 0
-					const int nbb = nes - 4 * q;
+					const int nbb = min(nes, es_end) - 4 * q;
 					const uint32_t keep = nbb >= 4 ? 0xFFFFFFFFu : (nbb <= 0 ? 0u : (1u << 8 * nbb) - 1u);
 					uint32_t v = 0x01010101u * ET_EQ;
 #pragma unroll 1
@@ -332,7 +351,7 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 				}
 #pragma unroll 1
 				for (int q = lane; q < (int)rp.tr_cap / 4; q += 32) {         // tr[i] = '=' (2) for TR k-mers, '.' (1) otherwise: 4 TR ballot bits -> 4 bytes
-					const int nbb = ntr - 4 * q;
+					const int nbb = min(ntr, tr_end) - 4 * q;
 					const uint32_t keep = nbb >= 4 ? 0xFFFFFFFFu : (nbb <= 0 ? 0u : (1u << 8 * nbb) - 1u);
 					const uint32_t bits = 4 * q < ng * 32 ? (W.T[(4 * q) >> 5] >> ((4 * q) & 31)) & 0xFu : 0u;
 					const uint32_t v = 0x01010101u + ((bits & 1u) | ((bits & 2u) << 7) | ((bits & 4u) << 14) | ((bits & 8u) << 21));
@@ -340,7 +359,7 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 				}
 				if (lane == 0) {
 					dbt_aln_mate* h = reinterpret_cast<dbt_aln_mate*>(b);
-					h->alned = nfix ? 2 : 1; h->err = (uint8_t)((int)len > (int)rp.es_cap || nkm > (int)rp.tr_cap);
+					h->alned = nfix ? 2 : 1;                          // cpp:1259 / 1184 h->err = (uint8_t)((int)len > (int)rp.es_cap || nkm > (int)rp.tr_cap);
 					h->nes = (uint16_t)len; h->ntr = (uint16_t)nkm; h->nkm = (uint16_t)nkm;
 					uint64_t hash = 0;
 					if (trace) {                                                // FNV-1a over the k-mer vector (parity tests only)
