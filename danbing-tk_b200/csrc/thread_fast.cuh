@@ -65,10 +65,11 @@ struct FastThreadWarp {
 	uint4    stage[MAXJ][B][32];               // home (then stash) buckets of every position of the mate being probed
 	uint64_t key[MAXJ * 32];                   // canonical k-mer | last base << 60 | THRF_RCFLAG; KMER_INVALID for an invalid window
 	uint32_t trx[MAXJ * 32];                   // count-array position + 1 of TR k-mers, else 0
-	uint8_t  nb[MAXJ * 32 + 32];               // nb[i + 1] = present | out-edge mask << 1 of position i (nb[0]: unused)
+	uint16_t nb[MAXJ * 32 + 32];               // nb[i + 1] = GNode bits 0-9 of position i: present | out-edge mask << 1 | the same of the reverse strand << 5 (nb[0]: unused)
 	uint64_t pk[2 * MAXJ + 6];                 // packed record of the mate (W64 <= 1.5 MAXJ + 4 for reads of <= MAXJ*32 k-mers)
 	uint32_t T[MAXJ];                          // TR ballots
 	uint32_t ok[MAXJ];                         // "on an out-edge of its predecessor" ballots (position 0: is a node)
+	uint32_t P[MAXJ];                          // "is a node" ballots
 };
 
 template <int B, int MAXJ>
@@ -163,7 +164,7 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 					}
 					if (!found && full && (k0 & SLOT_OVF)) need |= 1u << j;
 				}
-				W.nb[i + 1] = (uint8_t)(bi & 0x1Fu); W.trx[i] = trp;
+				W.nb[i + 1] = (uint16_t)(bi & 0x3FFu); W.trx[i] = trp;
 			}
 			if (__any_sync(0xffffffffu, need != 0)) {                        // second round: first stash bucket, batched like the first
 				__syncwarp();
@@ -198,7 +199,7 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 						const GNode n = g_lookup_canon_nl<B>(gt, canon, is_rc, dst, stash_next(gt, stash_bucket(gt, canon ^ lmix)));
 						bi = n.bits; trp = n.tr;
 					}
-					W.nb[i + 1] = (uint8_t)(bi & 0x1Fu); W.trx[i] = trp;
+					W.nb[i + 1] = (uint16_t)(bi & 0x3FFu); W.trx[i] = trp;
 				}
 			}
 			__syncwarp();
@@ -217,9 +218,11 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 				const uint32_t bo = __ballot_sync(0xffffffffu, ok);
 				if (bo != 0xffffffffu) clean = false;
 				const uint32_t bt = __ballot_sync(0xffffffffu, tr);
-				if (lane == 0) { W.T[j] = bt; W.ok[j] = bo; }
+				const uint32_t bp = __ballot_sync(0xffffffffu, i < nkm && (W.nb[i + 1] & 1u));
+				if (lane == 0) { W.T[j] = bt; W.ok[j] = bo; W.P[j] = bp; }
 			}
 			__syncwarp();
+			int es_beg = 0, tr_beg = 0;                                       // ... and skipped k-mers before the anchor leave the entries before it '*'
 			int es_end = (int)len, tr_end = nkm;                              // a walk that ends early (cpp:1182-1185) leaves the entries from here on '*'
 			uint64_t xlist = 0; int nfix = 0;                                 // corrected mate: 'X' entries of the CIGAR, 16 bits each: position | graph base (1-4) << 13
 			if (!clean && correction1) {
@@ -236,13 +239,78 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 				// near an end, an indel, a branch, a missing node -- is thread_kernel's, which starts over from the packed read.
 				const uint32_t maxskip = (uint32_t)nkm > rp.thread_cth ? (uint32_t)nkm - rp.thread_cth : 0u;
 				int from = 0; bool fail = false;
+				int nskip = 0;                                                    // k-mers skipped so far (cpp:1123); every correction adds its edit (cpp:1193)
+				// Start of the read.  The walk begins at the first k-mer `an` that is a node (find_anchor, cpp:878-888); the an k-mers
+				// before it are skipped, and when there are at least 6 of them errorCorrection_backward (cpp:1091-1106: the same
+				// scorer on the reverse complements, from the anchor towards the start) is tried once (cpp:1131-1141).  A wrong base
+				// in the first k bases makes exactly the k-mers that hold it non-nodes: an <= k, the mirror image of a stop with
+				// an k-mers left -- one 1-mismatch walk of an-1 steps on the reverse strand, the deletion families out of play under
+				// the same conditions -- and edit_kmers_backward (cpp:649-826) then rewrites k-mers 0..an-1, marks CIGAR entry an-1
+				// 'X' with the complement of the edge taken and the entries before it '=' (its merge rules see a tract of one entry).
+				{
+					int an = nkm;
+#pragma unroll 1
+					for (int j = ng - 1; j >= 0; --j) { const uint32_t z = W.P[j]; if (z) an = j * 32 + __ffs(z) - 1; }
+					if (an >= nkm) fail = true;                                   // no node at all: the read does not thread (cpp:1129)
+					else if (an > 0) {
+						if (an >= (int)THR_MSC + 1) {
+							const uint32_t nbw = W.nb[an + 1];
+							const uint32_t rm = (nbw >> 6) & 0xFu;                     // out-edges of the anchor's reverse complement
+							if (an > (int)K || !(nbw & GN_RCPRESENT) || __popc(rm) != 1 || rp.max_ncorrection < 1) fail = true;
+							else {
+								const uint32_t tb = 3u - ((uint32_t)__ffs(rm) - 1u);      // the base the graph has where the read is wrong (forward strand)
+								const int t = lane;                                       // lane t < an: k-mer an-1-t, wrong base = its base number t
+								uint64_t c = 0; uint32_t bits = 0, trp = 0, fb = 0;
+								if (t < an) {
+									const uint64_t kw = W.key[an - 1 - t];
+									const uint64_t cn = kw & kmask;
+									const uint64_t fw = (kw & THRF_RCFLAG) ? kmer_rc(cn, K) : cn;
+									const uint32_t shf = 2 * (K - 1 - (uint32_t)t);
+									c = (fw & ~(3ull << shf)) | ((uint64_t)tb << shf);
+									const GNode g = g_lookup_fast_nl<B>(gt, c, dst, K);
+									bits = g.bits; trp = g.tr;
+									++c_probe;
+									fb = (uint32_t)(c >> (2 * (K - 1))) & 3u;               // first base of the rewritten k-mer
+								}
+								const uint32_t fbn = __shfl_down_sync(0xffffffffu, fb, 1);  // first base of k-mer an-2-t: the next step of the reverse-strand walk appends its complement
+								bool good = true;
+								if (t + 1 < an) {
+									const uint32_t mk = gn_rcmask(bits);
+									good = (bits & GN_RCPRESENT) && ((mk >> (3u - fbn)) & 1u) && (t != 0 || __popc(mk) == 1);
+								}
+								{
+									const uint64_t kw = W.key[an - 1];
+									const uint64_t fw0 = (kw & THRF_RCFLAG) ? kmer_rc(kw & kmask, K) : (kw & kmask);
+									const uint32_t oldnt = 3u - ((uint32_t)(fw0 >> (2 * (K - 1))) & 3u);   // the wrong base as the reverse-strand walk reads it
+									const uint32_t m0 = __shfl_sync(0xffffffffu, gn_rcmask(bits), 0), m1 = __shfl_sync(0xffffffffu, gn_rcmask(bits), 1);
+									if (((m0 >> oldnt) & 1u) || (an >= 2 * (int)THR_MSC + 2 && ((m1 >> oldnt) & 1u))) good = false;
+								}
+								if (!__all_sync(0xffffffffu, good)) fail = true;
+								else {
+									__syncwarp();
+									if (t < an) {
+										const uint64_t rc = kmer_rc(c, K);
+										const bool is_rc = rc < c;
+										W.key[an - 1 - t] = (is_rc ? rc : c) | ((c & 3) << THRF_F3_SHIFT) | (is_rc ? THRF_RCFLAG : 0ull);
+										W.trx[an - 1 - t] = trp;
+									}
+									__syncwarp();
+									xlist |= (uint64_t)((uint32_t)(an - 1) | ((tb + 1) << 13)) << (16 * nfix);
+									++nfix; nskip = 1;                                      // cpp:690-694: the skipped k-mers are taken back, the edit stays
+									if (lane == 0) c_ec += (uint32_t)an + 1;
+								}
+							}
+						} else { nskip = an; es_beg = an; tr_beg = an; }            // too few k-mers to correct (cpp:1131): they stay skipped
+						from = an + 1;
+					}
+				}
 				// Stops near the end of the read.  With nrem = nkm - ki k-mers left: nrem <= 5 ends the walk (cpp:1182-1185: the rest is
 				// skipped, no correction); nrem = k+1 is the interior case (every family's walk is still at most k steps); 6 <= nrem <= k:
 				// the 1-mismatch walk is nrem-1 steps long and only the two deletion families walk one step further (jb = 0, cpp:961,
 				// 1040) -- they are not tried at all unless the wrong base is an out-edge of the corrected k-mer (1 deletion, cpp:957)
 				// or of its successor (2 deletions, cpp:1036, needs >= 12 k-mers left), and then the pair is left to thread_kernel.
 #pragma unroll 1
-				for (;;) {
+				for (; !fail;) {
 					int ki = nkm;
 #pragma unroll 1
 					for (int j = ng - 1; j >= (from >> 5); --j) {
@@ -253,11 +321,11 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 					if (ki >= nkm) break;                                         // nothing stops the walk any more
 					const int nrem = nkm - ki;
 					if (ki >= 1 && nrem <= (int)THR_MSC) {                           // cpp:1182-1185
-						if ((uint32_t)(nfix + nrem) > maxskip) { fail = true; break; }   // the read does not thread: thread_kernel reports it
+						nskip += nrem;
 						es_end = ki + (int)K - 1; tr_end = ki;
 						break;
 					}
-					if (nfix >= 4 || (uint32_t)nfix >= rp.max_ncorrection || (uint32_t)nfix + 1 > maxskip || ki < 1) { fail = true; break; }
+					if (nfix >= 4 || (uint32_t)nfix >= rp.max_ncorrection || (uint32_t)nskip + 1 > maxskip || ki < 1) { fail = true; break; }
 					const int nrw = min(nrem, (int)K);                            // k-mers the edit rewrites: ki .. ki+nrw-1
 					const uint32_t pm = (uint32_t)(W.nb[ki] >> 1) & 0xFu;        // out-edges of k-mer ki-1 (never a rewritten one: ki-1 >= from-1)
 					if (__popc(pm) != 1) { fail = true; break; }
@@ -297,11 +365,12 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 					}
 					__syncwarp();
 					xlist |= (uint64_t)((uint32_t)(ki + (int)K - 1) | ((a + 1) << 13)) << (16 * nfix);
-					++nfix;
+					++nfix; ++nskip;
 					from = ki + (int)K + 1;                                       // the walk resumes here (cpp:1197: ki += score - 1, then the loop's ++ki)
 					if (lane == 0) c_ec += K + 2;                                 // look-ups of the scorer's winning path: 1 + 1 expansion nodes + k walk steps
 				}
-				if (!fail && (nfix || tr_end < nkm)) {
+				if ((uint32_t)nskip > maxskip) fail = true;                       // cpp:1259: the read does not thread; thread_kernel reports it
+				if (!fail && (nfix || tr_end < nkm || tr_beg > 0)) {
 #pragma unroll 1
 					for (int j = 0; j < ng; ++j) {                                 // TR ballots again: the rewritten k-mers have their own
 						const int i = j * 32 + lane;
@@ -339,8 +408,8 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 				const int nes = min((int)len, (int)rp.es_cap), ntr = min(nkm, (int)rp.tr_cap);
 #pragma unroll 1
 				for (int q = lane; q < (int)rp.es_cap / 4; q += 32) {         // four entries per lane and store; entries >= nes read 0
-					const int nbb = min(nes, es_end) - 4 * q;
-					const uint32_t keep = nbb >= 4 ? 0xFFFFFFFFu : (nbb <= 0 ? 0u : (1u << 8 * nbb) - 1u);
+					const int nbb = min(nes, es_end) - 4 * q, nlo = es_beg - 4 * q;
+					const uint32_t keep = (nbb >= 4 ? 0xFFFFFFFFu : (nbb <= 0 ? 0u : (1u << 8 * nbb) - 1u)) & (nlo <= 0 ? 0xFFFFFFFFu : (nlo >= 4 ? 0u : 0xFFFFFFFFu << 8 * nlo));
 					uint32_t v = 0x01010101u * ET_EQ;
 #pragma unroll 1
 					for (int f = 0; f < nfix; ++f) {
@@ -351,8 +420,8 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 				}
 #pragma unroll 1
 				for (int q = lane; q < (int)rp.tr_cap / 4; q += 32) {         // tr[i] = '=' (2) for TR k-mers, '.' (1) otherwise: 4 TR ballot bits -> 4 bytes
-					const int nbb = min(ntr, tr_end) - 4 * q;
-					const uint32_t keep = nbb >= 4 ? 0xFFFFFFFFu : (nbb <= 0 ? 0u : (1u << 8 * nbb) - 1u);
+					const int nbb = min(ntr, tr_end) - 4 * q, nlo = tr_beg - 4 * q;
+					const uint32_t keep = (nbb >= 4 ? 0xFFFFFFFFu : (nbb <= 0 ? 0u : (1u << 8 * nbb) - 1u)) & (nlo <= 0 ? 0xFFFFFFFFu : (nlo >= 4 ? 0u : 0xFFFFFFFFu << 8 * nlo));
 					const uint32_t bits = 4 * q < ng * 32 ? (W.T[(4 * q) >> 5] >> ((4 * q) & 31)) & 0xFu : 0u;
 					const uint32_t v = 0x01010101u + ((bits & 1u) | ((bits & 2u) << 7) | ((bits & 4u) << 14) | ((bits & 8u) << 21));
 					reinterpret_cast<uint32_t*>(trb)[q] = v & keep;
