@@ -166,40 +166,60 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 				}
 				W.nb[i + 1] = (uint16_t)(bi & 0x3FFu); W.trx[i] = trp;
 			}
-			if (__any_sync(0xffffffffu, need != 0)) {                        // second round: first stash bucket, batched like the first
+			if (__any_sync(0xffffffffu, need != 0)) {
+				// second round: the first stash bucket of the few positions (7 % of the keys) whose home bucket overflowed.  They
+				// are compacted into a list first, so that the round is ONE pass of 32 lanes instead of a pass per 32-position
+				// group in which two or three lanes have work (those passes were a sixth of the kernel's instructions).
 				__syncwarp();
+				uint16_t* list = reinterpret_cast<uint16_t*>(&W.ok[0]);       // (W.ok / W.P are written by B2 below; 2 x MAXJ words hold 4 MAXJ entries)
+				int nlist = 0;
 #pragma unroll 1
 				for (int j = 0; j < ng; ++j) {
-					if (!((need >> j) & 1u)) continue;
-					const uint64_t canon = W.key[j * 32 + lane] & kmask;
-					const uint4* bp = gt.slots + stash_bucket(gt, canon ^ lmix) * B;
-#pragma unroll
-					for (int q = 0; q < B; ++q) cp_async16(&W.stage[j][q][lane], bp + q);
-					++c_probe;
+					const bool nd = (need >> j) & 1u;
+					const uint32_t bm = __ballot_sync(0xffffffffu, nd);
+					if (nd) { const int o = nlist + __popc(bm & ((1u << lane) - 1u)); if (o < 4 * MAXJ) list[o] = (uint16_t)(j * 32 + lane); }
+					nlist += __popc(bm);
 				}
-				cp_async_wait_all();
-#pragma unroll 1
-				for (int j = 0; j < ng; ++j) {
-					if (!((need >> j) & 1u)) continue;
-					const int i = j * 32 + lane;
-					const uint64_t kw = W.key[i];
+				__syncwarp();
+				if (nlist <= 4 * MAXJ && nlist <= 32) {
+					const bool act = lane < nlist;
+					const int i = act ? (int)list[lane] : 0;
+					const uint64_t kw = act ? W.key[i] : 0ull;
 					const uint64_t canon = kw & kmask;
-					const bool is_rc = (kw & THRF_RCFLAG) != 0;
-					uint32_t bi = 0, trp = 0;
-					bool full = true, found = false; uint64_t k0 = 0;
+					const uint64_t sb = stash_bucket(gt, canon ^ lmix);
+					if (act) {
+						const uint4* bp = gt.slots + sb * B;
 #pragma unroll
-					for (int q = 0; q < B; ++q) {
-						const uint4 sl = W.stage[j][q][lane];
-						const uint64_t kk = slot_key(sl);
-						if (q == 0) k0 = kk;
-						if (kk == SLOT_EMPTY) full = false;
-						else if ((kk & SLOT_KEYMASK) == canon && (sl.z & G_LOCUS_MASK) == dst) { const GNode n = g_decode(sl.z, sl.w, is_rc); bi = n.bits; trp = n.tr; found = true; }
+						for (int q = 0; q < B; ++q) cp_async16(&W.stage[0][q][lane], bp + q);
+						++c_probe;
 					}
-					if (!found && full && (k0 & SLOT_OVF)) {
-						const GNode n = g_lookup_canon_nl<B>(gt, canon, is_rc, dst, stash_next(gt, stash_bucket(gt, canon ^ lmix)));
-						bi = n.bits; trp = n.tr;
+					cp_async_wait_all();
+					if (act) {
+						const bool is_rc = (kw & THRF_RCFLAG) != 0;
+						uint32_t bi = 0, trp = 0;
+						bool full = true, found = false; uint64_t k0 = 0;
+#pragma unroll
+						for (int q = 0; q < B; ++q) {
+							const uint4 sl = W.stage[0][q][lane];
+							const uint64_t kk = slot_key(sl);
+							if (q == 0) k0 = kk;
+							if (kk == SLOT_EMPTY) full = false;
+							else if ((kk & SLOT_KEYMASK) == canon && (sl.z & G_LOCUS_MASK) == dst) { const GNode n = g_decode(sl.z, sl.w, is_rc); bi = n.bits; trp = n.tr; found = true; }
+						}
+						if (!found && full && (k0 & SLOT_OVF)) { const GNode n = g_lookup_canon_nl<B>(gt, canon, is_rc, dst, stash_next(gt, sb)); bi = n.bits; trp = n.tr; }
+						W.nb[i + 1] = (uint16_t)(bi & 0x3FFu); W.trx[i] = trp;
 					}
-					W.nb[i + 1] = (uint16_t)(bi & 0x3FFu); W.trx[i] = trp;
+				} else {
+					// more than 20 of them (never seen at load 0.4): the whole chain by plain look-ups
+#pragma unroll 1
+					for (int j = 0; j < ng; ++j) {
+						if (!((need >> j) & 1u)) continue;
+						const int i = j * 32 + lane;
+						const uint64_t kw = W.key[i];
+						const GNode n = g_lookup_canon_nl<B>(gt, kw & kmask, (kw & THRF_RCFLAG) != 0, dst, stash_bucket(gt, (kw & kmask) ^ lmix));
+						W.nb[i + 1] = (uint16_t)(n.bits & 0x3FFu); W.trx[i] = n.tr;
+						++c_probe;
+					}
 				}
 			}
 			__syncwarp();
