@@ -298,7 +298,7 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 		if (!xb.npairs) {
 			if (S.want_records && ngpu) {
 				const uint32_t stride = dbt_record_stride(w.ctx);
-				const int T = (int)std::min<uint64_t>(std::min<uint64_t>(std::max<uint64_t>(S.opt.nproc, 1), 16), ngpu / 8192 + 1);   // -p host threads format the lines
+				const int T = (int)std::min<uint64_t>(std::min<uint64_t>(std::max<uint64_t>(S.opt.nproc, 1), 16), ngpu / 1024 + 1);   // -p host threads format the lines
 				if (T <= 1) {
 					bo.parts.resize(1); bo.parts[0] = S.strings.get();
 					for (uint64_t i = 0; i < ngpu; ++i) format(bo.parts[0], w.recs[s] + i * stride, true);
@@ -421,7 +421,7 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 		}
 	}
 	if (!S.failed) for (int s = 0; s < DBT_N_SLOTS; ++s) { const int ss = (k + s) & 1; if (!finish(ss)) break; }
-	for (auto& r : w.recs) if (r) { dbt_host_free(r); r = nullptr; }
+	// (w.recs are released by main() after the last line is out: unpinning 1.4 GB takes longer than a chunk)
 	if (S.failed) { recycle.close(); S.turn.cv.notify_all(); }
 }
 
@@ -655,6 +655,7 @@ int main(int argc, char** argv) {
 			if (w->ctx) { dbt_destroy(w->ctx); w->ctx = nullptr; }
 		}
 	}
+	for (auto& w : workers) for (auto& r : w->recs) if (r) { dbt_host_free(r); r = nullptr; }
 	for (auto& hb : pool) { dbt_host_free(hb->bases); dbt_host_free(hb->offsets); }
 	for (auto& c : rpool) { dbt_host_free(c->buf); dbt_host_free(c->pair_offset); dbt_host_free(c->pair_hash); dbt_host_free(c->single_offset); }
 	if (o.timing) {
