@@ -183,6 +183,7 @@ def load_library(path=LIB_PATH):
     L.dbt_upload.argtypes = [ctxp, C.POINTER(Batch), C.c_int]
     L.dbt_upload_raw.argtypes = [ctxp, C.POINTER(RawBatch), C.POINTER(RawInfo), C.c_int]
     L.dbt_prepare.argtypes = [ctxp, C.c_uint64]
+    L.dbt_graph_merged.argtypes = [ctxp]
     L.dbt_bubble_events.argtypes = [ctxp, C.c_int, u64p, u64p, u32p, C.c_uint64, u64p]
     L.dbt_title_hash.argtypes = [C.c_char_p, C.c_size_t]
     L.dbt_title_hash.restype = C.c_uint64
@@ -218,7 +219,7 @@ def load_library(path=LIB_PATH):
     return L
 
 
-ABI_SYMBOLS = ["dbt_bubble_events", "dbt_prepare", "dbt_upload_raw", "dbt_title_hash", "dbt_raw_times", "dbt_abi_version", "dbt_device_count", "dbt_default_params", "dbt_create", "dbt_destroy",
+ABI_SYMBOLS = ["dbt_graph_merged", "dbt_bubble_events", "dbt_prepare", "dbt_upload_raw", "dbt_title_hash", "dbt_raw_times", "dbt_abi_version", "dbt_device_count", "dbt_default_params", "dbt_create", "dbt_destroy",
                "dbt_strerror", "dbt_last_error", "dbt_load_index", "dbt_upload", "dbt_process", "dbt_fetch",
                "dbt_submit", "dbt_wait", "dbt_download", "dbt_reset_counts", "dbt_nk_tr", "dbt_nloci",
                "dbt_record_stride", "dbt_record_as_stride", "dbt_record_aln_stride", "dbt_record_es_cap", "dbt_nccl_unique_id", "dbt_comm_init", "dbt_allreduce",

@@ -252,7 +252,8 @@ __device__ __noinline__ MateOut assign_masks(const MaskSet<MAXJ> Fs, const MaskS
 // out-of-line rare paths (kept out of the hot loop's instruction footprint)
 // ------------------------------------------------------------------------------------------------
 // continue a probe in the stash, starting with stash bucket b (home bucket full + overflow flag)
-template <int B>
+// (RAW: hand the value word out as stored, with the graph entry in its top bits -- candidate_fast_kernel; else masked)
+template <int B, bool RAW = false>
 __device__ __noinline__ uint2 probe_walk(const Table t, uint64_t key, uint64_t b) {
 	for (;;) {
 		bool full = true; uint64_t k0 = 0;
@@ -262,7 +263,7 @@ __device__ __noinline__ uint2 probe_walk(const Table t, uint64_t key, uint64_t b
 			const uint64_t kk = slot_key(e);
 			if (q == 0) k0 = kk;
 			if (kk == SLOT_EMPTY) full = false;
-			else if ((kk & SLOT_KEYMASK) == key) return make_uint2(e.z, e.w);
+			else if ((kk & SLOT_KEYMASK) == key) return make_uint2(RAW ? e.z : slot_val(e.z), e.w);
 		}
 		if (!full || !(k0 & SLOT_OVF)) return make_uint2(0u, AUX_MISS);
 		b = stash_next(t, b);
@@ -448,7 +449,7 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 						for (int q = 0; q < B; ++q) {
 							const uint64_t kk = slot_key(s[j][q]);
 							if (kk == SLOT_EMPTY) full = false;
-							else if ((kk & SLOT_KEYMASK) == key[j]) { v = s[j][q].z; a = s[j][q].w; found = true; }
+							else if ((kk & SLOT_KEYMASK) == key[j]) { v = slot_val(s[j][q].z); a = s[j][q].w; found = true; }
 						}
 						if (!found && full && (slot_key(s[j][0]) & SLOT_OVF)) { const uint2 r2 = probe_walk<B>(ix.table, key[j], stash_bucket(ix.table, key[j])); v = r2.x; a = r2.y; }
 					}

@@ -25,6 +25,7 @@
 // __match_any_sync before the 64-bit atomic.
 #pragma once
 #include "candidate.cuh"
+#include "thread_fast.cuh"      // thrf_finish_mate / thrf_finish_pair: threading from the index entries when the graphs are merged into them
 
 namespace dbt {
 
@@ -36,6 +37,16 @@ constexpr int CAND_FAST_WARPS = 8;
 // bound (stall_no_instruction 5.0 per issue, issue slots 29 % busy).  Index buckets are staged through
 // shared memory with cp.async so that the probe loop can be rolled and still keep MAXJ x B 16-byte loads
 // per lane in flight.
+// class word of a k-mer w.r.t. locus `loc` (classify2) from the RAW value word, plus its graph entry there
+__device__ __forceinline__ uint32_t classify2g(const DevIndex& ix, uint32_t z, uint32_t aux, uint32_t loc, uint32_t& g) {
+	g = 0;
+	if (aux == AUX_MISS) return 0;
+	if (!(z & 1u)) { if (((z & VAL_LOCUS_MASK) >> 1) != loc) return 0; g = z >> VAL_LOCUS_BITS; return aux; }
+	const uint32_t off = z >> 1, n = __ldg(ix.vv + off);
+	for (uint32_t j = 1; j <= n; ++j) if (__ldg(ix.vv + off + j) == loc) { if (ix.vv_g) g = __ldg(ix.vv_g + off + j); return __ldg(ix.vv_aux + off + j); }
+	return 0;
+}
+
 template <int B, int MAXJ>
 struct FastWarp {
 	uint4    slot[MAXJ][B][32];            // bucket staging: slot q of the bucket probed for position j*32+lane
@@ -43,6 +54,7 @@ struct FastWarp {
 	uint32_t val[2][MAXJ * 32];            // index value per position              (during the probe: k-mer, low half)
 	uint32_t aux[2][MAXJ * 32];            // aux word per position, AUX_MISS = not in the index (during the probe: k-mer, high half);
 	                                       // after classification: class word w.r.t. dst0
+	uint16_t g[2][MAXJ * 32];              // graph entry of the k-mer in dst0 (ten bits, canonical orientation first; graphs merged into the index only)
 	uint32_t hit[2][MAXJ], F[2][MAXJ], T[2][MAXJ];   // ballots: in the index / flank of dst0 / TR of dst0
 	dbt_mate_record mate[2];
 };
@@ -60,6 +72,10 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 	const uint32_t nloci = (uint32_t)ix.nloci, cth = rp.cth;
 	FastWarp<B, MAXJ>& W = wsm[wib];
 	uint32_t c_kf = 0, c_laf = 0, c_qc = 0, c_thr = 0, c_asgn = 0, c_h1 = 0, c_inc = 0, c_thr0 = 0;   // lane-0 accumulators
+	const bool fused = rp.thr_on && ix.gmerged && !(rp.flags & DBT_F_TRACE);   // thread the pairs here, from the index entries (graphs merged into the index)
+	const bool want_aln = (rp.flags & (DBT_F_ALN | DBT_F_ALN_MIN)) != 0;
+	uint32_t t_fea = 0, t_walk = 0, t_items = 0;
+	ThrfCount TC;
 	const uint32_t nwork = sv.ncand[0];
 
 #pragma unroll 1
@@ -154,7 +170,7 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 						else if ((kk & SLOT_KEYMASK) == key) { v = e.z; a = e.w; found = true; }
 					}
 					if (!found && full && (k0 & SLOT_OVF)) {           // second stash bucket and beyond: rare, divergent walk
-						const uint2 r2 = probe_walk<B>(ix.table, key, stash_next(ix.table, stash_bucket(ix.table, key)));
+						const uint2 r2 = probe_walk<B, true>(ix.table, key, stash_next(ix.table, stash_bucket(ix.table, key)));
 						v = r2.x; a = r2.y;
 					}
 					W.val[m][i] = v; W.aux[m][i] = a;
@@ -224,14 +240,14 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 				if (em) { val0 = __shfl_sync(0xffffffffu, v, __ffs(em) - 1); have0 = true; }
 			}
 		}
-		const uint32_t dst0 = val0 >> 1;
+		const uint32_t dst0 = (val0 & VAL_LOCUS_MASK) >> 1;             // (the value words are kept raw here: their top bits carry the graph entry)
 		// class of every k-mer w.r.t. A (= what assignTRkmc looks up, cpp:1464-1469); a hit belongs to A iff its class != 0
 		bool differs = false; uint32_t S2 = 0;                   // S2 = hit positions of surviving mates on multi-locus k-mers
 		if (have0) {
 #pragma unroll 1
 			for (int m = 0; m < 2; ++m) {
 				const bool rmv = (rmm >> m) & 1u;
-				if (rmv && !okam) {                                 // cpp:1451: a removed mate is only annotated for the kam line
+				if (rmv && !okam && !fused) {                       // cpp:1451: a removed mate is only annotated for the kam line (threading needs both mates)
 					if (lane == 0) {
 #pragma unroll
 						for (int j = 0; j < MAXJ; ++j) { W.F[m][j] = 0; W.T[m][j] = 0; }
@@ -243,9 +259,10 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 				for (int j = 0; j < MAXJ; ++j) {
 					const uint32_t i = j * 32 + lane;
 					const uint32_t v = W.val[m][i];
-					uint32_t cw = 0;
-					if (i < nkm) cw = classify2(ix, v, W.aux[m][i], dst0);
+					uint32_t cw = 0, gg = 0;
+					if (i < nkm) cw = classify2g(ix, v, W.aux[m][i], dst0, gg);
 					W.aux[m][i] = cw;                               // from here on: class word w.r.t. A
+					if (fused) W.g[m][i] = (uint16_t)gg;
 					const uint32_t fm = __ballot_sync(0xffffffffu, (cw >> AUX_CLASS_SHIFT) == 1);
 					const uint32_t tm = __ballot_sync(0xffffffffu, (cw >> AUX_CLASS_SHIFT) == 2);
 					const uint32_t om = __ballot_sync(0xffffffffu, v & 1u);
@@ -284,6 +301,67 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 		}
 
 		if (status < 0 && (rp.flags & DBT_F_THREADING)) {
+			if (rp.thr_on && fused) {
+				// restored threading, from what this warp already holds: the index entry of every position carries the graph entry
+				// of (k-mer, dst) and the count position of a TR k-mer, i.e. everything thread_fast_kernel would probe the graph table
+				// for.  The staging area of the probes is free now and takes the per-mate arrays thrf_finish_mate works on.
+				if (lane == 0) c_thr0 += 2;
+				const uint32_t dw = dst | (kfm << 28) | (rmm << 30);
+				const bool slot_ok = want_aln && c < rp.max_records;
+				uint8_t* recp = sv.records + (uint64_t)c * rp.rec_stride;
+				if (slot_ok && lane == 0) reinterpret_cast<dbt_pair_record*>(recp)->status = (uint8_t)DBT_ST_THREAD_PENDING;
+				uint8_t* ov = reinterpret_cast<uint8_t*>(&W.slot[0][0][0]);
+				ThrfArrays A;
+				A.key = reinterpret_cast<uint64_t*>(ov); A.trx = reinterpret_cast<uint32_t*>(ov + MAXJ * 32 * 8);
+				A.nb = reinterpret_cast<uint16_t*>(ov + MAXJ * 32 * 12); A.T = reinterpret_cast<uint32_t*>(ov + MAXJ * 32 * 12 + (MAXJ * 32 + 32) * 2);
+				A.ok = A.T + MAXJ; A.P = A.ok + MAXJ;
+				uint32_t dirty = 0;
+#pragma unroll 1
+				for (int m = 0; m < 2; ++m) {
+					const uint32_t nkm = m ? nk1 : nk0;
+					const uint32_t len = nkm + K - 1;
+					if ((int)nkm < 1 || nkm > (uint32_t)MAXJ * 32) { dirty |= 1u << m; continue; }
+					const uint64_t* rec = W.pk + m * W64;
+					const uint32_t* mk32 = reinterpret_cast<const uint32_t*>(rec + WB);
+					const uint32_t sh = 2 * lane;
+					const uint64_t kmask = (1ull << (2 * K)) - 1, vmask = (1ull << K) - 1;
+					const int ng = ((int)nkm + 31) >> 5;
+					bool plain = true, anyvalid = false;
+					__syncwarp();
+#pragma unroll 1
+					for (int j = 0; j < ng; ++j) {
+						const uint32_t i = j * 32 + lane;
+						const uint64_t wlo = rec[j], whi = (j + 1 < (int)WB) ? rec[j + 1] : 0ull;
+						const uint32_t mlo = mk32[j], mnx = ((uint32_t)(j + 1) < 2 * rp.lay.WM) ? mk32[j + 1] : 0xFFFFFFFFu;
+						const uint64_t wv = sh ? ((wlo >> sh) | (whi << (64 - sh))) : wlo;
+						const uint64_t mm = (((uint64_t)mnx << 32) | mlo) >> lane;
+						uint64_t kk = KMER_INVALID; uint32_t nbv = 0, trp = 0;
+						if (i < nkm) {
+							if ((mm & vmask) == 0) {
+								const uint64_t x = wv & kmask, rcx = (~wv) & kmask, fw = rev2(x) >> (64 - 2 * K);
+								const bool is_rc = rcx < fw;
+								kk = (is_rc ? rcx : fw) | ((fw & 3) << THRF_F3_SHIFT) | (is_rc ? THRF_RCFLAG : 0ull);
+								anyvalid = true;
+								if (i + 1 < nkm && ((wv >> 2) & kmask) == x) plain = false;
+								const uint32_t gg = W.g[m][i], cw = W.aux[m][i];
+								nbv = is_rc ? (((gg & 31u) << 5) | (gg >> 5)) : gg;
+								trp = (cw >> AUX_CLASS_SHIFT) == 2 ? (cw & AUX_IDX_MASK) + 1u
+								    : (((cw >> AUX_CLASS_SHIFT) == 1 && (cw & AUX_FLANK_TR)) ? (cw & (AUX_FLANK_TR - 1)) + 1u : 0u);   // a TR k-mer classed flank still counts here
+							} else plain = false;
+						}
+						A.key[i] = kk; A.nb[i + 1] = (uint16_t)nbv; A.trx[i] = trp;
+					}
+					__syncwarp();
+					anyvalid = __any_sync(0xffffffffu, anyvalid);
+					plain = __all_sync(0xffffffffu, plain);
+					if (lane == 0 && anyvalid) t_walk += nkm;
+					if (!plain) { dirty |= 1u << m; continue; }
+					if (!thrf_finish_mate<B, MAXJ>(ix, rp, sv, A, m, len, (int)nkm, dst, recp, slot_ok, false, lane, TC)) dirty |= 1u << m;
+				}
+				thrf_finish_pair(rp, sv, c, p, dw, dst, dirty, recp, slot_ok, want_aln, false, lane, t_fea, t_items);
+				__syncwarp();
+				continue;
+			}
 			if (rp.thr_on) {                                     // restored threading: hand the pair to thread_kernel (cpp:2070-2088)
 				status = DBT_ST_THREAD_PENDING;
 				if (lane == 0) { c_thr0 += 2; sv.thr[atomicAdd(sv.ncand + 3, 1u)] = make_uint4(c, p, dst | (kfm << 28) | (rmm << 30), 0u); }
@@ -408,6 +486,15 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel
 		counter_add(sv.counters, DBT_C_NASGNREADS, c_asgn);
 		counter_add(sv.counters, DBT_C_NHASH1, c_h1);
 		counter_add(sv.counters, DBT_C_NINC, c_inc);
+	}
+	if (fused) {                                                 // what thread_fast_kernel reports for the pairs it threads
+		const uint32_t t_probe = __reduce_add_sync(0xffffffffu, TC.probe);
+		if (lane == 0) {
+			counter_add(sv.counters, DBT_C_THR_WALK, t_walk); counter_add(sv.counters, DBT_C_THR_REFRESH, t_probe);
+			counter_add(sv.counters, DBT_C_THR_CLS, TC.cls); counter_add(sv.counters, DBT_C_NFEASIBLEREADS, t_fea);
+			counter_add(sv.counters, DBT_C_NINC, TC.inc); counter_add(sv.counters, DBT_C_THR2_PAIRS, t_items);
+			counter_add(sv.counters, DBT_C_THR1_FIXED, TC.fix); counter_add(sv.counters, DBT_C_THR_EC, TC.ec);
+		}
 	}
 }
 

@@ -128,6 +128,8 @@ struct dbt_ctx {
 	// owned device memory of the index
 	uint4* d_gslots = nullptr; uint64_t gtable_bytes = 0, gnodes = 0;   // graph table (restored threading)
 	uint4* d_tslots = nullptr; Table ttable{}; bool bubbles = false;    // TR edge table (`-bu`)
+	uint32_t gmerge_err = 0;             // why the merge was refused: 1 node not an index key, 2 key of another locus, 4 not in the shared list, 8/16 TR k-mer without its count position
+	uint32_t* d_vv_g = nullptr;                                          // graph entries of multi-locus k-mers (graphs merged into the index)
 	uint4* d_slots = nullptr; uint32_t* d_vv = nullptr; uint32_t* d_vv_aux = nullptr;
 	// results: ONE allocation [counts nk_tr | kmc nloci | totals DBT_N_COUNTERS] u64 + [nmapread nloci] u32, so that the
 	// end-of-run exchange is one grouped collective (a u64 part and a u32 part); d_red = the same layout, filled by dbt_allreduce
@@ -265,7 +267,7 @@ extern "C" void dbt_destroy(dbt_ctx* c) {
 	cudaSetDevice(c->p.device);
 	for (auto& s : c->slot) free_slot(s);
 	if (c->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
-	cudaFree(c->d_gslots); cudaFree(c->d_tslots);
+	cudaFree(c->d_gslots); cudaFree(c->d_tslots); cudaFree(c->d_vv_g);
 	cudaFree(c->d_slots); cudaFree(c->d_vv); cudaFree(c->d_vv_aux); cudaFree(c->d_results); cudaFree(c->d_red);
 	cudaFree(c->d_qc); cudaFree(c->d_permtab); cudaFree(c->d_vote_pool); cudaFree(c->d_vote_lock);
 	if (c->h_totals) cudaFreeHost(c->h_totals);
@@ -420,6 +422,50 @@ static int load_edges(dbt_ctx* c, const dbt_index* in) {
 	return DBT_OK;
 }
 
+// Graph entries into the index entries (kernels.cu, graph_merge_kernel): when every graph node is an index key of its locus and
+// every TR k-mer keeps its count position there -- true for RPGGs whose graph, TR and flank k-mers come from the same haplotype
+// sequences, as fa2kmers writes them -- candidate_fast_kernel reads the graph entry of every k-mer of a pair out of the index
+// buckets it has probed anyway and threads the pair itself; thread_fast_kernel then only sees what the generic kernel hands on.
+// Otherwise (or with DBT_NO_GRAPH_MERGE set: the test hook for the two-table path) nothing changes.
+static int merge_graph(dbt_ctx* c, const dbt_index* in, uint64_t ntr) {
+	const uint64_t nloci = in->nloci;
+	if (getenv("DBT_NO_GRAPH_MERGE") || nloci >= (1ull << (VAL_LOCUS_BITS - 1)) || c->rp.nk_max > 255) return DBT_OK;
+	uint64_t ng = 0;
+	for (uint64_t l = 0; l < nloci; ++l) ng += in->g_n[l];
+	cudaStream_t st; CU(cudaStreamCreate(&st));
+	TRY(dev_alloc(&c->d_vv_g, in->nvv + 1, "vv_g"));
+	CU(cudaMemsetAsync(c->d_vv_g, 0, (in->nvv + 1) * 4, st));
+	uint32_t* d_err; TRY(dev_alloc(&d_err, 1, "err")); CU(cudaMemsetAsync(d_err, 0, 4, st));
+	std::vector<uint32_t> loc(std::max<uint64_t>(ng, ntr));
+	uint64_t* dk; uint8_t* dm; uint32_t* dl;
+	TRY(dev_alloc(&dk, std::max<uint64_t>(ng, ntr), "graph kmers")); TRY(dev_alloc(&dm, ng, "graph masks")); TRY(dev_alloc(&dl, std::max<uint64_t>(ng, ntr), "graph loci"));
+	uint64_t j = 0;
+	for (uint64_t l = 0; l < nloci; ++l) for (uint64_t i = 0; i < in->g_n[l]; ++i) loc[j++] = (uint32_t)l;
+	if (ng) {
+		CU(cudaMemcpyAsync(dk, in->g_kmers, ng * 8, cudaMemcpyHostToDevice, st));
+		CU(cudaMemcpyAsync(dm, in->g_masks, ng, cudaMemcpyHostToDevice, st));
+		CU(cudaMemcpyAsync(dl, loc.data(), ng * 4, cudaMemcpyHostToDevice, st));
+		CU(launch_graph_merge(st, c->B, c->ix.table, c->d_vv, c->d_vv_g, dk, dm, dl, ng, c->p.k, d_err)); ++c->launches;
+		CU(cudaStreamSynchronize(st));
+	}
+	if (ntr) {
+		j = 0;
+		for (uint64_t l = 0; l < nloci; ++l) for (uint64_t i = 0; i < in->tr_n[l]; ++i) loc[j++] = (uint32_t)l;
+		CU(cudaMemcpyAsync(dk, in->tr_kmers, ntr * 8, cudaMemcpyHostToDevice, st));
+		CU(cudaMemcpyAsync(dl, loc.data(), ntr * 4, cudaMemcpyHostToDevice, st));
+		CU(launch_tr_class_check(st, c->B, c->ix.table, c->d_vv, c->d_vv_aux, dk, dl, ntr, d_err)); ++c->launches;
+		CU(cudaStreamSynchronize(st));
+	}
+	uint32_t herr = 0;
+	CU(cudaMemcpy(&herr, d_err, 4, cudaMemcpyDeviceToHost));
+	cudaFree(dk); cudaFree(dm); cudaFree(dl); cudaFree(d_err);
+	CU(cudaStreamDestroy(st));
+	c->ix.vv_g = c->d_vv_g;
+	c->ix.gmerged = herr ? 0u : 1u;       // (bits already OR-ed into value words are masked off by every reader: slot_val)
+	c->gmerge_err = herr;
+	return DBT_OK;
+}
+
 extern "C" int dbt_load_index(dbt_ctx* c, const dbt_index* in) {
 	if (!c || !in) return fail(DBT_E_BADARG, "null argument");
 	if (c->index_loaded) return fail(DBT_E_STATE, "index already loaded");
@@ -532,7 +578,8 @@ extern "C" int dbt_load_index(dbt_ctx* c, const dbt_index* in) {
 	c->ix.permtab = c->d_permtab; c->ix.vote_pool = c->d_vote_pool; c->ix.vote_lock = c->d_vote_lock; c->ix.vote_epoch = c->d_vote_lock + VOTE_POOL;
 	c->ix.nloci = nloci; c->ix.nk_tr = ntr;
 	c->ix.gtable = Table{nullptr, 0, 0};
-	if ((c->p.flags & DBT_F_THREADING) && in->g_n && in->g_kmers && in->g_masks) TRY(load_graph(c, in, ntr));
+	c->ix.vv_g = nullptr; c->ix.gmerged = 0;
+	if ((c->p.flags & DBT_F_THREADING) && in->g_n && in->g_kmers && in->g_masks) { TRY(load_graph(c, in, ntr)); TRY(merge_graph(c, in, ntr)); }
 	if (c->p.flags & DBT_F_BUBBLES) {
 		if (c->rp.thr_on) return fail(DBT_E_BADARG, "DBT_F_BUBBLES with graph threading: the reference counts bubbles only without threading (cpp:2110, 2160)");
 		if (!in->tre_n || (!in->tre_kmers && nloci)) return fail(DBT_E_BADARG, "DBT_F_BUBBLES needs tre_n / tre_kmers (PREF.tre.kdb)");
@@ -549,6 +596,7 @@ extern "C" uint32_t dbt_record_as_stride(const dbt_ctx* c) { return c ? c->rp.as
 extern "C" uint32_t dbt_record_aln_stride(const dbt_ctx* c) { return c ? c->rp.aln_stride : 0; }
 extern "C" uint32_t dbt_record_es_cap(const dbt_ctx* c) { return c ? c->rp.es_cap : 0; }
 extern "C" uint64_t dbt_graph_table_bytes(const dbt_ctx* c) { return c ? c->gtable_bytes : 0; }
+extern "C" int dbt_graph_merged(const dbt_ctx* c) { return !c ? 0 : (c->ix.gmerged ? 1 : -(int)c->gmerge_err); }
 extern "C" uint64_t dbt_launch_count(const dbt_ctx* c) { return c ? c->launches.load() : 0; }
 
 // ------------------------------------------------------------------------------------------

@@ -346,15 +346,63 @@ __global__ void fill_aux_kernel(Table t, const uint32_t* __restrict__ vv, uint32
 	if (!(val & 1)) {
 		if ((val >> 1) != loc) { atomicOr(err, ERR_INDEX_MISSING); return; }
 		if (cls == 2 && (w[3] >> AUX_CLASS_SHIFT) == 2) atomicOr(err, ERR_INDEX_DUPTR);
-		w[3] = word;
+		w[3] = (cls == 1 && (w[3] >> AUX_CLASS_SHIFT) == 2 && (w[3] & AUX_IDX_MASK) < AUX_FLANK_TR) ? (word | AUX_FLANK_TR | (w[3] & AUX_IDX_MASK)) : word;
 	} else {
 		uint32_t off = val >> 1, cnt = vv[off];
 		for (uint32_t j = 1; j <= cnt; ++j) if (vv[off + j] == loc) {
 			if (cls == 2 && (vv_aux[off + j] >> AUX_CLASS_SHIFT) == 2) atomicOr(err, ERR_INDEX_DUPTR);
-			vv_aux[off + j] = word; return;
+			const uint32_t old = vv_aux[off + j];
+			vv_aux[off + j] = (cls == 1 && (old >> AUX_CLASS_SHIFT) == 2 && (old & AUX_IDX_MASK) < AUX_FLANK_TR) ? (word | AUX_FLANK_TR | (old & AUX_IDX_MASK)) : word; return;
 		}
 		atomicOr(err, ERR_INDEX_MISSING);
 	}
+}
+
+// Merge of the de Bruijn graphs into the index (load time).  One thread per graph node (strand-specific k-mer, locus, mask):
+// its five bits (present | mask << 1) go into the index entry of (canonical k-mer, locus) -- the top bits of the value word
+// for a k-mer unique to the locus, vv_g for a k-mer listed in several loci -- in the half that belongs to its orientation.
+// A node that is not an index key of its locus raises ERR_INDEX_MISSING: the caller then leaves the merge switched off.
+template <int B>
+__global__ void graph_merge_kernel(Table t, const uint32_t* __restrict__ vv, uint32_t* __restrict__ vv_g, const uint64_t* __restrict__ kmers,
+                                   const uint8_t* __restrict__ masks, const uint32_t* __restrict__ locus_of, uint64_t n, uint32_t k, uint32_t* err) {
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const uint64_t fw = kmers[i]; const uint32_t loc = locus_of[i];
+	const uint64_t rc = rev2(~fw) >> (64 - 2 * k);
+	const bool is_rc = rc < fw;
+	const uint64_t canon = is_rc ? rc : fw;
+	uint32_t g = 1u | ((uint32_t)(masks[i] & 0xFu) << 1);
+	g = (rc == fw) ? (g | (g << 5)) : (is_rc ? g << 5 : g);                   // palindrome (even k): both orientations are this node
+	uint4* s = table_find_slot<B>(t, canon);
+	if (!s) { atomicOr(err, 1u); return; }                                 // node is no index key at all
+	uint32_t* w = reinterpret_cast<uint32_t*>(s);
+	const uint32_t z = w[2];
+	if (!(z & 1u)) {
+		if (((z & VAL_LOCUS_MASK) >> 1) != loc) { atomicOr(err, 2u); return; }  // ... is a key of another locus only
+		atomicOr(w + 2, g << VAL_LOCUS_BITS);
+	} else {
+		const uint32_t off = z >> 1, cnt = vv[off];
+		for (uint32_t j = 1; j <= cnt; ++j) if (vv[off + j] == loc) { atomicOr(vv_g + off + j, g); return; }
+		atomicOr(err, 4u);                                                    // ... is shared by other loci, not this one
+	}
+}
+
+// ... and every TR k-mer must still carry its count-array position in the index entry of its locus (a k-mer that is also a flank
+// k-mer of the locus is classed flank there, cpp:1467-1468, and has lost it)
+template <int B>
+__global__ void tr_class_check_kernel(Table t, const uint32_t* __restrict__ vv, const uint32_t* __restrict__ vv_aux, const uint64_t* __restrict__ kmers,
+                                      const uint32_t* __restrict__ locus_of, uint64_t n, uint32_t* err) {
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const uint32_t loc = locus_of[i];
+	const uint4* s = table_find_slot<B>(t, kmers[i]);
+	if (!s) { atomicOr(err, 8u); return; }
+	const uint32_t* w = reinterpret_cast<const uint32_t*>(s);
+	const uint32_t z = w[2];
+	uint32_t word = 0;
+	if (!(z & 1u)) word = (((z & VAL_LOCUS_MASK) >> 1) == loc) ? w[3] : 0u;
+	else { const uint32_t off = z >> 1, cnt = vv[off]; for (uint32_t j = 1; j <= cnt; ++j) if (vv[off + j] == loc) word = vv_aux[off + j]; }
+	if (word != ((2u << AUX_CLASS_SHIFT) | (uint32_t)i) && word != ((1u << AUX_CLASS_SHIFT) | AUX_FLANK_TR | (uint32_t)i)) atomicOr(err, 16u);   // a TR k-mer classed flank (or missing): its count position is not in the entry
 }
 
 // table occupancy statistics: [0] used slots, [1] main buckets with the overflow flag, [2] keys in the stash,
@@ -515,6 +563,19 @@ cudaError_t launch_fill_aux(cudaStream_t st, int B, Table t, const uint32_t* vv,
                             const uint32_t* locus_of, uint64_t n, uint32_t cls, uint32_t* err) {
 	if (!n) return cudaSuccess;
 	DISPATCH_B(B, fill_aux_kernel<BB><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(t, vv, vv_aux, kmers, locus_of, n, cls, err));
+	return cudaGetLastError();
+}
+
+cudaError_t launch_graph_merge(cudaStream_t st, int B, Table t, const uint32_t* vv, uint32_t* vv_g, const uint64_t* kmers, const uint8_t* masks,
+                               const uint32_t* locus_of, uint64_t n, uint32_t k, uint32_t* err) {
+	if (!n) return cudaSuccess;
+	DISPATCH_B(B, graph_merge_kernel<BB><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(t, vv, vv_g, kmers, masks, locus_of, n, k, err));
+	return cudaGetLastError();
+}
+
+cudaError_t launch_tr_class_check(cudaStream_t st, int B, Table t, const uint32_t* vv, const uint32_t* vv_aux, const uint64_t* kmers, const uint32_t* locus_of, uint64_t n, uint32_t* err) {
+	if (!n) return cudaSuccess;
+	DISPATCH_B(B, tr_class_check_kernel<BB><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(t, vv, vv_aux, kmers, locus_of, n, err));
 	return cudaGetLastError();
 }
 

@@ -20,6 +20,10 @@ cudaError_t launch_thread(cudaStream_t st, int B, int nsm, const DevIndex& ix, c
 // pass 0/1: graph nodes (canonical / reverse-complement orientation), pass 2: TR k-mers (masks == nullptr), pass 3: verify
 cudaError_t launch_graph_build(cudaStream_t st, int B, Table t, const uint64_t* kmers, const uint8_t* masks, const uint32_t* locus_of,
                                uint64_t n, uint32_t k, int pass, uint32_t* err);
+// graphs merged into the index entries (graph_merge_kernel) + the check that every TR k-mer keeps its count position there
+cudaError_t launch_graph_merge(cudaStream_t st, int B, Table t, const uint32_t* vv, uint32_t* vv_g, const uint64_t* kmers, const uint8_t* masks,
+                               const uint32_t* locus_of, uint64_t n, uint32_t k, uint32_t* err);
+cudaError_t launch_tr_class_check(cudaStream_t st, int B, Table t, const uint32_t* vv, const uint32_t* vv_aux, const uint64_t* kmers, const uint32_t* locus_of, uint64_t n, uint32_t* err);
 cudaError_t launch_table_stats(cudaStream_t st, int B, Table t, unsigned long long* out);
 cudaError_t launch_random_gather(cudaStream_t st, int nsm, const uint4* table, uint64_t table_bytes, uint32_t sector_bytes,
                                  uint64_t ngathers, uint64_t seed, uint32_t* sink);

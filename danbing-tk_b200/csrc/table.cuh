@@ -34,6 +34,8 @@ constexpr uint64_t SLOT_OVF   = 0x8000000000000000ull;
 constexpr uint64_t SLOT_KEYMASK = ~SLOT_OVF;
 constexpr uint32_t AUX_CLASS_SHIFT = 30;
 constexpr uint32_t AUX_IDX_MASK = (1u << AUX_CLASS_SHIFT) - 1;
+constexpr uint32_t AUX_FLANK_TR = 1u << 29;               // class 1 (flank wins, cpp:1467-1468) entry of a k-mer that is ALSO a TR k-mer of the locus:
+                                                          // bits 0-28 keep its count-array position (graph threading counts by trResults membership alone)
 constexpr uint32_t AUX_MISS = 3u << AUX_CLASS_SHIFT;      // per-position marker: k-mer not in the index
 
 struct Table {
@@ -81,6 +83,13 @@ __device__ __forceinline__ void cp_async_wait_all() {
 }
 
 // Looks key up. Returns true on hit and sets val/aux. key must be < 2^63 and != invalid.
+// Index value word (slot .z): even = locus << 1 for a k-mer unique to one locus, odd = (offset into vv) << 1 | 1.  When the de Bruijn
+// graphs are merged into the index (dbt_load_index, graph_merge_kernel) the top ten bits of an EVEN value carry the graph entry of
+// (k-mer, that locus): present + out-edge mask of the canonical orientation (bits 22-26) and of its reverse complement (27-31).
+constexpr uint32_t VAL_LOCUS_BITS = 22;
+constexpr uint32_t VAL_LOCUS_MASK = (1u << VAL_LOCUS_BITS) - 1;
+__host__ __device__ __forceinline__ uint32_t slot_val(uint32_t z) { return (z & 1u) ? z : (z & VAL_LOCUS_MASK); }
+
 template <int B>
 __device__ __forceinline__ bool table_lookup(const Table& t, uint64_t key, uint32_t& val, uint32_t& aux) {
 	uint64_t b = home_bucket(t, key);
@@ -95,7 +104,7 @@ __device__ __forceinline__ bool table_lookup(const Table& t, uint64_t key, uint3
 		for (int i = 0; i < B; ++i) {
 			uint64_t k = slot_key(s[i]);
 			if (k == SLOT_EMPTY) full = false;
-			else if ((k & SLOT_KEYMASK) == key) { val = s[i].z; aux = s[i].w; return true; }
+			else if ((k & SLOT_KEYMASK) == key) { val = slot_val(s[i].z); aux = s[i].w; return true; }
 		}
 		if (!full || !(slot_key(s[0]) & SLOT_OVF)) return false;
 		b = home ? stash_bucket(t, key) : stash_next(t, b);

@@ -60,6 +60,291 @@ __device__ __noinline__ GNode g_lookup_canon_nl(const Table gt, uint64_t canon, 
 template <int B>
 __device__ __noinline__ GNode g_lookup_fast_nl(const Table gt, uint64_t fw, uint32_t locus, uint32_t k) { return g_lookup<B>(gt, fw, locus, k); }
 
+// What is left of a mate once every position has its graph entry (W.key / W.nb / W.trx): is it on a path of the graph, can the
+// stops be settled here, and if so the counts and its half of the aln record.  Shared by thread_fast_kernel (which probes the graph
+// table for the entries) and candidate_fast_kernel (whose index entries carry the graph bits when the graph is merged into the index,
+// dbt_load_index).  Returns false when the mate has to go to thread_kernel.
+struct ThrfArrays { uint64_t* key; uint32_t* trx; uint16_t* nb; uint32_t* T; uint32_t* ok; uint32_t* P; };
+struct ThrfCount { uint32_t inc = 0, cls = 0, probe = 0, fix = 0, ec = 0; };
+
+template <int B, int MAXJ>
+__device__ __forceinline__ bool thrf_finish_mate(const DevIndex& ix, const RunParams& rp, const SlotView& sv, const ThrfArrays W, int m, uint32_t len, int nkm, uint32_t dst,
+                                                 uint8_t* rec, bool slot_ok, bool trace, int lane, ThrfCount& C) {
+	const uint32_t K = rp.k;
+	const Table gt = ix.gtable;
+	const uint64_t kmask = (1ull << (2 * K)) - 1;
+	const bool correction1 = rp.correction != 0 && rp.max_ncorrection >= 1;
+	const int ng = (nkm + 31) >> 5;
+	(void)sv;
+		__syncwarp();
+		// ---- B2: every k-mer on an out-edge of its predecessor, the first one a node? ----
+		bool clean = true;
+#pragma unroll 1
+		for (int j = 0; j < ng; ++j) {
+			const int i = j * 32 + lane;
+			bool ok = true, tr = false;
+			if (i < nkm) {
+				const uint32_t f3 = (uint32_t)(W.key[i] >> THRF_F3_SHIFT) & 3u;
+				const uint32_t pb = W.nb[i];                                 // node of position i-1 (i == 0: unused)
+				ok = i == 0 ? (W.nb[1] & 1u) != 0 : ((pb & 1u) && ((pb >> (1 + f3)) & 1u));
+				tr = W.trx[i] != 0;
+			}
+			const uint32_t bo = __ballot_sync(0xffffffffu, ok);
+			if (bo != 0xffffffffu) clean = false;
+			const uint32_t bt = __ballot_sync(0xffffffffu, tr);
+			const uint32_t bp = __ballot_sync(0xffffffffu, i < nkm && (W.nb[i + 1] & 1u));
+			if (lane == 0) { W.T[j] = bt; W.ok[j] = bo; W.P[j] = bp; }
+		}
+		__syncwarp();
+		int es_beg = 0, tr_beg = 0;                                       // ... and skipped k-mers before the anchor leave the entries before it '*'
+		int es_end = (int)len, tr_end = nkm;                              // a walk that ends early (cpp:1182-1185) leaves the entries from here on '*'
+		uint64_t xlist = 0; int nfix = 0;                                 // corrected mate: 'X' entries of the CIGAR, 16 bits each: position | graph base (1-4) << 13
+		if (!clean && correction1) {
+			// ---- substitutions in the interior of the read, graph without a branch there ----
+			// The walk (cpp:1167-1180) stops at the first k-mer ki that is not on an out-edge of its predecessor.  If that
+			// predecessor has ONE out-edge a, the k-mer with its last base replaced by a is a node whose one out-edge is the
+			// next read base, and the k following k-mers with that base replaced (the last of them is the read's own k-mer
+			// ki+k) form a path, then errorCorrection_forward (cpp:898-1089) scores the 1-mismatch edit `a` with the full
+			// extension k: no other edit can score more (every family's walk is at most k steps long here) and this one comes
+			// first in thread_ext_t::get_edit's scan (cpp:628-647).  edit_kmers_forward (cpp:828-862) rewrites exactly those
+			// k k-mers and one CIGAR entry, and the walk resumes behind them: the next stop, if any, is handled the same way
+			// while corrections (cpp:1186) and skips (cpp:1194) are left.  If every other k-mer is on an out-edge of its
+			// predecessor the read threads with nfix corrections (isThreadFeasible returns 2).  Anything else -- an error
+			// near an end, an indel, a branch, a missing node -- is thread_kernel's, which starts over from the packed read.
+			const uint32_t maxskip = (uint32_t)nkm > rp.thread_cth ? (uint32_t)nkm - rp.thread_cth : 0u;
+			int from = 0; bool fail = false;
+			int nskip = 0;                                                    // k-mers skipped so far (cpp:1123); every correction adds its edit (cpp:1193)
+			// Start of the read.  The walk begins at the first k-mer `an` that is a node (find_anchor, cpp:878-888); the an k-mers
+			// before it are skipped, and when there are at least 6 of them errorCorrection_backward (cpp:1091-1106: the same
+			// scorer on the reverse complements, from the anchor towards the start) is tried once (cpp:1131-1141).  A wrong base
+			// in the first k bases makes exactly the k-mers that hold it non-nodes: an <= k, the mirror image of a stop with
+			// an k-mers left -- one 1-mismatch walk of an-1 steps on the reverse strand, the deletion families out of play under
+			// the same conditions -- and edit_kmers_backward (cpp:649-826) then rewrites k-mers 0..an-1, marks CIGAR entry an-1
+			// 'X' with the complement of the edge taken and the entries before it '=' (its merge rules see a tract of one entry).
+			{
+				int an = nkm;
+#pragma unroll 1
+				for (int j = ng - 1; j >= 0; --j) { const uint32_t z = W.P[j]; if (z) an = j * 32 + __ffs(z) - 1; }
+				if (an >= nkm) fail = true;                                   // no node at all: the read does not thread (cpp:1129)
+				else if (an > 0) {
+					if (an >= (int)THR_MSC + 1) {
+						const uint32_t nbw = W.nb[an + 1];
+						const uint32_t rm = (nbw >> 6) & 0xFu;                     // out-edges of the anchor's reverse complement
+						if (an > (int)K || !(nbw & GN_RCPRESENT) || __popc(rm) != 1 || rp.max_ncorrection < 1) fail = true;
+						else {
+							const uint32_t tb = 3u - ((uint32_t)__ffs(rm) - 1u);      // the base the graph has where the read is wrong (forward strand)
+							const int t = lane;                                       // lane t < an: k-mer an-1-t, wrong base = its base number t
+							uint64_t c = 0; uint32_t bits = 0, trp = 0, fb = 0;
+							if (t < an) {
+								const uint64_t kw = W.key[an - 1 - t];
+								const uint64_t cn = kw & kmask;
+								const uint64_t fw = (kw & THRF_RCFLAG) ? kmer_rc(cn, K) : cn;
+								const uint32_t shf = 2 * (K - 1 - (uint32_t)t);
+								c = (fw & ~(3ull << shf)) | ((uint64_t)tb << shf);
+								const GNode g = g_lookup_fast_nl<B>(gt, c, dst, K);
+								bits = g.bits; trp = g.tr;
+								++C.probe;
+								fb = (uint32_t)(c >> (2 * (K - 1))) & 3u;               // first base of the rewritten k-mer
+							}
+							const uint32_t fbn = __shfl_down_sync(0xffffffffu, fb, 1);  // first base of k-mer an-2-t: the next step of the reverse-strand walk appends its complement
+							bool good = true;
+							if (t + 1 < an) {
+								const uint32_t mk = gn_rcmask(bits);
+								good = (bits & GN_RCPRESENT) && ((mk >> (3u - fbn)) & 1u) && (t != 0 || __popc(mk) == 1);
+							}
+							{
+								const uint64_t kw = W.key[an - 1];
+								const uint64_t fw0 = (kw & THRF_RCFLAG) ? kmer_rc(kw & kmask, K) : (kw & kmask);
+								const uint32_t oldnt = 3u - ((uint32_t)(fw0 >> (2 * (K - 1))) & 3u);   // the wrong base as the reverse-strand walk reads it
+								const uint32_t m0 = __shfl_sync(0xffffffffu, gn_rcmask(bits), 0), m1 = __shfl_sync(0xffffffffu, gn_rcmask(bits), 1);
+								if (((m0 >> oldnt) & 1u) || (an >= 2 * (int)THR_MSC + 2 && ((m1 >> oldnt) & 1u))) good = false;
+							}
+							if (!__all_sync(0xffffffffu, good)) fail = true;
+							else {
+								__syncwarp();
+								if (t < an) {
+									const uint64_t rc = kmer_rc(c, K);
+									const bool is_rc = rc < c;
+									W.key[an - 1 - t] = (is_rc ? rc : c) | ((c & 3) << THRF_F3_SHIFT) | (is_rc ? THRF_RCFLAG : 0ull);
+									W.trx[an - 1 - t] = trp;
+								}
+								__syncwarp();
+								xlist |= (uint64_t)((uint32_t)(an - 1) | ((tb + 1) << 13)) << (16 * nfix);
+								++nfix; nskip = 1;                                      // cpp:690-694: the skipped k-mers are taken back, the edit stays
+								if (lane == 0) C.ec += (uint32_t)an + 1;
+							}
+						}
+					} else { nskip = an; es_beg = an; tr_beg = an; }            // too few k-mers to correct (cpp:1131): they stay skipped
+					from = an + 1;
+				}
+			}
+			// Stops near the end of the read.  With nrem = nkm - ki k-mers left: nrem <= 5 ends the walk (cpp:1182-1185: the rest is
+			// skipped, no correction); nrem = k+1 is the interior case (every family's walk is still at most k steps); 6 <= nrem <= k:
+			// the 1-mismatch walk is nrem-1 steps long and only the two deletion families walk one step further (jb = 0, cpp:961,
+			// 1040) -- they are not tried at all unless the wrong base is an out-edge of the corrected k-mer (1 deletion, cpp:957)
+			// or of its successor (2 deletions, cpp:1036, needs >= 12 k-mers left), and then the pair is left to thread_kernel.
+#pragma unroll 1
+			for (; !fail;) {
+				int ki = nkm;
+#pragma unroll 1
+				for (int j = ng - 1; j >= (from >> 5); --j) {
+					uint32_t z = ~W.ok[j];
+					if (j == (from >> 5)) z &= 0xFFFFFFFFu << (from & 31);
+					if (z) ki = j * 32 + __ffs(z) - 1;
+				}
+				if (ki >= nkm) break;                                         // nothing stops the walk any more
+				const int nrem = nkm - ki;
+				if (ki >= 1 && nrem <= (int)THR_MSC) {                           // cpp:1182-1185
+					nskip += nrem;
+					es_end = ki + (int)K - 1; tr_end = ki;
+					break;
+				}
+				if (nfix >= 4 || (uint32_t)nfix >= rp.max_ncorrection || (uint32_t)nskip + 1 > maxskip || ki < 1) { fail = true; break; }
+				const int nrw = min(nrem, (int)K);                            // k-mers the edit rewrites: ki .. ki+nrw-1
+				const uint32_t pm = (uint32_t)(W.nb[ki] >> 1) & 0xFu;        // out-edges of k-mer ki-1 (never a rewritten one: ki-1 >= from-1)
+				if (__popc(pm) != 1) { fail = true; break; }
+				const uint32_t a = (uint32_t)__ffs(pm) - 1u;
+				const int t = lane;                                           // lane t < k: k-mer ki+t with the wrong base (2t bits up) replaced
+				uint64_t c = 0; uint32_t bits = 0, trp = 0, f3n = 0;
+				if (t < nrw) {
+					const uint64_t kw = W.key[ki + t];
+					const uint64_t cn = kw & kmask;
+					const uint64_t fw = (kw & THRF_RCFLAG) ? kmer_rc(cn, K) : cn;
+					c = (fw & ~(3ull << (2 * t))) | ((uint64_t)a << (2 * t));
+					const GNode g = g_lookup_fast_nl<B>(gt, c, dst, K);
+					bits = g.bits; trp = g.tr;
+					++C.probe;
+					if (ki + t + 1 < nkm) f3n = (uint32_t)(W.key[ki + t + 1] >> THRF_F3_SHIFT) & 3u;   // last base of the next k-mer
+				}
+				// lane t (< k): present, and the next k-mer's last base is an out-edge (lane 0: its ONLY out-edge, the level-2
+				// expansion of the scorer then holds just that base, cpp:907-920)
+				bool good = true;
+				if (t < nrw && ki + t + 1 < nkm) {                             // (the last k-mer of the read is only visited, cpp:553)
+					const uint32_t mk = gn_mask(bits);
+					good = (bits & GN_PRESENT) && ((mk >> f3n) & 1u) && (t != 0 || __popc(mk) == 1);
+				}
+				if (nrem <= (int)K) {                                         // deletion families must not be in play (see above)
+					const uint32_t oldnt = (uint32_t)(W.key[ki] >> THRF_F3_SHIFT) & 3u;
+					const uint32_t m0 = __shfl_sync(0xffffffffu, gn_mask(bits), 0), m1 = __shfl_sync(0xffffffffu, gn_mask(bits), 1);
+					if (((m0 >> oldnt) & 1u) || (nrem >= 2 * (int)THR_MSC + 2 && ((m1 >> oldnt) & 1u))) good = false;
+				}
+				const bool allgood = __all_sync(0xffffffffu, good);
+				if (!allgood) { fail = true; break; }
+				__syncwarp();
+				if (t < nrw) {
+					const uint64_t rc = kmer_rc(c, K);
+					const bool is_rc = rc < c;
+					W.key[ki + t] = (is_rc ? rc : c) | ((c & 3) << THRF_F3_SHIFT) | (is_rc ? THRF_RCFLAG : 0ull);
+					W.trx[ki + t] = trp;
+				}
+				__syncwarp();
+				xlist |= (uint64_t)((uint32_t)(ki + (int)K - 1) | ((a + 1) << 13)) << (16 * nfix);
+				++nfix; ++nskip;
+				from = ki + (int)K + 1;                                       // the walk resumes here (cpp:1197: ki += score - 1, then the loop's ++ki)
+				if (lane == 0) C.ec += K + 2;                                 // look-ups of the scorer's winning path: 1 + 1 expansion nodes + k walk steps
+			}
+			if ((uint32_t)nskip > maxskip) fail = true;                       // cpp:1259: the read does not thread; thread_kernel reports it
+			if (!fail && (nfix || tr_end < nkm || tr_beg > 0)) {
+#pragma unroll 1
+				for (int j = 0; j < ng; ++j) {                                 // TR ballots again: the rewritten k-mers have their own
+					const int i = j * 32 + lane;
+					const uint32_t bt = __ballot_sync(0xffffffffu, i < nkm && W.trx[i] != 0);
+					if (lane == 0) W.T[j] = bt;
+				}
+				__syncwarp();
+				clean = true;
+				if (lane == 0) ++C.fix;
+			}
+		}
+		if (!clean) return false;
+
+		// ---- clean mate: alned = 1, es all '=', tr from the TR ballots; count its TR k-mers (D1) ----
+		{
+			uint32_t inc_sum = 0;
+#pragma unroll 1
+			for (int j = 0; j < ng; ++j) {
+				const int i = j * 32 + lane;
+				const uint32_t tx = i < nkm ? W.trx[i] : 0u;
+				const uint32_t tm = W.T[j];
+				if (!tm) continue;
+				inc_sum += __popc(tm);
+				if (tx) {
+					const uint32_t peers = __match_any_sync(tm, tx);
+					if ((uint32_t)lane == (uint32_t)(__ffs(peers) - 1))
+						atomicAdd(reinterpret_cast<unsigned long long*>(ix.counts + (tx - 1)), (unsigned long long)__popc(peers));
+				}
+			}
+			if (lane == 0) { C.inc += inc_sum; C.cls += (uint32_t)nkm; }
+		}
+		if (slot_ok) {                                                   // sam_t.r1 / r2 -> dbt_aln_mate blob
+			uint8_t* b = rec + sizeof(dbt_pair_record) + (size_t)m * rp.aln_stride;
+			uint8_t* es = b + sizeof(dbt_aln_mate); uint8_t* trb = es + rp.es_cap;
+			const int nes = min((int)len, (int)rp.es_cap), ntr = min(nkm, (int)rp.tr_cap);
+#pragma unroll 1
+			for (int q = lane; q < (int)rp.es_cap / 4; q += 32) {         // four entries per lane and store; entries >= nes read 0
+				const int nbb = min(nes, es_end) - 4 * q, nlo = es_beg - 4 * q;
+				const uint32_t keep = (nbb >= 4 ? 0xFFFFFFFFu : (nbb <= 0 ? 0u : (1u << 8 * nbb) - 1u)) & (nlo <= 0 ? 0xFFFFFFFFu : (nlo >= 4 ? 0u : 0xFFFFFFFFu << 8 * nlo));
+				uint32_t v = 0x01010101u * ET_EQ;
+#pragma unroll 1
+				for (int f = 0; f < nfix; ++f) {
+					const uint32_t e = (uint32_t)(xlist >> (16 * f)) & 0xFFFFu, xp = e & 0x1FFFu, xb = e >> 13;
+					if ((int)(xp >> 2) == q) v = (v & ~(0xFFu << (8 * (xp & 3)))) | ((uint32_t)(ET_X | (xb << 3)) << (8 * (xp & 3)));
+				}
+				reinterpret_cast<uint32_t*>(es)[q] = v & keep;
+			}
+#pragma unroll 1
+			for (int q = lane; q < (int)rp.tr_cap / 4; q += 32) {         // tr[i] = '=' (2) for TR k-mers, '.' (1) otherwise: 4 TR ballot bits -> 4 bytes
+				const int nbb = min(ntr, tr_end) - 4 * q, nlo = tr_beg - 4 * q;
+				const uint32_t keep = (nbb >= 4 ? 0xFFFFFFFFu : (nbb <= 0 ? 0u : (1u << 8 * nbb) - 1u)) & (nlo <= 0 ? 0xFFFFFFFFu : (nlo >= 4 ? 0u : 0xFFFFFFFFu << 8 * nlo));
+				const uint32_t bits = 4 * q < ng * 32 ? (W.T[(4 * q) >> 5] >> ((4 * q) & 31)) & 0xFu : 0u;
+				const uint32_t v = 0x01010101u + ((bits & 1u) | ((bits & 2u) << 7) | ((bits & 4u) << 14) | ((bits & 8u) << 21));
+				reinterpret_cast<uint32_t*>(trb)[q] = v & keep;
+			}
+			if (lane == 0) {
+				dbt_aln_mate* h = reinterpret_cast<dbt_aln_mate*>(b);
+				h->alned = nfix ? 2 : 1; h->err = (uint8_t)((int)len > (int)rp.es_cap || nkm > (int)rp.tr_cap);   // cpp:1259 / 1184
+				h->nes = (uint16_t)len; h->ntr = (uint16_t)nkm; h->nkm = (uint16_t)nkm;
+				uint64_t hash = 0;
+				if (trace) {                                                // FNV-1a over the k-mer vector (parity tests only)
+					hash = 0xcbf29ce484222325ull;
+#pragma unroll 1
+					for (int i = 0; i < nkm; ++i) {
+						const uint64_t kw = W.key[i];
+						const uint64_t v = (kw & THRF_RCFLAG) ? kmer_rc(kw & kmask, K) : (kw & kmask);
+						for (int q = 0; q < 8; ++q) { hash ^= (v >> (8 * q)) & 0xFF; hash *= 0x100000001b3ull; }
+					}
+				}
+				h->kmers_hash = hash;
+			}
+		}
+	
+	return true;
+}
+
+// pair level: a clean (or corrected) mate makes the pair thread (commented caller, cpp:2082-2087); mates left over go to thread_kernel
+__device__ __forceinline__ void thrf_finish_pair(const RunParams& rp, const SlotView& sv, uint32_t c, uint32_t p, uint32_t dw, uint32_t dst, uint32_t dirty,
+                                                 uint8_t* rec, bool slot_ok, bool want_rec, bool trace, int lane, uint32_t& c_fea, uint32_t& c_items) {
+	if (dirty != 3u) {
+		if (lane == 0) c_fea += 2;
+		if (want_rec && !slot_ok) { if (lane == 0) atomicOr(sv.ncand + 1, ERR_RECORD_OVERFLOW); }
+		else if (slot_ok && lane == 0) {
+			dbt_pair_record* h = reinterpret_cast<dbt_pair_record*>(rec);
+			if (!trace) {                                                   // under DBT_F_TRACE the generic candidate kernel left the full header
+				h->pair_index = sv.first_pair_index + p; h->dst0 = dst; h->fc = 0; h->rc = 0; h->nhash0 = 0; h->nhash1 = 0;
+				h->pad[0] = h->pad[1] = h->pad[2] = 0;
+#pragma unroll 1
+				for (int m = 0; m < 2; ++m) {
+					dbt_mate_record& o = h->mate[m];
+					o.si = o.ei = o.si_ = o.ei_ = o.ti = -1; o.nt = 0; o.bs = 0; o.pad = 0; o.nk = 0;
+					o.flags = (uint8_t)((((dw >> (28 + m)) & 1u) ? DBT_MF_KF : 0) | (((dw >> (30 + m)) & 1u) ? DBT_MF_RM : 0));
+				}
+			}
+			h->dst = dst; h->status = (uint8_t)DBT_ST_COUNTED;
+		}
+	}
+	if (dirty && lane == 0) { sv.thr2[atomicAdd(sv.ncand + 4, 1u)] = make_uint4(c, p, dw, dirty | (dirty != 3u ? THR2_ALNED : 0u)); ++c_items; }
+}
+
 template <int B, int MAXJ>
 struct FastThreadWarp {
 	uint4    stage[MAXJ][B][32];               // home (then stash) buckets of every position of the mate being probed
@@ -85,8 +370,8 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 	const uint32_t W64 = rp.lay.W64, WB = rp.lay.WB, K = rp.k;
 	const Table gt = ix.gtable;
 	const uint64_t kmask = (1ull << (2 * K)) - 1, vmask = (1ull << K) - 1;
-	uint32_t c_fea = 0, c_inc = 0, c_cls = 0, c_walk = 0, c_probe = 0, c_items = 0, c_fix = 0, c_ec = 0;   // lane-0 accumulators (c_probe: per lane, reduced at the end)
-	const bool correction1 = rp.correction != 0 && rp.max_ncorrection >= 1;
+	uint32_t c_fea = 0, c_walk = 0, c_items = 0;                         // lane-0 accumulators
+	ThrfCount C;                                                         // (C.probe: per lane, reduced at the end)
 
 	uint4 item = gwarp < nwork ? sv.thr[gwarp] : make_uint4(0, 0, 0, 0);
 #pragma unroll 1
@@ -130,7 +415,7 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 						const uint4* bp = gt.slots + home_bucket(gt, canon ^ lmix) * B;
 #pragma unroll
 						for (int q = 0; q < B; ++q) cp_async16(&W.stage[j][q][lane], bp + q);
-						++c_probe;
+						++C.probe;
 						anyvalid = true;
 						if (i + 1 < nkm && ((wv >> 2) & kmask) == x) plain = false;   // kmers[i+1] == kmers[i]: cpp:1152 is thread_kernel's
 					} else plain = false;
@@ -191,7 +476,7 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 						const uint4* bp = gt.slots + sb * B;
 #pragma unroll
 						for (int q = 0; q < B; ++q) cp_async16(&W.stage[0][q][lane], bp + q);
-						++c_probe;
+						++C.probe;
 					}
 					cp_async_wait_all();
 					if (act) {
@@ -218,275 +503,21 @@ __global__ void __launch_bounds__(THRF_WARPS * 32, THRF_MINBLOCKS) thread_fast_k
 						const uint64_t kw = W.key[i];
 						const GNode n = g_lookup_canon_nl<B>(gt, kw & kmask, (kw & THRF_RCFLAG) != 0, dst, stash_bucket(gt, (kw & kmask) ^ lmix));
 						W.nb[i + 1] = (uint16_t)(n.bits & 0x3FFu); W.trx[i] = n.tr;
-						++c_probe;
+						++C.probe;
 					}
 				}
 			}
 			__syncwarp();
-			// ---- B2: every k-mer on an out-edge of its predecessor, the first one a node? ----
-			bool clean = true;
-#pragma unroll 1
-			for (int j = 0; j < ng; ++j) {
-				const int i = j * 32 + lane;
-				bool ok = true, tr = false;
-				if (i < nkm) {
-					const uint32_t f3 = (uint32_t)(W.key[i] >> THRF_F3_SHIFT) & 3u;
-					const uint32_t pb = W.nb[i];                                 // node of position i-1 (i == 0: unused)
-					ok = i == 0 ? (W.nb[1] & 1u) != 0 : ((pb & 1u) && ((pb >> (1 + f3)) & 1u));
-					tr = W.trx[i] != 0;
-				}
-				const uint32_t bo = __ballot_sync(0xffffffffu, ok);
-				if (bo != 0xffffffffu) clean = false;
-				const uint32_t bt = __ballot_sync(0xffffffffu, tr);
-				const uint32_t bp = __ballot_sync(0xffffffffu, i < nkm && (W.nb[i + 1] & 1u));
-				if (lane == 0) { W.T[j] = bt; W.ok[j] = bo; W.P[j] = bp; }
-			}
-			__syncwarp();
-			int es_beg = 0, tr_beg = 0;                                       // ... and skipped k-mers before the anchor leave the entries before it '*'
-			int es_end = (int)len, tr_end = nkm;                              // a walk that ends early (cpp:1182-1185) leaves the entries from here on '*'
-			uint64_t xlist = 0; int nfix = 0;                                 // corrected mate: 'X' entries of the CIGAR, 16 bits each: position | graph base (1-4) << 13
-			if (!clean && correction1) {
-				// ---- substitutions in the interior of the read, graph without a branch there ----
-				// The walk (cpp:1167-1180) stops at the first k-mer ki that is not on an out-edge of its predecessor.  If that
-				// predecessor has ONE out-edge a, the k-mer with its last base replaced by a is a node whose one out-edge is the
-				// next read base, and the k following k-mers with that base replaced (the last of them is the read's own k-mer
-				// ki+k) form a path, then errorCorrection_forward (cpp:898-1089) scores the 1-mismatch edit `a` with the full
-				// extension k: no other edit can score more (every family's walk is at most k steps long here) and this one comes
-				// first in thread_ext_t::get_edit's scan (cpp:628-647).  edit_kmers_forward (cpp:828-862) rewrites exactly those
-				// k k-mers and one CIGAR entry, and the walk resumes behind them: the next stop, if any, is handled the same way
-				// while corrections (cpp:1186) and skips (cpp:1194) are left.  If every other k-mer is on an out-edge of its
-				// predecessor the read threads with nfix corrections (isThreadFeasible returns 2).  Anything else -- an error
-				// near an end, an indel, a branch, a missing node -- is thread_kernel's, which starts over from the packed read.
-				const uint32_t maxskip = (uint32_t)nkm > rp.thread_cth ? (uint32_t)nkm - rp.thread_cth : 0u;
-				int from = 0; bool fail = false;
-				int nskip = 0;                                                    // k-mers skipped so far (cpp:1123); every correction adds its edit (cpp:1193)
-				// Start of the read.  The walk begins at the first k-mer `an` that is a node (find_anchor, cpp:878-888); the an k-mers
-				// before it are skipped, and when there are at least 6 of them errorCorrection_backward (cpp:1091-1106: the same
-				// scorer on the reverse complements, from the anchor towards the start) is tried once (cpp:1131-1141).  A wrong base
-				// in the first k bases makes exactly the k-mers that hold it non-nodes: an <= k, the mirror image of a stop with
-				// an k-mers left -- one 1-mismatch walk of an-1 steps on the reverse strand, the deletion families out of play under
-				// the same conditions -- and edit_kmers_backward (cpp:649-826) then rewrites k-mers 0..an-1, marks CIGAR entry an-1
-				// 'X' with the complement of the edge taken and the entries before it '=' (its merge rules see a tract of one entry).
-				{
-					int an = nkm;
-#pragma unroll 1
-					for (int j = ng - 1; j >= 0; --j) { const uint32_t z = W.P[j]; if (z) an = j * 32 + __ffs(z) - 1; }
-					if (an >= nkm) fail = true;                                   // no node at all: the read does not thread (cpp:1129)
-					else if (an > 0) {
-						if (an >= (int)THR_MSC + 1) {
-							const uint32_t nbw = W.nb[an + 1];
-							const uint32_t rm = (nbw >> 6) & 0xFu;                     // out-edges of the anchor's reverse complement
-							if (an > (int)K || !(nbw & GN_RCPRESENT) || __popc(rm) != 1 || rp.max_ncorrection < 1) fail = true;
-							else {
-								const uint32_t tb = 3u - ((uint32_t)__ffs(rm) - 1u);      // the base the graph has where the read is wrong (forward strand)
-								const int t = lane;                                       // lane t < an: k-mer an-1-t, wrong base = its base number t
-								uint64_t c = 0; uint32_t bits = 0, trp = 0, fb = 0;
-								if (t < an) {
-									const uint64_t kw = W.key[an - 1 - t];
-									const uint64_t cn = kw & kmask;
-									const uint64_t fw = (kw & THRF_RCFLAG) ? kmer_rc(cn, K) : cn;
-									const uint32_t shf = 2 * (K - 1 - (uint32_t)t);
-									c = (fw & ~(3ull << shf)) | ((uint64_t)tb << shf);
-									const GNode g = g_lookup_fast_nl<B>(gt, c, dst, K);
-									bits = g.bits; trp = g.tr;
-									++c_probe;
-									fb = (uint32_t)(c >> (2 * (K - 1))) & 3u;               // first base of the rewritten k-mer
-								}
-								const uint32_t fbn = __shfl_down_sync(0xffffffffu, fb, 1);  // first base of k-mer an-2-t: the next step of the reverse-strand walk appends its complement
-								bool good = true;
-								if (t + 1 < an) {
-									const uint32_t mk = gn_rcmask(bits);
-									good = (bits & GN_RCPRESENT) && ((mk >> (3u - fbn)) & 1u) && (t != 0 || __popc(mk) == 1);
-								}
-								{
-									const uint64_t kw = W.key[an - 1];
-									const uint64_t fw0 = (kw & THRF_RCFLAG) ? kmer_rc(kw & kmask, K) : (kw & kmask);
-									const uint32_t oldnt = 3u - ((uint32_t)(fw0 >> (2 * (K - 1))) & 3u);   // the wrong base as the reverse-strand walk reads it
-									const uint32_t m0 = __shfl_sync(0xffffffffu, gn_rcmask(bits), 0), m1 = __shfl_sync(0xffffffffu, gn_rcmask(bits), 1);
-									if (((m0 >> oldnt) & 1u) || (an >= 2 * (int)THR_MSC + 2 && ((m1 >> oldnt) & 1u))) good = false;
-								}
-								if (!__all_sync(0xffffffffu, good)) fail = true;
-								else {
-									__syncwarp();
-									if (t < an) {
-										const uint64_t rc = kmer_rc(c, K);
-										const bool is_rc = rc < c;
-										W.key[an - 1 - t] = (is_rc ? rc : c) | ((c & 3) << THRF_F3_SHIFT) | (is_rc ? THRF_RCFLAG : 0ull);
-										W.trx[an - 1 - t] = trp;
-									}
-									__syncwarp();
-									xlist |= (uint64_t)((uint32_t)(an - 1) | ((tb + 1) << 13)) << (16 * nfix);
-									++nfix; nskip = 1;                                      // cpp:690-694: the skipped k-mers are taken back, the edit stays
-									if (lane == 0) c_ec += (uint32_t)an + 1;
-								}
-							}
-						} else { nskip = an; es_beg = an; tr_beg = an; }            // too few k-mers to correct (cpp:1131): they stay skipped
-						from = an + 1;
-					}
-				}
-				// Stops near the end of the read.  With nrem = nkm - ki k-mers left: nrem <= 5 ends the walk (cpp:1182-1185: the rest is
-				// skipped, no correction); nrem = k+1 is the interior case (every family's walk is still at most k steps); 6 <= nrem <= k:
-				// the 1-mismatch walk is nrem-1 steps long and only the two deletion families walk one step further (jb = 0, cpp:961,
-				// 1040) -- they are not tried at all unless the wrong base is an out-edge of the corrected k-mer (1 deletion, cpp:957)
-				// or of its successor (2 deletions, cpp:1036, needs >= 12 k-mers left), and then the pair is left to thread_kernel.
-#pragma unroll 1
-				for (; !fail;) {
-					int ki = nkm;
-#pragma unroll 1
-					for (int j = ng - 1; j >= (from >> 5); --j) {
-						uint32_t z = ~W.ok[j];
-						if (j == (from >> 5)) z &= 0xFFFFFFFFu << (from & 31);
-						if (z) ki = j * 32 + __ffs(z) - 1;
-					}
-					if (ki >= nkm) break;                                         // nothing stops the walk any more
-					const int nrem = nkm - ki;
-					if (ki >= 1 && nrem <= (int)THR_MSC) {                           // cpp:1182-1185
-						nskip += nrem;
-						es_end = ki + (int)K - 1; tr_end = ki;
-						break;
-					}
-					if (nfix >= 4 || (uint32_t)nfix >= rp.max_ncorrection || (uint32_t)nskip + 1 > maxskip || ki < 1) { fail = true; break; }
-					const int nrw = min(nrem, (int)K);                            // k-mers the edit rewrites: ki .. ki+nrw-1
-					const uint32_t pm = (uint32_t)(W.nb[ki] >> 1) & 0xFu;        // out-edges of k-mer ki-1 (never a rewritten one: ki-1 >= from-1)
-					if (__popc(pm) != 1) { fail = true; break; }
-					const uint32_t a = (uint32_t)__ffs(pm) - 1u;
-					const int t = lane;                                           // lane t < k: k-mer ki+t with the wrong base (2t bits up) replaced
-					uint64_t c = 0; uint32_t bits = 0, trp = 0, f3n = 0;
-					if (t < nrw) {
-						const uint64_t kw = W.key[ki + t];
-						const uint64_t cn = kw & kmask;
-						const uint64_t fw = (kw & THRF_RCFLAG) ? kmer_rc(cn, K) : cn;
-						c = (fw & ~(3ull << (2 * t))) | ((uint64_t)a << (2 * t));
-						const GNode g = g_lookup_fast_nl<B>(gt, c, dst, K);
-						bits = g.bits; trp = g.tr;
-						++c_probe;
-						if (ki + t + 1 < nkm) f3n = (uint32_t)(W.key[ki + t + 1] >> THRF_F3_SHIFT) & 3u;   // last base of the next k-mer
-					}
-					// lane t (< k): present, and the next k-mer's last base is an out-edge (lane 0: its ONLY out-edge, the level-2
-					// expansion of the scorer then holds just that base, cpp:907-920)
-					bool good = true;
-					if (t < nrw && ki + t + 1 < nkm) {                             // (the last k-mer of the read is only visited, cpp:553)
-						const uint32_t mk = gn_mask(bits);
-						good = (bits & GN_PRESENT) && ((mk >> f3n) & 1u) && (t != 0 || __popc(mk) == 1);
-					}
-					if (nrem <= (int)K) {                                         // deletion families must not be in play (see above)
-						const uint32_t oldnt = (uint32_t)(W.key[ki] >> THRF_F3_SHIFT) & 3u;
-						const uint32_t m0 = __shfl_sync(0xffffffffu, gn_mask(bits), 0), m1 = __shfl_sync(0xffffffffu, gn_mask(bits), 1);
-						if (((m0 >> oldnt) & 1u) || (nrem >= 2 * (int)THR_MSC + 2 && ((m1 >> oldnt) & 1u))) good = false;
-					}
-					const bool allgood = __all_sync(0xffffffffu, good);
-					if (!allgood) { fail = true; break; }
-					__syncwarp();
-					if (t < nrw) {
-						const uint64_t rc = kmer_rc(c, K);
-						const bool is_rc = rc < c;
-						W.key[ki + t] = (is_rc ? rc : c) | ((c & 3) << THRF_F3_SHIFT) | (is_rc ? THRF_RCFLAG : 0ull);
-						W.trx[ki + t] = trp;
-					}
-					__syncwarp();
-					xlist |= (uint64_t)((uint32_t)(ki + (int)K - 1) | ((a + 1) << 13)) << (16 * nfix);
-					++nfix; ++nskip;
-					from = ki + (int)K + 1;                                       // the walk resumes here (cpp:1197: ki += score - 1, then the loop's ++ki)
-					if (lane == 0) c_ec += K + 2;                                 // look-ups of the scorer's winning path: 1 + 1 expansion nodes + k walk steps
-				}
-				if ((uint32_t)nskip > maxskip) fail = true;                       // cpp:1259: the read does not thread; thread_kernel reports it
-				if (!fail && (nfix || tr_end < nkm || tr_beg > 0)) {
-#pragma unroll 1
-					for (int j = 0; j < ng; ++j) {                                 // TR ballots again: the rewritten k-mers have their own
-						const int i = j * 32 + lane;
-						const uint32_t bt = __ballot_sync(0xffffffffu, i < nkm && W.trx[i] != 0);
-						if (lane == 0) W.T[j] = bt;
-					}
-					__syncwarp();
-					clean = true;
-					if (lane == 0) ++c_fix;
-				}
-			}
-			if (!clean) { dirty |= 1u << m; continue; }
-
-			// ---- clean mate: alned = 1, es all '=', tr from the TR ballots; count its TR k-mers (D1) ----
 			{
-				uint32_t inc_sum = 0;
-#pragma unroll 1
-				for (int j = 0; j < ng; ++j) {
-					const int i = j * 32 + lane;
-					const uint32_t tx = i < nkm ? W.trx[i] : 0u;
-					const uint32_t tm = W.T[j];
-					if (!tm) continue;
-					inc_sum += __popc(tm);
-					if (tx) {
-						const uint32_t peers = __match_any_sync(tm, tx);
-						if ((uint32_t)lane == (uint32_t)(__ffs(peers) - 1))
-							atomicAdd(reinterpret_cast<unsigned long long*>(ix.counts + (tx - 1)), (unsigned long long)__popc(peers));
-					}
-				}
-				if (lane == 0) { c_inc += inc_sum; c_cls += (uint32_t)nkm; }
-			}
-			if (slot_ok) {                                                   // sam_t.r1 / r2 -> dbt_aln_mate blob
-				uint8_t* b = rec + sizeof(dbt_pair_record) + (size_t)m * rp.aln_stride;
-				uint8_t* es = b + sizeof(dbt_aln_mate); uint8_t* trb = es + rp.es_cap;
-				const int nes = min((int)len, (int)rp.es_cap), ntr = min(nkm, (int)rp.tr_cap);
-#pragma unroll 1
-				for (int q = lane; q < (int)rp.es_cap / 4; q += 32) {         // four entries per lane and store; entries >= nes read 0
-					const int nbb = min(nes, es_end) - 4 * q, nlo = es_beg - 4 * q;
-					const uint32_t keep = (nbb >= 4 ? 0xFFFFFFFFu : (nbb <= 0 ? 0u : (1u << 8 * nbb) - 1u)) & (nlo <= 0 ? 0xFFFFFFFFu : (nlo >= 4 ? 0u : 0xFFFFFFFFu << 8 * nlo));
-					uint32_t v = 0x01010101u * ET_EQ;
-#pragma unroll 1
-					for (int f = 0; f < nfix; ++f) {
-						const uint32_t e = (uint32_t)(xlist >> (16 * f)) & 0xFFFFu, xp = e & 0x1FFFu, xb = e >> 13;
-						if ((int)(xp >> 2) == q) v = (v & ~(0xFFu << (8 * (xp & 3)))) | ((uint32_t)(ET_X | (xb << 3)) << (8 * (xp & 3)));
-					}
-					reinterpret_cast<uint32_t*>(es)[q] = v & keep;
-				}
-#pragma unroll 1
-				for (int q = lane; q < (int)rp.tr_cap / 4; q += 32) {         // tr[i] = '=' (2) for TR k-mers, '.' (1) otherwise: 4 TR ballot bits -> 4 bytes
-					const int nbb = min(ntr, tr_end) - 4 * q, nlo = tr_beg - 4 * q;
-					const uint32_t keep = (nbb >= 4 ? 0xFFFFFFFFu : (nbb <= 0 ? 0u : (1u << 8 * nbb) - 1u)) & (nlo <= 0 ? 0xFFFFFFFFu : (nlo >= 4 ? 0u : 0xFFFFFFFFu << 8 * nlo));
-					const uint32_t bits = 4 * q < ng * 32 ? (W.T[(4 * q) >> 5] >> ((4 * q) & 31)) & 0xFu : 0u;
-					const uint32_t v = 0x01010101u + ((bits & 1u) | ((bits & 2u) << 7) | ((bits & 4u) << 14) | ((bits & 8u) << 21));
-					reinterpret_cast<uint32_t*>(trb)[q] = v & keep;
-				}
-				if (lane == 0) {
-					dbt_aln_mate* h = reinterpret_cast<dbt_aln_mate*>(b);
-					h->alned = nfix ? 2 : 1;                          // cpp:1259 / 1184 h->err = (uint8_t)((int)len > (int)rp.es_cap || nkm > (int)rp.tr_cap);
-					h->nes = (uint16_t)len; h->ntr = (uint16_t)nkm; h->nkm = (uint16_t)nkm;
-					uint64_t hash = 0;
-					if (trace) {                                                // FNV-1a over the k-mer vector (parity tests only)
-						hash = 0xcbf29ce484222325ull;
-#pragma unroll 1
-						for (int i = 0; i < nkm; ++i) {
-							const uint64_t kw = W.key[i];
-							const uint64_t v = (kw & THRF_RCFLAG) ? kmer_rc(kw & kmask, K) : (kw & kmask);
-							for (int q = 0; q < 8; ++q) { hash ^= (v >> (8 * q)) & 0xFF; hash *= 0x100000001b3ull; }
-						}
-					}
-					h->kmers_hash = hash;
-				}
+				const ThrfArrays A{W.key, W.trx, W.nb, W.T, W.ok, W.P};
+				if (!thrf_finish_mate<B, MAXJ>(ix, rp, sv, A, m, len, nkm, dst, rec, slot_ok, trace, lane, C)) dirty |= 1u << m;
 			}
 		}
 
-		// ---- pair level: a clean mate makes the pair thread (commented caller, cpp:2082-2087) ----
-		if (dirty != 3u) {
-			if (lane == 0) c_fea += 2;
-			if (want_rec && !slot_ok) { if (lane == 0) atomicOr(sv.ncand + 1, ERR_RECORD_OVERFLOW); }
-			else if (slot_ok && lane == 0) {
-				dbt_pair_record* h = reinterpret_cast<dbt_pair_record*>(rec);
-				if (!trace) {                                                   // under DBT_F_TRACE the generic candidate kernel left the full header
-					h->pair_index = sv.first_pair_index + p; h->dst0 = dst; h->fc = 0; h->rc = 0; h->nhash0 = 0; h->nhash1 = 0;
-					h->pad[0] = h->pad[1] = h->pad[2] = 0;
-#pragma unroll 1
-					for (int m = 0; m < 2; ++m) {
-						dbt_mate_record& o = h->mate[m];
-						o.si = o.ei = o.si_ = o.ei_ = o.ti = -1; o.nt = 0; o.bs = 0; o.pad = 0; o.nk = 0;
-						o.flags = (uint8_t)((((dw >> (28 + m)) & 1u) ? DBT_MF_KF : 0) | (((dw >> (30 + m)) & 1u) ? DBT_MF_RM : 0));
-					}
-				}
-				h->dst = dst; h->status = (uint8_t)DBT_ST_COUNTED;
-			}
-		}
-		if (dirty && lane == 0) { sv.thr2[atomicAdd(sv.ncand + 4, 1u)] = make_uint4(c, p, dw, dirty | (dirty != 3u ? THR2_ALNED : 0u)); ++c_items; }
+		thrf_finish_pair(rp, sv, c, p, dw, dst, dirty, rec, slot_ok, want_rec, trace, lane, c_fea, c_items);
 	}
-	c_probe = __reduce_add_sync(0xffffffffu, c_probe);
+	const uint32_t c_probe = __reduce_add_sync(0xffffffffu, C.probe);
+	const uint32_t c_inc = C.inc, c_cls = C.cls, c_fix = C.fix, c_ec = C.ec;
 	if (lane == 0) {
 		if (c_walk) atomicAdd(sv.counters + DBT_C_THR_WALK, (unsigned long long)c_walk);
 		if (c_probe) atomicAdd(sv.counters + DBT_C_THR_REFRESH, (unsigned long long)c_probe);

@@ -333,6 +333,7 @@ int  dbt_batch_stats(dbt_ctx*, int slot, uint64_t stats[4]);
 /* [0] main buckets [1] slots per bucket [2] keys [3] used slots [4] main buckets that overflowed
    [5] keys in the stash [6] table bytes [7] stash buckets that overflowed */
 int  dbt_table_stats(const dbt_ctx*, uint64_t stats[8]);
+int  dbt_graph_merged(const dbt_ctx*);                         /* 1: the graphs are merged into the index entries (one probe round feeds the vote and the threading); 0: no graph / switched off; < 0: refused, -(1 a node is no index key | 2 key of another locus | 4 not in its shared list | 8, 16 a TR k-mer lost its count position to the flank class) */
 uint64_t dbt_graph_table_bytes(const dbt_ctx*);                /* bytes of the graph table in HBM (0 without restored threading) */
 int  dbt_random_gather_bench(int device, uint64_t table_bytes, uint32_t sector_bytes,
                              uint64_t n_gathers, int iters, float* best_ms); /* R_rand roofline    */

@@ -235,3 +235,48 @@ def test_mixed_packed_and_ascii_sub_batches_over_both_slots(lib=None):
     for a, b in zip(ctx.download()[:3], t_all):
         assert np.array_equal(a, b)
     ctx.close()
+
+
+STRESS = [
+    dict(seed=41, rseed=1, sub=0.02, ins=0.004, dele=0.004, npairs=6000, thread=60, maxnc=4, nloci=30),
+    dict(seed=42, rseed=2, sub=0.06, ins=0.02, dele=0.02, npairs=6000, thread=15, maxnc=12, cth=15, nloci=12),
+    dict(seed=43, rseed=3, sub=0.01, ins=0.03, dele=0.03, npairs=6000, thread=25, maxnc=6, cth=20, frac_n=0.2, nloci=12, k=17),
+    dict(seed=44, rseed=4, sub=0.03, ins=0.01, dele=0.01, npairs=4000, thread=30, maxnc=5, cth=20, rlen=250, nloci=12),
+    dict(seed=45, rseed=5, sub=0.004, ins=0.0002, dele=0.0002, npairs=8000, thread=85, maxnc=3, nloci=40),     # the bench's error model
+]
+
+
+@pytest.mark.parametrize("merge", [True, False], ids=["graph-in-index", "two-tables"])
+@pytest.mark.parametrize("cfg", list(CASES) + STRESS, ids=lambda c: f"s{c.get('seed')}")
+def test_production_mode_records_vs_oracle(cfg, merge, monkeypatch):
+    """`-a` without DBT_F_TRACE = the production kernels: with the graphs merged into the index candidate_fast_kernel threads the pairs
+    itself (thread_fast_kernel only sees what the generic kernel defers), with DBT_NO_GRAPH_MERGE thread_fast_kernel probes the graph
+    table; both must give the oracle's records (status, locus, alned, CIGAR, annotation) and counts."""
+    if not merge:
+        monkeypatch.setenv("DBT_NO_GRAPH_MERGE", "1")
+    gk, pk = split_case(cfg)
+    _, ix, seqs, _ = tc.thread_case(write_text=False, frac_bg=0.15, **gk)
+    bases, off = rpgg_io.seqs_to_batch(seqs)
+    rl = gk.get("rlen", 150)
+    pt = tc.thread_params(extra_flags=abi.F_TRACE, max_batch_pairs=8192, max_read_len=rl, **pk)
+    orecs, ocnt, otr, okmc, onmap = Oracle(ix).run(pt, bases, off)
+    p = tc.thread_params(aln=1, max_batch_pairs=8192, max_read_len=rl, **pk)
+    ctx = abi.Context(p, abi.make_index_struct(ix))
+    assert ctx.L.dbt_graph_merged(ctx.h) == (1 if merge else 0)
+    recs, cnt = ctx.run(bases, off)
+    trkmc, kmc, nmap, _ = ctx.download()
+    ctx.close()
+    assert np.array_equal(trkmc, otr) and np.array_equal(kmc, okmc) and np.array_equal(nmap, onmap)
+    st = orecs["h"]["status"]
+    want = np.nonzero((st == abi.ST_COUNTED) | (st == abi.ST_THREAD_FAILED))[0]
+    assert [int(x) for x in recs["h"]["pair_index"]] == [int(i) for i in want]
+    for r in recs:
+        o = orecs[int(r["h"]["pair_index"])]
+        assert r["h"]["status"] == o["h"]["status"] and r["h"]["dst"] == o["h"]["dst"], int(r["h"]["pair_index"])
+        for m in range(2):
+            a, b = r["aln"][m], o["aln"][m]
+            assert a["h"]["alned"] == b["h"]["alned"] and a["h"]["nes"] == b["h"]["nes"] and a["h"]["ntr"] == b["h"]["ntr"], (int(r["h"]["pair_index"]), m)
+            assert a["es"].tobytes() == b["es"].tobytes() and a["tr"].tobytes() == b["tr"].tobytes(), (int(r["h"]["pair_index"]), m)
+    for i, name in enumerate(abi.COUNTER_NAMES):
+        if name not in abi.MEASUREMENT_COUNTERS:
+            assert int(cnt[i]) == int(ocnt[i]), name
