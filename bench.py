@@ -638,6 +638,7 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
     p_sub = cnt["nhash0"] + 2 * ncand                       # ++nhash skips the iteration that breaks (cpp:176)
     bytes_sub = P * 75 + 32 * p_sub
     g_h1, g_thr, g_inc = cnt["gen_nhash1"], cnt["gen_nThreadingReads"], cnt["gen_ninc"]
+    merged = thr and L.dbt_graph_merged(ctx.h) == 1
     if thr:
         # candidate stage = kfilter + vote only (no assignTRkmc); threading: one node look-up per k-mer step of the walk
         # (cpp:1170), the look-ups of the correction code, one trResults look-up per k-mer of the edited vectors of
@@ -648,6 +649,12 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
         # classifies every error-free mate, thread_kernel the mates with errors (+ the correction look-ups)
         bytes_thr2 = 32 * (cnt["thr2_walk"] + cnt["thr_ec"] + cnt["thr2_cls"]) + 64 * cnt["thr2_ninc"]
         bytes_thr = 32 * (cnt["thr_walk"] + cnt["thr_ec"] + cnt["thr_cls"]) + 64 * cnt["ninc"] - bytes_thr2
+        if merged:
+            # graphs merged into the index entries: candidate_fast_kernel does thread_fast_kernel's work itself (walk + classification of
+            # every mate it can finish, their increments) out of the index buckets it has probed; thread_fast_kernel only sees the pairs
+            # the generic kernel defers (0.3 % of the candidates; its own counters are not kept apart, its share is booked with the rest)
+            bytes_fast += bytes_thr
+            bytes_thr = 0
     else:
         # candidate stage: kfilter probes (nhash1) + one classification probe per k-mer of pairs reaching assignTRkmc + increments,
         # split between the closed-form kernel and the generic kernel by the generic kernel's own counters
@@ -678,7 +685,10 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
     if thr:
         nthr_pairs = max(cnt["nThreadingReads"] // 2, 1)
         t_stage = t_thr + t_thr2
-        roofline["thread_stage"] = {"kernels": "thread_fast_kernel + thread_kernel (= round 1's single thread_kernel)", "ms": t_stage,
+        roofline["graphs_merged_into_index"] = bool(merged)
+        roofline["thread_stage"] = {"kernels": "thread_fast_kernel + thread_kernel (= round 1's single thread_kernel)" if not merged else
+                                    "thread_kernel only: with the graphs merged into the index candidate_fast_kernel threads the error-free / corrected mates itself "
+                                    "(its time and bytes are booked under candidate_fast_kernel); thread_fast_kernel takes the pairs the generic kernel defers", "ms": t_stage,
                                     "algorithmic_bytes": bytes_thr + bytes_thr2,
                                     "GBps": (bytes_thr + bytes_thr2) / (t_stage / 1e3) / 1e9 if t_stage > 0 else 0.0,
                                     "frac": (bytes_thr + bytes_thr2) / (t_stage / 1e3) / 1e9 / peak if t_stage > 0 else 0.0,
@@ -707,13 +717,15 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
         # this can exceed 1 -- it is the honest denominator for HBM-resident tables (--loci 20000 and up).
         # logical = the probes the REFERENCE algorithm makes (SURVEY §8(d) unit of work); issued = the bucket fetches the kernel
         # really starts (one graph probe answers walk + classification; kfilter and assignTRkmc share one index probe)
-        logical = {"thread_fast_kernel": (cnt["thr_walk"] - cnt["thr2_walk"]) + (cnt["thr_cls"] - cnt["thr2_cls"]) if thr else 0,
+        l_tf = (cnt["thr_walk"] - cnt["thr2_walk"]) + (cnt["thr_cls"] - cnt["thr2_cls"]) if thr else 0
+        i_tf = cnt["thr_refresh"] - cnt["thr2_refresh"] if thr else 0
+        logical = {"thread_fast_kernel": 0 if merged else l_tf,
                    "thread_kernel": cnt["thr2_walk"] + cnt["thr_ec"] + cnt["thr2_cls"] if thr else 0,
-                   "candidate_fast_kernel": (cnt["nhash1"] - g_h1) + (0 if thr else (cnt["nThreadingReads"] - g_thr) * nk),
+                   "candidate_fast_kernel": (cnt["nhash1"] - g_h1) + (0 if thr else (cnt["nThreadingReads"] - g_thr) * nk) + (l_tf if merged else 0),
                    "subfilter_kernel": p_sub}
-        issued = {"thread_fast_kernel": cnt["thr_refresh"] - cnt["thr2_refresh"] if thr else 0,
+        issued = {"thread_fast_kernel": 0 if merged else i_tf,
                   "thread_kernel": cnt["thr2_refresh"] + cnt["thr_ec"] if thr else 0,
-                  "candidate_fast_kernel": cnt["nhash1"] - g_h1,
+                  "candidate_fast_kernel": cnt["nhash1"] - g_h1 + (i_tf if merged else 0),
                   "subfilter_kernel": p_sub}
         if logical.get(dom) and dom_ms > 0:
             rr["dominant_kernel_Gprobes_per_s"] = logical[dom] / (dom_ms / 1e3) / 1e9

@@ -29,7 +29,13 @@
 
 namespace dbt {
 
-constexpr int CAND_FAST_WARPS = 8;
+#ifndef CANDF_WARPS_N
+#define CANDF_WARPS_N 8
+#endif
+#ifndef CANDF_MINBLOCKS
+#define CANDF_MINBLOCKS 3
+#endif
+constexpr int CAND_FAST_WARPS = CANDF_WARPS_N;
 
 // Per-warp shared-memory state.  Everything indexed by mate or by 32-position group lives here rather
 // than in registers so that the stages are ROLLED loops (2 mates x MAXJ groups): ncu showed the fully
@@ -61,7 +67,7 @@ struct FastWarp {
 
 
 template <int B, int MAXJ>
-__global__ void __launch_bounds__(CAND_FAST_WARPS * 32, 3) candidate_fast_kernel(DevIndex ix, RunParams rp, SlotView sv) {
+__global__ void __launch_bounds__(CAND_FAST_WARPS * 32, CANDF_MINBLOCKS) candidate_fast_kernel(DevIndex ix, RunParams rp, SlotView sv) {
 	extern __shared__ __align__(16) uint8_t fast_smem[];
 	FastWarp<B, MAXJ>* wsm = reinterpret_cast<FastWarp<B, MAXJ>*>(fast_smem);
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
