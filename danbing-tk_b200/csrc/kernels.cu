@@ -172,10 +172,13 @@ __global__ void __launch_bounds__(256) subfilter_kernel(DevIndex ix, RunParams r
 	const bool trace = (rp.flags & DBT_F_TRACE) != 0;
 	const bool filter_on = rp.n_filter && rp.nm_filter;
 	uint32_t c_short = 0, c_sub = 0, c_h0 = 0;
+	// a batch the packer flagged (a read longer than max_read_len: dbt_wait reports DBT_E_CAPACITY) must not be counted at all --
+	// the caller rebuilds the context and submits it again: no pair passes, nothing downstream runs on it
+	const bool dead = (sv.ncand[1] & ERR_READ_TOO_LONG) != 0;
 	for (uint64_t w = wid; w < nwords; w += nwarps) {
 		const uint64_t p = w * 32 + lane;
 		bool pass = false;
-		if (p < sv.npairs) {
+		if (p < sv.npairs && !dead) {
 			const uint16_t m1 = sv.meta[0][p], m2 = sv.meta[1][p];
 			uint32_t nh = 0; int status = -1;
 			if ((m1 | m2) & META_NOVALID) { status = DBT_ST_SHORT; ++c_short; }          // cpp:2037
