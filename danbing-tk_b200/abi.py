@@ -16,7 +16,7 @@ DBT_N_SLOTS = 2
 DBT_NCCL_ID_BYTES = 128
 
 F_KAM, F_QC, F_TRACE, F_THREADING, F_CORRECTION, F_ALN, F_ALN_MIN = 1, 2, 4, 8, 16, 32, 64
-F_EXTRACT, F_SIM, F_BUBBLES = 128, 256, 512
+F_EXTRACT, F_SIM, F_BUBBLES, F_BAIT = 128, 256, 512, 1024
 ST_SHORT, ST_SUBFILTERED, ST_KFILTERED, ST_UNASSIGNED, ST_QCFILTERED, ST_ASGN_REMOVED, ST_COUNTED, ST_NOT_THREADED, ST_THREAD_FAILED = range(9)
 LAYOUT_ASCII, LAYOUT_PACKED = 0, 1
 COUNTER_NAMES = ["nReads", "nShort", "nSubFiltered", "nKmerFiltered", "nBaitFiltered", "nQualFiltered",
@@ -46,7 +46,8 @@ class Params(C.Structure):
 class Index(C.Structure):
     _fields_ = [("nloci", C.c_uint64), ("nk_dbi", C.c_uint64), ("dbi_keys", u64p), ("dbi_vals", u32p),
                 ("nvv", C.c_uint64), ("vv", u32p), ("tr_n", u64p), ("tr_kmers", u64p), ("fl_n", u64p),
-                ("fl_kmers", u64p), ("qc", u8p), ("g_n", u64p), ("g_kmers", u64p), ("g_masks", u8p), ("tre_n", u64p), ("tre_kmers", u64p)]
+                ("fl_kmers", u64p), ("qc", u8p), ("g_n", u64p), ("g_kmers", u64p), ("g_masks", u8p),
+                ("bt_n", u64p), ("bt_kmers", u64p), ("bt_vals", C.POINTER(C.c_uint16)), ("tre_n", u64p), ("tre_kmers", u64p)]
 
 
 class Batch(C.Structure):
@@ -138,6 +139,10 @@ def make_index_struct(ix):
         s.g_n = ptr(ix["g_n"], u64p)
         s.g_kmers = ptr(ix["g_kmers"], u64p)
         s.g_masks = ptr(ix["g_masks"], u8p)
+    if ix.get("bt_n") is not None:                  # PREF.bt.kmdb (`-b`)
+        s.bt_n = ptr(ix["bt_n"], u64p)
+        s.bt_kmers = ptr(ix["bt_kmers"], u64p)
+        s.bt_vals = ix["bt_vals"].ctypes.data_as(C.POINTER(C.c_uint16))
     if ix.get("tre_n") is not None:                 # PREF.tre.kdb (`-bu`)
         s.tre_n = ptr(ix["tre_n"], u64p)
         s.tre_kmers = ptr(ix["tre_kmers"], u64p)

@@ -18,6 +18,7 @@
 #pragma once
 #include "device_types.cuh"
 #include "introsort.cuh"
+#include "bait.cuh"
 
 namespace dbt {
 
@@ -365,7 +366,7 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 	uint16_t* umid  = ustart + UMAX + 2;                                // first mate-1 element of the group
 	uint16_t* perm  = umid + UMAX;                                      // visiting order (cpp:320-327)
 
-	uint32_t c_kf = 0, c_laf = 0, c_qc = 0, c_thr = 0, c_asgn = 0, c_h1 = 0, c_inc = 0, c_pairs = 0, c_thr0 = 0;   // lane-0 accumulators
+	uint32_t c_kf = 0, c_laf = 0, c_qc = 0, c_thr = 0, c_asgn = 0, c_h1 = 0, c_inc = 0, c_pairs = 0, c_thr0 = 0, c_bait = 0;   // lane-0 accumulators
 	const uint32_t nwork = all ? sv.ncand[0] : sv.ncand[2];
 	const uint32_t stride = nwarps;
 
@@ -377,7 +378,7 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 		const uint32_t p = active ? sv.cand[c] : 0;
 		uint32_t nk[2] = {0, 0};
 		uint32_t hitmask[2][MAXJ];            // ballot of "k-mer is in the index" per 32 positions
-		int kf[2] = {0, 0}, rm[2] = {1, 1}, hf[2] = {0, 0};
+		int kf[2] = {0, 0}, rm[2] = {1, 1}, hf[2] = {0, 0}, bf[2] = {0, 0};
 		uint32_t nhash1 = 0;
 		int status = -1;
 		bool deferred = false;
@@ -642,6 +643,11 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 				if (lane == 0) c_thr += 2;
 				status = DBT_ST_COUNTED;
 			}
+			if (status < 0 && ix.btable.slots) {                 // `-b`: bait filter (cpp:2110-2125): either mate removes the pair
+#pragma unroll 1
+				for (int m = 0; m < 2; ++m) if (bait_filtered<B>(ix.btable, pk + m * W64, WB, nk[m], K, dst, lane)) bf[m] = 1;
+				if (bf[0] | bf[1]) { if (lane == 0) c_bait += (bf[0] & !rm[0]) + (bf[1] & !rm[1]); rm[0] = rm[1] = 1; }
+			}
 			if (status < 0) {
 				if (lane == 0) c_thr += 2;
 				// assignTRkmc (cpp:1450-1556) against the tables of destLocus0
@@ -714,7 +720,7 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 							dbt_mate_record& o = h->mate[m];
 							o.si = (int16_t)mo[m].si; o.ei = (int16_t)mo[m].ei; o.si_ = (int16_t)mo[m].si_; o.ei_ = (int16_t)mo[m].ei_;
 							o.ti = (int16_t)mo[m].ti; o.nt = (int8_t)mo[m].nt; o.bs = (int8_t)mo[m].bs;
-							o.flags = (uint8_t)((kf[m] ? DBT_MF_KF : 0) | (hf[m] ? DBT_MF_HF : 0) | (mo[m].af ? DBT_MF_AF : 0) | (rm[m] ? DBT_MF_RM : 0));
+							o.flags = (uint8_t)((kf[m] ? DBT_MF_KF : 0) | (hf[m] ? DBT_MF_HF : 0) | (bf[m] ? DBT_MF_BF : 0) | (mo[m].af ? DBT_MF_AF : 0) | (rm[m] ? DBT_MF_RM : 0));
 							o.pad = 0; o.nk = (uint16_t)nas[m];
 						}
 					}
@@ -741,6 +747,7 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 		counter_add(sv.counters, DBT_C_NKMERFILTERED, c_kf);
 		counter_add(sv.counters, DBT_C_NLOCUSASSIGNFILTERED, c_laf);
 		counter_add(sv.counters, DBT_C_NQCFILTERED, c_qc);
+		counter_add(sv.counters, DBT_C_NBAITFILTERED, c_bait);
 		counter_add(sv.counters, DBT_C_NTHREADINGREADS, c_thr + c_thr0);
 		counter_add(sv.counters, DBT_C_NFEASIBLEREADS, c_thr);
 		counter_add(sv.counters, DBT_C_NASGNREADS, c_asgn);

@@ -77,7 +77,7 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, CANDF_MINBLOCKS) candida
 	const bool wstat = okam || (rp.thr_on && (rp.flags & (DBT_F_ALN | DBT_F_ALN_MIN)));   // record slots are keyed by candidate ordinal: keep their status current
 	const uint32_t nloci = (uint32_t)ix.nloci, cth = rp.cth;
 	FastWarp<B, MAXJ>& W = wsm[wib];
-	uint32_t c_kf = 0, c_laf = 0, c_qc = 0, c_thr = 0, c_asgn = 0, c_h1 = 0, c_inc = 0, c_thr0 = 0;   // lane-0 accumulators
+	uint32_t c_kf = 0, c_laf = 0, c_qc = 0, c_thr = 0, c_asgn = 0, c_h1 = 0, c_inc = 0, c_thr0 = 0, c_bait = 0;   // lane-0 accumulators
 	const bool fused = rp.thr_on && ix.gmerged && !(rp.flags & DBT_F_TRACE);   // thread the pairs here, from the index entries (graphs merged into the index)
 	const bool want_aln = (rp.flags & (DBT_F_ALN | DBT_F_ALN_MIN)) != 0;
 	uint32_t t_fea = 0, t_walk = 0, t_items = 0;
@@ -386,6 +386,12 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, CANDF_MINBLOCKS) candida
 			__syncwarp();
 			status = DBT_ST_COUNTED;
 		}
+		uint32_t bfm = 0;                                        // bit m = bf[m]
+		if (status < 0 && ix.btable.slots) {                     // `-b`: bait filter (cpp:2110-2125): either mate removes the pair
+#pragma unroll 1
+			for (int m = 0; m < 2; ++m) if (bait_filtered<B>(ix.btable, W.pk + m * W64, WB, m ? nk1 : nk0, K, dst, lane)) bfm |= 1u << m;
+			if (bfm) { if (lane == 0) c_bait += __popc(bfm & ~rmm); rmm = 3u; }
+		}
 		if (status < 0) {
 			if (lane == 0) c_thr += 2;
 			int span = 0;
@@ -415,7 +421,7 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, CANDF_MINBLOCKS) candida
 					dbt_mate_record& o = W.mate[m];
 					o.si = (int16_t)mo.si; o.ei = (int16_t)mo.ei; o.si_ = (int16_t)mo.si_; o.ei_ = (int16_t)mo.ei_;
 					o.ti = (int16_t)mo.ti; o.nt = (int8_t)mo.nt; o.bs = (int8_t)mo.bs;
-					o.flags = (uint8_t)((((kfm >> m) & 1u) ? DBT_MF_KF : 0) | (mo.af ? DBT_MF_AF : 0) | (mo.rm ? DBT_MF_RM : 0));
+					o.flags = (uint8_t)((((kfm >> m) & 1u) ? DBT_MF_KF : 0) | (((bfm >> m) & 1u) ? DBT_MF_BF : 0) | (mo.af ? DBT_MF_AF : 0) | (mo.rm ? DBT_MF_RM : 0));
 					o.pad = 0; o.nk = (uint16_t)nas;
 				}
 			}
@@ -487,6 +493,7 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, CANDF_MINBLOCKS) candida
 		counter_add(sv.counters, DBT_C_NKMERFILTERED, c_kf);
 		counter_add(sv.counters, DBT_C_NLOCUSASSIGNFILTERED, c_laf);
 		counter_add(sv.counters, DBT_C_NQCFILTERED, c_qc);
+		counter_add(sv.counters, DBT_C_NBAITFILTERED, c_bait);
 		counter_add(sv.counters, DBT_C_NTHREADINGREADS, c_thr + c_thr0);
 		counter_add(sv.counters, DBT_C_NFEASIBLEREADS, c_thr);
 		counter_add(sv.counters, DBT_C_NASGNREADS, c_asgn);

@@ -129,6 +129,7 @@ struct dbt_ctx {
 	uint4* d_gslots = nullptr; uint64_t gtable_bytes = 0, gnodes = 0;   // graph table (restored threading)
 	uint4* d_tslots = nullptr; Table ttable{}; bool bubbles = false;    // TR edge table (`-bu`)
 	uint32_t gmerge_err = 0;             // why the merge was refused: 1 node not an index key, 2 key of another locus, 4 not in the shared list, 8/16 TR k-mer without its count position
+	uint4* d_bslots = nullptr;                                           // bait table (`-b`)
 	uint32_t* d_vv_g = nullptr;                                          // graph entries of multi-locus k-mers (graphs merged into the index)
 	uint4* d_slots = nullptr; uint32_t* d_vv = nullptr; uint32_t* d_vv_aux = nullptr;
 	// results: ONE allocation [counts nk_tr | kmc nloci | totals DBT_N_COUNTERS] u64 + [nmapread nloci] u32, so that the
@@ -267,7 +268,7 @@ extern "C" void dbt_destroy(dbt_ctx* c) {
 	cudaSetDevice(c->p.device);
 	for (auto& s : c->slot) free_slot(s);
 	if (c->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
-	cudaFree(c->d_gslots); cudaFree(c->d_tslots); cudaFree(c->d_vv_g);
+	cudaFree(c->d_gslots); cudaFree(c->d_tslots); cudaFree(c->d_vv_g); cudaFree(c->d_bslots);
 	cudaFree(c->d_slots); cudaFree(c->d_vv); cudaFree(c->d_vv_aux); cudaFree(c->d_results); cudaFree(c->d_red);
 	cudaFree(c->d_qc); cudaFree(c->d_permtab); cudaFree(c->d_vote_pool); cudaFree(c->d_vote_lock);
 	if (c->h_totals) cudaFreeHost(c->h_totals);
@@ -382,6 +383,41 @@ static int load_graph(dbt_ctx* c, const dbt_index* in, uint64_t ntr) {
 	c->ix.gtable = t;
 	c->rp.thr_on = 1;
 	c->rp.rec_stride = (uint32_t)sizeof(dbt_pair_record) + 2 * c->rp.aln_stride;
+	return DBT_OK;
+}
+
+// baitDB of all loci (PREF[.qc].bt.kmdb, cpp:2495-2499) -> one device table keyed (canonical k-mer, locus), payload = min << 8 | max
+static int load_baits(dbt_ctx* c, const dbt_index* in) {
+	const uint64_t nloci = in->nloci;
+	if (nloci >= G_LOCUS_MASK) return fail(DBT_E_CAPACITY, "-b supports < %u loci", G_LOCUS_MASK);
+	uint64_t nb = 0;
+	for (uint64_t l = 0; l < nloci; ++l) nb += in->bt_n[l];
+	const int B = c->B;
+	const uint64_t nbuckets = (uint64_t)((double)(nb + 1024) / c->p.table_load) / B + 64, nstash = std::max<uint64_t>(64, ((nb + 1024) / 2 + B - 1) / B);
+	if (nbuckets >= (1ull << 32) || nstash >= (1ull << 32)) return fail(DBT_E_CAPACITY, "bait table needs %llu buckets (limit 2^32)", (unsigned long long)nbuckets);
+	cudaStream_t st; CU(cudaStreamCreate(&st));
+	TRY(dev_alloc(&c->d_bslots, (nbuckets + nstash) * B, "bait table"));
+	CU(cudaMemsetAsync(c->d_bslots, 0xFF, (nbuckets + nstash) * B * sizeof(uint4), st));
+	Table t{c->d_bslots, nbuckets, nstash};
+	uint32_t herr = 0;
+	if (nb) {
+		uint32_t* d_err; TRY(dev_alloc(&d_err, 1, "err")); CU(cudaMemsetAsync(d_err, 0, 4, st));
+		std::vector<uint32_t> loc(nb);
+		uint64_t j = 0;
+		for (uint64_t l = 0; l < nloci; ++l) for (uint64_t i = 0; i < in->bt_n[l]; ++i) loc[j++] = (uint32_t)l;
+		uint64_t* dk; uint16_t* dv; uint32_t* dl;
+		TRY(dev_alloc(&dk, nb, "bait kmers")); TRY(dev_alloc(&dv, nb, "bait bounds")); TRY(dev_alloc(&dl, nb, "bait loci"));
+		CU(cudaMemcpyAsync(dk, in->bt_kmers, nb * 8, cudaMemcpyHostToDevice, st));
+		CU(cudaMemcpyAsync(dv, in->bt_vals, nb * 2, cudaMemcpyHostToDevice, st));
+		CU(cudaMemcpyAsync(dl, loc.data(), nb * 4, cudaMemcpyHostToDevice, st));
+		CU(launch_bait_insert(st, B, t, dk, dv, dl, nb, d_err)); ++c->launches;
+		CU(cudaMemcpyAsync(&herr, d_err, 4, cudaMemcpyDeviceToHost, st));
+		CU(cudaStreamSynchronize(st));
+		cudaFree(dk); cudaFree(dv); cudaFree(dl); cudaFree(d_err);
+	}
+	CU(cudaStreamDestroy(st));
+	if (herr & ERR_INDEX_FULL) return fail(DBT_E_CAPACITY, "bait table overflow: lower table_load");
+	c->ix.btable = t;
 	return DBT_OK;
 }
 
@@ -580,6 +616,12 @@ extern "C" int dbt_load_index(dbt_ctx* c, const dbt_index* in) {
 	c->ix.gtable = Table{nullptr, 0, 0};
 	c->ix.vv_g = nullptr; c->ix.gmerged = 0;
 	if ((c->p.flags & DBT_F_THREADING) && in->g_n && in->g_kmers && in->g_masks) { TRY(load_graph(c, in, ntr)); TRY(merge_graph(c, in, ntr)); }
+	c->ix.btable = Table{nullptr, 0, 0};
+	if (c->p.flags & DBT_F_BAIT) {
+		if (c->rp.thr_on) return fail(DBT_E_BADARG, "DBT_F_BAIT with graph threading: the reference filters baits only without threading (cpp:2110)");
+		if (!in->bt_n || ((!in->bt_kmers || !in->bt_vals) && nloci)) return fail(DBT_E_BADARG, "DBT_F_BAIT needs bt_n / bt_kmers / bt_vals (PREF.bt.kmdb)");
+		TRY(load_baits(c, in));
+	}
 	if (c->p.flags & DBT_F_BUBBLES) {
 		if (c->rp.thr_on) return fail(DBT_E_BADARG, "DBT_F_BUBBLES with graph threading: the reference counts bubbles only without threading (cpp:2110, 2160)");
 		if (!in->tre_n || (!in->tre_kmers && nloci)) return fail(DBT_E_BADARG, "DBT_F_BUBBLES needs tre_n / tre_kmers (PREF.tre.kdb)");

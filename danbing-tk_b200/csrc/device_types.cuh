@@ -31,6 +31,7 @@ struct DevIndex {
 	uint32_t* vote_epoch;       // [VOTE_POOL] last epoch used in each array
 	uint64_t nloci, nk_tr;
 	Table    gtable;            // graphDB of all loci (graph_table.cuh); slots == nullptr when no graph is loaded
+	Table    btable;            // `-b`: bait k-mers of all loci, keyed (k-mer, locus), payload = min << 8 | max (bait.cuh); slots == nullptr: no bait filter
 	const uint32_t* vv_g;       // parallel to vv: graph entry (ten bits, see table.cuh slot_val) of the k-mer in that locus
 	uint32_t gmerged;           // 1: every graph node is an index key of its locus and every TR k-mer keeps its count position in the
 	                            // index entry -> candidate_fast_kernel threads the pairs itself from the entries it already holds

@@ -582,6 +582,12 @@ cudaError_t launch_tr_class_check(cudaStream_t st, int B, Table t, const uint32_
 	return cudaGetLastError();
 }
 
+cudaError_t launch_bait_insert(cudaStream_t st, int B, Table t, const uint64_t* kmers, const uint16_t* vals, const uint32_t* locus_of, uint64_t n, uint32_t* err) {
+	if (!n) return cudaSuccess;
+	DISPATCH_B(B, bait_insert_kernel<BB><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(t, kmers, vals, locus_of, n, err));
+	return cudaGetLastError();
+}
+
 cudaError_t launch_table_stats(cudaStream_t st, int B, Table t, unsigned long long* out) {
 	DISPATCH_B(B, table_stats_kernel<BB><<<(unsigned)((t.nbuckets + t.nstash + 255) / 256), 256, 0, st>>>(t, out));
 	return cudaGetLastError();

@@ -24,6 +24,7 @@ cudaError_t launch_graph_build(cudaStream_t st, int B, Table t, const uint64_t* 
 cudaError_t launch_graph_merge(cudaStream_t st, int B, Table t, const uint32_t* vv, uint32_t* vv_g, const uint64_t* kmers, const uint8_t* masks,
                                const uint32_t* locus_of, uint64_t n, uint32_t k, uint32_t* err);
 cudaError_t launch_tr_class_check(cudaStream_t st, int B, Table t, const uint32_t* vv, const uint32_t* vv_aux, const uint64_t* kmers, const uint32_t* locus_of, uint64_t n, uint32_t* err);
+cudaError_t launch_bait_insert(cudaStream_t st, int B, Table t, const uint64_t* kmers, const uint16_t* vals, const uint32_t* locus_of, uint64_t n, uint32_t* err);   // `-b` (bait.cuh)
 cudaError_t launch_table_stats(cudaStream_t st, int B, Table t, unsigned long long* out);
 cudaError_t launch_random_gather(cudaStream_t st, int nsm, const uint4* table, uint64_t table_bytes, uint32_t sector_bytes,
                                  uint64_t ngathers, uint64_t seed, uint32_t* sink);

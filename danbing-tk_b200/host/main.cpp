@@ -36,6 +36,7 @@
 #include "kam_writer.hpp"
 #include "aln_writer.hpp"
 #include "bubbles.hpp"
+#include "bait.hpp"
 
 using namespace dbt_host;
 
@@ -60,6 +61,7 @@ private:
 struct BatchOut {                       // what a worker hands to the writer
 	uint64_t index = 0;                 // ordinal of the batch / chunk in the stream: stdout and the per-batch stderr lines go out in this order
 	std::string text;                   // kam lines
+	std::vector<BubbleEvent> bait_events;   // `-tb`: the bait k-mer that removed a mate (key = pair ordinal << 10 | mate << 9)
 	std::vector<BubbleEvent> events;    // `-bu`: novel edges of the batch, ascending (pair, mate, position)
 	std::vector<std::string> parts;     // ... or several pieces in order (formatted by several threads); the strings come from and return to Shared::strings
 	uint64_t counters[DBT_N_COUNTERS] = {};
@@ -81,6 +83,7 @@ struct Shared {
 	Options opt;
 	StringPool strings;
 	std::unique_ptr<StreamPairer> pairer; PairTurn turn;
+	BaitDB baits; std::unique_ptr<BubbleAcc> bait_hits;                          // `-b` / `-tb`
 	std::unique_ptr<BubbleAcc> bubbles;                                          // `-bu`: replayed by the writer thread in stream order
 	uint64_t chunk_target = 0;          // raw text bytes per GPU submission
 	std::atomic<uint64_t> t_split_us{0}, t_pair_us{0}, t_wait_us{0}, t_format_us{0}, t_read_us{0}, n_slow_chunks{0}, n_chunks{0};
@@ -110,6 +113,9 @@ struct Worker {
 // one kam line, or none: with `-s` a record is printed when its read name carries a source locus or the pair was assigned (cpp:2169)
 bool append_kam_checked(Shared& S, std::string& o, const uint8_t* rec, uint32_t as_stride, const PairText& t) {
 	long long src = -1;
+	const dbt_pair_record* h0 = reinterpret_cast<const dbt_pair_record*>(rec);
+	if (!S.opt.okam) return true;                                                // (records only travel for `-tb`)
+	if (!S.opt.simmode && h0->dst == S.rpgg.nloci) return true;                  // removed pairs print only with a known source locus (cpp:2169)
 	if (S.opt.simmode) {
 		src = sim_source_locus(t, S.opt.simmode, S.rpgg.nloci);
 		if (src == -2) { S.fail("-s " + std::to_string(S.opt.simmode) + ": cannot read the source locus from read name " + std::string(t.title, t.title_len)); return false; }
@@ -136,13 +142,26 @@ bool fetch_bubbles(Shared& S, Worker& w, int slot, uint64_t npairs, F&& ordinal,
 	return true;
 }
 
+// `-tb`: for every mate of this record that the bait filter removed, the bait k-mer bfilter_FPSv1 stopped at (host/bait.hpp)
+void bait_track(Shared& S, const uint8_t* rec, const PairText& t, uint64_t ordinal, std::vector<BubbleEvent>& out) {
+	const dbt_pair_record* h = reinterpret_cast<const dbt_pair_record*>(rec);
+	if (h->dst0 >= S.baits.per_locus.size()) return;
+	for (int m = 0; m < 2; ++m) {
+		if (!(h->mate[m].flags & DBT_MF_BF)) continue;
+		uint64_t km = 0;
+		if (first_bait_violation(S.baits.per_locus[h->dst0], t.seq[m], t.seq_len[m], (uint32_t)S.opt.ksize, km))
+			out.push_back(BubbleEvent{(ordinal << 10) | ((uint64_t)m << 9), km, h->dst0});
+	}
+}
+
 bool make_ctx(Shared& S, Worker& w, uint32_t max_len) {
 	dbt_params p;
 	dbt_default_params(&p);
 	const Options& o = S.opt;
 	p.device = w.gpu; p.k = (uint32_t)o.ksize; p.n_filter = (uint32_t)o.N_FILTER; p.nm_filter = (uint32_t)o.NM_FILTER;
 	p.cth = (uint32_t)o.Cthreshold; p.nm_tr = (uint32_t)o.NM_TR; p.thread_cth = (uint32_t)o.thread_cth; p.max_ncorrection = (uint32_t)o.maxncorrection;
-	p.flags = (o.extractFastX ? DBT_F_EXTRACT : (o.okam ? DBT_F_KAM : 0)) | (o.simmode ? DBT_F_SIM : 0) | (o.outputBubbles ? DBT_F_BUBBLES : 0) | (o.qc ? DBT_F_QC : 0) | (o.threading ? DBT_F_THREADING : 0) | (o.threading && o.correction ? DBT_F_CORRECTION : 0) |
+	p.flags = (o.extractFastX ? DBT_F_EXTRACT : ((o.okam || o.trackBait) ? DBT_F_KAM : 0)) | ((o.simmode || o.trackBait) ? DBT_F_SIM : 0) | (o.outputBubbles ? DBT_F_BUBBLES : 0) |
+	          (o.bait ? DBT_F_BAIT : 0) | (o.qc ? DBT_F_QC : 0) | (o.threading ? DBT_F_THREADING : 0) | (o.threading && o.correction ? DBT_F_CORRECTION : 0) |
 	          (o.aln ? DBT_F_ALN : 0) | (o.aln_minimal ? DBT_F_ALN_MIN : 0);
 	p.max_read_len = max_len; p.max_batch_pairs = (uint32_t)S.batch_pairs; p.max_records = (uint32_t)S.batch_pairs;
 	p.table_load = o.table_load; p.bucket_slots = o.bucket_slots;
@@ -186,6 +205,15 @@ void worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<HostBatch
 		memcpy(bo.counters, f.res.counters, sizeof bo.counters);
 		if (!fetch_bubbles(S, w, s, f.hb->npairs, [&](uint64_t p) { return f.hb->first_pair_index + p; }, bo.events)) return false;
 		std::sort(bo.events.begin(), bo.events.end(), [](const BubbleEvent& a, const BubbleEvent& b) { return a.key < b.key; });
+		std::sort(bo.bait_events.begin(), bo.bait_events.end(), [](const BubbleEvent& a, const BubbleEvent& b) { return a.key < b.key; });
+		if (S.bait_hits) {
+			const uint32_t stride = dbt_record_stride(w.ctx);
+			for (uint64_t i = 0; i < f.res.n_records; ++i) {
+				const uint8_t* rec = f.recs.data() + i * stride;
+				const uint64_t pi = reinterpret_cast<const dbt_pair_record*>(rec)->pair_index - f.hb->first_pair_index;
+				bait_track(S, rec, pair_text(*f.hb, pi, S.opt.isFastq), f.hb->first_pair_index + pi, bo.bait_events);
+			}
+		}
 		if (S.want_records && f.res.n_records) {
 			const uint32_t stride = dbt_record_stride(w.ctx), as_stride = dbt_record_as_stride(w.ctx);
 			bo.text.reserve((size_t)f.res.n_records * 520);
@@ -295,6 +323,15 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 			else append_kam_checked(S, o, rec, dbt_record_as_stride(w.ctx), t);
 		};
 		auto tf = Clock::now();
+		if (S.bait_hits && ngpu) {
+			const uint32_t stride = dbt_record_stride(w.ctx);
+			for (uint64_t i = 0; i < ngpu; ++i) {
+				const uint8_t* rec = w.recs[s] + i * stride;
+				const uint64_t pi = reinterpret_cast<const dbt_pair_record*>(rec)->pair_index;
+				const uint64_t ord = f.first_pair + pi + (uint64_t)(std::lower_bound(f.ex.key.begin(), f.ex.key.end(), (uint64_t)ch->pair_offset[pi]) - f.ex.key.begin());
+				bait_track(S, rec, pair_text_raw(ch->text(), ch->pair_offset[pi], fq), ord, bo.bait_events);
+			}
+		}
 		if (!xb.npairs) {
 			if (S.want_records && ngpu) {
 				const uint32_t stride = dbt_record_stride(w.ctx);
@@ -342,6 +379,12 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 			if (!fetch_bubbles(S, w, s, xb.npairs, [&](uint64_t j) {
 				const uint64_t kj = f.ex.key[j];
 				return f.first_pair + j + (uint64_t)(kj > 0xFFFFFFFFull ? np_gpu : std::lower_bound(ch->pair_offset, ch->pair_offset + np_gpu, (uint32_t)kj) - ch->pair_offset); }, bo.events)) return false;
+			for (uint64_t j = 0; S.bait_hits && j < res2.n_records; ++j) {
+				const uint8_t* rec = recs2.data() + j * stride;
+				const uint64_t pj = reinterpret_cast<const dbt_pair_record*>(rec)->pair_index, kj = f.ex.key[pj];
+				const uint64_t ord = f.first_pair + pj + (uint64_t)(kj > 0xFFFFFFFFull ? np_gpu : std::lower_bound(ch->pair_offset, ch->pair_offset + np_gpu, (uint32_t)kj) - ch->pair_offset);
+				bait_track(S, rec, pair_text(xb, pj, fq), ord, bo.bait_events);
+			}
 			for (uint64_t j = 0; j < res2.n_records; ++j) {
 				const uint8_t* rec = recs2.data() + j * stride;
 				lines.emplace_back(f.ex.key[reinterpret_cast<const dbt_pair_record*>(rec)->pair_index], std::string());
@@ -434,7 +477,7 @@ int main(int argc, char** argv) {
 	std::string err = parse_args(argc, argv, o);
 	if (!err.empty()) { fprintf(stderr, "%s\n", err.c_str()); return 1; }
 	if (o.trPrefix.empty() || o.fastxFname.empty() || o.outPrefix.empty()) { fprintf(stderr, "-qs, -fa|-fq and -o|-on are required\n"); return 1; }
-	for (const char* unsupported : {o.bait ? "-b" : "", o.trackBait ? "-tb" : "",
+	for (const char* unsupported : {
 	                                o.g2pan ? "-m" : "", o.aug ? "-au" : "", o.trim ? "-t" : "", o.invkmer ? "-ik" : ""})
 		if (*unsupported) { fprintf(stderr, "option %s is not part of the B200 align path (SURVEY.md 8(f)); use the reference binary for it\n", unsupported); return 1; }
 	if (o.ksize < 1 || o.ksize > 27) { fprintf(stderr, "-k %llu unsupported (1..27)\n", (unsigned long long)o.ksize); return 1; }
@@ -474,6 +517,15 @@ int main(int argc, char** argv) {
 	}
 	if (o.extractFastX && S.thr_graph) { fprintf(stderr, "\n-e with a graph in the RPGG (restored threading) is outside the reference's behaviour; drop -g/-gc or the graph file\n"); return 1; }
 	if (o.extractFastX && o.extractFastX != 1 && o.extractFastX != 2) { fprintf(stderr, "\n-e takes 1 or 2\n"); return 1; }
+	if (o.trackBait && !o.bait) { fprintf(stderr, "\n-tb needs -b\n"); return 1; }
+	if (o.bait) {
+		if (S.thr_graph) { fprintf(stderr, "\n-b with a graph in the RPGG (restored threading): the reference filters baits only without threading\n"); return 1; }
+		if (o.isFastq) { fprintf(stderr, "\n-b with -fq (quality-masked bait histogram, qString2qMask) is not part of the B200 align path yet; use -fa\n"); return 1; }
+		if (o.extractFastX) { fprintf(stderr, "\n-b with -e: extraction stops before the bait filter\n"); return 1; }
+		if (!read_bait_kmdb(o.trPrefix + (o.qc ? ".qc" : "") + ".bt.kmdb", g.nloci, o.trackBait, S.baits, err)) { fprintf(stderr, "\n%s\n", err.c_str()); return 1; }
+		S.index.bt_n = S.baits.n.data(); S.index.bt_kmers = S.baits.kmers.data(); S.index.bt_vals = S.baits.vals.data();
+		if (o.trackBait) S.bait_hits.reset(new BubbleAcc(g.nloci, (uint64_t)(300000 * o.readsPerBatchFactor), 0, ".btk.kmdb"));
+	}
 	if (o.outputBubbles) {
 		if (S.thr_graph) { fprintf(stderr, "\n-bu with a graph in the RPGG (restored threading): the reference counts bubbles only without threading\n"); return 1; }
 		if (o.extractFastX) { fprintf(stderr, "\n-bu with -e: extraction counts nothing\n"); return 1; }
@@ -481,8 +533,8 @@ int main(int argc, char** argv) {
 		S.index.tre_n = S.rpgg.tre_n.data(); S.index.tre_kmers = S.rpgg.tre_kmers.data();
 		S.bubbles.reset(new BubbleAcc(g.nloci, (uint64_t)(300000 * o.readsPerBatchFactor)));
 	}
-	S.want_records = o.extractFastX ? true : (S.thr_graph ? o.aln : o.okam);
-	fprintf(stderr, "0 bait loci in baitDB\ndeserialized graph/index and read tr.kmers in %lld sec.\n# unique kmers in kmerDBi: %llu\n",
+	S.want_records = o.extractFastX ? true : (S.thr_graph ? o.aln : (o.okam || o.trackBait));
+	fprintf(stderr, "%llu bait loci in baitDB\ndeserialized graph/index and read tr.kmers in %lld sec.\n# unique kmers in kmerDBi: %llu\n", (unsigned long long)(o.bait ? g.nloci : 0),
 	        (long long)std::chrono::duration_cast<std::chrono::seconds>(std::chrono::steady_clock::now() - t_load).count(), (unsigned long long)g.dbi_keys.size());
 
 	// ---- batches ----
@@ -611,6 +663,7 @@ int main(int argc, char** argv) {
 		        (unsigned long long)c[DBT_C_NQCFILTERED], (unsigned long long)c[DBT_C_NTHREADINGREADS], (unsigned long long)c[DBT_C_NFEASIBLEREADS],
 		        (unsigned long long)c[DBT_C_NBAITFILTERED], (unsigned long long)c[DBT_C_NASGNREADS]);
 		if (S.bubbles) S.bubbles->replay(x.events);
+		if (S.bait_hits) S.bait_hits->replay(x.bait_events);
 		for (int i = 0; i < DBT_N_COUNTERS; ++i) tot[i] += c[i];
 		next_seq = x.index + 1;
 	};
@@ -688,6 +741,12 @@ int main(int argc, char** argv) {
 		uint64_t nskip = 0;
 		ok = S.bubbles->write(o.outPrefix, nskip, err);
 		fprintf(stderr, "# kmer skipped: %llu\nserializing %s.bub.kmdb\n", (unsigned long long)nskip, o.outPrefix.c_str());
+	}
+	if (ok && S.bait_hits) {                                                     // cpp:2652-2655
+		fprintf(stderr, "writing bait kmer hit statistics...\n");
+		uint64_t nskip = 0;
+		ok = S.bait_hits->write(o.outPrefix, nskip, err);
+		fprintf(stderr, "# kmer skipped: %llu\nserializing %s.btk.kmdb\n", (unsigned long long)nskip, o.outPrefix.c_str());
 	}
 	if (!ok) { fprintf(stderr, "danbing-tk: %s\n", err.c_str()); return 1; }
 	fprintf(stderr, "all done!\n");

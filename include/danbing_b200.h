@@ -55,6 +55,8 @@ extern "C" {
                                    caller prints them when the read name carries a source locus */
 #define DBT_F_BUBBLES    0x200u /* `-bu` (cpp:1559-1606): novel (k+1)-mer edges inside the observed TR segment of every kept mate of a counted
                                    pair are handed back as events (dbt_bubble_events); needs tre_n / tre_kmers in dbt_index; not with threading */
+#define DBT_F_BAIT       0x400u /* `-b` (cpp:1377-1396, 2110-2125), FASTA form: a pair is removed when a bait k-mer of its locus occurs in a mate fewer
+                                   than min or more than max times; needs bt_n / bt_kmers / bt_vals in dbt_index */
 #define DBT_F_EXTRACT    0x080u /* `-e 1|2` (cpp:2094-2099, 1618-1644): a pair that passes the locus vote and the QC gate is
                                    handed out as a record (status COUNTED, dst = its locus, no annotation) and NOTHING is counted */
 
@@ -155,6 +157,7 @@ typedef struct {
   const uint64_t* fl_n;   const uint64_t* fl_kmers;
   const uint8_t*  qc;
   const uint64_t* g_n;    const uint64_t* g_kmers;  const uint8_t* g_masks;
+  const uint64_t* bt_n;   const uint64_t* bt_kmers;  const uint16_t* bt_vals;   /* PREF[.qc].bt.kmdb: per-locus bait k-mers and (min << 8 | max), readBinaryBaitDB h:542-547; NULL unless DBT_F_BAIT */
   const uint64_t* tre_n;  const uint64_t* tre_kmers;  /* PREF.tre.kdb: per-locus TR (k+1)-mer edges (readBinaryKmerSetDB, h:675-698); NULL unless DBT_F_BUBBLES */
 } dbt_index;
 

@@ -307,3 +307,42 @@ def test_cli_vs_reference_live_bubbles(extra, tmp_path):
     nk = int(np.frombuffer(bub, "<u8", 1, 8 + 8 * nloci)[0])
     assert nk >= 10, "the input produced too few recurring novel edges to test anything"
     assert counters(a[1]) == counters(b[1])
+
+
+@needs_ref
+@pytest.mark.parametrize("track", [False, True], ids=["b", "b-tb"])
+def test_cli_vs_reference_live_bait_filter(track, tmp_path):
+    """`-b` (cpp:1377-1396, 2110-2125; FASTA form) and `-tb`: a bait file built by the reference's own `ktools serialize-bt`; pairs whose
+    mates hold a bait k-mer of the voted locus outside its [min, max] occurrence bounds are removed.  stdout, count files, counters and
+    (with -tb) OUT.btk.kmdb must equal the reference's (-p 1: its tracker merges batches in completion order otherwise)."""
+    pref, fa = stage_case("multi", tmp_path)
+    nloci = golden_case("multi")["ix"]["nloci"]
+    rng = random.Random(31)
+    per, l = [[] for _ in range(nloci)], -1
+    for line in open(pref + ".tr.kmers"):
+        if line[0] == ">":
+            l += 1
+        else:
+            per[l].append(int(line.split()[0]))
+    with open(tmp_path / "bait.txt", "w") as f:
+        for l in range(nloci):
+            f.write(f">{l}\n")
+            for km in rng.sample(per[l], min(len(per[l]), 40)):
+                mi, ma = rng.choice([(0, 0), (2, 255), (1, 255), (255, 0), (1, 1), (0, 3)])
+                f.write(f"{km}\t{mi}\t{ma}\n")
+    r = subprocess.run([ref_bin("ktools"), "serialize-bt", str(tmp_path / "bait.txt"), str(nloci), pref], capture_output=True)
+    assert r.returncode == 0, r.stderr
+    args = ["-k", 21, "-kf", 4, 1, "-cth", 30, "-b"] + (["-tb"] if track else []) + ["-p", 1, "-qs", pref, "-fa", fa]
+    for extra in ([], ["--batch-pairs", 300], ["--host-reader", "-r", 0.004]):
+        rflag = [x for x in extra if x in ("-r", 0.004)]
+        a = run_cli(CLI, args[:-4] + rflag + args[-4:] + [x for x in extra if x not in rflag] + ["-o", tmp_path / "gpu"], tmp_path)
+        b = run_cli(ref_bin("danbing-tk"), args[:-4] + rflag + args[-4:] + ["-o", tmp_path / "ref"], tmp_path)
+        assert a[0] == b[0]
+        assert open(tmp_path / "gpu.trkmc.ar", "rb").read() == open(tmp_path / "ref.trkmc.ar", "rb").read()
+        assert open(tmp_path / "gpu.tr.summary.txt").read() == open(tmp_path / "ref.tr.summary.txt").read()
+        ca, cb = counters(a[1]), counters(b[1])
+        assert ca == cb and ca["removed by bait locus"] > 20
+        if track:
+            btk = open(tmp_path / "ref.btk.kmdb", "rb").read()
+            assert open(tmp_path / "gpu.btk.kmdb", "rb").read() == btk
+            assert int(np.frombuffer(btk, "<u8", 1, 8 + 8 * nloci)[0]) >= 5
