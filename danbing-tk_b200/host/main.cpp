@@ -624,7 +624,8 @@ int main(int argc, char** argv) {
 			return;
 		}
 		FastxReader rd(o.isFastq, minlen, readsPerRefBatch);
-		if (!rd.open(o.fastxFname)) { S.fail("cannot open " + o.fastxFname); }
+		if (o.fastxFname.size() > 3 && o.fastxFname.compare(o.fastxFname.size() - 3, 3, ".gz") == 0) S.fail("--host-reader reads plain text only (the default reader inflates .gz)");
+		else if (!rd.open(o.fastxFname)) { S.fail("cannot open " + o.fastxFname); }
 		uint64_t first = 0, b = 0;
 		HostBatch* hb = nullptr;
 		while (!S.failed && recycle.pop(hb)) {

@@ -23,6 +23,7 @@
 #include <fcntl.h>
 #include <unistd.h>
 #include <sys/stat.h>
+#include <zlib.h>
 #include <algorithm>
 #include <thread>
 #if defined(__x86_64__)
@@ -72,12 +73,22 @@ class RawReader {
 public:
 	static constexpr uint64_t HEADROOM = 1 << 20;     // carried records are copied in front of the freshly read bytes
 	explicit RawReader(bool isFastq, int nthreads = 1) : L_(isFastq ? 4 : 2), nthreads_(std::max(1, nthreads)) {}
-	~RawReader() { if (fd_ > 0) close(fd_); }
+	~RawReader() { if (gz_) gzclose(gz_); else if (fd_ > 0) close(fd_); }
 	bool open(const std::string& fn) {
 		fd_ = ::open(fn.c_str(), O_RDONLY);
 		if (fd_ < 0) return false;
 		struct stat st;
 		if (fstat(fd_, &st) == 0 && S_ISREG(st.st_mode)) { regular_ = true; size_ = (uint64_t)st.st_size; }   // pipes / stdin: one sequential read
+		// gzip input (a convenience the reference does not have: its pipelines pipe `zcat` into /dev/stdin): a regular file that starts
+		// with the gzip magic, or any name ending in .gz, is inflated on the fly (zlib, one thread) and then treated like a pipe
+		unsigned char magic[2] = {0, 0};
+		const bool named_gz = fn.size() > 3 && fn.compare(fn.size() - 3, 3, ".gz") == 0;
+		if ((regular_ && pread(fd_, magic, 2, 0) == 2 && magic[0] == 0x1f && magic[1] == 0x8b) || named_gz) {
+			gz_ = gzdopen(fd_, "rb");
+			if (!gz_) return false;
+			gzbuffer(gz_, 1u << 20);
+			regular_ = false;
+		}
 		return true;
 	}
 	const std::string& error() const { return err_; }
@@ -117,8 +128,9 @@ public:
 			nl += count_nl(c.buf + start, HEADROOM - start);
 		} else {
 			while (have - HEADROOM < target && !src_eof_) {
-				const ssize_t r = ::read(fd_, c.buf + have, (size_t)std::min<uint64_t>(target - (have - HEADROOM), 1u << 30));
-				if (r < 0) { err_ = "read error"; done_ = true; return false; }
+				const size_t want = (size_t)std::min<uint64_t>(target - (have - HEADROOM), 1u << 30);
+				const ssize_t r = gz_ ? (ssize_t)gzread(gz_, c.buf + have, (unsigned)want) : ::read(fd_, c.buf + have, want);
+				if (r < 0) { err_ = gz_ ? "gzip read error (corrupt or truncated .gz?)" : "read error"; done_ = true; return false; }
 				if (r == 0) { src_eof_ = true; break; }
 				have += (uint64_t)r;
 			}
@@ -151,7 +163,7 @@ public:
 private:
 	uint32_t L_; int nthreads_;
 	bool regular_ = false; uint64_t size_ = 0, off_ = 0;
-	int fd_ = -1; bool src_eof_ = false, done_ = false;
+	int fd_ = -1; gzFile gz_ = nullptr; bool src_eof_ = false, done_ = false;
 	std::string carry_; uint64_t seq_ = 0;
 	std::string err_;
 

@@ -346,3 +346,21 @@ def test_cli_vs_reference_live_bait_filter(track, tmp_path):
             btk = open(tmp_path / "ref.btk.kmdb", "rb").read()
             assert open(tmp_path / "gpu.btk.kmdb", "rb").read() == btk
             assert int(np.frombuffer(btk, "<u8", 1, 8 + 8 * nloci)[0]) >= 5
+
+
+def test_cli_gzip_input_and_stdin(tmp_path):
+    """the GPU reader takes a gzip file (inflated on the fly) and a pipe on /dev/stdin like a plain file: same bytes"""
+    case = golden_case("multi")
+    run = case["meta"]["runs"]["cth45"]
+    pref, fa = stage_case("multi", tmp_path)
+    exp = golden_outputs(case, "cth45")
+    with open(fa, "rb") as f, gzip.open(str(tmp_path / "reads.fa.gz"), "wb") as o:
+        o.write(f.read())
+    out, err = run_cli(CLI, flags_of(run) + ["--batch-pairs", 700, "-qs", pref, "-fa", tmp_path / "reads.fa.gz", "-o", tmp_path / "gz"], tmp_path)
+    assert out.decode().splitlines() == exp["kam"]
+    assert np.array_equal(np.fromfile(tmp_path / "gz.trkmc.ar", "<u8")[1:], exp["trkmc"])
+    with open(fa, "rb") as f:
+        r = subprocess.run([CLI, *map(str, flags_of(run) + ["--batch-pairs", 700, "-qs", pref, "-fa", "/dev/stdin", "-o", tmp_path / "pipe"])], stdin=f, capture_output=True, cwd=tmp_path)
+    assert r.returncode == 0, r.stderr.decode()[-1000:]
+    assert r.stdout.decode().splitlines() == exp["kam"]
+    assert np.array_equal(np.fromfile(tmp_path / "pipe.trkmc.ar", "<u8")[1:], exp["trkmc"])

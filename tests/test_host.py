@@ -263,3 +263,19 @@ def test_raw_reader_parallel_pread(tmp_path):
     rng = random.Random(31)
     lines = make_fastx(rng, 30000, 0, False, 0)
     run_pair_raw(tmp_path, lines, 0, 300000, 5 << 20)
+
+
+def test_raw_reader_inflates_gzip(tmp_path):
+    """a .gz input (magic sniffed, or named *.gz) gives the same pairs as the plain text"""
+    rng = random.Random(77)
+    lines = make_fastx(rng, 3000, 1, True, 2)
+    exp, ndb = ref_pairing(lines, True, 55, 300000)
+    for name in ("reads.fq.gz", "reads.bin"):
+        fn = str(tmp_path / name)
+        with gzip.open(fn, "wt") as f:
+            f.write("\n".join(lines) + "\n")
+        r = run("pair-raw", fn, 1, 55, 300000, 40000)
+        assert r.returncode == 0, r.stderr
+        got = [tuple(l.split("\t")) for l in r.stdout.decode().split("\n")[:-1]]
+        assert got == [(t, s1, s2, q1, q2) for t, s1, s2, q1, q2 in exp]
+        assert r.stderr.decode().split()[:4] == ["reads", str(2 * len(exp)), "unpaired", str(ndb)]
