@@ -40,7 +40,7 @@ class Params(C.Structure):
                 ("cth", C.c_uint32), ("nm_tr", C.c_uint32), ("max_nt", C.c_uint32), ("thread_cth", C.c_uint32),
                 ("max_ncorrection", C.c_uint32), ("flags", C.c_uint32), ("max_read_len", C.c_uint32),
                 ("max_batch_pairs", C.c_uint32), ("max_records", C.c_uint32), ("table_load", C.c_float),
-                ("bucket_slots", C.c_uint32), ("reserved", C.c_uint32 * 3)]
+                ("bucket_slots", C.c_uint32), ("qth", C.c_uint32), ("reserved", C.c_uint32 * 2)]
 
 
 class Index(C.Structure):
@@ -52,7 +52,7 @@ class Index(C.Structure):
 
 class Batch(C.Structure):
     _fields_ = [("first_pair_index", C.c_uint64), ("npairs", C.c_uint64), ("layout", C.c_int32),
-                ("bases", u8p), ("offsets", u64p)]
+                ("bases", u8p), ("offsets", u64p), ("quals", u8p)]
 
 
 class RawInfo(C.Structure):
@@ -155,7 +155,7 @@ def default_params(k=21, cth=10, n_filter=4, nm_filter=1, nm_tr=40, flags=F_KAM,
     p = Params()
     p.device = device
     p.k, p.n_filter, p.nm_filter, p.cth, p.nm_tr, p.max_nt = k, n_filter, nm_filter, cth, nm_tr, 2
-    p.thread_cth, p.max_ncorrection = 100, 4
+    p.thread_cth, p.max_ncorrection, p.qth = 100, 4, 20
     p.flags = flags
     p.max_read_len = max_read_len
     p.max_batch_pairs = max_batch_pairs

@@ -645,7 +645,16 @@ __global__ void __launch_bounds__(CAND_WARPS_SLOW * 32, 4) candidate_kernel(DevI
 			}
 			if (status < 0 && ix.btable.slots) {                 // `-b`: bait filter (cpp:2110-2125): either mate removes the pair
 #pragma unroll 1
-				for (int m = 0; m < 2; ++m) if (bait_filtered<B>(ix.btable, pk + m * W64, WB, nk[m], K, dst, lane)) bf[m] = 1;
+				for (int m = 0; m < 2; ++m) {
+					uint32_t* qm = nullptr;
+					if (sv.qual) {                                  // FASTQ: the quality mask of the mate into the (spent) vote table
+						qm = lkey;
+						__syncwarp();
+						if (lane == 0) quality_mask(sv.qual + sv.qoff[2 * (uint64_t)p + m], (int)(nk[m] + K - 1), (int)K, (int)rp.qth, qm, MAXJ);
+						__syncwarp();
+					}
+					if (bait_filtered<B>(ix.btable, pk + m * W64, WB, nk[m], K, dst, lane, qm)) bf[m] = 1;
+				}
 				if (bf[0] | bf[1]) { if (lane == 0) c_bait += (bf[0] & !rm[0]) + (bf[1] & !rm[1]); rm[0] = rm[1] = 1; }
 			}
 			if (status < 0) {

@@ -389,7 +389,17 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, CANDF_MINBLOCKS) candida
 		uint32_t bfm = 0;                                        // bit m = bf[m]
 		if (status < 0 && ix.btable.slots) {                     // `-b`: bait filter (cpp:2110-2125): either mate removes the pair
 #pragma unroll 1
-			for (int m = 0; m < 2; ++m) if (bait_filtered<B>(ix.btable, W.pk + m * W64, WB, m ? nk1 : nk0, K, dst, lane)) bfm |= 1u << m;
+			for (int m = 0; m < 2; ++m) {
+				const uint32_t nkm = m ? nk1 : nk0;
+				uint32_t* qm = nullptr;
+				if (sv.qual) {                                      // FASTQ: the quality mask of the mate into the (free) probe staging area
+					qm = reinterpret_cast<uint32_t*>(&W.slot[0][0][0]);
+					__syncwarp();
+					if (lane == 0) quality_mask(sv.qual + sv.qoff[2 * (uint64_t)p + m], (int)(nkm + K - 1), (int)K, (int)rp.qth, qm, MAXJ);
+					__syncwarp();
+				}
+				if (bait_filtered<B>(ix.btable, W.pk + m * W64, WB, nkm, K, dst, lane, qm)) bfm |= 1u << m;
+			}
 			if (bfm) { if (lane == 0) c_bait += __popc(bfm & ~rmm); rmm = 3u; }
 		}
 		if (status < 0) {

@@ -61,7 +61,7 @@ extern "C" int dbt_device_count(void) {
 extern "C" void dbt_default_params(dbt_params* p) {
 	memset(p, 0, sizeof(*p));
 	p->device = 0; p->k = 21; p->n_filter = 4; p->nm_filter = 1; p->cth = 10; p->nm_tr = 40; p->max_nt = 2;   // cpp:26-33, 2338
-	p->thread_cth = 100; p->max_ncorrection = 4; p->flags = DBT_F_KAM;
+	p->thread_cth = 100; p->max_ncorrection = 4; p->flags = DBT_F_KAM; p->qth = 20;
 	p->max_read_len = 150; p->max_batch_pairs = 1u << 20; p->max_records = 0; p->table_load = 0.f; p->bucket_slots = 0;
 }
 
@@ -95,7 +95,9 @@ struct Slot {
 	uint32_t *d_nlmask = nullptr, *d_rblocksum = nullptr, *d_nl = nullptr, *d_rhdr = nullptr, *d_tlen = nullptr, *d_slen = nullptr;
 	uint64_t* d_rhash = nullptr; uint8_t* d_eq = nullptr;
 	uint32_t *d_pairmask = nullptr, *d_singlemask = nullptr, *d_pairlist = nullptr, *d_singlelist = nullptr, *d_pairoff = nullptr, *d_singleoff = nullptr;
-	uint64_t *d_rstart = nullptr, *d_rend = nullptr, *d_pairhash = nullptr;
+	uint64_t *d_rstart = nullptr, *d_rend = nullptr, *d_pairhash = nullptr, *d_rqual = nullptr;
+	uint8_t* d_qual = nullptr;               // quality strings of an ASCII batch (`-b` with FASTQ)
+	const uint8_t* q_base = nullptr; const uint64_t* q_off = nullptr;      // where the current batch's qualities are (nullptr: none)
 	uint32_t raw_max_lines = 0, raw_max_recs = 0, raw_max_single = 0;
 	uint32_t* h_rhdr = nullptr;              // pinned: dbt_raw_info
 	cudaEvent_t evr0 = nullptr, evr1 = nullptr;
@@ -194,7 +196,7 @@ extern "C" int dbt_create(dbt_ctx** out, const dbt_params* p) {
 
 	RunParams& rp = c->rp;
 	rp.k = p->k; rp.n_filter = p->n_filter; rp.nm_filter = p->nm_filter; rp.cth = p->cth; rp.nm_tr = p->nm_tr; rp.max_nt = c->p.max_nt;
-	rp.flags = p->flags;
+	rp.flags = p->flags; rp.qth = p->qth;
 	rp.lay = make_layout(p->max_read_len);
 	rp.max_read_len = p->max_read_len;
 	rp.nk_max = p->max_read_len - p->k + 1;
@@ -246,7 +248,7 @@ static void free_slot(Slot& s) {
 	cudaFree(s.d_records_out); cudaFree(s.d_emitmask); cudaFree(s.d_emitsum); cudaFree(s.d_emitlist); cudaFree(s.d_nemit);
 	cudaFree(s.d_raw); cudaFree(s.d_nlmask); cudaFree(s.d_rblocksum); cudaFree(s.d_nl); cudaFree(s.d_rhdr); cudaFree(s.d_tlen); cudaFree(s.d_slen);
 	cudaFree(s.d_rhash); cudaFree(s.d_eq); cudaFree(s.d_pairmask); cudaFree(s.d_singlemask); cudaFree(s.d_pairlist); cudaFree(s.d_singlelist);
-	cudaFree(s.d_pairoff); cudaFree(s.d_singleoff); cudaFree(s.d_rstart); cudaFree(s.d_rend); cudaFree(s.d_pairhash);
+	cudaFree(s.d_pairoff); cudaFree(s.d_singleoff); cudaFree(s.d_rstart); cudaFree(s.d_rend); cudaFree(s.d_pairhash); cudaFree(s.d_rqual); cudaFree(s.d_qual);
 	cudaFree(s.d_evkey); cudaFree(s.d_evedge); cudaFree(s.d_evlocus); cudaFree(s.d_nev);
 	if (s.h_nev) cudaFreeHost(s.h_nev);
 	if (s.h_rhdr) cudaFreeHost(s.h_rhdr);
@@ -702,6 +704,7 @@ static SlotView slot_view(const dbt_ctx* c, const Slot& s) {
 	v.packed[0] = s.d_packed[0]; v.packed[1] = s.d_packed[1]; v.meta[0] = s.d_meta[0]; v.meta[1] = s.d_meta[1];
 	v.passmask = s.d_passmask; v.blocksum = s.d_blocksum; v.cand = s.d_cand; v.ncand = s.d_ncand; v.slow = s.d_slow; v.thr = s.d_thr; v.thr2 = s.d_thr2; v.records = s.d_records;
 	v.counters = s.d_counters; v.npairs = s.npairs; v.first_pair_index = s.first_pair_index;
+	v.qual = s.q_base; v.qoff = s.q_off;
 	(void)c;
 	return v;
 }
@@ -729,6 +732,7 @@ extern "C" int dbt_upload(dbt_ctx* c, const dbt_batch* b, int slot) {
 	if (s.fetch_pending) return fail(DBT_E_STATE, "slot %d has an unfinished fetch; call dbt_wait", slot);
 	if (b->npairs > c->p.max_batch_pairs) return fail(DBT_E_CAPACITY, "npairs=%llu > max_batch_pairs=%u", (unsigned long long)b->npairs, c->p.max_batch_pairs);
 	s.npairs = b->npairs; s.first_pair_index = b->first_pair_index; s.processed = false; s.ev_pack = false;
+	s.q_base = nullptr; s.q_off = nullptr;
 	const RunParams& rp = c->rp;
 	CU(cudaMemsetAsync(s.d_ncand, 0, 32, s.st));
 	if (b->npairs) {
@@ -743,6 +747,11 @@ extern "C" int dbt_upload(dbt_ctx* c, const dbt_batch* b, int slot) {
 			}
 			CU(cudaMemcpyAsync(s.d_ascii, b->bases + b->offsets[0], nbytes, cudaMemcpyHostToDevice, s.st));
 			CU(cudaMemcpyAsync(s.d_offsets, b->offsets, (2 * b->npairs + 1) * 8, cudaMemcpyHostToDevice, s.st));
+			if (b->quals && (c->p.flags & DBT_F_BAIT)) {            // quality strings, laid out like the bases
+				if (!s.d_qual) TRY(dev_alloc(&s.d_qual, (size_t)2 * c->p.max_batch_pairs * rp.max_read_len + 16, "qualities"));
+				CU(cudaMemcpyAsync(s.d_qual, b->quals + b->offsets[0], nbytes, cudaMemcpyHostToDevice, s.st));
+				s.q_base = s.d_qual - b->offsets[0]; s.q_off = s.d_offsets;
+			}
 			// offsets are used relative to bases: shift by offsets[0] inside the kernel via pointer arithmetic
 			CU(cudaEventRecord(s.evp0, s.st));
 			CU(launch_pack(s.st, s.d_ascii - b->offsets[0], s.d_offsets, s.d_offsets + 1, b->npairs, rp, 0, s.d_packed[0], s.d_packed[1], s.d_meta[0], s.d_meta[1], s.d_ncand + 1)); ++c->launches;
@@ -770,7 +779,7 @@ static int ensure_raw(dbt_ctx* c, Slot& s, uint64_t nbytes) {
 		CU(cudaEventCreate(&s.evr0)); CU(cudaEventCreate(&s.evr1));
 		TRY(dev_alloc(&s.d_rhdr, 16, "raw header"));
 		const uint64_t P = c->p.max_batch_pairs;
-		TRY(dev_alloc(&s.d_rstart, 2 * P, "raw read starts")); TRY(dev_alloc(&s.d_rend, 2 * P, "raw read ends"));
+		TRY(dev_alloc(&s.d_rstart, 2 * P, "raw read starts")); TRY(dev_alloc(&s.d_rend, 2 * P, "raw read ends")); TRY(dev_alloc(&s.d_rqual, 2 * P, "raw quality starts"));
 		TRY(dev_alloc(&s.d_pairoff, P, "raw pair offsets")); TRY(dev_alloc(&s.d_pairhash, P, "raw pair hashes"));
 		s.raw_max_single = (uint32_t)std::min<uint64_t>(std::max<uint64_t>(P / 8, 1024), 1u << 22);
 		TRY(dev_alloc(&s.d_singleoff, s.raw_max_single, "raw singleton offsets"));
@@ -819,6 +828,7 @@ extern "C" int dbt_upload_raw(dbt_ctx* c, const dbt_raw_batch* b, dbt_raw_info* 
 	if (s.fetch_pending) return fail(DBT_E_STATE, "slot %d has an unfinished fetch; call dbt_wait", slot);
 	memset(info, 0, sizeof *info);
 	s.uploaded = false; s.processed = false; s.ev_pack = false; s.ev_raw = false; s.npairs = 0; s.first_pair_index = b->first_pair_index;
+	s.q_base = nullptr; s.q_off = nullptr;
 	if (b->nbytes >= (1ull << 32) - 64) return fail(DBT_E_CAPACITY, "raw text of %llu bytes: a batch must stay below 4 GiB", (unsigned long long)b->nbytes);
 	if (b->nbytes && (!b->text || b->text[b->nbytes - 1] != '\n')) return fail(DBT_E_BADARG, "raw text must hold whole lines (last byte '\\n')");
 	CU(cudaMemsetAsync(s.d_ncand, 0, 32, s.st));
@@ -829,8 +839,9 @@ extern "C" int dbt_upload_raw(dbt_ctx* c, const dbt_raw_batch* b, dbt_raw_info* 
 	RawView v{};
 	v.raw = s.d_raw; v.nlmask = s.d_nlmask; v.blocksum = s.d_rblocksum; v.nl = s.d_nl; v.hdr = s.d_rhdr; v.hash = s.d_rhash; v.tlen = s.d_tlen; v.slen = s.d_slen; v.eq = s.d_eq;
 	v.pairmask = s.d_pairmask; v.singlemask = s.d_singlemask; v.pairlist = s.d_pairlist; v.singlelist = s.d_singlelist;
-	v.rstart = s.d_rstart; v.rend = s.d_rend; v.pairoff = s.d_pairoff; v.pairhash = s.d_pairhash; v.singleoff = s.d_singleoff;
+	v.rstart = s.d_rstart; v.rend = s.d_rend; v.rqual = s.d_rqual; v.pairoff = s.d_pairoff; v.pairhash = s.d_pairhash; v.singleoff = s.d_singleoff;
 	v.max_lines = s.raw_max_lines; v.max_recs = s.raw_max_recs; v.max_pairs = c->p.max_batch_pairs; v.max_single = std::min(s.raw_max_single, b->single_cap);
+	if (b->is_fastq && (c->p.flags & DBT_F_BAIT)) { s.q_base = s.d_raw; s.q_off = s.d_rqual; }
 	CU(cudaEventRecord(s.evr0, s.st));
 	CU(cudaMemcpyAsync(s.d_raw, b->text, b->nbytes, cudaMemcpyHostToDevice, s.st));
 	CU(cudaMemsetAsync(s.d_raw + b->nbytes, 0, 64 + (32 - b->nbytes % 32) % 32, s.st));      // nl_mask_kernel reads 32-byte words, pack_kernel stages 16-byte words

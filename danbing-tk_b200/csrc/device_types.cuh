@@ -53,6 +53,7 @@ struct RunParams {
 	uint32_t thr_on;            // 1 = hand candidates to thread_kernel instead of the HEAD no-op
 	uint32_t thread_cth, max_ncorrection, correction;
 	uint32_t es_cap, tr_cap, aln_stride;   // record blob geometry (include/danbing_b200.h, dbt_aln_mate)
+	uint32_t qth;               // `-qth`
 };
 
 // one in-flight batch
@@ -71,6 +72,8 @@ struct SlotView {
 	uint8_t*  records;
 	unsigned long long* counters;   // DBT_N_COUNTERS
 	uint64_t npairs, first_pair_index;
+	const uint8_t*  qual;       // phred+33 quality strings (FASTQ + `-b`), or nullptr: read r (2 * pair + mate) starts at qual[qoff[r]]
+	const uint64_t* qoff;
 };
 
 // device buffers of the raw FASTA/FASTQ splitter (fastx.cu), one set per slot
@@ -83,6 +86,7 @@ struct RawView {
 	uint64_t* hash; uint32_t* tlen; uint32_t* slen; uint8_t* eq;       // per record (max_recs, eq: +2)
 	uint32_t* pairmask; uint32_t* singlemask; uint32_t* pairlist; uint32_t* singlelist;
 	uint64_t* rstart; uint64_t* rend;                                   // per read of the pairs formed: [start, end) of the sequence in raw
+	uint64_t* rqual;                                                    // ... and, FASTQ, the start of its quality line
 	uint32_t* pairoff; uint64_t* pairhash; uint32_t* singleoff;
 	uint32_t max_lines, max_recs, max_pairs, max_single;
 };

@@ -61,13 +61,48 @@ inline void canonical_kmers(const char* s, size_t len, uint32_t k, std::vector<u
 	}
 }
 
-// the k-mer bfilter_FPSv1 stops at (cpp:1386-1393); false when none is out of bounds
-inline bool first_bait_violation(const std::unordered_map<uint64_t, uint16_t>& baitdb, const char* seq, size_t len, uint32_t k, uint64_t& km_out) {
+// qString2qMask (src/aQueryFasta_thread.h:1038-1071): which k-mers of a FASTQ read enter the bait histogram -- those whose k bases all
+// have phred >= qth, as far as the reference's scan gets (its base index is bounded by the NUMBER OF K-MERS, so it stops k-1 bases
+// before the end of the read).  Same state machine as quality_mask in csrc/bait.cuh.
+inline void quality_mask(const char* q, size_t nq_, int k, int qth, std::vector<bool>& m) {
+	const int nq = (int)nq_, nk = nq - k + 1;
+	m.assign(nk > 0 ? nk : 0, false);
+	if (nk < 1) return;
+	auto lowq = [&](int i) { return (int)q[i] - 33 < qth; };
+	int qi = 0, ki = 0;
+	while (lowq(qi)) { ++qi; ++ki; if (qi >= nk) return; }
+	while (qi < nk) {
+		bool pass = true;
+		for (const int qj = qi; qi < qj + k; ++qi) {
+			if (lowq(qi)) {
+				pass = false; ki = qi;
+				while (lowq(qi)) { ++qi; ++ki; if (qi >= nk) return; }
+				break;
+			}
+		}
+		if (pass) {
+			m[ki] = true; ++ki;
+			if (qi >= nk) return;
+			while (!lowq(qi)) { m[ki] = true; ++qi; ++ki; if (qi >= nk) return; }
+			ki = qi;
+			while (lowq(qi)) { ++qi; ++ki; if (qi >= nk) return; }
+		}
+	}
+}
+
+// the k-mer bfilter_FPSv1 stops at (cpp:1386-1393; with a quality string, the masked form cpp:1398-1419); false when none is out of bounds
+inline bool first_bait_violation(const std::unordered_map<uint64_t, uint16_t>& baitdb, const char* seq, size_t len, uint32_t k, uint64_t& km_out,
+                                 const char* qual = nullptr, int qth = 20) {
 	std::vector<uint64_t> ks;
 	canonical_kmers(seq, len, k, ks);
 	if (ks.empty()) return false;
 	std::unordered_map<uint64_t, uint8_t> kc;                              // kc8_t
-	for (uint64_t km : ks) ++kc[km];
+	if (qual) {
+		std::vector<bool> m;
+		quality_mask(qual, len, (int)k, qth, m);
+		for (size_t i = 0; i < ks.size(); ++i) if (m[i]) ++kc[ks[i]];
+	} else
+		for (uint64_t km : ks) ++kc[km];
 	for (auto& p : kc) {
 		auto it = baitdb.find(p.first);
 		if (it == baitdb.end()) continue;

@@ -10,6 +10,7 @@
 #include <string>
 #include <vector>
 #include "options.hpp"
+#include "bait.hpp"
 #include "serialize.hpp"
 #include "fastx_reader.hpp"
 #include "kam_writer.hpp"
@@ -175,6 +176,17 @@ int main(int argc, char** argv) {
 	if (cmd == "pair-raw" && argc == 7) return cmd_pair_raw(argv[2], atoi(argv[3]) != 0, strtoull(argv[4], nullptr, 10), strtoull(argv[5], nullptr, 10), strtoull(argv[6], nullptr, 10));
 	if (cmd == "pair" && argc == 7) return cmd_pair(argv[2], atoi(argv[3]) != 0, strtoull(argv[4], nullptr, 10), strtoull(argv[5], nullptr, 10), strtoull(argv[6], nullptr, 10));
 	if (cmd == "kam" && argc == 8) return cmd_kam(argv[2], (uint32_t)atoi(argv[3]), (uint32_t)atoi(argv[4]), argv[5], atoi(argv[6]) != 0, strtoull(argv[7], nullptr, 10));
+	if (cmd == "qmask" && argc == 4) {                      // stdin: one quality string per line -> the bait histogram's k-mer mask as 0/1
+		std::string line; std::vector<bool> m;
+		char buf[1 << 16];
+		while (fgets(buf, sizeof buf, stdin)) {
+			size_t n = strlen(buf); while (n && (buf[n - 1] == '\n' || buf[n - 1] == '\r')) --n;
+			quality_mask(buf, n, atoi(argv[2]), atoi(argv[3]), m);
+			line.clear(); for (bool x : m) line.push_back(x ? '1' : '0');
+			puts(line.c_str());
+		}
+		return 0;
+	}
 	if (cmd == "args") return cmd_args(argc - 1, argv + 1);
 	fprintf(stderr, "bad arguments\n");
 	return 2;

@@ -142,6 +142,13 @@ bool fetch_bubbles(Shared& S, Worker& w, int slot, uint64_t npairs, F&& ordinal,
 	return true;
 }
 
+// `-b` with FASTQ: the batch's quality strings ride along, laid out like the bases (one phred score per base)
+bool batch_quals(const HostBatch& hb, dbt_batch& b) {
+	if (hb.qual_off.size() != 2 * hb.npairs + 1 || memcmp(hb.qual_off.data(), hb.offsets, (2 * hb.npairs + 1) * 8) != 0) return false;
+	b.quals = reinterpret_cast<const uint8_t*>(hb.quals.data());
+	return true;
+}
+
 // `-tb`: for every mate of this record that the bait filter removed, the bait k-mer bfilter_FPSv1 stopped at (host/bait.hpp)
 void bait_track(Shared& S, const uint8_t* rec, const PairText& t, uint64_t ordinal, std::vector<BubbleEvent>& out) {
 	const dbt_pair_record* h = reinterpret_cast<const dbt_pair_record*>(rec);
@@ -149,7 +156,7 @@ void bait_track(Shared& S, const uint8_t* rec, const PairText& t, uint64_t ordin
 	for (int m = 0; m < 2; ++m) {
 		if (!(h->mate[m].flags & DBT_MF_BF)) continue;
 		uint64_t km = 0;
-		if (first_bait_violation(S.baits.per_locus[h->dst0], t.seq[m], t.seq_len[m], (uint32_t)S.opt.ksize, km))
+		if (first_bait_violation(S.baits.per_locus[h->dst0], t.seq[m], t.seq_len[m], (uint32_t)S.opt.ksize, km, S.opt.isFastq ? t.qual[m] : nullptr, (int)S.opt.qth))
 			out.push_back(BubbleEvent{(ordinal << 10) | ((uint64_t)m << 9), km, h->dst0});
 	}
 }
@@ -163,7 +170,7 @@ bool make_ctx(Shared& S, Worker& w, uint32_t max_len) {
 	p.flags = (o.extractFastX ? DBT_F_EXTRACT : ((o.okam || o.trackBait) ? DBT_F_KAM : 0)) | ((o.simmode || o.trackBait) ? DBT_F_SIM : 0) | (o.outputBubbles ? DBT_F_BUBBLES : 0) |
 	          (o.bait ? DBT_F_BAIT : 0) | (o.qc ? DBT_F_QC : 0) | (o.threading ? DBT_F_THREADING : 0) | (o.threading && o.correction ? DBT_F_CORRECTION : 0) |
 	          (o.aln ? DBT_F_ALN : 0) | (o.aln_minimal ? DBT_F_ALN_MIN : 0);
-	p.max_read_len = max_len; p.max_batch_pairs = (uint32_t)S.batch_pairs; p.max_records = (uint32_t)S.batch_pairs;
+	p.qth = (uint32_t)o.qth; p.max_read_len = max_len; p.max_batch_pairs = (uint32_t)S.batch_pairs; p.max_records = (uint32_t)S.batch_pairs;
 	p.table_load = o.table_load; p.bucket_slots = o.bucket_slots;
 	int rc = dbt_create(&w.ctx, &p);
 	if (rc) { S.fail(dbt_err("dbt_create", rc)); return false; }
@@ -257,6 +264,7 @@ void worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<HostBatch
 		f.res.capacity = S.want_records ? S.batch_pairs : 0; f.res.records = S.want_records ? f.recs.data() : nullptr;
 		dbt_batch b{};
 		b.first_pair_index = hb->first_pair_index; b.npairs = hb->npairs; b.layout = DBT_LAYOUT_ASCII; b.bases = hb->bases; b.offsets = hb->offsets;
+		if (S.opt.bait && S.opt.isFastq && !batch_quals(*hb, b)) { S.fail("a FASTQ record whose quality string is not as long as its sequence (-b needs one phred score per base)"); break; }
 		int rc = dbt_submit(w.ctx, &b, &f.res, s);
 		if (rc) { S.fail(dbt_err("dbt_submit", rc)); break; }
 	}
@@ -371,6 +379,7 @@ void raw_worker_main(Shared& S, Worker& w, Channel<BatchOut>& out, Channel<RawCh
 			res2.capacity = S.want_records ? xb.npairs : 0; res2.records = S.want_records ? recs2.data() : nullptr;
 			dbt_batch b{};
 			b.first_pair_index = 0; b.npairs = xb.npairs; b.layout = DBT_LAYOUT_ASCII; b.bases = xb.bases; b.offsets = xb.offsets;
+			if (S.opt.bait && fq && !batch_quals(xb, b)) { S.fail("a FASTQ record whose quality string is not as long as its sequence (-b needs one phred score per base)"); return false; }
 			int rc = dbt_submit(w.ctx, &b, &res2, s);
 			if (!rc) rc = dbt_wait(w.ctx, s);
 			if (rc) { S.fail(dbt_err("dbt_submit (host-paired reads)", rc)); return false; }
@@ -520,7 +529,6 @@ int main(int argc, char** argv) {
 	if (o.trackBait && !o.bait) { fprintf(stderr, "\n-tb needs -b\n"); return 1; }
 	if (o.bait) {
 		if (S.thr_graph) { fprintf(stderr, "\n-b with a graph in the RPGG (restored threading): the reference filters baits only without threading\n"); return 1; }
-		if (o.isFastq) { fprintf(stderr, "\n-b with -fq (quality-masked bait histogram, qString2qMask) is not part of the B200 align path yet; use -fa\n"); return 1; }
 		if (o.extractFastX) { fprintf(stderr, "\n-b with -e: extraction stops before the bait filter\n"); return 1; }
 		if (!read_bait_kmdb(o.trPrefix + (o.qc ? ".qc" : "") + ".bt.kmdb", g.nloci, o.trackBait, S.baits, err)) { fprintf(stderr, "\n%s\n", err.c_str()); return 1; }
 		S.index.bt_n = S.baits.n.data(); S.index.bt_kmers = S.baits.kmers.data(); S.index.bt_vals = S.baits.vals.data();

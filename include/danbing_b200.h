@@ -55,7 +55,7 @@ extern "C" {
                                    caller prints them when the read name carries a source locus */
 #define DBT_F_BUBBLES    0x200u /* `-bu` (cpp:1559-1606): novel (k+1)-mer edges inside the observed TR segment of every kept mate of a counted
                                    pair are handed back as events (dbt_bubble_events); needs tre_n / tre_kmers in dbt_index; not with threading */
-#define DBT_F_BAIT       0x400u /* `-b` (cpp:1377-1396, 2110-2125), FASTA form: a pair is removed when a bait k-mer of its locus occurs in a mate fewer
+#define DBT_F_BAIT       0x400u /* `-b` (cpp:1377-1419, 2110-2125; with qualities in the batch the quality-masked form): a pair is removed when a bait k-mer of its locus occurs in a mate fewer
                                    than min or more than max times; needs bt_n / bt_kmers / bt_vals in dbt_index */
 #define DBT_F_EXTRACT    0x080u /* `-e 1|2` (cpp:2094-2099, 1618-1644): a pair that passes the locus vote and the QC gate is
                                    handed out as a record (status COUNTED, dst = its locus, no annotation) and NOTHING is counted */
@@ -132,7 +132,9 @@ typedef struct {
   uint32_t max_records;        /* record buffer capacity per slot; 0 = max_batch_pairs          */
   float    table_load;         /* hash table load factor; 0 = default                           */
   uint32_t bucket_slots;       /* 16-byte slots per probe bucket: 2 (one 32 B sector) or 4; 0 = default (2) */
-  uint32_t reserved[3];
+  uint32_t qth;                /* `-qth` [20]: with DBT_F_BAIT and qualities in the batch, only k-mers whose bases all have phred >= qth enter
+                                  the bait histogram (qString2qMask, h:1038-1071) */
+  uint32_t reserved[2];
 } dbt_params;
 
 /*
@@ -177,6 +179,7 @@ typedef struct {
   int32_t  layout;
   const uint8_t*  bases;
   const uint64_t* offsets;
+  const uint8_t*  quals;       /* ASCII layout only, may be NULL: phred+33 quality strings laid out like `bases` (same offsets); used by DBT_F_BAIT */
 } dbt_batch;
 
 /* per-mate part of a record == km_asgn_read_t (cpp:93-108) */

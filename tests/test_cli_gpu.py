@@ -310,12 +310,32 @@ def test_cli_vs_reference_live_bubbles(extra, tmp_path):
 
 
 @needs_ref
+@pytest.mark.parametrize("is_fastq", [False, True], ids=["fa", "fq"])
 @pytest.mark.parametrize("track", [False, True], ids=["b", "b-tb"])
-def test_cli_vs_reference_live_bait_filter(track, tmp_path):
-    """`-b` (cpp:1377-1396, 2110-2125; FASTA form) and `-tb`: a bait file built by the reference's own `ktools serialize-bt`; pairs whose
-    mates hold a bait k-mer of the voted locus outside its [min, max] occurrence bounds are removed.  stdout, count files, counters and
-    (with -tb) OUT.btk.kmdb must equal the reference's (-p 1: its tracker merges batches in completion order otherwise)."""
+def test_cli_vs_reference_live_bait_filter(track, is_fastq, tmp_path):
+    """`-b` (cpp:1377-1419, 2110-2125) and `-tb`: a bait file built by the reference's own `ktools serialize-bt`; pairs whose
+    mates hold a bait k-mer of the voted locus outside its [min, max] occurrence bounds are removed.  With FASTQ only k-mers whose
+    bases all reach `-qth` count (qString2qMask, h:1038-1071; qualities here have low runs at the ends and inside the reads).  stdout,
+    count files, counters and (with -tb) OUT.btk.kmdb must equal the reference's (-p 1: its tracker merges batches in completion
+    order otherwise)."""
     pref, fa = stage_case("multi", tmp_path)
+    if is_fastq:
+        qrng = random.Random(77)
+
+        def quality(n):
+            q = [qrng.choice("FGHI:5") for _ in range(n)]
+            for _ in range(qrng.randrange(4)):                 # a few low-quality stretches, anywhere incl. both ends
+                o, w = qrng.randrange(n), qrng.randrange(1, 12)
+                q[o:o + w] = [qrng.choice("#,+4") for _ in q[o:o + w]]
+            if qrng.random() < 0.02:
+                q = ["#"] * n
+            return "".join(q)
+        fq = tmp_path / "reads_b.fq"
+        lines = open(fa).read().split("\n")[:-1]
+        with open(fq, "w") as f:
+            for t, sq in zip(lines[0::2], lines[1::2]):
+                f.write("@" + t[1:] + "\n" + sq + "\n+\n" + quality(len(sq)) + "\n")
+        fa = fq
     nloci = golden_case("multi")["ix"]["nloci"]
     rng = random.Random(31)
     per, l = [[] for _ in range(nloci)], -1
@@ -332,7 +352,7 @@ def test_cli_vs_reference_live_bait_filter(track, tmp_path):
                 f.write(f"{km}\t{mi}\t{ma}\n")
     r = subprocess.run([ref_bin("ktools"), "serialize-bt", str(tmp_path / "bait.txt"), str(nloci), pref], capture_output=True)
     assert r.returncode == 0, r.stderr
-    args = ["-k", 21, "-kf", 4, 1, "-cth", 30, "-b"] + (["-tb"] if track else []) + ["-p", 1, "-qs", pref, "-fa", fa]
+    args = ["-k", 21, "-kf", 4, 1, "-cth", 30, "-b"] + (["-tb"] if track else []) + (["-qth", 21] if is_fastq else []) + ["-p", 1, "-qs", pref, "-fq" if is_fastq else "-fa", fa]
     for extra in ([], ["--batch-pairs", 300], ["--host-reader", "-r", 0.004]):
         rflag = [x for x in extra if x in ("-r", 0.004)]
         a = run_cli(CLI, args[:-4] + rflag + args[-4:] + [x for x in extra if x not in rflag] + ["-o", tmp_path / "gpu"], tmp_path)
@@ -359,8 +379,8 @@ def test_cli_gzip_input_and_stdin(tmp_path):
     out, err = run_cli(CLI, flags_of(run) + ["--batch-pairs", 700, "-qs", pref, "-fa", tmp_path / "reads.fa.gz", "-o", tmp_path / "gz"], tmp_path)
     assert out.decode().splitlines() == exp["kam"]
     assert np.array_equal(np.fromfile(tmp_path / "gz.trkmc.ar", "<u8")[1:], exp["trkmc"])
-    with open(fa, "rb") as f:
-        r = subprocess.run([CLI, *map(str, flags_of(run) + ["--batch-pairs", 700, "-qs", pref, "-fa", "/dev/stdin", "-o", tmp_path / "pipe"])], stdin=f, capture_output=True, cwd=tmp_path)
+    r = subprocess.run([CLI, *map(str, flags_of(run) + ["--batch-pairs", 700, "-qs", pref, "-fa", "/dev/stdin", "-o", tmp_path / "pipe"])],
+                       input=open(fa, "rb").read(), capture_output=True, cwd=tmp_path)
     assert r.returncode == 0, r.stderr.decode()[-1000:]
     assert r.stdout.decode().splitlines() == exp["kam"]
     assert np.array_equal(np.fromfile(tmp_path / "pipe.trkmc.ar", "<u8")[1:], exp["trkmc"])

@@ -279,3 +279,79 @@ def test_raw_reader_inflates_gzip(tmp_path):
         got = [tuple(l.split("\t")) for l in r.stdout.decode().split("\n")[:-1]]
         assert got == [(t, s1, s2, q1, q2) for t, s1, s2, q1, q2 in exp]
         assert r.stderr.decode().split()[:4] == ["reads", str(2 * len(exp)), "unpaired", str(ndb)]
+
+
+def ref_qmask(qual, qth, k):
+    """qString2qMask restated (src/aQueryFasta_thread.h:1038-1071): the scan's base index is bounded by the number of k-mers"""
+    nq = len(qual)
+    nk = nq - k + 1
+    qs = [ord(c) - 33 for c in qual]
+    m = [False] * max(nk, 0)
+    if nk < 1:
+        return m
+    qi = ki = 0
+    while qs[qi] < qth:
+        qi += 1
+        ki += 1
+        if qi >= nk:
+            return m
+    while qi < nk:
+        ok = True
+        qj = qi
+        while qi < qj + k:
+            if qs[qi] < qth:
+                ok = False
+                ki = qi
+                while qs[qi] < qth:
+                    qi += 1
+                    ki += 1
+                    if qi >= nk:
+                        return m
+                break
+            qi += 1
+        if ok:
+            m[ki] = True
+            ki += 1
+            if qi >= nk:
+                return m
+            while qs[qi] >= qth:
+                m[ki] = True
+                qi += 1
+                ki += 1
+                if qi >= nk:
+                    return m
+            ki = qi
+            while qs[qi] < qth:
+                qi += 1
+                ki += 1
+                if qi >= nk:
+                    return m
+    return m
+
+
+def test_quality_mask_matches_the_reference_scan():
+    """`-b` with FASTQ: host/bait.hpp quality_mask (the device's quality_mask in csrc/bait.cuh is the same state machine, checked
+    against the live reference in tests/test_cli_gpu.py) against the restated qString2qMask, incl. its early stop k-1 bases
+    before the end of the read"""
+    rng = random.Random(5)
+    quals = []
+    for n in [21, 22, 40, 41, 42, 63, 100, 150, 151, 250]:
+        for _ in range(40):
+            q = [rng.choice("FGHI5") for _ in range(n)]
+            for _ in range(rng.randrange(5)):
+                o, w = rng.randrange(n), rng.randrange(1, 25)
+                q[o:o + w] = [rng.choice("#,+4") for _ in q[o:o + w]]
+            quals.append("".join(q))
+        quals += ["#" * n, "I" * n, "#" + "I" * (n - 1), "I" * (n - 1) + "#"]
+    r = subprocess.run([HOSTCHECK, "qmask", "21", "20"], input="\n".join(quals) + "\n", capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    got = r.stdout.split("\n")[:-1]
+    assert len(got) == len(quals)
+    nset = 0
+    for q, g in zip(quals, got):
+        e = "".join("1" if x else "0" for x in ref_qmask(q, 20, 21))
+        assert g == e, q
+        nset += e.count("1")
+    assert nset > 1000
+    # the all-high read of 150 bases (130 k-mers): the scan stops k-1 bases early, so the last k-1 k-mers stay out
+    assert got[quals.index("I" * 150)].count("1") == 110
