@@ -894,6 +894,18 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
         best = max(runs, key=lambda n: runs[n]["value"])
         e2e = dict(runs[best])
         e2e["path"] = best
+        # which resource the e2e step saturates: the bus (against this box's own pinned-copy rate, measured now), the host
+        # packer cores (hybrid / hostpack: packer busy time against the step), or neither (the kernels)
+        h2d_ms, d2h_ms = C.c_float(0), C.c_float(0)
+        abi.check(L, L.dbt_bus_bench(local, 1 << 30, 3, C.byref(h2d_ms), C.byref(d2h_ms)), "bus bench")
+        bus_h2d, bus_d2h = (1 << 30) / h2d_ms.value / 1e6, (1 << 30) / d2h_ms.value / 1e6
+        ach_h2d, ach_d2h = e2e["h2d_bytes_per_step"] / e2e["ms_per_step"] / 1e6, e2e["d2h_bytes_per_step"] / e2e["ms_per_step"] / 1e6
+        packer_busy = e2e.get("host_pack_ms_per_step", 0.0) / e2e["ms_per_step"]
+        e2e["saturated"] = {"resource": ("PCIe host->device" if ach_h2d >= 0.8 * bus_h2d else "host packer cores" if packer_busy >= 0.8 else "GPU kernels / launch latency"),
+                            "h2d_GBps": ach_h2d, "h2d_GBps_box_peak_pinned_1GiB_copy": bus_h2d, "h2d_frac": ach_h2d / bus_h2d,
+                            "d2h_GBps": ach_d2h, "d2h_GBps_box_peak_pinned_1GiB_copy": bus_d2h,
+                            "host_packer_busy_frac": packer_busy, "host_cores": len(os.sched_getaffinity(0)),
+                            "gpu_step_ms_inputs_resident": step_ms}
         nkey = "aln_records_per_step" if thr else "kam_records_per_step"
         e2e["other_paths"] = []
         for n, r in runs.items():

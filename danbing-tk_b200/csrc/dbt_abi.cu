@@ -1140,6 +1140,29 @@ extern "C" int dbt_random_gather_bench(int device, uint64_t table_bytes, uint32_
 	return DBT_OK;
 }
 
+extern "C" int dbt_bus_bench(int device, uint64_t bytes, int iters, float* h2d_ms, float* d2h_ms) {
+	if (!h2d_ms || !d2h_ms || !bytes) return fail(DBT_E_BADARG, "null argument");
+	CU(cudaSetDevice(device));
+	void* h = nullptr; uint8_t* d = nullptr;
+	CU(cudaMallocHost(&h, bytes));
+	memset(h, 1, bytes);
+	if (int rc = dev_alloc(&d, bytes, "bus bench")) { cudaFreeHost(h); return rc; }
+	cudaEvent_t a, b; CU(cudaEventCreate(&a)); CU(cudaEventCreate(&b));
+	float best[2] = {1e30f, 1e30f};
+	for (int dir = 0; dir < 2; ++dir)
+		for (int it = 0; it < iters + 1; ++it) {
+			CU(cudaEventRecord(a, 0));
+			CU(dir ? cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, 0) : cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, 0));
+			CU(cudaEventRecord(b, 0));
+			CU(cudaEventSynchronize(b));
+			float ms; CU(cudaEventElapsedTime(&ms, a, b));
+			if (it > 0 && ms < best[dir]) best[dir] = ms;
+		}
+	cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(d); cudaFreeHost(h);
+	*h2d_ms = best[0]; *d2h_ms = best[1];
+	return DBT_OK;
+}
+
 // ------------------------------------------------------------------------------------------
 // NCCL (dlopen'ed: the library loads and runs single-GPU without libnccl)
 // ------------------------------------------------------------------------------------------

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define DBT_ABI_VERSION 5
+#define DBT_ABI_VERSION 6
 
 /* ---- error codes -------------------------------------------------------------------------- */
 #define DBT_OK            0
@@ -343,6 +343,10 @@ int  dbt_graph_merged(const dbt_ctx*);                         /* 1: the graphs 
 uint64_t dbt_graph_table_bytes(const dbt_ctx*);                /* bytes of the graph table in HBM (0 without restored threading) */
 int  dbt_random_gather_bench(int device, uint64_t table_bytes, uint32_t sector_bytes,
                              uint64_t n_gathers, int iters, float* best_ms); /* R_rand roofline    */
+
+/* pinned host -> device copy rate of this box (what bounds `e2e` once the kernels are faster than the bus): best of `iters`
+   copies of `bytes`, and the same for device -> host */
+int  dbt_bus_bench(int device, uint64_t bytes, int iters, float* h2d_ms, float* d2h_ms);
 
 /* ---- host helpers --------------------------------------------------------------------------- */
 void* dbt_host_alloc(size_t bytes);                           /* pinned */

@@ -22,15 +22,41 @@ def test_header_and_python_mirror_agree():
 def test_library_exports_every_declared_symbol(lib):
     for s in declared_symbols():
         assert hasattr(lib, s), s
-    assert lib.dbt_abi_version() == 4
+    assert lib.dbt_abi_version() == header_facts()["abi"]
+
+
+_facts = None
+
+
+def header_facts():
+    """sizeof of every struct of include/danbing_b200.h and its version, as a C compiler sees them"""
+    global _facts
+    if _facts is None:
+        import subprocess
+        import tempfile
+        src = ('#include <stdio.h>\n#include "danbing_b200.h"\nint main(void){printf("abi %d\\nparams %zu\\nindex %zu\\nbatch %zu\\nresult %zu\\n'
+               'rawbatch %zu\\nrawinfo %zu\\nrecord %zu\\ncounters %d\\n", DBT_ABI_VERSION, sizeof(dbt_params), sizeof(dbt_index), sizeof(dbt_batch), '
+               'sizeof(dbt_batch_result), sizeof(dbt_raw_batch), sizeof(dbt_raw_info), sizeof(dbt_pair_record), DBT_N_COUNTERS);return 0;}\n')
+        with tempfile.TemporaryDirectory() as d:
+            with open(os.path.join(d, "s.c"), "w") as f:
+                f.write(src)
+            subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), "-o", os.path.join(d, "s"), os.path.join(d, "s.c")], check=True)
+            out = subprocess.run([os.path.join(d, "s")], capture_output=True, text=True, check=True).stdout
+        _facts = {l.split()[0]: int(l.split()[1]) for l in out.splitlines()}
+    return _facts
 
 
 def test_struct_sizes():
-    assert C.sizeof(abi.Params) == 18 * 4
-    assert C.sizeof(abi.Index) == 14 * 8
-    assert C.sizeof(abi.Batch) == 40
-    assert C.sizeof(abi.BatchResult) == 24 + abi.DBT_N_COUNTERS * 8
-    assert abi.RECORD_HEADER_DTYPE.itemsize == 64
+    """the ctypes mirrors (danbing-tk_b200/abi.py) against the header compiled by gcc"""
+    f = header_facts()
+    assert C.sizeof(abi.Params) == f["params"]
+    assert C.sizeof(abi.Index) == f["index"]
+    assert C.sizeof(abi.Batch) == f["batch"]
+    assert C.sizeof(abi.BatchResult) == f["result"]
+    assert C.sizeof(abi.RawBatch) == f["rawbatch"]
+    assert C.sizeof(abi.RawInfo) == f["rawinfo"]
+    assert abi.DBT_N_COUNTERS == f["counters"]
+    assert abi.RECORD_HEADER_DTYPE.itemsize == f["record"] == 64
 
 
 def test_no_cpu_fallback(lib):
