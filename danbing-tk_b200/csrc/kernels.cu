@@ -109,7 +109,11 @@ __global__ void __launch_bounds__(PACK_WARPS * 32) pack_kernel(const uint8_t* __
 		uint64_t* orec = tout + ((size_t)mate * 16 + (lane >> 1)) * W64;
 		if (active) {
 			const uint32_t so = (uint32_t)((ascii + off) - a0);                         // byte offset of the read inside the tile
-			(mate ? meta1 : meta0)[pair] = pack_read_swar(reinterpret_cast<const uint32_t*>(tin + (so & ~3u)), (so & 3u) * 8, (uint32_t)len64, k, lay, orec);
+			const uint32_t* sw = reinterpret_cast<const uint32_t*>(tin + (so & ~3u));
+			uint16_t mt;
+			if (!pack_read_fast(sw, (so & 3u) * 8, (uint32_t)len64, k, lay, orec, &mt))      // a byte outside ACGT: the exact path
+				mt = pack_read_swar(sw, (so & 3u) * 8, (uint32_t)len64, k, lay, orec);
+			(mate ? meta1 : meta0)[pair] = mt;
 		}
 		__syncwarp();
 		// ---- write the two record blocks out: coalesced 128-bit stores ----

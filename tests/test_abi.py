@@ -175,5 +175,6 @@ def test_device_packer_body_matches_host_packer(tmp_path):
                     os.path.join(root, "danbing-tk_b200/csrc/host_pack.cpp")], check=True)
     out = subprocess.run([exe], capture_output=True, text=True)
     assert out.returncode == 0 and out.stdout.startswith("OK"), out.stdout
-    ncase, nnovalid = map(int, out.stdout.split()[1:3])
+    ncase, nnovalid, nfast = map(int, out.stdout.split()[1:4])
     assert ncase >= 50000 and 1000 < nnovalid < ncase - 1000
+    assert 5000 < nfast < ncase - 5000            # reads the fast (clean-read) path packed itself; it refused exactly the others
