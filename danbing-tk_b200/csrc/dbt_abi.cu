@@ -32,6 +32,12 @@ static int fail(int code, const char* fmt, ...) {
 	va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
 	return code;
 }
+namespace dbt {   // for the other translation units of the library (noalloc.cu): sets dbt_last_error(), returns code
+int abi_fail(int code, const char* fmt, ...) {
+	va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
+	return code;
+}
+}
 #define CU(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return fail(DBT_E_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); } while (0)
 
 extern "C" const char* dbt_strerror(int code) {

@@ -344,6 +344,22 @@ uint64_t dbt_graph_table_bytes(const dbt_ctx*);                /* bytes of the g
 int  dbt_random_gather_bench(int device, uint64_t table_bytes, uint32_t sector_bytes,
                              uint64_t n_gathers, int iters, float* best_ms); /* R_rand roofline    */
 
+/* ---- allocation-free packing ------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * dbt_pack_reads_device_noalloc = dbt_pack_reads (same arguments minus the thread count, same output layout and bytes), computed
+ * by pack_kernel on GPU `device` inside a fixed, file-scope device array of DBT_NOALLOC_SCRATCH_BYTES that every GPU loading the
+ * library holds until exit.  It calls no cudaMalloc / cudaFree / allocating routine and works on the legacy default stream.
+ * Limits: npairs <= DBT_NOALLOC_MAX_PAIRS and dbt_noalloc_scratch_needed(max_read_len, npairs, bases in the batch) <=
+ * DBT_NOALLOC_SCRATCH_BYTES; anything larger returns DBT_E_CAPACITY (message in dbt_last_error), nothing is allocated instead.
+ * All calls share the array (it keeps the previous call's contents; the call clears what must start at zero): calls that overlap
+ * on one GPU race -- callers inside one process are serialised by the library, other users of the GPU are the caller's business. */
+#define DBT_NOALLOC_SCRATCH_BYTES (8u << 20)
+#define DBT_NOALLOC_MAX_PAIRS     16384u
+size_t dbt_noalloc_scratch_needed(uint32_t max_read_len, uint64_t npairs, uint64_t nbases);
+int  dbt_pack_reads_device_noalloc(int device, uint32_t k, uint32_t max_read_len, uint64_t npairs, const uint8_t* ascii,
+                                   const uint64_t* offsets, uint8_t* packed_out);
+
 /* pinned host -> device copy rate of this box (what bounds `e2e` once the kernels are faster than the bus): best of `iters`
    copies of `bytes`, and the same for device -> host */
 int  dbt_bus_bench(int device, uint64_t bytes, int iters, float* h2d_ms, float* d2h_ms);
