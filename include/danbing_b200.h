@@ -344,6 +344,24 @@ uint64_t dbt_graph_table_bytes(const dbt_ctx*);                /* bytes of the g
 int  dbt_random_gather_bench(int device, uint64_t table_bytes, uint32_t sector_bytes,
                              uint64_t n_gathers, int iters, float* best_ms); /* R_rand roofline    */
 
+/* ---- bias correction downstream of OUT.trkmc.ar ---------------------------
+ * dbt_pred replaces load_eachBinGT + norm_rd + bias_correction of `danbing-tk-pred` (src/pred.cpp:58-80, src/pred.h:141-195).
+ * All matrices are column-major float32 as the reference's Eigen arrays are: element (sample s, k-mer k) of gt at s + k*ns,
+ * (sample s, locus t) of bias at s + t*ns.  Results are bit-identical to the reference's (same IEEE operations in the same order).
+ * Columns of `bias` (and blocks of gt_corrected = gt_raw) of loci without k-mers or without invariant k-mers are left as the caller
+ * passed them / uncorrected (pred.h:181).  Every invariant k-mer index must lie inside its own locus (DBT_E_INDEX otherwise). */
+typedef struct {
+  uint64_t ns, nk, n_tr, n_ik;     /* samples, k-mers, loci, invariant k-mers                                          */
+  const uint64_t* const* kmc;      /* ns arrays of nk counts: the payload of each sample's OUT.trkmc.ar (pred.h:141-164) */
+  const float*    rd;              /* ns read depths (column 2 of the metadata file, pred.h:41-50)                     */
+  const uint32_t* nk_cum;          /* n_tr: k-mers up to and including locus t (ikmer.meta, pred.h:69-123)             */
+  const uint32_t* nik_cum;         /* n_tr: invariant k-mers up to and including locus t                               */
+  const uint32_t* iki;             /* n_ik: k-mer index of each invariant k-mer                                        */
+  const uint8_t*  ikmc;            /* n_ik: its expected count                                                         */
+} dbt_pred_input;
+/* kernel_ms (may be NULL): [0] normalisation + transpose, [1] bias correction, CUDA events */
+int  dbt_pred(int device, const dbt_pred_input* in, float* gt_raw, float* gt_corrected, float* bias, float kernel_ms[2]);
+
 /* ---- allocation-free packing ------------------------------------------------------------------
  * No counterpart in the reference: added for callers that cannot call cudaMalloc
  * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
