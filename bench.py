@@ -264,6 +264,8 @@ def main():
     ap.add_argument("--hbm-cpu-sample", type=int, default=200_000)
     ap.add_argument("--file-pairs", type=int, default=8_000_000, help="block `e2e_file` (N=1): FASTA of this many pairs in /dev/shm -> the drop-in CLI -> "
                     "outputs in /dev/shm, beside the reference binary on the same file; 0 = off")
+    ap.add_argument("--pred-samples", type=int, default=48, help="block `pred` (N=1): samples given to danbing-tk-pred (SURVEY §8(f) row 4); 0 = skip")
+    ap.add_argument("--pred-kmers", type=int, default=2_000_000)
     ap.add_argument("--rrand", action=argparse.BooleanOptionalAction, default=True,
                     help="also measure the random-sector roofline R_rand (32 B / 64 B gathers over an 8 GiB table, < 1 s) and report the "
                          "probe rate of the dominant kernel as a fraction of it")
@@ -299,12 +301,97 @@ def main():
             out["hbm_resident"] = hbm_resident_block(a, workdir)
         if rank == 0 and world == 1 and a.file_pairs > 0 and a.loci == 1000:
             out["e2e_file"] = e2e_file_block(a, pref, pool, hap_off, workdir, local)
+        if rank == 0 and world == 1 and a.pred_samples > 0:
+            out["pred"] = pred_block(a, workdir, local)
         if rank == 0:
             print(json.dumps(out))
     finally:
         shutil.rmtree(workdir, ignore_errors=True)
         if dist is not None:
             dist.destroy_process_group()
+
+
+def pred_block(a, workdir, device):
+    """SURVEY §8(f) row 4, `danbing-tk-pred`: --pred-samples count arrays (synthetic OUT.trkmc.ar of --pred-kmers k-mers) through
+    dbt_pred (kernel times by CUDA events, algorithmic bytes vs the HBM peak), the drop-in CLI and the unmodified reference binary
+    (single-threaded Eigen) on the same files in /dev/shm; the three output files are compared byte for byte."""
+    L = abi.load_library()
+    ns, nk = a.pred_samples, a.pred_kmers
+    rng = np.random.default_rng(77)
+    n_tr = max(10, nk // 180)                                 # ~180 k-mers per locus, a fifth of them invariant
+    cuts = np.sort(rng.choice(np.arange(1, nk), n_tr - 1, replace=False))
+    nk_cum = np.append(cuts, nk).astype(np.uint32)
+    starts = np.concatenate([[0], cuts]).astype(np.int64)
+    inv = np.flatnonzero(rng.random(nk) < 0.2).astype(np.uint32)
+    first = starts[np.searchsorted(nk_cum, starts, side="right") == np.arange(n_tr)]   # every locus keeps at least its first k-mer
+    inv = np.union1d(inv, first.astype(np.uint32)).astype(np.uint32)
+    nik_cum = np.searchsorted(inv, nk_cum, side="left").astype(np.uint32)
+    ikmc = rng.integers(1, 4, len(inv)).astype(np.uint8)
+    rd = rng.uniform(20, 40, ns).round(2)
+    d = os.path.join(workdir, "pred")
+    os.makedirs(d, exist_ok=True)
+    kmc, fns = [], []
+    for s in range(ns):
+        v = (rng.poisson(rd[s], nk) + 1).astype(np.uint64)
+        kmc.append(v)
+        fn = os.path.join(d, f"s{s}.trkmc.ar")
+        with open(fn, "wb") as f:
+            f.write(np.uint64(nk).tobytes())
+            f.write(v.tobytes())
+        fns.append(fn)
+    with open(os.path.join(d, "meta.txt"), "w") as f:
+        for fn, r in zip(fns, rd):
+            f.write(f"{fn}\t{r}\n")
+    rec = np.zeros(len(inv), np.dtype([("i", "<u4"), ("c", "u1")]))
+    rec["i"], rec["c"] = inv, ikmc
+    with open(os.path.join(d, "ikmer.meta"), "wb") as f:
+        f.write(np.array([nk, len(inv), n_tr], np.uint64).tobytes() + nk_cum.tobytes() + nik_cum.tobytes() + rec.tobytes())
+    # ---- dbt_pred through the C ABI ----
+    inp = abi.PredInput()
+    inp.ns, inp.nk, inp.n_tr, inp.n_ik = ns, nk, n_tr, len(inv)
+    arr = (abi.u64p * ns)(*[abi.ptr(v, abi.u64p) for v in kmc])
+    inp.kmc = C.cast(arr, C.POINTER(abi.u64p))
+    fp = C.POINTER(C.c_float)
+    rdf = np.array([np.float32(float(f"{r}")) for r in rd], np.float32)
+    inp.rd = rdf.ctypes.data_as(fp)
+    inp.nk_cum, inp.nik_cum, inp.iki, inp.ikmc = abi.ptr(nk_cum, abi.u32p), abi.ptr(nik_cum, abi.u32p), abi.ptr(inv, abi.u32p), abi.ptr(ikmc, abi.u8p)
+    raw, cor, bias = np.zeros((nk, ns), np.float32), np.zeros((nk, ns), np.float32), np.zeros((n_tr, ns), np.float32)
+    ms = np.zeros(2, np.float32)
+    best = None
+    for _ in range(3):
+        t0 = time.perf_counter()
+        abi.check(L, L.dbt_pred(device, C.byref(inp), raw.ctypes.data_as(fp), cor.ctypes.data_as(fp), bias.ctypes.data_as(fp), ms.ctypes.data_as(fp)), "dbt_pred")
+        wall = time.perf_counter() - t0
+        if best is None or ms.sum() < best[0].sum():
+            best = (ms.copy(), wall)
+    ms, wall = [float(x) for x in best[0]], best[1]
+    peak, peak_src = peaks()
+    b_norm = ns * nk * 12
+    b_bias = ns * nk * 8 + ns * len(inv) * 4 + ns * n_tr * 8
+    blk = {"samples": ns, "kmers": nk, "loci": n_tr, "invariant_kmers": int(len(inv)), "dtype": "f32",
+           "kernels": {"pred_norm_kernel": {"ms": float(ms[0]), "algorithmic_bytes": int(b_norm), "GBps": b_norm / ms[0] / 1e6, "frac_of_hbm_peak": b_norm / ms[0] / 1e6 / peak},
+                       "pred_bias_kernel": {"ms": float(ms[1]), "algorithmic_bytes": int(b_bias), "GBps": b_bias / ms[1] / 1e6, "frac_of_hbm_peak": b_bias / ms[1] / 1e6 / peak}},
+           "peak_GBps": peak, "peak_source": peak_src,
+           "c_abi_call_s": wall, "c_abi_note": "dbt_pred with pageable host arrays: H2D of the counts, both kernels, D2H of the three matrices"}
+    # ---- the two binaries on the same files ----
+    def run(exe, tag):
+        outs = [os.path.join(d, f"{tag}.{x}") for x in ("raw", "cor", "bias.tsv")]
+        t0 = time.perf_counter()
+        r = subprocess.run([exe, os.path.join(d, "meta.txt"), os.path.join(d, "ikmer.meta")] + outs, capture_output=True)
+        if r.returncode:
+            raise RuntimeError(f"{exe} failed: {r.stderr.decode()[-400:]}")
+        return time.perf_counter() - t0, outs
+    t_gpu, o_gpu = run(os.path.join(ROOT, "danbing-tk_b200", "bin", "danbing-tk-pred"), "gpu")
+    blk["cli_wall_s"] = t_gpu
+    ref = os.path.join(ROOT, "oracle", "_ref", "danbing-tk-pred")
+    if os.path.exists(ref):
+        t_ref, o_ref = run(ref, "ref")
+        same = [open(x, "rb").read() == open(y, "rb").read() for x, y in zip(o_gpu, o_ref)]
+        blk["reference_binary"] = {"wall_s": t_ref, "threads": 1, "outputs_identical": {"raw": same[0], "corrected": same[1], "bias_tsv": same[2]}}
+        blk["cli_speedup_vs_reference_binary"] = t_ref / t_gpu
+        blk["abi_matches_cli"] = bool(np.array_equal(np.fromfile(o_gpu[1], np.float32, offset=8), cor.ravel()))
+    shutil.rmtree(d, ignore_errors=True)
+    return blk
 
 
 def e2e_file_block(a, pref, pool, hap_off, workdir, device):

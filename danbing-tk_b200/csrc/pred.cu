@@ -45,61 +45,91 @@ __global__ void __launch_bounds__(256) pred_norm_kernel(const uint64_t* __restri
 	}
 }
 
-// Eigen 3.4 redux<sum> of a contiguous, 16-byte aligned float array with 4-float packets (Redux.h, LinearVectorizedTraversal)
-__device__ float eigen_sum4(const float* a, uint32_t n) {
+// Eigen 3.4 redux<sum> of a contiguous, 16-byte aligned float array with 4-float packets (Redux.h, LinearVectorizedTraversal),
+// by one warp: the eight lanes of the two packet accumulators are eight independent chains, one per lane 0..7; the rest of the
+// order (accumulators added, one more packet, (a0+a2)+(a1+a3), scalar tail) is replayed with shuffles.  Result in every lane.
+__device__ float eigen_sum4_warp(const float* a, uint32_t n, uint32_t lane) {
 	const uint32_t n2 = (n / 8) * 8, n1 = (n / 4) * 4;
 	float r;
-	if (!n1) { r = a[0]; for (uint32_t i = 1; i < n; ++i) r = __fadd_rn(r, a[i]); return r; }
-	float p0[4] = {a[0], a[1], a[2], a[3]};
-	if (n1 > 4) {
-		float p1[4] = {a[4], a[5], a[6], a[7]};
-		for (uint32_t i = 8; i < n2; i += 8)
-			for (int l = 0; l < 4; ++l) { p0[l] = __fadd_rn(p0[l], a[i + l]); p1[l] = __fadd_rn(p1[l], a[i + 4 + l]); }
-		for (int l = 0; l < 4; ++l) p0[l] = __fadd_rn(p0[l], p1[l]);
-		if (n1 > n2) for (int l = 0; l < 4; ++l) p0[l] = __fadd_rn(p0[l], a[n2 + l]);
+	if (!n1) {
+		r = a[0];
+		for (uint32_t i = 1; i < n; ++i) r = __fadd_rn(r, a[i]);
+		return r;
 	}
-	r = __fadd_rn(__fadd_rn(p0[0], p0[2]), __fadd_rn(p0[1], p0[3]));
+	float acc = 0.f;
+	if (n1 > 4) {                                                      // two accumulators: lane l < 4 is p0[l], lane 4 + l is p1[l]
+		if (lane < 8) { acc = a[lane]; for (uint32_t i = 8; i < n2; i += 8) acc = __fadd_rn(acc, a[i + lane]); }
+		const float other = __shfl_down_sync(0xffffffffu, acc, 4);
+		acc = __fadd_rn(acc, other);                                   // p0 += p1 (lanes 0..3)
+		if (n1 > n2 && lane < 4) acc = __fadd_rn(acc, a[n2 + lane]);
+	} else if (lane < 4) acc = a[lane];
+	const float a2 = __shfl_down_sync(0xffffffffu, acc, 2);            // lane 0: p0[2], lane 1: p0[3]
+	const float h = __fadd_rn(acc, a2);                                // lane 0: a0+a2, lane 1: a1+a3
+	const float h1 = __shfl_down_sync(0xffffffffu, h, 1);
+	r = __fadd_rn(h, h1);
 	for (uint32_t i = n1; i < n; ++i) r = __fadd_rn(r, a[i]);
-	return r;
+	return __shfl_sync(0xffffffffu, r, 0);
 }
 
 // one block per locus.  bias: [locus][ns] (column-major ns x n_tr); skipped loci (no k-mers or no invariant k-mers) leave their
-// column untouched and their block of `cor` equal to `raw`, pred.h:181
+// column untouched and their block of `cor` equal to `raw`, pred.h:181.
+// The per-sample sum over the invariant k-mers must be added up left to right, but the gathers and divisions feeding it are
+// independent: with ns <= 256 the block first fills a shared-memory tile B[c][s] = raw[s, iki[j0+c]] / ikmc[j0+c] for 256/ns
+// invariant k-mers at a time (all threads, coalesced along s), then thread s adds the tile's column in order.
 __global__ void __launch_bounds__(256) pred_bias_kernel(const float* __restrict__ raw, float* __restrict__ cor, float* __restrict__ bias, uint64_t ns, uint32_t n_tr,
                                                         const uint32_t* __restrict__ nk_cum, const uint32_t* __restrict__ nik_cum,
                                                         const uint32_t* __restrict__ iki, const uint8_t* __restrict__ ikmc) {
 	__shared__ float s_mean;
+	__shared__ float s_b[256];
+	const uint32_t tid = threadIdx.x;
 	for (uint32_t t = blockIdx.x; t < n_tr; t += gridDim.x) {
 		const uint32_t si = t ? nk_cum[t - 1] : 0, ei = nk_cum[t], isi = t ? nik_cum[t - 1] : 0, iei = nik_cum[t];
 		if (si == ei) continue;
+		const uint64_t n = (uint64_t)(ei - si) * ns, o = (uint64_t)si * ns;    // the locus' block is contiguous in the column-major matrix
 		if (isi == iei) {                                                // skipped locus: its block stays uncorrected
-			const uint64_t n = (uint64_t)(ei - si) * ns, o = (uint64_t)si * ns;
-			for (uint64_t i = threadIdx.x; i < n; i += blockDim.x) cor[o + i] = raw[o + i];
+			for (uint64_t i = tid; i < n; i += blockDim.x) cor[o + i] = raw[o + i];
 			continue;
 		}
 		float* b = bias + (uint64_t)t * ns;
 		const float fn = (float)(iei - isi);
-		for (uint64_t s = threadIdx.x; s < ns; s += blockDim.x) {       // consecutive threads = consecutive samples of one column: coalesced
-			float acc = __fdiv_rn(raw[(uint64_t)iki[isi] * ns + s], (float)ikmc[isi]);
-			for (uint32_t j = isi + 1; j < iei; ++j) acc = __fadd_rn(acc, __fdiv_rn(raw[(uint64_t)iki[j] * ns + s], (float)ikmc[j]));
-			b[s] = __fdiv_rn(acc, fn);
+		if (ns <= blockDim.x) {
+			const uint32_t nsv = (uint32_t)ns, cpb = blockDim.x / nsv, s = tid % nsv, c = tid / nsv;
+			float acc = 0.f;
+			for (uint32_t j0 = isi; j0 < iei; j0 += cpb) {
+				const uint32_t cnt = min(cpb, iei - j0);
+				if (c < cnt) s_b[c * nsv + s] = __fdiv_rn(raw[(uint64_t)iki[j0 + c] * ns + s], (float)ikmc[j0 + c]);
+				__syncthreads();
+				if (c == 0) {
+					uint32_t q = 0;
+					if (j0 == isi) { acc = s_b[s]; q = 1; }
+					for (; q < cnt; ++q) acc = __fadd_rn(acc, s_b[q * nsv + s]);
+				}
+				__syncthreads();
+			}
+			if (c == 0) b[s] = __fdiv_rn(acc, fn);
+		} else {
+			for (uint64_t s = tid; s < ns; s += blockDim.x) {
+				float acc = __fdiv_rn(raw[(uint64_t)iki[isi] * ns + s], (float)ikmc[isi]);
+				for (uint32_t j = isi + 1; j < iei; ++j) acc = __fadd_rn(acc, __fdiv_rn(raw[(uint64_t)iki[j] * ns + s], (float)ikmc[j]));
+				b[s] = __fdiv_rn(acc, fn);
+			}
 		}
 		__syncthreads();
-		if (threadIdx.x == 0) s_mean = __fdiv_rn(eigen_sum4(b, (uint32_t)ns), (float)ns);
+		if (tid < 32) { const float m = __fdiv_rn(eigen_sum4_warp(b, (uint32_t)ns, tid), (float)ns); if (tid == 0) s_mean = m; }
 		__syncthreads();
 		const float m = s_mean;
-		for (uint64_t s = threadIdx.x; s < ns; s += blockDim.x) b[s] = __fdiv_rn(b[s], m);
+		for (uint64_t s = tid; s < ns; s += blockDim.x) b[s] = __fdiv_rn(b[s], m);
 		__syncthreads();
-		const float* rp = raw + (uint64_t)si * ns;                       // the locus' block is contiguous in the column-major matrix
-		float* cp = cor + (uint64_t)si * ns;
+		const float* rp = raw + o;
+		float* cp = cor + o;
 		if (ns <= blockDim.x) {                                          // several columns per pass, each thread keeps its sample
-			const uint32_t cpb = blockDim.x / (uint32_t)ns, s = threadIdx.x % (uint32_t)ns, c = threadIdx.x / (uint32_t)ns;
+			const uint32_t cpb = blockDim.x / (uint32_t)ns, s = tid % (uint32_t)ns, c = tid / (uint32_t)ns;
 			if (c < cpb) {
 				const float bs = b[s];
 				for (uint64_t k = c; k < ei - si; k += cpb) cp[k * ns + s] = __fdiv_rn(rp[k * ns + s], bs);
 			}
 		} else {
-			for (uint64_t s = threadIdx.x; s < ns; s += blockDim.x) {
+			for (uint64_t s = tid; s < ns; s += blockDim.x) {
 				const float bs = b[s];
 				for (uint64_t k = 0; k < ei - si; ++k) cp[k * ns + s] = __fdiv_rn(rp[k * ns + s], bs);
 			}

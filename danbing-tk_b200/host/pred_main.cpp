@@ -17,6 +17,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
+#include <memory>
 #include <string>
 #include <vector>
 #include "danbing_b200.h"
@@ -114,7 +115,9 @@ int main(int argc, char** argv) {
 		kmc[s] = reinterpret_cast<const uint64_t*>(static_cast<const uint8_t*>(maps[s].p) + 8);
 	}
 
-	std::vector<float> raw((size_t)ns * nk), cor((size_t)ns * nk), bias((size_t)ns * n_tr, 0.f);
+	std::unique_ptr<float[]> raw_mem(new float[(size_t)ns * nk]), cor_mem(new float[(size_t)ns * nk]);   // filled entirely by dbt_pred: not zeroed first
+	struct { float* p; float* data() { return p; } } raw{raw_mem.get()}, cor{cor_mem.get()};
+	std::vector<float> bias((size_t)ns * n_tr, 0.f);
 	dbt_pred_input in{};
 	in.ns = ns; in.nk = nk; in.n_tr = n_tr; in.n_ik = n_ik; in.kmc = kmc.data(); in.rd = rds.data();
 	in.nk_cum = nk_cum.data(); in.nik_cum = nik_cum.data(); in.iki = iki.data(); in.ikmc = ikmc.data();
