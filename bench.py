@@ -795,10 +795,18 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
         pass
     if a.rrand and rank == 0:
         rr = {}
-        for sect in (32, 64):
+        # R_rand depends on HOW a sector is asked for (profiles/r2/k4_rrand_sweep.json): two 16-byte loads of one thread, one 256-bit
+        # load per thread (what the probe functions issue), or one coalesced request from adjacent lanes.  The denominator of every
+        # fraction below is the BEST of them -- the rate the memory system can deliver, not the rate of one access pattern.
+        def gather_rate(mode_bits, sect):
             msr = C.c_float()
-            abi.check(L, L.dbt_random_gather_bench(local, 8 << 30, sect, 1 << 28, 3, C.byref(msr)), "rrand")
-            rr[f"{sect}B_Gsectors_per_s"] = (1 << 28) / (msr.value / 1e3) / 1e9
+            abi.check(L, L.dbt_random_gather_bench(local, 8 << 30, sect | mode_bits, 1 << 28, 3, C.byref(msr)), "rrand")
+            return (1 << 28) / (msr.value / 1e3) / 1e9
+        rr["32B_by_access_pattern"] = {"two_16B_loads_per_thread": gather_rate(0, 32), "one_256bit_load_per_thread": gather_rate(0x20000, 32),
+                                       "one_coalesced_request_from_2_lanes": gather_rate(0x10000, 32)}
+        rr["128B_line_one_coalesced_request_Glines_per_s"] = gather_rate(0x10000, 128)
+        rr["32B_Gsectors_per_s"] = max(rr["32B_by_access_pattern"].values())
+        rr["64B_Gsectors_per_s"] = max(gather_rate(0, 64), gather_rate(0x10000, 64))
         # the "HBM random-access roofline" of SURVEY.md 8(d): logical probes (one 32 B sector each) per second of the dominant
         # kernel against the measured gather rate over a table far beyond L2.  At the default index size most probes hit L2, so
         # this can exceed 1 -- it is the honest denominator for HBM-resident tables (--loci 20000 and up).

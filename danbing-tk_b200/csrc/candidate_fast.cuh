@@ -66,7 +66,10 @@ struct FastWarp {
 };
 
 
-template <int B, int MAXJ>
+// COOP: the bucket staging of the probe round -- false: every lane fetches the B slots of its own bucket (tables in L2: fewest
+// instructions), true: B adjacent lanes fetch one bucket as one coalesced request (tables in HBM: table.cuh, stage_buckets_coop).
+// A template parameter, not a run-time switch: the uniform branch alone cost 4 % of this issue-bound kernel (profiles/r2/k7).
+template <int B, int MAXJ, bool COOP>
 __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, CANDF_MINBLOCKS) candidate_fast_kernel(DevIndex ix, RunParams rp, SlotView sv) {
 	extern __shared__ __align__(16) uint8_t fast_smem[];
 	FastWarp<B, MAXJ>* wsm = reinterpret_cast<FastWarp<B, MAXJ>*>(fast_smem);
@@ -121,7 +124,10 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, CANDF_MINBLOCKS) candida
 					kk = fw < rcx ? fw : rcx;
 				}
 				W.val[m][i] = (uint32_t)kk; W.aux[m][i] = (uint32_t)(kk >> 32);
-				if (kk != KMER_INVALID) {
+if constexpr (COOP) {                                 // tables in HBM: one coalesced request per bucket (table.cuh)
+					const bool valid = kk != KMER_INVALID;
+					stage_buckets_coop<B>(ix.table.slots, valid, valid ? (uint32_t)home_bucket(ix.table, kk) : 0u, W.slot[j], lane);
+				} else if (kk != KMER_INVALID) {
 					const uint4* bp = ix.table.slots + home_bucket(ix.table, kk) * B;
 #pragma unroll
 					for (int q = 0; q < B; ++q) cp_async16(&W.slot[j][q][lane], bp + q);

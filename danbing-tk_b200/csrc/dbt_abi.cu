@@ -635,6 +635,12 @@ extern "C" int dbt_load_index(dbt_ctx* c, const dbt_index* in) {
 		if (!in->tre_n || (!in->tre_kmers && nloci)) return fail(DBT_E_BADARG, "DBT_F_BUBBLES needs tre_n / tre_kmers (PREF.tre.kdb)");
 		TRY(load_edges(c, in));
 	}
+	{	// tables far beyond L2: the probe rounds are bound by the random-sector rate of HBM -> one coalesced request per bucket
+		int l2 = 0;
+		if (cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, c->p.device) != cudaSuccess) { cudaGetLastError(); l2 = 0; }
+		c->rp.coop_stage = (l2 > 0 && c->table_bytes + c->gtable_bytes > 2 * (uint64_t)l2) ? 1u : 0u;
+		if (const char* e = getenv("DBT_COOP_STAGE")) c->rp.coop_stage = atoi(e) ? 1u : 0u;
+	}
 	c->index_loaded = true;
 	return DBT_OK;
 }

@@ -54,6 +54,7 @@ struct RunParams {
 	uint32_t thread_cth, max_ncorrection, correction;
 	uint32_t es_cap, tr_cap, aln_stride;   // record blob geometry (include/danbing_b200.h, dbt_aln_mate)
 	uint32_t qth;               // `-qth`
+	uint32_t coop_stage;        // the tables are far beyond L2: stage buckets with one coalesced request each (table.cuh, stage_buckets_coop)
 };
 
 // one in-flight batch

@@ -70,9 +70,10 @@ __device__ __forceinline__ GNode g_lookup(const Table& t, uint64_t fw, uint32_t 
 	for (;;) {
 		const uint4* bp = t.slots + b * B;
 		// named registers, not an array: inside divergent callers nvcc kept `uint4 s[B]` in local memory (ncu: 50 M LDL/STL)
-		const uint4 s0 = ldg128(bp), s1 = ldg128(bp + 1);
+		uint4 s0, s1;
+		ldg256(bp, s0, s1);
 		uint4 s2 = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0, 0), s3 = s2;
-		if (B == 4) { s2 = ldg128(bp + 2); s3 = ldg128(bp + 3); }
+		if (B == 4) ldg256(bp + 2, s2, s3);
 		const uint64_t k0 = slot_key(s0), k1 = slot_key(s1), k2 = slot_key(s2), k3 = slot_key(s3);
 		if ((k0 & SLOT_KEYMASK) == canon && k0 != SLOT_EMPTY && (s0.z & G_LOCUS_MASK) == locus) return g_decode(s0.z, s0.w, is_rc);
 		if ((k1 & SLOT_KEYMASK) == canon && k1 != SLOT_EMPTY && (s1.z & G_LOCUS_MASK) == locus) return g_decode(s1.z, s1.w, is_rc);

@@ -453,6 +453,47 @@ __global__ void random_gather_kernel(const uint4* __restrict__ table, uint64_t n
 	if (acc == 0x12345678u) *sink = acc;
 }
 
+// the same gathers done the way the probe kernels stage a bucket: LANES adjacent lanes take 16 bytes each of one chunk, so a chunk
+// is ONE coalesced request of LANES * 16 bytes (32 / LANES gathers per load instruction) instead of LANES requests of one thread
+template <int LANES>
+__global__ void random_gather_coop_kernel(const uint4* __restrict__ table, uint64_t nchunks, uint64_t ngathers, uint64_t seed, uint32_t* sink) {
+	const uint32_t sub = threadIdx.x % LANES;
+	uint64_t i = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES;
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x / LANES;
+	uint32_t acc = 0;
+	for (; i < ngathers; i += stride * 8) {
+		uint4 v[8];
+#pragma unroll
+		for (int u = 0; u < 8; ++u) {
+			const uint64_t g = i + u * stride;
+			const uint64_t c = __umul64hi(mix64(g ^ seed), nchunks);
+			v[u] = (g < ngathers) ? __ldg(table + c * LANES + sub) : make_uint4(0, 0, 0, 0);
+		}
+#pragma unroll
+		for (int u = 0; u < 8; ++u) acc += v[u].x ^ v[u].w;
+	}
+	if (acc == 0x12345678u) *sink = acc;
+}
+
+// ... and 32-byte chunks by ONE 256-bit load per thread (what table_lookup / g_lookup issue)
+__global__ void random_gather_ldg256_kernel(const uint4* __restrict__ table, uint64_t nchunks, uint64_t ngathers, uint64_t seed, uint32_t* sink) {
+	uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	uint32_t acc = 0;
+	for (; i < ngathers; i += stride * 4) {
+		uint4 a[4], b[4];
+#pragma unroll
+		for (int u = 0; u < 4; ++u) {
+			const uint64_t g = i + u * stride;
+			const uint64_t c = __umul64hi(mix64(g ^ seed), nchunks);
+			if (g < ngathers) ldg256(table + c * 2, a[u], b[u]); else a[u] = b[u] = make_uint4(0, 0, 0, 0);
+		}
+#pragma unroll
+		for (int u = 0; u < 4; ++u) acc += a[u].x ^ b[u].w;
+	}
+	if (acc == 0x12345678u) *sink = acc;
+}
+
 // ============================================================================================
 // host-callable launchers (used by dbt_abi.cu)
 // ============================================================================================
@@ -537,13 +578,18 @@ static cudaError_t launch_candidate_t(cudaStream_t st, unsigned nsm, unsigned gr
 	if constexpr (MAXJ <= 8) {
 		if (!all) {
 			constexpr size_t smem_fast = sizeof(FastWarp<B, MAXJ>) * CAND_FAST_WARPS;
-			e = cudaFuncSetAttribute(candidate_fast_kernel<B, MAXJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_fast);
+			auto launch = [&](auto kern) -> cudaError_t {
+				cudaError_t e2 = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_fast);
+				if (e2 != cudaSuccess) return e2;
+				int per_sm = 0;
+				e2 = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, CAND_FAST_WARPS * 32, smem_fast);
+				if (e2 != cudaSuccess) return e2;
+				if (per_sm < 1) return cudaErrorInvalidConfiguration;
+				kern<<<nsm * (unsigned)per_sm, CAND_FAST_WARPS * 32, smem_fast, st>>>(ix, rp, sv);
+				return cudaSuccess;
+			};
+			e = rp.coop_stage ? launch(candidate_fast_kernel<B, MAXJ, true>) : launch(candidate_fast_kernel<B, MAXJ, false>);
 			if (e != cudaSuccess) return e;
-			int per_sm = 0;
-			e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, candidate_fast_kernel<B, MAXJ>, CAND_FAST_WARPS * 32, smem_fast);
-			if (e != cudaSuccess) return e;
-			if (per_sm < 1) return cudaErrorInvalidConfiguration;
-			candidate_fast_kernel<B, MAXJ><<<nsm * (unsigned)per_sm, CAND_FAST_WARPS * 32, smem_fast, st>>>(ix, rp, sv);
 		}
 	}
 	if (mid) { e = cudaEventRecord(mid, st); if (e != cudaSuccess) return e; }
@@ -600,6 +646,21 @@ cudaError_t launch_table_stats(cudaStream_t st, int B, Table t, unsigned long lo
 cudaError_t launch_random_gather(cudaStream_t st, int nsm, const uint4* table, uint64_t table_bytes, uint32_t sector_bytes,
                                  uint64_t ngathers, uint64_t seed, uint32_t* sink) {
 	unsigned grid = (unsigned)nsm * 8;
+	if (sector_bytes == (DBT_GATHER_WIDE_LOAD | 32u)) {
+		random_gather_ldg256_kernel<<<grid, 256, 0, st>>>(table, table_bytes / 32, ngathers, seed, sink);
+		return cudaGetLastError();
+	}
+	if (sector_bytes & DBT_GATHER_COOPERATIVE) {
+		sector_bytes &= ~DBT_GATHER_COOPERATIVE;
+		const uint64_t nch = table_bytes / sector_bytes;
+		switch (sector_bytes) {
+		case 32:  random_gather_coop_kernel<2><<<grid, 256, 0, st>>>(table, nch, ngathers, seed, sink); break;
+		case 64:  random_gather_coop_kernel<4><<<grid, 256, 0, st>>>(table, nch, ngathers, seed, sink); break;
+		case 128: random_gather_coop_kernel<8><<<grid, 256, 0, st>>>(table, nch, ngathers, seed, sink); break;
+		default: return cudaErrorInvalidValue;
+		}
+		return cudaGetLastError();
+	}
 	uint64_t nchunks = table_bytes / sector_bytes;
 	switch (sector_bytes) {
 	case 16:  random_gather_kernel<1><<<grid, 256, 0, st>>>(table, nchunks, ngathers, seed, sink); break;

@@ -68,6 +68,20 @@ __device__ __forceinline__ uint4 ldg128(const uint4* p) { return __ldcg(p); }   
 __device__ __forceinline__ uint4 ldg128(const uint4* p) { return __ldg(p); }
 #endif
 
+// One 32-byte bucket half (two slots) in ONE 256-bit load (LDG.E.256, new on sm_100): one request to L2 per bucket instead of two.
+// Random gathers issued as one request per 32-byte sector run at 45 G/s on B200, as two 16-byte requests of one thread at 28 G/s
+// (profiles/r2/k4_rrand_sweep.json).  p must be 32-byte aligned (buckets are: B * 16 bytes from a 256-byte aligned base).
+__device__ __forceinline__ void ldg256(const uint4* p, uint4& a, uint4& b) {
+	uint64_t r0, r1, r2, r3;
+#ifdef DBT_PROBE_LDCG
+	asm volatile("ld.global.cg.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(r0), "=l"(r1), "=l"(r2), "=l"(r3) : "l"(p));
+#else
+	asm volatile("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(r0), "=l"(r1), "=l"(r2), "=l"(r3) : "l"(p));
+#endif
+	a = make_uint4((uint32_t)r0, (uint32_t)(r0 >> 32), (uint32_t)r1, (uint32_t)(r1 >> 32));
+	b = make_uint4((uint32_t)r2, (uint32_t)(r2 >> 32), (uint32_t)r3, (uint32_t)(r3 >> 32));
+}
+
 // bucket staging: 16-byte asynchronous copies HBM/L2 -> shared memory, so that probe loops can be ROLLED (small code,
 // the kernels are instruction-fetch sensitive) and still keep every probe of a read in flight at once
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
@@ -77,6 +91,22 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
 #else
 	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(d), "l"(gsrc) : "memory");
 #endif
+}
+// Stages the home bucket of every lane's key (valid lanes; hb = bucket number < 2^32) into dst[slot][lane], with B ADJACENT LANES
+// fetching the B slots of one bucket, so that a bucket is one coalesced request to L2 instead of B 16-byte requests of one lane.
+// Random 32-byte sectors: 43-45 G/s as one request, 27.5 G/s as two (profiles/r2/k4_rrand_sweep.json) -- this is what bounds the
+// probe rounds when the tables live in HBM.  It costs a ballot and B shuffles per 32 buckets, so kernels that are bound by
+// instruction issue with L2-resident tables keep the per-lane form (RunParams::coop_stage).  All 32 lanes must call it.
+template <int B>
+__device__ __forceinline__ void stage_buckets_coop(const uint4* __restrict__ slots, bool valid, uint32_t hb, uint4 (*dst)[32], uint32_t lane) {
+	const uint32_t vm = __ballot_sync(0xffffffffu, valid);
+	const uint32_t q = lane % B;
+#pragma unroll
+	for (int h = 0; h < B; ++h) {
+		const uint32_t src = h * (32 / B) + lane / B;
+		const uint32_t b = __shfl_sync(0xffffffffu, hb, src);
+		if ((vm >> src) & 1u) cp_async16(&dst[q][src], slots + (uint64_t)b * B + q);
+	}
 }
 __device__ __forceinline__ void cp_async_wait_all() {
 	asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
@@ -98,7 +128,7 @@ __device__ __forceinline__ bool table_lookup(const Table& t, uint64_t key, uint3
 		const uint4* bp = t.slots + b * B;
 		uint4 s[B];
 #pragma unroll
-		for (int i = 0; i < B; ++i) s[i] = ldg128(bp + i);
+		for (int i = 0; i < B; i += 2) ldg256(bp + i, s[i], s[i + 1]);
 		bool full = true;
 #pragma unroll
 		for (int i = 0; i < B; ++i) {

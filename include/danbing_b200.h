@@ -341,6 +341,8 @@ int  dbt_batch_stats(dbt_ctx*, int slot, uint64_t stats[4]);
 int  dbt_table_stats(const dbt_ctx*, uint64_t stats[8]);
 int  dbt_graph_merged(const dbt_ctx*);                         /* 1: the graphs are merged into the index entries (one probe round feeds the vote and the threading); 0: no graph / switched off; < 0: refused, -(1 a node is no index key | 2 key of another locus | 4 not in its shared list | 8, 16 a TR k-mer lost its count position to the flank class) */
 uint64_t dbt_graph_table_bytes(const dbt_ctx*);                /* bytes of the graph table in HBM (0 without restored threading) */
+#define DBT_GATHER_COOPERATIVE 0x10000u /* OR into sector_bytes (32 / 64 / 128): sector_bytes/16 adjacent lanes fetch one chunk as ONE coalesced request */
+#define DBT_GATHER_WIDE_LOAD   0x20000u /* OR into sector_bytes = 32: each thread fetches its chunk with one 256-bit load (what the probe functions issue) */
 int  dbt_random_gather_bench(int device, uint64_t table_bytes, uint32_t sector_bytes,
                              uint64_t n_gathers, int iters, float* best_ms); /* R_rand roofline    */
 

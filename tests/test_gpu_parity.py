@@ -105,10 +105,13 @@ def test_gpu_matches_oracle_seeded(k, cth, flank, bucket):
     oracle_vs_gpu(ix, seqs, p)
 
 
+@pytest.mark.parametrize("coop", [False, True], ids=["per-lane-staging", "coalesced-staging"])
 @pytest.mark.parametrize("k,cth,bucket,err", [(21, 45, 2, 0.0), (21, 30, 4, 0.004), (17, 25, 2, 0.002), (25, 40, 2, 0.0), (21, 10, 2, 0.01)])
-def test_gpu_fast_path_matches_oracle(k, cth, bucket, err):
+def test_gpu_fast_path_matches_oracle(k, cth, bucket, err, coop, monkeypatch):
     """production mode (no DBT_F_TRACE): candidate_fast_kernel decides one-locus pairs in closed form and defers the
-    rest to the generic kernel; one-mate pairs sweep the order-dependent band 2*cth <= hits < 3*cth-1"""
+    rest to the generic kernel; one-mate pairs sweep the order-dependent band 2*cth <= hits < 3*cth-1.  Both forms of the bucket
+    staging: per lane (tables in L2) and one coalesced request per bucket (tables far beyond L2, forced here by DBT_COOP_STAGE)"""
+    monkeypatch.setenv("DBT_COOP_STAGE", "1" if coop else "0")
     ix, seqs, _ = synthetic_case(nloci=60, seed=300 + k + cth, k=k, flank=300, npairs=12000, read_seed=cth + 1,
                                  frac_locus=0.35, frac_chimeric=0.15, frac_border=0.1, frac_onemate=0.3, err=err)
     p = abi.default_params(k=k, cth=cth, flags=abi.F_KAM, max_batch_pairs=12288)

@@ -246,7 +246,7 @@ STRESS = [
 ]
 
 
-@pytest.mark.parametrize("merge", [True, False], ids=["graph-in-index", "two-tables"])
+@pytest.mark.parametrize("merge", [True, False, "coop"], ids=["graph-in-index", "two-tables", "graph-in-index-coalesced-staging"])
 @pytest.mark.parametrize("cfg", list(CASES) + STRESS, ids=lambda c: f"s{c.get('seed')}")
 def test_production_mode_records_vs_oracle(cfg, merge, monkeypatch):
     """`-a` without DBT_F_TRACE = the production kernels: with the graphs merged into the index candidate_fast_kernel threads the pairs
@@ -254,6 +254,8 @@ def test_production_mode_records_vs_oracle(cfg, merge, monkeypatch):
     table; both must give the oracle's records (status, locus, alned, CIGAR, annotation) and counts."""
     if not merge:
         monkeypatch.setenv("DBT_NO_GRAPH_MERGE", "1")
+    if merge == "coop":                              # the bucket staging used when the tables are far beyond L2 (stage_buckets_coop)
+        monkeypatch.setenv("DBT_COOP_STAGE", "1")
     gk, pk = split_case(cfg)
     _, ix, seqs, _ = tc.thread_case(write_text=False, frac_bg=0.15, **gk)
     bases, off = rpgg_io.seqs_to_batch(seqs)
