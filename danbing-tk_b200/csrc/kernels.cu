@@ -175,22 +175,59 @@ __global__ void __launch_bounds__(256) subfilter_kernel(DevIndex ix, RunParams r
 	const uint64_t nwords = (sv.npairs + 31) / 32;
 	const bool trace = (rp.flags & DBT_F_TRACE) != 0;
 	const bool filter_on = rp.n_filter && rp.nm_filter;
+	const bool coop2 = rp.n_filter <= 4;                                   // mate 2 by four lanes per pair (the default -kf 4 1 and smaller)
 	uint32_t c_short = 0, c_sub = 0, c_h0 = 0;
 	// a batch the packer flagged (a read longer than max_read_len: dbt_wait reports DBT_E_CAPACITY) must not be counted at all --
 	// the caller rebuilds the context and submits it again: no pair passes, nothing downstream runs on it
 	const bool dead = (sv.ncand[1] & ERR_READ_TOO_LONG) != 0;
 	for (uint64_t w = wid; w < nwords; w += nwarps) {
 		const uint64_t p = w * 32 + lane;
-		bool pass = false;
+		bool pass = false, need2 = false;
+		uint32_t nh = 0; int status = -1; uint16_t m2v = 0;
 		if (p < sv.npairs && !dead) {
 			const uint16_t m1 = sv.meta[0][p], m2 = sv.meta[1][p];
-			uint32_t nh = 0; int status = -1;
 			if ((m1 | m2) & META_NOVALID) { status = DBT_ST_SHORT; ++c_short; }          // cpp:2037
 			else if (filter_on) {
 				bool ok = subfilter_mate<B>(ix, rp, sv.packed[0] + p * rp.lay.W64, m1 & META_LENMASK, nh);
-				if (ok) ok = subfilter_mate<B>(ix, rp, sv.packed[1] + p * rp.lay.W64, m2 & META_LENMASK, nh);
-				if (!ok) { status = DBT_ST_SUBFILTERED; ++c_sub; }
+				if (ok && coop2) need2 = true;                                   // mate 2: by the whole warp, below
+				else {
+					if (ok) ok = subfilter_mate<B>(ix, rp, sv.packed[1] + p * rp.lay.W64, m2 & META_LENMASK, nh);
+					if (!ok) { status = DBT_ST_SUBFILTERED; ++c_sub; }
+				}
 			}
+			m2v = m2;
+		}
+		// ---- mate 2 of the pairs whose mate 1 passed (a few lanes per warp): four lanes per pair, one sampled k-mer each, up to
+		// eight pairs per round -- instead of those lanes running the whole per-thread loop while the rest of the warp waits ----
+		uint32_t pend = __ballot_sync(0xffffffffu, need2);
+		while (pend) {
+			const uint32_t slot = lane >> 2, u = lane & 3u;
+			const uint32_t src = __fns(pend, 0, slot + 1);                       // lane that owns the slot-th pending pair, or 0xffffffff
+			const bool act = src != 0xffffffffu;
+			const uint32_t mm = __shfl_sync(0xffffffffu, (uint32_t)m2v, src & 31u);
+			bool hit = false;
+			if (act && u < rp.n_filter) {
+				const uint32_t L = (mm & META_LENMASK) - rp.k + 1, N = rp.n_filter;
+				const uint32_t idx = (u != N - 1) ? u * (L / (N - 1)) : L - 1;
+				const uint64_t key = canonical_kmer_at(sv.packed[1] + (w * 32 + src) * rp.lay.W64, rp.lay.WB, idx, rp.k);
+				uint32_t v, a2;
+				hit = key != KMER_INVALID && table_lookup<B>(ix.table, key, v, a2);
+			}
+			const uint32_t hm = (__ballot_sync(0xffffffffu, hit) >> (4 * slot)) & 0xFu;
+			// the reference's loop over the N samples of this mate (cpp:174-177): break at the M-th hit, before the header's ++nhash
+			uint32_t h = 0, dnh = 0; bool ok2 = false;
+			for (uint32_t i = 0; i < rp.n_filter; ++i) { h += (hm >> i) & 1u; if (h >= rp.nm_filter) { ok2 = true; break; } ++dnh; }
+			// back to the owner: the r-th pending lane reads slot r
+			const uint32_t r = __popc(pend & ((1u << lane) - 1u));
+			const uint32_t res = __shfl_sync(0xffffffffu, (ok2 ? 0x80000000u : 0u) | dnh, (4 * r) & 31u);
+			if (need2 && r < 8) {
+				need2 = false;
+				nh += res & 0x7FFFFFFFu;
+				if (!(res >> 31)) { status = DBT_ST_SUBFILTERED; ++c_sub; }
+			}
+			for (int q = 0; q < 8 && pend; ++q) pend &= pend - 1;                // the eight lowest pending pairs are done
+		}
+		if (p < sv.npairs && !dead) {
 			c_h0 += nh;
 			pass = status < 0;
 			if (trace) {
