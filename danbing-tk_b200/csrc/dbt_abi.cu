@@ -135,6 +135,7 @@ struct dbt_ctx {
 	DevIndex ix{};
 	// owned device memory of the index
 	uint4* d_gslots = nullptr; uint64_t gtable_bytes = 0, gnodes = 0;   // graph table (restored threading)
+	uint32_t* d_pre = nullptr;                                           // presence bitmap of the index keys (subfilter_kernel)
 	uint4* d_tslots = nullptr; Table ttable{}; bool bubbles = false;    // TR edge table (`-bu`)
 	uint32_t gmerge_err = 0;             // why the merge was refused: 1 node not an index key, 2 key of another locus, 4 not in the shared list, 8/16 TR k-mer without its count position
 	uint4* d_bslots = nullptr;                                           // bait table (`-b`)
@@ -276,7 +277,7 @@ extern "C" void dbt_destroy(dbt_ctx* c) {
 	cudaSetDevice(c->p.device);
 	for (auto& s : c->slot) free_slot(s);
 	if (c->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
-	cudaFree(c->d_gslots); cudaFree(c->d_tslots); cudaFree(c->d_vv_g); cudaFree(c->d_bslots);
+	cudaFree(c->d_gslots); cudaFree(c->d_pre); cudaFree(c->d_tslots); cudaFree(c->d_vv_g); cudaFree(c->d_bslots);
 	cudaFree(c->d_slots); cudaFree(c->d_vv); cudaFree(c->d_vv_aux); cudaFree(c->d_results); cudaFree(c->d_red);
 	cudaFree(c->d_qc); cudaFree(c->d_permtab); cudaFree(c->d_vote_pool); cudaFree(c->d_vote_lock);
 	if (c->h_totals) cudaFreeHost(c->h_totals);
@@ -552,6 +553,17 @@ extern "C" int dbt_load_index(dbt_ctx* c, const dbt_index* in) {
 			CU(cudaMemcpyAsync(dk, in->dbi_keys, in->nk_dbi * 8, cudaMemcpyHostToDevice, st));
 			CU(cudaMemcpyAsync(dv, in->dbi_vals, in->nk_dbi * 4, cudaMemcpyHostToDevice, st));
 			CU(launch_insert(st, B, t, dk, dv, in->nk_dbi, d_err)); ++c->launches;
+			// presence bitmap for subfilter_kernel: >= 30 bits per key, at most 32 MB so that it stays in L2 beside the streamed reads
+			// (a genome-scale index gets none: its bitmap would live in HBM like the table and save nothing).  DBT_PREFILTER=0: off
+			uint32_t pb = 16;
+			while ((1ull << pb) < 30 * in->nk_dbi) ++pb;
+			const char* pe = getenv("DBT_PREFILTER");
+			if ((1ull << pb) / 8 <= (32ull << 20) && !(pe && atoi(pe) == 0)) {
+				TRY(dev_alloc(&c->d_pre, (1ull << pb) / 32, "presence bitmap"));
+				CU(cudaMemsetAsync(c->d_pre, 0, (1ull << pb) / 8, st));
+				CU(launch_prefilter_build(st, dk, in->nk_dbi, c->d_pre, pb)); ++c->launches;
+				c->ix.pre = c->d_pre; c->ix.pre_bits = pb;
+			}
 		}
 		CU(cudaStreamSynchronize(st));
 		cudaFree(dk); cudaFree(dv);

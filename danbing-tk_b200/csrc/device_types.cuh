@@ -33,6 +33,8 @@ struct DevIndex {
 	Table    gtable;            // graphDB of all loci (graph_table.cuh); slots == nullptr when no graph is loaded
 	Table    btable;            // `-b`: bait k-mers of all loci, keyed (k-mer, locus), payload = min << 8 | max (bait.cuh); slots == nullptr: no bait filter
 	const uint32_t* vv_g;       // parallel to vv: graph entry (ten bits, see table.cuh slot_val) of the k-mer in that locus
+	const uint32_t* pre;        // presence bitmap over the index keys (one hash, 2^pre_bits bits, >= 30 bits per key): a clear bit proves a
+	uint32_t pre_bits;          // k-mer absent without touching the table -- subfilter_kernel's probes of background reads.  0: none
 	uint32_t gmerged;           // 1: every graph node is an index key of its locus and every TR k-mer keeps its count position in the
 	                            // index entry -> candidate_fast_kernel threads the pairs itself from the entries it already holds
 };

@@ -150,10 +150,18 @@ __device__ __forceinline__ bool subfilter_mate(const DevIndex& ix, const RunPara
 			key[u] = KMER_INVALID;
 			if (i < N) { uint32_t idx = (i != N - 1) ? i * S : L - 1; key[u] = canonical_kmer_at(rec, rp.lay.WB, idx, rp.k); }
 		}
+		// a clear bit of the presence bitmap (L2-resident: 4 bytes per key against the table's 48) answers the probe of a background
+		// k-mer without a fetch from the table
+		bool maybe[4];
+#pragma unroll
+		for (int u = 0; u < 4; ++u) {
+			maybe[u] = key[u] != KMER_INVALID;
+			if (maybe[u] && ix.pre_bits) { const uint32_t b = pre_bit(key[u], ix.pre_bits); maybe[u] = (__ldg(ix.pre + (b >> 5)) >> (b & 31u)) & 1u; }
+		}
 #pragma unroll
 		for (int u = 0; u < 4; ++u) {
 			uint32_t v, a;
-			hit[u] = (key[u] != KMER_INVALID) && table_lookup<B>(ix.table, key[u], v, a);
+			hit[u] = maybe[u] && table_lookup<B>(ix.table, key[u], v, a);
 		}
 #pragma unroll
 		for (int u = 0; u < 4; ++u) {
@@ -211,7 +219,9 @@ __global__ void __launch_bounds__(256) subfilter_kernel(DevIndex ix, RunParams r
 				const uint32_t idx = (u != N - 1) ? u * (L / (N - 1)) : L - 1;
 				const uint64_t key = canonical_kmer_at(sv.packed[1] + (w * 32 + src) * rp.lay.W64, rp.lay.WB, idx, rp.k);
 				uint32_t v, a2;
-				hit = key != KMER_INVALID && table_lookup<B>(ix.table, key, v, a2);
+				hit = key != KMER_INVALID;
+				if (hit && ix.pre_bits) { const uint32_t b = pre_bit(key, ix.pre_bits); hit = (__ldg(ix.pre + (b >> 5)) >> (b & 31u)) & 1u; }
+				hit = hit && table_lookup<B>(ix.table, key, v, a2);
 			}
 			const uint32_t hm = (__ballot_sync(0xffffffffu, hit) >> (4 * slot)) & 0xFu;
 			// the reference's loop over the N samples of this mate (cpp:174-177): break at the M-th hit, before the header's ++nhash
@@ -467,6 +477,14 @@ __global__ void table_stats_kernel(Table t, unsigned long long* out) {
 	if (used && b >= t.nbuckets) atomicAdd(out + 2, (unsigned long long)used);
 }
 
+// presence bitmap over the index keys (load time)
+__global__ void prefilter_build_kernel(const uint64_t* __restrict__ keys, uint64_t n, uint32_t* __restrict__ bitmap, uint32_t bits) {
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const uint32_t b = pre_bit(keys[i], bits);
+	atomicOr(bitmap + (b >> 5), 1u << (b & 31u));
+}
+
 // R_rand microbenchmark: random aligned gathers of sector_bytes from a big table
 template <int WORDS16>
 __global__ void random_gather_kernel(const uint4* __restrict__ table, uint64_t nchunks, uint64_t ngathers, uint64_t seed, uint32_t* sink) {
@@ -677,6 +695,12 @@ cudaError_t launch_bait_insert(cudaStream_t st, int B, Table t, const uint64_t* 
 
 cudaError_t launch_table_stats(cudaStream_t st, int B, Table t, unsigned long long* out) {
 	DISPATCH_B(B, table_stats_kernel<BB><<<(unsigned)((t.nbuckets + t.nstash + 255) / 256), 256, 0, st>>>(t, out));
+	return cudaGetLastError();
+}
+
+cudaError_t launch_prefilter_build(cudaStream_t st, const uint64_t* keys, uint64_t n, uint32_t* bitmap, uint32_t bits) {
+	if (!n) return cudaSuccess;
+	prefilter_build_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(keys, n, bitmap, bits);
 	return cudaGetLastError();
 }
 

@@ -13,6 +13,7 @@ cudaError_t launch_compact(cudaStream_t st, const SlotView& sv);
 cudaError_t launch_record_emit(cudaStream_t st, int nsm, const uint8_t* records, uint32_t stride, const uint32_t* nslots, uint32_t cap, int emit_failed,
                                uint32_t* mask, uint32_t* blocksum, uint32_t* list, uint32_t* nemit, uint8_t* out);
 cudaError_t launch_candidate(cudaStream_t st, int B, unsigned grid_fast, unsigned grid_slow, const DevIndex& ix, const RunParams& rp, const SlotView& sv, cudaEvent_t mid);
+cudaError_t launch_prefilter_build(cudaStream_t st, const uint64_t* keys, uint64_t n, uint32_t* bitmap, uint32_t bits);   // presence bitmap of the index keys
 cudaError_t launch_insert(cudaStream_t st, int B, Table t, const uint64_t* keys, const uint32_t* vals, uint64_t n, uint32_t* err);
 cudaError_t launch_fill_aux(cudaStream_t st, int B, Table t, const uint32_t* vv, uint32_t* vv_aux, const uint64_t* kmers,
                             const uint32_t* locus_of, uint64_t n, uint32_t cls, uint32_t* err);

@@ -112,6 +112,9 @@ __device__ __forceinline__ void cp_async_wait_all() {
 	asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
 }
 
+// presence bitmap (DevIndex::pre): bit of a key
+__host__ __device__ __forceinline__ uint32_t pre_bit(uint64_t key, uint32_t bits) { return (uint32_t)((key * 0xA24BAED4963EE407ull) >> (64 - bits)); }
+
 // Looks key up. Returns true on hit and sets val/aux. key must be < 2^63 and != invalid.
 // Index value word (slot .z): even = locus << 1 for a k-mer unique to one locus, odd = (offset into vv) << 1 | 1.  When the de Bruijn
 // graphs are merged into the index (dbt_load_index, graph_merge_kernel) the top ten bits of an EVEN value carry the graph entry of

@@ -112,6 +112,7 @@ def test_gpu_fast_path_matches_oracle(k, cth, bucket, err, coop, monkeypatch):
     rest to the generic kernel; one-mate pairs sweep the order-dependent band 2*cth <= hits < 3*cth-1.  Both forms of the bucket
     staging: per lane (tables in L2) and one coalesced request per bucket (tables far beyond L2, forced here by DBT_COOP_STAGE)"""
     monkeypatch.setenv("DBT_COOP_STAGE", "1" if coop else "0")
+    monkeypatch.setenv("DBT_PREFILTER", "0" if coop else "1")      # genome-scale tables also run without subfilter's presence bitmap
     ix, seqs, _ = synthetic_case(nloci=60, seed=300 + k + cth, k=k, flank=300, npairs=12000, read_seed=cth + 1,
                                  frac_locus=0.35, frac_chimeric=0.15, frac_border=0.1, frac_onemate=0.3, err=err)
     p = abi.default_params(k=k, cth=cth, flags=abi.F_KAM, max_batch_pairs=12288)
