@@ -175,8 +175,11 @@ __device__ __forceinline__ bool subfilter_mate(const DevIndex& ix, const RunPara
 	return h >= M;
 }
 
+#ifndef SUBF_MINBLOCKS
+#define SUBF_MINBLOCKS 6       // <= 42 registers, no spills: the kernel waits on dependent loads (meta -> record -> bitmap / bucket), so resident warps count
+#endif
 template <int B>
-__global__ void __launch_bounds__(256) subfilter_kernel(DevIndex ix, RunParams rp, SlotView sv) {
+__global__ void __launch_bounds__(256, SUBF_MINBLOCKS) subfilter_kernel(DevIndex ix, RunParams rp, SlotView sv) {
 	const uint32_t lane = threadIdx.x & 31;
 	const uint64_t nwarps = (uint64_t)gridDim.x * (blockDim.x >> 5);
 	const uint64_t wid = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
