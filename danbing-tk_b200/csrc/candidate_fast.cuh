@@ -101,6 +101,7 @@ __global__ void __launch_bounds__(CAND_FAST_WARPS * 32, CANDF_MINBLOCKS) candida
 		__syncwarp();
 
 		// ---- all canonical k-mers + ONE index probe each (A2 + the look-ups of kfilter, cpp:207/218) ----
+		uint32_t nhit0 = 0, nhit1 = 0;                                     // index hits per mate (warp-uniform)
 #pragma unroll 1
 		for (int m = 0; m < 2; ++m) {
 			const uint32_t nkm = m ? nk1 : nk0;
@@ -178,11 +179,14 @@ if constexpr (COOP) {                                 // tables in HBM: one coal
 				}
 				__syncwarp();
 			}
+			uint32_t hsum = 0;
 #pragma unroll 1
 			for (int j = 0; j < MAXJ; ++j) {
 				const uint32_t hm = __ballot_sync(0xffffffffu, W.aux[m][j * 32 + lane] != AUX_MISS);
 				if (lane == 0) W.hit[m][j] = hm;
+				hsum += __popc(hm);
 			}
+			if (m) nhit1 = hsum; else nhit0 = hsum;
 		}
 		__syncwarp();
 
@@ -197,6 +201,8 @@ if constexpr (COOP) {                                 // tables in HBM: one coal
 				if ((rmm >> m) & 1u) continue;
 				const uint32_t nkm = m ? nk1 : nk0;
 				const uint32_t max_ns = nkm - cth;
+				// the common case first: too few misses (invalid k-mers included) in the whole mate to abort it -- nk probes, nothing to locate
+				if (nkm - (m ? nhit1 : nhit0) <= max_ns) { nhash1 += nkm; if (m) cnt1 = nhit1; else cnt0 = nhit0; continue; }
 				uint32_t cum = 0, probes = nkm, aword = 0, abase = 0, arank = 0, hits = 0; bool aborted = false;
 #pragma unroll 1
 				for (int j = 0; j < MAXJ; ++j) {
