@@ -332,6 +332,9 @@ __device__ __forceinline__ void thrf_finish_pair(const RunParams& rp, const Slot
 			if (!trace) {                                                   // under DBT_F_TRACE the generic candidate kernel left the full header
 				h->pair_index = sv.first_pair_index + p; h->dst0 = dst; h->fc = 0; h->rc = 0; h->nhash0 = 0; h->nhash1 = 0;
 				h->pad[0] = h->pad[1] = h->pad[2] = 0;
+#ifdef DBT_DEBUG_DIRTY
+				h->pad[0] = (uint8_t)(0x80u | (dirty & 3u));      // development aid (tools/dirty_breakdown.py): which mates go on to thread_kernel
+#endif
 #pragma unroll 1
 				for (int m = 0; m < 2; ++m) {
 					dbt_mate_record& o = h->mate[m];
