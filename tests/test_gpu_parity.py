@@ -105,6 +105,20 @@ def test_gpu_matches_oracle_seeded(k, cth, flank, bucket):
     oracle_vs_gpu(ix, seqs, p)
 
 
+@pytest.mark.parametrize("kf", [(2, 1), (3, 2), (4, 2), (4, 4), (6, 2), (8, 3)], ids=lambda x: f"kf{x[0]}-{x[1]}")
+@pytest.mark.parametrize("trace", [True, False], ids=["trace", "production"])
+def test_gpu_subfilter_kf_variants(kf, trace):
+    """`-kf N M` other than the default 4 1: subfilter_kernel's mate-2 phase by four lanes per pair (N <= 4) and by the per-thread
+    loop (N > 4), the break at the M-th hit and the per-pair nhash0 it leaves (compared under DBT_F_TRACE), with and without the
+    presence bitmap's shortcut for background k-mers (reads here are a mix of locus, chimeric, borderline and background pairs)"""
+    ix, seqs, _ = synthetic_case(nloci=40, seed=500 + 10 * kf[0] + kf[1], k=21, flank=300, npairs=6000, read_seed=kf[0] + kf[1],
+                                 frac_locus=0.3, frac_chimeric=0.2, frac_border=0.2, frac_onemate=0.15, err=0.004)
+    p = abi.default_params(k=21, cth=30, n_filter=kf[0], nm_filter=kf[1], flags=abi.F_KAM | (abi.F_TRACE if trace else 0), max_batch_pairs=8192)
+    recs, cnt = oracle_vs_gpu(ix, seqs, p)
+    c = dict(zip(abi.COUNTER_NAMES, cnt.tolist()))
+    assert c["nSubFiltered"] > 1000 and c["nAsgnReads"] > 100
+
+
 @pytest.mark.parametrize("coop", [False, True], ids=["per-lane-staging", "coalesced-staging"])
 @pytest.mark.parametrize("k,cth,bucket,err", [(21, 45, 2, 0.0), (21, 30, 4, 0.004), (17, 25, 2, 0.002), (25, 40, 2, 0.0), (21, 10, 2, 0.01)])
 def test_gpu_fast_path_matches_oracle(k, cth, bucket, err, coop, monkeypatch):
