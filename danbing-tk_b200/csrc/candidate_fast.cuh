@@ -334,11 +334,13 @@ if constexpr (COOP) {                                 // tables in HBM: one coal
 					const uint32_t sh = 2 * lane;
 					const uint64_t kmask = (1ull << (2 * K)) - 1, vmask = (1ull << K) - 1;
 					const int ng = ((int)nkm + 31) >> 5;
-					bool plain = true, anyvalid = false;
+					bool plain = true, anyvalid = false, b2clean = true;
+					uint32_t carry_nb = 0;                              // node bits of position j*32-1 (lane 31 of the previous group)
 					__syncwarp();
 #pragma unroll 1
 					for (int j = 0; j < ng; ++j) {
 						const uint32_t i = j * 32 + lane;
+						uint32_t f3 = 0;
 						const uint64_t wlo = rec[j], whi = (j + 1 < (int)WB) ? rec[j + 1] : 0ull;
 						const uint32_t mlo = mk32[j], mnx = ((uint32_t)(j + 1) < 2 * rp.lay.WM) ? mk32[j + 1] : 0xFFFFFFFFu;
 						const uint64_t wv = sh ? ((wlo >> sh) | (whi << (64 - sh))) : wlo;
@@ -349,6 +351,7 @@ if constexpr (COOP) {                                 // tables in HBM: one coal
 								const uint64_t x = wv & kmask, rcx = (~wv) & kmask, fw = rev2(x) >> (64 - 2 * K);
 								const bool is_rc = rcx < fw;
 								kk = (is_rc ? rcx : fw) | ((fw & 3) << THRF_F3_SHIFT) | (is_rc ? THRF_RCFLAG : 0ull);
+								f3 = (uint32_t)fw & 3u;
 								anyvalid = true;
 								if (i + 1 < nkm && ((wv >> 2) & kmask) == x) plain = false;
 								const uint32_t gg = W.g[m][i], cw = W.aux[m][i];
@@ -358,13 +361,25 @@ if constexpr (COOP) {                                 // tables in HBM: one coal
 							} else plain = false;
 						}
 						A.key[i] = kk; A.nb[i + 1] = (uint16_t)nbv; A.trx[i] = trp;
+						// the B2 pass of thrf_finish_mate, from the registers: every k-mer on an out-edge of its predecessor (the first one a node)?
+						{
+							const uint32_t up = __shfl_up_sync(0xffffffffu, nbv, 1);
+							const uint32_t pb = lane ? up : carry_nb;
+							carry_nb = __shfl_sync(0xffffffffu, nbv, 31);
+							const bool ok = i >= nkm || (i == 0 ? (nbv & 1u) != 0 : ((pb & 1u) && ((pb >> (1 + f3)) & 1u)));
+							const uint32_t bo = __ballot_sync(0xffffffffu, ok);
+							const uint32_t bt = __ballot_sync(0xffffffffu, i < nkm && trp != 0);
+							const uint32_t bp = __ballot_sync(0xffffffffu, i < nkm && (nbv & 1u));
+							if (bo != 0xffffffffu) b2clean = false;
+							if (lane == 0) { A.T[j] = bt; A.ok[j] = bo; A.P[j] = bp; }
+						}
 					}
 					__syncwarp();
 					anyvalid = __any_sync(0xffffffffu, anyvalid);
 					plain = __all_sync(0xffffffffu, plain);
 					if (lane == 0 && anyvalid) t_walk += nkm;
 					if (!plain) { dirty |= 1u << m; continue; }
-					if (!thrf_finish_mate<B, MAXJ>(ix, rp, sv, A, m, len, (int)nkm, dst, recp, slot_ok, false, lane, TC)) dirty |= 1u << m;
+					if (!thrf_finish_mate<B, MAXJ, true>(ix, rp, sv, A, m, len, (int)nkm, dst, recp, slot_ok, false, lane, TC, b2clean)) dirty |= 1u << m;
 				}
 				thrf_finish_pair(rp, sv, c, p, dw, dst, dirty, recp, slot_ok, want_aln, false, lane, t_fea, t_items);
 				__syncwarp();

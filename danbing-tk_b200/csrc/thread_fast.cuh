@@ -67,9 +67,12 @@ __device__ __noinline__ GNode g_lookup_fast_nl(const Table gt, uint64_t fw, uint
 struct ThrfArrays { uint64_t* key; uint32_t* trx; uint16_t* nb; uint32_t* T; uint32_t* ok; uint32_t* P; };
 struct ThrfCount { uint32_t inc = 0, cls = 0, probe = 0, fix = 0, ec = 0; };
 
-template <int B, int MAXJ>
+// HAVE_B2: the caller has already formed the three ballots of the B2 pass (W.T / W.ok / W.P) while it filled the arrays and says
+// whether the mate is clean (candidate_fast_kernel: the values are in registers there, a second pass over shared memory is 8 % of
+// that kernel's instructions)
+template <int B, int MAXJ, bool HAVE_B2 = false>
 __device__ __forceinline__ bool thrf_finish_mate(const DevIndex& ix, const RunParams& rp, const SlotView& sv, const ThrfArrays W, int m, uint32_t len, int nkm, uint32_t dst,
-                                                 uint8_t* rec, bool slot_ok, bool trace, int lane, ThrfCount& C) {
+                                                 uint8_t* rec, bool slot_ok, bool trace, int lane, ThrfCount& C, bool clean_in = true) {
 	const uint32_t K = rp.k;
 	const Table gt = ix.gtable;
 	const uint64_t kmask = (1ull << (2 * K)) - 1;
@@ -78,9 +81,9 @@ __device__ __forceinline__ bool thrf_finish_mate(const DevIndex& ix, const RunPa
 	(void)sv;
 		__syncwarp();
 		// ---- B2: every k-mer on an out-edge of its predecessor, the first one a node? ----
-		bool clean = true;
+		bool clean = clean_in;
 #pragma unroll 1
-		for (int j = 0; j < ng; ++j) {
+		for (int j = 0; j < (HAVE_B2 ? 0 : ng); ++j) {
 			const int i = j * 32 + lane;
 			bool ok = true, tr = false;
 			if (i < nkm) {
