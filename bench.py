@@ -380,6 +380,9 @@ def pred_block(a, workdir, device):
         r = subprocess.run([exe, os.path.join(d, "meta.txt"), os.path.join(d, "ikmer.meta")] + outs, capture_output=True)
         if r.returncode:
             raise RuntimeError(f"{exe} failed: {r.stderr.decode()[-400:]}")
+        ph = [l for l in r.stderr.decode().splitlines() if "phases:" in l]
+        if ph:
+            blk["cli_phases"] = ph[-1].split("phases:", 1)[1].strip()
         return time.perf_counter() - t0, outs
     t_gpu, o_gpu = run(os.path.join(ROOT, "danbing-tk_b200", "bin", "danbing-tk-pred"), "gpu")
     blk["cli_wall_s"] = t_gpu

@@ -219,6 +219,7 @@ def load_library(path=LIB_PATH):
     L.dbt_table_stats.argtypes = [ctxp, u64p]
     L.dbt_batch_stats.argtypes = [ctxp, C.c_int, u64p]
     L.dbt_random_gather_bench.argtypes = [C.c_int, C.c_uint64, C.c_uint32, C.c_uint64, C.c_int, C.POINTER(C.c_float)]
+    L.dbt_init_device.argtypes = [C.c_int]
     L.dbt_pred.argtypes = [C.c_int, C.POINTER(PredInput), C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float)]
     L.dbt_noalloc_scratch_needed.argtypes = [C.c_uint32, C.c_uint64, C.c_uint64]
     L.dbt_noalloc_scratch_needed.restype = C.c_size_t
@@ -239,7 +240,7 @@ ABI_SYMBOLS = ["dbt_graph_merged", "dbt_bubble_events", "dbt_prepare", "dbt_uplo
                "dbt_submit", "dbt_wait", "dbt_download", "dbt_reset_counts", "dbt_nk_tr", "dbt_nloci",
                "dbt_record_stride", "dbt_record_as_stride", "dbt_record_aln_stride", "dbt_record_es_cap", "dbt_nccl_unique_id", "dbt_comm_init", "dbt_allreduce",
                "dbt_timer_start", "dbt_timer_stop", "dbt_kernel_times", "dbt_launch_count", "dbt_table_stats", "dbt_graph_table_bytes", "dbt_batch_stats",
-               "dbt_random_gather_bench", "dbt_pred", "dbt_noalloc_scratch_needed", "dbt_pack_reads_device_noalloc", "dbt_bus_bench", "dbt_host_alloc", "dbt_host_free", "dbt_packed_bytes", "dbt_pack_reads"]
+               "dbt_random_gather_bench", "dbt_init_device", "dbt_pred", "dbt_noalloc_scratch_needed", "dbt_pack_reads_device_noalloc", "dbt_bus_bench", "dbt_host_alloc", "dbt_host_free", "dbt_packed_bytes", "dbt_pack_reads"]
 
 
 class DbtError(RuntimeError):

@@ -1164,6 +1164,12 @@ extern "C" int dbt_random_gather_bench(int device, uint64_t table_bytes, uint32_
 	return DBT_OK;
 }
 
+extern "C" int dbt_init_device(int device) {
+	CU(cudaSetDevice(device));
+	CU(cudaFree(nullptr));
+	return DBT_OK;
+}
+
 extern "C" int dbt_bus_bench(int device, uint64_t bytes, int iters, float* h2d_ms, float* d2h_ms) {
 	if (!h2d_ms || !d2h_ms || !bytes) return fail(DBT_E_BADARG, "null argument");
 	CU(cudaSetDevice(device));

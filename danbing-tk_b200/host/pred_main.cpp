@@ -17,7 +17,9 @@
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
+#include <algorithm>
 #include <memory>
+#include <thread>
 #include <string>
 #include <vector>
 #include "danbing_b200.h"
@@ -68,6 +70,13 @@ int main(int argc, char** argv) {
 		else { fprintf(stderr, "danbing-tk-pred: unsupported option %s (the reference's developer switch -f does nothing there either)\n", argv[argi]); return 1; }
 	}
 	if (argc - argi != 5) { fprintf(stderr, "danbing-tk-pred: expected 5 file arguments\n"); return 1; }
+	// the CUDA context (about half a second) comes up on a helper thread while the inputs are parsed and mapped
+	const auto tstart = std::chrono::steady_clock::now();
+	auto since = [&](std::chrono::steady_clock::time_point a) { return std::chrono::duration<double>(std::chrono::steady_clock::now() - a).count(); };
+	double t_parse = 0, t_initwait = 0, t_alloc = 0, t_pred = 0, t_write = 0;
+	int init_rc = 0;
+	std::thread warm([&] { init_rc = dbt_init_device(device); });
+	struct Joiner { std::thread& t; ~Joiner() { if (t.joinable()) t.join(); } } warm_guard{warm};
 	const std::string finGtMeta = argv[argi], finIkMeta = argv[argi + 1], foutRaw = argv[argi + 2], fout = argv[argi + 3], foutBias = argv[argi + 4];
 	printf("metadata of *.trkmc.ar: %s\ninvariant kmers: %s\nraw genotype matrix will be written to: %s\n"
 	       "bias-corrected genotype matrix will be written to: %s\nbias matrix will be written to: %s\n",
@@ -115,9 +124,30 @@ int main(int argc, char** argv) {
 		kmc[s] = reinterpret_cast<const uint64_t*>(static_cast<const uint8_t*>(maps[s].p) + 8);
 	}
 
-	std::unique_ptr<float[]> raw_mem(new float[(size_t)ns * nk]), cor_mem(new float[(size_t)ns * nk]);   // filled entirely by dbt_pred: not zeroed first
+	// result buffers: pageable, but touched by a few threads while the CUDA context is still coming up, so that the device-to-host
+	// copies land in pages that exist (pinning 2 x ns*nk*4 bytes instead costs 0.3 s per 0.8 GB, more than the copies themselves)
+	const size_t nelem = (size_t)ns * nk;
+	std::unique_ptr<float[]> raw_mem(new float[nelem]), cor_mem(new float[nelem]);
+	{
+		std::vector<std::thread> th;
+		const unsigned nt = std::max(1u, std::min(8u, std::thread::hardware_concurrency()));
+		for (unsigned i = 0; i < nt; ++i) th.emplace_back([&, i] {
+			for (float* base : {raw_mem.get(), cor_mem.get()}) {
+				char* b = reinterpret_cast<char*>(base);
+				const size_t bytes = nelem * 4, lo = bytes * i / nt, hi = bytes * (i + 1) / nt;
+				for (size_t o = lo; o < hi; o += 4096) b[o] = 0;
+			}
+		});
+		for (auto& t : th) t.join();
+	}
+	t_parse = since(tstart);
+	auto tp = std::chrono::steady_clock::now();
+	warm.join();
+	t_initwait = since(tp); tp = std::chrono::steady_clock::now();
+	if (init_rc) { fprintf(stderr, "danbing-tk-pred: %s: %s\n", dbt_strerror(init_rc), dbt_last_error()); return 1; }
 	struct { float* p; float* data() { return p; } } raw{raw_mem.get()}, cor{cor_mem.get()};
 	std::vector<float> bias((size_t)ns * n_tr, 0.f);
+	t_alloc = since(tp); tp = std::chrono::steady_clock::now();
 	dbt_pred_input in{};
 	in.ns = ns; in.nk = nk; in.n_tr = n_tr; in.n_ik = n_ik; in.kmc = kmc.data(); in.rd = rds.data();
 	in.nk_cum = nk_cum.data(); in.nik_cum = nik_cum.data(); in.iki = iki.data(); in.ikmc = ikmc.data();
@@ -125,15 +155,17 @@ int main(int argc, char** argv) {
 	printf("normalizaing read depth\ncomputing/correcting bias\n");
 	const int rc = dbt_pred(device, &in, raw.data(), cor.data(), bias.data(), kms);
 	if (rc) { fprintf(stderr, "danbing-tk-pred: %s: %s\n", dbt_strerror(rc), dbt_last_error()); return 1; }
+	t_pred = since(tp); tp = std::chrono::steady_clock::now();
 	const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 	fprintf(stderr, "[danbing-tk-pred] GPU %d: %llu samples x %llu k-mers, %llu loci: normalise %.3f ms, bias correction %.3f ms (kernels); read + compute %.3f s\n",
 	        device, (unsigned long long)ns, (unsigned long long)nk, (unsigned long long)n_tr, kms[0], kms[1], sec);
 
-	printf("saving matrix to %s\n", foutRaw.c_str());
-	if (!write_matrix(foutRaw, raw.data(), ns, nk)) { fprintf(stderr, "danbing-tk-pred: cannot write %s\n", foutRaw.c_str()); return 1; }
-	printf("saving matrix to %s\n", fout.c_str());
-	if (!write_matrix(fout, cor.data(), ns, nk)) { fprintf(stderr, "danbing-tk-pred: cannot write %s\n", fout.c_str()); return 1; }
-	printf("saving matrix to %s\n", foutBias.c_str());
+	// the three outputs are written side by side: two threads stream the matrices out while this one formats the bias table
+	printf("saving matrix to %s\nsaving matrix to %s\nsaving matrix to %s\n", foutRaw.c_str(), fout.c_str(), foutBias.c_str());
+	bool ok_raw = false, ok_cor = false;
+	std::thread w_raw([&] { ok_raw = write_matrix(foutRaw, raw.data(), ns, nk); });
+	std::thread w_cor([&] { ok_cor = write_matrix(fout, cor.data(), ns, nk); });
+	struct Join2 { std::thread &a, &b; ~Join2() { if (a.joinable()) a.join(); if (b.joinable()) b.join(); } } wguard{w_raw, w_cor};
 	{	// Eigen's operator<< with StreamPrecision: every coefficient through an ostream at its default precision (6 significant digits, %g)
 		std::string out;
 		out.reserve((size_t)ns * n_tr * 10);
@@ -148,5 +180,11 @@ int main(int argc, char** argv) {
 		FILE* f = fopen(foutBias.c_str(), "wb");
 		if (!f || fwrite(out.data(), 1, out.size(), f) != out.size() || fclose(f) != 0) { fprintf(stderr, "danbing-tk-pred: cannot write %s\n", foutBias.c_str()); return 1; }
 	}
+	w_raw.join(); w_cor.join();
+	if (!ok_raw) { fprintf(stderr, "danbing-tk-pred: cannot write %s\n", foutRaw.c_str()); return 1; }
+	if (!ok_cor) { fprintf(stderr, "danbing-tk-pred: cannot write %s\n", fout.c_str()); return 1; }
+	t_write = since(tp);
+	fprintf(stderr, "[danbing-tk-pred] phases: parse+map+touch buffers %.3f s, wait for the CUDA context %.3f s, dbt_pred %.3f s, write %.3f s, total %.3f s\n",
+	        t_parse, t_initwait, t_alloc + t_pred, t_write, since(tstart));
 	return 0;
 }

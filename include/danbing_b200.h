@@ -384,6 +384,10 @@ int  dbt_pack_reads_device_noalloc(int device, uint32_t k, uint32_t max_read_len
    copies of `bytes`, and the same for device -> host */
 int  dbt_bus_bench(int device, uint64_t bytes, int iters, float* h2d_ms, float* d2h_ms);
 
+/* Creates the CUDA context of `device` (nothing else), so that a later dbt_create / dbt_pred does not pay for it: meant to be
+   called from a helper thread while the host parses its inputs (bin/danbing-tk-pred does). */
+int  dbt_init_device(int device);
+
 /* ---- host helpers --------------------------------------------------------------------------- */
 void* dbt_host_alloc(size_t bytes);                           /* pinned */
 void  dbt_host_free(void*);
