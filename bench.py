@@ -544,6 +544,7 @@ def per_locus_multiset_equal(ix, a, b):
 
 
 _numa_bound = False
+_numa_info = {"bound_to_gpu_local_cpus": False}
 
 
 def bind_to_gpu_numa_node(local):
@@ -558,7 +559,9 @@ def bind_to_gpu_numa_node(local):
         pynvml.nvmlInit()
         h = pynvml.nvmlDeviceGetHandleByIndex(local)
         pynvml.nvmlDeviceSetCpuAffinity(h)
-        log(f"[bench] rank-local GPU {local}: bound to {len(os.sched_getaffinity(0))} NUMA-local CPUs")
+        cpus = sorted(os.sched_getaffinity(0))
+        _numa_info.update({"bound_to_gpu_local_cpus": True, "ncpus": len(cpus), "cpus": f"{cpus[0]}-{cpus[-1]}" if cpus else ""})
+        log(f"[bench] rank-local GPU {local}: bound to {len(cpus)} NUMA-local CPUs")
     except Exception as e:                                    # affinity is an optimisation only
         log(f"[bench] NUMA binding skipped: {e}")
 
@@ -1068,6 +1071,7 @@ def b200_mode(mode, a, ix, pref, pool, hap_off, workdir, rank, world, local, dis
            "warmup": a.warmup, "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
            "dtype": "u64", "data": "synthetic", "config": config, "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches,
            "roofline": roofline, "cpu_baseline": cpu,
+           "host_binding_rank0": dict(_numa_info, ncpus_in_affinity_mask=len(os.sched_getaffinity(0))),
            "timing": {"device_events_ms_per_step": step_ms, "host_wall_ms_per_step": wall_step_ms,
                       "note": "value uses the CUDA-event time at every N (max over ranks); at N > 1 a step ends with the host-synchronous NCCL reduce"},
            "multi_gpu_parity": mgp,
