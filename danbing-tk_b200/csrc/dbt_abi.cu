@@ -863,6 +863,7 @@ extern "C" int dbt_upload_raw(dbt_ctx* c, const dbt_raw_batch* b, dbt_raw_info* 
 	RawView v{};
 	v.raw = s.d_raw; v.nlmask = s.d_nlmask; v.blocksum = s.d_rblocksum; v.nl = s.d_nl; v.hdr = s.d_rhdr; v.hash = s.d_rhash; v.tlen = s.d_tlen; v.slen = s.d_slen; v.eq = s.d_eq;
 	v.pairmask = s.d_pairmask; v.singlemask = s.d_singlemask; v.pairlist = s.d_pairlist; v.singlelist = s.d_singlelist;
+	v.check_qual = (b->is_fastq && (c->p.flags & DBT_F_BAIT)) ? 1u : 0u;
 	v.rstart = s.d_rstart; v.rend = s.d_rend; v.rqual = s.d_rqual; v.pairoff = s.d_pairoff; v.pairhash = s.d_pairhash; v.singleoff = s.d_singleoff;
 	v.max_lines = s.raw_max_lines; v.max_recs = s.raw_max_recs; v.max_pairs = c->p.max_batch_pairs; v.max_single = std::min(s.raw_max_single, b->single_cap);
 	if (b->is_fastq && (c->p.flags & DBT_F_BAIT)) { s.q_base = s.d_raw; s.q_off = s.d_rqual; }

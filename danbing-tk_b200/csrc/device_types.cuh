@@ -90,6 +90,8 @@ struct RawView {
 	uint32_t* pairmask; uint32_t* singlemask; uint32_t* pairlist; uint32_t* singlelist;
 	uint64_t* rstart; uint64_t* rend;                                   // per read of the pairs formed: [start, end) of the sequence in raw
 	uint64_t* rqual;                                                    // ... and, FASTQ, the start of its quality line
+	uint32_t check_qual;                                                // the quality strings will be read per base (`-b`): a record whose quality line is not
+	                                                                    // as long as its sequence sends the chunk to the host pairer, which refuses it by name
 	uint32_t* pairoff; uint64_t* pairhash; uint32_t* singleoff;
 	uint32_t max_lines, max_recs, max_pairs, max_single;
 };

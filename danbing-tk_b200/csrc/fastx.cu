@@ -104,14 +104,18 @@ __global__ void __launch_bounds__(256) rec_class_kernel(uint32_t* hdr, const uin
 __global__ void __launch_bounds__(256) pair_fill_kernel(const uint32_t* __restrict__ nl, uint32_t* __restrict__ hdr, uint32_t L, const uint32_t* __restrict__ pairlist,
                                                        const uint32_t* __restrict__ singlelist, const uint64_t* __restrict__ hash, uint32_t max_pairs, uint32_t max_single,
                                                        uint64_t* __restrict__ rstart, uint64_t* __restrict__ rend, uint64_t* __restrict__ rqual, uint32_t* __restrict__ pairoff,
-                                                       uint64_t* __restrict__ pairhash, uint32_t* __restrict__ singleoff) {
+                                                       uint64_t* __restrict__ pairhash, uint32_t* __restrict__ singleoff, uint32_t check_qual) {
 	const uint32_t np = hdr[2], ns = hdr[3];
 	if (blockIdx.x == 0 && threadIdx.x == 0 && (np > max_pairs || ns > max_single)) atomicOr(hdr + 5, DBT_RAW_OVERFLOW);
 	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < min(np, max_pairs); i += gridDim.x * blockDim.x) {
 		const uint32_t r = pairlist[i];                              // the late mate; its partner is record r - 1
 		rstart[2 * i] = (uint64_t)nl[L * r] + 1;           rend[2 * i] = nl[L * r + 1];
 		rstart[2 * i + 1] = (uint64_t)nl[L * (r - 1)] + 1; rend[2 * i + 1] = nl[L * (r - 1) + 1];
-		if (L == 4) { rqual[2 * i] = (uint64_t)nl[L * r + 2] + 1; rqual[2 * i + 1] = (uint64_t)nl[L * (r - 1) + 2] + 1; }
+		if (L == 4) {
+			rqual[2 * i] = (uint64_t)nl[L * r + 2] + 1; rqual[2 * i + 1] = (uint64_t)nl[L * (r - 1) + 2] + 1;
+			if (check_qual && (nl[L * r + 3] - nl[L * r + 2] != nl[L * r + 1] - nl[L * r] || nl[L * (r - 1) + 3] - nl[L * (r - 1) + 2] != nl[L * (r - 1) + 1] - nl[L * (r - 1)]))
+				atomicOr(hdr + 5, DBT_RAW_SLOWPATH);                     // one phred score per base or the chunk is the host's
+		}
 		pairoff[i] = r >= 2 ? nl[L * (r - 1) - 1] + 1 : 0;
 		pairhash[i] = hash[r];
 	}
@@ -135,7 +139,7 @@ cudaError_t launch_fastx_split(cudaStream_t st, int nsm, const RawView& v, uint6
 	if (e != cudaSuccess) return e;
 	e = launch_compact_bits(st, v.singlemask, v.max_recs, v.blocksum, v.singlelist, v.hdr + 3, v.max_recs);
 	if (e != cudaSuccess) return e;
-	pair_fill_kernel<<<g, 256, 0, st>>>(v.nl, v.hdr, L, v.pairlist, v.singlelist, v.hash, v.max_pairs, v.max_single, v.rstart, v.rend, v.rqual, v.pairoff, v.pairhash, v.singleoff);
+	pair_fill_kernel<<<g, 256, 0, st>>>(v.nl, v.hdr, L, v.pairlist, v.singlelist, v.hash, v.max_pairs, v.max_single, v.rstart, v.rend, v.rqual, v.pairoff, v.pairhash, v.singleoff, v.check_qual);
 	return cudaGetLastError();
 }
 

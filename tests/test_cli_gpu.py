@@ -366,6 +366,15 @@ def test_cli_vs_reference_live_bait_filter(track, is_fastq, tmp_path):
             btk = open(tmp_path / "ref.btk.kmdb", "rb").read()
             assert open(tmp_path / "gpu.btk.kmdb", "rb").read() == btk
             assert int(np.frombuffer(btk, "<u8", 1, 8 + 8 * nloci)[0]) >= 5
+    if is_fastq and not track:
+        # one phred score per base: a record whose quality line is shorter than its sequence is refused by name, with either reader
+        lines = open(fa).read().split("\n")
+        lines[4 * 777 + 3] = lines[4 * 777 + 3][:-7]
+        bad = tmp_path / "reads_badq.fq"
+        open(bad, "w").write("\n".join(lines))
+        for extra in ([], ["--host-reader"]):
+            r = subprocess.run([CLI, *map(str, args[:-1] + [bad] + extra + ["-o", tmp_path / "bad"])], capture_output=True, cwd=tmp_path)
+            assert r.returncode != 0 and b"quality string is not as long as its sequence" in r.stderr, r.stderr[-500:]
 
 
 def test_cli_gzip_input_and_stdin(tmp_path):
