@@ -7,4 +7,4 @@ name=$1; shift
 mkdir -p build/var
 nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-Wall,-Wno-unused-function -cudart static "$@" -Xptxas -v -c csrc/kernels.cu -o build/var/kernels_$name.o 2> build/var/kernels_$name.ptxas
 grep -A2 "candidate_fast_kernelILi2ELi5" build/var/kernels_$name.ptxas | grep -E "spill|registers" | head -2
-nvcc -gencode arch=compute_100a,code=sm_100a -shared -cudart static -o build/var/lib_$name.so build/var/kernels_$name.o build/fastx.o build/bubbles.o build/thread.o build/dbt_abi.o build/host_pack.o -ldl -lpthread
+nvcc -gencode arch=compute_100a,code=sm_100a -shared -cudart static -o build/var/lib_$name.so build/var/kernels_$name.o build/fastx.o build/bubbles.o build/thread.o build/dbt_abi.o build/noalloc.o build/pred.o build/host_pack.o -ldl -lpthread
