@@ -178,3 +178,18 @@ def test_device_packer_body_matches_host_packer(tmp_path):
     ncase, nnovalid, nfast = map(int, out.stdout.split()[1:4])
     assert ncase >= 50000 and 1000 < nnovalid < ncase - 1000
     assert 5000 < nfast < ncase - 5000            # reads the fast (clean-read) path packed itself; it refused exactly the others
+
+
+def test_header_constants_match_the_python_mirror():
+    """every DBT_F_ / DBT_ST_ / DBT_MF_ / DBT_LAYOUT_ / DBT_RAW_ constant of include/danbing_b200.h against danbing-tk_b200/abi.py"""
+    hdr = open(os.path.join(ROOT, "include", "danbing_b200.h")).read()
+    defs = {m.group(1): int(m.group(2), 0) for m in re.finditer(r"#define\s+DBT_((?:F|ST|MF|LAYOUT|RAW)_[A-Z0-9_]+)\s+(0x[0-9a-fA-F]+|\d+)u?\b", hdr)}
+    assert len(defs) >= 30
+    checked = 0
+    for name, val in defs.items():
+        if hasattr(abi, name):
+            assert getattr(abi, name) == val, name
+            checked += 1
+    assert checked >= 25                                  # the mirror carries (nearly) all of them
+    for must in ("F_KAM", "F_BAIT", "F_EXTRACT", "ST_COUNTED", "ST_THREAD_FAILED", "MF_BF", "LAYOUT_PACKED", "RAW_SLOWPATH"):
+        assert must in defs and hasattr(abi, must), must
